@@ -1,0 +1,417 @@
+// ekf_capi.cu -- C ABI (include/ekfslam_b200.h) over the sm_100a kernels.  No CPU fallback: every entry point
+// that computes enqueues CUDA kernels on the handle's stream; without a device ekf_create fails.
+#include "../../include/ekfslam_b200.h"
+#include "ekf_kernels.h"
+#include "ekf_device.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace ekf;
+
+struct ekf_handle {
+    ekf_params p;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int N = 0;                 // landmarks in the state (host-tracked; appends are host-driven)
+    int cap_n = 0;             // 3 + 2*capacity
+    int64_t ld = 0;            // leading dimension of P (multiple of 16)
+    double* P = nullptr;
+    double* x = nullptr;
+    double* s = nullptr;
+    double2* Kd = nullptr;
+    double2* Bd = nullptr;
+    Lin* lin = nullptr;
+    void* partial = nullptr;
+    unsigned int* ticket = nullptr;
+    AssocResult* d_res = nullptr;
+    AssocResult* h_res = nullptr;   // pinned
+    bool prof = false;
+    std::vector<cudaEvent_t> ev;
+    size_t ev_used = 0;
+    double dd_ms = 0.0;
+    int64_t dd_launches = 0;
+    int64_t launches = 0;
+    std::string err;
+};
+
+static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
+    if (h) h->err = msg;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(h, EKF_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e__));        \
+    } while (0)
+#define CKH(h)                                                                                     \
+    do { if (!(h)) return EKF_EINVAL; } while (0)
+
+static inline int n_of(const ekf_handle* h) { return 3 + 2 * h->N; }
+static inline int sym_of(const ekf_handle* h) { return h->p.storage == EKF_STORAGE_SYM ? 1 : 0; }
+
+extern "C" const char* ekf_version(void) { return "ekfslam_b200 0.1 (sm_100a)"; }
+
+extern "C" int32_t ekf_params_default(ekf_params* p, int32_t variant) {
+    if (!p) return EKF_EINVAL;
+    memset(p, 0, sizeof(*p));
+    p->C = 0.2;                                         // EKF_SLAM.m:12
+    p->Rc[0] = (variant == EKF_VARIANT_UC) ? 0.1 : 0.01;   // EKF_SLAM_UC.m:13 / EKF_SLAM.m:13
+    p->Rc[1] = 5.0;
+    p->s_cost = 0.00000000001;                          // EKF_SLAM.m:14, EKF_SLAM_UC.m:16
+    p->s_thresh = 1000000000.0;                         // EKF_SLAM.m:16
+    p->variant = variant;
+    p->assoc_mode = EKF_ASSOC_SIGNATURE;                // Correspondence.m:75
+    p->storage = EKF_STORAGE_FULL;
+    p->capacity_landmarks = 1024;
+    p->device = 0;
+    p->defer_m = 0;
+    p->stream = 0;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_destroy(ekf_handle* h) {
+    if (!h) return EKF_OK;
+    cudaSetDevice(h->p.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (auto e : h->ev) cudaEventDestroy(e);
+    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd);
+    cudaFree(h->lin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
+    if (h->h_res) cudaFreeHost(h->h_res);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return EKF_OK;
+}
+
+static int32_t init_state(ekf_handle* h) {
+    // x = [0 0 0], P = 0.1*eye(3), s = []   (EKF_SLAM.m:28-31)
+    CK(cudaMemsetAsync(h->P, 0, sizeof(double) * h->ld * h->cap_n, h->stream));
+    CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
+    CK(cudaMemsetAsync(h->s, 0, sizeof(double) * (h->p.capacity_landmarks + 1), h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld, h->stream));
+    CK(cudaMemsetAsync(h->Bd, 0, sizeof(double2) * h->ld, h->stream));
+    const double d = 0.1;
+    for (int i = 0; i < 3; ++i)
+        CK(cudaMemcpyAsync(h->P + i + i * h->ld, &d, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->N = 0;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
+    if (!p || !out || p->capacity_landmarks < 1) return EKF_EINVAL;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= p->device) {
+        fprintf(stderr, "ekfslam_b200: no CUDA device %d (this library has no CPU fallback)\n", p->device);
+        return EKF_ECUDA;
+    }
+    ekf_handle* h = new ekf_handle();
+    h->p = *p;
+    if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) g_downdate_variant = atoi(v);
+    int32_t rc = [&]() -> int32_t {
+        CK(cudaSetDevice(p->device));
+        if (p->stream) { h->stream = (cudaStream_t)(uintptr_t)p->stream; }
+        else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
+        h->cap_n = 3 + 2 * p->capacity_landmarks;
+        h->ld = ((int64_t)h->cap_n + 15) / 16 * 16;
+        CK(cudaMalloc(&h->P, sizeof(double) * h->ld * h->cap_n));
+        CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
+        CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
+        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld));
+        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld));
+        CK(cudaMalloc(&h->lin, sizeof(Lin)));
+        CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
+        CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
+        CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
+        CK(cudaMalloc(&h->d_res, sizeof(AssocResult)));
+        CK(cudaMallocHost(&h->h_res, sizeof(AssocResult)));
+        return init_state(h);
+    }();
+    if (rc != EKF_OK) {
+        fprintf(stderr, "ekfslam_b200: ekf_create failed: %s\n", h->err.c_str());
+        ekf_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return EKF_OK;
+}
+
+extern "C" const char* ekf_last_error(ekf_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" int32_t ekf_sync(ekf_handle* h) {
+    CKH(h);
+    CK(cudaStreamSynchronize(h->stream));
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N) {
+    CKH(h);
+    if (!N) return fail(h, EKF_EINVAL, "N is null");
+    *N = h->N;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh) {
+    CKH(h);
+    h->p.C = C; h->p.Rc[0] = Rc[0]; h->p.Rc[1] = Rc[1]; h->p.s_cost = s_cost; h->p.s_thresh = s_thresh;
+    return EKF_OK;
+}
+
+// ---------------------------------------------------------------- predict / update / append / associate
+extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
+    CKH(h);
+    if (!u) return fail(h, EKF_EINVAL, "u is null");
+    CK(cudaSetDevice(h->p.device));
+    launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+    h->launches += 2;
+    CK(cudaGetLastError());
+    return EKF_OK;
+}
+
+static int32_t downdate(ekf_handle* h) {
+    if (h->prof) {
+        if (h->ev_used + 2 > h->ev.size()) {
+            size_t old = h->ev.size();
+            h->ev.resize(old + 512);
+            for (size_t i = old; i < h->ev.size(); ++i) CK(cudaEventCreate(&h->ev[i]));
+        }
+        CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
+    }
+    launch_downdate(h->stream, h->P, h->ld, n_of(h), sym_of(h), h->Kd, h->Bd);
+    if (h->prof) {
+        CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
+        h->ev_used += 2;
+    }
+    h->dd_launches += 1;
+    h->launches += 1;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdiag[2], int32_t idx1) {
+    CKH(h);
+    if (!z || !Rdiag) return fail(h, EKF_EINVAL, "null argument");
+    if (idx1 < 1 || idx1 > h->N)      // MATLAB would raise "index exceeds array bounds" at EKF_SLAM.m:125
+        return fail(h, EKF_EINVAL, "ekf_update: landmark index " + std::to_string(idx1) + " outside 1.." + std::to_string(h->N));
+    CK(cudaSetDevice(h->p.device));
+    const int a = 3 + 2 * (idx1 - 1);
+    launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
+                          h->lin, h->Kd, h->Bd);
+    h->launches += 2;
+    int32_t rc = downdate(h);
+    if (rc != EKF_OK) return rc;
+    CK(cudaGetLastError());
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdiag[2], const double pos[2],
+                              double signature) {
+    CKH(h);
+    if (!u || !Rdiag || !pos) return fail(h, EKF_EINVAL, "null argument");
+    if (h->N >= h->p.capacity_landmarks)
+        return fail(h, EKF_ECAPACITY, "ekf_append: capacity_landmarks=" + std::to_string(h->p.capacity_landmarks) + " reached");
+    CK(cudaSetDevice(h->p.device));
+    launch_append(h->stream, h->P, h->ld, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1], pos[0], pos[1],
+                  signature, sym_of(h));
+    h->launches += 1;
+    CK(cudaGetLastError());
+    h->N += 1;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double Rdiag[2], int32_t* newLL,
+                                 int32_t* idx1) {
+    CKH(h);
+    if (!z || !Rdiag || !newLL || !idx1) return fail(h, EKF_EINVAL, "null argument");
+    if (h->N == 0) { *newLL = 1; *idx1 = 1; return EKF_OK; }   // Correspondence.m:33,40 with an empty loop
+    CK(cudaSetDevice(h->p.device));
+    launch_associate(h->stream, h->P, h->ld, h->x, h->s, h->N, z[0], z[1], z[2], Rdiag[0], Rdiag[1],
+                     h->p.s_cost, h->p.s_thresh, h->p.assoc_mode, sym_of(h), h->partial, h->ticket, h->d_res);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *newLL = h->h_res->newLL;
+    *idx1 = h->h_res->index1;
+    return EKF_OK;
+}
+
+// measure() control flow, EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151 (host-driven in this revision).
+extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k, const double u[2],
+                                     const double* loc_table, const int32_t* index_table, int32_t n_table,
+                                     int32_t* action_out) {
+    CKH(h);
+    if (k < 0 || (k > 0 && !obs) || !u) return fail(h, EKF_EINVAL, "null argument");
+    auto loc_by_index = [&](double want, double pos[2]) -> bool {          // find([..index]==want), first hit
+        for (int i = 0; i < n_table; ++i)
+            if ((double)index_table[i] == want) { pos[0] = loc_table[i]; pos[1] = loc_table[i + n_table]; return true; }
+        return false;
+    };
+    for (int ii = 1; ii <= k; ++ii) {                                      // :107
+        const double z[3] = {obs[ii - 1], obs[ii - 1 + k], obs[ii - 1 + 2 * k]};
+        const double Rd[2] = {z[0] * h->p.Rc[0], z[1] * h->p.Rc[1]};       // :108
+        double pos[2];
+        int32_t rc, act;
+        if (h->N == 0) {                                                   // :110  length(x) < 4
+            bool ok = false;                                               // find([..index]) -> first non-zero index (F15)
+            for (int i = 0; i < n_table && !ok; ++i)
+                if (index_table[i] != 0) { pos[0] = loc_table[i]; pos[1] = loc_table[i + n_table]; ok = true; }
+            if (!ok) return fail(h, EKF_EINVAL, "measure: no indexed landmark in the table (EKF_SLAM.m:111)");
+            rc = ekf_append(h, u, Rd, pos, 1.0);                           // :111
+            act = -1;
+        } else if (h->p.variant == EKF_VARIANT_KNOWN) {
+            if (z[2] > (double)h->N) {                                     // :118
+                if (!loc_by_index(z[2], pos)) return fail(h, EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM.m:120)");
+                rc = ekf_append(h, u, Rd, pos, z[2]);                      // :120
+                act = -(int32_t)z[2];
+            } else {
+                rc = ekf_update(h, z, Rd, ii);                             // :123  idx = ii (row number)
+                act = ii;
+            }
+        } else {
+            int32_t newLL = 0, idx = 0;
+            rc = ekf_associate(h, z, Rd, &newLL, &idx);                    // EKF_SLAM_UC.m:119
+            if (rc != EKF_OK) return rc;
+            if (newLL) {                                                   // :121
+                if (!loc_by_index((double)idx, pos)) return fail(h, EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM_UC.m:123)");
+                rc = ekf_append(h, u, Rd, pos, (double)idx);               // :123
+                act = -idx;
+            } else {
+                rc = ekf_update(h, z, Rd, idx);                            // :125-146
+                act = idx;
+            }
+        }
+        if (rc != EKF_OK) return rc;
+        if (action_out) action_out[ii - 1] = act;
+    }
+    return EKF_OK;
+}
+
+// ---------------------------------------------------------------- state access
+extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
+    CKH(h);
+    if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len) {
+    CKH(h);
+    if (h->N == 0) return EKF_OK;
+    if (!s || len < h->N) return fail(h, EKF_EINVAL, "ekf_get_s: buffer too small");
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaMemcpyAsync(s, h->s, sizeof(double) * h->N, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
+    CKH(h);
+    const int n = n_of(h);
+    if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_get_P: lda < n");
+    CK(cudaSetDevice(h->p.device));
+    if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
+    CK(cudaMemcpy2DAsync(P, sizeof(double) * lda, h->P, sizeof(double) * h->ld, sizeof(double) * n, n,
+                         cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_t nr, int32_t nc, double* out,
+                                   int32_t ldo) {
+    CKH(h);
+    const int n = n_of(h);
+    if (!out || r0 < 0 || c0 < 0 || nr < 1 || nc < 1 || r0 + nr > n || c0 + nc > n || ldo < nr)
+        return fail(h, EKF_EINVAL, "ekf_get_P_block: bad block");
+    CK(cudaSetDevice(h->p.device));
+    if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
+    CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, h->P + r0 + (int64_t)c0 * h->ld, sizeof(double) * h->ld,
+                         sizeof(double) * nr, nc, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t lda, const double* s,
+                                 int32_t N) {
+    CKH(h);
+    if (N < 0 || N > h->p.capacity_landmarks) return fail(h, EKF_ECAPACITY, "ekf_set_state: N beyond capacity");
+    const int n = 3 + 2 * N;
+    if (!x || !P || lda < n || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state: bad argument");
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld, h->stream));
+    CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
+    CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+    if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpy2DAsync(h->P, sizeof(double) * h->ld, P, sizeof(double) * lda, sizeof(double) * n, n,
+                         cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->N = N;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const double* s, int32_t N, const double* A,
+                                         int32_t r, const double* d) {
+    CKH(h);
+    if (N < 0 || N > h->p.capacity_landmarks) return fail(h, EKF_ECAPACITY, "ekf_set_state_lowrank: N beyond capacity");
+    const int n = 3 + 2 * N;
+    if (!x || !A || !d || r < 1 || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state_lowrank: bad argument");
+    CK(cudaSetDevice(h->p.device));
+    double *dA = nullptr, *dd = nullptr;
+    CK(cudaMalloc(&dA, sizeof(double) * (size_t)n * r));
+    CK(cudaMalloc(&dd, sizeof(double) * n));
+    CK(cudaMemcpyAsync(dA, A, sizeof(double) * (size_t)n * r, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(dd, d, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld, h->stream));
+    CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
+    CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+    if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
+    launch_init_lowrank(h->stream, h->P, h->ld, n, dA, r, dd);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(h->stream));
+    cudaFree(dA); cudaFree(dd);
+    h->N = N;
+    return EKF_OK;
+}
+
+// ---------------------------------------------------------------- measurement hooks
+extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
+    CKH(h);
+    CK(cudaStreamSynchronize(h->stream));
+    h->prof = on != 0;
+    h->ev_used = 0;
+    h->dd_ms = 0.0;
+    h->dd_launches = 0;
+    h->launches = 0;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, int64_t* downdate_launches,
+                                    int64_t* kernel_launches_total) {
+    CKH(h);
+    CK(cudaStreamSynchronize(h->stream));
+    for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+        h->dd_ms += ms;
+    }
+    h->ev_used = 0;
+    if (downdate_ms_total) *downdate_ms_total = h->dd_ms;
+    if (downdate_launches) *downdate_launches = h->dd_launches;
+    if (kernel_launches_total) *kernel_launches_total = h->launches;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes) {
+    CKH(h);
+    if (!bytes) return fail(h, EKF_EINVAL, "bytes is null");
+    const double n = (double)n_of(h);
+    *bytes = sym_of(h) ? 8.0 * n * (n + 1.0) : 16.0 * n * n;   // read + write of every live element
+    return EKF_OK;
+}

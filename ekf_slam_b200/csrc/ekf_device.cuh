@@ -1,0 +1,143 @@
+// ekf_device.cuh -- device-side helpers shared by the EKF-SLAM kernels (sm_100a).
+//
+// Layout in HBM (DESIGN.md "Data layout"):
+//   P   : column-major fp64, leading dimension ld (multiple of 16 doubles = 128 B, so every
+//         column starts on a cache-line boundary); element (i,j) at P[i + j*ld]; allocated once
+//         at capacity (the reference reallocates on every append, EKF_SLAM.m:91).
+//   x   : ld doubles (n active), s : capacity doubles (N active).
+//   Kd  : ld x double2  = rows of the Kalman gain K (n x 2), zero beyond n.
+//   Bd  : ld x double2  = columns of B = H_k * P (2 x n).
+//   EKF_STORAGE_SYM: only elements with i <= j are live; (i > j) is don't-care.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ekf {
+
+struct Lin {            // written by k_linearize, consumed by k_gain (one observation)
+    double Hs[2][5];    // the 5 non-zero columns of H_k (EKF_SLAM.m:137-138)
+    double nu[2];       // innovation z - z_k (EKF_SLAM.m:144), NOT angle wrapped
+    double Sinv[2][2];  // phi_k^-1 (EKF_SLAM.m:143)
+    double S[2][2];     // phi_k (EKF_SLAM.m:141)
+    int    c[5];        // 0-based state indices [0,1,2,a,a+1], a = 3+2(idx-1)
+    int    nonfinite;   // 1 when phi_k or its inverse is not finite
+};
+
+struct AssocResult {    // written by k_associate's last block
+    int    newLL;       // Correspondence.m:33/82
+    int    index1;      // 1-based, Correspondence.m:40/84
+    double cost;        // min_log_likelihood (Inf when newLL)
+};
+
+// ---- MATLAB degree helpers (restated semantics; toolbox source is not in the reference) ----
+__device__ __forceinline__ void reduce90(double x, int& m, double& r) {
+    x = fmod(x, 360.0);
+    double n = rint(x / 90.0);
+    r = x - 90.0 * n;
+    m = ((int)n) & 3;
+}
+__device__ __forceinline__ double sind(double x) {      // EKF_SLAM.m:42,59,63,84,87-88
+    int m; double r; reduce90(x, m, r);
+    const double d2r = 0.017453292519943295;
+    double a = r * d2r;
+    switch (m) { case 0: return sin(a); case 1: return cos(a); case 2: return -sin(a); default: return -cos(a); }
+}
+__device__ __forceinline__ double cosd(double x) {      // EKF_SLAM.m:42,58,64,85,87-88
+    int m; double r; reduce90(x, m, r);
+    const double d2r = 0.017453292519943295;
+    double a = r * d2r;
+    switch (m) { case 0: return cos(a); case 1: return -sin(a); case 2: return -cos(a); default: return sin(a); }
+}
+__device__ __forceinline__ double atan2d(double y, double x) {   // EKF_SLAM.m:130
+    return __dmul_rn(atan2(y, x), 57.29577951308232);
+}
+__device__ __forceinline__ double wrapTo360(double a) {          // EKF_SLAM.m:50,130; Correspondence.m:56
+    double r = fmod(a, 360.0);
+    if (r != 0.0 && r < 0.0) r = __dadd_rn(r, 360.0);
+    if (r == 0.0 && a > 0.0) r = 360.0;
+    return r;
+}
+
+// Element read honouring the storage mode (SYM keeps only i <= j live).
+__device__ __forceinline__ double ldP(const double* __restrict__ P, int64_t ld, int i, int j, int sym) {
+    if (sym && i > j) { int t = i; i = j; j = t; }
+    return P[(int64_t)i + (int64_t)j * ld];
+}
+
+// Range-bearing measurement model about landmark slot a (0-based state index of its x coordinate).
+// Follows EKF_SLAM.m:125-138 == Correspondence.m:50-63 with explicit (non-contracted) roundings so a
+// plain C restatement compiled with -ffp-contract=off reproduces every bit except atan2's last ulp.
+__device__ __forceinline__ void measurement_model(const double xr[3], double mx, double my,
+                                                  double zk[2], double Hs[2][5]) {
+    double d0 = __dsub_rn(mx, xr[0]);
+    double d1 = __dsub_rn(my, xr[1]);
+    double q = __dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1));
+    double sq = sqrt(q);
+    zk[0] = sq;
+    zk[1] = wrapTo360(__dsub_rn(atan2d(d1, d0), xr[2]));
+    double iq = 1.0 / q;
+    Hs[0][0] = __dmul_rn(iq, __dmul_rn(-sq, d0));
+    Hs[0][1] = __dmul_rn(iq, __dmul_rn(-sq, d1));
+    Hs[0][2] = __dmul_rn(iq, 0.0);
+    Hs[0][3] = __dmul_rn(iq, __dmul_rn(sq, d0));
+    Hs[0][4] = __dmul_rn(iq, __dmul_rn(sq, d1));
+    Hs[1][0] = __dmul_rn(iq, d1);
+    Hs[1][1] = __dmul_rn(iq, -d0);
+    Hs[1][2] = __dmul_rn(iq, -q);
+    Hs[1][3] = __dmul_rn(iq, -d1);
+    Hs[1][4] = __dmul_rn(iq, d0);
+}
+
+// phi = (Hs * Pcc) * Hs' + diag(R)   (EKF_SLAM.m:141, left-to-right like MATLAB), 2x2 inverse.
+__device__ __forceinline__ void innovation_cov(const double Hs[2][5], const double Pcc[5][5],
+                                               const double Rd[2], double S[2][2], double Si[2][2]) {
+    double HP[2][5];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int b = 0; b < 5; ++b) {
+            double acc = __dmul_rn(Hs[r][0], Pcc[0][b]);
+#pragma unroll
+            for (int a = 1; a < 5; ++a) acc = __dadd_rn(acc, __dmul_rn(Hs[r][a], Pcc[a][b]));
+            HP[r][b] = acc;
+        }
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            double acc = __dmul_rn(HP[r][0], Hs[t][0]);
+#pragma unroll
+            for (int b = 1; b < 5; ++b) acc = __dadd_rn(acc, __dmul_rn(HP[r][b], Hs[t][b]));
+            S[r][t] = (r == t) ? __dadd_rn(acc, Rd[r]) : acc;
+        }
+    double det = __dsub_rn(__dmul_rn(S[0][0], S[1][1]), __dmul_rn(S[0][1], S[1][0]));
+    double id = 1.0 / det;
+    Si[0][0] = __dmul_rn(S[1][1], id);
+    Si[0][1] = __dmul_rn(-S[0][1], id);
+    Si[1][0] = __dmul_rn(-S[1][0], id);
+    Si[1][1] = __dmul_rn(S[0][0], id);
+}
+
+// ---- streaming vector access for the downdate (LDG.E.128/256 with L1 no-allocate) ----
+struct __align__(32) double4a { double x, y, z, w; };
+
+__device__ __forceinline__ double2 ld_stream2(const double* p) {
+    double2 v;
+    asm volatile("ld.global.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_stream2(double* p, double2 v) {
+    asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1,%2};" :: "l"(p), "d"(v.x), "d"(v.y) : "memory");
+}
+__device__ __forceinline__ double4a ld_stream4(const double* p) {
+    double4a v;
+    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_stream4(double* p, double4a v) {
+    asm volatile("st.global.L1::no_allocate.v4.f64 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w) : "memory");
+}
+
+}  // namespace ekf

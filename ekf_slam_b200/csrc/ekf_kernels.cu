@@ -1,0 +1,440 @@
+// ekf_kernels.cu -- hand-written sm_100a kernels of the EKF-SLAM hot path.
+//   K1 k_predict_P / k_predict_x  : EKF_SLAM.m:40-65   (F P F' + Q without touching the landmark block)
+//   K2 k_linearize / k_gain       : EKF_SLAM.m:124-144 (5-column gather, S, S^-1, K, x)
+//   K3 k_downdate                 : EKF_SLAM.m:145     (P -= K * (H P), streaming, HBM-bound)
+//   K4 k_associate                : Correspondence.m:28-88 (gating + first-argmin)
+//   K5 k_append                   : EKF_SLAM.m:67-98
+#include "ekf_kernels.h"
+#include "ekf_device.cuh"
+#include <math_constants.h>
+#include <limits.h>
+
+namespace ekf {
+
+// ------------------------------------------------------------------ K1 predict
+// F = I + a e1 e3' + b e2 e3' (EKF_SLAM.m:62-64): (F P) adds a,b * row 3 to rows 1,2; (.) F' adds a,b * col 3
+// to cols 1,2.  Thread t >= 3 owns column t of the row pass and row t of the column pass; thread 0 of block 0
+// owns the 3x3 corner (both passes, then + Q = (W C) W', EKF_SLAM.m:42-47).  x is NOT written here so that
+// every block sees the pre-motion heading (EKF_SLAM.m:42,63-64 use theta before f()).
+__global__ void k_predict_P(double* __restrict__ P, int64_t ld, const double* __restrict__ x, int n,
+                            double u1, double u2, double C, int sym) {
+    const double th = x[2];
+    const double st = sind(th), ct = cosd(th);
+    const double a = -1.0 * u1 * st;      // F(1,3), EKF_SLAM.m:63
+    const double b = u1 * ct;             // F(2,3), EKF_SLAM.m:64
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) {
+        double M[3][3];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) M[i][j] = ldP(P, ld, i, j, sym);
+        for (int j = 0; j < 3; ++j) {     // F*P
+            M[0][j] = M[0][j] + a * M[2][j];
+            M[1][j] = M[1][j] + b * M[2][j];
+        }
+        for (int i = 0; i < 3; ++i) {     // (F*P)*F'
+            M[i][0] = M[i][0] + M[i][2] * a;
+            M[i][1] = M[i][1] + M[i][2] * b;
+        }
+        double W[3] = {u1 * ct, u1 * st, u2};      // EKF_SLAM.m:42
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) P[i + j * ld] = M[i][j] + (W[i] * C) * W[j];   // :44,47
+    } else if (t >= 3 && t < n) {
+        double* col = P + (int64_t)t * ld;         // rows 0..2 of column t: one 32 B sector
+        double p2 = col[2];
+        col[0] = col[0] + a * p2;
+        col[1] = col[1] + b * p2;
+        if (!sym) {                                // row t, columns 0..2 (dead triangle in SYM storage)
+            double q2 = P[t + 2 * ld];
+            P[t] = P[t] + q2 * a;
+            P[t + ld] = P[t + ld] + q2 * b;
+        }
+    }
+}
+
+__global__ void k_predict_x(double* __restrict__ x, double u1, double u2) {   // EKF_SLAM.m:57-60, :50
+    double th = x[2];
+    x[0] = x[0] + u1 * cosd(th + u2);
+    x[1] = x[1] + u1 * sind(th + u2);
+    x[2] = wrapTo360(th + u2);
+}
+
+// ------------------------------------------------------------------ K2 linearize + gain
+// One warp: lanes 0..24 fetch the 5x5 block P(c,c); lane 0 builds z_k, H_k, phi_k, phi_k^-1.
+__global__ void k_linearize(const double* __restrict__ P, int64_t ld, const double* __restrict__ x,
+                            int a, double z0, double z1, double R0, double R1, int sym, Lin* __restrict__ lin) {
+    __shared__ double Pcc[5][5];
+    int lane = threadIdx.x;
+    int c[5] = {0, 1, 2, a, a + 1};
+    if (lane < 25) {
+        int i = lane / 5, j = lane % 5;
+        Pcc[i][j] = ldP(P, ld, c[i], c[j], sym);
+    }
+    __syncwarp();
+    if (lane == 0) {
+        double xr[3] = {x[0], x[1], x[2]};
+        double zk[2], Hs[2][5], S[2][2], Si[2][2];
+        measurement_model(xr, x[a], x[a + 1], zk, Hs);
+        double Rd[2] = {R0, R1};
+        double Pl[5][5];
+        for (int i = 0; i < 5; ++i)
+            for (int j = 0; j < 5; ++j) Pl[i][j] = Pcc[i][j];
+        innovation_cov(Hs, Pl, Rd, S, Si);
+        int bad = 0;
+        for (int r = 0; r < 2; ++r) {
+            for (int k = 0; k < 5; ++k) lin->Hs[r][k] = Hs[r][k];
+            for (int t = 0; t < 2; ++t) {
+                lin->S[r][t] = S[r][t];
+                lin->Sinv[r][t] = Si[r][t];
+                if (!isfinite(S[r][t]) || !isfinite(Si[r][t])) bad = 1;
+            }
+        }
+        lin->nu[0] = z0 - zk[0];
+        lin->nu[1] = z1 - zk[1];
+        for (int k = 0; k < 5; ++k) lin->c[k] = c[k];
+        lin->nonfinite = bad;
+    }
+}
+
+// Row i of P H' (5-column gather), K = (P H') phi^-1, x += K nu, and column i of B = H P.
+__global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int a, int sym,
+                       const Lin* __restrict__ lin, double2* __restrict__ Kd, double2* __restrict__ Bd) {
+    __shared__ Lin L;
+    if (threadIdx.x < sizeof(Lin) / sizeof(double)) ((double*)&L)[threadIdx.x] = ((const double*)lin)[threadIdx.x];
+    __syncthreads();
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c[5] = {0, 1, 2, a, a + 1};
+    double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
+    if (sym) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            double p = (i <= c[k]) ? P[(int64_t)i + (int64_t)c[k] * ld] : P[(int64_t)c[k] + (int64_t)i * ld];
+            ph0 += p * L.Hs[0][k];
+            ph1 += p * L.Hs[1][k];
+        }
+        b0 = ph0; b1 = ph1;                       // B = (P H')' when P is symmetric
+    } else {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            double pc = P[(int64_t)i + (int64_t)c[k] * ld];     // P(i, c_k): column c_k, coalesced over i
+            double pr = P[(int64_t)c[k] + (int64_t)i * ld];     // P(c_k, i): 2 sectors per column i
+            ph0 += pc * L.Hs[0][k];
+            ph1 += pc * L.Hs[1][k];
+            b0 += L.Hs[0][k] * pr;
+            b1 += L.Hs[1][k] * pr;
+        }
+    }
+    double k0 = ph0 * L.Sinv[0][0] + ph1 * L.Sinv[1][0];       // EKF_SLAM.m:143
+    double k1 = ph0 * L.Sinv[0][1] + ph1 * L.Sinv[1][1];
+    x[i] = x[i] + (k0 * L.nu[0] + k1 * L.nu[1]);               // EKF_SLAM.m:144
+    Kd[i] = make_double2(k0, k1);
+    Bd[i] = make_double2(b0, b1);
+}
+
+// ------------------------------------------------------------------ K5 append
+// New landmark at state rows n, n+1 (0-based), n = 3 + 2N.  EKF_SLAM.m:84-97.
+__global__ void k_append(double* __restrict__ P, int64_t ld, double* __restrict__ x, double* __restrict__ s,
+                         int N, double u1, double u2, double R0, double R1, double px, double py, double sig, int sym) {
+    const int n = 3 + 2 * N;
+    const double th = x[2];
+    const double j02 = -u1 * sind(th), j12 = u1 * cosd(th);    // jxr = [1 0 j02; 0 1 j12], :84-85
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < N) {                                               // old landmark t: blocks F and G, :94-97
+        int a = 3 + 2 * t;
+        for (int m = 0; m < 2; ++m) {
+            double p0 = ldP(P, ld, a + m, 0, sym), p1 = ldP(P, ld, a + m, 1, sym), p2 = ldP(P, ld, a + m, 2, sym);
+            double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;        // jxr * P(lm,1:3)'
+            double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+            P[(int64_t)(a + m) + (int64_t)n * ld] = f0;        // G (upper part)
+            P[(int64_t)(a + m) + (int64_t)(n + 1) * ld] = f1;
+            P[(int64_t)n + (int64_t)(a + m) * ld] = f0;        // F (lower part; don't-care in SYM)
+            P[(int64_t)(n + 1) + (int64_t)(a + m) * ld] = f1;
+        }
+    } else if (t == N) {                                       // robot block, new diagonal block, x, s
+        double Prr[3][3];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) Prr[i][j] = ldP(P, ld, i, j, sym);
+        const double jxr[2][3] = {{1.0, 0.0, j02}, {0.0, 1.0, j12}};
+        const double cu = cosd(u2), su = sind(u2);
+        const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};     // :87-88
+        double JP[2][3];
+        for (int r = 0; r < 2; ++r)
+            for (int j = 0; j < 3; ++j) JP[r][j] = jxr[r][0] * Prr[0][j] + jxr[r][1] * Prr[1][j] + jxr[r][2] * Prr[2][j];
+        double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+        for (int r = 0; r < 2; ++r)
+            for (int c = 0; c < 2; ++c) {
+                double v = (JP[r][0] * jxr[c][0] + JP[r][1] * jxr[c][1] + JP[r][2] * jxr[c][2]) +
+                           (JR[r][0] * jz[c][0] + JR[r][1] * jz[c][1]);                  // :91
+                P[(int64_t)(n + r) + (int64_t)(n + c) * ld] = v;
+            }
+        for (int i = 0; i < 3; ++i)
+            for (int c = 0; c < 2; ++c) {
+                double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];   // :92
+                P[(int64_t)i + (int64_t)(n + c) * ld] = v;
+                P[(int64_t)(n + c) + (int64_t)i * ld] = v;                                          // :93
+            }
+        x[n] = px; x[n + 1] = py;                              // :79
+        s[N] = sig;                                            // :70
+    }
+}
+
+// ------------------------------------------------------------------ K4 association
+struct Cand { double cost; int idx; };
+__device__ __forceinline__ bool cand_less(double c1, int i1, double c2, int i2) {
+    return (c1 < c2) || (c1 == c2 && i1 < i2);     // strict '<' scan == lexicographic (cost, index) min
+}
+
+__global__ void k_associate(const double* __restrict__ P, int64_t ld, const double* __restrict__ x,
+                            const double* __restrict__ s, int N, double z0, double z1, double z2,
+                            double R0, double R1, double s_cost, double s_thresh, int mode, int sym,
+                            Cand* __restrict__ partial, unsigned int* __restrict__ ticket,
+                            AssocResult* __restrict__ out) {
+    __shared__ double Prr[3][3];
+    __shared__ double wc[32];
+    __shared__ int wi[32];
+    __shared__ bool is_last;
+    if (mode == 1 && threadIdx.x < 9) Prr[threadIdx.x / 3][threadIdx.x % 3] = ldP(P, ld, threadIdx.x / 3, threadIdx.x % 3, sym);
+    __syncthreads();
+    int kk = blockIdx.x * blockDim.x + threadIdx.x;            // 0-based landmark
+    double best = CUDART_INF;
+    int bidx = INT_MAX;
+    if (kk < N) {
+        double d = __dsub_rn(z2, s[kk]);
+        double sig = __dmul_rn(__dmul_rn(d, 1.0 / s_cost), d); // Correspondence.m:71
+        double ll = sig;                                       // :75
+        if (mode == 1) {                                       // :74 (commented out upstream)
+            int a = 3 + 2 * kk;
+            double xr[3] = {x[0], x[1], x[2]};
+            double zk[2], Hs[2][5], S[2][2], Si[2][2], Pcc[5][5];
+            measurement_model(xr, x[a], x[a + 1], zk, Hs);
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) Pcc[i][j] = Prr[i][j];
+            for (int i = 0; i < 3; ++i)
+                for (int m = 0; m < 2; ++m) {
+                    Pcc[i][3 + m] = P[(int64_t)i + (int64_t)(a + m) * ld];
+                    Pcc[3 + m][i] = sym ? Pcc[i][3 + m] : P[(int64_t)(a + m) + (int64_t)i * ld];
+                }
+            Pcc[3][3] = P[(int64_t)a + (int64_t)a * ld];
+            Pcc[3][4] = P[(int64_t)a + (int64_t)(a + 1) * ld];
+            Pcc[4][3] = sym ? Pcc[3][4] : P[(int64_t)(a + 1) + (int64_t)a * ld];
+            Pcc[4][4] = P[(int64_t)(a + 1) + (int64_t)(a + 1) * ld];
+            double Rd[2] = {R0, R1};
+            innovation_cov(Hs, Pcc, Rd, S, Si);
+            double n0 = __dsub_rn(z0, zk[0]), n1 = __dsub_rn(z1, zk[1]);
+            double t0 = __dadd_rn(__dmul_rn(n0, Si[0][0]), __dmul_rn(n1, Si[1][0]));   // (nu' * phi^-1) * nu, :69
+            double t1 = __dadd_rn(__dmul_rn(n0, Si[0][1]), __dmul_rn(n1, Si[1][1]));
+            double pos = __dadd_rn(__dmul_rn(t0, n0), __dmul_rn(t1, n1));
+            ll = __dadd_rn(pos, sig);
+        }
+        if (ll <= s_thresh && ll < CUDART_INF) { best = ll; bidx = kk + 1; }   // :78,:81 (NaN fails the gate; Inf never beats the initial Inf)
+    }
+    // warp-level first-argmin
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double oc = __shfl_down_sync(0xffffffffu, best, o);
+        int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+        if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+    }
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { wc[w] = best; wi[w] = bidx; }
+    __syncthreads();
+    if (w == 0) {
+        int nw = (blockDim.x + 31) >> 5;
+        best = (lane < nw) ? wc[lane] : CUDART_INF;
+        bidx = (lane < nw) ? wi[lane] : INT_MAX;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            double oc = __shfl_down_sync(0xffffffffu, best, o);
+            int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+            if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+        }
+        if (lane == 0) {
+            partial[blockIdx.x].cost = best;
+            partial[blockIdx.x].idx = bidx;
+            __threadfence();
+            unsigned int tk = atomicAdd(ticket, 1u);
+            is_last = (tk == gridDim.x - 1);
+        }
+    }
+    __syncthreads();
+    if (is_last && w == 0) {                                   // last block folds the per-block minima
+        __threadfence();
+        best = CUDART_INF; bidx = INT_MAX;
+        for (int b = lane; b < (int)gridDim.x; b += 32) {
+            double oc = ((volatile Cand*)partial)[b].cost;
+            int oi = ((volatile Cand*)partial)[b].idx;
+            if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            double oc = __shfl_down_sync(0xffffffffu, best, o);
+            int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+            if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+        }
+        if (lane == 0) {
+            bool found = (bidx != INT_MAX);
+            out->newLL = found ? 0 : 1;                        // :33,82
+            out->index1 = found ? bidx : N + 1;                // :40,84
+            out->cost = best;
+            *ticket = 0;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K3 covariance downdate
+// P(i,j) -= K(i,0) B(0,j) + K(i,1) B(1,j)   ==   P <- (I - K H) P   (EKF_SLAM.m:145), 16 B of HBM traffic per
+// element and 4 flop: purely bandwidth bound.  Column-major P: a block owns TR = BLOCK*VEC contiguous rows and
+// TC columns; each thread keeps its VEC rows of K in registers, the TC columns of B sit in shared memory, and
+// the loop issues UNROLL independent 128/256-bit loads per thread before the first use (Little's law:
+// ~6.5 TB/s x ~1 us needs > 40 KB in flight per SM).  SYM storage launches the same grid and drops tiles
+// that lie strictly below the diagonal, halving the traffic.
+template <int VEC> struct VecIO;
+template <> struct VecIO<2> {
+    typedef double2 T;
+    static __device__ __forceinline__ T ld(const double* p) { return ld_stream2(p); }
+    static __device__ __forceinline__ void st(double* p, T v) { st_stream2(p, v); }
+    static __device__ __forceinline__ void fma(T& v, const double2 (&k)[2], double2 b) {
+        v.x -= k[0].x * b.x + k[0].y * b.y;
+        v.y -= k[1].x * b.x + k[1].y * b.y;
+    }
+};
+template <> struct VecIO<4> {
+    typedef double4a T;
+    static __device__ __forceinline__ T ld(const double* p) { return ld_stream4(p); }
+    static __device__ __forceinline__ void st(double* p, T v) { st_stream4(p, v); }
+    static __device__ __forceinline__ void fma(T& v, const double2 (&k)[4], double2 b) {
+        v.x -= k[0].x * b.x + k[0].y * b.y;
+        v.y -= k[1].x * b.x + k[1].y * b.y;
+        v.z -= k[2].x * b.x + k[2].y * b.y;
+        v.w -= k[3].x * b.x + k[3].y * b.y;
+    }
+};
+
+template <int VEC, int BLOCK, int TC, int UNROLL>
+__global__ void __launch_bounds__(BLOCK)
+k_downdate(double* __restrict__ P, int64_t ld, int n, int sym,
+           const double2* __restrict__ Kd, const double2* __restrict__ Bd) {
+    constexpr int TR = BLOCK * VEC;
+    typedef VecIO<VEC> IO;
+    const int r0 = blockIdx.x * TR;
+    const int c0 = blockIdx.y * TC;
+    if (sym && r0 > c0 + TC - 1) return;              // tile strictly below the diagonal: dead in SYM storage
+    __shared__ double2 Bs[TC];
+    for (int j = threadIdx.x; j < TC; j += BLOCK) Bs[j] = (c0 + j < n) ? Bd[c0 + j] : make_double2(0.0, 0.0);
+    __syncthreads();
+    const int r = r0 + threadIdx.x * VEC;
+    if (r >= n) return;                               // rows [n, ld) are padding; Kd is zero there
+    double2 k[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) k[v] = Kd[r + v];
+    double* p = P + (int64_t)r + (int64_t)c0 * ld;
+    const int nc = min(TC, n - c0);
+    int j = 0;
+    for (; j + UNROLL <= nc; j += UNROLL) {
+        typename IO::T v[UNROLL];
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) v[q] = IO::ld(p + (int64_t)(j + q) * ld);
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) IO::fma(v[q], k, Bs[j + q]);
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) IO::st(p + (int64_t)(j + q) * ld, v[q]);
+    }
+    for (; j < nc; ++j) {
+        typename IO::T v = IO::ld(p + (int64_t)j * ld);
+        IO::fma(v, k, Bs[j]);
+        IO::st(p + (int64_t)j * ld, v);
+    }
+}
+
+// ------------------------------------------------------------------ state initialisation helpers
+__global__ void k_init_lowrank(double* __restrict__ P, int64_t ld, int n, const double* __restrict__ A, int r,
+                               const double* __restrict__ d) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int j = blockIdx.y;
+    if (i >= n) return;
+    double acc = 0.0;
+    for (int q = 0; q < r; ++q) acc += A[i + (int64_t)q * n] * A[j + (int64_t)q * n];
+    acc = acc / (double)r;
+    if (i == j) acc += d[i];
+    P[(int64_t)i + (int64_t)j * ld] = acc;
+}
+
+// SYM storage read-back: copy the live upper triangle onto the dead lower one (32x32 smem transpose).
+__global__ void k_mirror_upper(double* __restrict__ P, int64_t ld, int n) {
+    __shared__ double t[32][33];
+    int bi = blockIdx.x, bj = blockIdx.y;
+    if (bi > bj) return;
+    int i = bi * 32 + threadIdx.x;
+    for (int jj = threadIdx.y; jj < 32; jj += blockDim.y) {
+        int j = bj * 32 + jj;
+        t[jj][threadIdx.x] = (i < n && j < n) ? P[(int64_t)i + (int64_t)j * ld] : 0.0;
+    }
+    __syncthreads();
+    int i2 = bj * 32 + threadIdx.x;                 // destination row (old column)
+    for (int jj = threadIdx.y; jj < 32; jj += blockDim.y) {
+        int j2 = bi * 32 + jj;                      // destination column (old row)
+        if (i2 < n && j2 < n && i2 > j2) P[(int64_t)i2 + (int64_t)j2 * ld] = t[threadIdx.x][jj];
+    }
+}
+
+// ------------------------------------------------------------------ launchers
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym) {
+    k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, u1, u2, C, sym);
+    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2);
+}
+
+void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
+                           double R0, double R1, int sym, Lin* lin, double2* Kd, double2* Bd) {
+    k_linearize<<<1, 32, 0, st>>>(P, ld, x, a, z0, z1, R0, R1, sym, lin);
+    k_gain<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, a, sym, lin, Kd, Bd);
+}
+
+template <int VEC, int BLOCK, int TC, int UNROLL>
+static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kd, const double2* Bd) {
+    dim3 grid(cdiv(n, BLOCK * VEC), cdiv(n, TC));
+    k_downdate<VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, sym, Kd, Bd);
+}
+
+int g_downdate_variant = 0;
+
+void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kd, const double2* Bd) {
+    switch (g_downdate_variant) {
+        default:
+        case 0: launch_dd<4, 128, 32, 8>(st, P, ld, n, sym, Kd, Bd); break;
+        case 1: launch_dd<2, 128, 64, 8>(st, P, ld, n, sym, Kd, Bd); break;
+        case 2: launch_dd<4, 64, 64, 8>(st, P, ld, n, sym, Kd, Bd); break;
+        case 3: launch_dd<4, 128, 64, 4>(st, P, ld, n, sym, Kd, Bd); break;
+        case 4: launch_dd<2, 256, 32, 8>(st, P, ld, n, sym, Kd, Bd); break;
+        case 5: launch_dd<4, 256, 16, 8>(st, P, ld, n, sym, Kd, Bd); break;
+        case 6: launch_dd<4, 128, 128, 8>(st, P, ld, n, sym, Kd, Bd); break;
+        case 7: launch_dd<2, 128, 32, 16>(st, P, ld, n, sym, Kd, Bd); break;
+    }
+}
+
+void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
+                   double R0, double R1, double px, double py, double sig, int sym) {
+    k_append<<<cdiv(N + 1, 128), 128, 0, st>>>(P, ld, x, s, N, u1, u2, R0, R1, px, py, sig, sym);
+}
+
+int assoc_blocks(int N) { return cdiv(N, 256); }
+
+void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double* x, const double* s, int N,
+                      double z0, double z1, double z2, double R0, double R1, double s_cost, double s_thresh,
+                      int mode, int sym, void* partial, unsigned int* ticket, AssocResult* out) {
+    k_associate<<<assoc_blocks(N), 256, 0, st>>>(P, ld, x, s, N, z0, z1, z2, R0, R1, s_cost, s_thresh, mode, sym,
+                                                 (Cand*)partial, ticket, out);
+}
+
+void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, const double* A, int r, const double* d) {
+    dim3 grid(cdiv(n, 256), n);
+    k_init_lowrank<<<grid, 256, 0, st>>>(P, ld, n, A, r, d);
+}
+
+void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n) {
+    dim3 grid(cdiv(n, 32), cdiv(n, 32));
+    k_mirror_upper<<<grid, dim3(32, 8), 0, st>>>(P, ld, n);
+}
+
+}  // namespace ekf

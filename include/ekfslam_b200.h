@@ -1,0 +1,129 @@
+/*
+ * ekfslam_b200.h -- C ABI of the B200-native EKF-SLAM filter core.
+ *
+ * This is the drop-in boundary under the reference's MATLAB class interface
+ * (SamShue/EKF_SLAM).  The reference has no FFI of its own; the seam is the
+ * class API (SLAM.m:110 `h.slam.predict(h.u)`, SLAM.m:116
+ * `h.slam.measure(laserData,h.u,h.LM)`, EKF_SLAM_UC.m:119
+ * `correspondence.estimateCorrespondence(z,R,x,P,s)`).  Each entry point below
+ * names the reference method whose body it replaces.
+ *
+ * Conventions
+ *   - every function returns an int32 status (EKF_OK == 0, negative on error);
+ *     ekf_last_error() returns the message for the last failure on a handle.
+ *   - host buffers are caller-owned, fp64, MATLAB column-major; indices that
+ *     cross the ABI are 1-based int32 like MATLAB's.
+ *   - the library owns all device memory.  One handle = one CUDA device and one
+ *     stream; a handle is NOT thread-safe, distinct handles are independent.
+ *   - calls enqueue work on the handle's stream and return; getters and
+ *     ekf_sync() synchronise.  There is no CPU fallback: without a CUDA device
+ *     ekf_create fails with EKF_ECUDA.
+ */
+#ifndef EKFSLAM_B200_H
+#define EKFSLAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EKF_OK          0
+#define EKF_EINVAL     (-1)   /* bad argument / bad state (e.g. idx out of range) */
+#define EKF_ECAPACITY  (-2)   /* append beyond capacity_landmarks */
+#define EKF_ECUDA      (-3)   /* CUDA runtime error (message in ekf_last_error) */
+#define EKF_ENCCL      (-4)   /* NCCL error */
+#define EKF_ENONFINITE (-5)   /* debug check: non-finite innovation covariance */
+
+#define EKF_VARIANT_KNOWN  0  /* EKF_SLAM.m    */
+#define EKF_VARIANT_UC     1  /* EKF_SLAM_UC.m */
+
+#define EKF_ASSOC_SIGNATURE 0 /* Correspondence.m:75 as shipped (signature cost only) */
+#define EKF_ASSOC_POSITION  1 /* Correspondence.m:74 (commented out upstream): position + signature */
+
+#define EKF_STORAGE_FULL 0    /* P <- P - K (H P): every element read+written, non-symmetric form of EKF_SLAM.m:145 */
+#define EKF_STORAGE_SYM  1    /* only tiles on/above the diagonal are kept live (half the HBM traffic) */
+
+typedef struct ekf_handle ekf_handle;
+
+/* Property defaults of the reference classes (EKF_SLAM.m:12-16, EKF_SLAM_UC.m:12-16). */
+typedef struct ekf_params {
+    double   C;                  /* process-noise constant, EKF_SLAM.m:12 */
+    double   Rc[2];              /* measurement-noise constants, EKF_SLAM.m:13 / EKF_SLAM_UC.m:13 */
+    double   s_cost;             /* Correspondence.m:16 */
+    double   s_thresh;           /* Correspondence.m:17 */
+    int32_t  variant;            /* EKF_VARIANT_* */
+    int32_t  assoc_mode;         /* EKF_ASSOC_* */
+    int32_t  storage;            /* EKF_STORAGE_* */
+    int32_t  capacity_landmarks; /* P is allocated once at 3+2*capacity (reference reallocates per append, EKF_SLAM.m:91) */
+    int32_t  device;             /* CUDA device ordinal */
+    int32_t  defer_m;            /* <=1: downdate P at every observation; >1: deferred rank-2m flush */
+    uint64_t stream;             /* cudaStream_t to enqueue on, 0 = library creates one */
+} ekf_params;
+
+/* Fill *p with the reference's defaults for EKF_SLAM (variant 0) or EKF_SLAM_UC (variant 1). */
+int32_t ekf_params_default(ekf_params* p, int32_t variant);
+
+/* Constructor: x=[0 0 0], P=0.1*eye(3), s=[]  (EKF_SLAM.m:26-34, EKF_SLAM_UC.m:27-36). */
+int32_t ekf_create(const ekf_params* p, ekf_handle** out);
+int32_t ekf_destroy(ekf_handle* h);
+
+/* predict(h,u): EKF_SLAM.m:40-51 (+ f, :56-65).  u = [dD, dtheta_deg]. */
+int32_t ekf_predict(ekf_handle* h, const double u[2]);
+
+/* Update branch of measure(): EKF_SLAM.m:124-145 == EKF_SLAM_UC.m:125-146.
+ * z = [range, bearing_deg]; Rdiag = diag of R (EKF_SLAM.m:108); idx1 = 1-based landmark slot. */
+int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdiag[2], int32_t idx1);
+
+/* append(h,u,R,landmarkPos,signature): EKF_SLAM.m:67-98 (append.m:1-27). */
+int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdiag[2],
+                   const double pos[2], double signature);
+
+/* [newLL,index] = estimateCorrespondence(z,R,x,P,s): Correspondence.m:28-88.
+ * z = [range, bearing_deg, signature].  Synchronises to return the two scalars. */
+int32_t ekf_associate(ekf_handle* h, const double z[3], const double Rdiag[2],
+                      int32_t* newLL, int32_t* idx1);
+
+/* Whole measure() loop for k observations: EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151.
+ * observed_LL is k x 3 column-major ([range | bearing | index], ld = k).
+ * loc_table (n_table x 2 column-major) and index_table (n_table) are the fields of
+ * landmark_list.landmarkObj.landmark(:) the reference reads (.loc, .index).
+ * action_out[i] receives +idx for an update of slot idx, -idx for an append with signature idx
+ * (may be NULL). */
+int32_t ekf_measure_batch(ekf_handle* h, const double* observed_LL, int32_t k,
+                          const double u[2], const double* loc_table,
+                          const int32_t* index_table, int32_t n_table,
+                          int32_t* action_out);
+
+/* State access (public properties x, P, s of the reference classes, EKF_SLAM.m:6-9). */
+int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N);
+int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len);            /* len >= 3+2N */
+int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len);            /* len >= N */
+int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda);            /* n x n column-major, lda >= n; SYM storage is mirrored */
+int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_t nr, int32_t nc,
+                        double* out, int32_t ldo);                   /* 0-based sub-block (sampled parity at large n) */
+int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t lda,
+                      const double* s, int32_t N);
+/* Populated synthetic map without a 3.2 GB H2D copy: P = A A^T / r + diag(d), A is n x r column-major. */
+int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const double* s, int32_t N,
+                              const double* A, int32_t r, const double* d);
+/* Property writes (public, mutable after construction in the reference). */
+int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh);
+
+int32_t ekf_sync(ekf_handle* h);
+const char* ekf_last_error(ekf_handle* h);
+
+/* Measurement hooks used by bench.py: CUDA-event timing of the covariance downdate kernel. */
+int32_t ekf_profile_enable(ekf_handle* h, int32_t on);
+int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, int64_t* downdate_launches,
+                         int64_t* kernel_launches_total);
+/* Bytes the downdate kernel must move per launch at the current n and storage. */
+int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes);
+
+/* Library identification. */
+const char* ekf_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EKFSLAM_B200_H */

@@ -1,0 +1,199 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI / class mirror) vs the dense-literal oracle
+on identical seeded inputs.  Tolerance (BASELINE.json north_star): association indices / actions identical,
+state and covariance <= 1e-9 relative Frobenius over 1000 steps."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-9
+
+
+def _rel(a, b):
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+def _run_pair(gpu, ora, w, check_every=100):
+    worst = (0.0, 0.0)
+    for t in range(w.T):
+        gpu.predict(w.u[t]); gpu.measure(None, w.u[t], w.stub(t))
+        ora.predict(w.u[t]); ora.measure(None, w.u[t], w.stub(t))
+        if (t + 1) % check_every == 0 or t == w.T - 1:
+            assert gpu.chosen == ora.chosen, 'actions differ by step %d' % t
+            ex, eP = _rel(gpu.x, ora.x), _rel(gpu.P, ora.P)
+            worst = (max(worst[0], ex), max(worst[1], eP))
+            assert ex <= TOL and eP <= TOL, (t, ex, eP)
+    return worst
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+@pytest.mark.parametrize('variant,mode,T', [('known', 'prefix', 1000), ('known', 'nearest', 50), ('uc', 'nearest', 1000)])
+def test_config1_example_style_1000_steps(storage, variant, mode, T):
+    """BASELINE config 1 (N=20): 1a prefix rule, 1b idx=ii quirk run (EKF_SLAM.m:123), UC k-nearest."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=20, T=T, k=5, mode=mode)
+    gpu = (E.EKF_SLAM if variant == 'known' else E.EKF_SLAM_UC)(capacity_landmarks=20, storage=storage)
+    ora = (O.EKF_SLAM if variant == 'known' else O.EKF_SLAM_UC)()
+    ex, eP = _run_pair(gpu, ora, w)
+    assert np.array_equal(gpu.s, ora.s)
+    assert gpu.N == (len(ora.x) - 3) // 2
+    print('config1 %s/%s/%s: worst rel err x %.2e P %.2e' % (variant, mode, storage, ex, eP))
+    gpu.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+def test_uc_200_landmarks(storage):
+    """One filter of BASELINE config 5 (N=200, EKF_SLAM_UC, k=5), 300 steps."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=200, T=300, k=5, mode='nearest', seed=7)
+    gpu = E.EKF_SLAM_UC(capacity_landmarks=200, storage=storage)
+    ora = O.EKF_SLAM_UC()
+    _run_pair(gpu, ora, w, check_every=100)
+    gpu.close()
+
+
+def _populated(N, storage, cls_name='EKF_SLAM', seed=3):
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, lowrank_to_dense
+    x, A, d, s, lms = synthetic_spd_state(N, seed=seed)
+    g = getattr(E, cls_name)(capacity_landmarks=N, storage=storage)
+    g.set_state_lowrank(x, s, A, d)
+    return g, x, lowrank_to_dense(A, d), s, lms
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+def test_lowrank_init_and_roundtrip(storage):
+    g, x, P, s, _ = _populated(150, storage)
+    assert _rel(g.P, P) < 1e-14
+    assert np.array_equal(g.x, x) and np.array_equal(g.s, s)
+    g.set_state(x, P, s)
+    assert np.array_equal(g.P, P)
+    blk = g.P_block(5, 17, 40, 33)
+    assert np.array_equal(blk, P[5:45, 17:50])
+    g.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+def test_config2_1k_landmarks_updates_vs_dense_literal(storage):
+    """BASELINE config 2 (N=1000, n=2003): populated map, predict + 8 updates per step, 5 steps, vs the dense
+    O(n^3) oracle."""
+    from ekf_slam_b200.synth import observe_from_truth
+    from oracle import dense_literal as O
+    N = 1000
+    g, x, P, s, lms = _populated(N, storage)
+    o = O.EKF_SLAM()
+    o.x, o.P, o.s = x.copy(), P.copy(), s.copy()
+    rng = np.random.default_rng(11)
+    for step in range(5):
+        u = np.array([0.3, 1.0])
+        g.predict(u); o.predict(u)
+        ids = rng.choice(N, 12, replace=False)
+        rows = observe_from_truth(lms, o.x[:3], ids, rng)[:8]
+        for r in rows:
+            R = np.diag([r[0] * 0.01, r[1] * 5.0])
+            g.update(r[:2], R, int(r[2]))
+            o._update(r, R, int(r[2]))
+    ex, eP = _rel(g.x, o.x), _rel(g.P, o.P)
+    print('1k/%s: rel err x %.2e P %.2e' % (storage, ex, eP))
+    assert ex <= TOL and eP <= TOL
+    g.close()
+
+
+def test_predict_leaves_landmark_block_bit_identical():
+    g, x, P, s, _ = _populated(64, 'full')
+    g.predict([0.4, 2.0])
+    P2 = g.P
+    assert np.array_equal(P2[3:, 3:], P[3:, 3:])
+    assert not np.array_equal(P2[:3, :], P[:3, :])
+    g.close()
+
+
+def test_append_keeps_old_block_bit_identical_and_capacity_error():
+    import ekf_slam_b200 as E
+    g, x, P, s, _ = _populated(10, 'full')
+    with pytest.raises(E.EkfError) as ei:
+        g.append([0.1, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], 11)
+    assert ei.value.code == -2
+    g.close()
+    g = E.EKF_SLAM(capacity_landmarks=12)
+    g.set_state(x, P, s)
+    g.append([0.1, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], 11)
+    P2 = g.P
+    assert P2.shape == (25, 25) and np.array_equal(P2[:23, :23], P)
+    assert np.array_equal(P2[23:, :23], P2[:23, 23:].T)
+    assert g.x[-2:].tolist() == [1.0, 2.0] and g.s[-1] == 11
+    g.close()
+
+
+def test_update_index_out_of_range_is_an_error():
+    import ekf_slam_b200 as E
+    g, *_ = _populated(10, 'full')
+    with pytest.raises(E.EkfError):
+        g.update([1.0, 90.0], np.diag([0.01, 450.0]), 11)
+    g.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+@pytest.mark.parametrize('mode', ['signature', 'position'])
+def test_association_indices_bit_exact(mode, storage):
+    """Correspondence.m:28-88: mode A as shipped (:75) and mode B (:74) with all signatures equal and a
+    chi-square gate, incl. the first-minimum tie rule (:81) on duplicated landmarks."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, lowrank_to_dense, observe_from_truth
+    from oracle import dense_literal as O
+    N = 300
+    x, A, d, s, lms = synthetic_spd_state(N, seed=5)
+    P = lowrank_to_dense(A, d)
+    if mode == 'position':
+        s = np.ones(N)
+        x[3 + 2 * 40: 5 + 2 * 40] = x[3 + 2 * 7: 5 + 2 * 7]          # duplicate landmark 8 into slot 41
+        P[:, 3 + 2 * 40: 5 + 2 * 40] = P[:, 3 + 2 * 7: 5 + 2 * 7]
+        P[3 + 2 * 40: 5 + 2 * 40, :] = P[3 + 2 * 7: 5 + 2 * 7, :]
+        P[3 + 2 * 40: 5 + 2 * 40, 3 + 2 * 40: 5 + 2 * 40] = P[3 + 2 * 7: 5 + 2 * 7, 3 + 2 * 7: 5 + 2 * 7]
+    g = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, assoc_mode=mode)
+    oc = O.Correspondence(1e-11, 1e9, 'EKF_SLAM_UC', position_cost_in_score=(mode == 'position'))
+    if mode == 'position':
+        g.correspondence.s_thresh = 9.21
+        oc.s_thresh = 9.21
+        g._sync_corr()
+    g.set_state(x, P, s)
+    rng = np.random.default_rng(2)
+    ids = np.concatenate([[7, 40], rng.choice(N, 60, replace=False)])
+    rows = observe_from_truth(lms, x[:3], ids, rng, seam_deg=0.0)
+    n_new = 0
+    for r in rows:
+        z = r.copy()
+        if mode == 'position':
+            z[2] = 1.0
+        elif rng.random() < 0.2:
+            z[2] = N + 5.0                                            # unseen signature -> new landmark
+        R = np.diag([z[0] * 0.1, z[1] * 5.0])
+        got = g.correspondence.estimateCorrespondence(z, R)
+        want = oc.estimateCorrespondence(z, R, x, P, s)
+        assert got == want, (z, got, want)
+        n_new += int(want[0])
+    assert 0 < n_new < len(rows) or mode == 'position'
+    # value-class form with explicit arrays (Correspondence.m:28 signature)
+    c2 = E.Correspondence(1e-11, 1e9, 'EKF_SLAM_UC')
+    z = rows[0]
+    assert c2.estimateCorrespondence(z, np.diag([z[0] * 0.1, z[1] * 5.0]), x, P, np.arange(1, N + 1.0)) == \
+        O.Correspondence(1e-11, 1e9, 'EKF_SLAM_UC').estimateCorrespondence(z, np.diag([z[0] * 0.1, z[1] * 5.0]), x, P, np.arange(1, N + 1.0))
+    g.close()
+
+
+def test_empty_observation_list_is_a_noop():
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import LandmarkStub
+    g = E.EKF_SLAM(capacity_landmarks=4)
+    g.measure(None, [0.1, 1.0], LandmarkStub(np.zeros((0, 3)), []))
+    assert g.N == 0 and np.array_equal(g.P, 0.1 * np.eye(3))
+    g.close()
+
+
+def test_smoke_entry():
+    import __graft_entry__ as ge
+    ge.smoke()
