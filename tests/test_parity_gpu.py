@@ -104,7 +104,8 @@ def test_config2_1k_landmarks_updates_vs_dense_literal(storage):
 
 
 def test_predict_leaves_landmark_block_bit_identical():
-    g, x, P, s, _ = _populated(64, 'full')
+    g, x, _, s, _ = _populated(64, 'full')
+    P = g.P
     g.predict([0.4, 2.0])
     P2 = g.P
     assert np.array_equal(P2[3:, 3:], P[3:, 3:])
@@ -121,6 +122,7 @@ def test_append_keeps_old_block_bit_identical_and_capacity_error():
     g.close()
     g = E.EKF_SLAM(capacity_landmarks=12)
     g.set_state(x, P, s)
+    P = g.P
     g.append([0.1, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], 11)
     P2 = g.P
     assert P2.shape == (25, 25) and np.array_equal(P2[:23, :23], P)
