@@ -22,8 +22,10 @@ struct ekf_handle {
     double* P = nullptr;
     double* x = nullptr;
     double* s = nullptr;
-    double2* Kd = nullptr;
-    double2* Bd = nullptr;
+    double2* Kd = nullptr;     // EKF_MAX_DEFER slabs of ld double2: gains K_q of the pending observations
+    double2* Bd = nullptr;     // EKF_MAX_DEFER slabs: B_q = H_q P
+    int m_pend = 0;            // pending (not yet flushed) rank-2 terms
+    int defer = 1;             // flush when m_pend reaches this (1 = immediate)
     Lin* lin = nullptr;
     void* partial = nullptr;
     unsigned int* ticket = nullptr;
@@ -34,6 +36,7 @@ struct ekf_handle {
     size_t ev_used = 0;
     double dd_ms = 0.0;
     int64_t dd_launches = 0;
+    int64_t dd_terms = 0;      // rank-2 terms (observations) applied by those launches
     int64_t launches = 0;
     std::string err;
 };
@@ -50,6 +53,9 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
     } while (0)
 #define CKH(h)                                                                                     \
     do { if (!(h)) return EKF_EINVAL; } while (0)
+
+static int32_t flush(ekf_handle* h);
+#define FLUSH(h) do { int32_t rc__ = flush(h); if (rc__ != EKF_OK) return rc__; } while (0)
 
 static inline int n_of(const ekf_handle* h) { return 3 + 2 * h->N; }
 static inline int sym_of(const ekf_handle* h) { return h->p.storage == EKF_STORAGE_SYM ? 1 : 0; }
@@ -92,13 +98,14 @@ static int32_t init_state(ekf_handle* h) {
     CK(cudaMemsetAsync(h->P, 0, sizeof(double) * h->ld * h->cap_n, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemsetAsync(h->s, 0, sizeof(double) * (h->p.capacity_landmarks + 1), h->stream));
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld, h->stream));
-    CK(cudaMemsetAsync(h->Bd, 0, sizeof(double2) * h->ld, h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
+    CK(cudaMemsetAsync(h->Bd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
     const double d = 0.1;
     for (int i = 0; i < 3; ++i)
         CK(cudaMemcpyAsync(h->P + i + i * h->ld, &d, sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     h->N = 0;
+    h->m_pend = 0;
     return EKF_OK;
 }
 
@@ -112,6 +119,7 @@ extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
     }
     ekf_handle* h = new ekf_handle();
     h->p = *p;
+    h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
     if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) g_downdate_variant = atoi(v);
     int32_t rc = [&]() -> int32_t {
         CK(cudaSetDevice(p->device));
@@ -122,8 +130,8 @@ extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
         CK(cudaMalloc(&h->P, sizeof(double) * h->ld * h->cap_n));
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
-        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld));
-        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld));
+        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
+        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
         CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
@@ -167,13 +175,16 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     CKH(h);
     if (!u) return fail(h, EKF_EINVAL, "u is null");
     CK(cudaSetDevice(h->p.device));
+    FLUSH(h);
     launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     h->launches += 2;
     CK(cudaGetLastError());
     return EKF_OK;
 }
 
-static int32_t downdate(ekf_handle* h) {
+// Apply the m_pend pending rank-2 terms to P in one pass (the K3 kernel).
+static int32_t flush(ekf_handle* h) {
+    if (h->m_pend == 0) return EKF_OK;
     if (h->prof) {
         if (h->ev_used + 2 > h->ev.size()) {
             size_t old = h->ev.size();
@@ -182,14 +193,23 @@ static int32_t downdate(ekf_handle* h) {
         }
         CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
     }
-    launch_downdate(h->stream, h->P, h->ld, n_of(h), sym_of(h), h->Kd, h->Bd);
+    launch_downdate(h->stream, h->P, h->ld, n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend);
     if (h->prof) {
         CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
         h->ev_used += 2;
     }
     h->dd_launches += 1;
+    h->dd_terms += h->m_pend;
     h->launches += 1;
+    h->m_pend = 0;
+    CK(cudaGetLastError());
     return EKF_OK;
+}
+
+extern "C" int32_t ekf_flush(ekf_handle* h) {
+    CKH(h);
+    CK(cudaSetDevice(h->p.device));
+    return flush(h);
 }
 
 extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdiag[2], int32_t idx1) {
@@ -200,11 +220,11 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     CK(cudaSetDevice(h->p.device));
     const int a = 3 + 2 * (idx1 - 1);
     launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
-                          h->lin, h->Kd, h->Bd);
+                          h->lin, h->Kd, h->Bd, h->ld, h->m_pend);
     h->launches += 2;
-    int32_t rc = downdate(h);
-    if (rc != EKF_OK) return rc;
     CK(cudaGetLastError());
+    h->m_pend += 1;
+    if (h->m_pend >= h->defer) FLUSH(h);
     return EKF_OK;
 }
 
@@ -215,6 +235,7 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
     if (h->N >= h->p.capacity_landmarks)
         return fail(h, EKF_ECAPACITY, "ekf_append: capacity_landmarks=" + std::to_string(h->p.capacity_landmarks) + " reached");
     CK(cudaSetDevice(h->p.device));
+    FLUSH(h);
     launch_append(h->stream, h->P, h->ld, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1], pos[0], pos[1],
                   signature, sym_of(h));
     h->launches += 1;
@@ -229,6 +250,7 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
     if (!z || !Rdiag || !newLL || !idx1) return fail(h, EKF_EINVAL, "null argument");
     if (h->N == 0) { *newLL = 1; *idx1 = 1; return EKF_OK; }   // Correspondence.m:33,40 with an empty loop
     CK(cudaSetDevice(h->p.device));
+    if (h->p.assoc_mode == EKF_ASSOC_POSITION) FLUSH(h);      // mode B reads P blocks; mode A only s
     launch_associate(h->stream, h->P, h->ld, h->x, h->s, h->N, z[0], z[1], z[2], Rdiag[0], Rdiag[1],
                      h->p.s_cost, h->p.s_thresh, h->p.assoc_mode, sym_of(h), h->partial, h->ticket, h->d_res);
     h->launches += 1;
@@ -288,7 +310,7 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
         if (rc != EKF_OK) return rc;
         if (action_out) action_out[ii - 1] = act;
     }
-    return EKF_OK;
+    return flush(h);                                                       // P is whole again when measure() returns
 }
 
 // ---------------------------------------------------------------- state access
@@ -316,6 +338,7 @@ extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_get_P: lda < n");
     CK(cudaSetDevice(h->p.device));
+    FLUSH(h);
     if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
     CK(cudaMemcpy2DAsync(P, sizeof(double) * lda, h->P, sizeof(double) * h->ld, sizeof(double) * n, n,
                          cudaMemcpyDeviceToHost, h->stream));
@@ -330,6 +353,7 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
     if (!out || r0 < 0 || c0 < 0 || nr < 1 || nc < 1 || r0 + nr > n || c0 + nc > n || ldo < nr)
         return fail(h, EKF_EINVAL, "ekf_get_P_block: bad block");
     CK(cudaSetDevice(h->p.device));
+    FLUSH(h);
     if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
     CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, h->P + r0 + (int64_t)c0 * h->ld, sizeof(double) * h->ld,
                          sizeof(double) * nr, nc, cudaMemcpyDeviceToHost, h->stream));
@@ -344,7 +368,8 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     const int n = 3 + 2 * N;
     if (!x || !P || lda < n || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state: bad argument");
     CK(cudaSetDevice(h->p.device));
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld, h->stream));
+    h->m_pend = 0;
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
@@ -362,12 +387,13 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     const int n = 3 + 2 * N;
     if (!x || !A || !d || r < 1 || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state_lowrank: bad argument");
     CK(cudaSetDevice(h->p.device));
+    h->m_pend = 0;
     double *dA = nullptr, *dd = nullptr;
     CK(cudaMalloc(&dA, sizeof(double) * (size_t)n * r));
     CK(cudaMalloc(&dd, sizeof(double) * n));
     CK(cudaMemcpyAsync(dA, A, sizeof(double) * (size_t)n * r, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(dd, d, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld, h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
@@ -388,6 +414,7 @@ extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
     h->ev_used = 0;
     h->dd_ms = 0.0;
     h->dd_launches = 0;
+    h->dd_terms = 0;
     h->launches = 0;
     return EKF_OK;
 }

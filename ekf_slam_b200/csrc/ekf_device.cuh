@@ -64,6 +64,24 @@ __device__ __forceinline__ double ldP(const double* __restrict__ P, int64_t ld, 
     return P[(int64_t)i + (int64_t)j * ld];
 }
 
+// One rank-2 term of the covariance downdate, v - K(i,:) * B(:,j), as two FMAs in a fixed order.  Every
+// consumer (flush kernel, deferred gathers) goes through this so that the deferred path reproduces the
+// immediate path bit for bit.
+__device__ __forceinline__ double rank2_sub(double v, double2 k, double2 b) {
+    return __fma_rn(-k.y, b.y, __fma_rn(-k.x, b.x, v));
+}
+
+// Deferred downdate: HBM holds P0 and m pending rank-2 terms (Kall/Ball slabs, slab stride lds);
+// the current covariance element is P0(i,j) - sum_q K_q(i,:) B_q(:,j), subtracted in observation order.
+__device__ __forceinline__ double ldP_def(const double* __restrict__ P, int64_t ld, int i, int j, int sym,
+                                          const double2* __restrict__ Kall, const double2* __restrict__ Ball,
+                                          int64_t lds, int m) {
+    if (sym && i > j) { int t = i; i = j; j = t; }
+    double v = P[(int64_t)i + (int64_t)j * ld];
+    for (int q = 0; q < m; ++q) v = rank2_sub(v, Kall[q * lds + i], Ball[q * lds + j]);
+    return v;
+}
+
 // Range-bearing measurement model about landmark slot a (0-based state index of its x coordinate).
 // Follows EKF_SLAM.m:125-138 == Correspondence.m:50-63 with explicit (non-contracted) roundings so a
 // plain C restatement compiled with -ffp-contract=off reproduces every bit except atan2's last ulp.

@@ -59,15 +59,19 @@ __global__ void k_predict_x(double* __restrict__ x, double u1, double u2) {   //
 }
 
 // ------------------------------------------------------------------ K2 linearize + gain
+// Both kernels read the CURRENT covariance = P0 - (m pending rank-2 terms) through ldP_def, so they serve the
+// immediate path (m = 0) and the deferred path alike, and write K, B of this observation into slab slot m.
 // One warp: lanes 0..24 fetch the 5x5 block P(c,c); lane 0 builds z_k, H_k, phi_k, phi_k^-1.
 __global__ void k_linearize(const double* __restrict__ P, int64_t ld, const double* __restrict__ x,
-                            int a, double z0, double z1, double R0, double R1, int sym, Lin* __restrict__ lin) {
+                            int a, double z0, double z1, double R0, double R1, int sym,
+                            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m,
+                            Lin* __restrict__ lin) {
     __shared__ double Pcc[5][5];
     int lane = threadIdx.x;
     int c[5] = {0, 1, 2, a, a + 1};
     if (lane < 25) {
         int i = lane / 5, j = lane % 5;
-        Pcc[i][j] = ldP(P, ld, c[i], c[j], sym);
+        Pcc[i][j] = ldP_def(P, ld, c[i], c[j], sym, Kall, Ball, lds, m);
     }
     __syncwarp();
     if (lane == 0) {
@@ -97,7 +101,8 @@ __global__ void k_linearize(const double* __restrict__ P, int64_t ld, const doub
 
 // Row i of P H' (5-column gather), K = (P H') phi^-1, x += K nu, and column i of B = H P.
 __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int a, int sym,
-                       const Lin* __restrict__ lin, double2* __restrict__ Kd, double2* __restrict__ Bd) {
+                       const Lin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball,
+                       int64_t lds, int m) {
     __shared__ Lin L;
     if (threadIdx.x < sizeof(Lin) / sizeof(double)) ((double*)&L)[threadIdx.x] = ((const double*)lin)[threadIdx.x];
     __syncthreads();
@@ -105,30 +110,23 @@ __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restr
     if (i >= n) return;
     const int c[5] = {0, 1, 2, a, a + 1};
     double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
-    if (sym) {
 #pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            double p = (i <= c[k]) ? P[(int64_t)i + (int64_t)c[k] * ld] : P[(int64_t)c[k] + (int64_t)i * ld];
-            ph0 += p * L.Hs[0][k];
-            ph1 += p * L.Hs[1][k];
-        }
-        b0 = ph0; b1 = ph1;                       // B = (P H')' when P is symmetric
-    } else {
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            double pc = P[(int64_t)i + (int64_t)c[k] * ld];     // P(i, c_k): column c_k, coalesced over i
-            double pr = P[(int64_t)c[k] + (int64_t)i * ld];     // P(c_k, i): 2 sectors per column i
-            ph0 += pc * L.Hs[0][k];
-            ph1 += pc * L.Hs[1][k];
+    for (int k = 0; k < 5; ++k) {
+        double pc = ldP_def(P, ld, i, c[k], sym, Kall, Ball, lds, m);   // P(i, c_k)
+        ph0 += pc * L.Hs[0][k];
+        ph1 += pc * L.Hs[1][k];
+        if (!sym) {
+            double pr = ldP_def(P, ld, c[k], i, 0, Kall, Ball, lds, m); // P(c_k, i): 2 sectors per column i
             b0 += L.Hs[0][k] * pr;
             b1 += L.Hs[1][k] * pr;
         }
     }
+    if (sym) { b0 = ph0; b1 = ph1; }                           // B = (P H')' when P is symmetric
     double k0 = ph0 * L.Sinv[0][0] + ph1 * L.Sinv[1][0];       // EKF_SLAM.m:143
     double k1 = ph0 * L.Sinv[0][1] + ph1 * L.Sinv[1][1];
     x[i] = x[i] + (k0 * L.nu[0] + k1 * L.nu[1]);               // EKF_SLAM.m:144
-    Kd[i] = make_double2(k0, k1);
-    Bd[i] = make_double2(b0, b1);
+    Kall[m * lds + i] = make_double2(k0, k1);                  // slot m is not read by ldP_def (q < m)
+    Ball[m * lds + i] = make_double2(b0, b1);
 }
 
 // ------------------------------------------------------------------ K5 append
@@ -281,67 +279,76 @@ __global__ void k_associate(const double* __restrict__ P, int64_t ld, const doub
     }
 }
 
-// ------------------------------------------------------------------ K3 covariance downdate
-// P(i,j) -= K(i,0) B(0,j) + K(i,1) B(1,j)   ==   P <- (I - K H) P   (EKF_SLAM.m:145), 16 B of HBM traffic per
-// element and 4 flop: purely bandwidth bound.  Column-major P: a block owns TR = BLOCK*VEC contiguous rows and
-// TC columns; each thread keeps its VEC rows of K in registers, the TC columns of B sit in shared memory, and
-// the loop issues UNROLL independent 128/256-bit loads per thread before the first use (Little's law:
-// ~6.5 TB/s x ~1 us needs > 40 KB in flight per SM).  SYM storage launches the same grid and drops tiles
-// that lie strictly below the diagonal, halving the traffic.
+// ------------------------------------------------------------------ K3 covariance downdate (rank-2M flush)
+// P(i,j) -= sum_{q<M} K_q(i,0) B_q(0,j) + K_q(i,1) B_q(1,j), terms subtracted in observation order (rank2_sub),
+// == M successive applications of P <- (I - K H) P (EKF_SLAM.m:145) in ONE pass over P: 16 B of HBM traffic per
+// live element for M observations.  M = 1 is the immediate path.  Column-major P: a block owns TR = BLOCK*VEC
+// contiguous rows and TC columns; each thread keeps its VEC rows of the M gains in registers (VEC*M double2),
+// the TC columns of the M B-rows sit in shared memory (broadcast LDS.128), and the loop issues UNROLL
+// independent 128/256-bit loads per thread before the first use.  SYM storage launches the same grid and drops
+// tiles strictly below the diagonal, halving the traffic.  4M flop per 16 B: HBM-bound up to M ~ 20 on B200.
 template <int VEC> struct VecIO;
 template <> struct VecIO<2> {
     typedef double2 T;
     static __device__ __forceinline__ T ld(const double* p) { return ld_stream2(p); }
     static __device__ __forceinline__ void st(double* p, T v) { st_stream2(p, v); }
-    static __device__ __forceinline__ void fma(T& v, const double2 (&k)[2], double2 b) {
-        v.x -= k[0].x * b.x + k[0].y * b.y;
-        v.y -= k[1].x * b.x + k[1].y * b.y;
+    static __device__ __forceinline__ void sub(T& v, const double2* k, int M, int q, double2 b) {
+        v.x = rank2_sub(v.x, k[0 * M + q], b);
+        v.y = rank2_sub(v.y, k[1 * M + q], b);
     }
 };
 template <> struct VecIO<4> {
     typedef double4a T;
     static __device__ __forceinline__ T ld(const double* p) { return ld_stream4(p); }
     static __device__ __forceinline__ void st(double* p, T v) { st_stream4(p, v); }
-    static __device__ __forceinline__ void fma(T& v, const double2 (&k)[4], double2 b) {
-        v.x -= k[0].x * b.x + k[0].y * b.y;
-        v.y -= k[1].x * b.x + k[1].y * b.y;
-        v.z -= k[2].x * b.x + k[2].y * b.y;
-        v.w -= k[3].x * b.x + k[3].y * b.y;
+    static __device__ __forceinline__ void sub(T& v, const double2* k, int M, int q, double2 b) {
+        v.x = rank2_sub(v.x, k[0 * M + q], b);
+        v.y = rank2_sub(v.y, k[1 * M + q], b);
+        v.z = rank2_sub(v.z, k[2 * M + q], b);
+        v.w = rank2_sub(v.w, k[3 * M + q], b);
     }
 };
 
-template <int VEC, int BLOCK, int TC, int UNROLL>
+template <int M, int VEC, int BLOCK, int TC, int UNROLL>
 __global__ void __launch_bounds__(BLOCK)
 k_downdate(double* __restrict__ P, int64_t ld, int n, int sym,
-           const double2* __restrict__ Kd, const double2* __restrict__ Bd) {
+           const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds) {
     constexpr int TR = BLOCK * VEC;
     typedef VecIO<VEC> IO;
     const int r0 = blockIdx.x * TR;
     const int c0 = blockIdx.y * TC;
     if (sym && r0 > c0 + TC - 1) return;              // tile strictly below the diagonal: dead in SYM storage
-    __shared__ double2 Bs[TC];
-    for (int j = threadIdx.x; j < TC; j += BLOCK) Bs[j] = (c0 + j < n) ? Bd[c0 + j] : make_double2(0.0, 0.0);
+    __shared__ double2 Bs[TC * M];                    // Bs[j*M + q] = B_q(:, c0+j)
+    for (int t = threadIdx.x; t < TC * M; t += BLOCK) {
+        int j = t / M, q = t - j * M;
+        Bs[t] = (c0 + j < n) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
+    }
     __syncthreads();
     const int r = r0 + threadIdx.x * VEC;
-    if (r >= n) return;                               // rows [n, ld) are padding; Kd is zero there
-    double2 k[VEC];
+    if (r >= n) return;                               // rows [n, ld) are padding; the K slabs are zero there
+    double2 k[VEC * M];
 #pragma unroll
-    for (int v = 0; v < VEC; ++v) k[v] = Kd[r + v];
+    for (int v = 0; v < VEC; ++v)
+#pragma unroll
+        for (int q = 0; q < M; ++q) k[v * M + q] = Kall[q * lds + r + v];
     double* p = P + (int64_t)r + (int64_t)c0 * ld;
     const int nc = min(TC, n - c0);
     int j = 0;
     for (; j + UNROLL <= nc; j += UNROLL) {
         typename IO::T v[UNROLL];
 #pragma unroll
-        for (int q = 0; q < UNROLL; ++q) v[q] = IO::ld(p + (int64_t)(j + q) * ld);
+        for (int u = 0; u < UNROLL; ++u) v[u] = IO::ld(p + (int64_t)(j + u) * ld);
 #pragma unroll
-        for (int q = 0; q < UNROLL; ++q) IO::fma(v[q], k, Bs[j + q]);
+        for (int u = 0; u < UNROLL; ++u)
 #pragma unroll
-        for (int q = 0; q < UNROLL; ++q) IO::st(p + (int64_t)(j + q) * ld, v[q]);
+            for (int q = 0; q < M; ++q) IO::sub(v[u], k, M, q, Bs[(j + u) * M + q]);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) IO::st(p + (int64_t)(j + u) * ld, v[u]);
     }
     for (; j < nc; ++j) {
         typename IO::T v = IO::ld(p + (int64_t)j * ld);
-        IO::fma(v, k, Bs[j]);
+#pragma unroll
+        for (int q = 0; q < M; ++q) IO::sub(v, k, M, q, Bs[j * M + q]);
         IO::st(p + (int64_t)j * ld, v);
     }
 }
@@ -386,31 +393,46 @@ void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, do
 }
 
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
-                           double R0, double R1, int sym, Lin* lin, double2* Kd, double2* Bd) {
-    k_linearize<<<1, 32, 0, st>>>(P, ld, x, a, z0, z1, R0, R1, sym, lin);
-    k_gain<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, a, sym, lin, Kd, Bd);
+                           double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m) {
+    k_linearize<<<1, 32, 0, st>>>(P, ld, x, a, z0, z1, R0, R1, sym, Kall, Ball, lds, m, lin);
+    k_gain<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, a, sym, lin, Kall, Ball, lds, m);
 }
 
-template <int VEC, int BLOCK, int TC, int UNROLL>
-static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kd, const double2* Bd) {
+template <int M, int VEC, int BLOCK, int TC, int UNROLL>
+static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall, const double2* Ball,
+                      int64_t lds) {
     dim3 grid(cdiv(n, BLOCK * VEC), cdiv(n, TC));
-    k_downdate<VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, sym, Kd, Bd);
+    k_downdate<M, VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, sym, Kall, Ball, lds);
 }
 
 int g_downdate_variant = 0;
 
-void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kd, const double2* Bd) {
-    switch (g_downdate_variant) {
-        default:
-        case 0: launch_dd<4, 128, 32, 8>(st, P, ld, n, sym, Kd, Bd); break;
-        case 1: launch_dd<2, 128, 64, 8>(st, P, ld, n, sym, Kd, Bd); break;
-        case 2: launch_dd<4, 64, 64, 8>(st, P, ld, n, sym, Kd, Bd); break;
-        case 3: launch_dd<4, 128, 64, 4>(st, P, ld, n, sym, Kd, Bd); break;
-        case 4: launch_dd<2, 256, 32, 8>(st, P, ld, n, sym, Kd, Bd); break;
-        case 5: launch_dd<4, 256, 16, 8>(st, P, ld, n, sym, Kd, Bd); break;
-        case 6: launch_dd<4, 128, 128, 8>(st, P, ld, n, sym, Kd, Bd); break;
-        case 7: launch_dd<2, 128, 32, 16>(st, P, ld, n, sym, Kd, Bd); break;
+// m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
+void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall, const double2* Ball,
+                     int64_t lds, int m) {
+    const int v = g_downdate_variant;
+#define DD(M_) \
+    if (v == 1) launch_dd<M_, 2, 128, 64, 8>(st, P, ld, n, sym, Kall, Ball, lds); \
+    else if (v == 2) launch_dd<M_, 2, 256, 32, 4>(st, P, ld, n, sym, Kall, Ball, lds); \
+    else if (v == 3) launch_dd<M_, 2, 128, 32, 8>(st, P, ld, n, sym, Kall, Ball, lds); \
+    else launch_dd<M_, 2, 128, 32, 4>(st, P, ld, n, sym, Kall, Ball, lds);
+    switch (m) {
+        case 1:
+            if (v == 1) launch_dd<1, 2, 128, 64, 8>(st, P, ld, n, sym, Kall, Ball, lds);
+            else if (v == 2) launch_dd<1, 4, 64, 64, 8>(st, P, ld, n, sym, Kall, Ball, lds);
+            else if (v == 3) launch_dd<1, 4, 128, 64, 4>(st, P, ld, n, sym, Kall, Ball, lds);
+            else launch_dd<1, 4, 128, 32, 8>(st, P, ld, n, sym, Kall, Ball, lds);
+            break;
+        case 2: { DD(2) } break;
+        case 3: { DD(3) } break;
+        case 4: { DD(4) } break;
+        case 5: { DD(5) } break;
+        case 6: { DD(6) } break;
+        case 7: { DD(7) } break;
+        case 8: { DD(8) } break;
+        default: break;
     }
+#undef DD
 }
 
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,

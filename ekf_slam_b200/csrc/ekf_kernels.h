@@ -9,9 +9,11 @@ struct Lin;
 struct AssocResult;
 
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym);
+#define EKF_MAX_DEFER 8
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
-                           double R0, double R1, int sym, Lin* lin, double2* Kd, double2* Bd);
-void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kd, const double2* Bd);
+                           double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m);
+void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall, const double2* Ball,
+                     int64_t lds, int m);
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym);
 int  assoc_blocks(int N);

@@ -31,7 +31,7 @@ class _FilterBase:
     _VARIANT = L.VARIANT_KNOWN
 
     def __init__(self, capacity_landmarks=1024, storage='full', device=0, stream=0,
-                 assoc_mode='signature'):
+                 assoc_mode='signature', defer_m=0):
         self._lib = L.load()
         p = L.EkfParams()
         L.check(None, self._lib.ekf_params_default(ct.byref(p), self._VARIANT))
@@ -39,6 +39,7 @@ class _FilterBase:
         p.storage = L.STORAGE_SYM if storage in ('sym', L.STORAGE_SYM) else L.STORAGE_FULL
         p.assoc_mode = L.ASSOC_POSITION if assoc_mode in ('position', L.ASSOC_POSITION) else L.ASSOC_SIGNATURE
         p.device = int(device)
+        p.defer_m = int(defer_m)
         p.stream = int(stream)
         self._p = p
         self._h = L._H()
@@ -201,6 +202,9 @@ class _FilterBase:
     def plot(self, landmark_list=None):
         """EKF_SLAM.m:154-234 draws MATLAB figures; unavailable on this box (no graphics stack)."""
         return None
+
+    def flush(self):
+        self._ck(self._lib.ekf_flush(self._h))
 
     def sync(self):
         self._ck(self._lib.ekf_sync(self._h))

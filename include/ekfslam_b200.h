@@ -57,7 +57,7 @@ typedef struct ekf_params {
     int32_t  storage;            /* EKF_STORAGE_* */
     int32_t  capacity_landmarks; /* P is allocated once at 3+2*capacity (reference reallocates per append, EKF_SLAM.m:91) */
     int32_t  device;             /* CUDA device ordinal */
-    int32_t  defer_m;            /* <=1: downdate P at every observation; >1: deferred rank-2m flush */
+    int32_t  defer_m;            /* <=1: one pass over P per observation; 2..8: deferred, one rank-2m pass per m observations (same sequence of linearisations) */
     uint64_t stream;             /* cudaStream_t to enqueue on, 0 = library creates one */
 } ekf_params;
 
@@ -110,6 +110,9 @@ int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const double* s, i
 /* Property writes (public, mutable after construction in the reference). */
 int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh);
 
+/* Apply any deferred (defer_m > 1) rank-2 terms to P now.  predict, append, getters and the end of
+ * ekf_measure_batch flush implicitly; ekf_update flushes when defer_m terms are pending. */
+int32_t ekf_flush(ekf_handle* h);
 int32_t ekf_sync(ekf_handle* h);
 const char* ekf_last_error(ekf_handle* h);
 

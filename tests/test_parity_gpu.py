@@ -199,3 +199,42 @@ def test_empty_observation_list_is_a_noop():
 def test_smoke_entry():
     import __graft_entry__ as ge
     ge.smoke()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+@pytest.mark.parametrize('defer_m', [2, 5, 8])
+def test_deferred_flush_is_bit_identical_to_immediate(storage, defer_m):
+    """Deferred rank-2m downdate: same sequence of linearisations, one pass over P per m
+    observations.  All consumers share rank2_sub, so x and P must equal the immediate path bit for bit."""
+    from ekf_slam_b200.synth import observe_from_truth
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state
+    N = 257
+    x, A, d, s, lms = synthetic_spd_state(N, seed=9)
+    fs = [E.EKF_SLAM(capacity_landmarks=N, storage=storage, defer_m=m) for m in (0, defer_m)]
+    for f in fs:
+        f.set_state_lowrank(x, s, A, d)
+    rng = np.random.default_rng(4)
+    for step in range(4):
+        rows = observe_from_truth(lms, x[:3], rng.choice(N, 16, replace=False), rng)[:11]
+        for f in fs:
+            f.predict([0.2, 1.0])
+            for r in rows:
+                f.update(r[:2], np.diag([r[0] * 0.01, r[1] * 5.0]), int(r[2]))
+    assert np.array_equal(fs[0].x, fs[1].x)
+    assert np.array_equal(fs[0].P, fs[1].P)
+    for f in fs:
+        f.close()
+
+
+@pytest.mark.parametrize('variant', ['known', 'uc'])
+def test_deferred_full_loop_vs_oracle(variant):
+    """1000-step config-1 loop with defer_m=8 (appends, associations and predicts force flushes) vs the oracle."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=20, T=1000, k=5, mode='prefix' if variant == 'known' else 'nearest')
+    gpu = (E.EKF_SLAM if variant == 'known' else E.EKF_SLAM_UC)(capacity_landmarks=20, storage='sym', defer_m=8)
+    ora = (O.EKF_SLAM if variant == 'known' else O.EKF_SLAM_UC)()
+    _run_pair(gpu, ora, w)
+    gpu.close()
