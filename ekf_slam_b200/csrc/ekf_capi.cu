@@ -24,6 +24,7 @@ struct ekf_handle {
     double* s = nullptr;
     double2* Kd = nullptr;     // EKF_MAX_DEFER slabs of ld double2: gains K_q of the pending observations
     double2* Bd = nullptr;     // EKF_MAX_DEFER slabs: B_q = H_q P
+    double* Bpk = nullptr;     // ld x 16 doubles: B of the pending observations packed for the tensor-core flush
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
     int defer = 1;             // flush when m_pend reaches this (1 = immediate)
     Lin* lin = nullptr;
@@ -86,7 +87,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd);
-    cudaFree(h->lin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
+    cudaFree(h->Bpk); cudaFree(h->lin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -121,6 +122,7 @@ extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
     h->p = *p;
     h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
     if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) g_downdate_variant = atoi(v);
+    if (const char* v = getenv("EKF_DOWNDATE_CCH")) g_downdate_cch = atoi(v) < 64 ? 64 : (atoi(v) / 8) * 8;
     int32_t rc = [&]() -> int32_t {
         CK(cudaSetDevice(p->device));
         if (p->stream) { h->stream = (cudaStream_t)(uintptr_t)p->stream; }
@@ -132,6 +134,8 @@ extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
         CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
         CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
+        CK(cudaMalloc(&h->Bpk, sizeof(double) * h->ld * 16));
+        CK(cudaMemset(h->Bpk, 0, sizeof(double) * h->ld * 16));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
         CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
@@ -193,7 +197,7 @@ static int32_t flush(ekf_handle* h) {
         }
         CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
     }
-    launch_downdate(h->stream, h->P, h->ld, n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend);
+    launch_downdate(h->stream, h->P, h->ld, n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend, h->Bpk);
     if (h->prof) {
         CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
         h->ev_used += 2;
@@ -220,7 +224,7 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     CK(cudaSetDevice(h->p.device));
     const int a = 3 + 2 * (idx1 - 1);
     launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
-                          h->lin, h->Kd, h->Bd, h->ld, h->m_pend);
+                          h->lin, h->Kd, h->Bd, h->ld, h->m_pend, h->Bpk);
     h->launches += 2;
     CK(cudaGetLastError());
     h->m_pend += 1;

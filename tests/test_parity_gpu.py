@@ -238,3 +238,32 @@ def test_deferred_full_loop_vs_oracle(variant):
     ora = (O.EKF_SLAM if variant == 'known' else O.EKF_SLAM_UC)()
     _run_pair(gpu, ora, w)
     gpu.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+@pytest.mark.parametrize('defer_m', [2, 3, 8])
+@pytest.mark.parametrize('variant', ['4', '8', '12'])
+def test_tensor_core_flush_matches_immediate(storage, defer_m, variant, monkeypatch):
+    """K3b (mma.sync.m8n8k4.f64 flush) vs the immediate CUDA-core path: same terms in the same order."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
+    N = 300
+    x, A, d, s, lms = synthetic_spd_state(N, seed=9)
+    fs = []
+    for m, var in ((0, '0'), (defer_m, variant)):
+        monkeypatch.setenv('EKF_DOWNDATE_VARIANT', var)
+        fs.append(E.EKF_SLAM(capacity_landmarks=N + 3, storage=storage, defer_m=m))
+    for f in fs:
+        f.set_state_lowrank(x, s, A, d)
+    rng = np.random.default_rng(4)
+    for step in range(3):
+        rows = observe_from_truth(lms, x[:3], rng.choice(N, 16, replace=False), rng)[:11]
+        for f in fs:
+            f.predict([0.2, 1.0])
+            for r in rows:
+                f.update(r[:2], np.diag([r[0] * 0.01, r[1] * 5.0]), int(r[2]))
+    P0, P1 = fs[0].P, fs[1].P
+    print('mma flush v%s m=%d %s: bit-identical=%s rel=%.2e' % (variant, defer_m, storage, np.array_equal(P0, P1), _rel(P1, P0)))
+    assert _rel(P1, P0) < 1e-13 and _rel(fs[1].x, fs[0].x) < 1e-13
+    for f in fs:
+        f.close()
