@@ -4,9 +4,12 @@
 #include "ekf_kernels.h"
 #include "ekf_device.cuh"
 
+#include <nccl.h>
+#include <dlfcn.h>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -24,7 +27,14 @@ struct ekf_handle {
     double* s = nullptr;
     double2* Kd = nullptr;     // EKF_MAX_DEFER slabs of ld double2: gains K_q of the pending observations
     double2* Bd = nullptr;     // EKF_MAX_DEFER slabs: B_q = H_q P
-    double* Bpk = nullptr;     // ld x 16 doubles: B of the pending observations packed for the tensor-core flush
+    // ---- column-slab sharding (world > 1): this rank stores columns [c_lo, c_hi) of P, FULL storage ----
+    int rank = 0, world = 1;
+    int c_lo = 0, c_hi = 0;
+    ncclComm_t comm = nullptr;
+    double* Pc = nullptr;      // EKF_MAX_SLOTS x ld: broadcast columns of the current batch
+    double2* Bc = nullptr;     // EKF_MAX_DEFER x EKF_MAX_SLOTS: B_q(:, col(slot))
+    struct QObs { double z0, z1, R0, R1; int a; };
+    std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
     int defer = 1;             // flush when m_pend reaches this (1 = immediate)
     Lin* lin = nullptr;
@@ -61,6 +71,71 @@ static int32_t flush(ekf_handle* h);
 static inline int n_of(const ekf_handle* h) { return 3 + 2 * h->N; }
 static inline int sym_of(const ekf_handle* h) { return h->p.storage == EKF_STORAGE_SYM ? 1 : 0; }
 
+// ---- NCCL is bound lazily (dlopen) so that the single-GPU library loads anywhere libcudart does ----
+struct NcclApi {
+    void* so = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+static bool nccl_load(std::string& err) {
+    if (g_nccl.so) return true;
+    void* so = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!so) { err = std::string("dlopen libnccl.so.2: ") + dlerror(); return false; }
+#define SYM(field, name) \
+    *(void**)(&g_nccl.field) = dlsym(so, name); \
+    if (!g_nccl.field) { err = std::string("dlsym ") + name; return false; }
+    SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
+    SYM(Broadcast, "ncclBroadcast") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
+    SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+    g_nccl.so = so;
+    return true;
+}
+#define CKN(call)                                                                                  \
+    do {                                                                                           \
+        ncclResult_t r__ = (call);                                                                 \
+        if (r__ != ncclSuccess)                                                                    \
+            return fail(h, EKF_ENCCL, std::string(#call) + ": " + g_nccl.GetErrorString(r__));     \
+    } while (0)
+
+// Slab partition: landmark-aligned contiguous column ranges, balanced on capacity.  Rank 0 also owns the robot
+// columns 0..2; a landmark's two columns never straddle a boundary.
+static inline int slab_first_landmark(int capN, int world, int g) { return (int)((int64_t)g * capN / world); }
+extern "C" int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t* c_lo, int32_t* c_hi) {
+    if (capacity_landmarks < 1 || world < 1 || rank < 0 || rank >= world || !c_lo || !c_hi) return EKF_EINVAL;
+    *c_lo = rank == 0 ? 0 : 3 + 2 * slab_first_landmark(capacity_landmarks, world, rank);
+    *c_hi = 3 + 2 * slab_first_landmark(capacity_landmarks, world, rank + 1);
+    return EKF_OK;
+}
+static inline int owner_of_col(const ekf_handle* h, int col) {
+    if (col < 3) return 0;
+    const int l = (col - 3) / 2;
+    for (int g = h->world - 1; g > 0; --g)
+        if (l >= slab_first_landmark(h->p.capacity_landmarks, h->world, g)) return g;
+    return 0;
+}
+static inline int ncols_loc(const ekf_handle* h) {      // active columns of the local slab
+    int hi = std::min(h->c_hi, 3 + 2 * h->N);
+    return hi > h->c_lo ? hi - h->c_lo : 0;
+}
+
+extern "C" int32_t ekf_nccl_unique_id(uint8_t* id128) {
+    std::string err;
+    if (!id128) return EKF_EINVAL;
+    if (!nccl_load(err)) { fprintf(stderr, "ekfslam_b200: %s\n", err.c_str()); return EKF_ENCCL; }
+    ncclUniqueId id;
+    if (g_nccl.GetUniqueId(&id) != ncclSuccess) return EKF_ENCCL;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    memcpy(id128, &id, 128);
+    return EKF_OK;
+}
+
 extern "C" const char* ekf_version(void) { return "ekfslam_b200 0.1 (sm_100a)"; }
 
 extern "C" int32_t ekf_params_default(ekf_params* p, int32_t variant) {
@@ -87,7 +162,9 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd);
-    cudaFree(h->Bpk); cudaFree(h->lin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
+    cudaFree(h->Pc); cudaFree(h->Bc);
+    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    cudaFree(h->lin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -96,13 +173,13 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
 
 static int32_t init_state(ekf_handle* h) {
     // x = [0 0 0], P = 0.1*eye(3), s = []   (EKF_SLAM.m:28-31)
-    CK(cudaMemsetAsync(h->P, 0, sizeof(double) * h->ld * h->cap_n, h->stream));
+    CK(cudaMemsetAsync(h->P, 0, sizeof(double) * h->ld * (h->c_hi - h->c_lo), h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemsetAsync(h->s, 0, sizeof(double) * (h->p.capacity_landmarks + 1), h->stream));
     CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
     CK(cudaMemsetAsync(h->Bd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
     const double d = 0.1;
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 3 && h->rank == 0; ++i)
         CK(cudaMemcpyAsync(h->P + i + i * h->ld, &d, sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     h->N = 0;
@@ -110,9 +187,14 @@ static int32_t init_state(ekf_handle* h) {
     return EKF_OK;
 }
 
-extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
+static int32_t create_common(const ekf_params* p, int rank, int world, const uint8_t* id128, ekf_handle** out) {
     if (!p || !out || p->capacity_landmarks < 1) return EKF_EINVAL;
     *out = nullptr;
+    if (world < 1 || rank < 0 || rank >= world || (world > 1 && !id128)) return EKF_EINVAL;
+    if (world > 1 && (p->storage != EKF_STORAGE_FULL || p->capacity_landmarks < world)) {
+        fprintf(stderr, "ekfslam_b200: sharded filters use EKF_STORAGE_FULL and need capacity_landmarks >= world\n");
+        return EKF_EINVAL;
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= p->device) {
         fprintf(stderr, "ekfslam_b200: no CUDA device %d (this library has no CPU fallback)\n", p->device);
@@ -120,22 +202,30 @@ extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
     }
     ekf_handle* h = new ekf_handle();
     h->p = *p;
+    h->rank = rank;
+    h->world = world;
     h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
     if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) g_downdate_variant = atoi(v);
-    if (const char* v = getenv("EKF_DOWNDATE_CCH")) g_downdate_cch = atoi(v) < 64 ? 64 : (atoi(v) / 8) * 8;
     int32_t rc = [&]() -> int32_t {
         CK(cudaSetDevice(p->device));
         if (p->stream) { h->stream = (cudaStream_t)(uintptr_t)p->stream; }
         else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
         h->cap_n = 3 + 2 * p->capacity_landmarks;
         h->ld = ((int64_t)h->cap_n + 15) / 16 * 16;
-        CK(cudaMalloc(&h->P, sizeof(double) * h->ld * h->cap_n));
+        ekf_slab_range(p->capacity_landmarks, world, rank, &h->c_lo, &h->c_hi);
+        CK(cudaMalloc(&h->P, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
+        if (world > 1) {
+            if (!nccl_load(h->err)) return EKF_ENCCL;
+            CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS));
+            CK(cudaMalloc(&h->Bc, sizeof(double2) * EKF_MAX_DEFER * EKF_MAX_SLOTS));
+            ncclUniqueId id;
+            memcpy(&id, id128, 128);
+            CKN(g_nccl.CommInitRank(&h->comm, world, id, rank));
+        }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
         CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
         CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
-        CK(cudaMalloc(&h->Bpk, sizeof(double) * h->ld * 16));
-        CK(cudaMemset(h->Bpk, 0, sizeof(double) * h->ld * 16));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
         CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
@@ -150,6 +240,22 @@ extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) {
         return rc;
     }
     *out = h;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_create(const ekf_params* p, ekf_handle** out) { return create_common(p, 0, 1, nullptr, out); }
+
+extern "C" int32_t ekf_create_sharded(const ekf_params* p, int32_t rank, int32_t world, const uint8_t* id128,
+                                      ekf_handle** out) {
+    return create_common(p, rank, world, id128, out);
+}
+
+extern "C" int32_t ekf_shard_info(ekf_handle* h, int32_t* rank, int32_t* world, int32_t* c_lo, int32_t* c_hi) {
+    CKH(h);
+    if (rank) *rank = h->rank;
+    if (world) *world = h->world;
+    if (c_lo) *c_lo = h->c_lo;
+    if (c_hi) *c_hi = h->c_hi;
     return EKF_OK;
 }
 
@@ -180,14 +286,78 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     if (!u) return fail(h, EKF_EINVAL, "u is null");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
-    launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+    if (h->world > 1)
+        launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C);
+    else
+        launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     h->launches += 2;
     CK(cudaGetLastError());
     return EKF_OK;
 }
 
 // Apply the m_pend pending rank-2 terms to P in one pass (the K3 kernel).
+static int32_t prof_begin(ekf_handle* h) {
+    if (!h->prof) return EKF_OK;
+    if (h->ev_used + 2 > h->ev.size()) {
+        size_t old = h->ev.size();
+        h->ev.resize(old + 512);
+        for (size_t i = old; i < h->ev.size(); ++i) CK(cudaEventCreate(&h->ev[i]));
+    }
+    CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
+    return EKF_OK;
+}
+static int32_t prof_end(ekf_handle* h) {
+    if (!h->prof) return EKF_OK;
+    CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
+    h->ev_used += 2;
+    return EKF_OK;
+}
+
+// Sharded flush = execute the queued batch: one exchange of the 3 + 2k owner columns, k communication-free
+// linearise/gain steps replicated on every rank, one rank-2k pass over the local slab.
+static int32_t flush_sharded(ekf_handle* h) {
+    const int k = (int)h->q.size();
+    if (k == 0) return EKF_OK;
+    const int n = n_of(h);
+    SlotSet ss;
+    ss.n = 3 + 2 * k;
+    ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
+    for (int m = 0; m < k; ++m) { ss.col[3 + 2 * m] = h->q[m].a; ss.col[4 + 2 * m] = h->q[m].a + 1; }
+    launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld);
+    CK(cudaGetLastError());
+    CKN(g_nccl.GroupStart());
+    CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
+    for (int m = 0; m < k; ++m) {
+        double* p = h->Pc + (size_t)(3 + 2 * m) * h->ld;
+        CKN(g_nccl.Broadcast(p, p, 2 * (size_t)h->ld, ncclDouble, owner_of_col(h, h->q[m].a), h->comm, h->stream));
+    }
+    CKN(g_nccl.GroupEnd());
+    for (int m = 0; m < k; ++m) {
+        const ekf_handle::QObs& o = h->q[m];
+        launch_lin_gain_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n, o.a, 3 + 2 * m, o.z0, o.z1, o.R0, o.R1,
+                              ss, h->Pc, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m);
+    }
+    h->launches += 1 + 2 * k;
+    CK(cudaGetLastError());
+    const int ncl = ncols_loc(h);
+    if (ncl > 0) {
+        int32_t rc = prof_begin(h);
+        if (rc != EKF_OK) return rc;
+        launch_downdate(h->stream, h->P, h->ld, n, ncl, 0, h->Kd, h->Bd + h->c_lo, h->ld, k);
+        rc = prof_end(h);
+        if (rc != EKF_OK) return rc;
+        h->dd_launches += 1;
+        h->dd_terms += k;
+        h->launches += 1;
+        CK(cudaGetLastError());
+    }
+    h->q.clear();
+    h->m_pend = 0;
+    return EKF_OK;
+}
+
 static int32_t flush(ekf_handle* h) {
+    if (h->world > 1) return flush_sharded(h);
     if (h->m_pend == 0) return EKF_OK;
     if (h->prof) {
         if (h->ev_used + 2 > h->ev.size()) {
@@ -197,7 +367,7 @@ static int32_t flush(ekf_handle* h) {
         }
         CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
     }
-    launch_downdate(h->stream, h->P, h->ld, n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend, h->Bpk);
+    launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend);
     if (h->prof) {
         CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
         h->ev_used += 2;
@@ -223,8 +393,14 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
         return fail(h, EKF_EINVAL, "ekf_update: landmark index " + std::to_string(idx1) + " outside 1.." + std::to_string(h->N));
     CK(cudaSetDevice(h->p.device));
     const int a = 3 + 2 * (idx1 - 1);
+    if (h->world > 1) {                   // queue; the batch runs at the next flush point
+        h->q.push_back({z[0], z[1], Rdiag[0], Rdiag[1], a});
+        h->m_pend = (int)h->q.size();
+        if (h->m_pend >= h->defer) FLUSH(h);
+        return EKF_OK;
+    }
     launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
-                          h->lin, h->Kd, h->Bd, h->ld, h->m_pend, h->Bpk);
+                          h->lin, h->Kd, h->Bd, h->ld, h->m_pend);
     h->launches += 2;
     CK(cudaGetLastError());
     h->m_pend += 1;
@@ -240,6 +416,14 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
         return fail(h, EKF_ECAPACITY, "ekf_append: capacity_landmarks=" + std::to_string(h->p.capacity_landmarks) + " reached");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
+    if (h->world > 1) {                   // the new rows need P(:,1:3): one 3-column broadcast from rank 0
+        SlotSet ss; ss.n = 3; ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
+        launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n_of(h), h->Pc, h->ld);
+        CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
+        launch_append_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1],
+                            pos[0], pos[1], signature, h->Pc, h->ld);
+        h->launches += 1;
+    } else
     launch_append(h->stream, h->P, h->ld, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1], pos[0], pos[1],
                   signature, sym_of(h));
     h->launches += 1;
@@ -254,6 +438,8 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
     if (!z || !Rdiag || !newLL || !idx1) return fail(h, EKF_EINVAL, "null argument");
     if (h->N == 0) { *newLL = 1; *idx1 = 1; return EKF_OK; }   // Correspondence.m:33,40 with an empty loop
     CK(cudaSetDevice(h->p.device));
+    if (h->world > 1 && h->p.assoc_mode == EKF_ASSOC_POSITION)
+        return fail(h, EKF_EINVAL, "ekf_associate: position-cost association is not available on a sharded filter");
     if (h->p.assoc_mode == EKF_ASSOC_POSITION) FLUSH(h);      // mode B reads P blocks; mode A only s
     launch_associate(h->stream, h->P, h->ld, h->x, h->s, h->N, z[0], z[1], z[2], Rdiag[0], Rdiag[1],
                      h->p.s_cost, h->p.s_thresh, h->p.assoc_mode, sym_of(h), h->partial, h->ticket, h->d_res);
@@ -264,6 +450,19 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
     *newLL = h->h_res->newLL;
     *idx1 = h->h_res->index1;
     return EKF_OK;
+}
+
+// k updates with explicit slots: the update branch of measure() (EKF_SLAM.m:124-145) for a batch whose
+// correspondences are already decided.  z is k x 2 and Rdiag k x 2, column-major like observed_LL.
+extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, const double* Rdiag, const int32_t* idx1) {
+    CKH(h);
+    if (k < 0 || (k > 0 && (!z || !Rdiag || !idx1))) return fail(h, EKF_EINVAL, "null argument");
+    for (int i = 0; i < k; ++i) {
+        const double zi[2] = {z[i], z[i + k]}, Ri[2] = {Rdiag[i], Rdiag[i + k]};
+        int32_t rc = ekf_update(h, zi, Ri, idx1[i]);
+        if (rc != EKF_OK) return rc;
+    }
+    return flush(h);
 }
 
 // measure() control flow, EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151 (host-driven in this revision).
@@ -322,6 +521,7 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     CKH(h);
     if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
     CK(cudaSetDevice(h->p.device));
+    if (h->world > 1) FLUSH(h);           // sharded: x of queued observations is produced by the batch
     CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return EKF_OK;
@@ -341,6 +541,7 @@ extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
     CKH(h);
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_get_P: lda < n");
+    if (h->world > 1) return fail(h, EKF_EINVAL, "ekf_get_P: sharded filter, read the local slab with ekf_get_P_block");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
@@ -356,10 +557,13 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
     const int n = n_of(h);
     if (!out || r0 < 0 || c0 < 0 || nr < 1 || nc < 1 || r0 + nr > n || c0 + nc > n || ldo < nr)
         return fail(h, EKF_EINVAL, "ekf_get_P_block: bad block");
+    if (c0 < h->c_lo || c0 + nc > h->c_hi)
+        return fail(h, EKF_EINVAL, "ekf_get_P_block: columns outside this rank's slab [" + std::to_string(h->c_lo) + "," +
+                                       std::to_string(h->c_hi) + ")");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
-    CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, h->P + r0 + (int64_t)c0 * h->ld, sizeof(double) * h->ld,
+    CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, h->P + r0 + (int64_t)(c0 - h->c_lo) * h->ld, sizeof(double) * h->ld,
                          sizeof(double) * nr, nc, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return EKF_OK;
@@ -377,9 +581,14 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemcpy2DAsync(h->P, sizeof(double) * h->ld, P, sizeof(double) * lda, sizeof(double) * n, n,
-                         cudaMemcpyHostToDevice, h->stream));
+    {
+        const int hi = std::min(h->c_hi, n);
+        if (hi > h->c_lo)
+            CK(cudaMemcpy2DAsync(h->P, sizeof(double) * h->ld, P + (size_t)h->c_lo * lda, sizeof(double) * lda,
+                                 sizeof(double) * n, hi - h->c_lo, cudaMemcpyHostToDevice, h->stream));
+    }
     CK(cudaStreamSynchronize(h->stream));
+    h->q.clear();
     h->N = N;
     return EKF_OK;
 }
@@ -401,7 +610,8 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
-    launch_init_lowrank(h->stream, h->P, h->ld, n, dA, r, dd);
+    launch_init_lowrank(h->stream, h->P, h->ld, n, h->c_lo, std::min(h->c_hi, n) - h->c_lo, dA, r, dd);
+    h->q.clear();
     h->launches += 1;
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(h->stream));
@@ -443,6 +653,7 @@ extern "C" int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes) {
     CKH(h);
     if (!bytes) return fail(h, EKF_EINVAL, "bytes is null");
     const double n = (double)n_of(h);
+    if (h->world > 1) { *bytes = 16.0 * n * (double)ncols_loc(h); return EKF_OK; }   // local slab, FULL storage
     *bytes = sym_of(h) ? 8.0 * n * (n + 1.0) : 16.0 * n * n;   // read + write of every live element
     return EKF_OK;
 }

@@ -102,7 +102,7 @@ __global__ void k_linearize(const double* __restrict__ P, int64_t ld, const doub
 // Row i of P H' (5-column gather), K = (P H') phi^-1, x += K nu, and column i of B = H P.
 __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int a, int sym,
                        const Lin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball,
-                       int64_t lds, int m, double* __restrict__ Bpk) {
+                       int64_t lds, int m) {
     __shared__ Lin L;
     if (threadIdx.x < sizeof(Lin) / sizeof(double)) ((double*)&L)[threadIdx.x] = ((const double*)lin)[threadIdx.x];
     __syncthreads();
@@ -127,10 +127,6 @@ __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restr
     x[i] = x[i] + (k0 * L.nu[0] + k1 * L.nu[1]);               // EKF_SLAM.m:144
     Kall[m * lds + i] = make_double2(k0, k1);                  // slot m is not read by ldP_def (q < m)
     Ball[m * lds + i] = make_double2(b0, b1);
-    // packed copy for the tensor-core flush: column i owns 16 doubles; element e = 2m+comp sits at (e%4)*4 + e/4
-    // so that MMA lane t = e%4 finds its k-step values s = e/4 contiguous (one LDG.256 per 8x8 group).
-    Bpk[(int64_t)i * 16 + ((2 * m) & 3) * 4 + ((2 * m) >> 2)] = b0;
-    Bpk[(int64_t)i * 16 + ((2 * m + 1) & 3) * 4 + ((2 * m + 1) >> 2)] = b1;
 }
 
 // ------------------------------------------------------------------ K5 append
@@ -315,7 +311,7 @@ template <> struct VecIO<4> {
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
 __global__ void __launch_bounds__(BLOCK)
-k_downdate(double* __restrict__ P, int64_t ld, int n, int sym,
+k_downdate(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds) {
     constexpr int TR = BLOCK * VEC;
     typedef VecIO<VEC> IO;
@@ -325,7 +321,7 @@ k_downdate(double* __restrict__ P, int64_t ld, int n, int sym,
     __shared__ double2 Bs[TC * M];                    // Bs[j*M + q] = B_q(:, c0+j)
     for (int t = threadIdx.x; t < TC * M; t += BLOCK) {
         int j = t / M, q = t - j * M;
-        Bs[t] = (c0 + j < n) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
+        Bs[t] = (c0 + j < ncols) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
     }
     __syncthreads();
     const int r = r0 + threadIdx.x * VEC;
@@ -336,7 +332,7 @@ k_downdate(double* __restrict__ P, int64_t ld, int n, int sym,
 #pragma unroll
         for (int q = 0; q < M; ++q) k[v * M + q] = Kall[q * lds + r + v];
     double* p = P + (int64_t)r + (int64_t)c0 * ld;
-    const int nc = min(TC, n - c0);
+    const int nc = min(TC, ncols - c0);
     int j = 0;
     for (; j + UNROLL <= nc; j += UNROLL) {
         typename IO::T v[UNROLL];
@@ -357,62 +353,6 @@ k_downdate(double* __restrict__ P, int64_t ld, int n, int sym,
     }
 }
 
-// K3 with a rotating register prefetch: D column loads stay in flight per thread while the 2*M FMAs of the
-// oldest one execute (the plain loop above alternates load and math phases, which costs bandwidth once M > 2).
-template <int M, int VEC, int BLOCK, int TC, int D>
-__global__ void __launch_bounds__(BLOCK)
-k_downdate_pf(double* __restrict__ P, int64_t ld, int n, int sym,
-              const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds) {
-    constexpr int TR = BLOCK * VEC;
-    typedef VecIO<VEC> IO;
-    const int r0 = blockIdx.x * TR;
-    const int c0 = blockIdx.y * TC;
-    if (sym && r0 > c0 + TC - 1) return;
-    const int r = r0 + threadIdx.x * VEC;
-    const int nc = min(TC, n - c0);
-    double* p = P + (int64_t)r + (int64_t)c0 * ld;
-    typename IO::T v[D];
-    const bool live = r < n;
-    if (live) {
-#pragma unroll
-        for (int u = 0; u < D; ++u)
-            if (u < nc) v[u] = IO::ld(p + (int64_t)u * ld);      // first D columns in flight before the prologue
-    }
-    __shared__ double2 Bs[TC * M];
-    for (int t = threadIdx.x; t < TC * M; t += BLOCK) {
-        int j = t / M, q = t - j * M;
-        Bs[t] = (c0 + j < n) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
-    }
-    __syncthreads();
-    if (!live) return;
-    double2 k[VEC * M];
-#pragma unroll
-    for (int vv = 0; vv < VEC; ++vv)
-#pragma unroll
-        for (int q = 0; q < M; ++q) k[vv * M + q] = Kall[q * lds + r + vv];
-#pragma unroll 1
-    for (int j = 0; j < nc; j += D) {
-#pragma unroll
-        for (int u = 0; u < D; ++u) {
-            const int jj = j + u;
-            if (jj < nc) {
-                typename IO::T c = v[u];
-#pragma unroll
-                for (int q = 0; q < M; ++q) IO::sub(c, k, M, q, Bs[jj * M + q]);
-                IO::st(p + (int64_t)jj * ld, c);
-                if (jj + D < nc) v[u] = IO::ld(p + (int64_t)(jj + D) * ld);
-            }
-        }
-    }
-}
-
-template <int M, int VEC, int BLOCK, int TC, int D>
-static void launch_dd_pf(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall,
-                         const double2* Ball, int64_t lds) {
-    dim3 grid((n + BLOCK * VEC - 1) / (BLOCK * VEC), (n + TC - 1) / TC);
-    k_downdate_pf<M, VEC, BLOCK, TC, D><<<grid, BLOCK, 0, st>>>(P, ld, n, sym, Kall, Ball, lds);
-}
-
 // ------------------------------------------------------------------ K3b rank-2M flush on FP64 tensor cores
 // Same update as k_downdate, contracted with mma.sync.m8n8k4.f64 (DMMA): for M >= 2 the flush is a SYRK-like
 // n x 2M x n contraction and the operands fit in a few fragment registers instead of VEC*M gains per thread,
@@ -430,7 +370,7 @@ __device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, double a, doub
 
 template <int KS, int TC, int UNROLL>      // KS = ceil(M/2) k-steps; 128 threads = 4 warps x 16 rows
 __global__ void __launch_bounds__(128)
-k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int sym,
+k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
                const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M) {
     constexpr int TR = 64;
     constexpr int SROW = 4 * KS + 4;                   // doubles per column in smem (+4 pad: 2-way max conflict)
@@ -441,7 +381,7 @@ k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int sym,
     __shared__ double Bs[TC * SROW];
     for (int e = threadIdx.x; e < TC * 2 * KS; e += 128) {
         int j = e / (2 * KS), q = e - j * (2 * KS);
-        double2 b = (c0 + j < n && q < M) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
+        double2 b = (c0 + j < ncols && q < M) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
         Bs[j * SROW + 2 * q] = b.x;
         Bs[j * SROW + 2 * q + 1] = b.y;
     }
@@ -469,7 +409,7 @@ k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int sym,
         bool ok[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
-            ok[u] = (g + u < NG) && (c0 + (g + u) * 8 + r < n);
+            ok[u] = (g + u < NG) && (c0 + (g + u) * 8 + r < ncols);
             if (ok[u]) v[u] = ld_stream4(p + (int64_t)(g + u) * 8 * ld);
             else { v[u].x = v[u].y = v[u].z = v[u].w = 0.0; }
         }
@@ -489,96 +429,24 @@ k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int sym,
     }
 }
 
-// K3c: sync-free variant.  A block is 4 independent warps (16 rows each); a work unit is 64 rows x CCH columns.
-// A-fragments come straight from the packed B copy (L1/L2 resident, 128 B per column): one LDG.256 per thread
-// per 8-column group next to the LDG.256 of P, both kept D groups ahead in a rotating register prefetch.
-template <int KS, int D>
-__global__ void __launch_bounds__(128)
-k_downdate_mma2(double* __restrict__ P, int64_t ld, int n, int sym, const double2* __restrict__ Kall, int64_t lds,
-                const double* __restrict__ Bpk, int M, int CCH) {
-    const int r0 = blockIdx.x * 64;
-    int cb = blockIdx.y * CCH;
-    const int ce = min(n, cb + CCH);
-    if (sym) {
-        if (r0 > ce - 1) return;                       // unit strictly below the diagonal
-        cb = max(cb, r0 & ~7);                         // columns left of the strip's first row are dead too
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int r = lane >> 2, t = lane & 3;
-    const int i0 = r0 + warp * 16;
-    if (i0 >= n) return;
-    double kf[2][KS];
-#pragma unroll
-    for (int s = 0; s < KS; ++s) {
-        const int q = 2 * s + (t >> 1);
-#pragma unroll
-        for (int tile = 0; tile < 2; ++tile) {
-            const int row = i0 + 4 * (r >> 1) + 2 * tile + (r & 1);
-            double2 kk = (q < M) ? Kall[q * lds + row] : make_double2(0.0, 0.0);
-            kf[tile][s] = -((t & 1) ? kk.y : kk.x);
-        }
-    }
-    const int ng = (ce - cb + 7) >> 3;
-    double* p = P + (int64_t)(i0 + 4 * t) + (int64_t)(cb + r) * ld;
-    const double* bp = Bpk + (int64_t)(cb + r) * 16 + t * 4;
-    const int64_t gstride = 8 * ld;
-    double4a v[D], a[D];
-#pragma unroll
-    for (int u = 0; u < D; ++u) {
-        const bool ok = (u < ng) && (cb + u * 8 + r < n);
-        if (ok) { v[u] = ld_stream4(p + u * gstride); a[u] = *reinterpret_cast<const double4a*>(bp + u * 128); }
-        else { v[u].x = v[u].y = v[u].z = v[u].w = 0.0; a[u] = v[u]; }
-    }
-#pragma unroll 1
-    for (int g = 0; g < ng; g += D) {
-#pragma unroll
-        for (int u = 0; u < D; ++u) {
-            const int gg = g + u;
-            if (gg < ng) {                              // warp-uniform
-                const bool ok = cb + gg * 8 + r < n;
-                double4a c = v[u];
-                const double av[4] = {a[u].x, a[u].y, a[u].z, a[u].w};
-#pragma unroll
-                for (int s = 0; s < KS; ++s) {
-                    dmma8x8x4(c.x, c.y, av[s], kf[0][s]);
-                    dmma8x8x4(c.z, c.w, av[s], kf[1][s]);
-                }
-                if (ok) st_stream4(p + (int64_t)gg * gstride, c);
-                const int gn = gg + D;                  // refill this slot D groups ahead
-                if (gn < ng && cb + gn * 8 + r < n) {
-                    v[u] = ld_stream4(p + (int64_t)gn * gstride);
-                    a[u] = *reinterpret_cast<const double4a*>(bp + (int64_t)gn * 128);
-                } else { v[u].x = v[u].y = v[u].z = v[u].w = 0.0; a[u] = v[u]; }
-            }
-        }
-    }
-}
-
-template <int KS, int D>
-static void launch_dd_mma2(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall, int64_t lds,
-                           const double* Bpk, int M, int cch) {
-    dim3 grid((n + 63) / 64, (n + cch - 1) / cch);
-    k_downdate_mma2<KS, D><<<grid, 128, 0, st>>>(P, ld, n, sym, Kall, lds, Bpk, M, cch);
-}
-
 template <int KS, int TC, int UNROLL>
-static void launch_dd_mma(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall,
+static void launch_dd_mma(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                           const double2* Ball, int64_t lds, int M) {
-    dim3 grid((n + 63) / 64, (n + TC - 1) / TC);
-    k_downdate_mma<KS, TC, UNROLL><<<grid, 128, 0, st>>>(P, ld, n, sym, Kall, Ball, lds, M);
+    dim3 grid((n + 63) / 64, (ncols + TC - 1) / TC);
+    k_downdate_mma<KS, TC, UNROLL><<<grid, 128, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M);
 }
 
 // ------------------------------------------------------------------ state initialisation helpers
-__global__ void k_init_lowrank(double* __restrict__ P, int64_t ld, int n, const double* __restrict__ A, int r,
+__global__ void k_init_lowrank(double* __restrict__ P, int64_t ld, int n, int c_lo, const double* __restrict__ A, int r,
                                const double* __restrict__ d) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    int j = blockIdx.y;
+    int j = c_lo + blockIdx.y;
     if (i >= n) return;
     double acc = 0.0;
     for (int q = 0; q < r; ++q) acc += A[i + (int64_t)q * n] * A[j + (int64_t)q * n];
     acc = acc / (double)r;
     if (i == j) acc += d[i];
-    P[(int64_t)i + (int64_t)j * ld] = acc;
+    P[(int64_t)i + (int64_t)(j - c_lo) * ld] = acc;
 }
 
 // SYM storage read-back: copy the live upper triangle onto the dead lower one (32x32 smem transpose).
@@ -607,72 +475,49 @@ void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, do
     k_predict_x<<<1, 1, 0, st>>>(x, u1, u2);
 }
 
+void launch_predict_x(cudaStream_t st, double* x, double u1, double u2) { k_predict_x<<<1, 1, 0, st>>>(x, u1, u2); }
+
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
-                           double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m,
-                           double* Bpk) {
+                           double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m) {
     k_linearize<<<1, 32, 0, st>>>(P, ld, x, a, z0, z1, R0, R1, sym, Kall, Ball, lds, m, lin);
-    k_gain<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, a, sym, lin, Kall, Ball, lds, m, Bpk);
+    k_gain<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, a, sym, lin, Kall, Ball, lds, m);
 }
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
-static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall, const double2* Ball,
+static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
                       int64_t lds) {
-    dim3 grid(cdiv(n, BLOCK * VEC), cdiv(n, TC));
-    k_downdate<M, VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, sym, Kall, Ball, lds);
+    dim3 grid(cdiv(n, BLOCK * VEC), cdiv(ncols, TC));
+    k_downdate<M, VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds);
 }
 
 int g_downdate_variant = 6;      // m >= 2: DMMA flush, 64 x 64 tiles (best measured, profiles/README.md); 0..3 CUDA cores
 
 // m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
-int g_downdate_cch = 512;
-
-void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int sym, const double2* Kall, const double2* Ball,
-                     int64_t lds, int m, const double* Bpk) {
+void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
+                     int64_t lds, int m) {
     const int v = g_downdate_variant;
-    if (m >= 2 && v >= 12) {
-#define DP(M_) \
-        if (v == 13) launch_dd_pf<M_, 2, 128, 128, 8>(st, P, ld, n, sym, Kall, Ball, lds); \
-        else if (v == 14) launch_dd_pf<M_, 2, 256, 64, 4>(st, P, ld, n, sym, Kall, Ball, lds); \
-        else if (v == 15) launch_dd_pf<M_, 2, 128, 64, 6>(st, P, ld, n, sym, Kall, Ball, lds); \
-        else launch_dd_pf<M_, 2, 128, 64, 4>(st, P, ld, n, sym, Kall, Ball, lds);
-        switch (m) { case 2: { DP(2) } break; case 3: { DP(3) } break; case 4: { DP(4) } break; case 5: { DP(5) } break;
-                     case 6: { DP(6) } break; case 7: { DP(7) } break; default: { DP(8) } break; }
-#undef DP
-        return;
-    }
-    if (m >= 2 && v >= 8) {
-        const int ks = (m + 1) / 2, cch = g_downdate_cch;
-#define DM2(KS_) \
-        if (v == 9) launch_dd_mma2<KS_, 6>(st, P, ld, n, sym, Kall, lds, Bpk, m, cch); \
-        else if (v == 10) launch_dd_mma2<KS_, 3>(st, P, ld, n, sym, Kall, lds, Bpk, m, cch); \
-        else if (v == 11) launch_dd_mma2<KS_, 8>(st, P, ld, n, sym, Kall, lds, Bpk, m, cch); \
-        else launch_dd_mma2<KS_, 4>(st, P, ld, n, sym, Kall, lds, Bpk, m, cch);
-        switch (ks) { case 1: { DM2(1) } break; case 2: { DM2(2) } break; case 3: { DM2(3) } break; default: { DM2(4) } break; }
-#undef DM2
-        return;
-    }
     if (m >= 2 && v >= 4) {
         const int ks = (m + 1) / 2;
 #define DM(KS_) \
-        if (v == 5) launch_dd_mma<KS_, 128, 8>(st, P, ld, n, sym, Kall, Ball, lds, m); \
-        else if (v == 6) launch_dd_mma<KS_, 64, 4>(st, P, ld, n, sym, Kall, Ball, lds, m); \
-        else if (v == 7) launch_dd_mma<KS_, 256, 4>(st, P, ld, n, sym, Kall, Ball, lds, m); \
-        else launch_dd_mma<KS_, 128, 4>(st, P, ld, n, sym, Kall, Ball, lds, m);
+        if (v == 5) launch_dd_mma<KS_, 128, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m); \
+        else if (v == 6) launch_dd_mma<KS_, 64, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m); \
+        else if (v == 7) launch_dd_mma<KS_, 256, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m); \
+        else launch_dd_mma<KS_, 128, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m);
         switch (ks) { case 1: { DM(1) } break; case 2: { DM(2) } break; case 3: { DM(3) } break; default: { DM(4) } break; }
 #undef DM
         return;
     }
 #define DD(M_) \
-    if (v == 1) launch_dd<M_, 2, 128, 64, 8>(st, P, ld, n, sym, Kall, Ball, lds); \
-    else if (v == 2) launch_dd<M_, 2, 256, 32, 4>(st, P, ld, n, sym, Kall, Ball, lds); \
-    else if (v == 3) launch_dd<M_, 2, 128, 32, 8>(st, P, ld, n, sym, Kall, Ball, lds); \
-    else launch_dd<M_, 2, 128, 32, 4>(st, P, ld, n, sym, Kall, Ball, lds);
+    if (v == 1) launch_dd<M_, 2, 128, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds); \
+    else if (v == 2) launch_dd<M_, 2, 256, 32, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds); \
+    else if (v == 3) launch_dd<M_, 2, 128, 32, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds); \
+    else launch_dd<M_, 2, 128, 32, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
     switch (m) {
         case 1:
-            if (v == 1) launch_dd<1, 2, 128, 64, 8>(st, P, ld, n, sym, Kall, Ball, lds);
-            else if (v == 2) launch_dd<1, 4, 64, 64, 8>(st, P, ld, n, sym, Kall, Ball, lds);
-            else if (v == 3) launch_dd<1, 4, 128, 64, 4>(st, P, ld, n, sym, Kall, Ball, lds);
-            else launch_dd<1, 4, 128, 32, 8>(st, P, ld, n, sym, Kall, Ball, lds);
+            if (v == 1) launch_dd<1, 2, 128, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
+            else if (v == 2) launch_dd<1, 4, 64, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
+            else if (v == 3) launch_dd<1, 4, 128, 64, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
+            else launch_dd<1, 4, 128, 32, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
             break;
         case 2: { DD(2) } break;
         case 3: { DD(3) } break;
@@ -700,9 +545,11 @@ void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double
                                                  (Cand*)partial, ticket, out);
 }
 
-void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, const double* A, int r, const double* d) {
-    dim3 grid(cdiv(n, 256), n);
-    k_init_lowrank<<<grid, 256, 0, st>>>(P, ld, n, A, r, d);
+void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo, int ncols, const double* A, int r,
+                         const double* d) {
+    if (ncols <= 0) return;
+    dim3 grid(cdiv(n, 256), ncols);
+    k_init_lowrank<<<grid, 256, 0, st>>>(P, ld, n, c_lo, A, r, d);
 }
 
 void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n) {

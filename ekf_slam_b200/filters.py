@@ -31,7 +31,7 @@ class _FilterBase:
     _VARIANT = L.VARIANT_KNOWN
 
     def __init__(self, capacity_landmarks=1024, storage='full', device=0, stream=0,
-                 assoc_mode='signature', defer_m=0):
+                 assoc_mode='signature', defer_m=0, rank=0, world=1, nccl_id=None):
         self._lib = L.load()
         p = L.EkfParams()
         L.check(None, self._lib.ekf_params_default(ct.byref(p), self._VARIANT))
@@ -43,7 +43,12 @@ class _FilterBase:
         p.stream = int(stream)
         self._p = p
         self._h = L._H()
-        rc = self._lib.ekf_create(ct.byref(p), ct.byref(self._h))
+        if world > 1:
+            idbuf = (ct.c_uint8 * 128).from_buffer_copy(bytes(nccl_id))
+            rc = self._lib.ekf_create_sharded(ct.byref(p), int(rank), int(world), idbuf, ct.byref(self._h))
+        else:
+            rc = self._lib.ekf_create(ct.byref(p), ct.byref(self._h))
+        self.rank, self.world = int(rank), int(world)
         if rc != L.EKF_OK:
             raise L.EkfError(rc, 'ekf_create failed (CUDA device required; there is no CPU fallback)')
         self._C = p.C
@@ -168,6 +173,28 @@ class _FilterBase:
     def update(self, z, R, idx):
         """Update branch of measure for one observation -- EKF_SLAM.m:124-145."""
         self._ck(self._lib.ekf_update(self._h, L.dptr(_f64(z, 2)), L.dptr(_rdiag(R)), int(idx)))
+
+    def update_batch(self, z, Rdiag, idx):
+        """k updates with explicit slots (z, Rdiag: k x 2; idx: k, 1-based), then a flush."""
+        z = np.asfortranarray(np.asarray(z, dtype=np.float64).reshape(-1, 2))
+        Rd = np.asfortranarray(np.asarray(Rdiag, dtype=np.float64).reshape(-1, 2))
+        ix = np.ascontiguousarray(np.asarray(idx, dtype=np.int32))
+        self._ck(self._lib.ekf_update_batch(self._h, z.shape[0], L.dptr(z), L.dptr(Rd), L.iptr(ix)))
+
+    def shard_info(self):
+        """(rank, world, c_lo, c_hi): this rank stores columns [c_lo, c_hi) of P."""
+        v = [ct.c_int32() for _ in range(4)]
+        self._ck(self._lib.ekf_shard_info(self._h, *[ct.byref(q) for q in v]))
+        return tuple(q.value for q in v)
+
+    def P_slab(self):
+        """Active part of this rank's column slab, n x (columns owned and < n), plus its first column."""
+        _, _, c_lo, c_hi = self.shard_info()
+        n = 3 + 2 * self.N
+        hi = min(c_hi, n)
+        if hi <= c_lo:
+            return np.zeros((n, 0)), c_lo
+        return self.P_block(0, c_lo, n, hi - c_lo), c_lo
 
     def _tables(self, landmark_list):
         lst = landmark_list.landmarkObj.landmark

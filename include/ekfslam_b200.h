@@ -68,12 +68,28 @@ int32_t ekf_params_default(ekf_params* p, int32_t variant);
 int32_t ekf_create(const ekf_params* p, ekf_handle** out);
 int32_t ekf_destroy(ekf_handle* h);
 
+/* One large filter across `world` GPUs (one process per GPU): rank g stores the column slab
+ * [c_lo, c_hi) of the column-major P (by symmetry the "row slab" of a row-major view), x/s/gains replicated.
+ * Every rank makes the same calls with the same arguments; per batch of <= defer_m observations the only
+ * exchange is an NCCL broadcast of the 3 robot columns and the 2 columns of each observed landmark.
+ * id128 = 128 bytes from ekf_nccl_unique_id() on rank 0, distributed by the host (MPI, torch.distributed, file).
+ * Sharded filters use EKF_STORAGE_FULL; ekf_get_P_block reads local columns only; association mode B is
+ * not available.  (The reference has no counterpart: EKF_SLAM.m is single-process.) */
+int32_t ekf_nccl_unique_id(uint8_t* id128);
+int32_t ekf_create_sharded(const ekf_params* p, int32_t rank, int32_t world, const uint8_t* id128, ekf_handle** out);
+int32_t ekf_shard_info(ekf_handle* h, int32_t* rank, int32_t* world, int32_t* c_lo, int32_t* c_hi);
+/* Pure host helper: column range of `rank` for a given capacity (landmark-aligned, rank 0 holds the robot). */
+int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t* c_lo, int32_t* c_hi);
+
 /* predict(h,u): EKF_SLAM.m:40-51 (+ f, :56-65).  u = [dD, dtheta_deg]. */
 int32_t ekf_predict(ekf_handle* h, const double u[2]);
 
 /* Update branch of measure(): EKF_SLAM.m:124-145 == EKF_SLAM_UC.m:125-146.
  * z = [range, bearing_deg]; Rdiag = diag of R (EKF_SLAM.m:108); idx1 = 1-based landmark slot. */
 int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdiag[2], int32_t idx1);
+
+/* The same update for k observations whose slots are known (z, Rdiag: k x 2 column-major); ends with a flush. */
+int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, const double* Rdiag, const int32_t* idx1);
 
 /* append(h,u,R,landmarkPos,signature): EKF_SLAM.m:67-98 (append.m:1-27). */
 int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdiag[2],

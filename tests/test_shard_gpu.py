@@ -1,0 +1,25 @@
+"""Multi-GPU parity of the column-slab sharded filter (needs >= 2 GPUs on one box; skipped otherwise)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize('world', [2, 4])
+def test_sharded_filter_matches_oracle_and_single_gpu(world):
+    if _ngpu() < world:
+        pytest.skip('needs %d GPUs' % world)
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
+           '--master-addr', '127.0.0.1', '--master-port', str(29500 + world), os.path.join(ROOT, 'tests', 'shard_worker.py')]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    print(r.stdout[-4000:]); print(r.stderr[-4000:])
+    assert r.returncode == 0 and 'SHARD_WORKER_OK' in r.stdout
