@@ -40,7 +40,7 @@ SIGNATURES = {
     'ekf_nccl_unique_id': [C.POINTER(C.c_uint8)],
     'ekf_create_sharded': [C.POINTER(EkfParams), C.c_int32, C.c_int32, C.POINTER(C.c_uint8), C.POINTER(_H)],
     'ekf_shard_info': [_H, _IP, _IP, _IP, _IP],
-    'ekf_slab_range': [C.c_int32, C.c_int32, C.c_int32, _IP, _IP],
+    'ekf_slab_range': [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _IP, _IP],
     'ekf_update_batch': [_H, C.c_int32, _DP, _DP, _IP],
     'ekf_predict': [_H, _DP],
     'ekf_update': [_H, _DP, _DP, C.c_int32],

@@ -6,6 +6,7 @@
 
 #include <nccl.h>
 #include <dlfcn.h>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -78,6 +79,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -91,7 +93,7 @@ static bool nccl_load(std::string& err) {
     *(void**)(&g_nccl.field) = dlsym(so, name); \
     if (!g_nccl.field) { err = std::string("dlsym ") + name; return false; }
     SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
-    SYM(Broadcast, "ncclBroadcast") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
+    SYM(Broadcast, "ncclBroadcast") SYM(AllReduce, "ncclAllReduce") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
     SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
     g_nccl.so = so;
@@ -106,18 +108,30 @@ static bool nccl_load(std::string& err) {
 
 // Slab partition: landmark-aligned contiguous column ranges, balanced on capacity.  Rank 0 also owns the robot
 // columns 0..2; a landmark's two columns never straddle a boundary.
-static inline int slab_first_landmark(int capN, int world, int g) { return (int)((int64_t)g * capN / world); }
-extern "C" int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t* c_lo, int32_t* c_hi) {
+// FULL storage: equal column counts.  SYM storage: column j has j+1 live rows, so equal live area puts the
+// boundaries at capN * sqrt(g / world).
+static inline int slab_first_landmark(int capN, int world, int g, int storage) {
+    if (g <= 0) return 0;
+    if (g >= world) return capN;
+    if (storage == EKF_STORAGE_SYM) {
+        int l = (int)llround((double)capN * sqrt((double)g / (double)world));
+        return std::min(std::max(l, g), capN - (world - g));      // every rank keeps at least one landmark
+    }
+    return (int)((int64_t)g * capN / world);
+}
+extern "C" int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t storage,
+                                  int32_t* c_lo, int32_t* c_hi) {
     if (capacity_landmarks < 1 || world < 1 || rank < 0 || rank >= world || !c_lo || !c_hi) return EKF_EINVAL;
-    *c_lo = rank == 0 ? 0 : 3 + 2 * slab_first_landmark(capacity_landmarks, world, rank);
-    *c_hi = 3 + 2 * slab_first_landmark(capacity_landmarks, world, rank + 1);
+    if (capacity_landmarks < world) return EKF_EINVAL;
+    *c_lo = rank == 0 ? 0 : 3 + 2 * slab_first_landmark(capacity_landmarks, world, rank, storage);
+    *c_hi = 3 + 2 * slab_first_landmark(capacity_landmarks, world, rank + 1, storage);
     return EKF_OK;
 }
 static inline int owner_of_col(const ekf_handle* h, int col) {
     if (col < 3) return 0;
     const int l = (col - 3) / 2;
     for (int g = h->world - 1; g > 0; --g)
-        if (l >= slab_first_landmark(h->p.capacity_landmarks, h->world, g)) return g;
+        if (l >= slab_first_landmark(h->p.capacity_landmarks, h->world, g, h->p.storage)) return g;
     return 0;
 }
 static inline int ncols_loc(const ekf_handle* h) {      // active columns of the local slab
@@ -191,8 +205,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
     if (!p || !out || p->capacity_landmarks < 1) return EKF_EINVAL;
     *out = nullptr;
     if (world < 1 || rank < 0 || rank >= world || (world > 1 && !id128)) return EKF_EINVAL;
-    if (world > 1 && (p->storage != EKF_STORAGE_FULL || p->capacity_landmarks < world)) {
-        fprintf(stderr, "ekfslam_b200: sharded filters use EKF_STORAGE_FULL and need capacity_landmarks >= world\n");
+    if (world > 1 && p->capacity_landmarks < world) {
+        fprintf(stderr, "ekfslam_b200: sharded filters need capacity_landmarks >= world\n");
         return EKF_EINVAL;
     }
     int ndev = 0;
@@ -212,7 +226,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
         h->cap_n = 3 + 2 * p->capacity_landmarks;
         h->ld = ((int64_t)h->cap_n + 15) / 16 * 16;
-        ekf_slab_range(p->capacity_landmarks, world, rank, &h->c_lo, &h->c_hi);
+        ekf_slab_range(p->capacity_landmarks, world, rank, p->storage, &h->c_lo, &h->c_hi);
         CK(cudaMalloc(&h->P, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
         if (world > 1) {
             if (!nccl_load(h->err)) return EKF_ENCCL;
@@ -287,7 +301,7 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     if (h->world > 1)
-        launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C);
+        launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     else
         launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     h->launches += 2;
@@ -313,6 +327,28 @@ static int32_t prof_end(ekf_handle* h) {
     return EKF_OK;
 }
 
+// The one data-path collective: make the current columns of the slot set available on every rank.
+//   FULL slabs: broadcast each column from its owner (robot columns from rank 0).
+//   SYM  slabs: each rank contributes the part of every symmetric column it stores, zero elsewhere; all-reduce.
+static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
+    const int sym = sym_of(h);
+    launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld, sym);
+    CK(cudaGetLastError());
+    if (sym) {
+        CKN(g_nccl.AllReduce(h->Pc, h->Pc, (size_t)ss.n * h->ld, ncclDouble, ncclSum, h->comm, h->stream));
+    } else {
+        CKN(g_nccl.GroupStart());
+        CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
+        for (int sl = 3; sl + 1 < ss.n; sl += 2) {
+            double* p = h->Pc + (size_t)sl * h->ld;
+            CKN(g_nccl.Broadcast(p, p, 2 * (size_t)h->ld, ncclDouble, owner_of_col(h, ss.col[sl]), h->comm, h->stream));
+        }
+        CKN(g_nccl.GroupEnd());
+    }
+    h->launches += 1;
+    return EKF_OK;
+}
+
 // Sharded flush = execute the queued batch: one exchange of the 3 + 2k owner columns, k communication-free
 // linearise/gain steps replicated on every rank, one rank-2k pass over the local slab.
 static int32_t flush_sharded(ekf_handle* h) {
@@ -323,27 +359,20 @@ static int32_t flush_sharded(ekf_handle* h) {
     ss.n = 3 + 2 * k;
     ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
     for (int m = 0; m < k; ++m) { ss.col[3 + 2 * m] = h->q[m].a; ss.col[4 + 2 * m] = h->q[m].a + 1; }
-    launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld);
-    CK(cudaGetLastError());
-    CKN(g_nccl.GroupStart());
-    CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
-    for (int m = 0; m < k; ++m) {
-        double* p = h->Pc + (size_t)(3 + 2 * m) * h->ld;
-        CKN(g_nccl.Broadcast(p, p, 2 * (size_t)h->ld, ncclDouble, owner_of_col(h, h->q[m].a), h->comm, h->stream));
-    }
-    CKN(g_nccl.GroupEnd());
+    int32_t rcx = exchange_cols(h, ss, n);
+    if (rcx != EKF_OK) return rcx;
     for (int m = 0; m < k; ++m) {
         const ekf_handle::QObs& o = h->q[m];
         launch_lin_gain_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n, o.a, 3 + 2 * m, o.z0, o.z1, o.R0, o.R1,
-                              ss, h->Pc, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m);
+                              ss, h->Pc, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m, sym_of(h));
     }
-    h->launches += 1 + 2 * k;
+    h->launches += 2 * k;
     CK(cudaGetLastError());
     const int ncl = ncols_loc(h);
     if (ncl > 0) {
         int32_t rc = prof_begin(h);
         if (rc != EKF_OK) return rc;
-        launch_downdate(h->stream, h->P, h->ld, n, ncl, 0, h->Kd, h->Bd + h->c_lo, h->ld, k);
+        launch_downdate(h->stream, h->P, h->ld, n, ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, k, h->c_lo);
         rc = prof_end(h);
         if (rc != EKF_OK) return rc;
         h->dd_launches += 1;
@@ -418,8 +447,8 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
     FLUSH(h);
     if (h->world > 1) {                   // the new rows need P(:,1:3): one 3-column broadcast from rank 0
         SlotSet ss; ss.n = 3; ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
-        launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n_of(h), h->Pc, h->ld);
-        CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
+        int32_t rcx = exchange_cols(h, ss, n_of(h));
+        if (rcx != EKF_OK) return rcx;
         launch_append_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1],
                             pos[0], pos[1], signature, h->Pc, h->ld);
         h->launches += 1;
@@ -562,7 +591,7 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
                                        std::to_string(h->c_hi) + ")");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
-    if (sym_of(h)) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
+    if (sym_of(h) && h->world == 1) { launch_mirror_upper(h->stream, h->P, h->ld, n); h->launches += 1; CK(cudaGetLastError()); }
     CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, h->P + r0 + (int64_t)(c0 - h->c_lo) * h->ld, sizeof(double) * h->ld,
                          sizeof(double) * nr, nc, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
@@ -653,7 +682,11 @@ extern "C" int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes) {
     CKH(h);
     if (!bytes) return fail(h, EKF_EINVAL, "bytes is null");
     const double n = (double)n_of(h);
-    if (h->world > 1) { *bytes = 16.0 * n * (double)ncols_loc(h); return EKF_OK; }   // local slab, FULL storage
+    if (h->world > 1) {                                         // local slab
+        const double lo = (double)h->c_lo, hi = lo + (double)ncols_loc(h);
+        *bytes = sym_of(h) ? 8.0 * (hi * (hi + 1.0) - lo * (lo + 1.0)) : 16.0 * n * (hi - lo);
+        return EKF_OK;
+    }
     *bytes = sym_of(h) ? 8.0 * n * (n + 1.0) : 16.0 * n * n;   // read + write of every live element
     return EKF_OK;
 }

@@ -312,12 +312,12 @@ template <> struct VecIO<4> {
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
 __global__ void __launch_bounds__(BLOCK)
 k_downdate(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
-           const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds) {
+           const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int col_off) {
     constexpr int TR = BLOCK * VEC;
     typedef VecIO<VEC> IO;
     const int r0 = blockIdx.x * TR;
     const int c0 = blockIdx.y * TC;
-    if (sym && r0 > c0 + TC - 1) return;              // tile strictly below the diagonal: dead in SYM storage
+    if (sym && r0 > col_off + c0 + TC - 1) return;    // tile strictly below the diagonal: dead in SYM storage
     __shared__ double2 Bs[TC * M];                    // Bs[j*M + q] = B_q(:, c0+j)
     for (int t = threadIdx.x; t < TC * M; t += BLOCK) {
         int j = t / M, q = t - j * M;
@@ -371,13 +371,13 @@ __device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, double a, doub
 template <int KS, int TC, int UNROLL>      // KS = ceil(M/2) k-steps; 128 threads = 4 warps x 16 rows
 __global__ void __launch_bounds__(128)
 k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
-               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M) {
+               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, int col_off) {
     constexpr int TR = 64;
     constexpr int SROW = 4 * KS + 4;                   // doubles per column in smem (+4 pad: 2-way max conflict)
     constexpr int NG = TC / 8;
     const int r0 = blockIdx.x * TR;
     const int c0 = blockIdx.y * TC;
-    if (sym && r0 > c0 + TC - 1) return;
+    if (sym && r0 > col_off + c0 + TC - 1) return;
     __shared__ double Bs[TC * SROW];
     for (int e = threadIdx.x; e < TC * 2 * KS; e += 128) {
         int j = e / (2 * KS), q = e - j * (2 * KS);
@@ -431,9 +431,9 @@ k_downdate_mma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
 
 template <int KS, int TC, int UNROLL>
 static void launch_dd_mma(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                          const double2* Ball, int64_t lds, int M) {
+                          const double2* Ball, int64_t lds, int M, int col_off) {
     dim3 grid((n + 63) / 64, (ncols + TC - 1) / TC);
-    k_downdate_mma<KS, TC, UNROLL><<<grid, 128, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M);
+    k_downdate_mma<KS, TC, UNROLL><<<grid, 128, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, col_off);
 }
 
 // ------------------------------------------------------------------ state initialisation helpers
@@ -485,39 +485,39 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
 static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
-                      int64_t lds) {
+                      int64_t lds, int col_off) {
     dim3 grid(cdiv(n, BLOCK * VEC), cdiv(ncols, TC));
-    k_downdate<M, VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds);
+    k_downdate<M, VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
 }
 
 int g_downdate_variant = 6;      // m >= 2: DMMA flush, 64 x 64 tiles (best measured, profiles/README.md); 0..3 CUDA cores
 
 // m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
-                     int64_t lds, int m) {
+                     int64_t lds, int m, int col_off) {
     const int v = g_downdate_variant;
     if (m >= 2 && v >= 4) {
         const int ks = (m + 1) / 2;
 #define DM(KS_) \
-        if (v == 5) launch_dd_mma<KS_, 128, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m); \
-        else if (v == 6) launch_dd_mma<KS_, 64, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m); \
-        else if (v == 7) launch_dd_mma<KS_, 256, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m); \
-        else launch_dd_mma<KS_, 128, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m);
+        if (v == 5) launch_dd_mma<KS_, 128, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 6) launch_dd_mma<KS_, 64, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 7) launch_dd_mma<KS_, 256, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else launch_dd_mma<KS_, 128, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
         switch (ks) { case 1: { DM(1) } break; case 2: { DM(2) } break; case 3: { DM(3) } break; default: { DM(4) } break; }
 #undef DM
         return;
     }
 #define DD(M_) \
-    if (v == 1) launch_dd<M_, 2, 128, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds); \
-    else if (v == 2) launch_dd<M_, 2, 256, 32, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds); \
-    else if (v == 3) launch_dd<M_, 2, 128, 32, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds); \
-    else launch_dd<M_, 2, 128, 32, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
+    if (v == 1) launch_dd<M_, 2, 128, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off); \
+    else if (v == 2) launch_dd<M_, 2, 256, 32, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off); \
+    else if (v == 3) launch_dd<M_, 2, 128, 32, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off); \
+    else launch_dd<M_, 2, 128, 32, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
     switch (m) {
         case 1:
-            if (v == 1) launch_dd<1, 2, 128, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
-            else if (v == 2) launch_dd<1, 4, 64, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
-            else if (v == 3) launch_dd<1, 4, 128, 64, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
-            else launch_dd<1, 4, 128, 32, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds);
+            if (v == 1) launch_dd<1, 2, 128, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
+            else if (v == 2) launch_dd<1, 4, 64, 64, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
+            else if (v == 3) launch_dd<1, 4, 128, 64, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
+            else launch_dd<1, 4, 128, 32, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
             break;
         case 2: { DD(2) } break;
         case 3: { DD(3) } break;

@@ -16,7 +16,7 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m);
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                     const double2* Ball, int64_t lds, int m);
+                     const double2* Ball, int64_t lds, int m, int col_off = 0);   // col_off: global index of column 0 (SYM slabs)
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym);
 int  assoc_blocks(int N);
@@ -29,12 +29,12 @@ void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo
 void launch_predict_x(cudaStream_t st, double* x, double u1, double u2);
 // ---- column-slab sharded filter (ekf_shard.cu) ----
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                      double* Pc, int64_t ldc);
+                      double* Pc, int64_t ldc, int sym);
 void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, int a,
                            int sa, double z0, double z1, double R0, double R1, const SlotSet& ss, const double* Pc,
-                           int64_t ldc, Lin* lin, double2* Kall, double2* Ball, int64_t lds, double2* Bc, int m);
+                           int64_t ldc, Lin* lin, double2* Kall, double2* Ball, int64_t lds, double2* Bc, int m, int sym);
 void launch_predict_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, double u1,
-                          double u2, double C);
+                          double u2, double C, int sym);
 void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, double* s, int N,
                          double u1, double u2, double R0, double R1, double px, double py, double sig, const double* Pc,
                          int64_t ldc);

@@ -13,12 +13,35 @@
 
 namespace ekf {
 
+// SYM storage: Pc[slot] is the assembled symmetric column c = col(slot); its element i is the live element
+// (min(i,c), max(i,c)), whose pending correction is K_q(min) * B_q(max) with B_q = (P H')' known for all rows on
+// every rank (Ball) -- exactly what ldP_def computes on one GPU, so sharded SYM == single-GPU SYM bit for bit.
 __device__ __forceinline__ double cur_col(const double* __restrict__ Pc, int64_t ldc, int slot, int i,
                                           const double2* __restrict__ Kall, int64_t lds,
-                                          const double2* __restrict__ Bc, int m) {
+                                          const double2* __restrict__ Bc, int m,
+                                          int sym = 0, int c = 0, const double2* __restrict__ Ball = nullptr) {
     double v = Pc[(int64_t)slot * ldc + i];
-    for (int q = 0; q < m; ++q) v = rank2_sub(v, Kall[q * lds + i], Bc[q * EKF_MAX_SLOTS + slot]);
+    if (sym) {
+        const int lo = i <= c ? i : c, hi = i <= c ? c : i;
+        for (int q = 0; q < m; ++q) v = rank2_sub(v, Kall[q * lds + lo], Ball[q * lds + hi]);
+    } else {
+        for (int q = 0; q < m; ++q) v = rank2_sub(v, Kall[q * lds + i], Bc[q * EKF_MAX_SLOTS + slot]);
+    }
     return v;
+}
+
+// SYM slabs: every rank writes the part of each symmetric column it holds (zeros elsewhere); an all-reduce(sum)
+// then assembles the columns exactly (each element has one non-zero contributor).
+__global__ void k_pack_cols_sym(const double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, SlotSet ss, int n,
+                                double* __restrict__ Pc, int64_t ldc) {
+    const int slot = blockIdx.y;
+    const int c = ss.col[slot];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double v = 0.0;
+    if (i <= c) { if (c >= c_lo && c < c_hi) v = Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld]; }
+    else if (i >= c_lo && i < c_hi) v = Ploc[(int64_t)c + (int64_t)(i - c_lo) * ld];
+    Pc[(int64_t)slot * ldc + i] = v;
 }
 
 // Owner ranks copy their columns of the batch set into Pc (P0 is current: nothing is pending at batch start).
@@ -36,7 +59,7 @@ __global__ void k_pack_cols(const double* __restrict__ Ploc, int64_t ld, int c_l
 __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet ss, const double* __restrict__ x,
                             int a, int sa, double z0, double z1, double R0, double R1,
                             const double2* __restrict__ Kall, int64_t lds, double2* __restrict__ Bc, int m,
-                            Lin* __restrict__ lin) {
+                            Lin* __restrict__ lin, int sym, const double2* __restrict__ Ball) {
     __shared__ double Pcc[5][5];
     __shared__ double Hsm[2][5];
     const int lane = threadIdx.x;
@@ -44,7 +67,7 @@ __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet 
     const int sl[5] = {0, 1, 2, sa, sa + 1};
     if (lane < 25) {
         int i = lane / 5, j = lane % 5;
-        Pcc[i][j] = cur_col(Pc, ldc, sl[j], c[i], Kall, lds, Bc, m);          // P(c_i, c_j)
+        Pcc[i][j] = cur_col(Pc, ldc, sl[j], c[i], Kall, lds, Bc, m, sym, c[j], Ball);   // P(c_i, c_j)
     }
     __syncwarp();
     if (lane == 0) {
@@ -70,7 +93,7 @@ __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet 
         lin->nonfinite = bad;
     }
     __syncwarp();
-    if (lane < ss.n) {                                   // B_m(:, col(slot)) = H_m * cur(c, col(slot))
+    if (!sym && lane < ss.n) {                           // B_m(:, col(slot)) = H_m * cur(c, col(slot))
         double b0 = 0.0, b1 = 0.0;
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
@@ -86,7 +109,7 @@ __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet 
 __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, double* __restrict__ x,
                              int n, int a, int sa, const Lin* __restrict__ lin, const double* __restrict__ Pc,
                              int64_t ldc, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
-                             const double2* __restrict__ Bc, int m) {
+                             const double2* __restrict__ Bc, int m, int sym) {
     __shared__ Lin L;
     if (threadIdx.x < sizeof(Lin) / sizeof(double)) ((double*)&L)[threadIdx.x] = ((const double*)lin)[threadIdx.x];
     __syncthreads();
@@ -97,7 +120,7 @@ __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_
     double ph0 = 0.0, ph1 = 0.0;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-        double pc = cur_col(Pc, ldc, sl[k], i, Kall, lds, Bc, m);            // P(i, c_k)
+        double pc = cur_col(Pc, ldc, sl[k], i, Kall, lds, Bc, m, sym, c[k], Ball);   // P(i, c_k)
         ph0 += pc * L.Hs[0][k];
         ph1 += pc * L.Hs[1][k];
     }
@@ -105,7 +128,9 @@ __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_
     double k1 = ph0 * L.Sinv[0][1] + ph1 * L.Sinv[1][1];
     x[i] = x[i] + (k0 * L.nu[0] + k1 * L.nu[1]);
     Kall[m * lds + i] = make_double2(k0, k1);
-    if (i >= c_lo && i < c_hi) {
+    if (sym) {
+        Ball[m * lds + i] = make_double2(ph0, ph1);      // B = (P H')', all rows on every rank
+    } else if (i >= c_lo && i < c_hi) {
         const double* col = Ploc + (int64_t)(i - c_lo) * ld;
         double b0 = 0.0, b1 = 0.0;
 #pragma unroll
@@ -121,7 +146,7 @@ __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_
 
 // predict on a slab: the row pass is local to every owned column, the column pass and the corner live on rank 0.
 __global__ void k_predict_shard(double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, const double* __restrict__ x,
-                                int n, double u1, double u2, double C) {
+                                int n, double u1, double u2, double C, int sym) {
     const double th = x[2];
     const double st = sind(th), ct = cosd(th);
     const double a = -1.0 * u1 * st, b = u1 * ct;
@@ -129,7 +154,7 @@ __global__ void k_predict_shard(double* __restrict__ Ploc, int64_t ld, int c_lo,
     if (t == 0 && c_lo == 0) {
         double M[3][3];
         for (int i = 0; i < 3; ++i)
-            for (int j = 0; j < 3; ++j) M[i][j] = Ploc[i + j * ld];
+            for (int j = 0; j < 3; ++j) M[i][j] = (sym && i > j) ? Ploc[j + i * ld] : Ploc[i + j * ld];
         for (int j = 0; j < 3; ++j) { M[0][j] = M[0][j] + a * M[2][j]; M[1][j] = M[1][j] + b * M[2][j]; }
         for (int i = 0; i < 3; ++i) { M[i][0] = M[i][0] + M[i][2] * a; M[i][1] = M[i][1] + M[i][2] * b; }
         double W[3] = {u1 * ct, u1 * st, u2};
@@ -142,7 +167,7 @@ __global__ void k_predict_shard(double* __restrict__ Ploc, int64_t ld, int c_lo,
             col[0] = col[0] + a * p2;
             col[1] = col[1] + b * p2;
         }
-        if (c_lo == 0) {                                 // rank 0 owns columns 0..2
+        if (c_lo == 0 && !sym) {                         // rank 0 owns columns 0..2 (dead triangle in SYM)
             double q2 = Ploc[t + 2 * ld];
             Ploc[t] = Ploc[t] + q2 * a;
             Ploc[t + ld] = Ploc[t + ld] + q2 * b;
@@ -206,21 +231,22 @@ __global__ void k_append_shard(double* __restrict__ Ploc, int64_t ld, int c_lo, 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                      double* Pc, int64_t ldc) {
+                      double* Pc, int64_t ldc, int sym) {
     dim3 grid(cdiv(n, 256), ss.n);
-    k_pack_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, Pc, ldc);
+    if (sym) k_pack_cols_sym<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, Pc, ldc);
+    else k_pack_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, Pc, ldc);
 }
 
 void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, int a,
                            int sa, double z0, double z1, double R0, double R1, const SlotSet& ss, const double* Pc,
-                           int64_t ldc, Lin* lin, double2* Kall, double2* Ball, int64_t lds, double2* Bc, int m) {
-    k_lin_shard<<<1, 32, 0, st>>>(Pc, ldc, ss, x, a, sa, z0, z1, R0, R1, Kall, lds, Bc, m, lin);
-    k_gain_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, x, n, a, sa, lin, Pc, ldc, Kall, Ball, lds, Bc, m);
+                           int64_t ldc, Lin* lin, double2* Kall, double2* Ball, int64_t lds, double2* Bc, int m, int sym) {
+    k_lin_shard<<<1, 32, 0, st>>>(Pc, ldc, ss, x, a, sa, z0, z1, R0, R1, Kall, lds, Bc, m, lin, sym, Ball);
+    k_gain_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, x, n, a, sa, lin, Pc, ldc, Kall, Ball, lds, Bc, m, sym);
 }
 
 void launch_predict_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, double u1,
-                          double u2, double C) {
-    k_predict_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, x, n, u1, u2, C);
+                          double u2, double C, int sym) {
+    k_predict_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, x, n, u1, u2, C, sym);
     launch_predict_x(st, x, u1, u2);
 }
 

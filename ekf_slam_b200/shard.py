@@ -7,18 +7,20 @@ import numpy as np
 from . import _lib as L
 
 
-def slab_range(capacity_landmarks, world, rank):
-    """Columns [c_lo, c_hi) of P stored by `rank` (pure host arithmetic, no GPU needed)."""
+def slab_range(capacity_landmarks, world, rank, storage='full'):
+    """Columns [c_lo, c_hi) of P stored by `rank` (pure host arithmetic, no GPU needed).
+    'full': equal column counts; 'sym': equal live (upper-triangle) area."""
     lo, hi = ct.c_int32(), ct.c_int32()
-    rc = L.load().ekf_slab_range(int(capacity_landmarks), int(world), int(rank), ct.byref(lo), ct.byref(hi))
+    st = L.STORAGE_SYM if storage in ('sym', L.STORAGE_SYM) else L.STORAGE_FULL
+    rc = L.load().ekf_slab_range(int(capacity_landmarks), int(world), int(rank), st, ct.byref(lo), ct.byref(hi))
     if rc != L.EKF_OK:
         raise ValueError('bad slab query (capacity=%r world=%r rank=%r)' % (capacity_landmarks, world, rank))
     return lo.value, hi.value
 
 
-def owner_of_column(capacity_landmarks, world, col):
+def owner_of_column(capacity_landmarks, world, col, storage='full'):
     for g in range(world):
-        lo, hi = slab_range(capacity_landmarks, world, g)
+        lo, hi = slab_range(capacity_landmarks, world, g, storage)
         if lo <= col < hi:
             return g
     raise ValueError(col)
@@ -37,10 +39,10 @@ def nccl_id_via_torch(dist, device=None):
     return bytes(t.cpu().numpy().astype(np.uint8).tobytes())
 
 
-def create_sharded(cls, dist, device_index, **kw):
+def create_sharded(cls, dist, device_index, storage='full', **kw):
     """cls = EKF_SLAM / EKF_SLAM_UC.  Collective: every rank of `dist` calls it with the same arguments."""
     import torch
     dev = torch.device('cuda', device_index) if dist.get_backend() == 'nccl' else None
     nid = nccl_id_via_torch(dist, dev)
     return cls(device=device_index, rank=dist.get_rank(), world=dist.get_world_size(), nccl_id=nid,
-               storage='full', **kw)
+               storage=storage, **kw)

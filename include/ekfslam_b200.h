@@ -73,13 +73,16 @@ int32_t ekf_destroy(ekf_handle* h);
  * Every rank makes the same calls with the same arguments; per batch of <= defer_m observations the only
  * exchange is an NCCL broadcast of the 3 robot columns and the 2 columns of each observed landmark.
  * id128 = 128 bytes from ekf_nccl_unique_id() on rank 0, distributed by the host (MPI, torch.distributed, file).
- * Sharded filters use EKF_STORAGE_FULL; ekf_get_P_block reads local columns only; association mode B is
- * not available.  (The reference has no counterpart: EKF_SLAM.m is single-process.) */
+ * FULL slabs hold equal column counts and exchange by broadcast from the owners; SYM slabs hold equal live
+ * area (boundaries at capacity*sqrt(g/world)) and assemble symmetric columns with one all-reduce of zero-padded
+ * contributions (exact).  ekf_get_P_block reads local columns only (SYM: rows <= column are live, no
+ * mirroring); association mode B is not available.  (The reference has no counterpart: EKF_SLAM.m is single-process.) */
 int32_t ekf_nccl_unique_id(uint8_t* id128);
 int32_t ekf_create_sharded(const ekf_params* p, int32_t rank, int32_t world, const uint8_t* id128, ekf_handle** out);
 int32_t ekf_shard_info(ekf_handle* h, int32_t* rank, int32_t* world, int32_t* c_lo, int32_t* c_hi);
 /* Pure host helper: column range of `rank` for a given capacity (landmark-aligned, rank 0 holds the robot). */
-int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t* c_lo, int32_t* c_hi);
+int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t storage,
+                       int32_t* c_lo, int32_t* c_hi);
 
 /* predict(h,u): EKF_SLAM.m:40-51 (+ f, :56-65).  u = [dD, dtheta_deg]. */
 int32_t ekf_predict(ekf_handle* h, const double u[2]);

@@ -25,43 +25,54 @@ def main():
     dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     rank, world = dist.get_rank(), dist.get_world_size()
 
-    # (a) full loop, N = 20, 400 steps, both variants, deferred batches
-    for cls, ocls, mode in ((E.EKF_SLAM, O.EKF_SLAM, 'prefix'), (E.EKF_SLAM_UC, O.EKF_SLAM_UC, 'nearest')):
-        w = make_world(N=20, T=400, k=5, mode=mode)
-        g = E.shard.create_sharded(cls, dist, local, capacity_landmarks=20, defer_m=8)
-        o = ocls()
-        for t in range(w.T):
-            g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
-            o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
-        assert g.chosen == o.chosen
-        slab, c_lo = g.P_slab()
-        ex, eP = rel(g.x, o.x), rel(slab, o.P[:, c_lo:c_lo + slab.shape[1]])
-        assert ex <= 1e-9 and eP <= 1e-9, (cls.__name__, rank, ex, eP)
-        assert np.array_equal(g.s, o.s)
-        print('rank %d %s loop: N=%d slab cols [%d,%d) rel err x %.2e P %.2e' %
-              (rank, cls.__name__, g.N, c_lo, c_lo + slab.shape[1], ex, eP), flush=True)
-        g.close()
+    def live(slab, c_lo, storage):
+        """Mask of live elements of a slab: everything (FULL) or rows <= global column (SYM)."""
+        if storage == 'full':
+            return np.ones(slab.shape, dtype=bool)
+        i = np.arange(slab.shape[0])[:, None]
+        j = c_lo + np.arange(slab.shape[1])[None, :]
+        return i <= j
 
-    # (b) populated 1k map: sharded deferred batches vs single-GPU FULL immediate path, bitwise
-    N = 1000
-    x, A, d, s, lms = synthetic_spd_state(N, seed=3)
-    g = E.shard.create_sharded(E.EKF_SLAM, dist, local, capacity_landmarks=N, defer_m=8)
-    ref = E.EKF_SLAM(capacity_landmarks=N, storage='full', device=local)
-    for f in (g, ref):
-        f.set_state_lowrank(x, s, A, d)
-    rng = np.random.default_rng(11)
-    for step in range(4):
-        rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:11]
-        Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+    for storage in ('full', 'sym'):
+        # (a) full loop, N = 20, 400 steps, both variants, deferred batches
+        for cls, ocls, mode in ((E.EKF_SLAM, O.EKF_SLAM, 'prefix'), (E.EKF_SLAM_UC, O.EKF_SLAM_UC, 'nearest')):
+            w = make_world(N=20, T=400, k=5, mode=mode)
+            g = E.shard.create_sharded(cls, dist, local, storage=storage, capacity_landmarks=20, defer_m=8)
+            o = ocls()
+            for t in range(w.T):
+                g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
+                o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
+            assert g.chosen == o.chosen
+            slab, c_lo = g.P_slab()
+            mk = live(slab, c_lo, storage)
+            ex, eP = rel(g.x, o.x), rel(slab * mk, o.P[:, c_lo:c_lo + slab.shape[1]] * mk)
+            assert ex <= 1e-9 and eP <= 1e-9, (cls.__name__, rank, ex, eP)
+            assert np.array_equal(g.s, o.s)
+            print('rank %d %s/%s loop: N=%d slab cols [%d,%d) rel err x %.2e P %.2e' %
+                  (rank, cls.__name__, storage, g.N, c_lo, c_lo + slab.shape[1], ex, eP), flush=True)
+            g.close()
+
+        # (b) populated 1k map: sharded deferred batches vs single-GPU FULL immediate path, bitwise
+        N = 1000
+        x, A, d, s, lms = synthetic_spd_state(N, seed=3)
+        g = E.shard.create_sharded(E.EKF_SLAM, dist, local, storage=storage, capacity_landmarks=N, defer_m=8)
+        ref = E.EKF_SLAM(capacity_landmarks=N, storage=storage, device=local)
         for f in (g, ref):
-            f.predict([0.3, 1.0])
-            f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
-    slab, c_lo = g.P_slab()
-    Pref = ref.P
-    assert np.array_equal(g.x, ref.x), rel(g.x, ref.x)
-    assert np.array_equal(slab, Pref[:, c_lo:c_lo + slab.shape[1]]), rel(slab, Pref[:, c_lo:c_lo + slab.shape[1]])
-    print('rank %d populated 1k: slab bit-identical to the single-GPU FULL path' % rank, flush=True)
-    g.close(); ref.close()
+            f.set_state_lowrank(x, s, A, d)
+        rng = np.random.default_rng(11)
+        for step in range(4):
+            rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:11]
+            Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+            for f in (g, ref):
+                f.predict([0.3, 1.0])
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+        slab, c_lo = g.P_slab()
+        Pref = ref.P
+        assert np.array_equal(g.x, ref.x), rel(g.x, ref.x)
+        mk = live(slab, c_lo, storage)
+        assert np.array_equal(slab * mk, Pref[:, c_lo:c_lo + slab.shape[1]] * mk), rel(slab * mk, Pref[:, c_lo:c_lo + slab.shape[1]] * mk)
+        print('rank %d populated 1k/%s: slab bit-identical to the single-GPU path' % (rank, storage), flush=True)
+        g.close(); ref.close()
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
