@@ -1,0 +1,219 @@
+"""CPU tests of the oracle itself (no GPU): golden-vector regression, MATLAB helper known answers, the reference's
+quirks, and an independent 50-digit mpmath restatement of the update/predict/append algebra
+that pins the oracle's floating-point path to the exact value of the source expressions."""
+import numpy as np
+import pytest
+
+from oracle import dense_literal as O
+from oracle import matlab_compat as M
+from tests import golden_util as G
+
+
+# ---------------------------------------------------------------- golden vectors
+@pytest.mark.parametrize('name', list(G.CASES))
+def test_oracle_reproduces_golden(name):
+    g = G.load(name)
+    o = getattr(O, G.CASES[name])()
+    seen = []
+
+    def cp(i, f):
+        xg = g['x_checkpoints'][i]
+        live = ~np.isnan(xg)
+        assert live.sum() == f.x.size
+        seen.append(np.array_equal(xg[live], f.x))
+
+    acts = G.replay(o, g, cp)
+    assert np.array_equal(acts, g['actions'])
+    assert all(seen) and len(seen) == len(g['checkpoint_steps'])
+    assert np.array_equal(o.x, g['x_final']) and np.array_equal(o.P, g['P_final'])
+    assert np.array_equal(np.asarray(o.s, dtype=np.float64), g['s_final'])
+
+
+def test_golden_association_cases():
+    g = G.load('association_N12')
+    for q in range(len(g['z'])):
+        z, R = g['z'][q], np.diag(g['Rdiag'][q])
+        a = O.Correspondence(1e-11, 1e9, 'EKF_SLAM_UC').estimateCorrespondence(z, R, g['x'], g['P'], g['s'])
+        assert [int(a[0]), a[1]] == list(g['modeA'][q])
+        zB = z.copy(); zB[2] = 1.0
+        b = O.Correspondence(1e-11, 9.21, 'EKF_SLAM_UC', position_cost_in_score=True).estimateCorrespondence(
+            zB, R, g['x'], g['P'], np.ones(len(g['s'])))
+        assert [int(b[0]), b[1]] == list(g['modeB'][q])
+    new = g['modeA'][:, 0] == 1
+    assert new.sum() >= 8 and set(g['modeA'][new, 1]) == {13}     # unseen signature (incl. 5, which no landmark carries): default index N+1 (:40)
+    assert 5 not in set(g['modeA'][:, 1])          # landmark 5 shares signature 3: the first minimum (3) wins (:81)
+
+
+# ---------------------------------------------------------------- MATLAB helper semantics
+def test_degree_trig_known_answers():
+    for a, s, c in [(0, 0.0, 1.0), (90, 1.0, 0.0), (180, 0.0, -1.0), (270, -1.0, 0.0), (360, 0.0, 1.0), (-90, -1.0, 0.0),
+                    (450, 1.0, 0.0)]:
+        assert M.sind(a) == s and M.cosd(a) == c, a          # exact at multiples of 90 like MATLAB's sind/cosd
+    assert abs(M.sind(30) - 0.5) < 1e-16 and abs(M.cosd(60) - 0.5) < 1.2e-16
+    assert M.atan2d(1.0, 1.0) == 45.0 and M.atan2d(0.0, -1.0) == 180.0 and M.atan2d(-1.0, 0.0) == -90.0
+
+
+def test_wrapTo360_and_mod_semantics():
+    assert M.wrapTo360(360.0) == 360.0 and M.wrapTo360(0.0) == 0.0 and M.wrapTo360(-10.0) == 350.0
+    assert M.wrapTo360(720.0) == 360.0 and M.wrapTo360(370.5) == 10.5 and M.wrapTo360(-360.0) == 0.0
+    assert M.mod(-1.0, 360.0) == 359.0 and M.mod(725.0, 360.0) == 5.0   # sign follows the divisor
+
+
+def test_inv2_is_an_inverse():
+    A = np.array([[4.0, 1.0], [2.0, 3.0]])
+    assert np.allclose(M.inv2(A) @ A, np.eye(2), atol=1e-15)
+
+
+# ---------------------------------------------------------------- quirks the oracle must keep
+def _stub(rows, table):
+    from types import SimpleNamespace
+    return G.Stub(np.array(rows, dtype=np.float64).reshape(-1, 3),
+                  [SimpleNamespace(index=i, loc=np.array(l, dtype=np.float64)) for i, l in table])
+
+
+def test_constructor_defaults():
+    a, b = O.EKF_SLAM(), O.EKF_SLAM_UC()
+    assert np.array_equal(a.x, [0, 0, 0]) and np.array_equal(a.P, 0.1 * np.eye(3))            # EKF_SLAM.m:28-31
+    assert a.C == 0.2 and list(a.Rc) == [0.01, 5] and list(b.Rc) == [0.1, 5]                   # :12-13 / _UC:13
+    assert b.correspondence.s_cost == 1e-11 and b.correspondence.s_thresh == 1e9               # _UC:16
+
+
+def test_predict_uses_premotion_heading_and_leaves_landmarks():
+    o = O.EKF_SLAM()
+    o.measure(None, [1.0, 10.0], _stub([[2.0, 30.0, 1]], [(1, (2.0, 1.0))]))     # first sighting -> append (:110-111)
+    o.measure(None, [1.0, 10.0], _stub([[2.0, 30.0, 1], [3.0, 60.0, 2]], [(1, (2.0, 1.0)), (2, (1.0, 3.0))]))
+    assert o.chosen == [('append', 1), ('update', 1), ('append', 2)]
+    P0, x0 = o.P.copy(), o.x.copy()
+    u = [0.5, 20.0]
+    o.predict(u)
+    assert np.array_equal(o.P[3:, 3:], P0[3:, 3:]) and np.array_equal(o.x[3:], x0[3:])       # landmark block untouched
+    th = x0[2]
+    a, b = -u[0] * M.sind(th), u[0] * M.cosd(th)                                  # F(1,3), F(2,3) at the OLD heading
+    F = np.eye(7); F[0, 2] = a; F[1, 2] = b
+    W = np.array([u[0] * M.cosd(th), u[0] * M.sind(th), u[1]])
+    Q = np.zeros((7, 7)); Q[:3, :3] = np.outer(W * 0.2, W)
+    assert np.allclose(o.P, F @ P0 @ F.T + Q, rtol=1e-15, atol=1e-18)
+    assert o.x[2] == M.wrapTo360(th + u[1]) and o.x[0] == x0[0] + u[0] * M.cosd(th + u[1])
+
+
+def test_known_correspondence_updates_slot_ii_not_z3():
+    """EKF_SLAM.m:123 idx = ii: the row number picks the slot, z(3) only decides append (F8)."""
+    o = O.EKF_SLAM()
+    tab = [(1, (2.0, 1.0)), (2, (1.0, 3.0))]
+    o.measure(None, [1.0, 5.0], _stub([[2.0, 30.0, 1]], tab))
+    o.measure(None, [1.0, 5.0], _stub([[9.9, 99.0, 7], [3.0, 70.0, 2]], tab[:1] + [(7, (5.0, 5.0))] + tab[1:]))
+    assert o.chosen[1] == ('append', 7)            # z(3)=7 > N=1 -> append with signature 7
+    o.measure(None, [1.0, 5.0], _stub([[3.0, 70.0, 2]], tab))
+    assert o.chosen[-1] == ('update', 1)           # observation of landmark "2" in row 1 updates slot 1
+
+
+def test_first_landmark_branch_uses_signature_one():
+    o = O.EKF_SLAM_UC()
+    o.measure(None, [0.3, 1.0], _stub([[4.0, 100.0, 9]], [(9, (1.5, -2.5))]))
+    assert o.chosen == [('append', 1)] and list(o.s) == [1] and np.array_equal(o.x[3:], [1.5, -2.5])   # :112-113, F15
+
+
+def test_association_scores_signature_only_as_shipped():
+    """Correspondence.m:75: the Mahalanobis cost is computed and discarded; an absurd range still associates (F9)."""
+    c = O.Correspondence(1e-11, 1e9, 'EKF_SLAM_UC')
+    x = np.array([0, 0, 0, 5.0, 0.0, 0.0, 5.0])
+    P = 0.1 * np.eye(7)
+    s = np.array([1.0, 2.0])
+    assert c.estimateCorrespondence(np.array([500.0, 10.0, 2.0]), np.eye(2), x, P, s) == (False, 2)
+    assert c.estimateCorrespondence(np.array([5.0, 0.0, 2.1]), np.eye(2), x, P, s) == (True, 3)     # (0.1)^2/1e-11 = 1e9 is NOT <= 1e9? it is; 0.1**2 rounds above -> gate fails
+    assert O.Correspondence(1, 1, 'bogus').method == 'ML'                                            # :19-23
+
+
+def test_innovation_is_not_wrapped():
+    """EKF_SLAM.m:144: z - z_k across the 0/360 seam is ~-360 deg, and the oracle keeps it (F10)."""
+    o = O.EKF_SLAM()
+    o.measure(None, [0.0, 0.0], _stub([[5.0, 1.0, 1]], [(1, (5.0, 0.05))]))
+    x0, P0 = o.x.copy(), o.P.copy()
+    o.measure(None, [0.0, 0.0], _stub([[5.0, 359.9, 1]], [(1, (5.0, 0.05))]))    # predicted bearing ~0.57 deg
+    d = x0[3:5] - x0[:2]
+    q = d @ d
+    zk = np.array([np.sqrt(q), M.wrapTo360(M.atan2d(d[1], d[0]) - x0[2])])
+    H = (1 / q) * np.array([[-np.sqrt(q) * d[0], -np.sqrt(q) * d[1], 0, np.sqrt(q) * d[0], np.sqrt(q) * d[1]],
+                            [d[1], -d[0], -q, -d[1], d[0]]])
+    K = P0 @ H.T @ np.linalg.inv(H @ P0 @ H.T + np.diag([5.0 * 0.01, 359.9 * 5]))
+    nu = np.array([5.0, 359.9]) - zk
+    assert nu[1] > 359.0                                            # not wrapped to -0.67 deg
+    assert np.allclose(o.x, x0 + K @ nu, rtol=1e-12, atol=1e-15)
+    nu_wrapped = nu - np.array([0.0, 360.0])
+    assert not np.allclose(o.x, x0 + K @ nu_wrapped, rtol=1e-3)
+
+
+# ---------------------------------------------------------------- independent exact-arithmetic restatement
+def test_oracle_matches_50_digit_restatement():
+    """One predict + append + update sequence redone in mpmath (50 digits) straight from the reference expressions
+    (EKF_SLAM.m:42-47, :84-97, :125-145); the float64 oracle must agree to rounding (<= 1e-12 relative)."""
+    mp = pytest.importorskip('mpmath')
+    mp.mp.dps = 50
+    deg = mp.pi / 180
+    sind = lambda a: mp.sin(mp.mpf(a) * deg)
+    cosd = lambda a: mp.cos(mp.mpf(a) * deg)
+
+    o = O.EKF_SLAM()
+    x = mp.matrix([0, 0, 0]).T
+    P = mp.eye(3) * mp.mpf('0.1000000000000000055511151231257827')     # the double nearest 0.1, as the oracle holds it
+    seq = [('predict', [0.7, 12.0]), ('append', [0.7, 12.0], [0.04, 150.0], [3.0, 1.0]),
+           ('predict', [0.5, -7.0]), ('append', [0.5, -7.0], [0.02, 300.0], [-1.0, 4.0]),
+           ('update', [3.1, 14.0], [0.031, 70.0], 1), ('update', [4.2, 110.0], [0.042, 550.0], 2)]
+    for op in seq:
+        n = x.cols
+        if op[0] == 'predict':
+            u = [mp.mpf(v) for v in op[1]]
+            th = x[0, 2]
+            W = mp.matrix([u[0] * cosd(th), u[0] * sind(th), u[1]])
+            Q = mp.zeros(n, n)
+            Q[0:3, 0:3] = W * mp.mpf('0.2000000000000000111022302462515654') * W.T
+            F = mp.eye(n)
+            F[0, 2] = -u[0] * sind(th)
+            F[1, 2] = u[0] * cosd(th)
+            x[0, 0] += u[0] * cosd(th + u[1]); x[0, 1] += u[0] * sind(th + u[1]); x[0, 2] = th + u[1]
+            P = F * P * F.T + Q
+            o.predict(op[1])
+        elif op[0] == 'append':
+            u = [mp.mpf(v) for v in op[1]]
+            R = mp.diag([mp.mpf(v) for v in op[2]])
+            th = x[0, 2]
+            jxr = mp.matrix([[1, 0, -u[0] * sind(th)], [0, 1, u[0] * cosd(th)]])
+            jz = mp.matrix([[cosd(u[1]), -u[0] * sind(u[1])], [sind(u[1]), u[0] * cosd(u[1])]])
+            Pn = mp.zeros(n + 2, n + 2)
+            Pn[0:n, 0:n] = P
+            Pn[n:n + 2, n:n + 2] = jxr * P[0:3, 0:3] * jxr.T + jz * R * jz.T
+            Pn[0:3, n:n + 2] = P[0:3, 0:3] * jxr.T
+            Pn[n:n + 2, 0:3] = Pn[0:3, n:n + 2].T
+            for a in range(3, n, 2):
+                Pn[n:n + 2, a:a + 2] = jxr * P[a:a + 2, 0:3].T
+                Pn[a:a + 2, n:n + 2] = Pn[n:n + 2, a:a + 2].T
+            P = Pn
+            xn = mp.zeros(1, n + 2)
+            xn[0, 0:n] = x
+            xn[0, n] = mp.mpf(op[3][0]); xn[0, n + 1] = mp.mpf(op[3][1])
+            x = xn
+            o.append(op[1], np.diag(op[2]), op[3], (n - 3) // 2 + 1)
+        else:
+            z = [mp.mpf(v) for v in op[1]]
+            R = mp.diag([mp.mpf(v) for v in op[2]])
+            a = 3 + 2 * (op[3] - 1)
+            d = mp.matrix([x[0, a] - x[0, 0], x[0, a + 1] - x[0, 1]])
+            q = d[0] ** 2 + d[1] ** 2
+            brg = mp.atan2(d[1], d[0]) / deg - x[0, 2]
+            brg = brg - 360 * mp.floor(brg / 360)
+            zk = mp.matrix([mp.sqrt(q), brg])
+            Fk = mp.zeros(5, n)
+            for i in range(3):
+                Fk[i, i] = 1
+            Fk[3, a] = 1; Fk[4, a + 1] = 1
+            sq = mp.sqrt(q)
+            H = (1 / q) * mp.matrix([[-sq * d[0], -sq * d[1], 0, sq * d[0], sq * d[1]],
+                                     [d[1], -d[0], -q, -d[1], d[0]]]) * Fk
+            S = H * P * H.T + R
+            K = P * H.T * S ** -1
+            x = x + (K * (mp.matrix(z) - zk)).T
+            P = (mp.eye(n) - K * H) * P
+            o._update(np.array(op[1] + [op[3]], dtype=np.float64), np.diag(op[2]), op[3])
+    xe = np.array([float(v) for v in x], dtype=np.float64)
+    Pe = np.array([[float(P[i, j]) for j in range(P.cols)] for i in range(P.rows)])
+    assert G.rel(o.x, xe) <= 1e-12 and G.rel(o.P, Pe) <= 1e-12, (G.rel(o.x, xe), G.rel(o.P, Pe))

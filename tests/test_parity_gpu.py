@@ -267,3 +267,48 @@ def test_tensor_core_flush_matches_immediate(storage, defer_m, variant, monkeypa
     assert _rel(P1, P0) < 1e-13 and _rel(fs[1].x, fs[0].x) < 1e-13
     for f in fs:
         f.close()
+
+
+# ---------------------------------------------------------------- committed golden vectors (tests/golden/)
+@pytest.mark.parametrize('storage,defer_m', [('full', 0), ('sym', 0), ('sym', 8), ('full', 4)])
+@pytest.mark.parametrize('name', ['known_prefix_N20', 'known_quirk_N20', 'uc_nearest_N20', 'uc_nearest_N8_seed7'])
+def test_gpu_reproduces_golden_vectors(name, storage, defer_m):
+    """Same inputs as the committed fixtures: actions identical, x at every checkpoint and final x, P within 1e-9."""
+    import ekf_slam_b200 as E
+    from tests import golden_util as GU
+    g = GU.load(name)
+    f = getattr(E, GU.CASES[name])(capacity_landmarks=20, storage=storage, defer_m=defer_m)
+    errs = []
+
+    def cp(i, flt):
+        xg = g['x_checkpoints'][i]
+        xg = xg[~np.isnan(xg)]
+        errs.append(GU.rel(flt.x, xg))
+
+    acts = GU.replay(f, g, cp)
+    assert np.array_equal(acts, g['actions'])
+    assert len(errs) == len(g['checkpoint_steps']) and max(errs) <= 1e-9, errs
+    assert GU.rel(f.x, g['x_final']) <= 1e-9 and GU.rel(f.P, g['P_final']) <= 1e-9
+    assert np.array_equal(f.s, g['s_final'])
+    f.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+def test_gpu_golden_association_cases(storage):
+    import ekf_slam_b200 as E
+    from tests import golden_util as GU
+    g = GU.load('association_N12')
+    N = len(g['s'])
+    fa = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage)
+    fa.set_state(g['x'], g['P'], g['s'])
+    fb = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, assoc_mode='position')
+    fb.correspondence.s_thresh = 9.21
+    fb.set_state(g['x'], g['P'], np.ones(N))
+    for q in range(len(g['z'])):
+        z, R = g['z'][q], np.diag(g['Rdiag'][q])
+        a = fa.correspondence.estimateCorrespondence(z, R)
+        assert [int(a[0]), a[1]] == list(g['modeA'][q]), q
+        zB = z.copy(); zB[2] = 1.0
+        b = fb.correspondence.estimateCorrespondence(zB, R)
+        assert [int(b[0]), b[1]] == list(g['modeB'][q]), q
+    fa.close(); fb.close()
