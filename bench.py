@@ -289,7 +289,7 @@ def main():
                    'downdate': 'one rank-%d pass over P per %d observations' % (2 * min(args.defer, k), min(args.defer, k)) if args.defer > 1 else 'one rank-2 pass over P per observation',
                    'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one NCCL %s of the 3+2k current columns; slowest slab cols [%d,%d)' % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', slab[2], slab[3])) if world > 1 else 'single GPU',
                    'l2': 'no flush needed: each update streams %.2f GB of P, far beyond the 126 MB L2' % (dd_bytes / 2e9)},
-        'roofline': {'bound': 'hbm', 'kernel': 'k_downdate_mma (rank-%d flush, FP64 DMMA)' % (2 * min(args.defer, k)) if args.defer > 1 else 'k_downdate (rank-2)', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+        'roofline': {'bound': 'hbm', 'kernel': 'k_downdate_tma (rank-%d flush: cp.async.bulk staging + FP64 DMMA)' % (2 * min(max(args.defer, 1), k)), 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
                      'frac_of_8TBps_nominal': achieved / 8000.0, 'traffic': None,
                      'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,

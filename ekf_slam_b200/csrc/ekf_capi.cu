@@ -38,6 +38,7 @@ struct ekf_handle {
     std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
     int defer = 1;             // flush when m_pend reaches this (1 = immediate)
+    int dd_variant = -1;       // downdate kernel variant (-1 = library default; EKF_DOWNDATE_VARIANT env at create)
     Lin* lin = nullptr;
     void* partial = nullptr;
     unsigned int* ticket = nullptr;
@@ -219,7 +220,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
     h->rank = rank;
     h->world = world;
     h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
-    if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) g_downdate_variant = atoi(v);
+    if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) h->dd_variant = atoi(v);
     int32_t rc = [&]() -> int32_t {
         CK(cudaSetDevice(p->device));
         if (p->stream) { h->stream = (cudaStream_t)(uintptr_t)p->stream; }
@@ -372,7 +373,7 @@ static int32_t flush_sharded(ekf_handle* h) {
     if (ncl > 0) {
         int32_t rc = prof_begin(h);
         if (rc != EKF_OK) return rc;
-        launch_downdate(h->stream, h->P, h->ld, n, ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, k, h->c_lo);
+        launch_downdate(h->stream, h->P, h->ld, n, ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, k, h->c_lo, h->dd_variant);
         rc = prof_end(h);
         if (rc != EKF_OK) return rc;
         h->dd_launches += 1;
@@ -396,7 +397,7 @@ static int32_t flush(ekf_handle* h) {
         }
         CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
     }
-    launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend);
+    launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend, 0, h->dd_variant);
     if (h->prof) {
         CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
         h->ev_used += 2;

@@ -436,6 +436,179 @@ static void launch_dd_mma(cudaStream_t st, double* P, int64_t ld, int n, int nco
     k_downdate_mma<KS, TC, UNROLL><<<grid, 128, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, col_off);
 }
 
+// ------------------------------------------------------------------ K3c rank-2M flush, TMA-staged (bulk async copies)
+// Same arithmetic as k_downdate_mma (same fragments, same term order -> bit-identical), but P never travels
+// through registers on its way from/to HBM: a producer warp moves 128-row column segments (1 KB contiguous each)
+// global -> shared with cp.async.bulk + mbarrier complete_tx, 8 consumer warps update the stage in place with DMMA,
+// and the producer writes it back shared -> global with cp.async.bulk (bulk_group).  NSTAGE stages of SCOLS columns
+// ring through shared memory, so every SM keeps NSTAGE*SCOLS KB of reads in flight with one issuing warp and the
+// DRAM sees long contiguous bursts.  Columns sit CS = 1040 B apart in shared memory (1 KB + 16 B pad) so the
+// 8-column x 128-B fragment reads (LDS.128) are bank-conflict free.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1>
+struct TmaCfg {
+    static constexpr int TR = 128;                       // rows per CTA tile: 8 consumer warps x 16 rows
+    static constexpr int CS = TR * 8 + 16;               // bytes between columns of a stage in shared memory
+    static constexpr int SROW = 4 * KS + 4;              // doubles per column of the B operand
+    static constexpr int STAGE_BYTES = SCOLS * CS;
+    static constexpr int SMEM = NSTAGE * STAGE_BYTES + TC * SROW * 8 + 2 * NSTAGE * 8;
+    static constexpr int CWARPS = 8 * CG;                // consumer warps: CG sets of 8 (set c takes column groups c, c+CG, ..)
+    static constexpr int THREADS = (CWARPS + 1) * 32;    // + 1 producer warp
+};
+
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG>
+__global__ void __launch_bounds__((8 * CG + 1) * 32)
+k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
+               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, int col_off) {
+    typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
+    const int r0 = blockIdx.x * C::TR;
+    const int c0 = blockIdx.y * TC;
+    if (sym && r0 > col_off + c0 + TC - 1) return;       // tile strictly below the diagonal: dead in SYM storage
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* stage = smem;
+    double* Bs = (double*)(smem + NSTAGE * C::STAGE_BYTES);
+    uint64_t* bars = (uint64_t*)(smem + NSTAGE * C::STAGE_BYTES + TC * C::SROW * 8);
+    const uint32_t full0 = smem_u32(bars), done0 = smem_u32(bars + NSTAGE);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile_cols = min(TC, ncols - c0);
+    const int ns = (tile_cols + SCOLS - 1) / SCOLS;      // stages of this tile
+    const int rows_here = (int)min((int64_t)C::TR, ld - r0);     // ld is a multiple of 16 rows -> 128-byte multiple
+    const uint32_t col_bytes = (uint32_t)rows_here * 8u;
+
+    if (tid == 0) {
+        for (int i = 0; i < NSTAGE; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(done0 + 8 * i, C::CWARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int e = tid; e < TC * 2 * KS; e += C::THREADS) {        // B operand of the whole tile (zero beyond M / ncols)
+        int j = e / (2 * KS), q = e - j * (2 * KS);
+        double2 b = (j < tile_cols && q < M) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
+        Bs[j * C::SROW + 2 * q] = b.x;
+        Bs[j * C::SROW + 2 * q + 1] = b.y;
+    }
+    __syncthreads();
+
+    if (warp == C::CWARPS) {
+        // ------------------------------------------------ producer: lane c owns column c of every stage
+        const bool col_lane = lane < SCOLS;
+        auto load_stage = [&](int s) {
+            const int slot = s % NSTAGE;
+            const int nc = min(SCOLS, tile_cols - s * SCOLS);
+            if (lane == 0) mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)nc * col_bytes);
+            __syncwarp();
+            if (col_lane && lane < nc)
+                bulk_g2s(smem_u32(stage + slot * C::STAGE_BYTES + lane * C::CS),
+                         P + (int64_t)r0 + (int64_t)(c0 + s * SCOLS + lane) * ld, col_bytes, full0 + 8 * slot);
+        };
+        for (int s = 0; s < NSTAGE - 1 && s < ns; ++s) load_stage(s);
+        for (int s = 0; s < ns; ++s) {
+            const int slot = s % NSTAGE;
+            mbar_wait(done0 + 8 * slot, (s / NSTAGE) & 1);           // consumers finished stage s (writes fenced)
+            const int nc = min(SCOLS, tile_cols - s * SCOLS);
+            if (col_lane && lane < nc)
+                bulk_s2g(P + (int64_t)r0 + (int64_t)(c0 + s * SCOLS + lane) * ld,
+                         smem_u32(stage + slot * C::STAGE_BYTES + lane * C::CS), col_bytes);
+            bulk_commit();
+            const int s2 = s + NSTAGE - 1;                           // refill the slot stage s-1 was stored from
+            if (s2 < ns) {
+                if (s >= 1) bulk_wait_read<1>();                     // every group but the newest (stage s) has read its smem
+                __syncwarp();
+                load_stage(s2);
+            }
+        }
+        bulk_wait_read<0>();                                         // shared memory must outlive the last store's read
+        return;
+    }
+
+    // ---------------------------------------------------- consumers: warp w owns rows r0 + 16w .. +15
+    const int r = lane >> 2, t = lane & 3;
+    const int rw = warp & 7, cg = warp >> 3;                         // row-warp within the tile, consumer set
+    const int i0 = r0 + rw * 16;
+    const bool active = i0 < n;                                      // rows [n, ld) are padding: K is zero there
+    double kf[2][KS];
+#pragma unroll
+    for (int s = 0; s < KS; ++s) {
+        const int q = 2 * s + (t >> 1);
+#pragma unroll
+        for (int tile = 0; tile < 2; ++tile) {
+            const int row = i0 + 4 * (r >> 1) + 2 * tile + (r & 1);
+            double2 kk = (active && q < M) ? Kall[q * lds + row] : make_double2(0.0, 0.0);
+            kf[tile][s] = -((t & 1) ? kk.y : kk.x);
+        }
+    }
+    const int row_off = (rw * 16 + 4 * t) * 8;                     // byte offset of this thread's 4 rows in a column
+    for (int s = 0; s < ns; ++s) {
+        const int slot = s % NSTAGE;
+        mbar_wait(full0 + 8 * slot, (s / NSTAGE) & 1);
+        if (active) {
+            unsigned char* sb = stage + slot * C::STAGE_BYTES + row_off;
+#pragma unroll
+            for (int g = cg; g < SCOLS / 8; g += CG) {
+                const int cs = g * 8 + r;                            // column within the stage
+                const int ct = s * SCOLS + cs;                       // column within the tile
+                if (s * SCOLS + g * 8 >= tile_cols) break;           // warp-uniform: whole group beyond the tile
+                const bool ok = ct < tile_cols;                      // per-lane; mma.sync itself must stay warp-wide
+                double2* pv = (double2*)(sb + cs * C::CS);
+                double2 lo = make_double2(0.0, 0.0), hi = lo;
+                if (ok) { lo = pv[0]; hi = pv[1]; }
+                const double* bs = Bs + (ok ? ct : 0) * C::SROW + t;
+#pragma unroll
+                for (int ks = 0; ks < KS; ++ks) {
+                    const double a = bs[4 * ks];
+                    dmma8x8x4(lo.x, lo.y, a, kf[0][ks]);
+                    dmma8x8x4(hi.x, hi.y, a, kf[1][ks]);
+                }
+                if (ok) { pv[0] = lo; pv[1] = hi; }
+            }
+        }
+        fence_async_smem();                                          // generic-proxy writes -> visible to the bulk store
+        __syncwarp();
+        if (lane == 0) mbar_arrive(done0 + 8 * slot);
+    }
+}
+
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1>
+static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
+                          const double2* Ball, int64_t lds, int M, int col_off) {
+    typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        attr_set = true;
+    }
+    dim3 grid((unsigned)((ld + C::TR - 1) / C::TR), (ncols + TC - 1) / TC);
+    if ((int64_t)grid.x * C::TR > ld + C::TR - 1) return;
+    k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG><<<grid, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, col_off);
+}
+
 // ------------------------------------------------------------------ state initialisation helpers
 __global__ void k_init_lowrank(double* __restrict__ P, int64_t ld, int n, int c_lo, const double* __restrict__ A, int r,
                                const double* __restrict__ d) {
@@ -490,12 +663,31 @@ static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int ncols, 
     k_downdate<M, VEC, BLOCK, TC, UNROLL><<<grid, BLOCK, 0, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, col_off);
 }
 
-int g_downdate_variant = 6;      // m >= 2: DMMA flush, 64 x 64 tiles (best measured, profiles/README.md); 0..3 CUDA cores
 
 // m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
-                     int64_t lds, int m, int col_off) {
-    const int v = g_downdate_variant;
+                     int64_t lds, int m, int col_off, int variant) {
+    // variants: 0..3 CUDA-core DFMA (LDG/STG), 4..7 DMMA with LDG/STG fragments, >= 8 DMMA with bulk-async (TMA) staging
+    // default (variant < 0), from the B200 sweep in profiles/README.md: TMA staging everywhere; tile shape by rank
+    //   m == 1: 64 x 16-col stages, 2 consumer sets (v18)   m = 2..4: 64-col tiles, 6 x 8-col stages (v17)
+    //   m >= 5: 128-col tiles, 4 x 8-col stages, 4 CTAs/SM (v13)
+    const int v = variant >= 0 ? variant : (m == 1 ? 18 : (m <= 4 ? 17 : 13));
+    if (m >= 1 && v >= 8) {
+        const int ks = (m + 1) / 2;
+#define DT(KS_) \
+        if (v == 9) launch_dd_tma<KS_, 128, 16, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 11) launch_dd_tma<KS_, 128, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 13) launch_dd_tma<KS_, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 14) launch_dd_tma<KS_, 64, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 15) launch_dd_tma<KS_, 128, 8, 8>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 16) launch_dd_tma<KS_, 128, 16, 3, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 17) launch_dd_tma<KS_, 64, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else if (v == 18) launch_dd_tma<KS_, 64, 16, 4, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); \
+        else launch_dd_tma<KS_, 128, 16, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+        switch (ks) { case 1: { DT(1) } break; case 2: { DT(2) } break; case 3: { DT(3) } break; default: { DT(4) } break; }
+#undef DT
+        return;
+    }
     if (m >= 2 && v >= 4) {
         const int ks = (m + 1) / 2;
 #define DM(KS_) \

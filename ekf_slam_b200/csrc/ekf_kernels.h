@@ -16,7 +16,7 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m);
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                     const double2* Ball, int64_t lds, int m, int col_off = 0);   // col_off: global index of column 0 (SYM slabs)
+                     const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1);   // col_off: global index of column 0 (SYM slabs); variant < 0: default
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym);
 int  assoc_blocks(int N);
@@ -40,6 +40,7 @@ void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, in
                          int64_t ldc);
 void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n);
 
-extern int g_downdate_variant;   // tuning knob (EKF_DOWNDATE_VARIANT env), see launch_downdate
+// downdate kernel variant: < 0 = library default (TMA-staged DMMA flush, tile shape by rank; see launch_downdate);
+// the EKF_DOWNDATE_VARIANT environment variable overrides it per handle at ekf_create time.
 
 }  // namespace ekf

@@ -242,7 +242,7 @@ def test_deferred_full_loop_vs_oracle(variant):
 
 @pytest.mark.parametrize('storage', ['full', 'sym'])
 @pytest.mark.parametrize('defer_m', [2, 3, 8])
-@pytest.mark.parametrize('variant', ['0', '4', '6'])
+@pytest.mark.parametrize('variant', ['0', '4', '6', '8', '9', '11', '13', '14', '15', '16', '17', '18'])
 def test_tensor_core_flush_matches_immediate(storage, defer_m, variant, monkeypatch):
     """K3b (mma.sync.m8n8k4.f64 flush) vs the immediate CUDA-core path: same terms in the same order."""
     import ekf_slam_b200 as E
