@@ -40,6 +40,7 @@ struct ekf_handle {
     int defer = 1;             // flush when m_pend reaches this (1 = immediate)
     int dd_variant = -1;       // downdate kernel variant (-1 = library default; EKF_DOWNDATE_VARIANT env at create)
     Lin* lin = nullptr;
+    BatchLin* blin = nullptr;  // scratch of the fused batch linearisation (ekf_update_batch)
     void* partial = nullptr;
     unsigned int* ticket = nullptr;
     AssocResult* d_res = nullptr;
@@ -179,7 +180,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd);
     cudaFree(h->Pc); cudaFree(h->Bc);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    cudaFree(h->lin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
+    cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -242,11 +243,12 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
         CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
+        CK(cudaMalloc(&h->blin, sizeof(BatchLin)));
         CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
         CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
         CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
-        CK(cudaMalloc(&h->d_res, sizeof(AssocResult)));
-        CK(cudaMallocHost(&h->h_res, sizeof(AssocResult)));
+        CK(cudaMalloc(&h->d_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
+        CK(cudaMallocHost(&h->h_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
         return init_state(h);
     }();
     if (rc != EKF_OK) {
@@ -487,7 +489,31 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
 extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, const double* Rdiag, const int32_t* idx1) {
     CKH(h);
     if (k < 0 || (k > 0 && (!z || !Rdiag || !idx1))) return fail(h, EKF_EINVAL, "null argument");
-    for (int i = 0; i < k; ++i) {
+    CK(cudaSetDevice(h->p.device));
+    int i = 0;
+    if (h->world == 1 && h->defer >= 2 && k >= 2) {
+        // fused path: chunks of <= defer_m observations, 2 launches (k_batch_lin + k_batch_gain) + 1 flush per chunk
+        for (int j = 0; j < k; ++j)
+            if (idx1[j] < 1 || idx1[j] > h->N)
+                return fail(h, EKF_EINVAL, "ekf_update_batch: landmark index " + std::to_string(idx1[j]) + " outside 1.." + std::to_string(h->N));
+        FLUSH(h);
+        while (k - i >= 2) {
+            BatchObs ob;
+            ob.k = std::min(k - i, std::min(h->defer, EKF_BATCH_MAX));
+            for (int q = 0; q < ob.k; ++q) {
+                ob.z0[q] = z[i + q]; ob.z1[q] = z[i + q + k];
+                ob.R0[q] = Rdiag[i + q]; ob.R1[q] = Rdiag[i + q + k];
+                ob.a[q] = 3 + 2 * (idx1[i + q] - 1);
+            }
+            launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld);
+            h->launches += 2;
+            CK(cudaGetLastError());
+            h->m_pend = ob.k;
+            FLUSH(h);
+            i += ob.k;
+        }
+    }
+    for (; i < k; ++i) {
         const double zi[2] = {z[i], z[i + k]}, Ri[2] = {Rdiag[i], Rdiag[i + k]};
         int32_t rc = ekf_update(h, zi, Ri, idx1[i]);
         if (rc != EKF_OK) return rc;
@@ -506,42 +532,94 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
             if ((double)index_table[i] == want) { pos[0] = loc_table[i]; pos[1] = loc_table[i + n_table]; return true; }
         return false;
     };
+    // Updates whose slot is already decided are queued and applied through ekf_update_batch (fused linearise/gain,
+    // one rank-2m pass over P per defer_m of them); an append drains the queue first, so the order of EKF_SLAM.m:107 holds.
+    std::vector<double> qz0, qz1, qr0, qr1;
+    std::vector<int32_t> qidx;
+    auto drain = [&]() -> int32_t {
+        const int m = (int)qidx.size();
+        if (m == 0) return EKF_OK;
+        std::vector<double> zz(2 * m), rr(2 * m);
+        for (int i = 0; i < m; ++i) { zz[i] = qz0[i]; zz[i + m] = qz1[i]; rr[i] = qr0[i]; rr[i + m] = qr1[i]; }
+        int32_t rc = ekf_update_batch(h, m, zz.data(), rr.data(), qidx.data());
+        qz0.clear(); qz1.clear(); qr0.clear(); qr1.clear(); qidx.clear();
+        return rc;
+    };
+    auto queue_update = [&](const double z[3], const double Rd[2], int32_t idx) -> int32_t {
+        if (idx < 1 || idx > h->N)
+            return fail(h, EKF_EINVAL, "ekf_update: landmark index " + std::to_string(idx) + " outside 1.." + std::to_string(h->N));
+        qz0.push_back(z[0]); qz1.push_back(z[1]); qr0.push_back(Rd[0]); qr1.push_back(Rd[1]); qidx.push_back(idx);
+        return EKF_OK;
+    };
+    // Mode-A associations of rows [from, k) against the current s, <= EKF_ASSOC_BATCH per launch + one D2H copy.
+    const bool batch_assoc = h->p.variant == EKF_VARIANT_UC && h->p.assoc_mode == EKF_ASSOC_SIGNATURE;
+    int assoc_from = 0, assoc_to = 0;                                      // h_res[j - assoc_from] valid for j in [from, to)
+    auto associate_ahead = [&](int from) -> int32_t {
+        AssocBatchZ zb;
+        const int cnt = std::min(k - from, EKF_ASSOC_BATCH);
+        for (int j = 0; j < cnt; ++j) zb.z2[j] = obs[from + j + 2 * k];
+        CK(cudaSetDevice(h->p.device));
+        launch_associate_sig_batch(h->stream, h->s, h->N, zb, cnt, h->p.s_cost, h->p.s_thresh, h->d_res);
+        h->launches += 1;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult) * cnt, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        assoc_from = from; assoc_to = from + cnt;
+        return EKF_OK;
+    };
     for (int ii = 1; ii <= k; ++ii) {                                      // :107
         const double z[3] = {obs[ii - 1], obs[ii - 1 + k], obs[ii - 1 + 2 * k]};
         const double Rd[2] = {z[0] * h->p.Rc[0], z[1] * h->p.Rc[1]};       // :108
         double pos[2];
-        int32_t rc, act;
+        int32_t rc = EKF_OK, act;
         if (h->N == 0) {                                                   // :110  length(x) < 4
             bool ok = false;                                               // find([..index]) -> first non-zero index (F15)
             for (int i = 0; i < n_table && !ok; ++i)
                 if (index_table[i] != 0) { pos[0] = loc_table[i]; pos[1] = loc_table[i + n_table]; ok = true; }
             if (!ok) return fail(h, EKF_EINVAL, "measure: no indexed landmark in the table (EKF_SLAM.m:111)");
             rc = ekf_append(h, u, Rd, pos, 1.0);                           // :111
+            assoc_to = 0;                                                  // s changed
             act = -1;
         } else if (h->p.variant == EKF_VARIANT_KNOWN) {
             if (z[2] > (double)h->N) {                                     // :118
                 if (!loc_by_index(z[2], pos)) return fail(h, EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM.m:120)");
+                if ((rc = drain()) != EKF_OK) return rc;
                 rc = ekf_append(h, u, Rd, pos, z[2]);                      // :120
                 act = -(int32_t)z[2];
             } else {
-                rc = ekf_update(h, z, Rd, ii);                             // :123  idx = ii (row number)
+                rc = queue_update(z, Rd, ii);                              // :123  idx = ii (row number)
                 act = ii;
             }
         } else {
             int32_t newLL = 0, idx = 0;
-            rc = ekf_associate(h, z, Rd, &newLL, &idx);                    // EKF_SLAM_UC.m:119
-            if (rc != EKF_OK) return rc;
+            if (batch_assoc) {
+                if (ii - 1 >= assoc_to || ii - 1 < assoc_from) {
+                    if ((rc = associate_ahead(ii - 1)) != EKF_OK) return rc;
+                }
+                newLL = h->h_res[ii - 1 - assoc_from].newLL;               // EKF_SLAM_UC.m:119
+                idx = h->h_res[ii - 1 - assoc_from].index1;
+            } else {
+                if ((rc = drain()) != EKF_OK) return rc;                   // mode B scores against the current x, P
+                rc = ekf_associate(h, z, Rd, &newLL, &idx);                // EKF_SLAM_UC.m:119
+                if (rc != EKF_OK) return rc;
+            }
             if (newLL) {                                                   // :121
                 if (!loc_by_index((double)idx, pos)) return fail(h, EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM_UC.m:123)");
+                if ((rc = drain()) != EKF_OK) return rc;
                 rc = ekf_append(h, u, Rd, pos, (double)idx);               // :123
+                assoc_to = 0;                                              // s changed: later rows are re-associated
                 act = -idx;
             } else {
-                rc = ekf_update(h, z, Rd, idx);                            // :125-146
+                rc = queue_update(z, Rd, idx);                             // :125-146
                 act = idx;
             }
         }
         if (rc != EKF_OK) return rc;
         if (action_out) action_out[ii - 1] = act;
+    }
+    {
+        int32_t rc = drain();
+        if (rc != EKF_OK) return rc;
     }
     return flush(h);                                                       // P is whole again when measure() returns
 }

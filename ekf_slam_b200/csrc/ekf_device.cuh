@@ -136,6 +136,41 @@ __device__ __forceinline__ void innovation_cov(const double Hs[2][5], const doub
     Si[1][1] = __dmul_rn(S[0][0], id);
 }
 
+// Gain arithmetic shared by every path (per-observation k_gain, fused k_batch_*, sharded k_gain_shard): explicit FMA
+// forms in a fixed order, so that the three paths stay bit-identical to each other whatever the compiler would contract.
+//   ph  += P(i, c_k) * Hs(:,k)                 row i of P H'  (EKF_SLAM.m:143, left factor)
+//   b   += Hs(:,k) * P(c_k, i)                 column i of H P (EKF_SLAM.m:145, right factor; FULL storage)
+//   K(i,:) = ph * phi^-1 ; dx = K(i,:) * nu    (EKF_SLAM.m:143-144)
+__device__ __forceinline__ void ph_acc(double& ph0, double& ph1, double pc, double h0k, double h1k) {
+    ph0 = __fma_rn(pc, h0k, ph0);
+    ph1 = __fma_rn(pc, h1k, ph1);
+}
+__device__ __forceinline__ void b_acc(double& b0, double& b1, double pr, double h0k, double h1k) {
+    b0 = __fma_rn(h0k, pr, b0);
+    b1 = __fma_rn(h1k, pr, b1);
+}
+__device__ __forceinline__ void gain_from_ph(double ph0, double ph1, const double Sinv[2][2], const double nu[2],
+                                             double& k0, double& k1, double& dx) {
+    k0 = __fma_rn(ph1, Sinv[1][0], __dmul_rn(ph0, Sinv[0][0]));
+    k1 = __fma_rn(ph1, Sinv[1][1], __dmul_rn(ph0, Sinv[0][1]));
+    dx = __fma_rn(k1, nu[1], __dmul_rn(k0, nu[0]));
+}
+
+// Fused batch (ekf_update_batch on one GPU): k <= EKF_MAX_DEFER observations with known slots are linearised
+// back to back by ONE warp (k_batch_lin) from the (3+2k)^2 sub-block of P, then ONE grid-wide kernel (k_batch_gain)
+// produces all k gain slabs -- 2 launches per batch instead of 2 per observation.
+#define EKF_BATCH_MAX 8
+#define EKF_BATCH_SLOTS (3 + 2 * EKF_BATCH_MAX)
+struct BatchObs { double z0[EKF_BATCH_MAX], z1[EKF_BATCH_MAX], R0[EKF_BATCH_MAX], R1[EKF_BATCH_MAX]; int a[EKF_BATCH_MAX]; int k; };
+struct BatchLin {                       // written by k_batch_lin, read by k_batch_gain
+    double  Hs[EKF_BATCH_MAX][2][5];
+    double  Sinv[EKF_BATCH_MAX][2][2];
+    double  nu[EKF_BATCH_MAX][2];
+    double2 Kslot[EKF_BATCH_MAX][EKF_BATCH_SLOTS];   // K_q(col(slot), :)
+    double2 Bslot[EKF_BATCH_MAX][EKF_BATCH_SLOTS];   // B_q(:, col(slot))
+    int     nonfinite;
+};
+
 // ---- streaming vector access for the downdate (LDG.E.128/256 with L1 no-allocate) ----
 struct __align__(32) double4a { double x, y, z, w; };
 

@@ -113,20 +113,147 @@ __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restr
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
         double pc = ldP_def(P, ld, i, c[k], sym, Kall, Ball, lds, m);   // P(i, c_k)
-        ph0 += pc * L.Hs[0][k];
-        ph1 += pc * L.Hs[1][k];
+        ph_acc(ph0, ph1, pc, L.Hs[0][k], L.Hs[1][k]);
         if (!sym) {
             double pr = ldP_def(P, ld, c[k], i, 0, Kall, Ball, lds, m); // P(c_k, i): 2 sectors per column i
-            b0 += L.Hs[0][k] * pr;
-            b1 += L.Hs[1][k] * pr;
+            b_acc(b0, b1, pr, L.Hs[0][k], L.Hs[1][k]);
         }
     }
     if (sym) { b0 = ph0; b1 = ph1; }                           // B = (P H')' when P is symmetric
-    double k0 = ph0 * L.Sinv[0][0] + ph1 * L.Sinv[1][0];       // EKF_SLAM.m:143
-    double k1 = ph0 * L.Sinv[0][1] + ph1 * L.Sinv[1][1];
-    x[i] = x[i] + (k0 * L.nu[0] + k1 * L.nu[1]);               // EKF_SLAM.m:144
+    double k0, k1, dx;
+    gain_from_ph(ph0, ph1, L.Sinv, L.nu, k0, k1, dx);          // EKF_SLAM.m:143
+    x[i] = __dadd_rn(x[i], dx);                                // EKF_SLAM.m:144
     Kall[m * lds + i] = make_double2(k0, k1);                  // slot m is not read by ldP_def (q < m)
     Ball[m * lds + i] = make_double2(b0, b1);
+}
+
+// ------------------------------------------------------------------ K2b fused batch linearise + gain
+// ekf_update_batch on one GPU.  The k observations of a batch are applied strictly in order (each linearised at
+// the x and P left by the previous one, EKF_SLAM.m:107), but everything observation q+1 needs from observation q
+// lives in the slot set S = {0,1,2} + {a_p, a_p+1 : p < k}: x at S and the |S| x |S| block of P.  k_batch_lin
+// (one warp) walks the k linearisations on that block, keeping it current with the same rank2_sub chain the
+// deferred gathers use; k_batch_gain (one thread per state row) then rebuilds row i of every K_q / B_q from the
+// |S| entries P0(i, S) it loads once.  Same operands, same order, same primitives as k_linearize + k_gain run k
+// times: the results are bit-identical (tests/test_parity_gpu.py::test_fused_batch_is_bit_identical).
+__global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
+                            BatchObs ob, BatchLin* __restrict__ out) {
+    __shared__ double G[EKF_BATCH_SLOTS][EKF_BATCH_SLOTS + 1];
+    __shared__ double xs[EKF_BATCH_SLOTS];
+    __shared__ double2 Ks[EKF_BATCH_SLOTS], Bs[EKF_BATCH_SLOTS];
+    __shared__ double Hs[2][5], Sinv[2][2], nu[2];
+    __shared__ int col[EKF_BATCH_SLOTS];
+    __shared__ int bad;
+    const int lane = threadIdx.x;
+    const int k = ob.k, ns = 3 + 2 * k;
+    if (lane < ns) col[lane] = lane < 3 ? lane : ob.a[(lane - 3) >> 1] + ((lane - 3) & 1);
+    if (lane == 0) bad = 0;
+    __syncwarp();
+    for (int e = lane; e < ns * ns; e += 32) {
+        const int i = e / ns, j = e - i * ns;
+        G[i][j] = ldP(P, ld, col[i], col[j], sym);                 // nothing is pending at batch start
+    }
+    if (lane < ns) xs[lane] = x[col[lane]];
+    __syncwarp();
+    for (int q = 0; q < k; ++q) {
+        const int sa = 3 + 2 * q;
+        const int sl[5] = {0, 1, 2, sa, sa + 1};
+        if (lane == 0) {
+            double xr[3] = {xs[0], xs[1], xs[2]};
+            double zk[2], H[2][5], S[2][2], Si[2][2], Pl[5][5];
+            measurement_model(xr, xs[sa], xs[sa + 1], zk, H);
+            for (int i = 0; i < 5; ++i)
+                for (int j = 0; j < 5; ++j) Pl[i][j] = G[sl[i]][sl[j]];
+            const double Rd[2] = {ob.R0[q], ob.R1[q]};
+            innovation_cov(H, Pl, Rd, S, Si);
+            for (int r = 0; r < 2; ++r) {
+                for (int c = 0; c < 5; ++c) { Hs[r][c] = H[r][c]; out->Hs[q][r][c] = H[r][c]; }
+                for (int t = 0; t < 2; ++t) {
+                    Sinv[r][t] = Si[r][t]; out->Sinv[q][r][t] = Si[r][t];
+                    if (!isfinite(S[r][t]) || !isfinite(Si[r][t])) bad = 1;
+                }
+            }
+            nu[0] = ob.z0[q] - zk[0];                               // EKF_SLAM.m:144, not wrapped (F10)
+            nu[1] = ob.z1[q] - zk[1];
+            out->nu[q][0] = nu[0]; out->nu[q][1] = nu[1];
+        }
+        __syncwarp();
+        if (lane < ns) {
+            double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) {
+                ph_acc(ph0, ph1, G[lane][sl[c]], Hs[0][c], Hs[1][c]);          // P(col_i, c_k)
+                if (!sym) b_acc(b0, b1, G[sl[c]][lane], Hs[0][c], Hs[1][c]);   // P(c_k, col_i)
+            }
+            if (sym) { b0 = ph0; b1 = ph1; }
+            double k0, k1, dx;
+            gain_from_ph(ph0, ph1, Sinv, nu, k0, k1, dx);
+            xs[lane] = __dadd_rn(xs[lane], dx);
+            Ks[lane] = make_double2(k0, k1);
+            Bs[lane] = make_double2(b0, b1);
+            out->Kslot[q][lane] = Ks[lane];
+            out->Bslot[q][lane] = Bs[lane];
+        }
+        __syncwarp();
+        for (int e = lane; e < ns * ns; e += 32) {                 // keep the block current: P <- P - K_q B_q
+            const int i = e / ns, j = e - i * ns;
+            const bool up = !sym || col[i] <= col[j];              // SYM: the live element is (min, max)
+            G[i][j] = rank2_sub(G[i][j], up ? Ks[i] : Ks[j], up ? Bs[j] : Bs[i]);
+        }
+        __syncwarp();
+    }
+    if (lane == 0) out->nonfinite = bad;
+}
+
+__global__ void __launch_bounds__(128)
+k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, BatchObs ob,
+             const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds) {
+    __shared__ BatchLin L;
+    for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
+        ((double*)&L)[e] = ((const double*)lin)[e];
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int k = ob.k, ns = 3 + 2 * k;
+    double pc[EKF_BATCH_SLOTS], pr[EKF_BATCH_SLOTS];               // current P(i, col_s) and (FULL) P(col_s, i)
+    bool own[EKF_BATCH_SLOTS];                                     // SYM: element (i, col_s) is stored as (i, col_s), i <= col_s
+#pragma unroll
+    for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
+        pc[s] = 0.0; pr[s] = 0.0; own[s] = true;
+        if (s < ns) {
+            const int c = s < 3 ? s : ob.a[(s - 3) >> 1] + ((s - 3) & 1);
+            own[s] = !sym || i <= c;
+            pc[s] = ldP(P, ld, i, c, sym);
+            if (!sym) pr[s] = P[(int64_t)c + (int64_t)i * ld];
+        }
+    }
+    double xi = x[i];
+#pragma unroll
+    for (int q = 0; q < EKF_BATCH_MAX; ++q) {
+        if (q < k) {
+            double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) {
+                const int s = c < 3 ? c : 3 + 2 * q + (c - 3);
+                ph_acc(ph0, ph1, pc[s], L.Hs[q][0][c], L.Hs[q][1][c]);
+                if (!sym) b_acc(b0, b1, pr[s], L.Hs[q][0][c], L.Hs[q][1][c]);
+            }
+            if (sym) { b0 = ph0; b1 = ph1; }
+            double k0, k1, dx;
+            gain_from_ph(ph0, ph1, L.Sinv[q], L.nu[q], k0, k1, dx);
+            xi = __dadd_rn(xi, dx);
+            const double2 Ki = make_double2(k0, k1), Bi = make_double2(b0, b1);
+            Kall[q * lds + i] = Ki;
+            Ball[q * lds + i] = Bi;
+#pragma unroll
+            for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
+                if (s < ns) {
+                    pc[s] = own[s] ? rank2_sub(pc[s], Ki, L.Bslot[q][s]) : rank2_sub(pc[s], L.Kslot[q][s], Bi);
+                    if (!sym) pr[s] = rank2_sub(pr[s], L.Kslot[q][s], Bi);
+                }
+            }
+        }
+    }
+    x[i] = xi;
 }
 
 // ------------------------------------------------------------------ K5 append
@@ -275,6 +402,50 @@ __global__ void k_associate(const double* __restrict__ P, int64_t ld, const doub
             out->index1 = found ? bidx : N + 1;                // :40,84
             out->cost = best;
             *ticket = 0;
+        }
+    }
+}
+
+// Mode-A association for a whole measure() batch: the shipped score (Correspondence.m:75) depends only on z(3) and
+// the signature vector s, not on x or P, so the k observations of one measure() call can be gated in ONE launch
+// (block b = observation b) and read back with ONE copy; the host re-runs it only after an append changed s.
+__global__ void k_associate_sig_batch(const double* __restrict__ s, int N, AssocBatchZ zb, double s_cost,
+                                      double s_thresh, AssocResult* __restrict__ out) {
+    __shared__ double wc[32];
+    __shared__ int wi[32];
+    const double z2 = zb.z2[blockIdx.x];
+    const double inv = 1.0 / s_cost;
+    double best = CUDART_INF;
+    int bidx = INT_MAX;
+    for (int kk = threadIdx.x; kk < N; kk += blockDim.x) {         // ascending kk per thread: strict '<' keeps the first
+        double d = __dsub_rn(z2, s[kk]);
+        double ll = __dmul_rn(__dmul_rn(d, inv), d);               // Correspondence.m:71,75
+        if (ll <= s_thresh && ll < best) { best = ll; bidx = kk + 1; }   // :78,:81
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double oc = __shfl_down_sync(0xffffffffu, best, o);
+        int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+        if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { wc[w] = best; wi[w] = bidx; }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        best = (lane < nw) ? wc[lane] : CUDART_INF;
+        bidx = (lane < nw) ? wi[lane] : INT_MAX;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            double oc = __shfl_down_sync(0xffffffffu, best, o);
+            int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+            if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+        }
+        if (lane == 0) {
+            const bool found = (bidx != INT_MAX);
+            out[blockIdx.x].newLL = found ? 0 : 1;                 // :33,82
+            out[blockIdx.x].index1 = found ? bidx : N + 1;         // :40,84
+            out[blockIdx.x].cost = best;
         }
     }
 }
@@ -474,6 +645,37 @@ template <int N> __device__ __forceinline__ void bulk_wait_read() {
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Live-tile enumeration for the TMA flush.  Tiles are TR rows x TC columns with TR = RPC * TC (RPC = 1 or 2).  In SYM
+// storage column tile y keeps row tiles 0 .. min(R, f(y)) - 1, f(y) = floor((A + y) / RPC) + 1 with
+// A = floor((col_off + TC - 1) / TC): the tiles that touch the upper triangle.  Launching exactly those (1-D grid, column
+// tile major) instead of the R x CT rectangle removes ~half the CTAs of a SYM launch, which only existed to exit.
+struct TileMap { int R, CT, A, RPC, ystar; };      // ystar: first column tile whose live count is clipped at R
+__host__ __device__ inline long long tm_G(long long m, int r) {          // sum_{t<m} floor(t / r)
+    const long long q = m / r, rem = m % r;
+    return (long long)r * q * (q - 1) / 2 + q * rem;
+}
+__host__ __device__ inline long long tm_prefix(const TileMap& tm, int Y) {   // live tiles in column tiles [0, Y)
+    const int y1 = Y < tm.ystar ? Y : tm.ystar;
+    return tm_G((long long)tm.A + y1, tm.RPC) - tm_G(tm.A, tm.RPC) + y1 + (long long)tm.R * (Y - y1);
+}
+static inline TileMap tm_make(int R, int CT, int TC, int RPC, int col_off, int sym) {
+    TileMap tm;
+    tm.R = R; tm.CT = CT; tm.RPC = RPC;
+    tm.A = (col_off + TC - 1) / TC;
+    long long ys = sym ? (long long)RPC * (R - 1) - tm.A : 0;            // f(y) >= R  <=>  y >= RPC (R - 1) - A
+    tm.ystar = (int)(ys < 0 ? 0 : (ys > CT ? CT : ys));
+    return tm;
+}
+__device__ __forceinline__ void tm_decode(const TileMap& tm, long long t, int& bx, int& by) {
+    int lo = 0, hi = tm.CT - 1;                                          // largest by with prefix(by) <= t
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (tm_prefix(tm, mid) <= t) lo = mid; else hi = mid - 1;
+    }
+    by = lo;
+    bx = (int)(t - tm_prefix(tm, lo));
+}
+
 template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1>
 struct TmaCfg {
     static constexpr int TR = 128;                       // rows per CTA tile: 8 consumer warps x 16 rows
@@ -488,11 +690,12 @@ struct TmaCfg {
 template <int KS, int TC, int SCOLS, int NSTAGE, int CG>
 __global__ void __launch_bounds__((8 * CG + 1) * 32)
 k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
-               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, int col_off) {
+               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, TileMap tm) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
-    const int r0 = blockIdx.x * C::TR;
-    const int c0 = blockIdx.y * TC;
-    if (sym && r0 > col_off + c0 + TC - 1) return;       // tile strictly below the diagonal: dead in SYM storage
+    int bx, by;
+    tm_decode(tm, (long long)blockIdx.x, bx, by);        // only live tiles are launched (column tile major)
+    const int r0 = bx * C::TR;
+    const int c0 = by * TC;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* stage = smem;
     double* Bs = (double*)(smem + NSTAGE * C::STAGE_BYTES);
@@ -604,9 +807,12 @@ static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int nco
         cudaFuncSetAttribute(k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         attr_set = true;
     }
-    dim3 grid((unsigned)((ld + C::TR - 1) / C::TR), (ncols + TC - 1) / TC);
-    if ((int64_t)grid.x * C::TR > ld + C::TR - 1) return;
-    k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG><<<grid, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, col_off);
+    static_assert(C::TR % TC == 0 && (C::TR / TC == 1 || C::TR / TC == 2), "tile map needs TR = TC or 2 TC");
+    const int R = (n + C::TR - 1) / C::TR, CT = (ncols + TC - 1) / TC;   // row tiles cover the active rows only
+    const TileMap tm = tm_make(R, CT, TC, C::TR / TC, col_off, sym);
+    const long long live = tm_prefix(tm, CT);
+    if (live <= 0 || live > 0x7fffffffLL) return;
+    k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, tm);
 }
 
 // ------------------------------------------------------------------ state initialisation helpers
@@ -654,6 +860,12 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m) {
     k_linearize<<<1, 32, 0, st>>>(P, ld, x, a, z0, z1, R0, R1, sym, Kall, Ball, lds, m, lin);
     k_gain<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, a, sym, lin, Kall, Ball, lds, m);
+}
+
+void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
+                           BatchLin* lin, double2* Kall, double2* Ball, int64_t lds) {
+    k_batch_lin<<<1, 32, 0, st>>>(P, ld, x, sym, ob, lin);
+    k_batch_gain<<<cdiv(n, 128), 128, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds);
 }
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
@@ -735,6 +947,11 @@ void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double
                       int mode, int sym, void* partial, unsigned int* ticket, AssocResult* out) {
     k_associate<<<assoc_blocks(N), 256, 0, st>>>(P, ld, x, s, N, z0, z1, z2, R0, R1, s_cost, s_thresh, mode, sym,
                                                  (Cand*)partial, ticket, out);
+}
+
+void launch_associate_sig_batch(cudaStream_t st, const double* s, int N, const AssocBatchZ& zb, int k, double s_cost,
+                                double s_thresh, AssocResult* out) {
+    k_associate_sig_batch<<<k, 256, 0, st>>>(s, N, zb, s_cost, s_thresh, out);
 }
 
 void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo, int ncols, const double* A, int r,

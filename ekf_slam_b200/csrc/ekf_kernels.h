@@ -7,6 +7,8 @@ namespace ekf {
 
 struct Lin;
 struct AssocResult;
+struct BatchObs;
+struct BatchLin;
 
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym);
 #define EKF_MAX_DEFER 8
@@ -17,8 +19,15 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                      const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1);   // col_off: global index of column 0 (SYM slabs); variant < 0: default
+// fused batch (<= 8 observations with known slots; nothing may be pending): fills gain slabs 0..k-1 and updates x
+void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
+                           BatchLin* lin, double2* Kall, double2* Ball, int64_t lds);
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym);
+#define EKF_ASSOC_BATCH 32
+struct AssocBatchZ { double z2[EKF_ASSOC_BATCH]; };   // signatures z(3) of up to 32 observations (by value)
+void launch_associate_sig_batch(cudaStream_t st, const double* s, int N, const AssocBatchZ& zb, int k, double s_cost,
+                                double s_thresh, AssocResult* out);
 int  assoc_blocks(int N);
 void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double* x, const double* s, int N,
                       double z0, double z1, double z2, double R0, double R1, double s_cost, double s_thresh,

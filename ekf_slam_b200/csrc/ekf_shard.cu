@@ -98,8 +98,7 @@ __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet 
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
             double pr = cur_col(Pc, ldc, lane, c[k], Kall, lds, Bc, m);
-            b0 += Hsm[0][k] * pr;
-            b1 += Hsm[1][k] * pr;
+            b_acc(b0, b1, pr, Hsm[0][k], Hsm[1][k]);
         }
         Bc[m * EKF_MAX_SLOTS + lane] = make_double2(b0, b1);
     }
@@ -121,12 +120,11 @@ __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
         double pc = cur_col(Pc, ldc, sl[k], i, Kall, lds, Bc, m, sym, c[k], Ball);   // P(i, c_k)
-        ph0 += pc * L.Hs[0][k];
-        ph1 += pc * L.Hs[1][k];
+        ph_acc(ph0, ph1, pc, L.Hs[0][k], L.Hs[1][k]);
     }
-    double k0 = ph0 * L.Sinv[0][0] + ph1 * L.Sinv[1][0];
-    double k1 = ph0 * L.Sinv[0][1] + ph1 * L.Sinv[1][1];
-    x[i] = x[i] + (k0 * L.nu[0] + k1 * L.nu[1]);
+    double k0, k1, dx;
+    gain_from_ph(ph0, ph1, L.Sinv, L.nu, k0, k1, dx);
+    x[i] = __dadd_rn(x[i], dx);
     Kall[m * lds + i] = make_double2(k0, k1);
     if (sym) {
         Ball[m * lds + i] = make_double2(ph0, ph1);      // B = (P H')', all rows on every rank
@@ -137,8 +135,7 @@ __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_
         for (int k = 0; k < 5; ++k) {
             double pr = col[c[k]];                                            // P0(c_k, i), local
             for (int q = 0; q < m; ++q) pr = rank2_sub(pr, Kall[q * lds + c[k]], Ball[q * lds + i]);
-            b0 += L.Hs[0][k] * pr;
-            b1 += L.Hs[1][k] * pr;
+            b_acc(b0, b1, pr, L.Hs[0][k], L.Hs[1][k]);
         }
         Ball[m * lds + i] = make_double2(b0, b1);
     }
