@@ -6,4 +6,5 @@ include/ekfslam_b200.h).  Importing this package needs the built library; there 
 """
 from ._lib import load as load_library, EkfError, LIB_PATH            # noqa: F401
 from .filters import EKF_SLAM, EKF_SLAM_UC, Correspondence, Landmark  # noqa: F401
-from . import synth, shard                                                    # noqa: F401
+from .batch import FilterBatch, shard_filters                         # noqa: F401
+from . import synth, shard, batch                                     # noqa: F401

@@ -62,8 +62,23 @@ SIGNATURES = {
     'ekf_profile_read': [_H, _DP, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
     'ekf_downdate_bytes': [_H, _DP],
     'ekf_version': [],
+    # Monte-Carlo batch
+    'ekfb_create': [C.POINTER(EkfParams), C.c_int32, C.c_int32, C.c_int32, C.POINTER(_H)],
+    'ekfb_destroy': [_H],
+    'ekfb_step': [_H, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                  C.c_int32, C.c_int32, _IP],
+    'ekfb_sync': [_H],
+    'ekfb_n_landmarks': [_H, _IP],
+    'ekfb_get_x': [_H, C.c_int32, _DP, C.c_int32],
+    'ekfb_get_s': [_H, C.c_int32, _DP, C.c_int32],
+    'ekfb_get_P': [_H, C.c_int32, _DP, C.c_int32],
+    'ekfb_set_state': [_H, C.c_int32, _DP, _DP, C.c_int32, _DP, C.c_int32],
+    'ekfb_get_poses': [_H, _DP],
+    'ekfb_downdate_bytes': [_H, _DP],
+    'ekfb_profile': [_H, C.c_int32, _DP, C.POINTER(C.c_int64), _DP],
+    'ekfb_last_error': [_H],
 }
-_RESTYPE = {'ekf_last_error': C.c_char_p, 'ekf_version': C.c_char_p}
+_RESTYPE = {'ekf_last_error': C.c_char_p, 'ekf_version': C.c_char_p, 'ekfb_last_error': C.c_char_p}
 
 _lib = None
 

@@ -687,15 +687,15 @@ struct TmaCfg {
     static constexpr int THREADS = (CWARPS + 1) * 32;    // + 1 producer warp
 };
 
-template <int KS, int TC, int SCOLS, int NSTAGE, int CG>
-__global__ void __launch_bounds__((8 * CG + 1) * 32)
-k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
-               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, TileMap tm) {
+// One tile (rows r0.., columns c0..) of the flush.  TRIM (SYM storage, column 0 of this P is global column 0): column
+// j of a diagonal tile is copied only down to the diagonal (rows <= j, rounded to a row pair), so the bytes moved are
+// exactly the live ones -- it matters for the small matrices of the Monte-Carlo batch, where diagonal tiles are a
+// large share; consumers then work on stale shared memory below the diagonal, which is never stored.
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG, bool TRIM>
+__device__ __forceinline__ void dd_tma_tile(double* __restrict__ P, int64_t ld, int n, int ncols,
+                                            const double2* __restrict__ Kall, const double2* __restrict__ Ball,
+                                            int64_t lds, int M, int r0, int c0) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
-    int bx, by;
-    tm_decode(tm, (long long)blockIdx.x, bx, by);        // only live tiles are launched (column tile major)
-    const int r0 = bx * C::TR;
-    const int c0 = by * TC;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* stage = smem;
     double* Bs = (double*)(smem + NSTAGE * C::STAGE_BYTES);
@@ -722,23 +722,32 @@ k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
     if (warp == C::CWARPS) {
         // ------------------------------------------------ producer: lane c owns column c of every stage
         const bool col_lane = lane < SCOLS;
+        auto bytes_of = [&](int s, int nc) -> uint32_t {                // bytes this lane moves for stage s
+            if (!(col_lane && lane < nc)) return 0u;
+            if (!TRIM) return col_bytes;
+            const int live = (c0 + s * SCOLS + lane) - r0 + 1;           // rows r0 .. j of column j
+            return live <= 0 ? 0u : min(col_bytes, (uint32_t)((live + 1) & ~1) * 8u);
+        };
         auto load_stage = [&](int s) {
             const int slot = s % NSTAGE;
             const int nc = min(SCOLS, tile_cols - s * SCOLS);
-            if (lane == 0) mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)nc * col_bytes);
+            const uint32_t mine = bytes_of(s, nc);
+            const uint32_t total = TRIM ? __reduce_add_sync(0xffffffffu, mine) : (uint32_t)nc * col_bytes;
+            if (lane == 0) mbar_arrive_expect_tx(full0 + 8 * slot, total);
             __syncwarp();
-            if (col_lane && lane < nc)
+            if (mine)
                 bulk_g2s(smem_u32(stage + slot * C::STAGE_BYTES + lane * C::CS),
-                         P + (int64_t)r0 + (int64_t)(c0 + s * SCOLS + lane) * ld, col_bytes, full0 + 8 * slot);
+                         P + (int64_t)r0 + (int64_t)(c0 + s * SCOLS + lane) * ld, mine, full0 + 8 * slot);
         };
         for (int s = 0; s < NSTAGE - 1 && s < ns; ++s) load_stage(s);
         for (int s = 0; s < ns; ++s) {
             const int slot = s % NSTAGE;
             mbar_wait(done0 + 8 * slot, (s / NSTAGE) & 1);           // consumers finished stage s (writes fenced)
             const int nc = min(SCOLS, tile_cols - s * SCOLS);
-            if (col_lane && lane < nc)
+            const uint32_t mine = bytes_of(s, nc);
+            if (mine)
                 bulk_s2g(P + (int64_t)r0 + (int64_t)(c0 + s * SCOLS + lane) * ld,
-                         smem_u32(stage + slot * C::STAGE_BYTES + lane * C::CS), col_bytes);
+                         smem_u32(stage + slot * C::STAGE_BYTES + lane * C::CS), mine);
             bulk_commit();
             const int s2 = s + NSTAGE - 1;                           // refill the slot stage s-1 was stored from
             if (s2 < ns) {
@@ -795,6 +804,62 @@ k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
         fence_async_smem();                                          // generic-proxy writes -> visible to the bulk store
         __syncwarp();
         if (lane == 0) mbar_arrive(done0 + 8 * slot);
+    }
+}
+
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG>
+__global__ void __launch_bounds__((8 * CG + 1) * 32)
+k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
+               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, TileMap tm) {
+    typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
+    int bx, by;
+    tm_decode(tm, (long long)blockIdx.x, bx, by);        // only live tiles are launched (column tile major)
+    dd_tma_tile<KS, TC, SCOLS, NSTAGE, CG, false>(P, ld, n, ncols, Kall, Ball, lds, M, bx * C::TR, by * TC);
+}
+
+// The same tile pipeline over a batch of small matrices (Monte-Carlo filters, ekf_mc.cu): blockIdx.y = filter,
+// blockIdx.x = live tile of that filter's n x n matrix (n and the pending count come from device arrays).
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG>
+__global__ void __launch_bounds__((8 * CG + 1) * 32)
+k_mc_flush_tma(McArgs a) {
+    typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
+    const int f = blockIdx.y;
+    const int n = 3 + 2 * a.N[f], M = a.Mpend[f];
+    if (M == 0) return;
+    TileMap tm;
+    tm.R = (n + C::TR - 1) / C::TR; tm.CT = (n + TC - 1) / TC; tm.RPC = C::TR / TC; tm.A = 0;
+    const int ys = a.sym ? tm.RPC * (tm.R - 1) : 0;
+    tm.ystar = ys > tm.CT ? tm.CT : ys;
+    if ((long long)blockIdx.x >= tm_prefix(tm, tm.CT)) return;
+    int bx, by;
+    tm_decode(tm, (long long)blockIdx.x, bx, by);
+    double* P = a.P + (int64_t)f * a.pstride;
+    const double2* Kg = a.Kg + (int64_t)f * a.maxd * a.ldp;
+    const double2* Bg = a.Bg + (int64_t)f * a.maxd * a.ldp;
+    if (a.sym) dd_tma_tile<KS, TC, SCOLS, NSTAGE, CG, true>(P, a.ldp, n, n, Kg, Bg, a.ldp, M, bx * C::TR, by * TC);
+    else dd_tma_tile<KS, TC, SCOLS, NSTAGE, CG, false>(P, a.ldp, n, n, Kg, Bg, a.ldp, M, bx * C::TR, by * TC);
+}
+
+template <int KS>
+static void launch_mc_flush_tma_ks(cudaStream_t st, const McArgs& a, int n_filters, int cap_n) {
+    constexpr int TC = 64, SCOLS = 8, NSTAGE = 6, CG = 1;
+    typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_mc_flush_tma<KS, TC, SCOLS, NSTAGE, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        attr_set = true;
+    }
+    TileMap tm = tm_make((cap_n + C::TR - 1) / C::TR, (cap_n + TC - 1) / TC, TC, C::TR / TC, 0, a.sym);
+    dim3 grid((unsigned)tm_prefix(tm, tm.CT), n_filters);            // live tiles at capacity; smaller filters exit early
+    k_mc_flush_tma<KS, TC, SCOLS, NSTAGE, CG><<<grid, C::THREADS, C::SMEM, st>>>(a);
+}
+
+void launch_mc_flush_tma(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max) {
+    switch ((m_max + 1) / 2) {
+        case 1: launch_mc_flush_tma_ks<1>(st, a, n_filters, cap_n); break;
+        case 2: launch_mc_flush_tma_ks<2>(st, a, n_filters, cap_n); break;
+        case 3: launch_mc_flush_tma_ks<3>(st, a, n_filters, cap_n); break;
+        default: launch_mc_flush_tma_ks<4>(st, a, n_filters, cap_n); break;
     }
 }
 

@@ -52,4 +52,32 @@ void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n);
 // downdate kernel variant: < 0 = library default (TMA-staged DMMA flush, tile shape by rank; see launch_downdate);
 // the EKF_DOWNDATE_VARIANT environment variable overrides it per handle at ekf_create time.
 
+// ---- Monte-Carlo batch of independent filters (ekf_mc.cu): one CTA per filter, whole predict+measure on device ----
+struct McArgs {
+    double* P; int64_t ldp; int64_t pstride;     // per filter: ldp x cap_n column-major, pstride doubles apart
+    double* x; int64_t xstride;
+    double* s; int64_t sstride;
+    int* N;                                      // landmarks per filter
+    int cap;                                     // capacity_landmarks
+    const double* u;                             // [nf][2]
+    const double* obs; int max_obs;              // [nf][3][max_obs]  (k x 3 column-major per filter, ld = max_obs)
+    const int* counts;                           // [nf] observations this step
+    const double* loc; int64_t loc_stride;       // [.][2][max_table] column-major; stride 0 = one table for all filters
+    const int* idx; int64_t idx_stride;          // [.][max_table]
+    const int* ntab; int ntab_stride;            // [.] valid table entries
+    int max_table;
+    int* actions;                                // [nf][max_obs] or null: +idx update, -idx append
+    int* err;                                    // [0] = first error code (0 ok), [1] = filter
+    double2* Kg; double2* Bg;                    // split step: gain slabs in global memory, [nf][maxd][ldp]
+    int* Mpend;                                  // split step: pending rank-2 terms per filter
+    double C, Rc0, Rc1, s_cost, s_thresh;
+    int variant, assoc_mode, sym, do_predict, do_measure, maxd;
+};
+
+enum { MC_ERR_TABLE = 1, MC_ERR_CAPACITY = 2, MC_ERR_INDEX = 3 };
+void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem);   // fused (one kernel)
+void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters);                            // split: latency half
+void launch_mc_flush_tma(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);  // split: bandwidth half, TMA-staged DMMA (default)
+void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);      // split: bandwidth half (m_max >= every Mpend[f])
+
 }  // namespace ekf

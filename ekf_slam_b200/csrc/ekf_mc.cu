@@ -1,0 +1,424 @@
+// ekf_mc.cu -- Monte-Carlo batch of independent EKF-SLAM filters (BASELINE config 5: 4096 x EKF_SLAM_UC x 200
+// landmarks).  One CTA owns one filter and runs a whole SLAM iteration for it on the device:
+//     predict(u)                                        EKF_SLAM.m:40-51
+//     measure(): for every observation                  EKF_SLAM.m:100-151 / EKF_SLAM_UC.m:102-152
+//         R = diag(range*Rc1, bearing*Rc2)              :108
+//         first-landmark branch / z(3) > N append / idx = ii     (known correspondence, :110-123)
+//         estimateCorrespondence -> append | update     (unknown correspondence, _UC:119-125; Correspondence.m:28-88)
+//         update: linearise, S, K, x                    :124-144
+//     P <- P - sum_q K_q B_q                            :145, deferred: ONE pass over this filter's P per measure()
+// No host round trip happens inside a step: association results, append decisions and the per-filter landmark count
+// N live on the device.  Filters never communicate; across GPUs filter f simply lives on rank f mod G.
+// The pending gain slabs K_q, B_q (<= maxd observations) sit in shared memory, so the deferred gathers
+// P0(i,c) - sum_q K_q(i) B_q(c) cost no extra HBM traffic and the flush streams P exactly once.
+#include "ekf_kernels.h"
+#include "ekf_device.cuh"
+#include <math_constants.h>
+#include <limits.h>
+
+namespace ekf {
+
+
+struct McShared {                                // small per-CTA scratch (the slabs follow in dynamic shared memory)
+    double Pcc[5][5];
+    double Hs[2][5], Sinv[2][2], nu[2];
+    double wc[32];
+    int wi[32];
+    double best; int bidx;
+    int N, m, action, fatal;
+    double pos[2];
+};
+
+__device__ __forceinline__ double mc_cur(const double* __restrict__ P, int64_t ldp, int i, int j, int sym,
+                                         const double2* Ks, const double2* Bs, int64_t lds, int m) {
+    if (sym && i > j) { int t = i; i = j; j = t; }
+    double v = P[(int64_t)i + (int64_t)j * ldp];
+    for (int q = 0; q < m; ++q) v = rank2_sub(v, Ks[q * lds + i], Bs[q * lds + j]);
+    return v;
+}
+
+// P(i,j) -= sum_q K_q(i,:) B_q(:,j) for the whole filter; row pairs as double2, UNR column-steps in flight per thread.
+__device__ __noinline__ void mc_flush(double* __restrict__ P, int64_t ldp, int n, int sym, const double2* Ks,
+                                         const double2* Bs, int64_t lds, int m) {
+    if (m == 0) return;
+    const int nrp = (n + 1) >> 1;                              // row pairs (row n of an odd n is padding: K = 0 there)
+    const int total = nrp * n;
+    constexpr int UNR = 8;
+    for (int e0 = threadIdx.x; e0 < total; e0 += UNR * blockDim.x) {
+        double2 v[UNR];
+        int jj[UNR], rr[UNR];
+        bool ok[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const int e = e0 + u * blockDim.x;
+            jj[u] = e / nrp;
+            rr[u] = 2 * (e - jj[u] * nrp);
+            ok[u] = e < total && !(sym && rr[u] > jj[u]);
+            if (ok[u]) v[u] = *(const double2*)(P + (int64_t)rr[u] + (int64_t)jj[u] * ldp);
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            if (ok[u]) {
+                for (int q = 0; q < m; ++q) {
+                    const double2 b = Bs[q * lds + jj[u]];
+                    v[u].x = rank2_sub(v[u].x, Ks[q * lds + rr[u]], b);
+                    v[u].y = rank2_sub(v[u].y, Ks[q * lds + rr[u] + 1], b);
+                }
+                *(double2*)(P + (int64_t)rr[u] + (int64_t)jj[u] * ldp) = v[u];
+            }
+        }
+    }
+}
+
+// Block-wide lexicographic (cost, index) minimum == the strict-'<' first-minimum scan of Correspondence.m:81.
+__device__ __forceinline__ void mc_argmin(double best, int bidx, McShared& sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double oc = __shfl_down_sync(0xffffffffu, best, o);
+        int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+        if ((oc < best) || (oc == best && oi < bidx)) { best = oc; bidx = oi; }
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { sh.wc[w] = best; sh.wi[w] = bidx; }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        best = (lane < nw) ? sh.wc[lane] : CUDART_INF;
+        bidx = (lane < nw) ? sh.wi[lane] : INT_MAX;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            double oc = __shfl_down_sync(0xffffffffu, best, o);
+            int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+            if ((oc < best) || (oc == best && oi < bidx)) { best = oc; bidx = oi; }
+        }
+        if (lane == 0) { sh.best = best; sh.bidx = bidx; }
+    }
+    __syncthreads();
+}
+
+// MODE_B = 1 compiles the Mahalanobis association (Correspondence.m:74) in.
+// SPLIT = 0: everything in one kernel, gain slabs in shared memory, the CTA also streams its P (256 threads).
+// SPLIT = 1: "front" half only -- the latency-bound sequential part (associate / linearise / gain per observation) with
+//            the slabs in global memory (L2 resident), 128 threads and no big shared-memory footprint so that many
+//            filters are resident per SM and hide each other's fp64 trig / dependent-chain latency; the pending count
+//            goes to Mpend[f] and the bandwidth-bound pass over every P is left to k_mc_flush at full HBM rate.
+template <int MODE_B, int SPLIT>
+__global__ void __launch_bounds__(SPLIT ? 128 : 256, SPLIT ? (MODE_B ? 2 : 4) : (MODE_B ? 1 : 2))
+k_mc_step(McArgs a) {
+    extern __shared__ __align__(16) unsigned char mc_dyn[];
+    __shared__ McShared sh;
+    const int f = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    double* __restrict__ P = a.P + (int64_t)f * a.pstride;
+    double* __restrict__ x = a.x + (int64_t)f * a.xstride;
+    double* __restrict__ s = a.s + (int64_t)f * a.sstride;
+    const int64_t ld = a.ldp, lds = a.ldp;
+    const int sym = a.sym;
+    double2* Ks = SPLIT ? a.Kg + (int64_t)f * a.maxd * lds : (double2*)mc_dyn;
+    double2* Bs = SPLIT ? a.Bg + (int64_t)f * a.maxd * lds : Ks + (int64_t)a.maxd * lds;
+    if (!SPLIT)
+        for (int64_t e = tid; e < 2 * (int64_t)a.maxd * lds; e += T) Ks[e] = make_double2(0.0, 0.0);
+    if (tid == 0) { sh.N = a.N[f]; sh.m = 0; sh.fatal = 0; }
+    __syncthreads();
+    const double u1 = a.u[2 * f], u2 = a.u[2 * f + 1];
+
+    // ------------------------------------------------------------ predict (EKF_SLAM.m:40-51), nothing pending
+    if (a.do_predict) {
+        const int n = 3 + 2 * sh.N;
+        const double th = x[2];
+        const double st = sind(th), ct = cosd(th);
+        const double fa = -1.0 * u1 * st, fb = u1 * ct;          // F(1,3), F(2,3): heading BEFORE the motion (:63-64)
+        __syncthreads();
+        if (tid == 0) {
+            double M[3][3];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) M[i][j] = ldP(P, ld, i, j, sym);
+            for (int j = 0; j < 3; ++j) { M[0][j] = M[0][j] + fa * M[2][j]; M[1][j] = M[1][j] + fb * M[2][j]; }
+            for (int i = 0; i < 3; ++i) { M[i][0] = M[i][0] + M[i][2] * fa; M[i][1] = M[i][1] + M[i][2] * fb; }
+            const double W[3] = {u1 * ct, u1 * st, u2};
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) P[i + j * ld] = M[i][j] + (W[i] * a.C) * W[j];
+            x[0] = x[0] + u1 * cosd(th + u2);                    // :57-60
+            x[1] = x[1] + u1 * sind(th + u2);
+            x[2] = wrapTo360(th + u2);                           // :50
+        }
+        for (int t = 3 + tid; t < n; t += T) {
+            double* col = P + (int64_t)t * ld;
+            const double p2 = col[2];
+            col[0] = col[0] + fa * p2;
+            col[1] = col[1] + fb * p2;
+            if (!sym) {
+                const double q2 = P[t + 2 * ld];
+                P[t] = P[t] + q2 * fa;
+                P[t + ld] = P[t + ld] + q2 * fb;
+            }
+        }
+        __syncthreads();
+    }
+
+    // ------------------------------------------------------------ measure (EKF_SLAM.m:100-151, EKF_SLAM_UC.m:102-152)
+    const int cnt = a.do_measure ? a.counts[f] : 0;
+    const double* ob = a.obs + (int64_t)f * 3 * a.max_obs;
+    const double* loc = a.loc + (int64_t)f * a.loc_stride;
+    const int* tix = a.idx + (int64_t)f * a.idx_stride;
+    const int ntab = a.ntab[f * a.ntab_stride];
+    for (int ii = 1; ii <= cnt; ++ii) {                          // :107
+        const double z0 = ob[ii - 1], z1 = ob[ii - 1 + a.max_obs], z2 = ob[ii - 1 + 2 * a.max_obs];
+        const double R0 = z0 * a.Rc0, R1 = z1 * a.Rc1;           // :108
+        const int N = sh.N, n = 3 + 2 * N, m = sh.m;
+        // ---- decide: append (with pos, signature) or update (slot idx)
+        int do_append = 0, idx = 0;
+        double want = 0.0, sig = 0.0;
+        int lookup = 0;                                          // 1: first non-zero index, 2: index == want
+        if (N == 0) { do_append = 1; sig = 1.0; lookup = 1; }    // :110-111 (F15)
+        else if (a.variant == 0 /* EKF_VARIANT_KNOWN */) {
+            if (z2 > (double)N) { do_append = 1; sig = z2; want = z2; lookup = 2; }      // :118-120
+            else idx = ii;                                       // :123 (F8)
+        } else {
+            double best = CUDART_INF;
+            int bidx = INT_MAX;
+            for (int kk = tid; kk < N; kk += T) {                // Correspondence.m:49
+                const double d = __dsub_rn(z2, s[kk]);
+                double ll = __dmul_rn(__dmul_rn(d, 1.0 / a.s_cost), d);      // :71, :75
+                if (MODE_B) {                                    // :74 (commented out upstream): + Mahalanobis cost
+                    const int al = 3 + 2 * kk;
+                    const int c[5] = {0, 1, 2, al, al + 1};
+                    double xr[3] = {x[0], x[1], x[2]};
+                    double zk[2], Hs[2][5], S[2][2], Si[2][2], Pcc[5][5];
+                    measurement_model(xr, x[al], x[al + 1], zk, Hs);
+                    for (int i = 0; i < 5; ++i)
+                        for (int j = 0; j < 5; ++j) Pcc[i][j] = mc_cur(P, ld, c[i], c[j], sym, Ks, Bs, lds, m);
+                    const double Rd[2] = {R0, R1};
+                    innovation_cov(Hs, Pcc, Rd, S, Si);
+                    const double n0 = __dsub_rn(z0, zk[0]), n1 = __dsub_rn(z1, zk[1]);
+                    const double t0 = __dadd_rn(__dmul_rn(n0, Si[0][0]), __dmul_rn(n1, Si[1][0]));   // :69
+                    const double t1 = __dadd_rn(__dmul_rn(n0, Si[0][1]), __dmul_rn(n1, Si[1][1]));
+                    ll = __dadd_rn(__dadd_rn(__dmul_rn(t0, n0), __dmul_rn(t1, n1)), ll);
+                }
+                if (ll <= a.s_thresh && ll < best) { best = ll; bidx = kk + 1; }         // :78, :81
+            }
+            mc_argmin(best, bidx, sh);
+            if (sh.bidx == INT_MAX) { do_append = 1; idx = N + 1; sig = (double)idx; want = (double)idx; lookup = 2; }   // :40, :121-123
+            else idx = sh.bidx;
+        }
+        if (tid == 0) {
+            int fatal = 0;
+            if (do_append) {
+                int hit = -1;
+                for (int i = 0; i < ntab && hit < 0; ++i)
+                    if (lookup == 1 ? (tix[i] != 0) : ((double)tix[i] == want)) hit = i;
+                if (hit < 0) fatal = MC_ERR_TABLE;
+                else { sh.pos[0] = loc[hit]; sh.pos[1] = loc[hit + a.max_table]; }
+                if (N >= a.cap) fatal = MC_ERR_CAPACITY;
+                sh.action = -(int)sig;
+            } else {
+                if (idx < 1 || idx > N) fatal = MC_ERR_INDEX;
+                sh.action = idx;
+            }
+            sh.fatal = fatal;
+        }
+        __syncthreads();
+        if (sh.fatal) break;
+        if (a.actions && tid == 0) a.actions[(int64_t)f * a.max_obs + ii - 1] = sh.action;
+
+        if (do_append) {
+            // ---------------------------------------------------- append (EKF_SLAM.m:67-98), needs the whole P
+            mc_flush(P, ld, n, sym, Ks, Bs, lds, m);
+            __syncthreads();
+            const double th = x[2];
+            const double j02 = -u1 * sind(th), j12 = u1 * cosd(th);          // jxr, :84-85
+            for (int t = tid; t <= N; t += T) {
+                if (t < N) {
+                    const int al = 3 + 2 * t;
+                    for (int mm = 0; mm < 2; ++mm) {
+                        const double p0 = ldP(P, ld, al + mm, 0, sym), p1 = ldP(P, ld, al + mm, 1, sym), p2 = ldP(P, ld, al + mm, 2, sym);
+                        const double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;    // jxr * P(lm,1:3)', :95
+                        const double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+                        P[(int64_t)(al + mm) + (int64_t)n * ld] = f0;
+                        P[(int64_t)(al + mm) + (int64_t)(n + 1) * ld] = f1;
+                        P[(int64_t)n + (int64_t)(al + mm) * ld] = f0;
+                        P[(int64_t)(n + 1) + (int64_t)(al + mm) * ld] = f1;
+                    }
+                } else {
+                    double Prr[3][3];
+                    for (int i = 0; i < 3; ++i)
+                        for (int j = 0; j < 3; ++j) Prr[i][j] = ldP(P, ld, i, j, sym);
+                    const double jxr[2][3] = {{1.0, 0.0, j02}, {0.0, 1.0, j12}};
+                    const double cu = cosd(u2), su = sind(u2);
+                    const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};             // :87-88
+                    double JP[2][3];
+                    for (int r = 0; r < 2; ++r)
+                        for (int j = 0; j < 3; ++j) JP[r][j] = jxr[r][0] * Prr[0][j] + jxr[r][1] * Prr[1][j] + jxr[r][2] * Prr[2][j];
+                    const double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+                    for (int r = 0; r < 2; ++r)
+                        for (int c = 0; c < 2; ++c)
+                            P[(int64_t)(n + r) + (int64_t)(n + c) * ld] =
+                                (JP[r][0] * jxr[c][0] + JP[r][1] * jxr[c][1] + JP[r][2] * jxr[c][2]) +
+                                (JR[r][0] * jz[c][0] + JR[r][1] * jz[c][1]);             // :91
+                    for (int i = 0; i < 3; ++i)
+                        for (int c = 0; c < 2; ++c) {
+                            const double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];   // :92
+                            P[(int64_t)i + (int64_t)(n + c) * ld] = v;
+                            P[(int64_t)(n + c) + (int64_t)i * ld] = v;                   // :93
+                        }
+                    x[n] = sh.pos[0]; x[n + 1] = sh.pos[1];                              // :79
+                    s[N] = sig;                                                          // :70
+                }
+            }
+            __syncthreads();
+            if (tid == 0) { sh.N = N + 1; sh.m = 0; }
+            __syncthreads();
+            continue;
+        }
+
+        // -------------------------------------------------------- update (EKF_SLAM.m:124-145)
+        const int al = 3 + 2 * (idx - 1);
+        const int c[5] = {0, 1, 2, al, al + 1};
+        if (tid < 32) {
+            if (tid < 25) sh.Pcc[tid / 5][tid % 5] = mc_cur(P, ld, c[tid / 5], c[tid % 5], sym, Ks, Bs, lds, m);
+            __syncwarp();
+            if (tid == 0) {
+                double xr[3] = {x[0], x[1], x[2]};
+                double zk[2], Hs[2][5], S[2][2], Si[2][2], Pl[5][5];
+                measurement_model(xr, x[al], x[al + 1], zk, Hs);
+                for (int i = 0; i < 5; ++i)
+                    for (int j = 0; j < 5; ++j) Pl[i][j] = sh.Pcc[i][j];
+                const double Rd[2] = {R0, R1};
+                innovation_cov(Hs, Pl, Rd, S, Si);
+                for (int r = 0; r < 2; ++r) {
+                    for (int k = 0; k < 5; ++k) sh.Hs[r][k] = Hs[r][k];
+                    for (int t = 0; t < 2; ++t) sh.Sinv[r][t] = Si[r][t];
+                }
+                sh.nu[0] = z0 - zk[0];                                                   // :144, not wrapped (F10)
+                sh.nu[1] = z1 - zk[1];
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += T) {
+            double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                ph_acc(ph0, ph1, mc_cur(P, ld, i, c[k], sym, Ks, Bs, lds, m), sh.Hs[0][k], sh.Hs[1][k]);
+                if (!sym) b_acc(b0, b1, mc_cur(P, ld, c[k], i, 0, Ks, Bs, lds, m), sh.Hs[0][k], sh.Hs[1][k]);
+            }
+            if (sym) { b0 = ph0; b1 = ph1; }
+            double k0, k1, dx;
+            gain_from_ph(ph0, ph1, sh.Sinv, sh.nu, k0, k1, dx);                          // :143
+            x[i] = __dadd_rn(x[i], dx);                                                  // :144
+            Ks[m * lds + i] = make_double2(k0, k1);
+            Bs[m * lds + i] = make_double2(b0, b1);
+        }
+        if (tid == 0) {                                  // n is odd: row n pads the last row pair of the flush
+            Ks[m * lds + n] = make_double2(0.0, 0.0);
+            Bs[m * lds + n] = make_double2(0.0, 0.0);
+        }
+        __syncthreads();
+        if (m + 1 >= a.maxd && !(SPLIT && ii == cnt)) {        // slabs full (split: the last batch is left to k_mc_flush)
+            mc_flush(P, ld, n, sym, Ks, Bs, lds, m + 1);
+            __syncthreads();
+            if (tid == 0) sh.m = 0;
+        } else if (tid == 0) sh.m = m + 1;
+        __syncthreads();
+    }
+    if (!SPLIT) {   // P is whole again when measure() returns; on a fatal row the terms applied so far are kept
+        const int n = 3 + 2 * sh.N;
+        mc_flush(P, ld, n, sym, Ks, Bs, lds, sh.m);
+    }
+    if (tid == 0) {
+        if (SPLIT) a.Mpend[f] = sh.m;                    // k_mc_flush applies them
+        a.N[f] = sh.N;
+        if (sh.fatal && atomicCAS(a.err, 0, sh.fatal) == 0) a.err[1] = f;
+    }
+}
+
+// Bandwidth half of the split step: P_f(i,j) -= sum_{q<Mpend[f]} K_q(i,:) B_q(:,j) for every filter.
+// One 64-thread CTA per (128-row x TC-column tile, filter): a thread owns a row pair (double2, 16 B) with its <= M gains
+// in registers and keeps UNR column loads in flight; the tile's B columns sit in shared memory.  Small CTAs with few
+// registers -> ~12 resident per SM -> ~100 KB of reads in flight per SM.  SYM drops tiles below the diagonal whole and
+// masks the diagonal tiles element by element.
+template <int M, int TC, int UNR>
+__global__ void __launch_bounds__(64)
+k_mc_flush(McArgs a, int row_tiles) {
+    const int f = blockIdx.y, tid = threadIdx.x;
+    const int rt = blockIdx.x % row_tiles, ct = blockIdx.x / row_tiles;
+    const int r0 = rt * 128, c0 = ct * TC;
+    const int n = 3 + 2 * a.N[f], m = min(a.Mpend[f], M);
+    const int sym = a.sym;
+    if (m == 0 || c0 >= n || r0 >= n) return;
+    const int nc = min(TC, n - c0);
+    if (sym && r0 > c0 + nc - 1) return;                 // tile strictly below the diagonal
+    const int64_t ld = a.ldp, lds = a.ldp;
+    double* __restrict__ P = a.P + (int64_t)f * a.pstride;
+    const double2* __restrict__ Kg = a.Kg + (int64_t)f * a.maxd * lds;
+    const double2* __restrict__ Bg = a.Bg + (int64_t)f * a.maxd * lds;
+    __shared__ double2 Bsh[TC * M];
+    for (int e = tid; e < nc * M; e += 64) {
+        const int j = e / M, q = e - j * M;
+        Bsh[e] = q < m ? Bg[q * lds + c0 + j] : make_double2(0.0, 0.0);
+    }
+    __syncthreads();
+    const int r = r0 + 2 * tid;
+    if (r >= n || (sym && r > c0 + nc - 1)) return;
+    double2 k0[M], k1[M];
+#pragma unroll
+    for (int q = 0; q < M; ++q) {
+        k0[q] = q < m ? Kg[q * lds + r] : make_double2(0.0, 0.0);
+        k1[q] = q < m ? Kg[q * lds + r + 1] : make_double2(0.0, 0.0);     // row n (n is odd) is written as zero by the front
+    }
+    double* p = P + (int64_t)r + (int64_t)c0 * ld;
+    const int j0 = sym ? max(0, r - c0) : 0;             // first live column of this row pair within the tile
+    for (int j = j0; j < nc; j += UNR) {
+        double2 v[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u)
+            if (j + u < nc) v[u] = *(const double2*)(p + (int64_t)(j + u) * ld);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            if (j + u < nc) {
+#pragma unroll
+                for (int q = 0; q < M; ++q) {
+                    const double2 b = Bsh[(j + u) * M + q];
+                    v[u].x = rank2_sub(v[u].x, k0[q], b);
+                    v[u].y = rank2_sub(v[u].y, k1[q], b);
+                }
+                *(double2*)(p + (int64_t)(j + u) * ld) = v[u];
+            }
+        }
+    }
+}
+
+void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem) {
+    static size_t smem_set[2] = {0, 0};
+    const int mb = a.assoc_mode == 1 && a.variant != 0;
+    if (smem > smem_set[mb]) {
+        if (mb) cudaFuncSetAttribute(k_mc_step<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        else cudaFuncSetAttribute(k_mc_step<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        smem_set[mb] = smem;
+    }
+    if (mb) k_mc_step<1, 0><<<n_filters, threads, smem, st>>>(a);
+    else k_mc_step<0, 0><<<n_filters, threads, smem, st>>>(a);
+}
+
+void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters) {
+    const int mb = a.assoc_mode == 1 && a.variant != 0;
+    if (mb) k_mc_step<1, 1><<<n_filters, 128, 0, st>>>(a);
+    else k_mc_step<0, 1><<<n_filters, 128, 0, st>>>(a);
+}
+
+void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max) {
+    constexpr int TC = 64;
+    const int row_tiles = (cap_n + 127) / 128, col_tiles = (cap_n + TC - 1) / TC;
+    dim3 grid(row_tiles * col_tiles, n_filters);
+    // terms with q >= Mpend[f] are zero-filled, so any M >= the largest pending count is exact
+    switch (m_max) {
+        case 1: k_mc_flush<1, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        case 2: k_mc_flush<2, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        case 3: k_mc_flush<3, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        case 4: k_mc_flush<4, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        case 5: k_mc_flush<5, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        case 6: k_mc_flush<6, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        case 7: k_mc_flush<7, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+        default: k_mc_flush<8, TC, 8><<<grid, 64, 0, st>>>(a, row_tiles); break;
+    }
+}
+
+}  // namespace ekf

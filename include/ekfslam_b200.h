@@ -142,6 +142,41 @@ int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, int64_t* down
 /* Bytes the downdate kernel must move per launch at the current n and storage. */
 int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Monte-Carlo batch: n_filters independent filters of one class (BASELINE config 5: 4096 x EKF_SLAM_UC x 200
+ * landmarks).  Replaces a host loop over n_filters reference objects, each doing
+ *     slam.predict(u); slam.measure(laserData, u, LM)        (SLAM.m:110,116)
+ * One CUDA block owns one filter and runs the whole iteration on the device (association, append / update decision,
+ * deferred covariance downdate: one pass over that filter's P per measure()).  Filters never communicate; across GPUs
+ * the caller gives each rank its own share of the filters (filter f on rank f mod G) -- no collective.
+ * Per-filter inputs are dense arrays, filter-major:
+ *   u            n_filters x 2                          [dD, dtheta_deg] per filter
+ *   observed_LL  n_filters x (max_obs x 3 column-major) rows [range | bearing_deg | index], counts[f] rows valid
+ *   loc_table    (n_filters or 1) x (max_table x 2 column-major), index_table (n_filters or 1) x max_table,
+ *   n_table      (n_filters or 1): landmark_list.landmarkObj.landmark(:).{loc,index};  shared_table != 0: one table for all
+ * mem = 0: host pointers (copied to the device inside the call);  mem = 1: device pointers (inputs already resident).
+ * actions_out (host, n_filters x max_obs, may be NULL) receives +idx for an update, -idx for an append; asking for it
+ * synchronises.  Errors inside a filter (landmark not in the table, capacity, slot out of range) surface at the next
+ * ekfb_sync / getter as EKF_EINVAL / EKF_ECAPACITY with the filter number in ekfb_last_error. */
+typedef struct ekfb_handle ekfb_handle;
+int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t max_obs, int32_t max_table, ekfb_handle** out);
+int32_t ekfb_destroy(ekfb_handle* h);
+int32_t ekfb_step(ekfb_handle* h, int32_t mem, const double* u, const double* observed_LL, const int32_t* counts,
+                  const double* loc_table, const int32_t* index_table, const int32_t* n_table, int32_t shared_table,
+                  int32_t do_predict, int32_t do_measure, int32_t* actions_out);
+int32_t ekfb_sync(ekfb_handle* h);
+int32_t ekfb_n_landmarks(ekfb_handle* h, int32_t* N /* n_filters */);
+int32_t ekfb_get_x(ekfb_handle* h, int32_t filter, double* x, int32_t len);
+int32_t ekfb_get_s(ekfb_handle* h, int32_t filter, double* s, int32_t len);
+int32_t ekfb_get_P(ekfb_handle* h, int32_t filter, double* P, int32_t lda);      /* SYM storage is mirrored on the host side copy */
+int32_t ekfb_set_state(ekfb_handle* h, int32_t filter /* < 0: every filter */, const double* x, const double* P, int32_t lda, const double* s, int32_t N);
+int32_t ekfb_get_poses(ekfb_handle* h, double* poses /* n_filters x 3, filter-major: x(1:3) of every filter */);
+/* Algorithmic HBM bytes of the covariance pass of one step over all filters at their current sizes. */
+int32_t ekfb_downdate_bytes(ekfb_handle* h, double* bytes);
+/* CUDA-event time of the step kernels (front + flush) and of the bandwidth-bound flush kernel alone; enable < 0 only reads. */
+int32_t ekfb_profile(ekfb_handle* h, int32_t enable, double* step_ms_total, int64_t* steps, double* flush_ms_total);
+const char* ekfb_last_error(ekfb_handle* h);
+
 /* Library identification. */
 const char* ekf_version(void);
 

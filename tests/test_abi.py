@@ -9,7 +9,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _declared():
     src = open(os.path.join(ROOT, 'include', 'ekfslam_b200.h')).read()
     src = re.sub(r'/\*.*?\*/', '', src, flags=re.S)
-    return sorted(set(re.findall(r'\b(ekf_[a-zA-Z0-9_]+)\s*\(', src)))
+    return sorted(set(re.findall(r'\b(ekfb?_[a-zA-Z0-9_]+)\s*\(', src)))
 
 
 def test_header_declares_the_boundary():

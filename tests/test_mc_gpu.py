@@ -1,0 +1,113 @@
+"""Monte-Carlo filter batch (ekfb_*, one CUDA block per filter, whole predict+measure on the device) vs the
+dense-literal oracle run filter by filter, and vs the single-filter CUDA path (bit-identical: same primitives)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+def _rel(a, b):
+    return float(np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300))
+
+
+def _worlds(nf, cls, N, T, k):
+    from ekf_slam_b200.synth import make_world
+    mode = 'prefix' if cls == 'EKF_SLAM' else 'nearest'
+    return [make_world(N=N, T=T, k=k, mode=mode, seed=1000 + 17 * f) for f in range(nf)]
+
+
+@pytest.mark.parametrize('storage', ['sym', 'full'])
+@pytest.mark.parametrize('cls,defer_m,assoc', [('EKF_SLAM_UC', 8, 'signature'), ('EKF_SLAM_UC', 1, 'signature'),
+                                                 ('EKF_SLAM', 8, 'signature'), ('EKF_SLAM_UC', 3, 'position')])
+def test_batch_matches_oracle_per_filter(storage, cls, defer_m, assoc):
+    import ekf_slam_b200 as E
+    from oracle import dense_literal as O
+    nf, N, T, k = 10, 14, 90, 5
+    ws = _worlds(nf, cls, N, T, k)
+    max_obs = max(len(o) for w in ws for o in w.observed)
+    b = E.FilterBatch(cls, nf, capacity_landmarks=N, max_obs=max_obs, max_table=N, storage=storage, defer_m=defer_m,
+                      assoc_mode=assoc)
+    os_ = [getattr(O, cls)() for _ in range(nf)]
+    if assoc == 'position':
+        for o in os_:
+            o.correspondence = O.Correspondence(1e-11, 1e9, 'EKF_SLAM_UC', position_cost_in_score=True)
+    acts = [[] for _ in range(nf)]
+    for t in range(T):
+        u = np.array([w.u[t] for w in ws])
+        a = b.step(u, [w.observed[t] for w in ws], [list(w.table[:w.n_table[t]]) for w in ws], want_actions=True)
+        for f, (w, o) in enumerate(zip(ws, os_)):
+            o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
+            acts[f] += [('update', int(v)) if v > 0 else ('append', int(-v)) for v in a[f, :len(w.observed[t])]]
+    worst = [0.0, 0.0]
+    for f, o in enumerate(os_):
+        assert acts[f] == o.chosen, 'filter %d: actions differ' % f
+        v = b[f]
+        assert v.N == (o.x.size - 3) // 2 and np.array_equal(v.s, np.asarray(o.s, dtype=np.float64))
+        ex, eP = _rel(v.x, o.x), _rel(v.P, o.P)
+        worst = [max(worst[0], ex), max(worst[1], eP)]
+        assert ex <= TOL and eP <= TOL, (f, ex, eP)
+    print('batch %s/%s defer=%d %s: %d filters x %d steps, worst rel err x %.2e P %.2e' %
+          (cls, storage, defer_m, assoc, nf, T, worst[0], worst[1]))
+    b.close()
+
+
+@pytest.mark.parametrize('impl', ['split-tma', 'split-ldg', 'fused'])
+@pytest.mark.parametrize('storage', ['sym', 'full'])
+def test_batch_equals_single_filter_path_bitwise(storage, impl, monkeypatch):
+    """All step implementations: split front + TMA-staged flush (default), split + register-path flush
+    (EKF_MC_FLUSH=ldg) and the one-kernel step (EKF_MC_FUSED=1)."""
+    import ekf_slam_b200 as E
+    monkeypatch.setenv('EKF_MC_FUSED', '1' if impl == 'fused' else '0')
+    monkeypatch.setenv('EKF_MC_FLUSH', 'ldg' if impl == 'split-ldg' else 'tma')
+    nf, N, T, k = 6, 12, 60, 4
+    ws = _worlds(nf, 'EKF_SLAM_UC', N, T, k)
+    b = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=N, max_obs=k, max_table=N, storage=storage, defer_m=4)
+    singles = [E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, defer_m=4) for _ in range(nf)]
+    for t in range(T):
+        b.step(np.array([w.u[t] for w in ws]), [w.observed[t] for w in ws], [list(w.table[:w.n_table[t]]) for w in ws])
+        for w, g in zip(ws, singles):
+            g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
+    for f, g in enumerate(singles):
+        assert np.array_equal(b[f].x, g.x), _rel(b[f].x, g.x)
+        assert np.array_equal(b[f].P, g.P), _rel(b[f].P, g.P)
+        g.close()
+    b.close()
+
+
+def test_batch_shared_table_ragged_counts_and_errors():
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=10, T=40, k=4, mode='nearest', seed=5)
+    nf = 5
+    b = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=10, max_obs=4, max_table=10, storage='sym', defer_m=8)
+    os_ = [O.EKF_SLAM_UC() for _ in range(nf)]
+    for t in range(w.T):
+        # filter f sees only the first (4 - f % 3) rows; filter 4 sees none on odd steps (empty observation list)
+        obs = [w.observed[t][:max(0, 4 - f % 3)] if not (f == 4 and t % 2) else np.zeros((0, 3)) for f in range(nf)]
+        b.step(np.tile(w.u[t], (nf, 1)), obs, list(w.table))          # one table object list -> shared by all filters
+        for f, o in enumerate(os_):
+            o.predict(w.u[t])
+            from tests.golden_util import Stub
+            o.measure(None, w.u[t], Stub(obs[f], w.table))
+    for f, o in enumerate(os_):
+        assert _rel(b[f].x, o.x) <= TOL and _rel(b[f].P, o.P) <= TOL
+    b.close()
+    # capacity: 3 landmarks offered to filters that can hold 2
+    b = E.FilterBatch('EKF_SLAM_UC', 2, capacity_landmarks=2, max_obs=3, max_table=3)
+    from types import SimpleNamespace
+    tab = [SimpleNamespace(index=i + 1, loc=np.array([1.0 + i, 2.0])) for i in range(3)]
+    obs = [np.array([[2.0, 30.0, 1], [3.0, 40.0, 2], [4.0, 50.0, 3]])] * 2
+    b.step(np.zeros((2, 2)), obs, tab)
+    with pytest.raises(E.EkfError) as e:
+        b.sync()
+    assert e.value.code == -2
+    b.close()
+    # unknown landmark index in the table
+    b = E.FilterBatch('EKF_SLAM', 1, capacity_landmarks=4, max_obs=2, max_table=2)
+    b.step(np.zeros((1, 2)), [np.array([[2.0, 30.0, 1], [3.0, 40.0, 7]])], [SimpleNamespace(index=1, loc=np.array([1.0, 2.0]))])
+    with pytest.raises(E.EkfError) as e:
+        b.sync()
+    assert e.value.code == -1
+    b.close()
