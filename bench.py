@@ -289,7 +289,7 @@ def main():
     peak = float(peaks.get('hbm_gbs', 6650.0))
     achieved = dd_bytes / (dd_ms / dd_n * 1e-3) / 1e9
     line = {
-        'metric': METRIC, 'value': K * k / (ms * 1e-3), 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W,
+        'metric': METRIC if N == 10000 else 'EKF updates/sec at %d landmarks' % N, 'value': K * k / (ms * 1e-3), 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W,
         'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'strong' if world > 1 else 'weak', 'vs_baseline': None, 'dtype': 'f64',
         'data': 'synthetic',
         'config': {'workload': '10k landmarks (P 20003^2 fp64), predict + %d updates per step' % k if N == 10000 else

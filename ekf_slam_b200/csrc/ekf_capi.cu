@@ -364,12 +364,26 @@ static int32_t flush_sharded(ekf_handle* h) {
     for (int m = 0; m < k; ++m) { ss.col[3 + 2 * m] = h->q[m].a; ss.col[4 + 2 * m] = h->q[m].a + 1; }
     int32_t rcx = exchange_cols(h, ss, n);
     if (rcx != EKF_OK) return rcx;
-    for (int m = 0; m < k; ++m) {
-        const ekf_handle::QObs& o = h->q[m];
-        launch_lin_gain_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n, o.a, 3 + 2 * m, o.z0, o.z1, o.R0, o.R1,
-                              ss, h->Pc, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m, sym_of(h));
+    if (k >= 2 && !getenv("EKF_SHARD_PEROBS")) {
+        // fused: one warp walks the k linearisations on the exchanged (3+2k)^2 block, one grid-wide kernel builds all
+        // k gain slabs (replicated on every rank from identical inputs) -- 2 launches per batch
+        BatchObs ob;
+        ob.k = k;
+        for (int m = 0; m < k; ++m) {
+            const ekf_handle::QObs& o = h->q[m];
+            ob.z0[m] = o.z0; ob.z1[m] = o.z1; ob.R0[m] = o.R0; ob.R1[m] = o.R1; ob.a[m] = o.a;
+        }
+        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n, sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc, h->ld,
+                              h->c_lo, h->c_hi);
+        h->launches += 2;
+    } else {
+        for (int m = 0; m < k; ++m) {
+            const ekf_handle::QObs& o = h->q[m];
+            launch_lin_gain_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n, o.a, 3 + 2 * m, o.z0, o.z1, o.R0, o.R1,
+                                  ss, h->Pc, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m, sym_of(h));
+        }
+        h->launches += 2 * k;
     }
-    h->launches += 2 * k;
     CK(cudaGetLastError());
     const int ncl = ncols_loc(h);
     if (ncl > 0) {

@@ -135,8 +135,10 @@ __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restr
 // deferred gathers use; k_batch_gain (one thread per state row) then rebuilds row i of every K_q / B_q from the
 // |S| entries P0(i, S) it loads once.  Same operands, same order, same primitives as k_linearize + k_gain run k
 // times: the results are bit-identical (tests/test_parity_gpu.py::test_fused_batch_is_bit_identical).
+// Sharded filters pass Pc/ldc: the exchanged current columns of the slot set (Pc[slot][i] = P(i, col(slot)), see
+// ekf_shard.cu) replace the gathers from P, and [c_lo, c_hi) names the columns this rank stores.
 __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
-                            BatchObs ob, BatchLin* __restrict__ out) {
+                            BatchObs ob, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc) {
     __shared__ double G[EKF_BATCH_SLOTS][EKF_BATCH_SLOTS + 1];
     __shared__ double xs[EKF_BATCH_SLOTS];
     __shared__ double2 Ks[EKF_BATCH_SLOTS], Bs[EKF_BATCH_SLOTS];
@@ -150,7 +152,7 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
     __syncwarp();
     for (int e = lane; e < ns * ns; e += 32) {
         const int i = e / ns, j = e - i * ns;
-        G[i][j] = ldP(P, ld, col[i], col[j], sym);                 // nothing is pending at batch start
+        G[i][j] = Pc ? Pc[(int64_t)j * ldc + col[i]] : ldP(P, ld, col[i], col[j], sym);   // nothing is pending at batch start
     }
     if (lane < ns) xs[lane] = x[col[lane]];
     __syncwarp();
@@ -206,7 +208,8 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
 
 __global__ void __launch_bounds__(128)
 k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, BatchObs ob,
-             const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds) {
+             const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
+             const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi) {
     __shared__ BatchLin L;
     for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
         ((double*)&L)[e] = ((const double*)lin)[e];
@@ -214,6 +217,7 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int k = ob.k, ns = 3 + 2 * k;
+    const bool mine = i >= c_lo && i < c_hi;                       // column i of P is stored here (always, on one GPU)
     double pc[EKF_BATCH_SLOTS], pr[EKF_BATCH_SLOTS];               // current P(i, col_s) and (FULL) P(col_s, i)
     bool own[EKF_BATCH_SLOTS];                                     // SYM: element (i, col_s) is stored as (i, col_s), i <= col_s
 #pragma unroll
@@ -222,8 +226,8 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
         if (s < ns) {
             const int c = s < 3 ? s : ob.a[(s - 3) >> 1] + ((s - 3) & 1);
             own[s] = !sym || i <= c;
-            pc[s] = ldP(P, ld, i, c, sym);
-            if (!sym) pr[s] = P[(int64_t)c + (int64_t)i * ld];
+            pc[s] = Pc ? Pc[(int64_t)s * ldc + i] : ldP(P, ld, i, c, sym);
+            if (!sym && mine) pr[s] = P[(int64_t)c + (int64_t)(i - c_lo) * ld];    // row c of the (local) column i
         }
     }
     double xi = x[i];
@@ -243,12 +247,12 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
             xi = __dadd_rn(xi, dx);
             const double2 Ki = make_double2(k0, k1), Bi = make_double2(b0, b1);
             Kall[q * lds + i] = Ki;
-            Ball[q * lds + i] = Bi;
+            if (sym || mine) Ball[q * lds + i] = Bi;               // FULL slabs: B_q(:, i) only where column i lives
 #pragma unroll
             for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
                 if (s < ns) {
                     pc[s] = own[s] ? rank2_sub(pc[s], Ki, L.Bslot[q][s]) : rank2_sub(pc[s], L.Kslot[q][s], Bi);
-                    if (!sym) pr[s] = rank2_sub(pr[s], L.Kslot[q][s], Bi);
+                    if (!sym && mine) pr[s] = rank2_sub(pr[s], L.Kslot[q][s], Bi);
                 }
             }
         }
@@ -883,8 +887,8 @@ static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int nco
 // ------------------------------------------------------------------ state initialisation helpers
 __global__ void k_init_lowrank(double* __restrict__ P, int64_t ld, int n, int c_lo, const double* __restrict__ A, int r,
                                const double* __restrict__ d) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    int j = c_lo + blockIdx.y;
+    int i = blockIdx.y * blockDim.x + threadIdx.x;   // columns on grid.x: a slab can hold > 65535 of them (80k landmarks)
+    int j = c_lo + blockIdx.x;
     if (i >= n) return;
     double acc = 0.0;
     for (int q = 0; q < r; ++q) acc += A[i + (int64_t)q * n] * A[j + (int64_t)q * n];
@@ -928,9 +932,11 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 }
 
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
-                           BatchLin* lin, double2* Kall, double2* Ball, int64_t lds) {
-    k_batch_lin<<<1, 32, 0, st>>>(P, ld, x, sym, ob, lin);
-    k_batch_gain<<<cdiv(n, 128), 128, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds);
+                           BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc, int64_t ldc,
+                           int c_lo, int c_hi) {
+    if (!Pc) { c_lo = 0; c_hi = n; }
+    k_batch_lin<<<1, 32, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc);
+    k_batch_gain<<<cdiv(n, 128), 128, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi);
 }
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
@@ -1022,7 +1028,7 @@ void launch_associate_sig_batch(cudaStream_t st, const double* s, int N, const A
 void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo, int ncols, const double* A, int r,
                          const double* d) {
     if (ncols <= 0) return;
-    dim3 grid(cdiv(n, 256), ncols);
+    dim3 grid(ncols, cdiv(n, 256));
     k_init_lowrank<<<grid, 256, 0, st>>>(P, ld, n, c_lo, A, r, d);
 }
 

@@ -20,8 +20,10 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                      const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1);   // col_off: global index of column 0 (SYM slabs); variant < 0: default
 // fused batch (<= 8 observations with known slots; nothing may be pending): fills gain slabs 0..k-1 and updates x
+// Pc != null (sharded): slot columns come from the exchanged Pc[slot][0..n), P is the local slab of columns [c_lo, c_hi)
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
-                           BatchLin* lin, double2* Kall, double2* Ball, int64_t lds);
+                           BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc = nullptr,
+                           int64_t ldc = 0, int c_lo = 0, int c_hi = 0);
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym);
 #define EKF_ASSOC_BATCH 32
