@@ -691,6 +691,25 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
     return EKF_OK;
 }
 
+// Headless stand-in for the ellipse part of plot() (EKF_SLAM.m:180-229): numbers instead of figure calls.
+extern "C" int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo) {
+    CKH(h);
+    const int nb = h->N + 1;
+    if (!out || ldo < nb) return fail(h, EKF_EINVAL, "ekf_get_ellipses: buffer too small");
+    if (h->world > 1) return fail(h, EKF_EINVAL, "ekf_get_ellipses: not available on a sharded filter (diagonal blocks live on different ranks)");
+    CK(cudaSetDevice(h->p.device));
+    FLUSH(h);
+    double* d = nullptr;
+    CK(cudaMallocAsync(&d, sizeof(double) * 5 * nb, h->stream));
+    launch_ellipses(h->stream, h->P, h->ld, h->x, h->N, d, nb);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, d, sizeof(double) * nb, sizeof(double) * nb, 5, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaFreeAsync(d, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return EKF_OK;
+}
+
 extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t lda, const double* s,
                                  int32_t N) {
     CKH(h);

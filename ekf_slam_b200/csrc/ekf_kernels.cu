@@ -918,6 +918,42 @@ __global__ void k_mirror_upper(double* __restrict__ P, int64_t ld, int n) {
 // ------------------------------------------------------------------ launchers
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
+// ------------------------------------------------------------------ K6 covariance ellipses (headless plot data)
+// EKF_SLAM.m:180-229 draws, for the robot and for every landmark, the ellipse of the 2x2 diagonal block of P:
+// eig of the block, extents 2*sqrt(chi_square*lambda) with chi_square = 2.2788, rotated by arc = atan(v_y / v_x) of
+// the eigenvector of the LARGER eigenvalue (both branches of the reference's if/else reduce to that), scaled by .25
+// (robot, :198) or .50 (landmarks, :221) and centred on the estimate.  There is no graphics stack here, so the kernel
+// returns the numbers instead of drawing: out(b, :) = [cx, cy, semi-axis along v_max, semi-axis across, arc (rad)].
+__global__ void k_ellipses(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int N,
+                           double* __restrict__ out, int64_t ldo) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;           // block 0 = robot, b >= 1 = landmark b
+    if (b > N) return;
+    const int i = b == 0 ? 0 : 3 + 2 * (b - 1);
+    const double a = P[(int64_t)i + (int64_t)i * ld];
+    const double c = P[(int64_t)i + (int64_t)(i + 1) * ld];        // upper element: live in both storages
+    const double d = P[(int64_t)(i + 1) + (int64_t)(i + 1) * ld];
+    const double h = 0.5 * (a - d);
+    const double rad = sqrt(h * h + c * c);
+    const double mid = 0.5 * (a + d);
+    const double lmax = mid + rad, lmin = mid - rad;
+    double vx, vy;                                                 // eigenvector of lmax
+    if (c == 0.0) { vx = a > d ? 1.0 : 0.0; vy = a > d ? 0.0 : 1.0; }     // a == d: eig returns I, column 2 is used
+    else if (h >= 0.0) { vx = lmax - d; vy = c; }                  // (h + rad, c): no cancellation for h >= 0
+    else { vx = c; vy = lmax - a; }                                // (c, rad - h)
+    const double chi = 2.2788;
+    const double scale = b == 0 ? 0.25 : 0.50;
+    out[b] = x[i];
+    out[b + ldo] = x[i + 1];
+    out[b + 2 * ldo] = scale * (2.0 * sqrt(chi * lmax));
+    out[b + 3 * ldo] = scale * (2.0 * sqrt(chi * lmin));
+    out[b + 4 * ldo] = atan(vy / vx);
+}
+
+void launch_ellipses(cudaStream_t st, const double* P, int64_t ld, const double* x, int N, double* out, int64_t ldo) {
+    k_ellipses<<<cdiv(N + 1, 128), 128, 0, st>>>(P, ld, x, N, out, ldo);
+}
+
+
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym) {
     k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, u1, u2, C, sym);
     k_predict_x<<<1, 1, 0, st>>>(x, u1, u2);

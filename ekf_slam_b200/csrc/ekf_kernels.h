@@ -50,6 +50,7 @@ void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, in
                          double u1, double u2, double R0, double R1, double px, double py, double sig, const double* Pc,
                          int64_t ldc);
 void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n);
+void launch_ellipses(cudaStream_t st, const double* P, int64_t ld, const double* x, int N, double* out, int64_t ldo);
 
 // downdate kernel variant: < 0 = library default (TMA-staged DMMA flush, tile shape by rank; see launch_downdate);
 // the EKF_DOWNDATE_VARIANT environment variable overrides it per handle at ekf_create time.

@@ -227,8 +227,17 @@ class _FilterBase:
             self.chosen.append(('update', int(a)) if a > 0 else ('append', int(-a)))
 
     def plot(self, landmark_list=None):
-        """EKF_SLAM.m:154-234 draws MATLAB figures; unavailable on this box (no graphics stack)."""
+        """EKF_SLAM.m:154-234 draws MATLAB figures; unavailable on this box (no graphics stack).  The numbers it
+        would draw are available from covariance_ellipses()."""
         return None
+
+    def covariance_ellipses(self):
+        """The ellipses plot() draws (EKF_SLAM.m:180-229) as an (N+1) x 5 array [cx, cy, semi-axis along the major
+        eigenvector, semi-axis across, arc_rad]; row 0 = robot (scale .25), row b = landmark b (scale .50)."""
+        nb = self.N + 1
+        out = np.empty((nb, 5), order='F')
+        self._ck(self._lib.ekf_get_ellipses(self._h, L.dptr(out), nb))
+        return out
 
     def flush(self):
         self._ck(self._lib.ekf_flush(self._h))

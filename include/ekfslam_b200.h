@@ -126,6 +126,10 @@ int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t l
 /* Populated synthetic map without a 3.2 GB H2D copy: P = A A^T / r + diag(d), A is n x r column-major. */
 int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const double* s, int32_t N,
                               const double* A, int32_t r, const double* d);
+/* plot(h, landmark_list), EKF_SLAM.m:154-234, minus the drawing: the covariance ellipses it would draw (:180-229), as
+ * (N+1) x 5 column-major rows [cx, cy, semi-axis along the major eigenvector, semi-axis across, arc_rad]; row 0 is the
+ * robot (scale .25, :198), row b the landmark b (scale .50, :221); chi_square = 2.2788 as upstream. */
+int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo);
 /* Property writes (public, mutable after construction in the reference). */
 int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh);
 

@@ -141,7 +141,13 @@ classdef EKFSLAM_B200_Base < handle
         end
 
         function plot(~, ~)
-            % EKF_SLAM.m:154-234 draws figures; headless build: no-op.
+            % EKF_SLAM.m:154-234 draws figures; headless build: no-op (see covarianceEllipses).
+        end
+
+        function E = covarianceEllipses(h)
+            % rows [cx, cy, semi-axis along the major eigenvector, semi-axis across, arc_rad] of the ellipses
+            % plot() draws upstream (EKF_SLAM.m:180-229); row 1 = robot, row 1+b = landmark b.
+            E = ekfslam_mex('get_ellipses', h.hnd);
         end
 
         function flush(h)

@@ -177,6 +177,13 @@ void mexFunction(int nlhs, mxArray* plhs[], int nrhs, const mxArray* prhs[]) {
         check(h, ekf_get_P_block(h, r1 - 1, c1 - 1, nr, nc, mxGetPr(plhs[0]), nr));
         return;
     }
+    if (!strcmp(verb, "get_ellipses")) {      /* (N+1) x 5: what plot() would draw, EKF_SLAM.m:180-229 */
+        int32_t N = 0;
+        check(h, ekf_n_landmarks(h, &N));
+        plhs[0] = mxCreateDoubleMatrix((size_t)N + 1, 5, mxREAL);
+        check(h, ekf_get_ellipses(h, mxGetPr(plhs[0]), N + 1));
+        return;
+    }
     if (!strcmp(verb, "set_state")) {         /* ekfslam_mex('set_state', h, x, P, s) */
         size_t n = mxGetNumberOfElements(prhs[2]);
         int32_t N = (int32_t)((n - 3) / 2);

@@ -222,3 +222,33 @@ class EKF_SLAM_UC(EKF_SLAM):
                 else:
                     self._update(z, R, idx)                                   # :125-146
                     self.chosen.append(('update', idx))
+
+
+def ellipse_params(x, P):
+    """The ellipses EKF_SLAM.plot draws, EKF_SLAM.m:180-229, restated literally (eig of each 2x2 diagonal block taken
+    with both off-diagonal entries as the reference does, the if/else on eigval(1,1) > eigval(2,2), atan of the
+    eigenvector ratio, scale .25 for the robot and .50 for landmarks) but returning numbers instead of plotting:
+    rows [cx, cy, semi-axis along the drawn x direction, semi-axis along y, arc_rad].  Test infrastructure only."""
+    x = np.asarray(x, dtype=np.float64)
+    out = []
+    starts = [0] + list(range(3, x.size, 2))                                  # :181 robot, :203 ii = 4:2:end
+    for b, i in enumerate(starts):
+        Sigma = np.array([[P[i, i], P[i, i + 1]], [P[i + 1, i], P[i + 1, i + 1]]])   # :181 / :204
+        mu = (x[i], x[i + 1])                                                 # :182 / :205
+        if Sigma[0, 1] == Sigma[1, 0]:
+            eigval, eigvec = np.linalg.eigh(Sigma)                            # MATLAB eig, symmetric input: ascending
+        else:
+            eigval, eigvec = np.linalg.eig(Sigma)                             # :183 / :207
+        chi_square = 2.2788                                                   # :184 / :208
+        major = 2 * np.sqrt(chi_square * eigval[0])                           # :185
+        minor = 2 * np.sqrt(chi_square * eigval[1])                           # :186
+        with np.errstate(divide='ignore'):
+            if eigval[0] > eigval[1]:                                         # :188
+                arc = np.arctan(np.divide(eigvec[1, 0], eigvec[0, 0]))        # :189
+                ax, ay = major, minor                                         # :190-191
+            else:
+                arc = np.arctan(np.divide(eigvec[1, 1], eigvec[0, 1]))        # :193
+                ax, ay = minor, major                                         # :194-195
+        scale = 0.25 if b == 0 else 0.50                                      # :198 / :221
+        out.append([mu[0], mu[1], ax * scale, ay * scale, arc])
+    return np.array(out)

@@ -217,3 +217,18 @@ def test_oracle_matches_50_digit_restatement():
     xe = np.array([float(v) for v in x], dtype=np.float64)
     Pe = np.array([[float(P[i, j]) for j in range(P.cols)] for i in range(P.rows)])
     assert G.rel(o.x, xe) <= 1e-12 and G.rel(o.P, Pe) <= 1e-12, (G.rel(o.x, xe), G.rel(o.P, Pe))
+
+
+def test_ellipse_params_known_answers():
+    """EKF_SLAM.m:180-229: a diagonal block draws an axis-aligned ellipse, extents 2*sqrt(2.2788*lambda)*scale."""
+    x = np.array([1.0, 2.0, 30.0, 5.0, 6.0])
+    P = np.diag([0.04, 0.01, 0.1, 0.09, 0.25])
+    e = O.ellipse_params(x, P)
+    assert e.shape == (2, 5) and np.array_equal(e[:, :2], [[1.0, 2.0], [5.0, 6.0]])
+    assert np.allclose(e[0, 2:4], [0.25 * 2 * np.sqrt(2.2788 * 0.04), 0.25 * 2 * np.sqrt(2.2788 * 0.01)]) and e[0, 4] == 0.0
+    assert np.allclose(e[1, 2:4], [0.5 * 2 * np.sqrt(2.2788 * 0.25), 0.5 * 2 * np.sqrt(2.2788 * 0.09)])
+    assert abs(abs(e[1, 4]) - np.pi / 2) < 1e-15                       # larger variance along y: atan(1/0)
+    P2 = P.copy(); P2[3, 4] = P2[4, 3] = 0.05
+    a = O.ellipse_params(x, P2)[1, 4]
+    lam, vec = np.linalg.eigh(P2[3:5, 3:5])
+    assert abs(np.tan(a) - vec[1, 1] / vec[0, 1]) < 1e-12

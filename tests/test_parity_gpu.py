@@ -361,3 +361,29 @@ def test_measure_batches_associations_and_handles_appends_mid_batch():
     assert multi > 0 and g.N == (o.x.size - 3) // 2
     print('UC k=9 with mid-batch appends: worst rel err x %.2e P %.2e' % worst)
     g.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+def test_covariance_ellipses_match_reference_plot_math(storage):
+    """K6: the ellipses plot() would draw (EKF_SLAM.m:180-229) vs the literal eig-based restatement."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=20, T=150, k=5, mode='nearest')
+    g = E.EKF_SLAM_UC(capacity_landmarks=20, storage=storage, defer_m=4)
+    o = O.EKF_SLAM_UC()
+    for t in range(w.T):
+        g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
+        o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
+    got, want = g.covariance_ellipses(), O.ellipse_params(o.x, o.P)
+    assert got.shape == want.shape == (g.N + 1, 5)
+    assert np.allclose(got[:, :4], want[:, :4], rtol=1e-9, atol=0)
+    d = np.abs(got[:, 4] - want[:, 4])
+    d = np.minimum(d, np.abs(d - np.pi))                               # atan branch: +-pi/2 is the same axis
+    assert d.max() < 1e-7, d.max()
+    # exact diagonal blocks (fresh filter: P = 0.1*eye(3)): equal eigenvalues -> eig returns I, column 2 -> pi/2
+    f = E.EKF_SLAM(capacity_landmarks=2, storage=storage)
+    e0 = f.covariance_ellipses()
+    assert e0.shape == (1, 5) and abs(e0[0, 4] - np.pi / 2) < 1e-15
+    assert np.allclose(e0[0, 2:4], 0.25 * 2 * np.sqrt(2.2788 * 0.1))
+    f.close(); g.close()
