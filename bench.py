@@ -112,7 +112,7 @@ class ClockSampler:
             try:
                 mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 rs = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
-                self.samples.append((mhz, rs))
+                self.samples.append((mhz, rs, time.perf_counter()))
             except Exception:
                 pass
             time.sleep(0.002)
@@ -121,17 +121,21 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(',')])
 
-    def stop(self):
+    def stop(self, window=None):
+        """window = (t0, t1) in time.perf_counter() seconds: keep only the samples taken inside the timed region."""
         if self.nv is not None:
             self.stop_flag = True
             self.th.join(timeout=1.0)
+            if window is not None:
+                inside = [q for q in self.samples if window[0] <= q[2] <= window[1]]
+                self.samples = inside if inside else self.samples[-1:]
             nv = self.nv
             masks = {'hw_slowdown': getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8),
                      'hw_thermal_slowdown': getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40),
                      'sw_thermal_slowdown': getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20),
                      'sw_power_cap': getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4)}
-            sm = [m for m, _ in self.samples]
-            reasons = sorted(nm for nm, bit in masks.items() if any(r & bit for _, r in self.samples))
+            sm = [q[0] for q in self.samples]
+            reasons = sorted(nm for nm, bit in masks.items() if any(q[1] & bit for q in self.samples))
             return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': self.max_mhz, 'samples': len(sm),
                     'reasons': reasons, 'source': 'nvml @2ms'}
         if not self.proc:
@@ -270,20 +274,24 @@ def main():
 
     for t in range(W):
         step_resident(t)
-    barrier()
     f.profile_enable(True)
     clocks = ClockSampler(local)
     if rank == 0:
-        clocks.start()
+        clocks.start()                  # before the barrier: NVML start-up must not make rank 0 a straggler inside the timed region
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    th0 = time.perf_counter()
     for t in range(W, W + K):
         step_resident(t)
+    host_ms = (time.perf_counter() - th0) * 1e3          # host time to ENQUEUE the K steps (no sync inside)
     e1.record()
     barrier()
+    th1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
-    clk = clocks.stop() if rank == 0 else None
+    clk = clocks.stop((th0, th1)) if rank == 0 else None
     dd_ms, dd_n, launches = f.profile_read()
+    xch_ms, xch_n, xch_p2p = f.profile_exchange() if world > 1 else (0.0, 0, False)
     f.profile_enable(False)
     dd_bytes = f.downdate_bytes()
     slab = f.shard_info()
@@ -341,17 +349,18 @@ def main():
                    '%d landmarks, predict + %d updates per step' % (N, k),
                    'landmarks': N, 'k': k, 'storage': args.storage, 'n_state': n, 'defer_m': args.defer,
                    'downdate': 'one rank-%d pass over P per %d observations' % (2 * min(args.defer, k), min(args.defer, k)) if args.defer > 1 else 'one rank-2 pass over P per observation',
-                   'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one NCCL %s of the 3+2k current columns; slowest slab cols [%d,%d)' % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', slab[2], slab[3])) if world > 1 else 'single GPU',
+                   'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one exchange of the 3+2k current columns (peer-memory scatter, or NCCL %s with EKF_SHARD_EXCHANGE=nccl); slowest slab cols [%d,%d)' % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', slab[2], slab[3])) if world > 1 else 'single GPU',
                    'l2': 'no flush needed: each update streams %.2f GB of P, far beyond the 126 MB L2' % (dd_bytes / 2e9)},
         'roofline': {'bound': 'hbm', 'kernel': 'k_downdate_tma (rank-%d flush: cp.async.bulk staging + FP64 DMMA)' % (2 * min(max(args.defer, 1), k)), 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
                      'frac_of_8TBps_nominal': achieved / 8000.0, 'traffic': None,
                      'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,
                      'share_of_step': dd_ms / ms},
+        'exchange': ({'avg_ms': xch_ms / max(xch_n, 1), 'per_step': xch_n / K, 'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if xch_p2p else 'NCCL'} if world > 1 else None),
         'e2e': {'value': K * k / (e2e_ms * 1e-3), 'unit': UNIT,
                 'h2d_bytes_per_step': int(16 + obs[0].nbytes + k * (24 + 16)), 'd2h_bytes_per_step': int(2 * 8 * n + k * 24),
                 'api': 'EKF_SLAM_UC.predict(u); .measure(laserData,u,landmark_list); read x'},
-        'gpu_launches': int(launches), 'clocks': clk,
+        'gpu_launches': int(launches), 'clocks': clk, 'host_enqueue_ms_per_step': host_ms / K,
     }
     if not args.no_cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(N, k, x, A, d, us, obs, args.cpu_budget)
@@ -438,19 +447,21 @@ def run_mc(args):
 
     for t in range(W):
         step_resident(t)
-    barrier()
     b.profile(True)
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    th0 = time.perf_counter()
     for t in range(W, W + K):
         step_resident(t)
     e1.record()
     barrier()
+    th1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
-    clk = clocks.stop() if rank == 0 else None
+    clk = clocks.stop((th0, th1)) if rank == 0 else None
     kern_ms, kern_n, flush_ms = b.profile(False)
     dd_bytes = b.downdate_bytes()
     b.sync()

@@ -61,6 +61,7 @@ SIGNATURES = {
     'ekf_last_error': [_H],
     'ekf_profile_enable': [_H, C.c_int32],
     'ekf_profile_read': [_H, _DP, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
+    'ekf_profile_exchange': [_H, _DP, C.POINTER(C.c_int64), _IP],
     'ekf_downdate_bytes': [_H, _DP],
     'ekf_version': [],
     # Monte-Carlo batch

@@ -32,7 +32,16 @@ struct ekf_handle {
     int rank = 0, world = 1;
     int c_lo = 0, c_hi = 0;
     ncclComm_t comm = nullptr;
-    double* Pc = nullptr;      // EKF_MAX_SLOTS x ld: broadcast columns of the current batch
+    double* Pc = nullptr;      // 2 x EKF_MAX_SLOTS x ld: exchanged columns of the current batch (double-buffered by batch parity)
+    double* Pc_cur = nullptr;  // buffer holding the batch being consumed
+    bool p2p = false;          // exchange by direct stores into cudaIpc-mapped peer memory (default) instead of NCCL
+    PeerSet peers;             // every rank's Pc / flag words as seen from this process
+    int* xflags = nullptr;     // [world] batch number last published by each rank
+    unsigned int* xticket = nullptr;
+    int epoch = 0;
+    double xch_ms = 0.0;       // profile: exchange time (CUDA events)
+    std::vector<cudaEvent_t> xev;
+    size_t xev_used = 0;
     double2* Bc = nullptr;     // EKF_MAX_DEFER x EKF_MAX_SLOTS: B_q(:, col(slot))
     struct QObs { double z0, z1, R0, R1; int a; };
     std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
@@ -82,6 +91,7 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -95,7 +105,7 @@ static bool nccl_load(std::string& err) {
     *(void**)(&g_nccl.field) = dlsym(so, name); \
     if (!g_nccl.field) { err = std::string("dlsym ") + name; return false; }
     SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
-    SYM(Broadcast, "ncclBroadcast") SYM(AllReduce, "ncclAllReduce") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
+    SYM(Broadcast, "ncclBroadcast") SYM(AllReduce, "ncclAllReduce") SYM(AllGather, "ncclAllGather") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
     SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
     g_nccl.so = so;
@@ -178,7 +188,10 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd);
-    cudaFree(h->Pc); cudaFree(h->Bc);
+    for (int g = 0; g < h->world && h->p2p; ++g)
+        if (g != h->rank) { if (h->peers.pc[g]) cudaIpcCloseMemHandle(h->peers.pc[g]); if (h->peers.flags[g]) cudaIpcCloseMemHandle(h->peers.flags[g]); }
+    for (auto e : h->xev) cudaEventDestroy(e);
+    cudaFree(h->Pc); cudaFree(h->Bc); cudaFree(h->xflags); cudaFree(h->xticket);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
@@ -200,6 +213,49 @@ static int32_t init_state(ekf_handle* h) {
     CK(cudaStreamSynchronize(h->stream));
     h->N = 0;
     h->m_pend = 0;
+    return EKF_OK;
+}
+
+// Map every rank's Pc buffer and flag words into this process (cudaIpc), handles all-gathered over NCCL once at
+// creation.  If any rank cannot map a peer (no P2P path), every rank falls back to the NCCL exchange together.
+static int32_t setup_p2p(ekf_handle* h) {
+    const int W = h->world;
+    CK(cudaMalloc(&h->xflags, sizeof(int) * EKF_MAX_PEERS));
+    CK(cudaMemset(h->xflags, 0, sizeof(int) * EKF_MAX_PEERS));
+    CK(cudaMalloc(&h->xticket, sizeof(unsigned int)));
+    CK(cudaMemset(h->xticket, 0, sizeof(unsigned int)));
+    struct Pack { cudaIpcMemHandle_t pc, fl; int ok; int pad[15]; };
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    Pack mine;
+    memset(&mine, 0, sizeof(mine));
+    mine.ok = cudaIpcGetMemHandle(&mine.pc, h->Pc) == cudaSuccess && cudaIpcGetMemHandle(&mine.fl, h->xflags) == cudaSuccess;
+    cudaGetLastError();
+    Pack* d_all = nullptr;
+    CK(cudaMalloc(&d_all, sizeof(Pack) * (W + 1)));
+    CK(cudaMemcpy(d_all + W, &mine, sizeof(Pack), cudaMemcpyHostToDevice));
+    CKN(g_nccl.AllGather(d_all + W, d_all, sizeof(Pack), ncclChar, h->comm, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<Pack> all(W);
+    CK(cudaMemcpy(all.data(), d_all, sizeof(Pack) * W, cudaMemcpyDeviceToHost));
+    int ok = 1;
+    for (int g = 0; g < W; ++g) ok &= all[g].ok;
+    memset(&h->peers, 0, sizeof(h->peers));
+    h->peers.world = W; h->peers.rank = h->rank;
+    for (int g = 0; g < W && ok; ++g) {
+        if (g == h->rank) { h->peers.pc[g] = h->Pc; h->peers.flags[g] = h->xflags; continue; }
+        void *ppc = nullptr, *pfl = nullptr;
+        if (cudaIpcOpenMemHandle(&ppc, all[g].pc, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+            cudaIpcOpenMemHandle(&pfl, all[g].fl, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cudaGetLastError(); break; }
+        h->peers.pc[g] = (double*)ppc; h->peers.flags[g] = (int*)pfl;
+    }
+    // agree: P2P only if every rank mapped every peer
+    int* d_ok = (int*)d_all;
+    CK(cudaMemcpy(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice));
+    CKN(g_nccl.AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, h->comm, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost));
+    cudaFree(d_all);
+    h->p2p = ok != 0;
     return EKF_OK;
 }
 
@@ -232,11 +288,17 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMalloc(&h->P, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
         if (world > 1) {
             if (!nccl_load(h->err)) return EKF_ENCCL;
-            CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS));
+            CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS * 2));
+            h->Pc_cur = h->Pc;
             CK(cudaMalloc(&h->Bc, sizeof(double2) * EKF_MAX_DEFER * EKF_MAX_SLOTS));
             ncclUniqueId id;
             memcpy(&id, id128, 128);
             CKN(g_nccl.CommInitRank(&h->comm, world, id, rank));
+            const char* xe = getenv("EKF_SHARD_EXCHANGE");
+            if (!(xe && std::string(xe) == "nccl") && world <= EKF_MAX_PEERS) {
+                int32_t rp = setup_p2p(h);
+                if (rp != EKF_OK) return rp;
+            }
         }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
@@ -335,20 +397,44 @@ static int32_t prof_end(ekf_handle* h) {
 //   SYM  slabs: each rank contributes the part of every symmetric column it stores, zero elsewhere; all-reduce.
 static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
     const int sym = sym_of(h);
-    launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld, sym);
-    CK(cudaGetLastError());
-    if (sym) {
-        CKN(g_nccl.AllReduce(h->Pc, h->Pc, (size_t)ss.n * h->ld, ncclDouble, ncclSum, h->comm, h->stream));
-    } else {
-        CKN(g_nccl.GroupStart());
-        CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
-        for (int sl = 3; sl + 1 < ss.n; sl += 2) {
-            double* p = h->Pc + (size_t)sl * h->ld;
-            CKN(g_nccl.Broadcast(p, p, 2 * (size_t)h->ld, ncclDouble, owner_of_col(h, ss.col[sl]), h->comm, h->stream));
+    if (h->prof) {
+        if (h->xev_used + 2 > h->xev.size()) {
+            size_t old = h->xev.size();
+            h->xev.resize(old + 256);
+            for (size_t i = old; i < h->xev.size(); ++i) CK(cudaEventCreate(&h->xev[i]));
         }
-        CKN(g_nccl.GroupEnd());
+        CK(cudaEventRecord(h->xev[h->xev_used], h->stream));
     }
-    h->launches += 1;
+    if (h->p2p) {
+        // peer-memory scatter: every rank stores the elements it owns into every rank's buffer, then publishes the batch
+        h->epoch += 1;
+        const int64_t buf_off = (int64_t)(h->epoch & 1) * EKF_MAX_SLOTS * h->ld;
+        launch_scatter_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->peers, buf_off, sym, h->epoch, h->xticket,
+                            h->xflags);
+        h->Pc_cur = h->Pc + buf_off;
+        h->launches += 2;
+        CK(cudaGetLastError());
+    } else {
+        h->Pc_cur = h->Pc;
+        launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld, sym);
+        CK(cudaGetLastError());
+        if (sym) {
+            CKN(g_nccl.AllReduce(h->Pc, h->Pc, (size_t)ss.n * h->ld, ncclDouble, ncclSum, h->comm, h->stream));
+        } else {
+            CKN(g_nccl.GroupStart());
+            CKN(g_nccl.Broadcast(h->Pc, h->Pc, 3 * (size_t)h->ld, ncclDouble, 0, h->comm, h->stream));
+            for (int sl = 3; sl + 1 < ss.n; sl += 2) {
+                double* p = h->Pc + (size_t)sl * h->ld;
+                CKN(g_nccl.Broadcast(p, p, 2 * (size_t)h->ld, ncclDouble, owner_of_col(h, ss.col[sl]), h->comm, h->stream));
+            }
+            CKN(g_nccl.GroupEnd());
+        }
+        h->launches += 1;
+    }
+    if (h->prof) {
+        CK(cudaEventRecord(h->xev[h->xev_used + 1], h->stream));
+        h->xev_used += 2;
+    }
     return EKF_OK;
 }
 
@@ -373,14 +459,14 @@ static int32_t flush_sharded(ekf_handle* h) {
             const ekf_handle::QObs& o = h->q[m];
             ob.z0[m] = o.z0; ob.z1[m] = o.z1; ob.R0[m] = o.R0; ob.R1[m] = o.R1; ob.a[m] = o.a;
         }
-        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n, sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc, h->ld,
+        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n, sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc_cur, h->ld,
                               h->c_lo, h->c_hi);
         h->launches += 2;
     } else {
         for (int m = 0; m < k; ++m) {
             const ekf_handle::QObs& o = h->q[m];
             launch_lin_gain_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n, o.a, 3 + 2 * m, o.z0, o.z1, o.R0, o.R1,
-                                  ss, h->Pc, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m, sym_of(h));
+                                  ss, h->Pc_cur, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m, sym_of(h));
         }
         h->launches += 2 * k;
     }
@@ -467,7 +553,7 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
         int32_t rcx = exchange_cols(h, ss, n_of(h));
         if (rcx != EKF_OK) return rcx;
         launch_append_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1],
-                            pos[0], pos[1], signature, h->Pc, h->ld);
+                            pos[0], pos[1], signature, h->Pc_cur, h->ld);
         h->launches += 1;
     } else
     launch_append(h->stream, h->P, h->ld, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1], pos[0], pos[1],
@@ -766,7 +852,14 @@ extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
     CKH(h);
     CK(cudaStreamSynchronize(h->stream));
     h->prof = on != 0;
+    if (h->prof) {          // create the event pool here, outside anybody's timed region (cudaEventCreate costs microseconds)
+        CK(cudaSetDevice(h->p.device));
+        while (h->ev.size() < 8192) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->ev.push_back(e); }
+        while (h->world > 1 && h->xev.size() < 2048) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->xev.push_back(e); }
+    }
     h->ev_used = 0;
+    h->xev_used = 0;
+    h->xch_ms = 0.0;
     h->dd_ms = 0.0;
     h->dd_launches = 0;
     h->dd_terms = 0;
@@ -787,6 +880,23 @@ extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, in
     if (downdate_ms_total) *downdate_ms_total = h->dd_ms;
     if (downdate_launches) *downdate_launches = h->dd_launches;
     if (kernel_launches_total) *kernel_launches_total = h->launches;
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_profile_exchange(ekf_handle* h, double* exchange_ms_total, int64_t* exchanges, int32_t* p2p) {
+    CKH(h);
+    CK(cudaStreamSynchronize(h->stream));
+    const int64_t cnt = (int64_t)(h->xev_used / 2);
+    for (size_t i = 0; i + 1 < h->xev_used; i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->xev[i], h->xev[i + 1]));
+        h->xch_ms += ms;
+    }
+    h->xev_used = 0;
+    if (exchange_ms_total) *exchange_ms_total = h->xch_ms;
+    if (exchanges) *exchanges = cnt;
+    if (p2p) *p2p = h->p2p ? 1 : 0;
+    h->xch_ms = 0.0;
     return EKF_OK;
 }
 

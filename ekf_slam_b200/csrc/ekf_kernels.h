@@ -39,6 +39,10 @@ void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo
                          const double* d);
 void launch_predict_x(cudaStream_t st, double* x, double u1, double u2);
 // ---- column-slab sharded filter (ekf_shard.cu) ----
+#define EKF_MAX_PEERS 8
+struct PeerSet { double* pc[EKF_MAX_PEERS]; int* flags[EKF_MAX_PEERS]; int world, rank; };   // cudaIpc-mapped Pc buffers / flag words of every rank
+void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags);
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
                       double* Pc, int64_t ldc, int sym);
 void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, int a,

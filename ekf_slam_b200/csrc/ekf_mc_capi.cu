@@ -248,6 +248,12 @@ extern "C" int32_t ekfb_profile(ekfb_handle* h, int32_t enable, double* step_ms_
     if (flush_ms_total) *flush_ms_total = h->flush_ms;
     if (steps) *steps = h->steps;
     if (enable >= 0) { h->prof = enable != 0; h->step_ms = 0.0; h->flush_ms = 0.0; h->steps = 0; }
+    if (h->prof)            // event pool created here, outside anybody's timed region
+        while (h->evs.size() < 4096) {
+            cudaEvent_t a0 = nullptr, a1 = nullptr;
+            CKB(cudaEventCreate(&a0)); CKB(cudaEventCreate(&a1));
+            h->evs.push_back({a0, a1});
+        }
     return EKF_OK;
 }
 

@@ -54,6 +54,59 @@ __global__ void k_pack_cols(const double* __restrict__ Ploc, int64_t ld, int c_l
     if (i < n) Pc[(int64_t)slot * ldc + i] = Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld];
 }
 
+// ---- peer-memory exchange (default on one box): no collective library call on the data path ----
+// Every element of an exchanged column has exactly one rank that stores it, so the "all-reduce" is really a scatter:
+// the pack kernel writes each element it owns straight into the Pc buffer of EVERY rank over NVLink (plain stores into
+// cudaIpc-mapped peer memory, coalesced along the column), then publishes the batch number in every peer's flag
+// word (system-scope release).  Consumers wait on their local flag words (k_wait_flags).  Pc is double-buffered by
+// batch parity: a rank can only start writing batch e+2 after it consumed batch e+1, which every peer signalled
+// after it had finished reading batch e.
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void k_scatter_cols(const double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, SlotSet ss, int n,
+                               PeerSet ps, int64_t buf_off, int sym, int epoch, unsigned int* __restrict__ ticket) {
+    const int slot = blockIdx.y;
+    const int c = ss.col[slot];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        bool have = false;
+        double v = 0.0;
+        if (!sym || i <= c) { if (c >= c_lo && c < c_hi) { v = Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld]; have = true; } }
+        else if (i >= c_lo && i < c_hi) { v = Ploc[(int64_t)c + (int64_t)(i - c_lo) * ld]; have = true; }   // (c, i) lives in column i
+        if (have)
+            for (int g = 0; g < ps.world; ++g) ps.pc[g][buf_off + (int64_t)slot * ld + i] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int total = gridDim.x * gridDim.y;
+        if (atomicAdd(ticket, 1u) == total - 1) {              // last block: every block's stores are fenced
+            *ticket = 0;
+            __threadfence_system();
+            for (int g = 0; g < ps.world; ++g) st_release_sys(ps.flags[g] + ps.rank, epoch);
+        }
+    }
+}
+
+__global__ void k_wait_flags(const int* __restrict__ flags, int world, int epoch) {
+    if ((int)threadIdx.x < world)
+        while (ld_acquire_sys(flags + threadIdx.x) < epoch) { }
+}
+
+void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags) {
+    dim3 grid((n + 255) / 256, ss.n);
+    k_scatter_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, ps, buf_off, sym, epoch, ticket);
+    k_wait_flags<<<1, 32, 0, st>>>(flags, ps.world, epoch);
+}
+
 // One warp, replicated on every rank: EKF_SLAM.m:125-143 from the broadcast columns, plus B_m(:, c) for every
 // column c of the batch set (needed to correct the columns of later observations).
 __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet ss, const double* __restrict__ x,

@@ -256,6 +256,12 @@ class _FilterBase:
         self._ck(self._lib.ekf_profile_read(self._h, ct.byref(ms), ct.byref(nd), ct.byref(nl)))
         return ms.value, nd.value, nl.value
 
+    def profile_exchange(self):
+        """(total ms, count, p2p flag) of the sharded column exchanges since profiling was enabled."""
+        ms, n, p = ct.c_double(), ct.c_int64(), ct.c_int32()
+        self._ck(self._lib.ekf_profile_exchange(self._h, ct.byref(ms), ct.byref(n), ct.byref(p)))
+        return ms.value, n.value, bool(p.value)
+
     def downdate_bytes(self):
         b = ct.c_double()
         self._ck(self._lib.ekf_downdate_bytes(self._h, ct.byref(b)))

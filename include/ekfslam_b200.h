@@ -71,7 +71,9 @@ int32_t ekf_destroy(ekf_handle* h);
 /* One large filter across `world` GPUs (one process per GPU): rank g stores the column slab
  * [c_lo, c_hi) of the column-major P (by symmetry the "row slab" of a row-major view), x/s/gains replicated.
  * Every rank makes the same calls with the same arguments; per batch of <= defer_m observations the only
- * exchange is an NCCL broadcast of the 3 robot columns and the 2 columns of each observed landmark.
+ * exchange is that of the 3 robot columns and the 2 columns of each observed landmark: by default every rank stores the
+ * elements it owns straight into every peer's buffer (cudaIpc-mapped peer memory over NVLink, flag-word handshake);
+ * EKF_SHARD_EXCHANGE=nccl (or no P2P path) uses NCCL instead (broadcast from the owners / all-reduce below).
  * id128 = 128 bytes from ekf_nccl_unique_id() on rank 0, distributed by the host (MPI, torch.distributed, file).
  * FULL slabs hold equal column counts and exchange by broadcast from the owners; SYM slabs hold equal live
  * area (boundaries at capacity*sqrt(g/world)) and assemble symmetric columns with one all-reduce of zero-padded
@@ -143,6 +145,9 @@ const char* ekf_last_error(ekf_handle* h);
 int32_t ekf_profile_enable(ekf_handle* h, int32_t on);
 int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, int64_t* downdate_launches,
                          int64_t* kernel_launches_total);
+/* Sharded filters: CUDA-event time of the column exchanges since profiling was enabled (and whether the peer-memory
+ * path is in use, 0 = NCCL collectives).  Resets the accumulated time. */
+int32_t ekf_profile_exchange(ekf_handle* h, double* exchange_ms_total, int64_t* exchanges, int32_t* p2p);
 /* Bytes the downdate kernel must move per launch at the current n and storage. */
 int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes);
 

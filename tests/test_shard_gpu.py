@@ -14,12 +14,15 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
+@pytest.mark.parametrize('exchange', ['p2p', 'nccl'])
 @pytest.mark.parametrize('world', [2, 4])
-def test_sharded_filter_matches_oracle_and_single_gpu(world):
+def test_sharded_filter_matches_oracle_and_single_gpu(world, exchange):
+    """Both exchange paths: peer-memory scatter over cudaIpc-mapped buffers (default) and NCCL collectives."""
     if _ngpu() < world:
         pytest.skip('needs %d GPUs' % world)
+    env = dict(os.environ, EKF_SHARD_EXCHANGE=exchange)
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
-           '--master-addr', '127.0.0.1', '--master-port', str(29500 + world), os.path.join(ROOT, 'tests', 'shard_worker.py')]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+           '--master-addr', '127.0.0.1', '--master-port', str(29500 + world + (10 if exchange == 'nccl' else 0)), os.path.join(ROOT, 'tests', 'shard_worker.py')]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, cwd=ROOT, env=env)
     print(r.stdout[-4000:]); print(r.stderr[-4000:])
     assert r.returncode == 0 and 'SHARD_WORKER_OK' in r.stdout
