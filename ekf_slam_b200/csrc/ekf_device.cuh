@@ -85,55 +85,80 @@ __device__ __forceinline__ double ldP_def(const double* __restrict__ P, int64_t 
 // Range-bearing measurement model about landmark slot a (0-based state index of its x coordinate).
 // Follows EKF_SLAM.m:125-138 == Correspondence.m:50-63 with explicit (non-contracted) roundings so a
 // plain C restatement compiled with -ffp-contract=off reproduces every bit except atan2's last ulp.
+// It is written as entry-wise pieces (mm_* / ic_*) so that a warp can evaluate the entries on different lanes
+// (k_batch_lin) and still produce exactly the bits of the one-thread form below.
+struct MMPrep { double d0, d1, q, sq, iq; };
+__device__ __forceinline__ MMPrep mm_prep(const double xr[3], double mx, double my) {
+    MMPrep p;
+    p.d0 = __dsub_rn(mx, xr[0]);
+    p.d1 = __dsub_rn(my, xr[1]);
+    p.q = __dadd_rn(__dmul_rn(p.d0, p.d0), __dmul_rn(p.d1, p.d1));
+    p.sq = sqrt(p.q);
+    p.iq = 1.0 / p.q;
+    return p;
+}
+__device__ __forceinline__ double mm_bearing(const MMPrep& p, double theta) {          // z_k(2), EKF_SLAM.m:130
+    return wrapTo360(__dsub_rn(atan2d(p.d1, p.d0), theta));
+}
+__device__ __forceinline__ double mm_H(const MMPrep& p, int e) {                        // entry e = 5 r + c of H_k's 2 x 5 block, :137-138
+    switch (e) {
+        case 0: return __dmul_rn(p.iq, __dmul_rn(-p.sq, p.d0));
+        case 1: return __dmul_rn(p.iq, __dmul_rn(-p.sq, p.d1));
+        case 2: return __dmul_rn(p.iq, 0.0);
+        case 3: return __dmul_rn(p.iq, __dmul_rn(p.sq, p.d0));
+        case 4: return __dmul_rn(p.iq, __dmul_rn(p.sq, p.d1));
+        case 5: return __dmul_rn(p.iq, p.d1);
+        case 6: return __dmul_rn(p.iq, -p.d0);
+        case 7: return __dmul_rn(p.iq, -p.q);
+        case 8: return __dmul_rn(p.iq, -p.d1);
+        default: return __dmul_rn(p.iq, p.d0);
+    }
+}
 __device__ __forceinline__ void measurement_model(const double xr[3], double mx, double my,
                                                   double zk[2], double Hs[2][5]) {
-    double d0 = __dsub_rn(mx, xr[0]);
-    double d1 = __dsub_rn(my, xr[1]);
-    double q = __dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1));
-    double sq = sqrt(q);
-    zk[0] = sq;
-    zk[1] = wrapTo360(__dsub_rn(atan2d(d1, d0), xr[2]));
-    double iq = 1.0 / q;
-    Hs[0][0] = __dmul_rn(iq, __dmul_rn(-sq, d0));
-    Hs[0][1] = __dmul_rn(iq, __dmul_rn(-sq, d1));
-    Hs[0][2] = __dmul_rn(iq, 0.0);
-    Hs[0][3] = __dmul_rn(iq, __dmul_rn(sq, d0));
-    Hs[0][4] = __dmul_rn(iq, __dmul_rn(sq, d1));
-    Hs[1][0] = __dmul_rn(iq, d1);
-    Hs[1][1] = __dmul_rn(iq, -d0);
-    Hs[1][2] = __dmul_rn(iq, -q);
-    Hs[1][3] = __dmul_rn(iq, -d1);
-    Hs[1][4] = __dmul_rn(iq, d0);
+    const MMPrep p = mm_prep(xr, mx, my);
+    zk[0] = p.sq;
+    zk[1] = mm_bearing(p, xr[2]);
+#pragma unroll
+    for (int e = 0; e < 10; ++e) Hs[e / 5][e % 5] = mm_H(p, e);
 }
 
 // phi = (Hs * Pcc) * Hs' + diag(R)   (EKF_SLAM.m:141, left-to-right like MATLAB), 2x2 inverse.
-__device__ __forceinline__ void innovation_cov(const double Hs[2][5], const double Pcc[5][5],
-                                               const double Rd[2], double S[2][2], double Si[2][2]) {
-    double HP[2][5];
+template <typename HT, typename PT>
+__device__ __forceinline__ double ic_HP(const HT& Hs, const PT& Pcc, int r, int b) {    // (Hs * Pcc)(r, b)
+    double acc = __dmul_rn(Hs[r][0], Pcc[0][b]);
 #pragma unroll
-    for (int r = 0; r < 2; ++r)
+    for (int a = 1; a < 5; ++a) acc = __dadd_rn(acc, __dmul_rn(Hs[r][a], Pcc[a][b]));
+    return acc;
+}
+template <typename HPT, typename HT>
+__device__ __forceinline__ double ic_S(const HPT& HP, const HT& Hs, const double Rd[2], int r, int t) {
+    double acc = __dmul_rn(HP[r][0], Hs[t][0]);
 #pragma unroll
-        for (int b = 0; b < 5; ++b) {
-            double acc = __dmul_rn(Hs[r][0], Pcc[0][b]);
-#pragma unroll
-            for (int a = 1; a < 5; ++a) acc = __dadd_rn(acc, __dmul_rn(Hs[r][a], Pcc[a][b]));
-            HP[r][b] = acc;
-        }
-#pragma unroll
-    for (int r = 0; r < 2; ++r)
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            double acc = __dmul_rn(HP[r][0], Hs[t][0]);
-#pragma unroll
-            for (int b = 1; b < 5; ++b) acc = __dadd_rn(acc, __dmul_rn(HP[r][b], Hs[t][b]));
-            S[r][t] = (r == t) ? __dadd_rn(acc, Rd[r]) : acc;
-        }
+    for (int b = 1; b < 5; ++b) acc = __dadd_rn(acc, __dmul_rn(HP[r][b], Hs[t][b]));
+    return (r == t) ? __dadd_rn(acc, Rd[r]) : acc;
+}
+template <typename ST>
+__device__ __forceinline__ void ic_inv(const ST& S, double Si[2][2]) {
     double det = __dsub_rn(__dmul_rn(S[0][0], S[1][1]), __dmul_rn(S[0][1], S[1][0]));
     double id = 1.0 / det;
     Si[0][0] = __dmul_rn(S[1][1], id);
     Si[0][1] = __dmul_rn(-S[0][1], id);
     Si[1][0] = __dmul_rn(-S[1][0], id);
     Si[1][1] = __dmul_rn(S[0][0], id);
+}
+__device__ __forceinline__ void innovation_cov(const double Hs[2][5], const double Pcc[5][5],
+                                               const double Rd[2], double S[2][2], double Si[2][2]) {
+    double HP[2][5];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int b = 0; b < 5; ++b) HP[r][b] = ic_HP(Hs, Pcc, r, b);
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int t = 0; t < 2; ++t) S[r][t] = ic_S(HP, Hs, Rd, r, t);
+    ic_inv(S, Si);
 }
 
 // Gain arithmetic shared by every path (per-observation k_gain, fused k_batch_*, sharded k_gain_shard): explicit FMA

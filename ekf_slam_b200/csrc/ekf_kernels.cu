@@ -137,12 +137,19 @@ __global__ void k_gain(const double* __restrict__ P, int64_t ld, double* __restr
 // times: the results are bit-identical (tests/test_parity_gpu.py::test_fused_batch_is_bit_identical).
 // Sharded filters pass Pc/ldc: the exchanged current columns of the slot set (Pc[slot][i] = P(i, col(slot)), see
 // ekf_shard.cu) replace the gathers from P, and [c_lo, c_hi) names the columns this rank stores.
+// View of the 5 x 5 block P(c,c) of observation q inside the slot block G (row stride EKF_BATCH_SLOTS + 1).
+struct GSel {
+    const double* g; const int* sl;
+    struct Row { const double* g; const int* sl; int a; __device__ double operator[](int b) const { return g[sl[a] * (EKF_BATCH_SLOTS + 1) + sl[b]]; } };
+    __device__ Row operator[](int a) const { return Row{g, sl, a}; }
+};
+
 __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
                             BatchObs ob, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc) {
     __shared__ double G[EKF_BATCH_SLOTS][EKF_BATCH_SLOTS + 1];
     __shared__ double xs[EKF_BATCH_SLOTS];
     __shared__ double2 Ks[EKF_BATCH_SLOTS], Bs[EKF_BATCH_SLOTS];
-    __shared__ double Hs[2][5], Sinv[2][2], nu[2];
+    __shared__ double Hs[2][5], HPs[2][5], Ss[2][2], Sinv[2][2], nu[2];
     __shared__ int col[EKF_BATCH_SLOTS];
     __shared__ int bad;
     const int lane = threadIdx.x;
@@ -159,24 +166,27 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
     for (int q = 0; q < k; ++q) {
         const int sa = 3 + 2 * q;
         const int sl[5] = {0, 1, 2, sa, sa + 1};
-        if (lane == 0) {
-            double xr[3] = {xs[0], xs[1], xs[2]};
-            double zk[2], H[2][5], S[2][2], Si[2][2], Pl[5][5];
-            measurement_model(xr, xs[sa], xs[sa + 1], zk, H);
-            for (int i = 0; i < 5; ++i)
-                for (int j = 0; j < 5; ++j) Pl[i][j] = G[sl[i]][sl[j]];
+        {   // the linearisation, entry-wise across the warp (same pieces, same bits as measurement_model / innovation_cov)
+            const double xr[3] = {xs[0], xs[1], xs[2]};
+            const MMPrep mp = mm_prep(xr, xs[sa], xs[sa + 1]);               // redundantly on every lane
+            if (lane < 10) { const double hv = mm_H(mp, lane); Hs[lane / 5][lane % 5] = hv; out->Hs[q][lane / 5][lane % 5] = hv; }
+            else if (lane == 10) { nu[0] = ob.z0[q] - mp.sq; out->nu[q][0] = nu[0]; }                   // EKF_SLAM.m:144, not wrapped (F10)
+            else if (lane == 11) { nu[1] = ob.z1[q] - mm_bearing(mp, xr[2]); out->nu[q][1] = nu[1]; }
+            __syncwarp();
+            if (lane < 10) HPs[lane / 5][lane % 5] = ic_HP(Hs, GSel{&G[0][0], sl}, lane / 5, lane % 5);
+            __syncwarp();
             const double Rd[2] = {ob.R0[q], ob.R1[q]};
-            innovation_cov(H, Pl, Rd, S, Si);
-            for (int r = 0; r < 2; ++r) {
-                for (int c = 0; c < 5; ++c) { Hs[r][c] = H[r][c]; out->Hs[q][r][c] = H[r][c]; }
-                for (int t = 0; t < 2; ++t) {
-                    Sinv[r][t] = Si[r][t]; out->Sinv[q][r][t] = Si[r][t];
-                    if (!isfinite(S[r][t]) || !isfinite(Si[r][t])) bad = 1;
-                }
+            if (lane < 4) Ss[lane / 2][lane % 2] = ic_S(HPs, Hs, Rd, lane / 2, lane % 2);
+            __syncwarp();
+            if (lane == 0) {
+                double Si[2][2];
+                ic_inv(Ss, Si);
+                for (int r = 0; r < 2; ++r)
+                    for (int t = 0; t < 2; ++t) {
+                        Sinv[r][t] = Si[r][t]; out->Sinv[q][r][t] = Si[r][t];
+                        if (!isfinite(Ss[r][t]) || !isfinite(Si[r][t])) bad = 1;
+                    }
             }
-            nu[0] = ob.z0[q] - zk[0];                               // EKF_SLAM.m:144, not wrapped (F10)
-            nu[1] = ob.z1[q] - zk[1];
-            out->nu[q][0] = nu[0]; out->nu[q][1] = nu[1];
         }
         __syncwarp();
         if (lane < ns) {

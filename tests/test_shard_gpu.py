@@ -15,7 +15,7 @@ def _ngpu():
 
 
 @pytest.mark.parametrize('exchange', ['p2p', 'nccl'])
-@pytest.mark.parametrize('world', [2, 4])
+@pytest.mark.parametrize('world', [2, 4, 8])
 def test_sharded_filter_matches_oracle_and_single_gpu(world, exchange):
     """Both exchange paths: peer-memory scatter over cudaIpc-mapped buffers (default) and NCCL collectives."""
     if _ngpu() < world:
