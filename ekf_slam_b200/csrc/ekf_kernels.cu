@@ -680,14 +680,25 @@ static inline TileMap tm_make(int R, int CT, int TC, int RPC, int col_off, int s
     tm.ystar = (int)(ys < 0 ? 0 : (ys > CT ? CT : ys));
     return tm;
 }
-__device__ __forceinline__ void tm_decode(const TileMap& tm, long long t, int& bx, int& by) {
+// Device-side decode runs once per CTA before anything else can start, so it is 32-bit and division-free (RPC is a
+// template constant: / and % become shifts); launchers guarantee the live-tile count fits 31 bits.
+template <int RPC> __device__ __forceinline__ int tm_G32(int m) {
+    const int q = m / RPC, rem = m % RPC;
+    return RPC * (q * (q - 1) / 2) + q * rem;
+}
+template <int RPC> __device__ __forceinline__ int tm_prefix32(const TileMap& tm, int gA, int Y) {
+    const int y1 = Y < tm.ystar ? Y : tm.ystar;
+    return tm_G32<RPC>(tm.A + y1) - gA + y1 + tm.R * (Y - y1);
+}
+template <int RPC> __device__ __forceinline__ void tm_decode(const TileMap& tm, int t, int& bx, int& by) {
+    const int gA = tm_G32<RPC>(tm.A);
     int lo = 0, hi = tm.CT - 1;                                          // largest by with prefix(by) <= t
     while (lo < hi) {
         const int mid = (lo + hi + 1) >> 1;
-        if (tm_prefix(tm, mid) <= t) lo = mid; else hi = mid - 1;
+        if (tm_prefix32<RPC>(tm, gA, mid) <= t) lo = mid; else hi = mid - 1;
     }
     by = lo;
-    bx = (int)(t - tm_prefix(tm, lo));
+    bx = t - tm_prefix32<RPC>(tm, gA, lo);
 }
 
 template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1>
@@ -725,13 +736,17 @@ __device__ __forceinline__ void dd_tma_tile(double* __restrict__ P, int64_t ld, 
         for (int i = 0; i < NSTAGE; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(done0 + 8 * i, C::CWARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int e = tid; e < TC * 2 * KS; e += C::THREADS) {        // B operand of the whole tile (zero beyond M / ncols)
-        int j = e / (2 * KS), q = e - j * (2 * KS);
-        double2 b = (j < tile_cols && q < M) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
-        Bs[j * C::SROW + 2 * q] = b.x;
-        Bs[j * C::SROW + 2 * q + 1] = b.y;
+    __syncthreads();                                             // barriers visible; nothing has touched memory yet
+
+    if (warp != C::CWARPS) {
+        // consumers stage the B operand of the tile (zero beyond M / ncols) while the producer already streams P
+        for (int e = tid; e < TC * 2 * KS; e += C::CWARPS * 32) {
+            int j = e / (2 * KS), q = e - j * (2 * KS);
+            double2 b = (j < tile_cols && q < M) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
+            Bs[j * C::SROW + 2 * q] = b.x;
+            Bs[j * C::SROW + 2 * q + 1] = b.y;
+        }
     }
-    __syncthreads();
 
     if (warp == C::CWARPS) {
         // ------------------------------------------------ producer: lane c owns column c of every stage
@@ -791,6 +806,7 @@ __device__ __forceinline__ void dd_tma_tile(double* __restrict__ P, int64_t ld, 
         }
     }
     const int row_off = (rw * 16 + 4 * t) * 8;                     // byte offset of this thread's 4 rows in a column
+    asm volatile("bar.sync 1, %0;" :: "n"(C::CWARPS * 32) : "memory");   // B operand staged (consumer warps only)
     for (int s = 0; s < ns; ++s) {
         const int slot = s % NSTAGE;
         mbar_wait(full0 + 8 * slot, (s / NSTAGE) & 1);
@@ -827,7 +843,7 @@ k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
                const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, TileMap tm) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
     int bx, by;
-    tm_decode(tm, (long long)blockIdx.x, bx, by);        // only live tiles are launched (column tile major)
+    tm_decode<C::TR / TC>(tm, (int)blockIdx.x, bx, by);   // only live tiles are launched (column tile major)
     dd_tma_tile<KS, TC, SCOLS, NSTAGE, CG, false>(P, ld, n, ncols, Kall, Ball, lds, M, bx * C::TR, by * TC);
 }
 
@@ -846,7 +862,7 @@ k_mc_flush_tma(McArgs a) {
     tm.ystar = ys > tm.CT ? tm.CT : ys;
     if ((long long)blockIdx.x >= tm_prefix(tm, tm.CT)) return;
     int bx, by;
-    tm_decode(tm, (long long)blockIdx.x, bx, by);
+    tm_decode<C::TR / TC>(tm, (int)blockIdx.x, bx, by);
     double* P = a.P + (int64_t)f * a.pstride;
     const double2* Kg = a.Kg + (int64_t)f * a.maxd * a.ldp;
     const double2* Bg = a.Bg + (int64_t)f * a.maxd * a.ldp;
@@ -890,7 +906,7 @@ static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int nco
     const int R = (n + C::TR - 1) / C::TR, CT = (ncols + TC - 1) / TC;   // row tiles cover the active rows only
     const TileMap tm = tm_make(R, CT, TC, C::TR / TC, col_off, sym);
     const long long live = tm_prefix(tm, CT);
-    if (live <= 0 || live > 0x7fffffffLL) return;
+    if (live <= 0 || live > 0x3fffffffLL) return;        // device decode is 32-bit
     k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, tm);
 }
 

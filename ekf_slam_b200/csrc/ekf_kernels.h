@@ -85,6 +85,7 @@ enum { MC_ERR_TABLE = 1, MC_ERR_CAPACITY = 2, MC_ERR_INDEX = 3 };
 void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem);   // fused (one kernel)
 void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters);                            // split: latency half
 void launch_mc_flush_tma(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);  // split: bandwidth half, TMA-staged DMMA (default)
-void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);      // split: bandwidth half (m_max >= every Mpend[f])
+void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);
+void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);    // split: bandwidth half, warp-per-column-group (default)      // split: bandwidth half (m_max >= every Mpend[f])
 
 }  // namespace ekf

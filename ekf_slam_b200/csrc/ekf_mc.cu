@@ -386,6 +386,110 @@ k_mc_flush(McArgs a, int row_tiles) {
     }
 }
 
+// Third flush variant, "warp streams whole columns": a warp owns 4 adjacent columns of one filter and walks down their
+// rows (lane = row pair, 64 rows per step), so every warp request is a long contiguous run of a column (the
+// microbenchmark tools/tri_stream.cu reaches 6.0 TB/s on exactly this traffic with that mapping, against 4.1 TB/s
+// for the tiled kernels above).  The gains cannot sit in registers then (a lane meets every row), so the K slab of
+// the filter is staged in shared memory once per CTA ([row][q], 2M LDS.128 per row pair, amortised over the 4
+// columns) and B_q of the 4 columns is read as shared-memory broadcasts.
+template <int M, int TC>
+__global__ void __launch_bounds__(256, 4)
+k_mc_flush_w(McArgs a) {
+    extern __shared__ __align__(16) unsigned char fw_dyn[];
+    const int f = blockIdx.y, c0 = blockIdx.x * TC, tid = threadIdx.x;
+    const int n = 3 + 2 * a.N[f], m = min(a.Mpend[f], M);
+    if (m == 0 || c0 >= n) return;
+    const int sym = a.sym;
+    const int64_t ld = a.ldp, lds = a.ldp;
+    double* __restrict__ P = a.P + (int64_t)f * a.pstride;
+    const double2* __restrict__ Kg = a.Kg + (int64_t)f * a.maxd * lds;
+    const double2* __restrict__ Bg = a.Bg + (int64_t)f * a.maxd * lds;
+    const int nc = min(TC, n - c0);
+    const int nrows = sym ? min(n + 1, ((c0 + nc + 1) & ~1)) : n + 1;     // rows this column range can touch (n is odd: row n pads)
+    const int NRH = a.cap + 2;                                             // row pairs per (q, parity) plane
+    double2* Ksh = (double2*)fw_dyn;                                       // [q][row parity][row / 2]: a lane's K_q(r), K_q(r+1) are two conflict-free LDS.128
+    double2* Bsh = Ksh + (size_t)2 * NRH * M;                              // [TC][M]
+    const int warp = tid >> 5, lane = tid & 31;
+    // work list of the warp: (column group g, 64-row step rb), flattened and software-pipelined one item ahead so the
+    // loads of the next item are in flight while this one is computed and stored
+    auto grp_rend = [&](int g) { const int jmax = c0 + min(g + 3, nc - 1); return sym ? min(n, jmax + 1) : n; };
+    auto load = [&](double2 (&v)[4], int g, int rb) {
+        const int r = rb + 2 * lane;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int col = c0 + g + c;
+            if (g + c < nc && (sym ? r <= col : r < n)) v[c] = ld_stream2(P + (int64_t)r + (int64_t)col * ld);
+        }
+    };
+    int g = warp * 4, rb = 0;
+    bool have = g < nc;
+    double2 vn[4];
+    if (have) load(vn, g, rb);                                             // first item's loads overlap the gain staging below
+    for (int e = tid; e < nrows * M; e += 256) {
+        const int q = e / nrows, i = e - q * nrows;
+        Ksh[(q * 2 + (i & 1)) * NRH + (i >> 1)] = q < m ? Kg[q * lds + i] : make_double2(0.0, 0.0);   // row n was written as zero by the front
+    }
+    for (int e = tid; e < nc * M; e += 256) {
+        const int j = e / M, q = e - j * M;
+        Bsh[e] = q < m ? Bg[q * lds + c0 + j] : make_double2(0.0, 0.0);
+    }
+    __syncthreads();
+    while (have) {
+        double2 v[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[c] = vn[c];
+        const int cg = g, r = rb + 2 * lane;
+        rb += 64;
+        if (rb >= grp_rend(g)) { g += 32; rb = 0; }
+        have = g < nc;
+        if (have) load(vn, g, rb);
+        if (r <= min(NRH * 2 - 2, n)) {                                    // lanes past the matrix have nothing to do (and no K rows staged)
+#pragma unroll
+            for (int q = 0; q < M; ++q) {
+                const double2 k0 = Ksh[(q * 2) * NRH + (r >> 1)], k1 = Ksh[(q * 2 + 1) * NRH + (r >> 1)];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const double2 b = Bsh[min(cg + c, nc - 1) * M + q];
+                    v[c].x = rank2_sub(v[c].x, k0, b);
+                    v[c].y = rank2_sub(v[c].y, k1, b);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int col = c0 + cg + c;
+                if (cg + c < nc && (sym ? r <= col : r < n)) st_stream2(P + (int64_t)r + (int64_t)col * ld, v[c]);
+            }
+        }
+    }
+}
+
+template <int M>
+static void launch_mc_flush_w_m(cudaStream_t st, const McArgs& a, int n_filters, int cap_n) {
+    constexpr int TC = 64;
+    const size_t smem = ((size_t)(a.cap + 2) * 2 * M + (size_t)TC * M) * sizeof(double2);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        cudaFuncSetAttribute(k_mc_flush_w<M, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        // no max-shared carve-out here: the LDG stream needs the L1 as its landing buffer (tools/tri_stream.cu: 4.2 -> 5.5 TB/s)
+        smem_set = smem;
+    }
+    dim3 grid((cap_n + TC - 1) / TC, n_filters);
+    k_mc_flush_w<M, TC><<<grid, 256, smem, st>>>(a);
+}
+
+void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max) {
+    switch (m_max) {
+        case 1: launch_mc_flush_w_m<1>(st, a, n_filters, cap_n); break;
+        case 2: launch_mc_flush_w_m<2>(st, a, n_filters, cap_n); break;
+        case 3: launch_mc_flush_w_m<3>(st, a, n_filters, cap_n); break;
+        case 4: launch_mc_flush_w_m<4>(st, a, n_filters, cap_n); break;
+        case 5: launch_mc_flush_w_m<5>(st, a, n_filters, cap_n); break;
+        case 6: launch_mc_flush_w_m<6>(st, a, n_filters, cap_n); break;
+        case 7: launch_mc_flush_w_m<7>(st, a, n_filters, cap_n); break;
+        default: launch_mc_flush_w_m<8>(st, a, n_filters, cap_n); break;
+    }
+}
+
 void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem) {
     static size_t smem_set[2] = {0, 0};
     const int mb = a.assoc_mode == 1 && a.variant != 0;

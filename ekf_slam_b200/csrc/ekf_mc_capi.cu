@@ -22,7 +22,7 @@ struct ekfb_handle {
     int* err = nullptr;
     double2 *Kg = nullptr, *Bg = nullptr;    // split step: gain slabs [nf][maxd][ldp]
     int* Mpend = nullptr;
-    bool flush_ldg = true;                   // register-path flush kernel (measured >= the TMA-staged one on 403-row matrices); EKF_MC_FLUSH=tma selects the latter
+    int flush_kind = 0;                      // 0: warp-per-column-group flush (default); EKF_MC_FLUSH=ldg -> 1 (tiled, gains in registers), =tma -> 2 (TMA-staged DMMA)
     bool split = true;                       // front (latency) + flush (bandwidth) kernels; EKF_MC_FUSED=1 selects the one-kernel step
     double flush_ms = 0.0;
     int* h_err = nullptr;                    // pinned
@@ -91,7 +91,7 @@ extern "C" int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t m
         int maxd = p->defer_m < 1 ? 1 : std::min(p->defer_m, EKF_MAX_DEFER);
         if (!h->split) maxd = std::min(maxd, max_obs);     // fused: slabs cost shared memory; split: global memory
         if (const char* v = getenv("EKF_MC_FUSED")) h->split = atoi(v) == 0;
-        if (const char* v = getenv("EKF_MC_FLUSH")) h->flush_ldg = std::string(v) != "tma";
+        if (const char* v = getenv("EKF_MC_FLUSH")) h->flush_kind = std::string(v) == "ldg" ? 1 : (std::string(v) == "tma" ? 2 : 0);
         int dev_smem = 0;
         CKB(cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
         if (!h->split) {
@@ -214,8 +214,10 @@ extern "C" int32_t ekfb_step(ekfb_handle* h, int32_t mem, const double* u, const
         launch_mc_front(h->stream, a, nf);
         if (h->prof) CKB(cudaEventRecord(*ev(2), h->stream));
         if (do_measure) {
-            if (h->flush_ldg) launch_mc_flush(h->stream, a, nf, h->cap_n, std::min(h->maxd, h->max_obs));
-            else launch_mc_flush_tma(h->stream, a, nf, h->cap_n, std::min(h->maxd, h->max_obs));
+            const int mm = std::min(h->maxd, h->max_obs);
+            if (h->flush_kind == 1) launch_mc_flush(h->stream, a, nf, h->cap_n, mm);
+            else if (h->flush_kind == 2) launch_mc_flush_tma(h->stream, a, nf, h->cap_n, mm);
+            else launch_mc_flush_w(h->stream, a, nf, h->cap_n, mm);
         }
         if (h->prof) CKB(cudaEventRecord(*ev(3), h->stream));
     } else {
