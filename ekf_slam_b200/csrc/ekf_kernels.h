@@ -83,7 +83,7 @@ struct McArgs {
 
 enum { MC_ERR_TABLE = 1, MC_ERR_CAPACITY = 2, MC_ERR_INDEX = 3 };
 void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem);   // fused (one kernel)
-void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters);                            // split: latency half
+void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters, size_t smem_limit, int front_kind);   // split: latency half (run-based k_mc_front, or k_mc_step<.,1> when front_kind = 1 / mode B / the slot cache does not fit)
 void launch_mc_flush_tma(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);  // split: bandwidth half, TMA-staged DMMA (default)
 void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);
 void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);    // split: bandwidth half, warp-per-column-group (default)      // split: bandwidth half (m_max >= every Mpend[f])

@@ -22,6 +22,8 @@ namespace ekf {
 struct McShared {                                // small per-CTA scratch (the slabs follow in dynamic shared memory)
     double Pcc[5][5];
     double Hs[2][5], Sinv[2][2], nu[2];
+    double HP[2][5], S[2][2];
+    double2 Kc[EKF_MAX_DEFER][5], Bc[EKF_MAX_DEFER][5];   // pending gains at the 5 slot rows / columns of the current observation
     double wc[32];
     int wi[32];
     double best; int bidx;
@@ -103,7 +105,10 @@ __device__ __forceinline__ void mc_argmin(double best, int bidx, McShared& sh) {
 //            filters are resident per SM and hide each other's fp64 trig / dependent-chain latency; the pending count
 //            goes to Mpend[f] and the bandwidth-bound pass over every P is left to k_mc_flush at full HBM rate.
 template <int MODE_B, int SPLIT>
-__global__ void __launch_bounds__(SPLIT ? 128 : 256, SPLIT ? (MODE_B ? 2 : 4) : (MODE_B ? 1 : 2))
+#ifndef MC_FRONT_MINB
+#define MC_FRONT_MINB 4
+#endif
+__global__ void __launch_bounds__(SPLIT ? 128 : 256, SPLIT ? (MODE_B ? 2 : MC_FRONT_MINB) : (MODE_B ? 1 : 2))
 k_mc_step(McArgs a) {
     extern __shared__ __align__(16) unsigned char mc_dyn[];
     __shared__ McShared sh;
@@ -273,32 +278,73 @@ k_mc_step(McArgs a) {
         // -------------------------------------------------------- update (EKF_SLAM.m:124-145)
         const int al = 3 + 2 * (idx - 1);
         const int c[5] = {0, 1, 2, al, al + 1};
+        // pending gains of the 5 slot rows / columns, gathered once per observation: every later correction then
+        // costs shared-memory reads instead of a chain of dependent L2 round trips (same terms, same order as mc_cur)
+        if (tid < 10 * m) {
+            const int q = tid / 10, r = tid - 10 * q;
+            if (r < 5) sh.Kc[q][r] = Ks[q * lds + c[r]];
+            else sh.Bc[q][r - 5] = Bs[q * lds + c[r - 5]];
+        }
+        __syncthreads();
         if (tid < 32) {
-            if (tid < 25) sh.Pcc[tid / 5][tid % 5] = mc_cur(P, ld, c[tid / 5], c[tid % 5], sym, Ks, Bs, lds, m);
+            // one warp, one entry per lane (the pieces of ekf_device.cuh give the bits of the one-thread form)
+            if (tid < 25) {
+                int i = tid / 5, j = tid - 5 * (tid / 5);
+                if (sym && i > j) { const int t = i; i = j; j = t; }     // c[] is increasing: stored element is (c[i], c[j]), i <= j
+                double v = P[(int64_t)c[i] + (int64_t)c[j] * ld];
+                for (int q = 0; q < m; ++q) v = rank2_sub(v, sh.Kc[q][i], sh.Bc[q][j]);
+                sh.Pcc[tid / 5][tid - 5 * (tid / 5)] = v;
+            }
+            const double xr[3] = {x[0], x[1], x[2]};
+            const MMPrep mp = mm_prep(xr, x[al], x[al + 1]);             // every lane: cheaper than a broadcast
+            if (tid < 10) sh.Hs[tid / 5][tid % 5] = mm_H(mp, tid);
+            if (tid == 31) {                                             // the atan2d chain runs beside the S chain
+                sh.nu[0] = z0 - mp.sq;                                   // :144, not wrapped (F10)
+                sh.nu[1] = z1 - mm_bearing(mp, xr[2]);
+            }
+            __syncwarp();
+            if (tid < 10) sh.HP[tid / 5][tid % 5] = ic_HP(sh.Hs, sh.Pcc, tid / 5, tid % 5);
+            __syncwarp();
+            const double Rd[2] = {R0, R1};
+            if (tid < 4) sh.S[tid >> 1][tid & 1] = ic_S(sh.HP, sh.Hs, Rd, tid >> 1, tid & 1);
             __syncwarp();
             if (tid == 0) {
-                double xr[3] = {x[0], x[1], x[2]};
-                double zk[2], Hs[2][5], S[2][2], Si[2][2], Pl[5][5];
-                measurement_model(xr, x[al], x[al + 1], zk, Hs);
-                for (int i = 0; i < 5; ++i)
-                    for (int j = 0; j < 5; ++j) Pl[i][j] = sh.Pcc[i][j];
-                const double Rd[2] = {R0, R1};
-                innovation_cov(Hs, Pl, Rd, S, Si);
-                for (int r = 0; r < 2; ++r) {
-                    for (int k = 0; k < 5; ++k) sh.Hs[r][k] = Hs[r][k];
-                    for (int t = 0; t < 2; ++t) sh.Sinv[r][t] = Si[r][t];
-                }
-                sh.nu[0] = z0 - zk[0];                                                   // :144, not wrapped (F10)
-                sh.nu[1] = z1 - zk[1];
+                double Si[2][2];
+                ic_inv(sh.S, Si);
+                sh.Sinv[0][0] = Si[0][0]; sh.Sinv[0][1] = Si[0][1]; sh.Sinv[1][0] = Si[1][0]; sh.Sinv[1][1] = Si[1][1];
             }
         }
         __syncthreads();
         for (int i = tid; i < n; i += T) {
+            // current P(i, c[k]) (and P(c[k], i) in FULL storage): all loads of the row are issued before any is used
+            double pc[5], pr[5];
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                if (sym) pc[k] = i <= c[k] ? P[(int64_t)i + (int64_t)c[k] * ld] : P[(int64_t)c[k] + (int64_t)i * ld];
+                else { pc[k] = P[(int64_t)i + (int64_t)c[k] * ld]; pr[k] = P[(int64_t)c[k] + (int64_t)i * ld]; }
+            }
+            for (int q0 = 0; q0 < m; q0 += 4) {                  // pending terms four at a time: their slab loads overlap too
+                double2 kq[4], bq[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (q0 + u < m) { kq[u] = Ks[(q0 + u) * lds + i]; bq[u] = Bs[(q0 + u) * lds + i]; }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (q0 + u < m) {
+                        const int q = q0 + u;
+#pragma unroll
+                        for (int k = 0; k < 5; ++k) {
+                            if (sym) pc[k] = i <= c[k] ? rank2_sub(pc[k], kq[u], sh.Bc[q][k]) : rank2_sub(pc[k], sh.Kc[q][k], bq[u]);
+                            else { pc[k] = rank2_sub(pc[k], kq[u], sh.Bc[q][k]); pr[k] = rank2_sub(pr[k], sh.Kc[q][k], bq[u]); }
+                        }
+                    }
+                }
+            }
             double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
 #pragma unroll
             for (int k = 0; k < 5; ++k) {
-                ph_acc(ph0, ph1, mc_cur(P, ld, i, c[k], sym, Ks, Bs, lds, m), sh.Hs[0][k], sh.Hs[1][k]);
-                if (!sym) b_acc(b0, b1, mc_cur(P, ld, c[k], i, 0, Ks, Bs, lds, m), sh.Hs[0][k], sh.Hs[1][k]);
+                ph_acc(ph0, ph1, pc[k], sh.Hs[0][k], sh.Hs[1][k]);
+                if (!sym) b_acc(b0, b1, pr[k], sh.Hs[0][k], sh.Hs[1][k]);
             }
             if (sym) { b0 = ph0; b1 = ph1; }
             double k0, k1, dx;
@@ -490,6 +536,336 @@ void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Run-based front half (split step, association mode A).  k_mc_step<.,1> above pays 3-4 dependent memory round trips
+// per observation (signature scan, slot block, gain rows); here nothing on the per-observation chain touches memory:
+//   * the remaining observations are associated together, one warp each (the mode-A cost depends only on s);
+//   * a RUN = the following consecutive updates (up to the free slab depth).  Its 3 + 2 len slot columns of the
+//     stored P -- every column any of its observations reads -- are loaded once into shared memory;
+//   * per observation: warp 0 linearises from that cache, every thread turns its rows of the cache into K, B, dx,
+//     the cache columns later observations need are brought up to date with the same rank2_sub terms, in the same
+//     order, as the lazy mc_cur() evaluation (bit-identical results);
+//   * an append ends the run (flush of the pending terms by this CTA, EKF_SLAM.m:67-98), then association restarts.
+// A run always starts with nothing pending: it ends by an append, by full slabs (inline flush) or with the step.
+template <int SYM, int RPT>   // RPT: rows of the state per thread (n <= 256 RPT)
+__global__ void __launch_bounds__(256, RPT <= 2 ? (SYM ? 3 : 2) : 1)
+k_mc_front(McArgs a) {
+    extern __shared__ __align__(16) unsigned char fr_dyn[];
+    __shared__ McShared sh;
+    __shared__ double2 Kc[EKF_MAX_SLOTS], Bc[EKF_MAX_SLOTS];       // gains of the current observation at the slot rows
+    __shared__ int sc[EKF_MAX_SLOTS];                              // slot -> state index (column of P)
+    const int f = blockIdx.x, tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
+    const int64_t ld = a.ldp, lds = a.ldp;
+    const int NS = 3 + 2 * a.maxd;
+    double* xs = (double*)fr_dyn;                                  // state vector
+    double* pcs = xs + ld;                                         // [NS][ld]: current P(i, sc[k])
+    double* prs = pcs + (int64_t)NS * ld;                          // [NS][ld]: current P(sc[k], i), FULL storage only
+    int* act = (int*)(SYM ? prs : prs + (int64_t)NS * ld);         // [max_obs]: slot (1-based) to update, 0 = append
+    double* __restrict__ P = a.P + (int64_t)f * a.pstride;
+    double* __restrict__ x = a.x + (int64_t)f * a.xstride;
+    double* __restrict__ s = a.s + (int64_t)f * a.sstride;
+    double2* Ks = a.Kg + (int64_t)f * a.maxd * lds;
+    double2* Bs = a.Bg + (int64_t)f * a.maxd * lds;
+    if (tid == 0) { sh.N = a.N[f]; sh.m = 0; sh.fatal = 0; }
+    __syncthreads();
+    {
+        const int n0 = 3 + 2 * sh.N;
+        for (int i = tid; i < n0; i += T) xs[i] = x[i];
+    }
+    const double u1 = a.u[2 * f], u2 = a.u[2 * f + 1];
+    __syncthreads();
+
+    // ------------------------------------------------------------ predict (EKF_SLAM.m:40-51), nothing pending
+    if (a.do_predict) {
+        const int n = 3 + 2 * sh.N;
+        const double th = xs[2];
+        const double st = sind(th), ct = cosd(th);
+        const double fa = -1.0 * u1 * st, fb = u1 * ct;          // F(1,3), F(2,3): heading BEFORE the motion (:63-64)
+        __syncthreads();
+        if (tid == 0) {
+            double M[3][3];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) M[i][j] = ldP(P, ld, i, j, SYM);
+            for (int j = 0; j < 3; ++j) { M[0][j] = M[0][j] + fa * M[2][j]; M[1][j] = M[1][j] + fb * M[2][j]; }
+            for (int i = 0; i < 3; ++i) { M[i][0] = M[i][0] + M[i][2] * fa; M[i][1] = M[i][1] + M[i][2] * fb; }
+            const double W[3] = {u1 * ct, u1 * st, u2};
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) P[i + j * ld] = M[i][j] + (W[i] * a.C) * W[j];
+            xs[0] = xs[0] + u1 * cosd(th + u2);                  // :57-60
+            xs[1] = xs[1] + u1 * sind(th + u2);
+            xs[2] = wrapTo360(th + u2);                          // :50
+        }
+        for (int t = 3 + tid; t < n; t += T) {
+            double* col = P + (int64_t)t * ld;
+            const double p2 = col[2];
+            col[0] = col[0] + fa * p2;
+            col[1] = col[1] + fb * p2;
+            if (!SYM) {
+                const double q2 = P[t + 2 * ld];
+                P[t] = P[t] + q2 * fa;
+                P[t + ld] = P[t + ld] + q2 * fb;
+            }
+        }
+        __syncthreads();
+    }
+    // ------------------------------------------------------------ measure (EKF_SLAM.m:100-151, EKF_SLAM_UC.m:102-152)
+    const int cnt = a.do_measure ? a.counts[f] : 0;
+    const double* ob = a.obs + (int64_t)f * 3 * a.max_obs;
+    const double* loc = a.loc + (int64_t)f * a.loc_stride;
+    const int* tix = a.idx + (int64_t)f * a.idx_stride;
+    const int ntab = a.ntab[f * a.ntab_stride];
+    int ii = 1, mpend = 0;                                       // both uniform over the CTA
+    bool need_assoc = true;
+    while (ii <= cnt) {                                          // :107
+        const int N = sh.N, n = 3 + 2 * N;
+        if (need_assoc) {
+            // ---- associate observations ii..cnt against the current map, one warp each
+            for (int t = ii + warp; t <= cnt; t += NW) {
+                const double z2 = ob[t - 1 + 2 * a.max_obs];
+                int r;
+                if (N == 0) r = 0;                                                   // :110-111 (F15)
+                else if (a.variant == 0 /* EKF_VARIANT_KNOWN */) r = (z2 > (double)N) ? 0 : t;   // :118-123 (F8: idx = ii)
+                else {
+                    double best = CUDART_INF;
+                    int bidx = INT_MAX;
+                    for (int kk = lane; kk < N; kk += 32) {                          // Correspondence.m:49
+                        const double d = __dsub_rn(z2, s[kk]);
+                        const double ll = __dmul_rn(__dmul_rn(d, 1.0 / a.s_cost), d);            // :71, :75
+                        if (ll <= a.s_thresh && ll < best) { best = ll; bidx = kk + 1; }         // :78, :81
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {                               // lexicographic (cost, index) minimum
+                        const double oc = __shfl_xor_sync(0xffffffffu, best, o);
+                        const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
+                        if ((oc < best) || (oc == best && oi < bidx)) { best = oc; bidx = oi; }
+                    }
+                    r = bidx == INT_MAX ? 0 : bidx;                                  // :40: no match -> new landmark
+                }
+                if (lane == 0) act[t - 1] = r;
+            }
+            need_assoc = false;
+            __syncthreads();
+        }
+        // ---- the run: consecutive updates of valid slots, as many as the slabs hold (nothing is pending here)
+        int len = 0;
+        while (ii + len <= cnt && len < a.maxd) {
+            const int r = act[ii + len - 1];
+            if (r < 1 || r > N) break;
+            ++len;
+        }
+        if (len > 0) {
+            const int NSr = 3 + 2 * len;
+            if (tid < NSr) sc[tid] = tid < 3 ? tid : 3 + 2 * (act[ii - 1 + ((tid - 3) >> 1)] - 1) + ((tid - 3) & 1);
+            __syncthreads();
+            constexpr int SB = SYM ? 8 : 4;
+            for (int k0 = 0; k0 < NSr; k0 += SB) {               // slot columns of the stored P, SB RPT loads in flight per thread
+                double v[SB][RPT], w[SYM ? 1 : SB][RPT];
+#pragma unroll
+                for (int q = 0; q < SB; ++q) {
+                    const int c = sc[min(k0 + q, NSr - 1)];
+#pragma unroll
+                    for (int r = 0; r < RPT; ++r) {
+                        const int i = tid + r * T;
+                        if (k0 + q < NSr && i < n) {
+                            if (SYM) v[q][r] = i <= c ? P[(int64_t)i + (int64_t)c * ld] : P[(int64_t)c + (int64_t)i * ld];
+                            else { v[q][r] = P[(int64_t)i + (int64_t)c * ld]; w[SYM ? 0 : q][r] = P[(int64_t)c + (int64_t)i * ld]; }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < SB; ++q) {
+#pragma unroll
+                    for (int r = 0; r < RPT; ++r) {
+                        const int i = tid + r * T;
+                        if (k0 + q < NSr && i < n) {
+                            pcs[(k0 + q) * ld + i] = v[q][r];
+                            if (!SYM) prs[(k0 + q) * ld + i] = w[SYM ? 0 : q][r];
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+            for (int t = 0; t < len; ++t) {
+                const int o = ii + t, m = t;                     // observation ordinal; its slab index
+                const double z0 = ob[o - 1], z1 = ob[o - 1 + a.max_obs];
+                const double R0 = z0 * a.Rc0, R1 = z1 * a.Rc1;   // :108
+                const int ks[5] = {0, 1, 2, 3 + 2 * t, 4 + 2 * t};
+                const int al = sc[3 + 2 * t];
+                if (tid < 32) {                                  // linearise: one entry per lane, bits of the one-thread form
+                    if (tid < 25) {
+                        const int pi = tid / 5, pj = tid - 5 * pi;
+                        const int si = pi < 3 ? pi : 2 * t + pi, sj = pj < 3 ? pj : 2 * t + pj;   // slots {0, 1, 2, 3 + 2t, 4 + 2t}
+                        sh.Pcc[pi][pj] = pcs[sj * ld + sc[si]];
+                    }
+                    const double xr[3] = {xs[0], xs[1], xs[2]};
+                    const MMPrep mp = mm_prep(xr, xs[al], xs[al + 1]);
+                    if (tid < 10) sh.Hs[tid / 5][tid % 5] = mm_H(mp, tid);
+                    if (tid == 31) {
+                        sh.nu[0] = z0 - mp.sq;                   // :144, not wrapped (F10)
+                        sh.nu[1] = z1 - mm_bearing(mp, xr[2]);
+                    }
+                    __syncwarp();
+                    if (tid < 10) sh.HP[tid / 5][tid % 5] = ic_HP(sh.Hs, sh.Pcc, tid / 5, tid % 5);
+                    __syncwarp();
+                    const double Rd[2] = {R0, R1};
+                    if (tid < 4) sh.S[tid >> 1][tid & 1] = ic_S(sh.HP, sh.Hs, Rd, tid >> 1, tid & 1);
+                    __syncwarp();
+                    if (tid == 0) {
+                        double Si[2][2];
+                        ic_inv(sh.S, Si);
+                        sh.Sinv[0][0] = Si[0][0]; sh.Sinv[0][1] = Si[0][1]; sh.Sinv[1][0] = Si[1][0]; sh.Sinv[1][1] = Si[1][1];
+                        if (a.actions) a.actions[(int64_t)f * a.max_obs + o - 1] = act[o - 1];
+                    }
+                }
+                __syncthreads();
+                double2 kown[RPT], bown[RPT];
+#pragma unroll
+                for (int r = 0; r < RPT; ++r) {
+                    const int i = tid + r * T;
+                    if (i < n) {
+                        double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+                        for (int k = 0; k < 5; ++k) {
+                            ph_acc(ph0, ph1, pcs[ks[k] * ld + i], sh.Hs[0][k], sh.Hs[1][k]);
+                            if (!SYM) b_acc(b0, b1, prs[ks[k] * ld + i], sh.Hs[0][k], sh.Hs[1][k]);
+                        }
+                        if (SYM) { b0 = ph0; b1 = ph1; }
+                        double k0, k1, dx;
+                        gain_from_ph(ph0, ph1, sh.Sinv, sh.nu, k0, k1, dx);              // :143
+                        xs[i] = __dadd_rn(xs[i], dx);                                    // :144
+                        kown[r] = make_double2(k0, k1);
+                        bown[r] = make_double2(b0, b1);
+                        Ks[m * lds + i] = kown[r];
+                        Bs[m * lds + i] = bown[r];
+                        if (t + 1 < len)
+                            for (int k = 0; k < NSr; ++k)
+                                if (sc[k] == i) { Kc[k] = kown[r]; Bc[k] = bown[r]; }
+                    }
+                }
+                if (tid == 0) {                                  // n is odd: row n pads the last row pair of the flush
+                    Ks[m * lds + n] = make_double2(0.0, 0.0);
+                    Bs[m * lds + n] = make_double2(0.0, 0.0);
+                }
+                __syncthreads();
+                if (t + 1 < len) {                               // columns the later observations of the run read: same terms as mc_cur
+#pragma unroll
+                    for (int r = 0; r < RPT; ++r) {
+                        const int i = tid + r * T;
+                        if (i < n) {
+#pragma unroll 4
+                            for (int kk = 0; kk < NSr - 2 - 2 * t; ++kk) {
+                                const int k = kk < 3 ? kk : kk + 2 + 2 * t;      // robot slots, then the slots of observations > t
+                                const int c = sc[k];
+                                if (SYM) pcs[k * ld + i] = i <= c ? rank2_sub(pcs[k * ld + i], kown[r], Bc[k]) : rank2_sub(pcs[k * ld + i], Kc[k], bown[r]);
+                                else {
+                                    pcs[k * ld + i] = rank2_sub(pcs[k * ld + i], kown[r], Bc[k]);
+                                    prs[k * ld + i] = rank2_sub(prs[k * ld + i], Kc[k], bown[r]);
+                                }
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+            ii += len;
+            mpend = len;
+            if (len >= a.maxd && ii <= cnt) {                    // slabs full and the step goes on: this CTA streams its P
+                mc_flush(P, ld, n, SYM, Ks, Bs, lds, mpend);
+                __syncthreads();
+                mpend = 0;
+            }
+            if (ii > cnt) break;
+            const int rn = act[ii - 1];
+            if (rn >= 1 && rn <= N) continue;                    // the run was cut by the slab depth only
+        }
+        // ---- observation ii is an append (or names a slot that does not exist)
+        const int r = act[ii - 1];
+        const double z0 = ob[ii - 1], z1 = ob[ii - 1 + a.max_obs], z2 = ob[ii - 1 + 2 * a.max_obs];
+        const double R0 = z0 * a.Rc0, R1 = z1 * a.Rc1;
+        double want = 0.0, sig = 0.0;
+        int lookup = 2;                                          // 1: first non-zero index, 2: index == want
+        if (N == 0) { sig = 1.0; lookup = 1; }                   // :110-111 (F15)
+        else if (a.variant == 0) { sig = z2; want = z2; }        // :118-120
+        else { sig = (double)(N + 1); want = sig; }              // :121-123
+        if (tid == 0) {
+            int fatal = 0;
+            if (r > 0) fatal = MC_ERR_INDEX;
+            else {
+                int hit = -1;
+                for (int i = 0; i < ntab && hit < 0; ++i)
+                    if (lookup == 1 ? (tix[i] != 0) : ((double)tix[i] == want)) hit = i;
+                if (hit < 0) fatal = MC_ERR_TABLE;
+                else { sh.pos[0] = loc[hit]; sh.pos[1] = loc[hit + a.max_table]; }
+                if (N >= a.cap) fatal = MC_ERR_CAPACITY;
+            }
+            sh.fatal = fatal;
+        }
+        __syncthreads();
+        if (sh.fatal) break;
+        if (a.actions && tid == 0) a.actions[(int64_t)f * a.max_obs + ii - 1] = -(int)sig;
+        // ---------------------------------------------------- append (EKF_SLAM.m:67-98), needs the whole P
+        mc_flush(P, ld, n, SYM, Ks, Bs, lds, mpend);
+        mpend = 0;
+        __syncthreads();
+        {
+            const double th = xs[2];
+            const double j02 = -u1 * sind(th), j12 = u1 * cosd(th);          // jxr, :84-85
+            for (int t = tid; t <= N; t += T) {
+                if (t < N) {
+                    const int al = 3 + 2 * t;
+                    for (int mm = 0; mm < 2; ++mm) {
+                        const double p0 = ldP(P, ld, al + mm, 0, SYM), p1 = ldP(P, ld, al + mm, 1, SYM), p2 = ldP(P, ld, al + mm, 2, SYM);
+                        const double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;    // jxr * P(lm,1:3)', :95
+                        const double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+                        P[(int64_t)(al + mm) + (int64_t)n * ld] = f0;
+                        P[(int64_t)(al + mm) + (int64_t)(n + 1) * ld] = f1;
+                        P[(int64_t)n + (int64_t)(al + mm) * ld] = f0;
+                        P[(int64_t)(n + 1) + (int64_t)(al + mm) * ld] = f1;
+                    }
+                } else {
+                    double Prr[3][3];
+                    for (int i = 0; i < 3; ++i)
+                        for (int j = 0; j < 3; ++j) Prr[i][j] = ldP(P, ld, i, j, SYM);
+                    const double jxr[2][3] = {{1.0, 0.0, j02}, {0.0, 1.0, j12}};
+                    const double cu = cosd(u2), su = sind(u2);
+                    const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};             // :87-88
+                    double JP[2][3];
+                    for (int rr = 0; rr < 2; ++rr)
+                        for (int j = 0; j < 3; ++j) JP[rr][j] = jxr[rr][0] * Prr[0][j] + jxr[rr][1] * Prr[1][j] + jxr[rr][2] * Prr[2][j];
+                    const double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+                    for (int rr = 0; rr < 2; ++rr)
+                        for (int c = 0; c < 2; ++c)
+                            P[(int64_t)(n + rr) + (int64_t)(n + c) * ld] =
+                                (JP[rr][0] * jxr[c][0] + JP[rr][1] * jxr[c][1] + JP[rr][2] * jxr[c][2]) +
+                                (JR[rr][0] * jz[c][0] + JR[rr][1] * jz[c][1]);           // :91
+                    for (int i = 0; i < 3; ++i)
+                        for (int c = 0; c < 2; ++c) {
+                            const double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];   // :92
+                            P[(int64_t)i + (int64_t)(n + c) * ld] = v;
+                            P[(int64_t)(n + c) + (int64_t)i * ld] = v;                   // :93
+                        }
+                    xs[n] = sh.pos[0]; xs[n + 1] = sh.pos[1];                            // :79
+                    s[N] = sig;                                                          // :70
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) sh.N = N + 1;
+        __syncthreads();
+        ++ii;
+        need_assoc = true;
+    }
+    {
+        const int n1 = 3 + 2 * sh.N;
+        for (int i = tid; i < n1; i += T) x[i] = xs[i];
+    }
+    if (tid == 0) {
+        a.Mpend[f] = mpend;                              // k_mc_flush applies them
+        a.N[f] = sh.N;
+        if (sh.fatal && atomicCAS(a.err, 0, sh.fatal) == 0) a.err[1] = f;
+    }
+}
+
 void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem) {
     static size_t smem_set[2] = {0, 0};
     const int mb = a.assoc_mode == 1 && a.variant != 0;
@@ -502,8 +878,34 @@ void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads
     else k_mc_step<0, 0><<<n_filters, threads, smem, st>>>(a);
 }
 
-void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters) {
+template <int SYM, int RPT>
+static void launch_mc_front_t(cudaStream_t st, const McArgs& a, int n_filters, size_t smem) {
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        cudaFuncSetAttribute(k_mc_front<SYM, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        smem_set = smem;
+    }
+    k_mc_front<SYM, RPT><<<n_filters, 256, smem, st>>>(a);
+}
+
+// smem_limit: the device's opt-in shared memory per block; front_kind 0 = run-based kernel when it applies, 1 = k_mc_step<.,1>
+void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters, size_t smem_limit, int front_kind) {
     const int mb = a.assoc_mode == 1 && a.variant != 0;
+    const int n_cap = 3 + 2 * a.cap, NS = 3 + 2 * a.maxd;
+    const size_t smem = sizeof(double) * (size_t)a.ldp * (1 + (a.sym ? 1 : 2) * NS) + sizeof(int) * (size_t)((a.max_obs + 3) & ~3);
+    if (front_kind == 0 && !mb && n_cap <= 2048 && smem + 4096 <= smem_limit) {
+        const int rpt = (n_cap + 255) / 256;
+        if (a.sym) {
+            if (rpt <= 2) launch_mc_front_t<1, 2>(st, a, n_filters, smem);
+            else if (rpt <= 4) launch_mc_front_t<1, 4>(st, a, n_filters, smem);
+            else launch_mc_front_t<1, 8>(st, a, n_filters, smem);
+        } else {
+            if (rpt <= 2) launch_mc_front_t<0, 2>(st, a, n_filters, smem);
+            else if (rpt <= 4) launch_mc_front_t<0, 4>(st, a, n_filters, smem);
+            else launch_mc_front_t<0, 8>(st, a, n_filters, smem);
+        }
+        return;
+    }
     if (mb) k_mc_step<1, 1><<<n_filters, 128, 0, st>>>(a);
     else k_mc_step<0, 1><<<n_filters, 128, 0, st>>>(a);
 }

@@ -22,6 +22,8 @@ struct ekfb_handle {
     int* err = nullptr;
     double2 *Kg = nullptr, *Bg = nullptr;    // split step: gain slabs [nf][maxd][ldp]
     int* Mpend = nullptr;
+    int dev_smem = 0;                        // opt-in shared memory per block of the device
+    int front_kind = 1;                      // 1: k_mc_step<.,1>, one observation at a time (default, measured faster); EKF_MC_FRONT=run -> 0 (run-based k_mc_front)
     int flush_kind = 0;                      // 0: warp-per-column-group flush (default); EKF_MC_FLUSH=ldg -> 1 (tiled, gains in registers), =tma -> 2 (TMA-staged DMMA)
     bool split = true;                       // front (latency) + flush (bandwidth) kernels; EKF_MC_FUSED=1 selects the one-kernel step
     double flush_ms = 0.0;
@@ -92,8 +94,10 @@ extern "C" int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t m
         if (!h->split) maxd = std::min(maxd, max_obs);     // fused: slabs cost shared memory; split: global memory
         if (const char* v = getenv("EKF_MC_FUSED")) h->split = atoi(v) == 0;
         if (const char* v = getenv("EKF_MC_FLUSH")) h->flush_kind = std::string(v) == "ldg" ? 1 : (std::string(v) == "tma" ? 2 : 0);
+        if (const char* v = getenv("EKF_MC_FRONT")) h->front_kind = std::string(v) == "run" ? 0 : 1;
         int dev_smem = 0;
         CKB(cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
+        h->dev_smem = dev_smem;
         if (!h->split) {
             while (maxd > 1 && (size_t)2 * maxd * h->ldp * 16 + 4096 > (size_t)dev_smem) --maxd;
             if ((size_t)2 * maxd * h->ldp * 16 + 4096 > (size_t)dev_smem)
@@ -200,25 +204,27 @@ extern "C" int32_t ekfb_step(ekfb_handle* h, int32_t mem, const double* u, const
     a.do_predict = do_predict; a.do_measure = do_measure; a.maxd = h->maxd;
     if (actions_out) CKB(cudaMemsetAsync(h->d_act, 0, sizeof(int) * h->max_obs * nf, h->stream));
     a.Kg = h->Kg; a.Bg = h->Bg; a.Mpend = h->Mpend;
+    const size_t epp = 2;                                // event pairs per step: whole step, flush launch
     auto ev = [&](size_t i) -> cudaEvent_t* {            // event i of this step (0,1: whole step; 2,3: flush kernel)
-        while (h->evs.size() < 2 * (h->ev_used + 1)) {
+        while (h->evs.size() < epp * (h->ev_used + 1)) {
             cudaEvent_t a0 = nullptr, a1 = nullptr;
             cudaEventCreate(&a0); cudaEventCreate(&a1);
             h->evs.push_back({a0, a1});
         }
-        auto& pr = h->evs[2 * h->ev_used + i / 2];
+        auto& pr = h->evs[epp * h->ev_used + i / 2];
         return (i & 1) ? &pr.second : &pr.first;
+    };
+    auto flush = [&](cudaStream_t st, const McArgs& s, int cnt_f) {
+        const int mm = std::min(h->maxd, h->max_obs);
+        if (h->flush_kind == 1) launch_mc_flush(st, s, cnt_f, h->cap_n, mm);
+        else if (h->flush_kind == 2) launch_mc_flush_tma(st, s, cnt_f, h->cap_n, mm);
+        else launch_mc_flush_w(st, s, cnt_f, h->cap_n, mm);
     };
     if (h->prof) CKB(cudaEventRecord(*ev(0), h->stream));
     if (h->split) {
-        launch_mc_front(h->stream, a, nf);
+        launch_mc_front(h->stream, a, nf, (size_t)h->dev_smem, h->front_kind);
         if (h->prof) CKB(cudaEventRecord(*ev(2), h->stream));
-        if (do_measure) {
-            const int mm = std::min(h->maxd, h->max_obs);
-            if (h->flush_kind == 1) launch_mc_flush(h->stream, a, nf, h->cap_n, mm);
-            else if (h->flush_kind == 2) launch_mc_flush_tma(h->stream, a, nf, h->cap_n, mm);
-            else launch_mc_flush_w(h->stream, a, nf, h->cap_n, mm);
-        }
+        if (do_measure) flush(h->stream, a, nf);
         if (h->prof) CKB(cudaEventRecord(*ev(3), h->stream));
     } else {
         launch_mc_step(h->stream, a, nf, 256, h->smem);
@@ -238,12 +244,15 @@ extern "C" int32_t ekfb_profile(ekfb_handle* h, int32_t enable, double* step_ms_
                                 double* flush_ms_total) {
     if (!h) return EKF_EINVAL;
     CKB(cudaStreamSynchronize(h->stream));
+    const size_t epp = 2;
     for (size_t i = 0; i < h->ev_used; ++i) {
         float ms = 0.f;
-        CKB(cudaEventElapsedTime(&ms, h->evs[2 * i].first, h->evs[2 * i].second));
+        CKB(cudaEventElapsedTime(&ms, h->evs[epp * i].first, h->evs[epp * i].second));
         h->step_ms += ms;
-        CKB(cudaEventElapsedTime(&ms, h->evs[2 * i + 1].first, h->evs[2 * i + 1].second));
-        h->flush_ms += ms;
+        for (size_t c = 1; c < epp; ++c) {
+            CKB(cudaEventElapsedTime(&ms, h->evs[epp * i + c].first, h->evs[epp * i + c].second));
+            h->flush_ms += ms;
+        }
     }
     h->ev_used = 0;
     if (step_ms_total) *step_ms_total = h->step_ms;

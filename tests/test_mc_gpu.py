@@ -52,14 +52,16 @@ def test_batch_matches_oracle_per_filter(storage, cls, defer_m, assoc):
     b.close()
 
 
-@pytest.mark.parametrize('impl', ['split-warp', 'split-tma', 'split-ldg', 'fused'])
+@pytest.mark.parametrize('impl', ['split-warp', 'split-tma', 'split-ldg', 'split-run', 'fused'])
 @pytest.mark.parametrize('storage', ['sym', 'full'])
 def test_batch_equals_single_filter_path_bitwise(storage, impl, monkeypatch):
-    """All step implementations: split front + TMA-staged flush (default), split + register-path flush
-    (EKF_MC_FLUSH=ldg) and the one-kernel step (EKF_MC_FUSED=1)."""
+    """All step implementations: split front + warp-per-column-group flush (default), the TMA-staged and the tiled
+    register-path flush (EKF_MC_FLUSH=tma|ldg), the run-based front (EKF_MC_FRONT=run) and the one-kernel step
+    (EKF_MC_FUSED=1)."""
     import ekf_slam_b200 as E
     monkeypatch.setenv('EKF_MC_FUSED', '1' if impl == 'fused' else '0')
     monkeypatch.setenv('EKF_MC_FLUSH', {'split-ldg': 'ldg', 'split-tma': 'tma'}.get(impl, 'warp'))
+    monkeypatch.setenv('EKF_MC_FRONT', 'run' if impl == 'split-run' else 'step')
     nf, N, T, k = 6, 12, 60, 4
     ws = _worlds(nf, 'EKF_SLAM_UC', N, T, k)
     b = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=N, max_obs=k, max_table=N, storage=storage, defer_m=4)
