@@ -173,7 +173,25 @@ def cpu_baseline(N, k, x, A, d, us, obs, budget_s):
     t_upd, _, _ = cb.sampled_update_seconds(x, P, r[:2], [r[0] * 0.1, r[1] * 5.0], int(r[2]), m)
     t_step = t_pred + k * t_upd
     cores = os.cpu_count()
-    return {'value': k / t_step, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+    # second CPU number, for scale only: the same O(n^2) structured algebra the GPU runs, in C on the host threads
+    # (oracle/structured.c).  It is NOT the reference's algorithm, so it is reported beside the baseline, not as it.
+    structured = None
+    try:
+        from oracle import structured as S
+        so = S.EKF_SLAM_UC(capacity_landmarks=N)
+        so.set_state(x, P, np.arange(1, N + 1, dtype=np.float64))
+        del P
+        so.predict(us[0]); so.update(r[:2], [r[0] * 0.1, r[1] * 5.0], int(r[2]))            # warm the pages
+        t0 = time.perf_counter()
+        so.predict(us[1 % len(us)])
+        for q in range(k):
+            rq = obs[1 % len(obs)][q]
+            so.update(rq[:2], [rq[0] * 0.1, rq[1] * 5.0], int(rq[2]))
+        structured = {'value': k / (time.perf_counter() - t0), 'unit': UNIT, 'cores': min(16, cores),
+                      'what': 'oracle/structured.c (5-column O(n^2) form, pthreads): 1 predict + %d updates in full' % k}
+    except Exception as e:                      # test infrastructure missing a compiler must not break the bench line
+        structured = {'unavailable': str(e)[:120]}
+    return {'value': k / t_step, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'structured_port': structured,
             'sample': 'dense reference algebra (EKF_SLAM.m:47,141-145) at n=%d via NumPy/OpenBLAS: 1 predict + 1 update, '
                       'n^3 products on the first %d of %d output rows scaled by n/m (O(n^2) parts in full); '
                       'step = predict + %d updates; gemm %.0f GFLOP/s' % (n, m, n, k, rate / 1e9),

@@ -232,3 +232,78 @@ def test_ellipse_params_known_answers():
     a = O.ellipse_params(x, P2)[1, 4]
     lam, vec = np.linalg.eigh(P2[3:5, 3:5])
     assert abs(np.tan(a) - vec[1, 1] / vec[0, 1]) < 1e-12
+
+
+# ---------------------------------------------------------------- structured C oracle (oracle/structured.c)
+@pytest.mark.parametrize('name', list(G.CASES))
+def test_structured_oracle_matches_golden(name):
+    """The O(n^2) C oracle against the committed fixtures (made by the dense oracle): identical actions and
+    signatures, x at every checkpoint and final x, P within 1e-12 (different grouping of the same products)."""
+    from oracle import structured as S
+    g = G.load(name)
+    o = getattr(S, G.CASES[name])(capacity_landmarks=24)
+    errs = []
+
+    def cp(i, f):
+        xg = g['x_checkpoints'][i]
+        errs.append(G.rel(f.x, xg[~np.isnan(xg)]))
+
+    acts = G.replay(o, g, cp)
+    assert np.array_equal(acts, g['actions'])
+    assert len(errs) == len(g['checkpoint_steps']) and max(errs) <= 1e-12, errs
+    assert G.rel(o.x, g['x_final']) <= 1e-12 and G.rel(o.P, g['P_final']) <= 1e-12
+    assert np.array_equal(o.s, g['s_final'])
+
+
+def test_structured_oracle_association_cases():
+    from oracle import structured as S
+    g = G.load('association_N12')
+    N = len(g['s'])
+    for q in range(len(g['z'])):
+        a = S.EKF_SLAM_UC(capacity_landmarks=N)
+        a.set_state(g['x'], g['P'], g['s'])
+        new, idx = a.associate(g['z'][q], g['Rdiag'][q])
+        assert [int(new), idx] == list(g['modeA'][q])
+        b = S.EKF_SLAM_UC(capacity_landmarks=N, assoc_mode=1)
+        b.set_state(g['x'], g['P'], np.ones(N))
+        b.s_thresh = 9.21
+        zB = g['z'][q].copy(); zB[2] = 1.0
+        new, idx = b.associate(zB, g['Rdiag'][q])
+        assert [int(new), idx] == list(g['modeB'][q])
+
+
+def test_structured_helpers_equal_numpy_restatement():
+    """The C helpers and oracle/matlab_compat.py state the same MathWorks semantics: equal to the last bit (atan2d: to
+    one ulp, glibc vs NumPy) on a grid that includes the exact cases (multiples of 90, +-360, 0)."""
+    from oracle import structured as S
+    L = S.lib()
+    xs = np.concatenate([np.arange(-720.0, 721.0, 15.0), np.random.default_rng(3).uniform(-1e4, 1e4, 500)])
+    for v in xs:
+        assert L.so_sind(v) == M.sind(v) and L.so_cosd(v) == M.cosd(v), v
+        assert L.so_wrapTo360(v) == M.wrapTo360(v), v
+    for y, x in np.random.default_rng(4).normal(size=(200, 2)):
+        assert abs(L.so_atan2d(y, x) - M.atan2d(y, x)) <= 2 * np.spacing(abs(M.atan2d(y, x)))   # libm vs NumPy atan2: last ulp of the radian value
+    assert L.so_wrapTo360(360.0) == 360.0 and L.so_wrapTo360(0.0) == 0.0 and L.so_wrapTo360(-90.0) == 270.0
+
+
+def test_structured_oracle_200_landmarks_vs_dense():
+    """A longer map (N = 200 fills through append, 120 steps): the two oracles stay within 1e-12."""
+    from oracle import structured as S
+    from ekf_slam_b200.synth import make_world
+    w = make_world(N=60, T=120, k=5, mode='nearest')
+    a, b = S.EKF_SLAM_UC(capacity_landmarks=64), O.EKF_SLAM_UC()
+    for t in range(w.T):
+        a.predict(w.u[t]); a.measure(None, w.u[t], w.stub(t))
+        b.predict(w.u[t]); b.measure(None, w.u[t], w.stub(t))
+    assert a.chosen == b.chosen and a.N == (len(b.x) - 3) // 2
+    assert G.rel(a.x, b.x) <= 1e-12 and G.rel(a.P, b.P) <= 1e-12
+
+
+def test_structured_oracle_errors():
+    from oracle import structured as S
+    a = S.EKF_SLAM(capacity_landmarks=1)
+    with pytest.raises(IndexError):
+        a.update([1.0, 2.0], [0.1, 0.1], 1)                 # no landmark yet
+    a.append([1.0, 0.0], [0.1, 0.1], [3.0, 4.0], 1)
+    with pytest.raises(MemoryError):
+        a.append([1.0, 0.0], [0.1, 0.1], [5.0, 6.0], 2)     # capacity

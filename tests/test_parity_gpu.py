@@ -387,3 +387,43 @@ def test_covariance_ellipses_match_reference_plot_math(storage):
     assert e0.shape == (1, 5) and abs(e0[0, 4] - np.pi / 2) < 1e-15
     assert np.allclose(e0[0, 2:4], 0.25 * 2 * np.sqrt(2.2788 * 0.1))
     f.close(); g.close()
+
+
+# ---------------------------------------------------------------- BASELINE's full size: 10 000 landmarks vs the structured C oracle
+def _blocked_rel(Pg, Po, step=1024):
+    """Relative Frobenius error of two 3.2 GB matrices without a third one."""
+    num = den = 0.0
+    for j in range(0, Po.shape[1], step):
+        a, b = Pg[:, j:j + step], Po[:, j:j + step]
+        num += float(np.sum((a - b) ** 2)); den += float(np.sum(b * b))
+    return (num / den) ** 0.5
+
+
+@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 1)])
+def test_config3_10k_landmarks_vs_structured_oracle(storage, defer_m):
+    """BASELINE config 3 at full size (N = 10 000, n = 20 003, P 3.2 GB): the populated synthetic map of the bench,
+    2 steps of predict + 8 associated updates through the class API (EKF_SLAM_UC.measure: batched association, fused
+    deferred update), against oracle/structured.c stepping the same P on the host.  Association actions identical;
+    x and P within 1e-9 relative (Frobenius)."""
+    import ekf_slam_b200 as E
+    from oracle import structured as S
+    from bench import make_inputs
+    from tests.golden_util import Stub
+    from types import SimpleNamespace
+    N, k, T = 10000, 8, 2
+    x, A, d, s, lms, us, obs = make_inputs(N, k, T)
+    g = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, defer_m=defer_m)
+    g.set_state_lowrank(x, s, A, d)
+    o = S.EKF_SLAM_UC(capacity_landmarks=N)
+    o.set_state(x, g.P, s)                       # the oracle starts from the very bits the device built
+    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
+    for t in range(T):
+        stub = Stub(obs[t], table)
+        g.predict(us[t]); g.measure(None, us[t], stub)
+        o.predict(us[t]); o.measure(None, us[t], stub)
+    assert g.chosen == o.chosen and len(g.chosen) == T * k and all(a == 'update' for a, _ in g.chosen)
+    ex = np.linalg.norm(g.x - o.x) / np.linalg.norm(o.x)
+    eP = _blocked_rel(g.P, o._P)
+    print('10k %s/defer %d vs structured oracle: rel err x %.2e P %.2e' % (storage, defer_m, ex, eP))
+    assert ex <= 1e-9 and eP <= 1e-9
+    g.close()
