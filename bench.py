@@ -371,7 +371,10 @@ def main():
                    'l2': 'no flush needed: each update streams %.2f GB of P, far beyond the 126 MB L2' % (dd_bytes / 2e9)},
         'roofline': {'bound': 'hbm', 'kernel': 'k_downdate_tma (rank-%d flush: cp.async.bulk staging + FP64 DMMA)' % (2 * min(max(args.defer, 1), k)), 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
-                     'frac_of_8TBps_nominal': achieved / 8000.0, 'traffic': None,
+                     'frac_of_8TBps_nominal': achieved / 8000.0,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
+                     # of exactly this configuration (profiles/ncu_downdate_r01_tma_rank16_raw.csv); null for any other
+                     'traffic': 3.175e9 if (N == 10000 and args.storage == 'sym' and args.defer == 8 and k == 8 and world == 1) else None,
                      'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,
                      'share_of_step': dd_ms / ms},
         'exchange': ({'avg_ms': xch_ms / max(xch_n, 1), 'per_step': xch_n / K, 'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if xch_p2p else 'NCCL'} if world > 1 else None),
@@ -535,10 +538,13 @@ def run_mc(args):
                                % (args.filters, N, n, k), 'filters': args.filters, 'landmarks': N, 'k': k, 'storage': args.storage,
                    'defer_m': args.defer, 'parallelism': 'filter f on rank f mod %d, no communication (replicas only)' % world,
                    'l2': 'no flush needed: each step streams %.2f GB of covariances per GPU, far beyond the 126 MB L2' % (dd_bytes / 1e9)},
-        'roofline': {'bound': 'hbm', 'kernel': 'k_mc_flush (one deferred rank-%d pass over every filter\'s P; k_mc_front does predict + %d associate/linearise/gain per filter before it)' % (2 * min(k, args.defer), k),
+        'roofline': {'bound': 'hbm', 'kernel': 'k_mc_flush_w (one deferred rank-%d pass over every filter\'s P; k_mc_front does predict + %d associate/linearise/gain per filter before it)' % (2 * min(k, args.defer), k),
                      'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
-                     'frac_of_8TBps_nominal': achieved / 8000.0, 'traffic': None, 'algorithmic_bytes_per_launch': dd_bytes,
+                     'frac_of_8TBps_nominal': achieved / 8000.0,
+                     # from profiles/ncu_mcflush_r01_raw.csv (this configuration only): 3.044 GB read + 2.643 GB written
+                     'traffic': 5.687e9 if (N == 200 and k == 5 and args.filters == 4096 and args.storage == 'sym' and world == 1) else None,
+                     'algorithmic_bytes_per_launch': dd_bytes,
                      'avg_launch_ms': flush_avg_ms, 'launches': kern_n, 'share_of_step': flush_avg_ms * K / ms,
                      'front_kernel_avg_ms': kern_avg_ms - flush_avg_ms},
         'e2e': {'value': K * k * nf_total / (e2e_ms * 1e-3), 'unit': UNIT,
