@@ -33,6 +33,46 @@ def main():
         j = c_lo + np.arange(slab.shape[1])[None, :]
         return i <= j
 
+    if os.environ.get('SHARD_CASE') == '80k':
+        # BASELINE config 4: 80 000 landmarks (n = 160 003, P 205 GB dense) in SYM column slabs; x and sampled rows
+        # of P against the matrix-free oracle; 1e-9 relative
+        from bench import make_inputs
+        from oracle.lowrank_lazy import LazyLowRankFilter
+        N, k, T = int(os.environ.get('SHARD_LANDMARKS', '80000')), 8, 2
+        x, A, d, s, lms, us, obs = make_inputs(N, k, T)
+        g = E.shard.create_sharded(E.EKF_SLAM_UC, dist, local, storage='sym', capacity_landmarks=N, defer_m=8)
+        g.set_state_lowrank(x, s, A, d)
+        o = LazyLowRankFilter(x, A, d, s, Rc=g.Rc)
+        for t in range(T):
+            g.predict(us[t]); o.predict(us[t])
+            rows = obs[t]
+            g.update_batch(rows[:, :2], np.column_stack([rows[:, 0] * g.Rc[0], rows[:, 1] * g.Rc[1]]), rows[:, 2].astype(np.int32))
+            acts = o.measure_rows(rows)
+            assert [i for _, i in acts] == [int(r[2]) for r in rows]
+        _, _, c_lo, c_hi = g.shard_info()
+        n = 3 + 2 * N
+        c_hi = min(c_hi, n)
+        ex = rel(g.x, o.x)
+        rng = np.random.default_rng(5 + rank)
+        sample = sorted(set([0, 1, 2, 3 + 2 * (int(obs[0][0][2]) - 1), c_lo] + list(rng.integers(0, c_hi, 12))))
+        worst = 0.0
+        for i in sample:
+            j0 = max(c_lo, i)                                   # SYM slab: rows <= column are live
+            if j0 >= c_hi:
+                continue
+            got = g.P_block(i, j0, 1, c_hi - j0)
+            want = o.block([i], j0, c_hi)
+            worst = max(worst, rel(got, want))
+        print('rank %d 80k-case N=%d slab cols [%d,%d): rel err x %.2e, %d sampled rows of P worst %.2e' %
+              (rank, N, c_lo, c_hi, ex, len(sample), worst), flush=True)
+        assert ex <= 1e-9 and worst <= 1e-9, (rank, ex, worst)
+        g.close()
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank == 0:
+            print('SHARD_WORKER_OK', flush=True)
+        return
+
     for storage in ('full', 'sym'):
         # (a) full loop, N = 20, 400 steps, both variants, deferred batches
         for cls, ocls, mode in ((E.EKF_SLAM, O.EKF_SLAM, 'prefix'), (E.EKF_SLAM_UC, O.EKF_SLAM_UC, 'nearest')):

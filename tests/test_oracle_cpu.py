@@ -307,3 +307,30 @@ def test_structured_oracle_errors():
     a.append([1.0, 0.0], [0.1, 0.1], [3.0, 4.0], 1)
     with pytest.raises(MemoryError):
         a.append([1.0, 0.0], [0.1, 0.1], [5.0, 6.0], 2)     # capacity
+
+
+# ---------------------------------------------------------------- matrix-free oracle (oracle/lowrank_lazy.py)
+def test_matrix_free_oracle_matches_structured_on_a_materialised_map():
+    """The matrix-free oracle used for the 80 000-landmark rows, against oracle/structured.c on the same populated
+    synthetic map small enough to materialise (N = 300): 3 steps of predict + 8 associated updates."""
+    from oracle import structured as S
+    from oracle.lowrank_lazy import LazyLowRankFilter
+    from ekf_slam_b200.synth import lowrank_to_dense
+    from bench import make_inputs
+    N, k, T = 300, 8, 3
+    x, A, d, s, lms, us, obs = make_inputs(N, k, T)
+    a = S.EKF_SLAM_UC(capacity_landmarks=N)
+    a.set_state(x, lowrank_to_dense(A, d), s)
+    b = LazyLowRankFilter(x, A, d, s)
+    for t in range(T):
+        a.predict(us[t]); b.predict(us[t])
+        acts = b.measure_rows(obs[t])
+        for row, (_, idx) in zip(obs[t], acts):
+            a.update(row[:2], [row[0] * a.Rc[0], row[1] * a.Rc[1]], idx)
+        assert [i for _, i in acts] == [int(r[2]) for r in obs[t]]          # signature association finds the true slot
+    assert G.rel(b.x, a.x) <= 1e-12
+    P = a.P
+    rows = [0, 1, 2, 3, 77, 300, 2 * N + 2]
+    assert G.rel(np.vstack([b.row(i) for i in rows]), P[rows, :]) <= 1e-11
+    assert G.rel(np.column_stack([b.col(j) for j in rows]), P[:, rows]) <= 1e-11
+    assert G.rel(b.block(rows, 100, 140), P[np.ix_(rows, range(100, 140))]) <= 1e-11

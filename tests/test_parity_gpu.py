@@ -427,3 +427,28 @@ def test_config3_10k_landmarks_vs_structured_oracle(storage, defer_m):
     print('10k %s/defer %d vs structured oracle: rel err x %.2e P %.2e' % (storage, defer_m, ex, eP))
     assert ex <= 1e-9 and eP <= 1e-9
     g.close()
+
+
+@pytest.mark.parametrize('storage', ['sym', 'full'])
+def test_config3_10k_sampled_rows_vs_matrix_free_oracle(storage):
+    """Same configuration, 3 steps, against the matrix-free oracle (oracle/lowrank_lazy.py) that also checks the
+    80 000-landmark slabs: here it additionally covers the device-side construction of the synthetic map."""
+    import ekf_slam_b200 as E
+    from oracle.lowrank_lazy import LazyLowRankFilter
+    from bench import make_inputs
+    N, k, T = 10000, 8, 3
+    x, A, d, s, lms, us, obs = make_inputs(N, k, T)
+    g = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, defer_m=8)
+    g.set_state_lowrank(x, s, A, d)
+    o = LazyLowRankFilter(x, A, d, s, Rc=g.Rc)
+    for t in range(T):
+        g.predict(us[t]); o.predict(us[t])
+        rows = obs[t]
+        g.update_batch(rows[:, :2], np.column_stack([rows[:, 0] * g.Rc[0], rows[:, 1] * g.Rc[1]]), rows[:, 2].astype(np.int32))
+        o.measure_rows(rows)
+    n = 3 + 2 * N
+    assert np.linalg.norm(g.x - o.x) / np.linalg.norm(o.x) <= 1e-9
+    for i in [0, 1, 2, 3 + 2 * (int(obs[0][0][2]) - 1), 4711, n - 1]:
+        got, want = g.P_block(i, 0, 1, n), o.block([i], 0, n)
+        assert np.linalg.norm(got - want) / np.linalg.norm(want) <= 1e-9, i
+    g.close()

@@ -26,3 +26,17 @@ def test_sharded_filter_matches_oracle_and_single_gpu(world, exchange):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, cwd=ROOT, env=env)
     print(r.stdout[-4000:]); print(r.stderr[-4000:])
     assert r.returncode == 0 and 'SHARD_WORKER_OK' in r.stdout
+
+
+@pytest.mark.parametrize('world', [2, 8])
+def test_80k_landmarks_rows_vs_matrix_free_oracle(world):
+    """BASELINE config 4 at full size: the 80 000-landmark filter (P 205 GB dense, SYM slabs) for 2 steps of predict +
+    8 updates; x and sampled rows of every rank's slab against oracle/lowrank_lazy.py, 1e-9 relative."""
+    if _ngpu() < world:
+        pytest.skip('needs %d GPUs' % world)
+    env = dict(os.environ, SHARD_CASE='80k')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
+           '--master-addr', '127.0.0.1', '--master-port', str(29540 + world), os.path.join(ROOT, 'tests', 'shard_worker.py')]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    print(r.stdout[-4000:]); print(r.stderr[-4000:])
+    assert r.returncode == 0 and 'SHARD_WORKER_OK' in r.stdout
