@@ -663,7 +663,7 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 // storage column tile y keeps row tiles 0 .. min(R, f(y)) - 1, f(y) = floor((A + y) / RPC) + 1 with
 // A = floor((col_off + TC - 1) / TC): the tiles that touch the upper triangle.  Launching exactly those (1-D grid, column
 // tile major) instead of the R x CT rectangle removes ~half the CTAs of a SYM launch, which only existed to exit.
-struct TileMap { int R, CT, A, RPC, ystar; };      // ystar: first column tile whose live count is clipped at R
+struct TileMap { int R, CT, A, RPC, ystar, order; };   // ystar: first column tile whose live count is clipped at R; order 1: two fronts (k_downdate_tma)
 __host__ __device__ inline long long tm_G(long long m, int r) {          // sum_{t<m} floor(t / r)
     const long long q = m / r, rem = m % r;
     return (long long)r * q * (q - 1) / 2 + q * rem;
@@ -674,7 +674,7 @@ __host__ __device__ inline long long tm_prefix(const TileMap& tm, int Y) {   // 
 }
 static inline TileMap tm_make(int R, int CT, int TC, int RPC, int col_off, int sym) {
     TileMap tm;
-    tm.R = R; tm.CT = CT; tm.RPC = RPC;
+    tm.R = R; tm.CT = CT; tm.RPC = RPC; tm.order = 0;
     tm.A = (col_off + TC - 1) / TC;
     long long ys = sym ? (long long)RPC * (R - 1) - tm.A : 0;            // f(y) >= R  <=>  y >= RPC (R - 1) - A
     tm.ystar = (int)(ys < 0 ? 0 : (ys > CT ? CT : ys));
@@ -843,7 +843,14 @@ k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
                const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, TileMap tm) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
     int bx, by;
-    tm_decode<C::TR / TC>(tm, (int)blockIdx.x, bx, by);   // only live tiles are launched (column tile major)
+    // Launch order of the live tiles.  Natural = column-tile major (neighbouring CTAs stream neighbouring 1 KB segments of
+    // the same columns: DRAM page locality; a scattered order measures 12 % slower).  For the triangle the natural order
+    // starts with the short column tiles, where that locality is weakest, and ends far from where it started; walking
+    // the list from both ends at once (even CTAs ascending, odd CTAs descending, meeting in the middle) measured 2.5 %
+    // faster at 10k for the rank-16 flush (0.527 -> 0.514 ms, profiles/README.md) and is its default in SYM storage.
+    const int T = (int)gridDim.x, t0 = (int)blockIdx.x;
+    const int t = tm.order == 1 ? ((t0 & 1) ? T - 1 - (t0 >> 1) : (t0 >> 1)) : t0;
+    tm_decode<C::TR / TC>(tm, t, bx, by);   // only live tiles are launched
     dd_tma_tile<KS, TC, SCOLS, NSTAGE, CG, false>(P, ld, n, ncols, Kall, Ball, lds, M, bx * C::TR, by * TC);
 }
 
@@ -904,7 +911,11 @@ static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int nco
     }
     static_assert(C::TR % TC == 0 && (C::TR / TC == 1 || C::TR / TC == 2), "tile map needs TR = TC or 2 TC");
     const int R = (n + C::TR - 1) / C::TR, CT = (ncols + TC - 1) / TC;   // row tiles cover the active rows only
-    const TileMap tm = tm_make(R, CT, TC, C::TR / TC, col_off, sym);
+    TileMap tm = tm_make(R, CT, TC, C::TR / TC, col_off, sym);
+    { static int ord = -1; if (ord < 0) { const char* v = getenv("EKF_TILE_ORDER"); ord = v ? atoi(v) : -2; }
+      // default: two fronts for the 128-column tiles of the rank >= 10 flush; the 64-column tile shapes of the lower ranks
+      // measure 1-2 % faster in natural order (profiles/README.md)
+      tm.order = !sym ? 0 : (ord == -2 ? (TC == 128 ? 1 : 0) : ord); }
     const long long live = tm_prefix(tm, CT);
     if (live <= 0 || live > 0x3fffffffLL) return;        // device decode is 32-bit
     k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, tm);
