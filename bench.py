@@ -373,8 +373,8 @@ def main():
                      'frac': achieved / peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
                      'frac_of_8TBps_nominal': achieved / 8000.0,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
-                     # of exactly this configuration (profiles/ncu_downdate_r01_tma_rank16_raw.csv); null for any other
-                     'traffic': 3.175e9 if (N == 10000 and args.storage == 'sym' and args.defer == 8 and k == 8 and world == 1) else None,
+                     # of exactly this configuration (profiles/ncu_downdate_r01_twofront_rank16_raw.csv); null for any other
+                     'traffic': 3.182e9 if (N == 10000 and args.storage == 'sym' and args.defer == 8 and k == 8 and world == 1) else None,
                      'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,
                      'share_of_step': dd_ms / ms},
         'exchange': ({'avg_ms': xch_ms / max(xch_n, 1), 'per_step': xch_n / K, 'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if xch_p2p else 'NCCL'} if world > 1 else None),
