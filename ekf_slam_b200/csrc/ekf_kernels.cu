@@ -152,26 +152,28 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
     __shared__ double Hs[2][5], HPs[2][5], Ss[2][2], Sinv[2][2], nu[2];
     __shared__ int col[EKF_BATCH_SLOTS];
     __shared__ int bad;
-    const int lane = threadIdx.x;
+    // 12 warps: warp 0 walks the linearisation chain, warp 1 evaluates the bearing (atan2d, the longest single piece)
+    // beside it -- lanes of ONE warp would run the two branches one after the other --, and every thread owns one
+    // entry of the slot block for the rank-2 refresh.  Same pieces, same bits as the one-warp form.
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int k = ob.k, ns = 3 + 2 * k;
-    if (lane < ns) col[lane] = lane < 3 ? lane : ob.a[(lane - 3) >> 1] + ((lane - 3) & 1);
-    if (lane == 0) bad = 0;
-    __syncwarp();
-    for (int e = lane; e < ns * ns; e += 32) {
-        const int i = e / ns, j = e - i * ns;
-        G[i][j] = Pc ? Pc[(int64_t)j * ldc + col[i]] : ldP(P, ld, col[i], col[j], sym);   // nothing is pending at batch start
-    }
-    if (lane < ns) xs[lane] = x[col[lane]];
-    __syncwarp();
+    if (tid < ns) col[tid] = tid < 3 ? tid : ob.a[(tid - 3) >> 1] + ((tid - 3) & 1);
+    if (tid == 0) bad = 0;
+    __syncthreads();
+    const int gi = tid / ns, gj = tid - gi * ns;                   // this thread's entry of G (tid < ns * ns <= 361)
+    const bool gown = tid < ns * ns;
+    if (gown) G[gi][gj] = Pc ? Pc[(int64_t)gj * ldc + col[gi]] : ldP(P, ld, col[gi], col[gj], sym);   // nothing is pending at batch start
+    if (tid < ns) xs[tid] = x[col[tid]];
+    const bool gup = gown && (!sym || col[gi] <= col[gj]);         // SYM: the live element is (min, max)
+    __syncthreads();
     for (int q = 0; q < k; ++q) {
         const int sa = 3 + 2 * q;
         const int sl[5] = {0, 1, 2, sa, sa + 1};
-        {   // the linearisation, entry-wise across the warp (same pieces, same bits as measurement_model / innovation_cov)
+        if (warp == 0) {   // the linearisation, entry-wise across the warp (same pieces, same bits as measurement_model / innovation_cov)
             const double xr[3] = {xs[0], xs[1], xs[2]};
             const MMPrep mp = mm_prep(xr, xs[sa], xs[sa + 1]);               // redundantly on every lane
             if (lane < 10) { const double hv = mm_H(mp, lane); Hs[lane / 5][lane % 5] = hv; out->Hs[q][lane / 5][lane % 5] = hv; }
             else if (lane == 10) { nu[0] = ob.z0[q] - mp.sq; out->nu[q][0] = nu[0]; }                   // EKF_SLAM.m:144, not wrapped (F10)
-            else if (lane == 11) { nu[1] = ob.z1[q] - mm_bearing(mp, xr[2]); out->nu[q][1] = nu[1]; }
             __syncwarp();
             if (lane < 10) HPs[lane / 5][lane % 5] = ic_HP(Hs, GSel{&G[0][0], sl}, lane / 5, lane % 5);
             __syncwarp();
@@ -187,33 +189,34 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
                         if (!isfinite(Ss[r][t]) || !isfinite(Si[r][t])) bad = 1;
                     }
             }
+        } else if (tid == 32) {
+            const double xr[3] = {xs[0], xs[1], xs[2]};
+            const MMPrep mp = mm_prep(xr, xs[sa], xs[sa + 1]);
+            nu[1] = ob.z1[q] - mm_bearing(mp, xr[2]);
+            out->nu[q][1] = nu[1];
         }
-        __syncwarp();
-        if (lane < ns) {
+        __syncthreads();
+        if (tid < ns) {
             double ph0 = 0.0, ph1 = 0.0, b0 = 0.0, b1 = 0.0;
 #pragma unroll
             for (int c = 0; c < 5; ++c) {
-                ph_acc(ph0, ph1, G[lane][sl[c]], Hs[0][c], Hs[1][c]);          // P(col_i, c_k)
-                if (!sym) b_acc(b0, b1, G[sl[c]][lane], Hs[0][c], Hs[1][c]);   // P(c_k, col_i)
+                ph_acc(ph0, ph1, G[tid][sl[c]], Hs[0][c], Hs[1][c]);          // P(col_i, c_k)
+                if (!sym) b_acc(b0, b1, G[sl[c]][tid], Hs[0][c], Hs[1][c]);   // P(c_k, col_i)
             }
             if (sym) { b0 = ph0; b1 = ph1; }
             double k0, k1, dx;
             gain_from_ph(ph0, ph1, Sinv, nu, k0, k1, dx);
-            xs[lane] = __dadd_rn(xs[lane], dx);
-            Ks[lane] = make_double2(k0, k1);
-            Bs[lane] = make_double2(b0, b1);
-            out->Kslot[q][lane] = Ks[lane];
-            out->Bslot[q][lane] = Bs[lane];
+            xs[tid] = __dadd_rn(xs[tid], dx);
+            Ks[tid] = make_double2(k0, k1);
+            Bs[tid] = make_double2(b0, b1);
+            out->Kslot[q][tid] = Ks[tid];
+            out->Bslot[q][tid] = Bs[tid];
         }
-        __syncwarp();
-        for (int e = lane; e < ns * ns; e += 32) {                 // keep the block current: P <- P - K_q B_q
-            const int i = e / ns, j = e - i * ns;
-            const bool up = !sym || col[i] <= col[j];              // SYM: the live element is (min, max)
-            G[i][j] = rank2_sub(G[i][j], up ? Ks[i] : Ks[j], up ? Bs[j] : Bs[i]);
-        }
-        __syncwarp();
+        __syncthreads();
+        if (gown) G[gi][gj] = rank2_sub(G[gi][gj], gup ? Ks[gi] : Ks[gj], gup ? Bs[gj] : Bs[gi]);   // keep the block current: P <- P - K_q B_q
+        __syncthreads();
     }
-    if (lane == 0) out->nonfinite = bad;
+    if (tid == 0) out->nonfinite = bad;
 }
 
 __global__ void __launch_bounds__(128)
@@ -1008,7 +1011,7 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc, int64_t ldc,
                            int c_lo, int c_hi) {
     if (!Pc) { c_lo = 0; c_hi = n; }
-    k_batch_lin<<<1, 32, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc);
+    k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc);   // >= EKF_BATCH_SLOTS^2 = 361 threads
     k_batch_gain<<<cdiv(n, 128), 128, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi);
 }
 

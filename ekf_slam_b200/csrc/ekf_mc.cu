@@ -298,10 +298,7 @@ k_mc_step(McArgs a) {
             const double xr[3] = {x[0], x[1], x[2]};
             const MMPrep mp = mm_prep(xr, x[al], x[al + 1]);             // every lane: cheaper than a broadcast
             if (tid < 10) sh.Hs[tid / 5][tid % 5] = mm_H(mp, tid);
-            if (tid == 31) {                                             // the atan2d chain runs beside the S chain
-                sh.nu[0] = z0 - mp.sq;                                   // :144, not wrapped (F10)
-                sh.nu[1] = z1 - mm_bearing(mp, xr[2]);
-            }
+            if (tid == 31) sh.nu[0] = z0 - mp.sq;                        // :144, not wrapped (F10)
             __syncwarp();
             if (tid < 10) sh.HP[tid / 5][tid % 5] = ic_HP(sh.Hs, sh.Pcc, tid / 5, tid % 5);
             __syncwarp();
@@ -313,6 +310,12 @@ k_mc_step(McArgs a) {
                 ic_inv(sh.S, Si);
                 sh.Sinv[0][0] = Si[0][0]; sh.Sinv[0][1] = Si[0][1]; sh.Sinv[1][0] = Si[1][0]; sh.Sinv[1][1] = Si[1][1];
             }
+        } else if (tid == 32) {
+            // the bearing (atan2d, the longest single piece) on a second warp, beside the S chain of the first:
+            // lanes of one warp would run the two branches one after the other
+            const double xr[3] = {x[0], x[1], x[2]};
+            const MMPrep mp = mm_prep(xr, x[al], x[al + 1]);
+            sh.nu[1] = z1 - mm_bearing(mp, xr[2]);
         }
         __syncthreads();
         for (int i = tid; i < n; i += T) {
