@@ -166,7 +166,9 @@ class FilterBatch:
         self.set_state(-1, x, P, s)
 
     def poses(self):
-        """x(1:3) of every filter, [nf,3] (one strided device-to-host copy; synchronises)."""
+        """x(1:3) of every filter, [nf,3].  A small kernel packs the strided triples, one copy brings them to the host.
+        After a split step the call returns as soon as the front kernel of that step is done (the poses are final
+        then), while its flush still streams the covariances; device-side errors of the step are raised here too."""
         out = np.empty((self.n_filters, 3))
         self._ck(self._lib.ekfb_get_poses(self._h, L.dptr(out)))
         return out

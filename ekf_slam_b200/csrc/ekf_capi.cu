@@ -46,6 +46,17 @@ struct ekf_handle {
     struct QObs { double z0, z1, R0, R1; int a; };
     std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
+    // ---- decoupled state chain (single-GPU handles; EKF_ASYNC_X=0 disables) ----
+    // x, s and the mode-A association do not depend on the O(n^2) flush of P, so the state half of predict, the batched
+    // signature association and the x read-back run on a side stream `sx`, ordered against the handle's stream by two
+    // events: ev_mx = "every kernel enqueued so far on the main stream that reads or writes x / s", ev_pp = "the covariance
+    // half of the last predict" (it reads xprev, which the next state half overwrites), ev_px = "the state half of the
+    // last predict".  A caller that reads x after measure() gets it when the gains are
+    // done, while the flush of that measure still streams P; its next predict/measure calls queue up behind the flush.
+    bool async_x = false;
+    cudaStream_t sx = nullptr;
+    cudaEvent_t ev_mx = nullptr, ev_px = nullptr, ev_pp = nullptr;
+    double* xprev = nullptr;   // pre-motion pose saved by the state half of predict for the covariance half
     int defer = 1;             // flush when m_pend reaches this (1 = immediate)
     int dd_variant = -1;       // downdate kernel variant (-1 = library default; EKF_DOWNDATE_VARIANT env at create)
     Lin* lin = nullptr;
@@ -79,6 +90,12 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
 
 static int32_t flush(ekf_handle* h);
 #define FLUSH(h) do { int32_t rc__ = flush(h); if (rc__ != EKF_OK) return rc__; } while (0)
+
+static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing main-stream work that touches x / s
+    if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->stream));
+    return EKF_OK;
+}
+#define MARK_X(h) do { int32_t rc__ = mark_x(h); if (rc__ != EKF_OK) return rc__; } while (0)
 
 static inline int n_of(const ekf_handle* h) { return 3 + 2 * h->N; }
 static inline int sym_of(const ekf_handle* h) { return h->p.storage == EKF_STORAGE_SYM ? 1 : 0; }
@@ -195,6 +212,11 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
+    if (h->sx) { cudaStreamSynchronize(h->sx); cudaStreamDestroy(h->sx); }
+    if (h->ev_mx) cudaEventDestroy(h->ev_mx);
+    if (h->ev_px) cudaEventDestroy(h->ev_px);
+    if (h->ev_pp) cudaEventDestroy(h->ev_pp);
+    cudaFree(h->xprev);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return EKF_OK;
@@ -311,6 +333,17 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
         CK(cudaMalloc(&h->d_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
         CK(cudaMallocHost(&h->h_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
+        {
+            const char* ax = getenv("EKF_ASYNC_X");
+            h->async_x = world == 1 && !(ax && atoi(ax) == 0);
+        }
+        if (h->async_x) {
+            CK(cudaStreamCreateWithFlags(&h->sx, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&h->ev_mx, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_px, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_pp, cudaEventDisableTiming));
+            CK(cudaMalloc(&h->xprev, sizeof(double) * 4));
+        }
         return init_state(h);
     }();
     if (rc != EKF_OK) {
@@ -343,6 +376,7 @@ extern "C" const char* ekf_last_error(ekf_handle* h) { return h ? h->err.c_str()
 extern "C" int32_t ekf_sync(ekf_handle* h) {
     CKH(h);
     CK(cudaStreamSynchronize(h->stream));
+    if (h->sx) CK(cudaStreamSynchronize(h->sx));
     return EKF_OK;
 }
 
@@ -367,7 +401,18 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     FLUSH(h);
     if (h->world > 1)
         launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
-    else
+    else if (h->async_x) {
+        // state half first, on the side stream, as soon as the last writer of x is done (not the flush behind it);
+        // covariance half on the main stream with the heading the state half saved (EKF_SLAM.m:42,63-64 use theta before f())
+        CK(cudaStreamWaitEvent(h->sx, h->ev_mx, 0));
+        CK(cudaStreamWaitEvent(h->sx, h->ev_pp, 0));
+        launch_predict_x_save(h->sx, h->x, u[0], u[1], h->xprev);
+        CK(cudaEventRecord(h->ev_px, h->sx));
+        CK(cudaStreamWaitEvent(h->stream, h->ev_px, 0));
+        launch_predict_P(h->stream, h->P, h->ld, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(h->ev_pp, h->stream));   // NOT ev_mx: a reader of x must not wait for this kernel (it sits behind the flush)
+    } else
         launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     h->launches += 2;
     CK(cudaGetLastError());
@@ -535,6 +580,7 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
                           h->lin, h->Kd, h->Bd, h->ld, h->m_pend);
     h->launches += 2;
     CK(cudaGetLastError());
+    MARK_X(h);
     h->m_pend += 1;
     if (h->m_pend >= h->defer) FLUSH(h);
     return EKF_OK;
@@ -560,6 +606,7 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
                   signature, sym_of(h));
     h->launches += 1;
     CK(cudaGetLastError());
+    MARK_X(h);
     h->N += 1;
     return EKF_OK;
 }
@@ -608,6 +655,7 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
             launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld);
             h->launches += 2;
             CK(cudaGetLastError());
+            MARK_X(h);                      // x is final for this chunk here, before the flush
             h->m_pend = ob.k;
             FLUSH(h);
             i += ob.k;
@@ -659,11 +707,16 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
         const int cnt = std::min(k - from, EKF_ASSOC_BATCH);
         for (int j = 0; j < cnt; ++j) zb.z2[j] = obs[from + j + 2 * k];
         CK(cudaSetDevice(h->p.device));
-        launch_associate_sig_batch(h->stream, h->s, h->N, zb, cnt, h->p.s_cost, h->p.s_thresh, h->d_res);
+        cudaStream_t st = h->stream;
+        if (h->async_x) {                   // mode A reads only s (written by append): no need to wait for a flush
+            st = h->sx;
+            CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
+        }
+        launch_associate_sig_batch(st, h->s, h->N, zb, cnt, h->p.s_cost, h->p.s_thresh, h->d_res);
         h->launches += 1;
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult) * cnt, cudaMemcpyDeviceToHost, h->stream));
-        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult) * cnt, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
         assoc_from = from; assoc_to = from + cnt;
         return EKF_OK;
     };
@@ -730,8 +783,13 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
     CK(cudaSetDevice(h->p.device));
     if (h->world > 1) FLUSH(h);           // sharded: x of queued observations is produced by the batch
-    CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    cudaStream_t st = h->stream;
+    if (h->async_x) {                     // behind the last writer of x, not behind the flush that follows it
+        st = h->sx;
+        CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
+    }
+    CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return EKF_OK;
 }
 
@@ -815,6 +873,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
                                  sizeof(double) * n, hi - h->c_lo, cudaMemcpyHostToDevice, h->stream));
     }
     CK(cudaStreamSynchronize(h->stream));
+    MARK_X(h);
     h->q.clear();
     h->N = N;
     return EKF_OK;
@@ -842,6 +901,7 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     h->launches += 1;
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(h->stream));
+    MARK_X(h);
     cudaFree(dA); cudaFree(dd);
     h->N = N;
     return EKF_OK;

@@ -51,8 +51,11 @@ __global__ void k_predict_P(double* __restrict__ P, int64_t ld, const double* __
     }
 }
 
-__global__ void k_predict_x(double* __restrict__ x, double u1, double u2) {   // EKF_SLAM.m:57-60, :50
+// `prev` (may be null): receives the pre-motion pose.  The decoupled predict (ekf_capi.cu, async_x) runs this kernel
+// FIRST on the side stream and hands k_predict_P `prev` as its x, so that it still sees the heading before f().
+__global__ void k_predict_x(double* __restrict__ x, double u1, double u2, double* __restrict__ prev) {   // EKF_SLAM.m:57-60, :50
     double th = x[2];
+    if (prev) { prev[0] = x[0]; prev[1] = x[1]; prev[2] = th; }
     x[0] = x[0] + u1 * cosd(th + u2);
     x[1] = x[1] + u1 * sind(th + u2);
     x[2] = wrapTo360(th + u2);
@@ -996,10 +999,19 @@ void launch_ellipses(cudaStream_t st, const double* P, int64_t ld, const double*
 
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym) {
     k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, u1, u2, C, sym);
-    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2);
+    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr);
 }
 
-void launch_predict_x(cudaStream_t st, double* x, double u1, double u2) { k_predict_x<<<1, 1, 0, st>>>(x, u1, u2); }
+void launch_predict_x(cudaStream_t st, double* x, double u1, double u2) { k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr); }
+
+// The two halves of launch_predict for the decoupled path: the state half saves the pre-motion pose into xprev, the
+// covariance half reads its heading from there (same arithmetic, bit-identical results).
+void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev) {
+    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, xprev);
+}
+void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym) {
+    k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, xprev, n, u1, u2, C, sym);
+}
 
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
                            double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m) {

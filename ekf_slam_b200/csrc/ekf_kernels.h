@@ -38,6 +38,8 @@ void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double
 void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo, int ncols, const double* A, int r,
                          const double* d);
 void launch_predict_x(cudaStream_t st, double* x, double u1, double u2);
+void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev);      // decoupled predict, state half (side stream)
+void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym);   // covariance half
 // ---- column-slab sharded filter (ekf_shard.cu) ----
 #define EKF_MAX_PEERS 8
 struct PeerSet { double* pc[EKF_MAX_PEERS]; int* flags[EKF_MAX_PEERS]; int world, rank; };   // cudaIpc-mapped Pc buffers / flag words of every rank
@@ -83,9 +85,10 @@ struct McArgs {
 
 enum { MC_ERR_TABLE = 1, MC_ERR_CAPACITY = 2, MC_ERR_INDEX = 3 };
 void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem);   // fused (one kernel)
+void launch_mc_pack_poses(cudaStream_t st, const double* x, int64_t xstride, int n_filters, double* out, const int* err);   // out[3 nf] = x(1:3) of every filter, then the 2-int error word
 void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters, size_t smem_limit, int front_kind);   // split: latency half (run-based k_mc_front, or k_mc_step<.,1> when front_kind = 1 / mode B / the slot cache does not fit)
 void launch_mc_flush_tma(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);  // split: bandwidth half, TMA-staged DMMA (default)
 void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);
-void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max);    // split: bandwidth half, warp-per-column-group (default)      // split: bandwidth half (m_max >= every Mpend[f])
+void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max, int tc = 64);   // tc: columns of a filter per CTA (32 | 64 | 128)    // split: bandwidth half, warp-per-column-group (default)      // split: bandwidth half (m_max >= every Mpend[f])
 
 }  // namespace ekf

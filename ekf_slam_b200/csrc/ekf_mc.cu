@@ -15,6 +15,7 @@
 #include "ekf_device.cuh"
 #include <math_constants.h>
 #include <limits.h>
+#include <cstdlib>
 
 namespace ekf {
 
@@ -512,9 +513,28 @@ k_mc_flush_w(McArgs a) {
     }
 }
 
-template <int M>
+// Pose read-back: x(1:3) of every filter (stride xstride) packed into out[3 nf]; the device error word rides behind it
+// so that one contiguous copy brings both to the host.
+__global__ void k_mc_pack_poses(const double* __restrict__ x, int64_t xstride, int nf, double* __restrict__ out,
+                                const int* __restrict__ err) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < 3 * nf) {
+        const int f = e / 3, c = e - 3 * f;
+        out[e] = x[(int64_t)f * xstride + c];
+    }
+    if (e == 0) {
+        int* w = (int*)(out + 3 * (int64_t)nf);
+        w[0] = err[0];
+        w[1] = err[1];
+    }
+}
+
+void launch_mc_pack_poses(cudaStream_t st, const double* x, int64_t xstride, int n_filters, double* out, const int* err) {
+    k_mc_pack_poses<<<(3 * n_filters + 255) / 256, 256, 0, st>>>(x, xstride, n_filters, out, err);
+}
+
+template <int M, int TC>
 static void launch_mc_flush_w_m(cudaStream_t st, const McArgs& a, int n_filters, int cap_n) {
-    constexpr int TC = 64;
     const size_t smem = ((size_t)(a.cap + 2) * 2 * M + (size_t)TC * M) * sizeof(double2);
     static size_t smem_set = 0;
     if (smem > smem_set) {
@@ -526,17 +546,26 @@ static void launch_mc_flush_w_m(cudaStream_t st, const McArgs& a, int n_filters,
     k_mc_flush_w<M, TC><<<grid, 256, smem, st>>>(a);
 }
 
-void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max) {
+template <int TC>
+static void launch_mc_flush_w_tc(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max) {
     switch (m_max) {
-        case 1: launch_mc_flush_w_m<1>(st, a, n_filters, cap_n); break;
-        case 2: launch_mc_flush_w_m<2>(st, a, n_filters, cap_n); break;
-        case 3: launch_mc_flush_w_m<3>(st, a, n_filters, cap_n); break;
-        case 4: launch_mc_flush_w_m<4>(st, a, n_filters, cap_n); break;
-        case 5: launch_mc_flush_w_m<5>(st, a, n_filters, cap_n); break;
-        case 6: launch_mc_flush_w_m<6>(st, a, n_filters, cap_n); break;
-        case 7: launch_mc_flush_w_m<7>(st, a, n_filters, cap_n); break;
-        default: launch_mc_flush_w_m<8>(st, a, n_filters, cap_n); break;
+        case 1: launch_mc_flush_w_m<1, TC>(st, a, n_filters, cap_n); break;
+        case 2: launch_mc_flush_w_m<2, TC>(st, a, n_filters, cap_n); break;
+        case 3: launch_mc_flush_w_m<3, TC>(st, a, n_filters, cap_n); break;
+        case 4: launch_mc_flush_w_m<4, TC>(st, a, n_filters, cap_n); break;
+        case 5: launch_mc_flush_w_m<5, TC>(st, a, n_filters, cap_n); break;
+        case 6: launch_mc_flush_w_m<6, TC>(st, a, n_filters, cap_n); break;
+        case 7: launch_mc_flush_w_m<7, TC>(st, a, n_filters, cap_n); break;
+        default: launch_mc_flush_w_m<8, TC>(st, a, n_filters, cap_n); break;
     }
+}
+
+// Columns of one filter per CTA (EKF_MC_TC = 32 | 64 | 128, default 64): wider CTAs stage the filter's K slab fewer
+// times, narrower ones balance the triangle better; all give bit-identical results.
+void launch_mc_flush_w(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max, int tc) {
+    if (tc == 128) launch_mc_flush_w_tc<128>(st, a, n_filters, cap_n, m_max);
+    else if (tc == 32) launch_mc_flush_w_tc<32>(st, a, n_filters, cap_n, m_max);
+    else launch_mc_flush_w_tc<64>(st, a, n_filters, cap_n, m_max);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

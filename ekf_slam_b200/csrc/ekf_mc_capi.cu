@@ -25,9 +25,17 @@ struct ekfb_handle {
     int dev_smem = 0;                        // opt-in shared memory per block of the device
     int front_kind = 1;                      // 1: k_mc_step<.,1>, one observation at a time (default, measured faster); EKF_MC_FRONT=run -> 0 (run-based k_mc_front)
     int flush_kind = 0;                      // 0: warp-per-column-group flush (default); EKF_MC_FLUSH=ldg -> 1 (tiled, gains in registers), =tma -> 2 (TMA-staged DMMA)
+    int flush_tc = 64;                       // columns of one filter per CTA of the warp flush (EKF_MC_TC = 32 | 64 | 128)
     bool split = true;                       // front (latency) + flush (bandwidth) kernels; EKF_MC_FUSED=1 selects the one-kernel step
     double flush_ms = 0.0;
     int* h_err = nullptr;                    // pinned
+    // early pose read-back (EKF_MC_EARLY_POSES=0 disables): the poses of a split step are final when the front kernel
+    // ends, so ekfb_get_poses packs and copies them on a side stream behind `ev_front` while the flush still streams P
+    cudaStream_t sx = nullptr;
+    cudaEvent_t ev_front = nullptr;
+    bool early = true, front_ev_valid = false;
+    double* d_poses = nullptr;               // [nf][3] packed + 2 ints of the device error word behind them
+    double* h_poses = nullptr;               // pinned mirror of d_poses
     // staging for host inputs (mem = 0)
     double *d_u = nullptr, *d_obs = nullptr, *d_loc = nullptr;
     int *d_counts = nullptr, *d_idx = nullptr, *d_ntab = nullptr, *d_act = nullptr;
@@ -64,6 +72,10 @@ extern "C" int32_t ekfb_destroy(ekfb_handle* h) {
     cudaFree(h->d_u); cudaFree(h->d_obs); cudaFree(h->d_loc); cudaFree(h->d_counts); cudaFree(h->d_idx);
     cudaFree(h->d_ntab); cudaFree(h->d_act);
     if (h->h_err) cudaFreeHost(h->h_err);
+    if (h->sx) { cudaStreamSynchronize(h->sx); cudaStreamDestroy(h->sx); }
+    if (h->ev_front) cudaEventDestroy(h->ev_front);
+    cudaFree(h->d_poses);
+    if (h->h_poses) cudaFreeHost(h->h_poses);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return EKF_OK;
@@ -94,6 +106,7 @@ extern "C" int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t m
         if (!h->split) maxd = std::min(maxd, max_obs);     // fused: slabs cost shared memory; split: global memory
         if (const char* v = getenv("EKF_MC_FUSED")) h->split = atoi(v) == 0;
         if (const char* v = getenv("EKF_MC_FLUSH")) h->flush_kind = std::string(v) == "ldg" ? 1 : (std::string(v) == "tma" ? 2 : 0);
+        if (const char* v = getenv("EKF_MC_TC")) h->flush_tc = atoi(v);
         if (const char* v = getenv("EKF_MC_FRONT")) h->front_kind = std::string(v) == "run" ? 0 : 1;
         int dev_smem = 0;
         CKB(cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
@@ -120,6 +133,11 @@ extern "C" int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t m
         CKB(cudaMalloc(&h->N, sizeof(int) * n_filters));
         CKB(cudaMalloc(&h->err, sizeof(int) * 2));
         CKB(cudaMallocHost(&h->h_err, sizeof(int) * 2));
+        if (const char* v = getenv("EKF_MC_EARLY_POSES")) h->early = atoi(v) != 0;
+        CKB(cudaStreamCreateWithFlags(&h->sx, cudaStreamNonBlocking));
+        CKB(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming));
+        CKB(cudaMalloc(&h->d_poses, sizeof(double) * (3 * (size_t)n_filters + 1)));
+        CKB(cudaMallocHost(&h->h_poses, sizeof(double) * (3 * (size_t)n_filters + 1)));
         CKB(cudaMalloc(&h->d_u, sizeof(double) * 2 * n_filters));
         CKB(cudaMalloc(&h->d_obs, sizeof(double) * 3 * max_obs * n_filters));
         CKB(cudaMalloc(&h->d_loc, sizeof(double) * 2 * max_table * n_filters));
@@ -150,17 +168,14 @@ extern "C" int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t m
     return EKF_OK;
 }
 
+static int32_t decode_err(ekfb_handle* h, int code, int f);
 static int32_t check_err(ekfb_handle* h) {
     CKB(cudaMemcpyAsync(h->h_err, h->err, sizeof(int) * 2, cudaMemcpyDeviceToHost, h->stream));
     CKB(cudaStreamSynchronize(h->stream));
     if (h->h_err[0] == 0) return EKF_OK;
     const int code = h->h_err[0], f = h->h_err[1];
     CKB(cudaMemsetAsync(h->err, 0, sizeof(int) * 2, h->stream));
-    if (code == MC_ERR_CAPACITY)
-        return failb(h, EKF_ECAPACITY, "filter " + std::to_string(f) + ": append beyond capacity_landmarks");
-    if (code == MC_ERR_TABLE)
-        return failb(h, EKF_EINVAL, "filter " + std::to_string(f) + ": measure: landmark index not in the table (EKF_SLAM.m:111,120 / EKF_SLAM_UC.m:123)");
-    return failb(h, EKF_EINVAL, "filter " + std::to_string(f) + ": update slot outside 1..N (EKF_SLAM.m:125)");
+    return decode_err(h, code, f);
 }
 
 extern "C" int32_t ekfb_sync(ekfb_handle* h) {
@@ -218,16 +233,18 @@ extern "C" int32_t ekfb_step(ekfb_handle* h, int32_t mem, const double* u, const
         const int mm = std::min(h->maxd, h->max_obs);
         if (h->flush_kind == 1) launch_mc_flush(st, s, cnt_f, h->cap_n, mm);
         else if (h->flush_kind == 2) launch_mc_flush_tma(st, s, cnt_f, h->cap_n, mm);
-        else launch_mc_flush_w(st, s, cnt_f, h->cap_n, mm);
+        else launch_mc_flush_w(st, s, cnt_f, h->cap_n, mm, h->flush_tc);
     };
     if (h->prof) CKB(cudaEventRecord(*ev(0), h->stream));
     if (h->split) {
         launch_mc_front(h->stream, a, nf, (size_t)h->dev_smem, h->front_kind);
+        if (h->early) { CKB(cudaEventRecord(h->ev_front, h->stream)); h->front_ev_valid = true; }   // x, N, err are final here; the flush only touches P
         if (h->prof) CKB(cudaEventRecord(*ev(2), h->stream));
         if (do_measure) flush(h->stream, a, nf);
         if (h->prof) CKB(cudaEventRecord(*ev(3), h->stream));
     } else {
         launch_mc_step(h->stream, a, nf, 256, h->smem);
+        h->front_ev_valid = false;
         if (h->prof) { CKB(cudaEventRecord(*ev(2), h->stream)); CKB(cudaEventRecord(*ev(3), h->stream)); }
     }
     if (h->prof) { CKB(cudaEventRecord(*ev(1), h->stream)); h->ev_used++; }
@@ -323,6 +340,7 @@ extern "C" int32_t ekfb_get_P(ekfb_handle* h, int32_t f, double* P, int32_t lda)
 
 extern "C" int32_t ekfb_set_state(ekfb_handle* h, int32_t f, const double* x, const double* P, int32_t lda,
                                   const double* s, int32_t N) {
+    if (h) h->front_ev_valid = false;      // x changes on the handle's stream from here on
     if (!h) return EKF_EINVAL;
     if (f < 0) {                                  // every filter gets the same state: upload once, replicate on the device
         int32_t rc = ekfb_set_state(h, 0, x, P, lda, s, N);
@@ -352,13 +370,36 @@ extern "C" int32_t ekfb_set_state(ekfb_handle* h, int32_t f, const double* x, co
     return EKF_OK;
 }
 
-// Robot poses x(1:3) of every filter in one strided copy: the per-step result a Monte-Carlo driver reads back.
+// Robot poses x(1:3) of every filter, the per-step result a Monte-Carlo driver reads back: one small kernel packs the
+// nf strided triples (and the device error word) into a contiguous buffer, one copy brings them to pinned memory.
+// After a split step this runs on the side stream behind the front kernel's event, so the caller gets the poses while
+// the flush of that step is still streaming P (it does not touch x); otherwise on the handle's stream.
+static int32_t decode_err(ekfb_handle* h, int code, int f) {
+    if (code == MC_ERR_CAPACITY)
+        return failb(h, EKF_ECAPACITY, "filter " + std::to_string(f) + ": append beyond capacity_landmarks");
+    if (code == MC_ERR_TABLE)
+        return failb(h, EKF_EINVAL, "filter " + std::to_string(f) + ": measure: landmark index not in the table (EKF_SLAM.m:111,120 / EKF_SLAM_UC.m:123)");
+    return failb(h, EKF_EINVAL, "filter " + std::to_string(f) + ": update slot outside 1..N (EKF_SLAM.m:125)");
+}
+
 extern "C" int32_t ekfb_get_poses(ekfb_handle* h, double* poses) {
     if (!h || !poses) return EKF_EINVAL;
     CKB(cudaSetDevice(h->p.device));
-    CKB(cudaMemcpy2DAsync(poses, sizeof(double) * 3, h->x, sizeof(double) * h->ldp, sizeof(double) * 3, h->nf,
-                          cudaMemcpyDeviceToHost, h->stream));
-    return check_err(h);
+    cudaStream_t st = h->stream;
+    if (h->early && h->front_ev_valid) {
+        st = h->sx;
+        CKB(cudaStreamWaitEvent(st, h->ev_front, 0));
+    }
+    launch_mc_pack_poses(st, h->x, h->ldp, h->nf, h->d_poses, h->err);
+    CKB(cudaGetLastError());
+    CKB(cudaMemcpyAsync(h->h_poses, h->d_poses, sizeof(double) * (3 * (size_t)h->nf + 1), cudaMemcpyDeviceToHost, st));
+    CKB(cudaStreamSynchronize(st));
+    memcpy(poses, h->h_poses, sizeof(double) * 3 * (size_t)h->nf);
+    int e2[2];
+    memcpy(e2, h->h_poses + 3 * (size_t)h->nf, sizeof(e2));
+    if (e2[0] == 0) return EKF_OK;
+    CKB(cudaMemsetAsync(h->err, 0, sizeof(int) * 2, h->stream));      // stream-ordered before the next step's front
+    return decode_err(h, e2[0], e2[1]);
 }
 
 extern "C" int32_t ekfb_downdate_bytes(ekfb_handle* h, double* bytes) {

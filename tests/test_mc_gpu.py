@@ -52,13 +52,14 @@ def test_batch_matches_oracle_per_filter(storage, cls, defer_m, assoc):
     b.close()
 
 
-@pytest.mark.parametrize('impl', ['split-warp', 'split-tma', 'split-ldg', 'split-run', 'fused'])
+@pytest.mark.parametrize('impl', ['split-warp', 'split-warp-tc32', 'split-warp-tc128', 'split-tma', 'split-ldg', 'split-run', 'fused'])
 @pytest.mark.parametrize('storage', ['sym', 'full'])
 def test_batch_equals_single_filter_path_bitwise(storage, impl, monkeypatch):
     """All step implementations: split front + warp-per-column-group flush (default), the TMA-staged and the tiled
     register-path flush (EKF_MC_FLUSH=tma|ldg), the run-based front (EKF_MC_FRONT=run) and the one-kernel step
-    (EKF_MC_FUSED=1)."""
+    (EKF_MC_FUSED=1); the warp flush also with 32 and 128 columns of a filter per CTA (EKF_MC_TC)."""
     import ekf_slam_b200 as E
+    monkeypatch.setenv('EKF_MC_TC', {'split-warp-tc32': '32', 'split-warp-tc128': '128'}.get(impl, '64'))
     monkeypatch.setenv('EKF_MC_FUSED', '1' if impl == 'fused' else '0')
     monkeypatch.setenv('EKF_MC_FLUSH', {'split-ldg': 'ldg', 'split-tma': 'tma'}.get(impl, 'warp'))
     monkeypatch.setenv('EKF_MC_FRONT', 'run' if impl == 'split-run' else 'step')
@@ -112,4 +113,44 @@ def test_batch_shared_table_ragged_counts_and_errors():
     with pytest.raises(E.EkfError) as e:
         b.sync()
     assert e.value.code == -1
+    b.close()
+
+
+@pytest.mark.parametrize('early', ['1', '0'])
+@pytest.mark.parametrize('fused', ['0', '1'])
+def test_poses_readback_early_and_late(early, fused, monkeypatch):
+    """ekfb_get_poses: after a split step the poses come back on the side stream behind the front kernel (while the
+    flush still runs); they must equal x(1:3) read filter by filter after a full sync, in every mode, also right after
+    set_state, and a device-side error of the step must surface through the same call."""
+    import ekf_slam_b200 as E
+    from types import SimpleNamespace
+    monkeypatch.setenv('EKF_MC_EARLY_POSES', early)
+    monkeypatch.setenv('EKF_MC_FUSED', fused)
+    nf, N, T, k = 7, 12, 25, 4
+    ws = _worlds(nf, 'EKF_SLAM_UC', N, T, k)
+    b = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=N, max_obs=k, max_table=N, storage='sym', defer_m=4)
+    assert np.array_equal(b.poses(), np.zeros((nf, 3)))
+    for t in range(T):
+        b.step(np.array([w.u[t] for w in ws]), [w.observed[t] for w in ws], [list(w.table[:w.n_table[t]]) for w in ws])
+        p = b.poses()                                    # possibly before the flush of this step has finished
+        if t % 6 == 0:
+            b.sync()
+            assert np.array_equal(p, np.array([b[f].x[:3] for f in range(nf)])), t
+    p_last = b.poses()
+    b.sync()
+    assert np.array_equal(p_last, np.array([b[f].x[:3] for f in range(nf)]))
+    # set_state invalidates the early path: the poses are those just written
+    x0 = b[0].x.copy(); x0[:3] = [1.5, -2.5, 33.0]
+    b.set_state(3, x0, b[0].P, b[0].s)
+    assert np.array_equal(b.poses()[3], [1.5, -2.5, 33.0])
+    b.close()
+    # a capacity error raised by the front kernel is reported by poses() as well, and cleared
+    b = E.FilterBatch('EKF_SLAM_UC', 2, capacity_landmarks=2, max_obs=3, max_table=3)
+    tab = [SimpleNamespace(index=i + 1, loc=np.array([1.0 + i, 2.0])) for i in range(3)]
+    obs = [np.array([[2.0, 30.0, 1], [3.0, 40.0, 2], [4.0, 50.0, 3]])] * 2
+    b.step(np.zeros((2, 2)), obs, tab)
+    with pytest.raises(E.EkfError) as e:
+        b.poses()
+    assert e.value.code == -2
+    b.sync()                                             # error word was cleared
     b.close()

@@ -452,3 +452,72 @@ def test_config3_10k_sampled_rows_vs_matrix_free_oracle(storage):
         got, want = g.P_block(i, 0, 1, n), o.block([i], 0, n)
         assert np.linalg.norm(got - want) / np.linalg.norm(want) <= 1e-9, i
     g.close()
+
+
+@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 0), ('sym', 3)])
+@pytest.mark.parametrize('variant', ['known', 'uc'])
+def test_decoupled_state_chain_is_bit_identical(variant, storage, defer_m, monkeypatch):
+    """EKF_ASYNC_X (default on): the state half of predict, the batched signature association and the x read-back run
+    on a side stream, ordered by events against the covariance work.  Same kernels, same arithmetic: x read at every
+    point of the loop, the actions and the final P must be bit-identical to the single-stream path (EKF_ASYNC_X=0),
+    whatever the interleaving of predict / read x / measure / read x / append / double predict."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    cls = E.EKF_SLAM if variant == 'known' else E.EKF_SLAM_UC
+    w = make_world(N=24, T=150, k=6, mode='prefix' if variant == 'known' else 'nearest', seed=11)
+    runs = {}
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_ASYNC_X', flag)
+        g = cls(capacity_landmarks=24, storage=storage, defer_m=defer_m)
+        xs = []
+        for t in range(w.T):
+            g.predict(w.u[t])
+            if t % 3 == 0:
+                xs.append(g.x)                       # x after the motion step, before the covariance half has run
+            if t % 7 == 3:
+                g.predict(w.u[t])                    # two predicts in a row (xprev must not be overwritten early)
+            g.measure(None, w.u[t], w.stub(t), pass_x=(t % 2 == 0))
+            xs.append(g.x)                           # x after measure, possibly while the flush still streams P
+            if t % 25 == 24:
+                xs.append(g.covariance_ellipses())   # main-stream reader of x and P
+                xs.append(g.P_block(0, 0, 3, 3))
+        runs[flag] = (xs, list(g.chosen), g.P, g.s)
+        g.close()
+    a, b = runs['0'], runs['1']
+    assert a[1] == b[1], 'actions differ'
+    assert len(a[0]) == len(b[0]) and all(np.array_equal(p, q, equal_nan=True) for p, q in zip(a[0], b[0])), 'x differs somewhere in the loop'
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+
+
+def test_decoupled_state_chain_large_map_overlaps_the_flush(monkeypatch):
+    """Same check where it matters: 5 000 landmarks (P 0.8 GB), so that the flush of one measure() is still streaming
+    P when x is read and the next predict / association are enqueued.  x after every predict and every measure, the
+    actions and sampled rows of P must be bit-identical with and without the side stream."""
+    import ekf_slam_b200 as E
+    from bench import make_inputs
+    from tests.golden_util import Stub
+    from types import SimpleNamespace
+    N, k, T = 5000, 8, 24
+    x, A, d, s, lms, us, obs = make_inputs(N, k, T)
+    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
+    n = 3 + 2 * N
+    runs = {}
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_ASYNC_X', flag)
+        g = E.EKF_SLAM_UC(capacity_landmarks=N, storage='sym', defer_m=8)
+        g.set_state_lowrank(x, s, A, d)
+        xs = []
+        for t in range(T):
+            g.predict(us[t])
+            if t % 5 == 4:
+                g.predict(us[t])
+            xs.append(g.x)
+            g.measure(None, us[t], Stub(obs[t], table))
+            xs.append(g.x)
+        rows = [g.P_block(i, 0, 1, n) for i in (0, 2, 3 + 2 * (int(obs[0][0][2]) - 1), 4711, n - 1)]
+        runs[flag] = (xs, list(g.chosen), rows)
+        g.close()
+    a, b = runs['0'], runs['1']
+    assert a[1] == b[1] and len(a[1]) == T * k
+    assert all(np.array_equal(p, q) for p, q in zip(a[0], b[0])), 'x differs somewhere in the loop'
+    assert all(np.array_equal(p, q) for p, q in zip(a[2], b[2])), 'P differs'
