@@ -338,7 +338,11 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             h->async_x = world == 1 && !(ax && atoi(ax) == 0);
         }
         if (h->async_x) {
-            CK(cudaStreamCreateWithFlags(&h->sx, cudaStreamNonBlocking));
+            // highest priority: its tiny kernels must be scheduled at once beside a flush that still has ~20 waves of
+            // CTAs waiting (at equal priority the block scheduler drains the flush's grid first)
+            int pr_lo = 0, pr_hi = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&pr_lo, &pr_hi));
+            CK(cudaStreamCreateWithPriority(&h->sx, cudaStreamNonBlocking, pr_hi));
             CK(cudaEventCreateWithFlags(&h->ev_mx, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&h->ev_px, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&h->ev_pp, cudaEventDisableTiming));

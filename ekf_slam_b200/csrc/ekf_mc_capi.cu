@@ -134,7 +134,11 @@ extern "C" int32_t ekfb_create(const ekf_params* p, int32_t n_filters, int32_t m
         CKB(cudaMalloc(&h->err, sizeof(int) * 2));
         CKB(cudaMallocHost(&h->h_err, sizeof(int) * 2));
         if (const char* v = getenv("EKF_MC_EARLY_POSES")) h->early = atoi(v) != 0;
-        CKB(cudaStreamCreateWithFlags(&h->sx, cudaStreamNonBlocking));
+        {   // highest priority, so that the pack kernel is scheduled beside a flush that still has CTAs waiting
+            int pr_lo = 0, pr_hi = 0;
+            CKB(cudaDeviceGetStreamPriorityRange(&pr_lo, &pr_hi));
+            CKB(cudaStreamCreateWithPriority(&h->sx, cudaStreamNonBlocking, pr_hi));
+        }
         CKB(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming));
         CKB(cudaMalloc(&h->d_poses, sizeof(double) * (3 * (size_t)n_filters + 1)));
         CKB(cudaMallocHost(&h->h_poses, sizeof(double) * (3 * (size_t)n_filters + 1)));

@@ -118,6 +118,8 @@ int32_t ekf_measure_batch(ekf_handle* h, const double* observed_LL, int32_t k,
 
 /* State access (public properties x, P, s of the reference classes, EKF_SLAM.m:6-9). */
 int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N);
+/* ekf_get_x returns x as of every call made before it.  It waits for the last kernel that writes x, not for the
+ * O(n^2) covariance flush queued behind that kernel (single-GPU handles; EKF_ASYNC_X=0 makes it wait for the stream). */
 int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len);            /* len >= 3+2N */
 int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len);            /* len >= N */
 int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda);            /* n x n column-major, lda >= n; SYM storage is mirrored */
@@ -179,6 +181,8 @@ int32_t ekfb_get_x(ekfb_handle* h, int32_t filter, double* x, int32_t len);
 int32_t ekfb_get_s(ekfb_handle* h, int32_t filter, double* s, int32_t len);
 int32_t ekfb_get_P(ekfb_handle* h, int32_t filter, double* P, int32_t lda);      /* SYM storage is mirrored on the host side copy */
 int32_t ekfb_set_state(ekfb_handle* h, int32_t filter /* < 0: every filter */, const double* x, const double* P, int32_t lda, const double* s, int32_t N);
+/* Poses as of every step made before the call; after a split step it returns when the front kernel of that step is done
+ * (the flush does not touch x) and reports that step's device-side errors.  EKF_MC_EARLY_POSES=0: waits for the stream. */
 int32_t ekfb_get_poses(ekfb_handle* h, double* poses /* n_filters x 3, filter-major: x(1:3) of every filter */);
 /* Algorithmic HBM bytes of the covariance pass of one step over all filters at their current sizes. */
 int32_t ekfb_downdate_bytes(ekfb_handle* h, double* bytes);

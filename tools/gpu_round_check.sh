@@ -30,6 +30,8 @@ lap "bench mc (default)"
 timeout 300 python bench.py --workload mc > $O/bench_mc.json 2> $O/bench_mc.err
 lap "bench mc, EKF_MC_EARLY_POSES=0"
 EKF_MC_EARLY_POSES=0 timeout 200 python bench.py --workload mc --no-cpu-baseline --steps 100 > $O/bench_mc_late.json 2> $O/bench_mc_late.err
+lap "bench mc, default, 100 steps (for the A/B legs)"
+timeout 200 python bench.py --workload mc --no-cpu-baseline --steps 100 > $O/bench_mc_100.json 2> $O/bench_mc_100.err
 lap "bench mc, EKF_MC_TC=128"
 EKF_MC_TC=128 timeout 200 python bench.py --workload mc --no-cpu-baseline --steps 100 > $O/bench_mc_tc128.json 2> $O/bench_mc_tc128.err
 lap "bench mc, EKF_MC_TC=32"
@@ -42,7 +44,7 @@ lap "ncu launch list mc"
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/launches_mc.csv \
     python bench.py --workload mc --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_mc.log 2>&1
 lap "done"
-for f in bench_10k bench_10k_sync bench_mc bench_mc_late bench_mc_tc128 bench_mc_tc32; do
+for f in bench_10k bench_10k_sync bench_mc bench_mc_100 bench_mc_late bench_mc_tc128 bench_mc_tc32; do
     python - "$O/$f.json" <<'EOF'
 import json, sys
 try:
