@@ -5,7 +5,9 @@ A "step" is one pass of the hot path over one batch of synthetic input: predict(
 measurement update of k=8 range-bearing observations on a fully populated 10 000-landmark map
 (P 20003^2 fp64).  `value` = updates/s with all inputs resident (direct C-ABI calls, scalars only);
 `e2e` = the same through the reference-facing class API (EKF_SLAM_UC.predict / .measure with a
-landmark_list stub: association + update per observation, host buffers, x read back each step).
+landmark_list stub: association + update per observation, host buffers, x read back twice per step), wall clock
+between two device-wide synchronisations.  The reads of x return behind the gains of the step, not behind its flush
+(DESIGN.md "Decoupled state chain"), so that loop keeps the device busy; EKF_ASYNC_X=0 shows the difference.
 """
 import argparse
 import json
@@ -373,8 +375,8 @@ def main():
                      'frac': achieved / peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
                      'frac_of_8TBps_nominal': achieved / 8000.0,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
-                     # of exactly this configuration (profiles/ncu_downdate_r01_twofront_rank16_raw.csv); null for any other
-                     'traffic': 3.182e9 if (N == 10000 and args.storage == 'sym' and args.defer == 8 and k == 8 and world == 1) else None,
+                     # of exactly this configuration (profiles/ncu_downdate_r01_final_rank16_raw.csv: 1.629 GB read + 1.551 GB written); null for any other
+                     'traffic': 3.181e9 if (N == 10000 and args.storage == 'sym' and args.defer == 8 and k == 8 and world == 1) else None,
                      'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,
                      'share_of_step': dd_ms / ms},
         'exchange': ({'avg_ms': xch_ms / max(xch_n, 1), 'per_step': xch_n / K, 'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if xch_p2p else 'NCCL'} if world > 1 else None),
@@ -542,8 +544,8 @@ def run_mc(args):
                      'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
                      'frac_of_8TBps_nominal': achieved / 8000.0,
-                     # from profiles/ncu_mcflush_r01_raw.csv (this configuration only): 3.044 GB read + 2.643 GB written
-                     'traffic': 5.687e9 if (N == 200 and k == 5 and args.filters == 4096 and args.storage == 'sym' and world == 1) else None,
+                     # from profiles/ncu_mcflush_r01_final_raw.csv (this configuration only): 3.044 GB read + 2.642 GB written
+                     'traffic': 5.686e9 if (N == 200 and k == 5 and args.filters == 4096 and args.storage == 'sym' and world == 1) else None,
                      'algorithmic_bytes_per_launch': dd_bytes,
                      'avg_launch_ms': flush_avg_ms, 'launches': kern_n, 'share_of_step': flush_avg_ms * K / ms,
                      'front_kernel_avg_ms': kern_avg_ms - flush_avg_ms},

@@ -46,7 +46,7 @@ struct ekf_handle {
     struct QObs { double z0, z1, R0, R1; int a; };
     std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
-    // ---- decoupled state chain (single-GPU handles; EKF_ASYNC_X=0 disables) ----
+    // ---- decoupled state chain (EKF_ASYNC_X=0 disables) ----
     // x, s and the mode-A association do not depend on the O(n^2) flush of P, so the state half of predict, the batched
     // signature association and the x read-back run on a side stream `sx`, ordered against the handle's stream by two
     // events: ev_mx = "every kernel enqueued so far on the main stream that reads or writes x / s", ev_pp = "the covariance
@@ -335,7 +335,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMallocHost(&h->h_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
         {
             const char* ax = getenv("EKF_ASYNC_X");
-            h->async_x = world == 1 && !(ax && atoi(ax) == 0);
+            h->async_x = !(ax && atoi(ax) == 0);
         }
         if (h->async_x) {
             // highest priority: its tiny kernels must be scheduled at once beside a flush that still has ~20 waves of
@@ -403,9 +403,7 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     if (!u) return fail(h, EKF_EINVAL, "u is null");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
-    if (h->world > 1)
-        launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
-    else if (h->async_x) {
+    if (h->async_x) {
         // state half first, on the side stream, as soon as the last writer of x is done (not the flush behind it);
         // covariance half on the main stream with the heading the state half saved (EKF_SLAM.m:42,63-64 use theta before f())
         CK(cudaStreamWaitEvent(h->sx, h->ev_mx, 0));
@@ -413,10 +411,15 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         launch_predict_x_save(h->sx, h->x, u[0], u[1], h->xprev);
         CK(cudaEventRecord(h->ev_px, h->sx));
         CK(cudaStreamWaitEvent(h->stream, h->ev_px, 0));
-        launch_predict_P(h->stream, h->P, h->ld, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+        if (h->world > 1)
+            launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+        else
+            launch_predict_P(h->stream, h->P, h->ld, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
         CK(cudaGetLastError());
         CK(cudaEventRecord(h->ev_pp, h->stream));   // NOT ev_mx: a reader of x must not wait for this kernel (it sits behind the flush)
-    } else
+    } else if (h->world > 1)
+        launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+    else
         launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     h->launches += 2;
     CK(cudaGetLastError());
@@ -520,6 +523,7 @@ static int32_t flush_sharded(ekf_handle* h) {
         h->launches += 2 * k;
     }
     CK(cudaGetLastError());
+    MARK_X(h);                              // x of the batch is final here, before the slab flush
     const int ncl = ncols_loc(h);
     if (ncl > 0) {
         int32_t rc = prof_begin(h);

@@ -52,6 +52,8 @@ void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int 
                            int64_t ldc, Lin* lin, double2* Kall, double2* Ball, int64_t lds, double2* Bc, int m, int sym);
 void launch_predict_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, double u1,
                           double u2, double C, int sym);
+void launch_predict_shard_P(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, const double* xprev, int n,
+                            double u1, double u2, double C, int sym);   // covariance half of the decoupled predict
 void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, double* s, int N,
                          double u1, double u2, double R0, double R1, double px, double py, double sig, const double* Pc,
                          int64_t ldc);

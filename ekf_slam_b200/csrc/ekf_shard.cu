@@ -300,6 +300,12 @@ void launch_predict_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, i
     launch_predict_x(st, x, u1, u2);
 }
 
+// covariance half alone (decoupled predict): the heading comes from the pre-motion pose the state half saved
+void launch_predict_shard_P(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, const double* xprev, int n,
+                            double u1, double u2, double C, int sym) {
+    k_predict_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, xprev, n, u1, u2, C, sym);
+}
+
 void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, double* s, int N,
                          double u1, double u2, double R0, double R1, double px, double py, double sig, const double* Pc,
                          int64_t ldc) {
