@@ -628,12 +628,17 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
     if (h->world > 1 && h->p.assoc_mode == EKF_ASSOC_POSITION)
         return fail(h, EKF_EINVAL, "ekf_associate: position-cost association is not available on a sharded filter");
     if (h->p.assoc_mode == EKF_ASSOC_POSITION) FLUSH(h);      // mode B reads P blocks; mode A only s
-    launch_associate(h->stream, h->P, h->ld, h->x, h->s, h->N, z[0], z[1], z[2], Rdiag[0], Rdiag[1],
+    cudaStream_t st = h->stream;
+    if (h->async_x && h->p.assoc_mode == EKF_ASSOC_SIGNATURE) {   // mode A: behind the last writer of s, not behind a flush
+        st = h->sx;
+        CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
+    }
+    launch_associate(st, h->P, h->ld, h->x, h->s, h->N, z[0], z[1], z[2], Rdiag[0], Rdiag[1],
                      h->p.s_cost, h->p.s_thresh, h->p.assoc_mode, sym_of(h), h->partial, h->ticket, h->d_res);
     h->launches += 1;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     *newLL = h->h_res->newLL;
     *idx1 = h->h_res->index1;
     return EKF_OK;

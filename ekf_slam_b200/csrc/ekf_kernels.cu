@@ -8,6 +8,7 @@
 #include "ekf_device.cuh"
 #include <math_constants.h>
 #include <limits.h>
+#include <cstdlib>
 
 namespace ekf {
 
@@ -1024,7 +1025,9 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            int c_lo, int c_hi) {
     if (!Pc) { c_lo = 0; c_hi = n; }
     k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc);   // >= EKF_BATCH_SLOTS^2 = 361 threads
-    k_batch_gain<<<cdiv(n, 128), 128, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi);
+    static int gb = 0;                     // rows per CTA of the gain kernel (EKF_GAIN_BLOCK = 32 | 64 | 128, default 128)
+    if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi);
 }
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>

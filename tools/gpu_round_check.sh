@@ -37,6 +37,12 @@ EKF_MC_TC=128 timeout 200 python bench.py --workload mc --no-cpu-baseline --step
 lap "bench mc, EKF_MC_TC=32"
 EKF_MC_TC=32 timeout 200 python bench.py --workload mc --no-cpu-baseline --steps 100 > $O/bench_mc_tc32.json 2> $O/bench_mc_tc32.err
 
+lap "10k other configurations (parity-test cases, short runs)"
+EKF_GAIN_BLOCK=64 timeout 200 python bench.py --no-cpu-baseline > $O/bench_10k_gain64.json 2> $O/bench_10k_gain64.err
+EKF_GAIN_BLOCK=32 timeout 200 python bench.py --no-cpu-baseline > $O/bench_10k_gain32.json 2> $O/bench_10k_gain32.err
+timeout 200 python bench.py --no-cpu-baseline --storage full --steps 100 > $O/bench_10k_full.json 2> $O/bench_10k_full.err
+timeout 200 python bench.py --no-cpu-baseline --defer 1 --steps 40 > $O/bench_10k_defer1.json 2> $O/bench_10k_defer1.err
+timeout 200 python bench.py --no-cpu-baseline --landmarks 1000 > $O/bench_1k.json 2> $O/bench_1k.err
 lap "ncu launch list 10k"
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches_10k.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_10k.log 2>&1
@@ -44,7 +50,7 @@ lap "ncu launch list mc"
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/launches_mc.csv \
     python bench.py --workload mc --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_mc.log 2>&1
 lap "done"
-for f in bench_10k bench_10k_sync bench_mc bench_mc_100 bench_mc_late bench_mc_tc128 bench_mc_tc32; do
+for f in bench_10k bench_10k_sync bench_10k_gain64 bench_10k_gain32 bench_10k_full bench_10k_defer1 bench_1k bench_mc bench_mc_100 bench_mc_late bench_mc_tc128 bench_mc_tc32; do
     python - "$O/$f.json" <<'EOF'
 import json, sys
 try:
