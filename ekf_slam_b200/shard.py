@@ -1,5 +1,6 @@
 """Host plumbing for the column-slab sharded filter: one process per GPU (torchrun), torch.distributed only
-carries the 128-byte NCCL id; the data path (column broadcasts) is NCCL inside libekfslam_b200.so."""
+carries the 128-byte NCCL id; the data path (exchange of the <= 19 slot columns per batch) is a peer-memory scatter
+over NVLink inside libekfslam_b200.so, NCCL collectives as the fallback (EKF_SHARD_EXCHANGE=nccl)."""
 import ctypes as ct
 
 import numpy as np

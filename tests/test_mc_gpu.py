@@ -154,3 +154,52 @@ def test_poses_readback_early_and_late(early, fused, monkeypatch):
     assert e.value.code == -2
     b.sync()                                             # error word was cleared
     b.close()
+
+
+@pytest.mark.parametrize('storage', ['sym', 'full'])
+def test_config5_full_size_4096_filters_x_200_landmarks(storage):
+    """BASELINE config 5 at full size: 4096 independent EKF_SLAM_UC filters x 200 landmarks (n = 403), the populated
+    synthetic map of the bench, 3 steps of predict + 5 associated updates per filter.  Sampled filters (first, last and
+    three in between) against the dense-literal oracle stepping the same inputs: actions identical, x and P <= 1e-9
+    relative.  Size-independent properties over ALL filters: the last filter is fed filter 0's inputs and must end
+    bit-identical to it (no cross-filter interference anywhere in the batch), every filter keeps its 200 landmarks,
+    every pose is finite, and poses() agrees with x(1:3) read filter by filter."""
+    import ekf_slam_b200 as E
+    from bench import make_mc_inputs
+    from oracle import dense_literal as O
+    from tests.golden_util import Stub
+    from types import SimpleNamespace
+    nf, N, k, T = 4096, 200, 5, 3
+    x, P, s, lms, U, OBS, loc, idx = make_mc_inputs(N, k, nf, T)
+    U[:, nf - 1] = U[:, 0]
+    OBS[:, nf - 1] = OBS[:, 0]
+    counts = np.full(nf, k, dtype=np.int32)
+    ntab = np.array([N], dtype=np.int32)
+    b = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=N, max_obs=k, max_table=N, storage=storage, defer_m=8)
+    b.set_state_all(x, P, s)
+    acts = []
+    for t in range(T):
+        a = b.step(np.ascontiguousarray(U[t]), packed=(np.ascontiguousarray(OBS[t]), counts, loc, idx, ntab, True),
+                   want_actions=True)
+        acts.append(a.copy())
+    poses = b.poses()
+    b.sync()
+    assert np.all(b.n_landmarks() == N) and np.all(np.isfinite(poses))
+    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
+    worst = [0.0, 0.0]
+    for f in (0, 1, 1234, 2777, nf - 2):
+        o = O.EKF_SLAM_UC()
+        o.x, o.P, o.s = x.copy(), P.copy(), list(s)
+        for t in range(T):
+            o.predict(U[t, f]); o.measure(None, U[t, f], Stub(OBS[t, f].T.copy(), table))
+        got = [('update', int(v)) for t in range(T) for v in acts[t][f, :k]]
+        assert got == o.chosen, 'filter %d: actions differ' % f
+        v = b[f]
+        ex, eP = _rel(v.x, o.x), _rel(v.P, o.P)
+        worst = [max(worst[0], ex), max(worst[1], eP)]
+        assert ex <= TOL and eP <= TOL, (f, ex, eP)
+        assert np.array_equal(poses[f], v.x[:3])
+    first, last = b[0], b[nf - 1]
+    assert np.array_equal(first.x, last.x) and np.array_equal(first.P, last.P)
+    print('4096 x 200 %s: sampled filters vs oracle, worst rel err x %.2e P %.2e' % (storage, worst[0], worst[1]))
+    b.close()
