@@ -57,7 +57,13 @@ struct ekf_handle {
     cudaStream_t sx = nullptr;
     cudaEvent_t ev_mx = nullptr, ev_px = nullptr, ev_pp = nullptr;
     double* xprev = nullptr;   // pre-motion pose saved by the state half of predict for the covariance half
-    int defer = 1;             // flush when m_pend reaches this (1 = immediate)
+    int defer = 1;             // flush when m_pend reaches this (1 = immediate); also the chunk size of the fused batch (<= 8)
+    // cross-step deferral (single GPU, defer_m = 9..EKF_MAX_PEND): terms stay pending across measure() and predict();
+    // the flush runs when the next chunk would not fit (or at a getter / append / mode-B association).  predict then
+    // transforms the pending slabs (K_q <- F K_q, B_q <- B_q F') instead of flushing.  Not bit-identical to the immediate
+    // path (F is applied to P0 and to the terms separately), but the same estimator to rounding: parity <= 1e-9.
+    int pend_cap = 1;          // = defer unless cross-step
+    bool xstep = false;
     int dd_variant = -1;       // downdate kernel variant (-1 = library default; EKF_DOWNDATE_VARIANT env at create)
     Lin* lin = nullptr;
     BatchLin* blin = nullptr;  // scratch of the fused batch linearisation (ekf_update_batch)
@@ -227,8 +233,8 @@ static int32_t init_state(ekf_handle* h) {
     CK(cudaMemsetAsync(h->P, 0, sizeof(double) * h->ld * (h->c_hi - h->c_lo), h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemsetAsync(h->s, 0, sizeof(double) * (h->p.capacity_landmarks + 1), h->stream));
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
-    CK(cudaMemsetAsync(h->Bd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
+    CK(cudaMemsetAsync(h->Bd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
     const double d = 0.1;
     for (int i = 0; i < 3 && h->rank == 0; ++i)
         CK(cudaMemcpyAsync(h->P + i + i * h->ld, &d, sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -299,6 +305,11 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
     h->rank = rank;
     h->world = world;
     h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
+    h->pend_cap = h->defer;
+    if (world == 1 && p->defer_m > EKF_MAX_DEFER) {
+        h->pend_cap = p->defer_m > EKF_MAX_PEND ? EKF_MAX_PEND : p->defer_m;
+        h->xstep = true;
+    }
     if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) h->dd_variant = atoi(v);
     int32_t rc = [&]() -> int32_t {
         CK(cudaSetDevice(p->device));
@@ -324,8 +335,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
-        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
-        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_DEFER));
+        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_PEND));
+        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_PEND));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->blin, sizeof(BatchLin)));
         CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
@@ -402,7 +413,7 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     CKH(h);
     if (!u) return fail(h, EKF_EINVAL, "u is null");
     CK(cudaSetDevice(h->p.device));
-    FLUSH(h);
+    if (!h->xstep) FLUSH(h);                 // cross-step deferral keeps the terms pending and transforms them below
     if (h->async_x) {
         // state half first, on the side stream, as soon as the last writer of x is done (not the flush behind it);
         // covariance half on the main stream with the heading the state half saved (EKF_SLAM.m:42,63-64 use theta before f())
@@ -415,11 +426,17 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
             launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
         else
             launch_predict_P(h->stream, h->P, h->ld, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+        if (h->xstep && h->m_pend > 0) { launch_predict_slabs(h->stream, h->Kd, h->Bd, h->ld, h->m_pend, h->xprev, u[0]); h->launches += 1; }
         CK(cudaGetLastError());
         CK(cudaEventRecord(h->ev_pp, h->stream));   // NOT ev_mx: a reader of x must not wait for this kernel (it sits behind the flush)
     } else if (h->world > 1)
         launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
-    else
+    else if (h->xstep && h->m_pend > 0) {    // single stream: covariance half, slab transform, then the state half (all see the pre-motion heading)
+        launch_predict_P(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+        launch_predict_slabs(h->stream, h->Kd, h->Bd, h->ld, h->m_pend, h->x, u[0]);
+        launch_predict_x(h->stream, h->x, u[0], u[1]);
+        h->launches += 1;
+    } else
         launch_predict(h->stream, h->P, h->ld, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     h->launches += 2;
     CK(cudaGetLastError());
@@ -590,7 +607,7 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     CK(cudaGetLastError());
     MARK_X(h);
     h->m_pend += 1;
-    if (h->m_pend >= h->defer) FLUSH(h);
+    if (h->m_pend >= h->pend_cap) FLUSH(h);
     return EKF_OK;
 }
 
@@ -656,21 +673,24 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
         for (int j = 0; j < k; ++j)
             if (idx1[j] < 1 || idx1[j] > h->N)
                 return fail(h, EKF_EINVAL, "ekf_update_batch: landmark index " + std::to_string(idx1[j]) + " outside 1.." + std::to_string(h->N));
-        FLUSH(h);
+        if (!h->xstep) FLUSH(h);
         while (k - i >= 2) {
             BatchObs ob;
             ob.k = std::min(k - i, std::min(h->defer, EKF_BATCH_MAX));
+            if (h->xstep && h->m_pend + ob.k > h->pend_cap) FLUSH(h);       // make room: one pass over P for everything pending
             for (int q = 0; q < ob.k; ++q) {
                 ob.z0[q] = z[i + q]; ob.z1[q] = z[i + q + k];
                 ob.R0[q] = Rdiag[i + q]; ob.R1[q] = Rdiag[i + q + k];
                 ob.a[q] = 3 + 2 * (idx1[i + q] - 1);
             }
-            launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld);
+            const int m0 = h->xstep ? h->m_pend : 0;
+            launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
+                                  nullptr, 0, 0, 0, m0);
             h->launches += 2;
             CK(cudaGetLastError());
             MARK_X(h);                      // x is final for this chunk here, before the flush
-            h->m_pend = ob.k;
-            FLUSH(h);
+            h->m_pend = m0 + ob.k;
+            if (!h->xstep || h->m_pend >= h->pend_cap) FLUSH(h);
             i += ob.k;
         }
     }
@@ -679,7 +699,7 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
         int32_t rc = ekf_update(h, zi, Ri, idx1[i]);
         if (rc != EKF_OK) return rc;
     }
-    return flush(h);
+    return h->xstep ? EKF_OK : flush(h);
 }
 
 // measure() control flow, EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151 (host-driven in this revision).
@@ -787,7 +807,7 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
         int32_t rc = drain();
         if (rc != EKF_OK) return rc;
     }
-    return flush(h);                                                       // P is whole again when measure() returns
+    return h->xstep ? EKF_OK : flush(h);                                   // P is whole again when measure() returns (cross-step deferral: at the next getter)
 }
 
 // ---------------------------------------------------------------- state access
@@ -875,7 +895,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     if (!x || !P || lda < n || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state: bad argument");
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
@@ -905,7 +925,7 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     CK(cudaMalloc(&dd, sizeof(double) * n));
     CK(cudaMemcpyAsync(dA, A, sizeof(double) * (size_t)n * r, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(dd, d, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_DEFER, h->stream));
+    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));

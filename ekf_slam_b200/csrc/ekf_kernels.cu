@@ -62,6 +62,26 @@ __global__ void k_predict_x(double* __restrict__ x, double u1, double u2, double
     x[2] = wrapTo360(th + u2);
 }
 
+// predict while m rank-2 terms are pending (cross-step deferral): the covariance is P0 - sum_q K_q B_q, so
+// F (.) F' + Q applies to P0 through k_predict_P and to the terms as K_q <- F K_q, B_q <- B_q F'.  F = I + a e1 e3' +
+// b e2 e3' touches rows 0, 1 of K_q and columns 0, 1 of B_q only (slab rows 0, 1; both components).  xpre = pose
+// BEFORE the motion step (EKF_SLAM.m:63-64).  Thread = (q, K or B).
+__global__ void k_predict_slabs(double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds, int m,
+                                const double* __restrict__ xpre, double u1) {
+    const int t = threadIdx.x;
+    if (t >= 2 * m) return;
+    const double th = xpre[2];
+    const double a = -1.0 * u1 * sind(th), b = u1 * cosd(th);
+    double2* S = (t & 1 ? Ball : Kall) + (int64_t)(t >> 1) * lds;
+    const double2 v0 = S[0], v1 = S[1], v2 = S[2];
+    S[0] = make_double2(v0.x + a * v2.x, v0.y + a * v2.y);
+    S[1] = make_double2(v1.x + b * v2.x, v1.y + b * v2.y);
+}
+
+void launch_predict_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int m, const double* xpre, double u1) {
+    if (m > 0) k_predict_slabs<<<1, 32, 0, st>>>(Kall, Ball, lds, m, xpre, u1);
+}
+
 // ------------------------------------------------------------------ K2 linearize + gain
 // Both kernels read the CURRENT covariance = P0 - (m pending rank-2 terms) through ldP_def, so they serve the
 // immediate path (m = 0) and the deferred path alike, and write K, B of this observation into slab slot m.
@@ -149,7 +169,8 @@ struct GSel {
 };
 
 __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
-                            BatchObs ob, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc) {
+                            BatchObs ob, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc,
+                            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0) {
     __shared__ double G[EKF_BATCH_SLOTS][EKF_BATCH_SLOTS + 1];
     __shared__ double xs[EKF_BATCH_SLOTS];
     __shared__ double2 Ks[EKF_BATCH_SLOTS], Bs[EKF_BATCH_SLOTS];
@@ -166,7 +187,8 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
     __syncthreads();
     const int gi = tid / ns, gj = tid - gi * ns;                   // this thread's entry of G (tid < ns * ns <= 361)
     const bool gown = tid < ns * ns;
-    if (gown) G[gi][gj] = Pc ? Pc[(int64_t)gj * ldc + col[gi]] : ldP(P, ld, col[gi], col[gj], sym);   // nothing is pending at batch start
+    // m0 = 0: nothing is pending at batch start; m0 > 0 (cross-step deferral): current = stored - the pending terms
+    if (gown) G[gi][gj] = Pc ? Pc[(int64_t)gj * ldc + col[gi]] : ldP_def(P, ld, col[gi], col[gj], sym, Kall, Ball, lds, m0);
     if (tid < ns) xs[tid] = x[col[tid]];
     const bool gup = gown && (!sym || col[gi] <= col[gj]);         // SYM: the live element is (min, max)
     __syncthreads();
@@ -226,7 +248,7 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
 __global__ void __launch_bounds__(128)
 k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, BatchObs ob,
              const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
-             const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi) {
+             const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi, int m0) {
     __shared__ BatchLin L;
     for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
         ((double*)&L)[e] = ((const double*)lin)[e];
@@ -243,8 +265,9 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
         if (s < ns) {
             const int c = s < 3 ? s : ob.a[(s - 3) >> 1] + ((s - 3) & 1);
             own[s] = !sym || i <= c;
-            pc[s] = Pc ? Pc[(int64_t)s * ldc + i] : ldP(P, ld, i, c, sym);
-            if (!sym && mine) pr[s] = P[(int64_t)c + (int64_t)(i - c_lo) * ld];    // row c of the (local) column i
+            pc[s] = Pc ? Pc[(int64_t)s * ldc + i] : ldP_def(P, ld, i, c, sym, Kall, Ball, lds, m0);
+            if (!sym && mine) pr[s] = Pc ? P[(int64_t)c + (int64_t)(i - c_lo) * ld]      // row c of the (local) column i
+                                         : ldP_def(P, ld, c, i, 0, Kall, Ball, lds, m0);
         }
     }
     double xi = x[i];
@@ -263,8 +286,8 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
             gain_from_ph(ph0, ph1, L.Sinv[q], L.nu[q], k0, k1, dx);
             xi = __dadd_rn(xi, dx);
             const double2 Ki = make_double2(k0, k1), Bi = make_double2(b0, b1);
-            Kall[q * lds + i] = Ki;
-            if (sym || mine) Ball[q * lds + i] = Bi;               // FULL slabs: B_q(:, i) only where column i lives
+            Kall[(m0 + q) * lds + i] = Ki;
+            if (sym || mine) Ball[(m0 + q) * lds + i] = Bi;        // FULL slabs: B_q(:, i) only where column i lives
 #pragma unroll
             for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
                 if (s < ns) {
@@ -1022,12 +1045,12 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc, int64_t ldc,
-                           int c_lo, int c_hi) {
+                           int c_lo, int c_hi, int m0) {
     if (!Pc) { c_lo = 0; c_hi = n; }
-    k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc);   // >= EKF_BATCH_SLOTS^2 = 361 threads
+    k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc, Kall, Ball, lds, m0);   // >= EKF_BATCH_SLOTS^2 = 361 threads
     static int gb = 0;                     // rows per CTA of the gain kernel (EKF_GAIN_BLOCK = 32 | 64 | 128, default 128)
     if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
-    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi);
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0);
 }
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
@@ -1046,6 +1069,15 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
     //   m == 1: 64 x 16-col stages, 2 consumer sets (v18)   m = 2..4: 64-col tiles, 6 x 8-col stages (v17)
     //   m >= 5: 128-col tiles, 4 x 8-col stages, 4 CTAs/SM (v13)
     const int v = variant >= 0 ? variant : (m == 1 ? 18 : (m <= 4 ? 17 : 13));
+    if (m > 8) {            // cross-step deferral (9..16 pending terms): rank <= 32 flush, 128-col tiles, 4 x 8-col stages
+        switch ((m + 1) / 2) {
+            case 5: launch_dd_tma<5, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            case 6: launch_dd_tma<6, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            case 7: launch_dd_tma<7, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            default: launch_dd_tma<8, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+        }
+        return;
+    }
     if (m >= 1 && v >= 8) {
         const int ks = (m + 1) / 2;
 #define DT(KS_) \

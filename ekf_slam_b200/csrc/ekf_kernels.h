@@ -12,6 +12,7 @@ struct BatchLin;
 
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym);
 #define EKF_MAX_DEFER 8
+#define EKF_MAX_PEND 16                             // single-GPU handles: rank-2 terms that may stay pending across predict (defer_m = 9..16)
 #define EKF_MAX_SLOTS (3 + 2 * EKF_MAX_DEFER)      // columns exchanged per sharded batch: robot + 2 per observation
 struct SlotSet { int n; int col[EKF_MAX_SLOTS]; }; // global column index of each slot (passed by value)
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
@@ -23,7 +24,9 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
 // Pc != null (sharded): slot columns come from the exchanged Pc[slot][0..n), P is the local slab of columns [c_lo, c_hi)
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc = nullptr,
-                           int64_t ldc = 0, int c_lo = 0, int c_hi = 0);
+                           int64_t ldc = 0, int c_lo = 0, int c_hi = 0, int m0 = 0);   // m0: terms already pending in slabs 0..m0-1; this batch fills m0..m0+k-1
+// predict with m pending terms: P0 takes F . F' + Q as usual, the slabs take K_q <- F K_q, B_q <- B_q F' (rows / columns 0, 1 only)
+void launch_predict_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int m, const double* xpre, double u1);
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym);
 #define EKF_ASSOC_BATCH 32

@@ -399,7 +399,7 @@ def _blocked_rel(Pg, Po, step=1024):
     return (num / den) ** 0.5
 
 
-@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 1)])
+@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 1), ('sym', 16)])
 def test_config3_10k_landmarks_vs_structured_oracle(storage, defer_m):
     """BASELINE config 3 at full size (N = 10 000, n = 20 003, P 3.2 GB): the populated synthetic map of the bench,
     2 steps of predict + 8 associated updates through the class API (EKF_SLAM_UC.measure: batched association, fused
@@ -454,7 +454,7 @@ def test_config3_10k_sampled_rows_vs_matrix_free_oracle(storage):
     g.close()
 
 
-@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 0), ('sym', 3)])
+@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 0), ('sym', 3), ('sym', 16), ('full', 13)])
 @pytest.mark.parametrize('variant', ['known', 'uc'])
 def test_decoupled_state_chain_is_bit_identical(variant, storage, defer_m, monkeypatch):
     """EKF_ASYNC_X (default on): the state half of predict, the batched signature association and the x read-back run
@@ -521,3 +521,53 @@ def test_decoupled_state_chain_large_map_overlaps_the_flush(monkeypatch):
     assert a[1] == b[1] and len(a[1]) == T * k
     assert all(np.array_equal(p, q) for p, q in zip(a[0], b[0])), 'x differs somewhere in the loop'
     assert all(np.array_equal(p, q) for p, q in zip(a[2], b[2])), 'P differs'
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+@pytest.mark.parametrize('defer_m', [16, 11])
+@pytest.mark.parametrize('variant,mode,T', [('known', 'prefix', 1000), ('uc', 'nearest', 1000)])
+def test_cross_step_deferral_1000_steps_vs_oracle(variant, mode, T, defer_m, storage):
+    """defer_m = 9..16: rank-2 terms stay pending across measure() and predict() (predict transforms the pending slabs,
+    K_q <- F K_q, B_q <- B_q F', instead of flushing) and one rank-<=32 pass over P applies up to 16 observations.  Same
+    estimator, different rounding than the immediate path: the bar is the north star's (actions identical, x and P
+    <= 1e-9 relative over 1000 steps, checked every 100), P read back mid-run included (that read flushes)."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=20, T=T, k=5, mode=mode)
+    g = (E.EKF_SLAM if variant == 'known' else E.EKF_SLAM_UC)(capacity_landmarks=24, storage=storage, defer_m=defer_m)
+    o = (O.EKF_SLAM if variant == 'known' else O.EKF_SLAM_UC)()
+    worst = _run_pair(g, o, w)
+    print('cross-step defer %d %s/%s: worst rel err x %.2e P %.2e' % (defer_m, variant, storage, worst[0], worst[1]))
+    g.close()
+
+
+@pytest.mark.parametrize('storage', ['full', 'sym'])
+def test_cross_step_deferral_200_landmarks_ragged_batches(storage):
+    """200 landmarks, batches of 1..9 observations per step (chunks of every size meet every pending count), explicit
+    slots through update_batch and single updates mixed, against the dense-literal oracle."""
+    import ekf_slam_b200 as E
+    from bench import make_inputs
+    from ekf_slam_b200.synth import lowrank_to_dense
+    from oracle import dense_literal as O
+    N, T = 200, 40
+    x, A, d, s, lms, us, obs = make_inputs(N, 9, T)
+    g = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, defer_m=16)
+    g.set_state_lowrank(x, s, A, d)
+    o = O.EKF_SLAM_UC()
+    o.x, o.P, o.s = x.copy(), lowrank_to_dense(A, d), list(s)
+    for t in range(T):
+        g.predict(us[t]); o.predict(us[t])
+        rows = obs[t][:1 + (t * 5) % 9]
+        Rd = np.column_stack([rows[:, 0] * g.Rc[0], rows[:, 1] * g.Rc[1]])
+        if t % 4 == 3:
+            for r, rd in zip(rows, Rd):
+                g.update(r[:2], rd, int(r[2]))
+        else:
+            g.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+        for r, rd in zip(rows, Rd):
+            o._update(r, np.diag(rd), int(r[2]))
+        if t % 10 == 9:
+            assert _rel(g.x, o.x) <= TOL and _rel(g.P, o.P) <= TOL, t
+    assert _rel(g.x, o.x) <= TOL and _rel(g.P, o.P) <= TOL
+    g.close()
