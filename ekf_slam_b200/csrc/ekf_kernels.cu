@@ -1074,7 +1074,18 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
             case 5: launch_dd_tma<5, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             case 6: launch_dd_tma<6, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             case 7: launch_dd_tma<7, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
-            default: launch_dd_tma<8, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            default:
+                // 15/16 terms: tile shape selectable for sweeps (EKF_DOWNDATE_VARIANT); default = the rank-16 shape
+                if (variant == 9) launch_dd_tma<8, 128, 16, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 11) launch_dd_tma<8, 128, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 14) launch_dd_tma<8, 64, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 16) launch_dd_tma<8, 128, 16, 3, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 17) launch_dd_tma<8, 64, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 18) launch_dd_tma<8, 64, 16, 4, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 19) launch_dd_tma<8, 128, 8, 4, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 20) launch_dd_tma<8, 128, 8, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else launch_dd_tma<8, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                break;
         }
         return;
     }
