@@ -867,8 +867,8 @@ __device__ __forceinline__ void dd_tma_tile(double* __restrict__ P, int64_t ld, 
     }
 }
 
-template <int KS, int TC, int SCOLS, int NSTAGE, int CG>
-__global__ void __launch_bounds__((8 * CG + 1) * 32)
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG, int MINB = 1>
+__global__ void __launch_bounds__((8 * CG + 1) * 32, MINB)
 k_downdate_tma(double* __restrict__ P, int64_t ld, int n, int ncols, int sym,
                const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int M, TileMap tm) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
@@ -930,13 +930,13 @@ void launch_mc_flush_tma(cudaStream_t st, const McArgs& a, int n_filters, int ca
     }
 }
 
-template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1>
+template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1, int MINB = 1>
 static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                           const double2* Ball, int64_t lds, int M, int col_off) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaFuncSetAttribute(k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         attr_set = true;
     }
     static_assert(C::TR % TC == 0 && (C::TR / TC == 1 || C::TR / TC == 2), "tile map needs TR = TC or 2 TC");
@@ -948,7 +948,7 @@ static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int nco
       tm.order = !sym ? 0 : (ord == -2 ? (TC == 128 ? 1 : 0) : ord); }
     const long long live = tm_prefix(tm, CT);
     if (live <= 0 || live > 0x3fffffffLL) return;        // device decode is 32-bit
-    k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, tm);
+    k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG, MINB><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, tm);
 }
 
 // ------------------------------------------------------------------ state initialisation helpers
@@ -1071,9 +1071,11 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
     const int v = variant >= 0 ? variant : (m == 1 ? 18 : (m <= 4 ? 17 : 13));
     if (m > 8) {            // cross-step deferral (9..16 pending terms): rank <= 32 flush, 128-col tiles, 4 x 8-col stages
         switch ((m + 1) / 2) {
-            case 5: launch_dd_tma<5, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
-            case 6: launch_dd_tma<6, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
-            case 7: launch_dd_tma<7, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            // MINB = 3: 72 registers x 288 threads and 70 KB of shared memory both allow 3 CTAs/SM; without the bound the
+            // 8-k-step kernel takes 80 registers -> 2 CTAs/SM and the flush goes from 0.674 to 0.773 ms (profiles/README.md)
+            case 5: launch_dd_tma<5, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            case 6: launch_dd_tma<6, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
+            case 7: launch_dd_tma<7, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             default:
                 // 15/16 terms: tile shape selectable for sweeps (EKF_DOWNDATE_VARIANT); default = the rank-16 shape
                 if (variant == 9) launch_dd_tma<8, 128, 16, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
@@ -1082,9 +1084,12 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
                 else if (variant == 16) launch_dd_tma<8, 128, 16, 3, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 else if (variant == 17) launch_dd_tma<8, 64, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 else if (variant == 18) launch_dd_tma<8, 64, 16, 4, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 19) launch_dd_tma<8, 128, 8, 4, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 else if (variant == 20) launch_dd_tma<8, 128, 8, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else launch_dd_tma<8, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 21) launch_dd_tma<8, 64, 8, 4, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);   // 56 registers, 51.7 KB: 4 CTAs/SM
+                else if (variant == 22) launch_dd_tma<8, 64, 8, 3, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 23) launch_dd_tma<8, 64, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
+                else if (variant == 24) launch_dd_tma<8, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);   // unbounded: 80 registers, 2 CTAs/SM
+                else launch_dd_tma<8, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 break;
         }
         return;
