@@ -416,7 +416,8 @@ def main():
                      'frac_of_8TBps_nominal': achieved / 8000.0,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
                      # of exactly this configuration (profiles/ncu_downdate_r01_final_rank16_raw.csv: 1.629 GB read + 1.551 GB written); null for any other
-                     'traffic': 3.181e9 if (N == 10000 and args.storage == 'sym' and args.defer == 8 and k == 8 and world == 1) else None,
+                     # defer 16: profiles/ncu_downdate_r01_rank32_raw.csv (1.639 GB read + 1.551 GB written per rank-32 launch)
+                     'traffic': (3.181e9 if args.defer == 8 else 3.191e9 if args.defer == 16 else None) if (N == 10000 and args.storage == 'sym' and k == 8 and world == 1) else None,
                      'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,
                      'share_of_step': dd_ms / ms,
                      # fp64 tensor-core side of the same launch: 2 flop x rank per live element; measured DMMA peak 37.2 TFLOP/s

@@ -250,12 +250,21 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
              const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
              const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi, int m0) {
     __shared__ BatchLin L;
+    __shared__ double2 Kc[EKF_MAX_PEND][EKF_BATCH_SLOTS], Bc[EKF_MAX_PEND][EKF_BATCH_SLOTS];   // pending K_q(col_s,:), B_q(:,col_s)
     for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
         ((double*)&L)[e] = ((const double*)lin)[e];
+    const int k = ob.k, ns = 3 + 2 * k;
+    const bool pend = m0 > 0 && !Pc;                               // cross-step deferral: current = stored - pending terms
+    if (pend)
+        for (int e = threadIdx.x; e < m0 * ns; e += blockDim.x) {
+            const int q = e / ns, sl = e - q * ns;
+            const int c = sl < 3 ? sl : ob.a[(sl - 3) >> 1] + ((sl - 3) & 1);
+            Kc[q][sl] = Kall[q * lds + c];
+            Bc[q][sl] = Ball[q * lds + c];
+        }
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int k = ob.k, ns = 3 + 2 * k;
     const bool mine = i >= c_lo && i < c_hi;                       // column i of P is stored here (always, on one GPU)
     double pc[EKF_BATCH_SLOTS], pr[EKF_BATCH_SLOTS];               // current P(i, col_s) and (FULL) P(col_s, i)
     bool own[EKF_BATCH_SLOTS];                                     // SYM: element (i, col_s) is stored as (i, col_s), i <= col_s
@@ -265,9 +274,21 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
         if (s < ns) {
             const int c = s < 3 ? s : ob.a[(s - 3) >> 1] + ((s - 3) & 1);
             own[s] = !sym || i <= c;
-            pc[s] = Pc ? Pc[(int64_t)s * ldc + i] : ldP_def(P, ld, i, c, sym, Kall, Ball, lds, m0);
-            if (!sym && mine) pr[s] = Pc ? P[(int64_t)c + (int64_t)(i - c_lo) * ld]      // row c of the (local) column i
-                                         : ldP_def(P, ld, c, i, 0, Kall, Ball, lds, m0);
+            pc[s] = Pc ? Pc[(int64_t)s * ldc + i] : ldP(P, ld, i, c, sym);
+            if (!sym && mine) pr[s] = P[(int64_t)c + (int64_t)(i - c_lo) * ld];    // row c of the (local) column i
+        }
+    }
+    if (pend) {
+        // same terms, same order as ldP_def element by element; this row's K_q(i,:), B_q(:,i) are loaded once per term
+        for (int q = 0; q < m0; ++q) {
+            const double2 ki = Kall[q * lds + i], bi = Ball[q * lds + i];
+#pragma unroll
+            for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
+                if (s < ns) {
+                    pc[s] = own[s] ? rank2_sub(pc[s], ki, Bc[q][s]) : rank2_sub(pc[s], Kc[q][s], bi);
+                    if (!sym) pr[s] = rank2_sub(pr[s], Kc[q][s], bi);
+                }
+            }
         }
     }
     double xi = x[i];
