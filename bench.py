@@ -406,7 +406,7 @@ def main():
         'data': 'synthetic',
         'config': {'workload': '10k landmarks (P 20003^2 fp64), predict + %d updates per step' % k if N == 10000 else
                    '%d landmarks, predict + %d updates per step' % (N, k),
-                   'landmarks': N, 'k': k, 'storage': args.storage, 'n_state': n, 'defer_m': args.defer,
+                   'landmarks': N, 'k': k, 'storage': args.storage, 'n_state': n, 'defer_m': args.defer if world == 1 else min(args.defer, 8),   # sharded handles clamp to 8 (no cross-step deferral yet)
                    'downdate': ('one rank-%d pass over P per %d observations (terms stay pending across predict: %d steps per pass)' % (2 * per_pass, per_pass, per_pass // k) if per_pass > k else
                                 'one rank-%d pass over P per %d observations' % (2 * per_pass, per_pass)) if args.defer > 1 else 'one rank-2 pass over P per observation',
                    'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one exchange of the 3+2k current columns (peer-memory scatter, or NCCL %s with EKF_SHARD_EXCHANGE=nccl); slowest slab cols [%d,%d)' % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', slab[2], slab[3])) if world > 1 else 'single GPU',
