@@ -334,3 +334,38 @@ def test_matrix_free_oracle_matches_structured_on_a_materialised_map():
     assert G.rel(np.vstack([b.row(i) for i in rows]), P[rows, :]) <= 1e-11
     assert G.rel(np.column_stack([b.col(j) for j in rows]), P[:, rows]) <= 1e-11
     assert G.rel(b.block(rows, 100, 140), P[np.ix_(rows, range(100, 140))]) <= 1e-11
+
+
+def test_cross_step_deferral_identity_on_the_oracle():
+    """The algebra behind defer_m = 9..16 (DESIGN.md "Cross-step deferral"), checked on the dense oracle's own matrices:
+    with P = P0 - sum_q K_q B_q pending, predict gives F P F' + Q = (F P0 F' + Q) - sum_q (F K_q)(B_q F'), and F only
+    changes rows 0, 1 of K_q and columns 0, 1 of B_q (EKF_SLAM.m:47, :62-64)."""
+    from oracle import dense_literal as O
+    from oracle.matlab_compat import sind, cosd
+    rng = np.random.default_rng(3)
+    n, m = 23, 5
+    A = rng.standard_normal((n, n))
+    P0 = A @ A.T / n + np.eye(n)
+    Ks = [rng.standard_normal((n, 2)) * 0.1 for _ in range(m)]
+    Bs = [rng.standard_normal((2, n)) * 0.1 for _ in range(m)]
+    P = P0 - sum(K @ B for K, B in zip(Ks, Bs))
+    o = O.EKF_SLAM()
+    o.x = np.concatenate([[0.3, -0.2, 37.0], rng.standard_normal(n - 3)])
+    o.P = P.copy()
+    o.s = list(range(1, (n - 3) // 2 + 1))
+    u = np.array([0.4, 2.0])
+    th = o.x[2]
+    o.predict(u)                                                   # the reference's dense F P F' + Q
+    a, b = -1 * u[0] * sind(th), u[0] * cosd(th)
+    F = np.eye(n); F[0, 2] = a; F[1, 2] = b
+    W = np.array([[u[0] * cosd(th)], [u[0] * sind(th)], [u[1]]])
+    Q = np.zeros((n, n)); Q[:3, :3] = (W * 0.2) @ W.T
+    Kt, Bt = [], []
+    for K, B in zip(Ks, Bs):
+        K2, B2 = K.copy(), B.copy()
+        K2[0] += a * K[2]; K2[1] += b * K[2]                       # K_q <- F K_q
+        B2[:, 0] += a * B[:, 2]; B2[:, 1] += b * B[:, 2]           # B_q <- B_q F'
+        assert np.allclose(K2, F @ K, rtol=0, atol=1e-15) and np.allclose(B2, B @ F.T, rtol=0, atol=1e-15)
+        Kt.append(K2); Bt.append(B2)
+    P_deferred = (F @ P0 @ F.T + Q) - sum(K @ B for K, B in zip(Kt, Bt))
+    assert np.linalg.norm(P_deferred - o.P) / np.linalg.norm(o.P) < 1e-14

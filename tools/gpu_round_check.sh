@@ -25,7 +25,7 @@ fi
 lap "bench 10k (default)"
 timeout 400 python bench.py > $O/bench_10k.json 2> $O/bench_10k.err
 lap "bench 10k, EKF_ASYNC_X=0"
-EKF_ASYNC_X=0 timeout 200 python bench.py --no-cpu-baseline > $O/bench_10k_sync.json 2> $O/bench_10k_sync.err
+EKF_ASYNC_X=0 timeout 200 python bench.py --no-cpu-baseline --defer 8 > $O/bench_10k_sync.json 2> $O/bench_10k_sync.err
 lap "bench mc (default)"
 timeout 300 python bench.py --workload mc > $O/bench_mc.json 2> $O/bench_mc.err
 lap "bench mc, EKF_MC_EARLY_POSES=0"
@@ -38,9 +38,9 @@ lap "bench mc, EKF_MC_TC=32"
 EKF_MC_TC=32 timeout 200 python bench.py --workload mc --no-cpu-baseline --steps 100 > $O/bench_mc_tc32.json 2> $O/bench_mc_tc32.err
 
 lap "10k other configurations (parity-test cases, short runs)"
-EKF_GAIN_BLOCK=64 timeout 200 python bench.py --no-cpu-baseline > $O/bench_10k_gain64.json 2> $O/bench_10k_gain64.err
-EKF_GAIN_BLOCK=32 timeout 200 python bench.py --no-cpu-baseline > $O/bench_10k_gain32.json 2> $O/bench_10k_gain32.err
-timeout 200 python bench.py --no-cpu-baseline --storage full --steps 100 > $O/bench_10k_full.json 2> $O/bench_10k_full.err
+EKF_GAIN_BLOCK=64 timeout 200 python bench.py --no-cpu-baseline --defer 8 > $O/bench_10k_gain64.json 2> $O/bench_10k_gain64.err
+EKF_GAIN_BLOCK=32 timeout 200 python bench.py --no-cpu-baseline --defer 8 > $O/bench_10k_gain32.json 2> $O/bench_10k_gain32.err
+timeout 200 python bench.py --no-cpu-baseline --defer 8 --storage full --steps 100 > $O/bench_10k_full.json 2> $O/bench_10k_full.err
 timeout 200 python bench.py --no-cpu-baseline --defer 1 --steps 40 > $O/bench_10k_defer1.json 2> $O/bench_10k_defer1.err
 timeout 200 python bench.py --no-cpu-baseline --landmarks 1000 > $O/bench_1k.json 2> $O/bench_1k.err
 lap "ncu launch list 10k"
