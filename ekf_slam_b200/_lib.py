@@ -54,6 +54,9 @@ SIGNATURES = {
     'ekf_get_P_block': [_H, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _DP, C.c_int32],
     'ekf_get_ellipses': [_H, _DP, C.c_int32],
     'ekf_set_state': [_H, _DP, _DP, C.c_int32, _DP, C.c_int32],
+    'ekf_set_x': [_H, _DP, C.c_int32],
+    'ekf_set_P': [_H, _DP, C.c_int32],
+    'ekf_set_s': [_H, _DP, C.c_int32],
     'ekf_set_state_lowrank': [_H, _DP, _DP, C.c_int32, _DP, C.c_int32, _DP],
     'ekf_set_noise': [_H, C.c_double, _DP, C.c_double, C.c_double],
     'ekf_flush': [_H],

@@ -28,6 +28,7 @@ struct ekf_handle {
     double* s = nullptr;
     double2* Kd = nullptr;     // EKF_MAX_DEFER slabs of ld double2: gains K_q of the pending observations
     double2* Bd = nullptr;     // EKF_MAX_DEFER slabs: B_q = H_q P
+    double* Bt = nullptr;      // (local columns) x EKF_BT_SROW: column-major copy of the pending B slabs for the hybrid flush kernels
     // ---- column-slab sharding (world > 1): this rank stores columns [c_lo, c_hi) of P, FULL storage ----
     int rank = 0, world = 1;
     int c_lo = 0, c_hi = 0;
@@ -71,6 +72,11 @@ struct ekf_handle {
     unsigned int* ticket = nullptr;
     AssocResult* d_res = nullptr;
     AssocResult* h_res = nullptr;   // pinned
+    // sticky device->host status words in mapped pinned memory (kernels write them only when something is wrong; the host
+    // looks at them after every synchronisation): [0] non-finite innovation covariance, [1] peer exchange timed out
+    int* hflags = nullptr;
+    int* dflags = nullptr;     // device alias of hflags
+    long long xch_timeout = 0; // clock cycles k_wait_flags spins before it gives up (EKF_XCHG_TIMEOUT_MS, default 20 s)
     bool prof = false;
     std::vector<cudaEvent_t> ev;
     size_t ev_used = 0;
@@ -96,6 +102,19 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
 
 static int32_t flush(ekf_handle* h);
 #define FLUSH(h) do { int32_t rc__ = flush(h); if (rc__ != EKF_OK) return rc__; } while (0)
+
+// Called after every stream synchronisation: surface what the kernels flagged since the last one.
+static int32_t after_sync(ekf_handle* h) {
+    if (!h->hflags) return EKF_OK;
+    if (h->hflags[1])       // sticky: the handle is unusable once a peer stopped answering
+        return fail(h, EKF_ENCCL, "sharded exchange: a peer rank did not publish its columns in time (EKF_XCHG_TIMEOUT_MS)");
+    if (h->hflags[0]) {
+        h->hflags[0] = 0;   // reported once; x and P keep the non-finite values, as the reference's would
+        return fail(h, EKF_ENONFINITE, "non-finite innovation covariance in an update since the last synchronisation "
+                                       "(EKF_SLAM.m:137-143: q = 0 when the robot stands on the observed landmark); x and P are poisoned");
+    }
+    return EKF_OK;
+}
 
 static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing main-stream work that touches x / s
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->stream));
@@ -210,7 +229,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     cudaSetDevice(h->p.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
-    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd);
+    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd); cudaFree(h->Bt);
     for (int g = 0; g < h->world && h->p2p; ++g)
         if (g != h->rank) { if (h->peers.pc[g]) cudaIpcCloseMemHandle(h->peers.pc[g]); if (h->peers.flags[g]) cudaIpcCloseMemHandle(h->peers.flags[g]); }
     for (auto e : h->xev) cudaEventDestroy(e);
@@ -218,6 +237,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
+    if (h->hflags) cudaFreeHost(h->hflags);
     if (h->sx) { cudaStreamSynchronize(h->sx); cudaStreamDestroy(h->sx); }
     if (h->ev_mx) cudaEventDestroy(h->ev_mx);
     if (h->ev_px) cudaEventDestroy(h->ev_px);
@@ -337,8 +357,25 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
         CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_PEND));
         CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_PEND));
+        CK(cudaMalloc(&h->Bt, sizeof(double) * EKF_BT_SROW * ((size_t)(h->c_hi - h->c_lo) + 16)));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->blin, sizeof(BatchLin)));
+        CK(cudaMemset(h->lin, 0, sizeof(Lin)));
+        CK(cudaMemset(h->blin, 0, sizeof(BatchLin)));
+        CK(cudaHostAlloc(&h->hflags, 4 * sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+        memset(h->hflags, 0, 4 * sizeof(int));
+        {
+            int* dflags = nullptr;
+            CK(cudaHostGetDevicePointer(&dflags, h->hflags, 0));
+            h->dflags = dflags;
+            CK(cudaMemcpy(&h->lin->nf, &dflags, sizeof(int*), cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(&h->blin->nf, &dflags, sizeof(int*), cudaMemcpyHostToDevice));
+            int khz = 0;
+            CK(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, p->device));
+            const char* tv = getenv("EKF_XCHG_TIMEOUT_MS");
+            const double tms = tv ? atof(tv) : 20000.0;
+            h->xch_timeout = (long long)(tms * (double)(khz > 0 ? khz : 1965000));
+        }
         CK(cudaMalloc(&h->partial, 16 * (size_t)(assoc_blocks(p->capacity_landmarks) + 1)));
         CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
         CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
@@ -392,7 +429,7 @@ extern "C" int32_t ekf_sync(ekf_handle* h) {
     CKH(h);
     CK(cudaStreamSynchronize(h->stream));
     if (h->sx) CK(cudaStreamSynchronize(h->sx));
-    return EKF_OK;
+    return after_sync(h);
 }
 
 extern "C" int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N) {
@@ -479,7 +516,7 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
         h->epoch += 1;
         const int64_t buf_off = (int64_t)(h->epoch & 1) * EKF_MAX_SLOTS * h->ld;
         launch_scatter_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->peers, buf_off, sym, h->epoch, h->xticket,
-                            h->xflags);
+                            h->xflags, h->xch_timeout, h->dflags + 1);
         h->Pc_cur = h->Pc + buf_off;
         h->launches += 2;
         CK(cudaGetLastError());
@@ -545,7 +582,7 @@ static int32_t flush_sharded(ekf_handle* h) {
     if (ncl > 0) {
         int32_t rc = prof_begin(h);
         if (rc != EKF_OK) return rc;
-        launch_downdate(h->stream, h->P, h->ld, n, ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, k, h->c_lo, h->dd_variant);
+        launch_downdate(h->stream, h->P, h->ld, n, ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, k, h->c_lo, h->dd_variant, h->Bt);
         rc = prof_end(h);
         if (rc != EKF_OK) return rc;
         h->dd_launches += 1;
@@ -569,7 +606,7 @@ static int32_t flush(ekf_handle* h) {
         }
         CK(cudaEventRecord(h->ev[h->ev_used], h->stream));
     }
-    launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend, 0, h->dd_variant);
+    launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), sym_of(h), h->Kd, h->Bd, h->ld, h->m_pend, 0, h->dd_variant, h->Bt);
     if (h->prof) {
         CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
         h->ev_used += 2;
@@ -658,7 +695,7 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
     CK(cudaStreamSynchronize(st));
     *newLL = h->h_res->newLL;
     *idx1 = h->h_res->index1;
-    return EKF_OK;
+    return after_sync(h);
 }
 
 // k updates with explicit slots: the update branch of measure() (EKF_SLAM.m:124-145) for a batch whose
@@ -732,6 +769,13 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
         qz0.push_back(z[0]); qz1.push_back(z[1]); qr0.push_back(Rd[0]); qr1.push_back(Rd[1]); qidx.push_back(idx);
         return EKF_OK;
     };
+    // The reference applies every earlier row before MATLAB raises on a later one: an early error return first applies
+    // the updates queued so far, so that the state after a failed measure() equals "rows 1..ii-1 done" on every path.
+    auto bail = [&](int32_t code, const std::string& msg) -> int32_t {
+        drain();
+        if (!h->xstep) flush(h);
+        return fail(h, code, msg);
+    };
     // Mode-A associations of rows [from, k) against the current s, <= EKF_ASSOC_BATCH per launch + one D2H copy.
     const bool batch_assoc = h->p.variant == EKF_VARIANT_UC && h->p.assoc_mode == EKF_ASSOC_SIGNATURE;
     int assoc_from = 0, assoc_to = 0;                                      // h_res[j - assoc_from] valid for j in [from, to)
@@ -762,13 +806,13 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
             bool ok = false;                                               // find([..index]) -> first non-zero index (F15)
             for (int i = 0; i < n_table && !ok; ++i)
                 if (index_table[i] != 0) { pos[0] = loc_table[i]; pos[1] = loc_table[i + n_table]; ok = true; }
-            if (!ok) return fail(h, EKF_EINVAL, "measure: no indexed landmark in the table (EKF_SLAM.m:111)");
+            if (!ok) return bail(EKF_EINVAL, "measure: no indexed landmark in the table (EKF_SLAM.m:111)");
             rc = ekf_append(h, u, Rd, pos, 1.0);                           // :111
             assoc_to = 0;                                                  // s changed
             act = -1;
         } else if (h->p.variant == EKF_VARIANT_KNOWN) {
             if (z[2] > (double)h->N) {                                     // :118
-                if (!loc_by_index(z[2], pos)) return fail(h, EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM.m:120)");
+                if (!loc_by_index(z[2], pos)) return bail(EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM.m:120)");
                 if ((rc = drain()) != EKF_OK) return rc;
                 rc = ekf_append(h, u, Rd, pos, z[2]);                      // :120
                 act = -(int32_t)z[2];
@@ -790,7 +834,7 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
                 if (rc != EKF_OK) return rc;
             }
             if (newLL) {                                                   // :121
-                if (!loc_by_index((double)idx, pos)) return fail(h, EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM_UC.m:123)");
+                if (!loc_by_index((double)idx, pos)) return bail(EKF_EINVAL, "measure: landmark index not in table (EKF_SLAM_UC.m:123)");
                 if ((rc = drain()) != EKF_OK) return rc;
                 rc = ekf_append(h, u, Rd, pos, (double)idx);               // :123
                 assoc_to = 0;                                              // s changed: later rows are re-associated
@@ -800,7 +844,13 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
                 act = idx;
             }
         }
-        if (rc != EKF_OK) return rc;
+        if (rc != EKF_OK) {                                                // rows before this one are applied, like the reference
+            const std::string msg = h->err;
+            drain();
+            if (!h->xstep) flush(h);
+            h->err = msg;
+            return rc;
+        }
         if (action_out) action_out[ii - 1] = act;
     }
     {
@@ -823,7 +873,7 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     }
     CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    return EKF_OK;
+    return after_sync(h);
 }
 
 extern "C" int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len) {
@@ -833,7 +883,7 @@ extern "C" int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len) {
     CK(cudaSetDevice(h->p.device));
     CK(cudaMemcpyAsync(s, h->s, sizeof(double) * h->N, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    return EKF_OK;
+    return after_sync(h);
 }
 
 extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
@@ -847,7 +897,7 @@ extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
     CK(cudaMemcpy2DAsync(P, sizeof(double) * lda, h->P, sizeof(double) * h->ld, sizeof(double) * n, n,
                          cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    return EKF_OK;
+    return after_sync(h);
 }
 
 extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_t nr, int32_t nc, double* out,
@@ -865,7 +915,7 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
     CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, h->P + r0 + (int64_t)(c0 - h->c_lo) * h->ld, sizeof(double) * h->ld,
                          sizeof(double) * nr, nc, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    return EKF_OK;
+    return after_sync(h);
 }
 
 // Headless stand-in for the ellipse part of plot() (EKF_SLAM.m:180-229): numbers instead of figure calls.
@@ -884,7 +934,7 @@ extern "C" int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo) {
     CK(cudaMemcpy2DAsync(out, sizeof(double) * ldo, d, sizeof(double) * nb, sizeof(double) * nb, 5, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaFreeAsync(d, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    return EKF_OK;
+    return after_sync(h);
 }
 
 extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t lda, const double* s,
@@ -909,6 +959,51 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     MARK_X(h);
     h->q.clear();
     h->N = N;
+    if (h->hflags) h->hflags[0] = 0;
+    return EKF_OK;
+}
+
+// Property writes h.x = v / h.P = M / h.s = v of the reference classes (public read/write, EKF_SLAM.m:6-9): one of the three
+// at the current number of landmarks, the other two untouched.  Pending rank-2 terms are applied first (they belong to
+// the old P); x and s are final as soon as their last kernel has run.
+extern "C" int32_t ekf_set_x(ekf_handle* h, const double* x, int32_t len) {
+    CKH(h);
+    if (!x || len != n_of(h)) return fail(h, EKF_EINVAL, "ekf_set_x: expected " + std::to_string(n_of(h)) + " elements (3 + 2 N); use ekf_set_state to change the number of landmarks");
+    CK(cudaSetDevice(h->p.device));
+    FLUSH(h);                             // sharded handles: queued observations still have to read the old x
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->sx) CK(cudaStreamSynchronize(h->sx));
+    CK(cudaMemcpyAsync(h->x, x, sizeof(double) * len, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    MARK_X(h);
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_set_s(ekf_handle* h, const double* s, int32_t len) {
+    CKH(h);
+    if (len != h->N || (len > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_s: expected " + std::to_string(h->N) + " signatures");
+    if (len == 0) return EKF_OK;
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->sx) CK(cudaStreamSynchronize(h->sx));
+    CK(cudaMemcpyAsync(h->s, s, sizeof(double) * len, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    MARK_X(h);
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_set_P(ekf_handle* h, const double* P, int32_t lda) {
+    CKH(h);
+    const int n = n_of(h);
+    if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_set_P: lda < n");
+    CK(cudaSetDevice(h->p.device));
+    FLUSH(h);
+    const int hi = std::min(h->c_hi, n);  // a sharded handle keeps its own columns of the caller's full matrix
+    if (hi > h->c_lo)
+        CK(cudaMemcpy2DAsync(h->P, sizeof(double) * h->ld, P + (size_t)h->c_lo * lda, sizeof(double) * lda,
+                             sizeof(double) * n, hi - h->c_lo, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->hflags) h->hflags[0] = 0;
     return EKF_OK;
 }
 
@@ -921,22 +1016,26 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
     double *dA = nullptr, *dd = nullptr;
-    CK(cudaMalloc(&dA, sizeof(double) * (size_t)n * r));
-    CK(cudaMalloc(&dd, sizeof(double) * n));
-    CK(cudaMemcpyAsync(dA, A, sizeof(double) * (size_t)n * r, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemcpyAsync(dd, d, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
-    CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
-    CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
-    if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
-    launch_init_lowrank(h->stream, h->P, h->ld, n, h->c_lo, std::min(h->c_hi, n) - h->c_lo, dA, r, dd);
-    h->q.clear();
-    h->launches += 1;
-    CK(cudaGetLastError());
-    CK(cudaStreamSynchronize(h->stream));
-    MARK_X(h);
+    int32_t rc = [&]() -> int32_t {               // scratch freed on every path
+        CK(cudaMalloc(&dA, sizeof(double) * (size_t)n * r));
+        CK(cudaMalloc(&dd, sizeof(double) * n));
+        CK(cudaMemcpyAsync(dA, A, sizeof(double) * (size_t)n * r, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(dd, d, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
+        CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
+        CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+        if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
+        launch_init_lowrank(h->stream, h->P, h->ld, n, h->c_lo, std::min(h->c_hi, n) - h->c_lo, dA, r, dd);
+        h->q.clear();
+        h->launches += 1;
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(h->stream));
+        return mark_x(h);
+    }();
     cudaFree(dA); cudaFree(dd);
+    if (rc != EKF_OK) return rc;
     h->N = N;
+    if (h->hflags) h->hflags[0] = 0;
     return EKF_OK;
 }
 

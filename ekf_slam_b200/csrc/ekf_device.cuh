@@ -14,6 +14,17 @@
 
 namespace ekf {
 
+// Host helper for the dynamic-shared-memory opt-in (cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device
+// attribute): true when `smem` exceeds what was requested so far on the CURRENT device, and records it.
+inline bool smem_grows(size_t (&seen)[64], size_t smem) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    if (smem <= seen[dev]) return false;
+    seen[dev] = smem;
+    return true;
+}
+
 struct Lin {            // written by k_linearize, consumed by k_gain (one observation)
     double Hs[2][5];    // the 5 non-zero columns of H_k (EKF_SLAM.m:137-138)
     double nu[2];       // innovation z - z_k (EKF_SLAM.m:144), NOT angle wrapped
@@ -21,6 +32,7 @@ struct Lin {            // written by k_linearize, consumed by k_gain (one obser
     double S[2][2];     // phi_k (EKF_SLAM.m:141)
     int    c[5];        // 0-based state indices [0,1,2,a,a+1], a = 3+2(idx-1)
     int    nonfinite;   // 1 when phi_k or its inverse is not finite
+    int*   nf;          // host-mapped sticky flag of the handle (set by report_nonfinite when nonfinite; read at sync points)
 };
 
 struct AssocResult {    // written by k_associate's last block
@@ -194,7 +206,14 @@ struct BatchLin {                       // written by k_batch_lin, read by k_bat
     double2 Kslot[EKF_BATCH_MAX][EKF_BATCH_SLOTS];   // K_q(col(slot), :)
     double2 Bslot[EKF_BATCH_MAX][EKF_BATCH_SLOTS];   // B_q(:, col(slot))
     int     nonfinite;
+    int*    nf;                         // host-mapped sticky flag of the handle, like Lin::nf
 };
+
+// phi_k or its inverse is not finite (EKF_SLAM.m:137 divides by q = 0 when the robot stands on the landmark): raise the
+// handle's sticky flag in mapped host memory; the next synchronising call returns EKF_ENONFINITE.  Costs nothing unless hit.
+__device__ __forceinline__ void report_nonfinite(int* nf) {
+    if (nf) { *(volatile int*)nf = 1; __threadfence_system(); }
+}
 
 // ---- streaming vector access for the downdate (LDG.E.128/256 with L1 no-allocate) ----
 struct __align__(32) double4a { double x, y, z, w; };

@@ -7,10 +7,25 @@
 #include "ekf_kernels.h"
 #include "ekf_device.cuh"
 #include <cstdlib>
+#include <atomic>
 
 namespace ekf {
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device (context): remember it per (kernel, device), so that a process
+// that creates handles on several devices (ekf_params.device, ekf_create_multi) opts in on each of them.
+template <auto KERNEL>
+static void smem_optin(int bytes) {
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_relaxed) & bit)) {
+        cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        done.fetch_or(bit, std::memory_order_relaxed);
+    }
+}
 
 // ------------------------------------------------------------------ K3 covariance downdate (rank-2M flush)
 // P(i,j) -= sum_{q<M} K_q(i,0) B_q(0,j) + K_q(i,1) B_q(1,j), terms subtracted in observation order (rank2_sub),
@@ -429,11 +444,7 @@ template <int KS>
 static void launch_mc_flush_tma_ks(cudaStream_t st, const McArgs& a, int n_filters, int cap_n) {
     constexpr int TC = 64, SCOLS = 8, NSTAGE = 6, CG = 1;
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_mc_flush_tma<KS, TC, SCOLS, NSTAGE, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        attr_set = true;
-    }
+    smem_optin<k_mc_flush_tma<KS, TC, SCOLS, NSTAGE, CG>>(C::SMEM);
     TileMap tm = tm_make((cap_n + C::TR - 1) / C::TR, (cap_n + TC - 1) / TC, TC, C::TR / TC, 0, a.sym);
     dim3 grid((unsigned)tm_prefix(tm, tm.CT), n_filters);            // live tiles at capacity; smaller filters exit early
     k_mc_flush_tma<KS, TC, SCOLS, NSTAGE, CG><<<grid, C::THREADS, C::SMEM, st>>>(a);
@@ -452,21 +463,212 @@ template <int KS, int TC, int SCOLS, int NSTAGE, int CG = 1, int MINB = 1>
 static void launch_dd_tma(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                           const double2* Ball, int64_t lds, int M, int col_off) {
     typedef TmaCfg<KS, TC, SCOLS, NSTAGE, CG> C;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        attr_set = true;
-    }
+    smem_optin<k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG, MINB>>(C::SMEM);
     static_assert(C::TR % TC == 0 && (C::TR / TC == 1 || C::TR / TC == 2), "tile map needs TR = TC or 2 TC");
     const int R = (n + C::TR - 1) / C::TR, CT = (ncols + TC - 1) / TC;   // row tiles cover the active rows only
     TileMap tm = tm_make(R, CT, TC, C::TR / TC, col_off, sym);
-    { static int ord = -1; if (ord < 0) { const char* v = getenv("EKF_TILE_ORDER"); ord = v ? atoi(v) : -2; }
+    { static int ord = -3; if (ord == -3) { const char* v = getenv("EKF_TILE_ORDER"); ord = v ? atoi(v) : -2; }   // -3: not read yet, -2: no override
       // default: two fronts for the 128-column tiles of the rank >= 10 flush; the 64-column tile shapes of the lower ranks
       // measure 1-2 % faster in natural order (profiles/README.md)
       tm.order = !sym ? 0 : (ord == -2 ? (TC == 128 ? 1 : 0) : ord); }
     const long long live = tm_prefix(tm, CT);
     if (live <= 0 || live > 0x3fffffffLL) return;        // device decode is 32-bit
     k_downdate_tma<KS, TC, SCOLS, NSTAGE, CG, MINB><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, sym, Kall, Ball, lds, M, tm);
+}
+
+// ------------------------------------------------------------------ K3d rank-2M flush, hybrid: bulk-async in, registers out
+// k_downdate_tma couples its loads to its arithmetic: a stage's slot can only be refilled after the consumers have
+// finished the DMMA chain, written the stage back to shared memory, fenced, and the producer has stored it out -- so a
+// CTA's loads run only ~2 stages ahead of its math, and at rank 32 (16 dependent-pair DMMAs per warp and stage) neither
+// HBM (0.75) nor the FP64 tensor pipe (0.53) is kept busy.  Here the way IN is the same (one producer warp, 1 KB column
+// segments global -> shared with cp.async.bulk + mbarrier complete_tx, NSTAGE ring), but the consumers read their
+// fragment out of the stage into the accumulator registers, RELEASE THE SLOT once the last fragment read has been
+// consumed by an issued DMMA, and store the updated 4 consecutive rows of a column straight from registers with one
+// 256-bit st.global (four lanes = one full 128-byte line, like k_downdate_mma): no STS, no proxy fence, no store
+// handshake, and all NSTAGE slots can be in flight while the DMMA chains run.
+// BST = 1: the B operand of a stage (SCOLS columns x 4 KS doubles, from the column-major copy Bt[col][SROW] that
+// k_pack_bt writes) rides in the stage itself with one extra bulk copy, instead of a per-CTA 37 KB operand tile:
+// shared memory per stage 10.6 KB -> deeper rings at the same CTAs/SM.
+// CH = 4 (SCOLS = 16): a warp runs the two 8-column groups of a stage as four interleaved DMMA chains.
+// Arithmetic, fragments and term order are those of k_downdate_mma / k_downdate_tma: bit-identical results.
+template <int KS, int SCOLS, int NSTAGE, int BST>
+struct HybCfg {
+    static constexpr int TR = 128, TC = 128;
+    static constexpr int CS = TR * 8 + 16;               // bytes between columns of a stage (16 B pad: conflict-free LDS.128)
+    static constexpr int SROW = 4 * KS + 4;              // doubles per column of the B operand
+    static constexpr int PBYTES = SCOLS * CS;
+    static constexpr int BBYTES = BST ? SCOLS * SROW * 8 : 0;
+    static constexpr int STAGE_BYTES = (PBYTES + BBYTES + 127) / 128 * 128;
+    static constexpr int BS_BYTES = BST ? 0 : TC * SROW * 8;
+    static constexpr int SMEM = NSTAGE * STAGE_BYTES + BS_BYTES + 2 * NSTAGE * 8;
+    static constexpr int THREADS = 9 * 32;               // 8 consumer warps x 16 rows + 1 producer warp
+};
+
+// Bt[col][SROW]: column-major copy of the pending B slabs, Bt[col * SROW + 2 q + c] = B_q(c, col), zero for q >= M.
+template <int KS>
+__global__ void k_pack_bt(const double2* __restrict__ Ball, int64_t lds, int M, int ncols, double* __restrict__ Bt) {
+    constexpr int SROW = 4 * KS + 4;
+    const int col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= ncols) return;
+    double* o = Bt + (int64_t)col * SROW;
+#pragma unroll
+    for (int q = 0; q < 2 * KS; ++q) {
+        const double2 b = q < M ? Ball[q * lds + col] : make_double2(0.0, 0.0);
+        *(double2*)(o + 2 * q) = b;
+    }
+    *(double2*)(o + 4 * KS) = make_double2(0.0, 0.0);
+    *(double2*)(o + 4 * KS + 2) = make_double2(0.0, 0.0);
+}
+
+template <int KS, int SCOLS, int NSTAGE, int BST, int MINB>
+__global__ void __launch_bounds__(288, MINB)
+k_downdate_hyb(double* __restrict__ P, int64_t ld, int n, int ncols, const double2* __restrict__ Kall,
+               const double2* __restrict__ Ball, const double* __restrict__ Bt, int64_t lds, int M, TileMap tm) {
+    typedef HybCfg<KS, SCOLS, NSTAGE, BST> C;
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* stage = smem;
+    double* Bs = (double*)(smem + NSTAGE * C::STAGE_BYTES);
+    uint64_t* bars = (uint64_t*)(smem + NSTAGE * C::STAGE_BYTES + C::BS_BYTES);
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + NSTAGE);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    int bx, by;
+    {
+        const int T = (int)gridDim.x, t0 = (int)blockIdx.x;
+        const int t = tm.order == 1 ? ((t0 & 1) ? T - 1 - (t0 >> 1) : (t0 >> 1)) : t0;   // two fronts (see k_downdate_tma)
+        tm_decode<1>(tm, t, bx, by);
+    }
+    const int r0 = bx * C::TR, c0 = by * C::TC;
+    const int tile_cols = min(C::TC, ncols - c0);
+    const int ns = (tile_cols + SCOLS - 1) / SCOLS;
+    const int rows_here = (int)min((int64_t)C::TR, ld - r0);
+    const uint32_t col_bytes = (uint32_t)rows_here * 8u;
+
+    if (tid == 0) {
+        for (int i = 0; i < NSTAGE; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 8) {
+        // ------------------------------------------------ producer: lane c moves column c of every stage, lane 31 its B operand
+        for (int s = 0; s < ns; ++s) {
+            const int slot = s % NSTAGE;
+            if (s >= NSTAGE) mbar_wait(empty0 + 8 * slot, ((s / NSTAGE) - 1) & 1);     // every consumer warp has read the slot
+            const int nc = min(SCOLS, tile_cols - s * SCOLS);
+            const uint32_t bbytes = BST ? (uint32_t)nc * C::SROW * 8u : 0u;
+            if (lane == 0) mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)nc * col_bytes + bbytes);
+            __syncwarp();
+            unsigned char* sb = stage + slot * C::STAGE_BYTES;
+            if (lane < nc)
+                bulk_g2s(smem_u32(sb + lane * C::CS), P + (int64_t)r0 + (int64_t)(c0 + s * SCOLS + lane) * ld, col_bytes,
+                         full0 + 8 * slot);
+            if (BST && lane == 31)
+                bulk_g2s(smem_u32(sb + C::PBYTES), Bt + (int64_t)(c0 + s * SCOLS) * C::SROW, bbytes, full0 + 8 * slot);
+        }
+        return;
+    }
+
+    // ---------------------------------------------------- consumers: warp w owns rows r0 + 16 w .. + 15
+    if (!BST) {
+        for (int e = tid; e < C::TC * 2 * KS; e += 256) {
+            const int j = e / (2 * KS), q = e - j * (2 * KS);
+            const double2 b = (j < tile_cols && q < M) ? Ball[q * lds + c0 + j] : make_double2(0.0, 0.0);
+            Bs[j * C::SROW + 2 * q] = b.x;
+            Bs[j * C::SROW + 2 * q + 1] = b.y;
+        }
+    }
+    const int r = lane >> 2, t = lane & 3;
+    const int i0 = r0 + warp * 16;
+    const bool active = i0 < n;                                      // rows [n, ld) are padding: never stored
+    double kf[2][KS];
+#pragma unroll
+    for (int s = 0; s < KS; ++s) {
+        const int q = 2 * s + (t >> 1);
+#pragma unroll
+        for (int tile = 0; tile < 2; ++tile) {
+            const int row = i0 + 4 * (r >> 1) + 2 * tile + (r & 1);
+            const double2 kk = (active && q < M) ? Kall[q * lds + row] : make_double2(0.0, 0.0);
+            kf[tile][s] = -((t & 1) ? kk.y : kk.x);
+        }
+    }
+    const int row_off = (warp * 16 + 4 * t) * 8;                     // byte offset of this lane's 4 rows within a column
+    double* gp = P + (int64_t)(i0 + 4 * t) + (int64_t)(c0 + r) * ld;  // this lane's 4 rows of column r of group 0
+    if (!BST) asm volatile("bar.sync 1, 256;" ::: "memory");         // B operand staged (consumer warps only)
+    constexpr int NG = SCOLS / 8;
+    for (int s = 0; s < ns; ++s) {
+        const int slot = s % NSTAGE;
+        mbar_wait(full0 + 8 * slot, (s / NSTAGE) & 1);
+        const unsigned char* sb = stage + slot * C::STAGE_BYTES;
+        const double* bop = BST ? (const double*)(sb + C::PBYTES) : Bs + (int64_t)s * SCOLS * C::SROW;
+        double2 lo[NG], hi[NG];
+        bool ok[NG];
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+            const int cs = g * 8 + r;
+            ok[g] = active && (s * SCOLS + cs < tile_cols);
+            lo[g] = make_double2(0.0, 0.0); hi[g] = lo[g];
+            if (ok[g]) {
+                const double2* pv = (const double2*)(sb + cs * C::CS + row_off);
+                lo[g] = pv[0]; hi[g] = pv[1];
+            }
+        }
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+            for (int g = 0; g < NG; ++g) {
+                // columns beyond the tile read stale operand rows: they only reach accumulator rows that are never stored
+                const double a = bop[(g * 8 + r) * C::SROW + 4 * ks + t];
+                dmma8x8x4(lo[g].x, lo[g].y, a, kf[0][ks]);
+                dmma8x8x4(hi[g].x, hi[g].y, a, kf[1][ks]);
+            }
+        }
+        // every shared-memory read of this stage has been consumed by an issued DMMA: the slot may be refilled
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+#pragma unroll
+        for (int g = 0; g < NG; ++g)
+            if (ok[g]) {
+                double4a v; v.x = lo[g].x; v.y = lo[g].y; v.z = hi[g].x; v.w = hi[g].y;
+                st_stream4(gp + (int64_t)(s * SCOLS + g * 8) * ld, v);
+            }
+    }
+}
+
+template <int KS, int SCOLS, int NSTAGE, int BST, int MINB>
+static void launch_dd_hyb(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
+                          const double2* Ball, double* Bt, int64_t lds, int M, int col_off) {
+    typedef HybCfg<KS, SCOLS, NSTAGE, BST> C;
+    smem_optin<k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB>>(C::SMEM);
+    const int R = (n + C::TR - 1) / C::TR, CT = (ncols + C::TC - 1) / C::TC;
+    TileMap tm = tm_make(R, CT, C::TC, 1, col_off, sym);
+    { static int ord = -3; if (ord == -3) { const char* v = getenv("EKF_TILE_ORDER"); ord = v ? atoi(v) : -2; }
+      tm.order = !sym ? 0 : (ord == -2 ? 1 : ord); }
+    const long long live = tm_prefix(tm, CT);
+    if (live <= 0 || live > 0x3fffffffLL) return;
+    if (BST) k_pack_bt<KS><<<cdiv(ncols, 128), 128, 0, st>>>(Ball, lds, M, ncols, Bt);
+    k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, Kall, Ball, Bt, lds, M, tm);
+}
+
+// hybrid variants by number (EKF_DOWNDATE_VARIANT >= 30); returns false when `v` names none
+template <int KS>
+static bool launch_dd_hyb_v(int v, cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
+                            const double2* Ball, double* Bt, int64_t lds, int M, int col_off) {
+#define HY(SC, NS, BS, MB) launch_dd_hyb<KS, SC, NS, BS, MB>(st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, M, col_off); return true
+    if (Bt == nullptr && v != 30 && v != 37) return false;       // the in-stage operand needs the Bt scratch buffer
+    switch (v) {
+        case 30: HY(8, 4, 0, 3);       // operand tile per CTA as in k_downdate_tma, 4 x 8-col stages
+        case 31: HY(8, 6, 1, 3);       // operand in the stage: 6 x 10.6 KB = 64 KB, 3 CTAs/SM
+        case 32: HY(8, 4, 1, 3);
+        case 33: HY(8, 8, 1, 2);       // 8 stages, 2 CTAs/SM
+        case 34: HY(16, 3, 1, 3);      // 16-col stages (four DMMA chains per warp), 3 x 21.2 KB
+        case 35: HY(16, 4, 1, 2);
+        case 36: HY(8, 5, 1, 4);       // 4 CTAs/SM if the registers allow (<= 56)
+        case 37: HY(8, 6, 0, 2);
+        case 38: HY(16, 5, 1, 2);
+        default: return false;
+    }
+#undef HY
 }
 
 template <int M, int VEC, int BLOCK, int TC, int UNROLL>
@@ -479,7 +681,19 @@ static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int ncols, 
 
 // m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
-                     int64_t lds, int m, int col_off, int variant) {
+                     int64_t lds, int m, int col_off, int variant, double* Bt) {
+    if (m < 1) return;
+    if (variant >= 30) {    // hybrid kernels (bulk-async in, registers out), any rank
+        bool done = false;
+        switch ((m + 1) / 2) {
+#define HV(KS_) case KS_: done = launch_dd_hyb_v<KS_>(variant, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+            HV(1) HV(2) HV(3) HV(4) HV(5) HV(6) HV(7) HV(8)
+#undef HV
+            default: break;
+        }
+        if (done) return;
+        variant = -1;
+    }
     // variants: 0..3 CUDA-core DFMA (LDG/STG), 4..7 DMMA with LDG/STG fragments, >= 8 DMMA with bulk-async (TMA) staging
     // default (variant < 0), from the B200 sweep in profiles/README.md: TMA staging everywhere; tile shape by rank
     //   m == 1: 64 x 16-col stages, 2 consumer sets (v18)   m = 2..4: 64-col tiles, 6 x 8-col stages (v17)
@@ -493,18 +707,7 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
             case 6: launch_dd_tma<6, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             case 7: launch_dd_tma<7, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             default:
-                // 15/16 terms: tile shape selectable for sweeps (EKF_DOWNDATE_VARIANT); default = the rank-16 shape
-                if (variant == 9) launch_dd_tma<8, 128, 16, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 11) launch_dd_tma<8, 128, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 14) launch_dd_tma<8, 64, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 16) launch_dd_tma<8, 128, 16, 3, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 17) launch_dd_tma<8, 64, 8, 6>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 18) launch_dd_tma<8, 64, 16, 4, 2>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 20) launch_dd_tma<8, 128, 8, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 21) launch_dd_tma<8, 64, 8, 4, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);   // 56 registers, 51.7 KB: 4 CTAs/SM
-                else if (variant == 22) launch_dd_tma<8, 64, 8, 3, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 23) launch_dd_tma<8, 64, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
-                else if (variant == 24) launch_dd_tma<8, 128, 8, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);   // unbounded: 80 registers, 2 CTAs/SM
+                if (variant == 21) launch_dd_tma<8, 64, 8, 4, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);   // 56 registers, 51.7 KB: 4 CTAs/SM (0.679 ms vs 0.674)
                 else launch_dd_tma<8, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 break;
         }

@@ -120,6 +120,7 @@ __global__ void k_linearize(const double* __restrict__ P, int64_t ld, const doub
         lin->nu[1] = z1 - zk[1];
         for (int k = 0; k < 5; ++k) lin->c[k] = c[k];
         lin->nonfinite = bad;
+        if (bad) report_nonfinite(lin->nf);
     }
 }
 
@@ -242,7 +243,7 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
         if (gown) G[gi][gj] = rank2_sub(G[gi][gj], gup ? Ks[gi] : Ks[gj], gup ? Bs[gj] : Bs[gi]);   // keep the block current: P <- P - K_q B_q
         __syncthreads();
     }
-    if (tid == 0) out->nonfinite = bad;
+    if (tid == 0) { out->nonfinite = bad; if (bad) report_nonfinite(out->nf); }
 }
 
 __global__ void __launch_bounds__(128)

@@ -19,7 +19,10 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m);
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                     const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1);   // col_off: global index of column 0 (SYM slabs); variant < 0: default
+                     const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1,
+                     double* Bt = nullptr);   // col_off: global index of column 0 (SYM slabs); variant < 0: default; Bt: scratch of
+                                              // ncols x EKF_BT_SROW doubles for the kernels that carry the B operand in their stages
+#define EKF_BT_SROW (4 * 8 + 4)
 // fused batch (<= 8 observations with known slots; nothing may be pending): fills gain slabs 0..k-1 and updates x
 // Pc != null (sharded): slot columns come from the exchanged Pc[slot][0..n), P is the local slab of columns [c_lo, c_hi)
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
@@ -47,7 +50,8 @@ void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xpre
 #define EKF_MAX_PEERS 8
 struct PeerSet { double* pc[EKF_MAX_PEERS]; int* flags[EKF_MAX_PEERS]; int world, rank; };   // cudaIpc-mapped Pc buffers / flag words of every rank
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags);
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags,
+                         long long timeout_cycles, int* err_word);   // err_word: mapped host memory, set to 1 when a peer does not answer in time
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
                       double* Pc, int64_t ldc, int sym);
 void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, int a,

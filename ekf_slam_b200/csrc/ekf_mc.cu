@@ -536,12 +536,10 @@ void launch_mc_pack_poses(cudaStream_t st, const double* x, int64_t xstride, int
 template <int M, int TC>
 static void launch_mc_flush_w_m(cudaStream_t st, const McArgs& a, int n_filters, int cap_n) {
     const size_t smem = ((size_t)(a.cap + 2) * 2 * M + (size_t)TC * M) * sizeof(double2);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        cudaFuncSetAttribute(k_mc_flush_w<M, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static size_t smem_set[64] = {0};                    // per device: the attribute belongs to the device's context
+    if (smem_grows(smem_set, smem))
         // no max-shared carve-out here: the LDG stream needs the L1 as its landing buffer (tools/tri_stream.cu: 4.2 -> 5.5 TB/s)
-        smem_set = smem;
-    }
+        cudaFuncSetAttribute(k_mc_flush_w<M, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((cap_n + TC - 1) / TC, n_filters);
     k_mc_flush_w<M, TC><<<grid, 256, smem, st>>>(a);
 }
@@ -899,12 +897,11 @@ k_mc_front(McArgs a) {
 }
 
 void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads, size_t smem) {
-    static size_t smem_set[2] = {0, 0};
+    static size_t smem_set[2][64] = {{0}, {0}};
     const int mb = a.assoc_mode == 1 && a.variant != 0;
-    if (smem > smem_set[mb]) {
+    if (smem_grows(smem_set[mb], smem)) {
         if (mb) cudaFuncSetAttribute(k_mc_step<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         else cudaFuncSetAttribute(k_mc_step<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        smem_set[mb] = smem;
     }
     if (mb) k_mc_step<1, 0><<<n_filters, threads, smem, st>>>(a);
     else k_mc_step<0, 0><<<n_filters, threads, smem, st>>>(a);
@@ -912,11 +909,9 @@ void launch_mc_step(cudaStream_t st, const McArgs& a, int n_filters, int threads
 
 template <int SYM, int RPT>
 static void launch_mc_front_t(cudaStream_t st, const McArgs& a, int n_filters, size_t smem) {
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
+    static size_t smem_set[64] = {0};
+    if (smem_grows(smem_set, smem))
         cudaFuncSetAttribute(k_mc_front<SYM, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        smem_set = smem;
-    }
     k_mc_front<SYM, RPT><<<n_filters, 256, smem, st>>>(a);
 }
 

@@ -95,16 +95,25 @@ __global__ void k_scatter_cols(const double* __restrict__ Ploc, int64_t ld, int 
     }
 }
 
-__global__ void k_wait_flags(const int* __restrict__ flags, int world, int epoch) {
-    if ((int)threadIdx.x < world)
-        while (ld_acquire_sys(flags + threadIdx.x) < epoch) { }
+// Bounded spin: a peer that died (or never made the matching call) must not hang this rank's stream for ever.  After
+// `timeout` clock cycles the waiter raises the handle's sticky exchange-error word in mapped host memory and gives up;
+// the work queued behind it runs on incomplete columns, and every later synchronising call returns EKF_ENCCL.
+__global__ void k_wait_flags(const int* __restrict__ flags, int world, int epoch, long long timeout, int* __restrict__ err) {
+    if ((int)threadIdx.x < world) {
+        const long long t0 = clock64();
+        while (ld_acquire_sys(flags + threadIdx.x) < epoch) {
+            if (*(volatile int*)err) break;                                   // already failed: do not wait again
+            if (clock64() - t0 > timeout) { *(volatile int*)err = 1; __threadfence_system(); break; }
+        }
+    }
 }
 
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags) {
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags,
+                         long long timeout_cycles, int* err_word) {
     dim3 grid((n + 255) / 256, ss.n);
     k_scatter_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, ps, buf_off, sym, epoch, ticket);
-    k_wait_flags<<<1, 32, 0, st>>>(flags, ps.world, epoch);
+    k_wait_flags<<<1, 32, 0, st>>>(flags, ps.world, epoch, timeout_cycles, err_word);
 }
 
 // One warp, replicated on every rank: EKF_SLAM.m:125-143 from the broadcast columns, plus B_m(:, c) for every
@@ -144,6 +153,7 @@ __global__ void k_lin_shard(const double* __restrict__ Pc, int64_t ldc, SlotSet 
         lin->nu[1] = z1 - zk[1];
         for (int k = 0; k < 5; ++k) lin->c[k] = c[k];
         lin->nonfinite = bad;
+        if (bad) report_nonfinite(lin->nf);
     }
     __syncwarp();
     if (!sym && lane < ss.n) {                           // B_m(:, col(slot)) = H_m * cur(c, col(slot))

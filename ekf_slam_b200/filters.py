@@ -59,7 +59,6 @@ class _FilterBase:
         self.observed = None               # EKF_SLAM.m:19
         self.chosen = []                   # per observation: ('update'|'append', idx) -- parity log
         self._last_predict = None
-        self._table_cache = (None, 0, None, None)
 
     # ---- lifetime ------------------------------------------------------
     def close(self):
@@ -90,6 +89,12 @@ class _FilterBase:
         self._ck(self._lib.ekf_get_x(self._h, L.dptr(out), n))
         return out                         # row vector 1 x n (EKF_SLAM.m:28)
 
+    @x.setter
+    def x(self, v):
+        """h.x = v (public read/write upstream, EKF_SLAM.m:6): same length as the current state; P and s untouched."""
+        v = _f64(v)
+        self._ck(self._lib.ekf_set_x(self._h, L.dptr(v), v.size))
+
     @property
     def P(self):
         n = 3 + 2 * self.N
@@ -97,12 +102,27 @@ class _FilterBase:
         self._ck(self._lib.ekf_get_P(self._h, L.dptr(out), n))
         return out
 
+    @P.setter
+    def P(self, M):
+        """h.P = M (EKF_SLAM.m:7): n x n at the current n; x and s untouched."""
+        M = np.asfortranarray(np.asarray(M, dtype=np.float64))
+        n = 3 + 2 * self.N
+        if M.shape != (n, n):
+            raise ValueError('P must be %d x %d (use set_state to change the number of landmarks)' % (n, n))
+        self._ck(self._lib.ekf_set_P(self._h, L.dptr(M), n))
+
     @property
     def s(self):
         N = self.N
         out = np.empty(N)
         self._ck(self._lib.ekf_get_s(self._h, L.dptr(out), N))
         return out
+
+    @s.setter
+    def s(self, v):
+        """h.s = v (EKF_SLAM.m:9): N signatures; x and P untouched."""
+        v = _f64(v) if np.size(v) else np.zeros(0)
+        self._ck(self._lib.ekf_set_s(self._h, L.dptr(v) if v.size else None, v.size))
 
     def P_block(self, r0, c0, nr, nc):
         out = np.empty((nr, nc), order='F')
@@ -197,13 +217,16 @@ class _FilterBase:
         return self.P_block(0, c_lo, n, hi - c_lo), c_lo
 
     def _tables(self, landmark_list):
+        # Rebuilt on every measure(): the reference's landmark DB mutates entries in place without changing the list or
+        # its length (RANSAC.m:262 promotes index 0 to max+1, :268 rewrites .loc), so identity/length is no cache key.
+        # A caller whose table is immutable can hand over a `tables()` method returning (index int32[T], loc float64[T,2]).
+        fast = getattr(landmark_list, 'tables', None)
+        if fast is not None:
+            idx, loc = fast()
+            return np.ascontiguousarray(idx, dtype=np.int32), np.asfortranarray(loc, dtype=np.float64).reshape(-1, 2, order='F')
         lst = landmark_list.landmarkObj.landmark
-        key, ln, idx, loc = self._table_cache
-        if key is lst and ln == len(lst):
-            return idx, loc
-        idx = np.array([int(e.index) for e in lst], dtype=np.int32)
+        idx = np.fromiter((int(e.index) for e in lst), dtype=np.int32, count=len(lst))
         loc = np.asfortranarray(np.array([e.loc for e in lst], dtype=np.float64).reshape(-1, 2))
-        self._table_cache = (lst, len(lst), idx, loc)
         return idx, loc
 
     def measure(self, laserData, u, landmark_list, pass_x=True):

@@ -40,6 +40,25 @@ class LandmarkStub:
     def getLandmark(self, laserdata, x):
         return self._observed
 
+    def tables(self):
+        """(index int32[T], loc float64[T,2]) of the landmark table.  The synthetic table never changes after it was
+        built, so the flattened arrays are cached per table list; the filter classes use this optional method when a
+        landmark_list offers it and otherwise flatten landmarkObj.landmark on every measure() (the reference's RANSAC
+        database mutates entries in place)."""
+        lst = self.landmarkObj.landmark
+        hit = _TABLES.get(id(lst))
+        if hit is None or hit[0] is not lst or hit[1] != len(lst):
+            idx = np.fromiter((int(e.index) for e in lst), dtype=np.int32, count=len(lst))
+            loc = np.asfortranarray(np.array([e.loc for e in lst], dtype=np.float64).reshape(-1, 2))
+            if len(_TABLES) >= 8:
+                _TABLES.clear()
+            hit = (lst, len(lst), idx, loc)
+            _TABLES[id(lst)] = hit
+        return hit[2], hit[3]
+
+
+_TABLES = {}
+
 
 class World:
     """A pre-generated trajectory: per step ``u`` (2,), ``observed_LL`` (k_t x 3)."""

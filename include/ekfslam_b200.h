@@ -32,8 +32,9 @@ extern "C" {
 #define EKF_EINVAL     (-1)   /* bad argument / bad state (e.g. idx out of range) */
 #define EKF_ECAPACITY  (-2)   /* append beyond capacity_landmarks */
 #define EKF_ECUDA      (-3)   /* CUDA runtime error (message in ekf_last_error) */
-#define EKF_ENCCL      (-4)   /* NCCL error */
-#define EKF_ENONFINITE (-5)   /* debug check: non-finite innovation covariance */
+#define EKF_ENCCL      (-4)   /* NCCL error, or a peer rank of a sharded filter did not answer within EKF_XCHG_TIMEOUT_MS (sticky) */
+#define EKF_ENONFINITE (-5)   /* an update since the last synchronising call had a non-finite innovation covariance (q = 0 at
+                                 EKF_SLAM.m:137: robot on the landmark); reported once by the next getter / ekf_sync, x and P stay poisoned */
 
 #define EKF_VARIANT_KNOWN  0  /* EKF_SLAM.m    */
 #define EKF_VARIANT_UC     1  /* EKF_SLAM_UC.m */
@@ -127,6 +128,12 @@ int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_t nr, int32
                         double* out, int32_t ldo);                   /* 0-based sub-block (sampled parity at large n) */
 int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t lda,
                       const double* s, int32_t N);
+/* Property writes `h.x = v`, `h.P = M`, `h.s = v` (x, P, s are public read/write properties upstream, EKF_SLAM.m:6-9):
+ * one of the three at the current number of landmarks (len = 3+2N resp. N; P is n x n column-major, lda >= n), the
+ * other two untouched.  ekf_set_state replaces all three and may change N.  A sharded handle keeps its own columns of P. */
+int32_t ekf_set_x(ekf_handle* h, const double* x, int32_t len);
+int32_t ekf_set_P(ekf_handle* h, const double* P, int32_t lda);
+int32_t ekf_set_s(ekf_handle* h, const double* s, int32_t len);
 /* Populated synthetic map without a 3.2 GB H2D copy: P = A A^T / r + diag(d), A is n x r column-major. */
 int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const double* s, int32_t N,
                               const double* A, int32_t r, const double* d);

@@ -6,8 +6,9 @@ classdef EKFSLAM_B200_Base < handle
     % append(u,R,landmarkPos,signature), measure(laserData,u,landmark_list), plot(landmark_list).
     % All filter arithmetic runs on the GPU inside libekfslam_b200.so; this class only marshals
     % arguments through ekfslam_mex (one MEX call per method).  x, P and s are Dependent: reading
-    % them copies device -> host (P is 3.2 GB at 10k landmarks, so read it only when needed);
-    % assigning all three via setState uploads a state.
+    % them copies device -> host (P is 3.2 GB at 10k landmarks, so read it only when needed), assigning
+    % one of them (h.x = v; h.P = M; h.s = v) uploads that property at the current size and keeps the
+    % other two; setState uploads all three and may change the number of landmarks.
 
     properties (Dependent)
         x;   % 1 x n row vector [x y theta_deg l1x l1y ...]
@@ -69,6 +70,17 @@ classdef EKFSLAM_B200_Base < handle
         end
         function v = get.s(h)
             v = ekfslam_mex('get_s', h.hnd);
+        end
+        % x, P, s are public read/write properties upstream (EKF_SLAM.m:6-9): assigning one of them keeps the other two.
+        % The size must match the current state (setState changes the number of landmarks).
+        function set.x(h, v)
+            ekfslam_mex('set_x', h.hnd, v(:)');
+        end
+        function set.P(h, M)
+            ekfslam_mex('set_P', h.hnd, M);
+        end
+        function set.s(h, v)
+            ekfslam_mex('set_s', h.hnd, v(:));
         end
         function setState(h, x, P, s)
             ekfslam_mex('set_state', h.hnd, x(:)', P, s(:));

@@ -94,6 +94,16 @@ void mexFunction(int nlhs, mxArray* plhs[], int nrhs, const mxArray* prhs[]) {
     }
 
     if (nrhs < 2) mexErrMsgIdAndTxt("ekfslam:EINVAL", "verb '%s' needs a handle", verb);
+    {   /* right-hand-side count per verb (incl. verb and handle): a short call is an error, not an out-of-bounds read */
+        static const struct { const char* verb; int nrhs; } need[] = {
+            {"destroy", 2}, {"predict", 3}, {"update", 5}, {"append", 6}, {"associate", 4}, {"measure", 6},
+            {"n_landmarks", 2}, {"get_x", 2}, {"get_s", 2}, {"get_P", 2}, {"get_P_block", 6}, {"get_ellipses", 2},
+            {"set_state", 5}, {"set_x", 3}, {"set_P", 3}, {"set_s", 3}, {"set_noise", 6}, {"flush", 2}, {"sync", 2}};
+        size_t v;
+        for (v = 0; v < sizeof need / sizeof need[0]; ++v)
+            if (!strcmp(verb, need[v].verb) && nrhs < need[v].nrhs)
+                mexErrMsgIdAndTxt("ekfslam:EINVAL", "verb '%s' needs %d arguments, got %d", verb, need[v].nrhs, nrhs);
+    }
     ekf_handle* h = get_handle(prhs[1]);
 
     if (!strcmp(verb, "destroy")) { check(NULL, ekf_destroy(h)); return; }
@@ -192,6 +202,26 @@ void mexFunction(int nlhs, mxArray* plhs[], int nrhs, const mxArray* prhs[]) {
             mexErrMsgIdAndTxt("ekfslam:EINVAL", "set_state: x must have 3+2N elements and P must be n x n");
         check(h, ekf_set_state(h, dbl(prhs[2], n, "x"), dbl(prhs[3], n * n, "P"), (int32_t)n,
                                N ? dbl(prhs[4], (size_t)N, "s") : &dummy, N));
+        return;
+    }
+    if (!strcmp(verb, "set_x")) {             /* h.x = v, EKF_SLAM.m:6 */
+        size_t n = mxGetNumberOfElements(prhs[2]);
+        check(h, ekf_set_x(h, dbl(prhs[2], n, "x"), (int32_t)n));
+        return;
+    }
+    if (!strcmp(verb, "set_s")) {             /* h.s = v, EKF_SLAM.m:9 */
+        size_t N = mxGetNumberOfElements(prhs[2]);
+        double dummy = 0.0;
+        check(h, ekf_set_s(h, N ? dbl(prhs[2], N, "s") : &dummy, (int32_t)N));
+        return;
+    }
+    if (!strcmp(verb, "set_P")) {             /* h.P = M, EKF_SLAM.m:7 */
+        size_t n = mxGetM(prhs[2]);
+        int32_t N = 0;
+        check(h, ekf_n_landmarks(h, &N));
+        if (n != (size_t)(3 + 2 * N) || mxGetN(prhs[2]) != n)
+            mexErrMsgIdAndTxt("ekfslam:EINVAL", "set_P: P must be n x n with n = 3 + 2 N = %d", 3 + 2 * N);
+        check(h, ekf_set_P(h, dbl(prhs[2], n * n, "P"), (int32_t)n));
         return;
     }
     if (!strcmp(verb, "set_noise")) {         /* ekfslam_mex('set_noise', h, C, Rc, s_cost, s_thresh) */
