@@ -11,6 +11,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "ekf_math_shared.h"
 
 namespace ekf {
 
@@ -61,7 +62,7 @@ __device__ __forceinline__ double cosd(double x) {      // EKF_SLAM.m:42,58,64,8
     switch (m) { case 0: return cos(a); case 1: return -sin(a); case 2: return -cos(a); default: return sin(a); }
 }
 __device__ __forceinline__ double atan2d(double y, double x) {   // EKF_SLAM.m:130
-    return __dmul_rn(atan2(y, x), 57.29577951308232);
+    return __dmul_rn(ekm_atan2(y, x), 57.29577951308232);   // shared restatement: same bits as the structured C oracle
 }
 __device__ __forceinline__ double wrapTo360(double a) {          // EKF_SLAM.m:50,130; Correspondence.m:56
     double r = fmod(a, 360.0);
@@ -96,7 +97,7 @@ __device__ __forceinline__ double ldP_def(const double* __restrict__ P, int64_t 
 
 // Range-bearing measurement model about landmark slot a (0-based state index of its x coordinate).
 // Follows EKF_SLAM.m:125-138 == Correspondence.m:50-63 with explicit (non-contracted) roundings so a
-// plain C restatement compiled with -ffp-contract=off reproduces every bit except atan2's last ulp.
+// plain C restatement compiled with -ffp-contract=off reproduces every bit (atan2 included: ekf_math_shared.h).
 // It is written as entry-wise pieces (mm_* / ic_*) so that a warp can evaluate the entries on different lanes
 // (k_batch_lin) and still produce exactly the bits of the one-thread form below.
 struct MMPrep { double d0, d1, q, sq, iq; };

@@ -10,7 +10,9 @@
  * phi_k = H P(c,c) H' + R (:141), K = P(:,c) H' phi_k^-1 (:143) and (I - K H) P = P - K (H P(c,:)) (:145).
  * It is an independent statement of the algebra (different language, different grouping of the products than both the
  * dense oracle and the CUDA kernels), compiled with -ffp-contract=off so every operation rounds once like MATLAB's
- * scalar arithmetic.  Each function cites the reference lines it follows.
+ * scalar arithmetic.  Each function cites the reference lines it follows.  atan2 comes from the restatement shared with
+ * the CUDA library (ekf_slam_b200/csrc/ekf_math_shared.h, < 1.3 ulp), every other operation is IEEE-exact, so index
+ * decisions that hang on a cost comparison (association mode B) can be required to match the GPU bit for bit.
  *
  * parity unpinned: the reference has no tests / golden vectors and cannot be run here (no MATLAB/Octave in the
  * image); this file is pinned by the source text, by agreement with dense_literal.py on the golden worlds
@@ -24,6 +26,11 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+
+/* The one transcendental on the association path, shared bit for bit with the CUDA library (see the header's comment):
+ * with the platform's atan2 the Mahalanobis costs of mode B (Correspondence.m:74) would agree with the GPU's only to
+ * 1-2 ulp and near-ties could pick different landmarks.  -DSO_PLATFORM_ATAN2 builds the oracle with libm's atan2. */
+#include "../ekf_slam_b200/csrc/ekf_math_shared.h"
 
 #define PI_ 3.14159265358979323846
 #define P_(i, j) P[(size_t)(i) + (size_t)(j) * (size_t)ld]
@@ -47,7 +54,11 @@ double so_cosd(double x) {                       /* EKF_SLAM.m:42,58,64,85,87-88
     const double t = r * (PI_ / 180.0);
     return m == 0 ? cos(t) : m == 1 ? -sin(t) : m == 2 ? -cos(t) : sin(t);
 }
+#ifdef SO_PLATFORM_ATAN2
 double so_atan2d(double y, double x) { return atan2(y, x) * (180.0 / PI_); }   /* EKF_SLAM.m:130 */
+#else
+double so_atan2d(double y, double x) { return ekm_atan2(y, x) * (180.0 / PI_); }   /* EKF_SLAM.m:130 */
+#endif
 double so_wrapTo360(double a) {                  /* EKF_SLAM.m:50,130; Correspondence.m:56 */
     double r = fmod(a, 360.0);
     if (r != 0.0 && r < 0.0) r += 360.0;

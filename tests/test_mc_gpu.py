@@ -203,3 +203,59 @@ def test_config5_full_size_4096_filters_x_200_landmarks(storage):
     assert np.array_equal(first.x, last.x) and np.array_equal(first.P, last.P)
     print('4096 x 200 %s: sampled filters vs oracle, worst rel err x %.2e P %.2e' % (storage, worst[0], worst[1]))
     b.close()
+
+
+def test_config5_full_size_200_steps_sampled_filters():
+    """BASELINE config 5 at full size over a long horizon: 4096 x EKF_SLAM_UC x 200 landmarks (SYM storage, the bench's
+    configuration), 200 steps of predict + 5 associated updates per filter = 4.1 M updates; 8 sampled filters against
+    oracle/structured.c stepping the same inputs (two of them also against the dense-literal oracle for the first 20
+    steps): actions identical at every observation, x and P <= 1e-9 relative at steps 20, 50, 100, 150, 200.  The last
+    filter is fed filter 0's inputs and must stay bit-identical to it throughout."""
+    import ekf_slam_b200 as E
+    from bench import make_mc_inputs
+    from oracle import dense_literal as O
+    from oracle import structured as S
+    from tests.golden_util import Stub
+    from types import SimpleNamespace
+    nf, N, k, T = 4096, 200, 5, 200
+    x, P, s, lms, U, OBS, loc, idx = make_mc_inputs(N, k, nf, T)
+    U[:, nf - 1] = U[:, 0]
+    OBS[:, nf - 1] = OBS[:, 0]
+    counts = np.full(nf, k, dtype=np.int32)
+    ntab = np.array([N], dtype=np.int32)
+    b = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=N, max_obs=k, max_table=N, storage='sym', defer_m=8)
+    b.set_state_all(x, P, s)
+    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
+    sample = (0, 1, 511, 1234, 2048, 2777, 3333, nf - 2)
+    os_, dense = {}, {}
+    for f in sample:
+        os_[f] = S.EKF_SLAM_UC(capacity_landmarks=N)
+        os_[f].set_state(x, P, s)
+    for f in (1, 2777):
+        dense[f] = O.EKF_SLAM_UC()
+        dense[f].x, dense[f].P, dense[f].s = x.copy(), P.copy(), list(s)
+    worst = [0.0, 0.0]
+    for t in range(T):
+        a = b.step(np.ascontiguousarray(U[t]), packed=(np.ascontiguousarray(OBS[t]), counts, loc, idx, ntab, True),
+                   want_actions=True)
+        for f, o in os_.items():
+            n0 = len(o.chosen)
+            stub = Stub(OBS[t, f].T.copy(), table)
+            o.predict(U[t, f]); o.measure(None, U[t, f], stub)
+            assert [('update', int(v)) for v in a[f, :k]] == o.chosen[n0:], (t, f)
+            if t < 20 and f in dense:
+                dense[f].predict(U[t, f]); dense[f].measure(None, U[t, f], stub)
+        if t + 1 in (20, 50, 100, 150, 200):
+            for f, o in os_.items():
+                v = b[f]
+                ex, eP = _rel(v.x, o.x), _rel(v.P, o.P)
+                worst = [max(worst[0], ex), max(worst[1], eP)]
+                assert ex <= TOL and eP <= TOL, (t, f, ex, eP)
+                if t + 1 == 20 and f in dense:
+                    assert dense[f].chosen == o.chosen
+                    assert _rel(v.x, dense[f].x) <= TOL and _rel(v.P, dense[f].P) <= TOL, (f, 'dense')
+            first, last = b[0], b[nf - 1]
+            assert np.array_equal(first.x, last.x) and np.array_equal(first.P, last.P)
+    assert np.all(b.n_landmarks() == N) and np.all(np.isfinite(b.poses()))
+    print('4096 x 200 x %d steps: 8 sampled filters vs oracle, worst rel err x %.2e P %.2e' % (T, worst[0], worst[1]))
+    b.close()

@@ -369,3 +369,55 @@ def test_cross_step_deferral_identity_on_the_oracle():
         Kt.append(K2); Bt.append(B2)
     P_deferred = (F @ P0 @ F.T + Q) - sum(K @ B for K, B in zip(Kt, Bt))
     assert np.linalg.norm(P_deferred - o.P) / np.linalg.norm(o.P) < 1e-14
+
+
+# ---------------------------------------------------------------- round 2: shared atan2, f(x,u)
+def test_shared_atan2_accuracy_and_conventions():
+    """ekf_math_shared.h (the atan2 both the CUDA library and oracle/structured.c evaluate, so that mode-B association
+    costs agree bit for bit): <= 1.5 ulp against a 50-digit reference across the reduction breakpoints and all four
+    quadrants, C99 conventions at zeros / infinities / NaN."""
+    import math
+    import mpmath as mp
+    from oracle import structured as S
+    L = S.lib()
+    mp.mp.dps = 50
+    rng = np.random.default_rng(12)
+    cases = [tuple(rng.normal(size=2) * 10.0 ** rng.integers(-3, 4, 2)) for _ in range(3000)]
+    for a in np.linspace(0.01, 3.0, 700):
+        cases += [(a, 1.0), (-a, -1.0), (a, -1.0), (-a, 1.0)]
+    worst = 0.0
+    for y, x in cases:
+        got = L.so_atan2d(float(y), float(x))
+        ref = mp.atan2(mp.mpf(float(y)), mp.mpf(float(x))) * 180 / mp.pi
+        worst = max(worst, float(abs(mp.mpf(got) - ref)) / math.ulp(float(ref)))
+    # 1.3 ulp in radians; the degree conversion (x 180/pi, itself a rounded constant) may move the result up a binade
+    # (ulp halves relative to the value) and rounds once more: <= 3.5 ulp of the result in degrees
+    assert worst <= 3.5, worst
+    d = 180.0 / math.pi
+    for y, x in [(0.0, 1.0), (-0.0, 1.0), (0.0, -1.0), (-0.0, -1.0), (1.0, 0.0), (-1.0, 0.0), (1.0, -0.0),
+                 (math.inf, 1.0), (1.0, math.inf), (1.0, -math.inf), (-1.0, -math.inf), (math.inf, math.inf),
+                 (math.inf, -math.inf), (-math.inf, -math.inf), (1e-310, 1.0), (1e300, 1e-300), (1e-300, -1e300)]:
+        g, r = L.so_atan2d(y, x), math.atan2(y, x) * d
+        assert g == r and math.copysign(1.0, g) == math.copysign(1.0, r), (y, x, g, r)
+    assert math.isnan(L.so_atan2d(math.nan, 1.0))
+
+
+def test_f_motion_model_matches_the_oracle():
+    """[x_new,F] = f(h,x,u), EKF_SLAM.m:56-65: the host mirror's public method (pure, needs no device) against the
+    dense-literal oracle's, incl. multiples of 90 degrees where sind/cosd are exact, and the Jacobian taken at the
+    heading BEFORE the motion (:63-64 use x(3), not x(3)+u(2))."""
+    from ekf_slam_b200.filters import _FilterBase
+    o = O.EKF_SLAM()
+    rng = np.random.default_rng(3)
+    for th in [0.0, 90.0, 180.0, 270.0, 360.0, 45.0, 359.5, -30.0, 725.0] + list(rng.uniform(-400, 400, 8)):
+        N = int(rng.integers(0, 5))
+        x = np.concatenate([[rng.normal(), rng.normal(), th], rng.normal(size=2 * N)])
+        u = np.array([rng.uniform(0.0, 2.0), rng.uniform(-20, 20)])
+        xg, Fg = _FilterBase.f(None, x, u)
+        xo, Fo = o.f(x.copy(), u)
+        assert np.array_equal(xg, np.asarray(xo).reshape(-1)) and np.array_equal(Fg, Fo), th
+        assert xg[2] == th + u[1]                                      # f does not wrap (predict does, :50)
+        assert np.array_equal(xg[3:], x[3:]) and Fg.shape == (3 + 2 * N, 3 + 2 * N)
+    x = np.array([0.0, 0.0, 90.0])
+    _, F = _FilterBase.f(None, x, [2.0, 45.0])
+    assert F[0, 2] == -2.0 and F[1, 2] == 0.0                          # sind(90) = 1, cosd(90) = 0 exactly
