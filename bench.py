@@ -42,8 +42,60 @@ def parse():
                     help='deferred downdate: one pass over P per this many observations (1 = every observation; <= 8: within one '
                          'measure, bit-identical to the immediate path; 9..16: terms also stay pending across predict, single GPU)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-streaming-variant', action='store_true', help='skip the secondary defer_m = 8 line')
+    ap.add_argument('--sustained', type=int, default=200, help='extra resident steps timed after the main region (0 = off)')
+    ap.add_argument('--parity-steps', type=int, default=6, help='steps of the parity block (class API vs the matrix-free oracle; 0 = off)')
+    ap.add_argument('--also-80k', type=int, default=1, help='N >= 2 only: add the 80 000-landmark block (BASELINE config 4) to the line')
+    ap.add_argument('--steps-80k', type=int, default=20)
+    ap.add_argument('--kernel-name', default='k_downdate_tma/k_downdate_hyb', help=argparse.SUPPRESS)
     ap.add_argument('--cpu-budget', type=float, default=12.0, help='seconds of CPU work for the cpu_baseline sample')
     return ap.parse_args()
+
+
+def workload_config(N, k):
+    """`config` of the JSON line: names the WORKLOAD only, so that the repo arm and the `--impl reference` arm print the
+    same object (how each arm executes it is in `implementation` / `cpu_baseline`)."""
+    n = 3 + 2 * N
+    return {'workload': ('10k landmarks (P 20003^2 fp64), predict + %d updates per step' % k) if N == 10000 else
+                        '%d landmarks, predict + %d updates per step' % (N, k),
+            'landmarks': N, 'k': k, 'n_state': n,
+            'l2': 'no flush needed: every update touches all of P (%.2f GB fp64 as a full square), far beyond the 126 MB L2 '
+                  'and any CPU cache' % (8.0 * n * n / 1e9)}
+
+
+def use_all_host_threads():
+    """The CPU arms use every host core whatever the launcher left in the environment (torch.distributed.run exports
+    OMP_NUM_THREADS=1, which made the round-1 N >= 2 reference numbers 25x slower than the N = 1 one)."""
+    cores = os.cpu_count() or 1
+    try:
+        import threadpoolctl
+        threadpoolctl.threadpool_limits(limits=cores)
+        blas = sorted({(d.get('internal_api'), d.get('num_threads')) for d in threadpoolctl.threadpool_info()})
+    except Exception as e:                                   # pragma: no cover
+        blas = [('threadpoolctl unavailable: %s' % e, None)]
+    return cores, blas
+
+
+def structured_port(N, k, x, P, us, obs):
+    """Like-for-like CPU number: the same O(n^2) structured algebra the GPU runs, in C on the host threads
+    (oracle/structured.c, pthreads): 1 predict + k updates in full.  NOT the reference's algorithm (that is the dense
+    port); reported beside it in both arms."""
+    try:
+        from oracle import structured as S
+        so = S.EKF_SLAM_UC(capacity_landmarks=N)
+        so.set_state(x, P, np.arange(1, N + 1, dtype=np.float64))
+        r = obs[0][0]
+        so.predict(us[0]); so.update(r[:2], [r[0] * 0.1, r[1] * 5.0], int(r[2]))            # warm the pages
+        t0 = time.perf_counter()
+        so.predict(us[1 % len(us)])
+        for q in range(k):
+            rq = obs[1 % len(obs)][q]
+            so.update(rq[:2], [rq[0] * 0.1, rq[1] * 5.0], int(rq[2]))
+        dt = time.perf_counter() - t0
+        return {'value': k / dt, 'unit': UNIT, 'cores': min(16, os.cpu_count() or 1), 'measured_wall_s': dt,
+                'what': 'oracle/structured.c (5-column O(n^2) form, pthreads): 1 predict + %d updates in full' % k}
+    except Exception as e:                      # test infrastructure missing a compiler must not break the bench line
+        return {'unavailable': str(e)[:120]}
 
 
 def make_inputs(N, k, steps, seed=20261104):
@@ -168,34 +220,20 @@ def cpu_baseline(N, k, x, A, d, us, obs, budget_s):
     """Reference's dense algorithm (oracle port, NumPy/OpenBLAS, all host threads) on a bounded sample."""
     from oracle import cpu_baseline as cb
     from ekf_slam_b200.synth import lowrank_to_dense
+    cores, blas = use_all_host_threads()
     n = 3 + 2 * N
     rate = cb.gemm_rate()
     P = lowrank_to_dense(A, d)
     m = cb.pick_rows(n, budget_s / 3.0, rate)
+    t0 = time.perf_counter()
     t_pred = cb.sampled_predict_seconds(x, P, us[0], 0.2, m)
     r = obs[0][0]
     t_upd, _, _ = cb.sampled_update_seconds(x, P, r[:2], [r[0] * 0.1, r[1] * 5.0], int(r[2]), m)
+    wall = time.perf_counter() - t0
     t_step = t_pred + k * t_upd
-    cores = os.cpu_count()
-    # second CPU number, for scale only: the same O(n^2) structured algebra the GPU runs, in C on the host threads
-    # (oracle/structured.c).  It is NOT the reference's algorithm, so it is reported beside the baseline, not as it.
-    structured = None
-    try:
-        from oracle import structured as S
-        so = S.EKF_SLAM_UC(capacity_landmarks=N)
-        so.set_state(x, P, np.arange(1, N + 1, dtype=np.float64))
-        del P
-        so.predict(us[0]); so.update(r[:2], [r[0] * 0.1, r[1] * 5.0], int(r[2]))            # warm the pages
-        t0 = time.perf_counter()
-        so.predict(us[1 % len(us)])
-        for q in range(k):
-            rq = obs[1 % len(obs)][q]
-            so.update(rq[:2], [rq[0] * 0.1, rq[1] * 5.0], int(rq[2]))
-        structured = {'value': k / (time.perf_counter() - t0), 'unit': UNIT, 'cores': min(16, cores),
-                      'what': 'oracle/structured.c (5-column O(n^2) form, pthreads): 1 predict + %d updates in full' % k}
-    except Exception as e:                      # test infrastructure missing a compiler must not break the bench line
-        structured = {'unavailable': str(e)[:120]}
-    return {'value': k / t_step, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'structured_port': structured,
+    sp = structured_port(N, k, x, P, us, obs)
+    return {'value': k / t_step, 'unit': UNIT, 'cores': cores, 'blas_threads': blas, 'kind': 'port', 'extrapolated': m < n,
+            'measured_wall_s': wall, 'structured_port': sp,
             'sample': 'dense reference algebra (EKF_SLAM.m:47,141-145) at n=%d via NumPy/OpenBLAS: 1 predict + 1 update, '
                       'n^3 products on the first %d of %d output rows scaled by n/m (O(n^2) parts in full); '
                       'step = predict + %d updates; gemm %.0f GFLOP/s' % (n, m, n, k, rate / 1e9),
@@ -209,33 +247,198 @@ def run_reference(args):
         return
     from oracle import cpu_baseline as cb
     from ekf_slam_b200.synth import lowrank_to_dense
+    cores, blas = use_all_host_threads()
     N, k = args.landmarks, args.k
     n = 3 + 2 * N
-    x, A, d, s, lms, us, obs = make_inputs(N, k, max(1, args.steps + args.warmup))
+    x, A, d, s, lms, us, obs = make_inputs(N, k, max(2, args.steps + args.warmup))
     P = lowrank_to_dense(A, d)
     rate = cb.gemm_rate()
     per_step_budget = min(6.0, 150.0 / max(1, args.steps + args.warmup))
     m = cb.pick_rows(n, per_step_budget / 3.0, rate)
     times = []
+    w0 = time.perf_counter()
     for t in range(args.warmup + args.steps):
         r = obs[t][0]
         tp = cb.sampled_predict_seconds(x, P, us[t], 0.2, m)
         tu, _, _ = cb.sampled_update_seconds(x, P, r[:2], [r[0] * 0.1, r[1] * 5.0], int(r[2]), m)
         if t >= args.warmup:
             times.append(tp + k * tu)
+    wall = time.perf_counter() - w0
     t_step = float(np.mean(times))
     val = k / t_step
     sample = ('each step: 1 dense predict + 1 dense update at n=%d, n^3 products on the first %d output rows scaled by '
-              'n/m, update cost x%d observations' % (n, m, k))
-    line = {'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
+              'n/m, update cost x%d observations; %d BLAS threads' % (n, m, k, cores))
+    sp = structured_port(N, k, x, P, us, obs)
+    line = {'impl': 'reference', 'metric': METRIC if N == 10000 else 'EKF updates/sec at %d landmarks' % N, 'value': val, 'unit': UNIT,
+            'n_gpus': args.gpus, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': t_step * 1e3, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': '10k landmarks (P 20003^2 fp64), predict + %d updates per step' % k if N == 10000 else
-                       '%d landmarks, predict + %d updates per step' % (N, k), 'landmarks': N, 'k': k},
-            'cpu_baseline': {'value': val, 'unit': UNIT, 'cores': os.cpu_count(), 'kind': 'port', 'sample': sample},
+            'config': workload_config(N, k),
+            # what the value is: an n/m extrapolation of row-sampled dense products, not a region timed in full
+            'extrapolated': m < n, 'measured_wall_s': wall, 'claimed_s': t_step * args.steps, 'cores': cores, 'blas_threads': blas,
+            'cpu_baseline': {'value': val, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample, 'extrapolated': m < n,
+                             'measured_wall_s': wall, 'structured_port': sp},
+            'cpu_structured': sp,
             'e2e': {'value': val, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line))
+
+
+def measure_filter(E, L, dist, world, rank, local, stream, barrier, N, k, K, W, storage, defer, clocks=None, want_e2e=True,
+                   sustained_steps=0, parity_steps=6):
+    """One large filter of N landmarks (single GPU, or ONE filter in `world` column slabs): resident arm (direct C-ABI calls,
+    inputs resident), end-to-end arm (class API, host buffers, x read back), parity block (class API vs the matrix-free
+    oracle).  Returns the raw measurements; every time is CUDA-event or wall time on this rank (reduced by the caller)."""
+    import torch
+    from ekf_slam_b200.synth import LandmarkStub
+    from types import SimpleNamespace
+    n = 3 + 2 * N
+    x, A, d, s, lms, us, obs = make_inputs(N, k, 2 * (K + W) + sustained_steps)
+
+    def make(cls):
+        if world > 1:      # ONE filter sharded over all ranks (column slabs of P, peer-memory column exchange per batch)
+            return E.shard.create_sharded(cls, dist, local, storage=storage, capacity_landmarks=N, stream=stream, defer_m=defer)
+        return cls(capacity_landmarks=N, storage=storage, device=local, stream=stream, defer_m=defer)
+
+    # ---------------- device-resident arm: direct C-ABI, known correspondence (idx given) ----------------
+    f = make(E.EKF_SLAM)
+    f.set_state_lowrank(x, s, A, d)
+    lib, h = f._lib, f._h
+    Rc = f.Rc
+    zs = [np.asfortranarray(o[:, :2]) for o in obs]
+    Rds = [np.asfortranarray(np.column_stack([o[:, 0] * Rc[0], o[:, 1] * Rc[1]])) for o in obs]
+    ids = [np.ascontiguousarray(o[:, 2].astype(np.int32)) for o in obs]
+
+    def step_resident(t):
+        L.check(h, lib.ekf_predict(h, L.dptr(us[t])))
+        L.check(h, lib.ekf_update_batch(h, k, L.dptr(zs[t]), L.dptr(Rds[t]), L.iptr(ids[t])))
+
+    for t in range(W):
+        step_resident(t)
+    f.flush()
+    f.profile_enable(True)
+    if clocks is not None:
+        clocks.start()                  # before the barrier: NVML start-up must not make rank 0 a straggler inside the timed region
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    th0 = time.perf_counter()
+    for t in range(W, W + K):
+        step_resident(t)
+    f.flush()                                            # cross-step deferral: the last pending terms belong to the timed region
+    host_ms = (time.perf_counter() - th0) * 1e3          # host time to ENQUEUE the K steps (no sync inside)
+    e1.record()
+    barrier()
+    th1 = time.perf_counter()
+    out = {'ms': e0.elapsed_time(e1), 'host_ms': host_ms, 'window': (th0, th1)}
+    out['clk'] = clocks.stop((th0, th1)) if clocks is not None else None
+    dd_ms, dd_n, launches = f.profile_read()
+    xch_ms, xch_n, xch_p2p = f.profile_exchange() if world > 1 else (0.0, 0, False)
+    out.update(dd_ms=dd_ms, dd_n=dd_n, launches=launches, xch_ms=xch_ms, xch_n=xch_n, xch_p2p=xch_p2p,
+               dd_bytes=f.downdate_bytes(), slab=f.shard_info(), pend_cap=f.pend_cap())
+    if sustained_steps > 0:             # same loop, longer: what the rate settles at once the power cap has had time to act
+        f.profile_enable(True)
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for t in range(W + K, W + K + sustained_steps):
+            step_resident(t)
+        f.flush()
+        s1.record()
+        barrier()
+        sd_ms, sd_n, _ = f.profile_read()
+        out['sustained'] = {'steps': sustained_steps, 'ms': s0.elapsed_time(s1), 'k3_avg_launch_ms': sd_ms / max(sd_n, 1)}
+    f.profile_enable(False)
+    assert np.all(np.isfinite(f.x[:3])), 'filter diverged'
+    f.close()
+
+    # ---------------- end-to-end arm: reference-facing class API, host buffers ----------------
+    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
+    if want_e2e:
+        g = make(E.EKF_SLAM_UC)
+        g.set_state_lowrank(x, s, A, d)
+
+        def step_e2e(t):
+            g.predict(us[t])
+            g.measure(None, us[t], LandmarkStub(obs[t], table))
+            return g.x
+
+        for t in range(W):
+            step_e2e(t)
+        g.flush()
+        barrier()
+        t0 = time.perf_counter()
+        for t in range(W, W + K):
+            step_e2e(t)
+        g.flush()
+        barrier()
+        out['e2e_s'] = time.perf_counter() - t0
+        assert all(a[0] == 'update' for a in g.chosen), 'e2e arm appended unexpectedly'
+        g.close()
+
+    # ---------------- parity block: the same class-API loop on a fresh filter vs the matrix-free oracle ----------------
+    # (oracle/lowrank_lazy.py: every row of the current P in O(n) per accumulated outer product, so it also covers the
+    # 80 000-landmark slabs).  Every rank steps the oracle on identical inputs and checks x and sampled rows of ITS slab.
+    if parity_steps > 0:
+        from oracle.lowrank_lazy import LazyLowRankFilter
+        g = make(E.EKF_SLAM_UC)
+        g.set_state_lowrank(x, s, A, d)
+        o = LazyLowRankFilter(x, A, d, s, Rc=g.Rc)
+        want = []
+        for t in range(parity_steps):
+            g.predict(us[t]); g.measure(None, us[t], LandmarkStub(obs[t], table))
+            o.predict(us[t]); want += o.measure_rows(obs[t])
+        _, _, c_lo, c_hi = g.shard_info()
+        c_hi = min(c_hi, n)
+        ex = float(np.linalg.norm(g.x - o.x) / np.linalg.norm(o.x))
+        rng = np.random.default_rng(5 + rank)
+        rows = sorted(set([0, 2, 3 + 2 * (int(obs[0][0][2]) - 1), c_lo, max(c_lo, c_hi - 1)] + [int(v) for v in rng.integers(0, c_hi, 8)]))
+        worst, checked = 0.0, 0
+        for i in rows:
+            j0 = max(c_lo, i) if storage == 'sym' else c_lo      # SYM slab: rows <= column are live
+            if j0 >= c_hi:
+                continue
+            got = g.P_block(i, j0, 1, c_hi - j0)
+            ref = o.block([i], j0, c_hi)
+            worst = max(worst, float(np.linalg.norm(got - ref) / np.linalg.norm(ref)))
+            checked += 1
+        out['parity'] = {'steps': parity_steps, 'updates': len(want), 'actions_identical': bool(g.chosen == want), 'max_rel_x': ex,
+                         'max_rel_P': worst, 'rows_checked': checked}
+        g.close()
+    out['inputs'] = (x, A, d, us, obs)
+    return out
+
+
+def reduce_measurements(torch, dist, world, m, K, k):
+    """MAX over ranks of the timed quantities; the roofline is that of the slowest rank's slab; parity = worst rank."""
+    vals = [m['ms'], m.get('e2e_s', 0.0) * 1e3, m['dd_ms'] / max(m['dd_n'], 1), m.get('sustained', {}).get('ms', 0.0)]
+    tt = torch.tensor(vals, dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    m['ms'], m['e2e_ms'], m['dd_avg_ms'] = float(tt[0]), float(tt[1]), float(tt[2])
+    if 'sustained' in m:
+        m['sustained']['ms'] = float(tt[3])
+    if world > 1:
+        allv = [None] * world
+        dist.all_gather_object(allv, (m['dd_ms'] / max(m['dd_n'], 1), m['dd_bytes'], m['slab'], m.get('parity'), m['xch_ms'] / max(m['xch_n'], 1)))
+        slow = max(allv, key=lambda v: v[0])
+        m['dd_one_ms'], m['dd_bytes'], m['slab'] = slow[0], slow[1], slow[2]
+        m['per_rank'] = [{'k3_avg_launch_ms': v[0], 'k3_bytes': v[1], 'cols': [v[2][2], v[2][3]], 'exchange_avg_ms': v[4]} for v in allv]
+        ps = [v[3] for v in allv if v[3]]
+        if ps:
+            m['parity'] = {'steps': ps[0]['steps'], 'updates': ps[0]['updates'],
+                           'actions_identical': all(p['actions_identical'] for p in ps),
+                           'max_rel_x': max(p['max_rel_x'] for p in ps), 'max_rel_P': max(p['max_rel_P'] for p in ps),
+                           'rows_checked': sum(p['rows_checked'] for p in ps), 'ranks': len(ps)}
+    else:
+        m['dd_one_ms'] = m['dd_ms'] / max(m['dd_n'], 1)
+    return m
+
+
+# ncu --set full captures of the shipped K3 kernels (profiles/): dram__bytes_read.sum + dram__bytes_write.sum per launch.
+# Keyed by (landmarks, storage, world, terms per launch); anything else prints null rather than a number from another kernel.
+NCU_TRAFFIC = {
+}
 
 
 def main():
@@ -254,8 +457,6 @@ def main():
     import torch.distributed as dist
     import ekf_slam_b200 as E
     from ekf_slam_b200 import _lib as L
-    from ekf_slam_b200.synth import LandmarkStub
-    from types import SimpleNamespace
 
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
@@ -265,7 +466,6 @@ def main():
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     N, k, K, W = args.landmarks, args.k, args.steps, args.warmup
     n = 3 + 2 * N
-    x, A, d, s, lms, us, obs = make_inputs(N, k, 2 * (K + W))
     tstream = torch.cuda.Stream()          # non-default stream: torch events and the library share it
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
@@ -276,116 +476,39 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---------------- device-resident arm: direct C-ABI, known correspondence (idx given) ----------------
-    def make(cls):
-        if world > 1:      # ONE filter sharded over all ranks (column slabs of P, NCCL column exchange per batch)
-            return E.shard.create_sharded(cls, dist, local, storage=args.storage, capacity_landmarks=N,
-                                          stream=stream, defer_m=args.defer)
-        return cls(capacity_landmarks=N, storage=args.storage, device=local, stream=stream, defer_m=args.defer)
-
-    f = make(E.EKF_SLAM)
-    f.set_state_lowrank(x, s, A, d)
-    lib, h = f._lib, f._h
-    Rc = f.Rc
-
-    zs = [np.asfortranarray(o[:, :2]) for o in obs]
-    Rds = [np.asfortranarray(np.column_stack([o[:, 0] * Rc[0], o[:, 1] * Rc[1]])) for o in obs]
-    ids = [np.ascontiguousarray(o[:, 2].astype(np.int32)) for o in obs]
-
-    def step_resident(t):
-        L.check(h, lib.ekf_predict(h, L.dptr(us[t])))
-        L.check(h, lib.ekf_update_batch(h, k, L.dptr(zs[t]), L.dptr(Rds[t]), L.iptr(ids[t])))
-
-    for t in range(W):
-        step_resident(t)
-    f.profile_enable(True)
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()                  # before the barrier: NVML start-up must not make rank 0 a straggler inside the timed region
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    th0 = time.perf_counter()
-    for t in range(W, W + K):
-        step_resident(t)
-    f.flush()                                            # cross-step deferral (--defer > 8): the last pending terms belong to the timed region
-    host_ms = (time.perf_counter() - th0) * 1e3          # host time to ENQUEUE the K steps (no sync inside)
-    e1.record()
-    barrier()
-    th1 = time.perf_counter()
-    ms = e0.elapsed_time(e1)
-    clk = clocks.stop((th0, th1)) if rank == 0 else None
-    dd_ms, dd_n, launches = f.profile_read()
-    xch_ms, xch_n, xch_p2p = f.profile_exchange() if world > 1 else (0.0, 0, False)
-    f.profile_enable(False)
-    dd_bytes = f.downdate_bytes()
-    slab = f.shard_info()
-    pose = f.x[:3]
-    assert np.all(np.isfinite(pose)), 'filter diverged'
-    f.close()
-
-    # ---------------- end-to-end arm: reference-facing class API, host buffers ----------------
-    g = make(E.EKF_SLAM_UC)
-    g.set_state_lowrank(x, s, A, d)
-    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
-
-    def step_e2e(t):
-        g.predict(us[t])
-        g.measure(None, us[t], LandmarkStub(obs[t], table))
-        return g.x
-
-    for t in range(W):
-        step_e2e(t)
-    barrier()
-    t0 = time.perf_counter()
-    for t in range(W, W + K):
-        xr = step_e2e(t)
-    g.flush()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    assert all(a[0] == 'update' for a in g.chosen), 'e2e arm appended unexpectedly'
-    g.close()
+    clocks = ClockSampler(local) if rank == 0 else None
+    m = measure_filter(E, L, dist, world, rank, local, stream, barrier, N, k, K, W, args.storage, args.defer, clocks=clocks,
+                       sustained_steps=args.sustained, parity_steps=args.parity_steps)
+    x, A, d, us, obs = m.pop('inputs')
+    m = reduce_measurements(torch, dist, world, m, K, k)
 
     # ---------------- secondary line (single GPU, cross-step deferral only): the same workload with one pass over P per
     # batch of 8 (defer_m = 8), where K3 is a pure streaming kernel -- its HBM fraction is reported beside the main roofline
     streaming = None
-    if world == 1 and args.defer > 8:
-        f8 = E.EKF_SLAM(capacity_landmarks=N, storage=args.storage, device=local, stream=stream, defer_m=8)
-        f8.set_state_lowrank(x, s, A, d)
+    if world == 1 and args.defer > 8 and not args.no_streaming_variant:
+        m8 = measure_filter(E, L, dist, world, rank, local, stream, barrier, N, k, min(K, 100), W, args.storage, 8,
+                            want_e2e=False, parity_steps=0)
+        m8.pop('inputs')
         K8 = min(K, 100)
+        d8 = m8['dd_ms'] / max(m8['dd_n'], 1)
+        streaming = {'defer_m': 8, 'steps': K8, 'updates_per_s': K8 * k / (m8['ms'] * 1e-3), 'ms_per_step': m8['ms'] / K8,
+                     'k3_avg_launch_ms': d8, 'k3_bytes_per_launch': m8['dd_bytes'], 'achieved': m8['dd_bytes'] / (d8 * 1e-3) / 1e9,
+                     'unit': 'GB/s', 'what': 'rank-16 flush, one pass over P per measure(): bit-identical to the immediate path'}
 
-        def step8(t):
-            L.check(f8._h, lib.ekf_predict(f8._h, L.dptr(us[t])))
-            L.check(f8._h, lib.ekf_update_batch(f8._h, k, L.dptr(zs[t]), L.dptr(Rds[t]), L.iptr(ids[t])))
+    # ---------------- secondary block at N >= 2: BASELINE config 4, the 80 000-landmark filter (P 205 GB dense, 102 GB live
+    # in SYM slabs), the size the north star's multi-GPU claim is about
+    big = None
+    if world > 1 and N == 10000 and args.also_80k:
+        try:
+            K80 = args.steps_80k
+            b = measure_filter(E, L, dist, world, rank, local, stream, barrier, 80000, k, K80, 3, 'sym', args.defer,
+                               want_e2e=False, parity_steps=4)
+            b.pop('inputs')
+            b = reduce_measurements(torch, dist, world, b, K80, k)
+            big = b
+        except Exception as e:                      # must not cost the main line
+            big = {'error': str(e)[:200]}
 
-        for t in range(W):
-            step8(t)
-        f8.profile_enable(True)
-        barrier()
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s0.record()
-        for t in range(W, W + K8):
-            step8(t)
-        s1.record()
-        barrier()
-        ms8 = s0.elapsed_time(s1)
-        d8_ms, d8_n, _ = f8.profile_read()
-        b8 = f8.downdate_bytes()
-        f8.close()
-        streaming = {'defer_m': 8, 'steps': K8, 'updates_per_s': K8 * k / (ms8 * 1e-3), 'ms_per_step': ms8 / K8,
-                     'k3_avg_launch_ms': d8_ms / max(d8_n, 1), 'k3_bytes_per_launch': b8,
-                     'achieved': b8 / (d8_ms / max(d8_n, 1) * 1e-3) / 1e9, 'unit': 'GB/s',
-                     'what': 'k_downdate_tma rank-16 flush, one pass over P per measure(): bit-identical to the immediate path'}
-
-    tt = torch.tensor([ms, e2e_s * 1e3, dd_ms / max(dd_n, 1)], dtype=torch.float64, device='cuda')
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms, e2e_ms, dd_avg_ms = float(tt[0]), float(tt[1]), float(tt[2])
-    if world > 1:      # roofline of the slowest rank's slab: gather (avg launch ms, bytes) and take the max-time rank
-        allv = [None] * world
-        dist.all_gather_object(allv, (dd_ms / max(dd_n, 1), dd_bytes, slab))
-        dd_one_ms, dd_bytes, slab = max(allv, key=lambda v: v[0])
-        dd_ms = dd_one_ms * dd_n
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -397,42 +520,68 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get('hbm_gbs', 6650.0))
-    achieved = dd_bytes / (dd_ms / dd_n * 1e-3) / 1e9
-    # observations one K3 launch applies: the batch (<= 8) -- or, single GPU with --defer 9..16, as many whole batches as fit
-    per_pass = min(max(args.defer, 1), k) if (args.defer <= 8 or world > 1) else (min(args.defer, 16) // k) * k if k <= 8 and min(args.defer, 16) >= 2 * k else min(8, k)
+    peak_src = 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)'
+
+    def roofline_of(mm, KK, NN, storage):
+        per_pass = int(round(KK * k / max(mm['dd_n'], 1)))           # observations one K3 launch applied, as executed
+        ach = mm['dd_bytes'] / (mm['dd_one_ms'] * 1e-3) / 1e9
+        key = (NN, storage, world, per_pass)
+        tr = NCU_TRAFFIC.get(key)
+        return {'bound': 'hbm', 'kernel': '%s (rank-%d flush of %d observations in one pass over P)' % (args.kernel_name, 2 * per_pass, per_pass),
+                'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak, 'peak_source': peak_src,
+                'frac_of_8TBps_nominal': ach / 8000.0,
+                'traffic': tr[0] if tr else None, 'traffic_source': tr[1] if tr else None,
+                'algorithmic_bytes_per_launch': mm['dd_bytes'], 'avg_launch_ms': mm['dd_one_ms'], 'launches': mm['dd_n'],
+                'share_of_step': mm['dd_one_ms'] * mm['dd_n'] / mm['ms'], 'observations_per_launch': per_pass,
+                # fp64 tensor-core side of the same launch: 2 flop x rank per live element; measured DMMA peak 37.2 TFLOP/s
+                'fp64_tflops': (mm['dd_bytes'] / 16.0) * 4.0 * per_pass / (mm['dd_one_ms'] * 1e-3) / 1e12, 'fp64_dmma_peak_tflops': 37.2}
+
+    roof = roofline_of(m, K, N, args.storage)
+    per_pass = roof['observations_per_launch']
     line = {
-        'metric': METRIC if N == 10000 else 'EKF updates/sec at %d landmarks' % N, 'value': K * k / (ms * 1e-3), 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W,
-        'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'strong' if world > 1 else 'weak', 'vs_baseline': None, 'dtype': 'f64',
-        'data': 'synthetic',
-        'config': {'workload': '10k landmarks (P 20003^2 fp64), predict + %d updates per step' % k if N == 10000 else
-                   '%d landmarks, predict + %d updates per step' % (N, k),
-                   'landmarks': N, 'k': k, 'storage': args.storage, 'n_state': n, 'defer_m': args.defer if world == 1 else min(args.defer, 8),   # sharded handles clamp to 8 (no cross-step deferral yet)
-                   'downdate': ('one rank-%d pass over P per %d observations (terms stay pending across predict: %d steps per pass)' % (2 * per_pass, per_pass, per_pass // k) if per_pass > k else
-                                'one rank-%d pass over P per %d observations' % (2 * per_pass, per_pass)) if args.defer > 1 else 'one rank-2 pass over P per observation',
-                   'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one exchange of the 3+2k current columns (peer-memory scatter, or NCCL %s with EKF_SHARD_EXCHANGE=nccl); slowest slab cols [%d,%d)' % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', slab[2], slab[3])) if world > 1 else 'single GPU',
-                   'l2': 'no flush needed: each update streams %.2f GB of P, far beyond the 126 MB L2' % (dd_bytes / 2e9)},
-        'roofline': {'bound': 'hbm', 'kernel': 'k_downdate_tma (rank-%d flush: cp.async.bulk staging + FP64 DMMA)' % (2 * per_pass), 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback 6650 (of fallback)',
-                     'frac_of_8TBps_nominal': achieved / 8000.0,
-                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
-                     # of exactly this configuration (profiles/ncu_downdate_r01_final_rank16_raw.csv: 1.629 GB read + 1.551 GB written); null for any other
-                     # defer 16: profiles/ncu_downdate_r01_rank32_raw.csv (1.639 GB read + 1.551 GB written per rank-32 launch)
-                     'traffic': (3.181e9 if args.defer == 8 else 3.191e9 if args.defer == 16 else None) if (N == 10000 and args.storage == 'sym' and k == 8 and world == 1) else None,
-                     'algorithmic_bytes_per_launch': dd_bytes, 'avg_launch_ms': dd_ms / dd_n, 'launches': dd_n,
-                     'share_of_step': dd_ms / ms,
-                     # fp64 tensor-core side of the same launch: 2 flop x rank per live element; measured DMMA peak 37.2 TFLOP/s
-                     'fp64_tflops': (dd_bytes / 16.0) * 4.0 * per_pass / (dd_ms / dd_n * 1e-3) / 1e12, 'fp64_dmma_peak_tflops': 37.2},
-        'exchange': ({'avg_ms': xch_ms / max(xch_n, 1), 'per_step': xch_n / K, 'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if xch_p2p else 'NCCL'} if world > 1 else None),
-        'e2e': {'value': K * k / (e2e_ms * 1e-3), 'unit': UNIT,
+        'metric': METRIC if N == 10000 else 'EKF updates/sec at %d landmarks' % N, 'value': K * k / (m['ms'] * 1e-3), 'unit': UNIT,
+        'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': m['ms'] / K, 'higher_is_better': True,
+        'scaling': 'strong' if world > 1 else 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': workload_config(N, k),
+        'implementation': {
+            'storage': args.storage, 'defer_m': m['pend_cap'],
+            'downdate': ('one rank-%d pass over P per %d observations%s' % (2 * per_pass, per_pass, ' (terms stay pending across predict: %d steps per pass)' % (per_pass // k) if per_pass > k else '')),
+            'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one exchange of the 3+2k current columns '
+                            '(peer-memory scatter; EKF_SHARD_EXCHANGE=nccl: NCCL %s); slowest slab cols [%d,%d)'
+                            % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', m['slab'][2], m['slab'][3])) if world > 1 else 'single GPU',
+            'serial_per_step': 'predict (P0 rows/cols 0-1 + pending slabs), exchange (sharded), k_batch_lin (k dependent linearisations), k_batch_gain'},
+        'roofline': roof,
+        'exchange': ({'avg_ms': m['xch_ms'] / max(m['xch_n'], 1), 'per_step': m['xch_n'] / K,
+                      'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if m['xch_p2p'] else 'NCCL'} if world > 1 else None),
+        'e2e': {'value': K * k / (m['e2e_ms'] * 1e-3), 'unit': UNIT,
                 'h2d_bytes_per_step': int(16 + obs[0].nbytes + k * (24 + 16)), 'd2h_bytes_per_step': int(2 * 8 * n + k * 24),
                 'api': 'EKF_SLAM_UC.predict(u); .measure(laserData,u,landmark_list); read x'},
-        'gpu_launches': int(launches), 'clocks': clk, 'host_enqueue_ms_per_step': host_ms / K,
+        'parity': m.get('parity'),
+        'gpu_launches': int(m['launches']), 'clocks': m['clk'], 'host_enqueue_ms_per_step': m['host_ms'] / K,
     }
+    if world > 1:
+        line['per_rank'] = m.get('per_rank')
+    if 'sustained' in m:
+        sm = m['sustained']
+        line['sustained'] = {'steps': sm['steps'], 'value': sm['steps'] * k / (sm['ms'] * 1e-3), 'unit': UNIT,
+                             'ms_per_step': sm['ms'] / sm['steps'], 'k3_avg_launch_ms': sm['k3_avg_launch_ms'],
+                             'what': 'the same resident loop continued for %d more steps (what the rate settles at under the power cap)' % sm['steps']}
     if streaming is not None:
         streaming['frac'] = streaming['achieved'] / peak
         line['roofline_streaming_variant'] = streaming
+    if big is not None:
+        if 'error' in big:
+            line['scaling_80k'] = big
+        else:
+            K80 = args.steps_80k
+            r80 = roofline_of(big, K80, 80000, 'sym')
+            line['scaling_80k'] = {'workload': workload_config(80000, k), 'storage': 'sym', 'steps': K80, 'warmup': 3,
+                                   'value': K80 * k / (big['ms'] * 1e-3), 'unit': UNIT, 'ms_per_step': big['ms'] / K80,
+                                   'roofline': r80, 'exchange_avg_ms': big['xch_ms'] / max(big['xch_n'], 1),
+                                   'per_rank': big.get('per_rank'), 'parity': big.get('parity')}
     if not args.no_cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(N, k, x, A, d, us, obs, args.cpu_budget)
+        line['cpu_structured'] = line['cpu_baseline'].get('structured_port')
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -699,15 +699,28 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
     //   m == 1: 64 x 16-col stages, 2 consumer sets (v18)   m = 2..4: 64-col tiles, 6 x 8-col stages (v17)
     //   m >= 5: 128-col tiles, 4 x 8-col stages, 4 CTAs/SM (v13)
     const int v = variant >= 0 ? variant : (m == 1 ? 18 : (m <= 4 ? 17 : 13));
-    if (m > 8) {            // cross-step deferral (9..16 pending terms): rank <= 32 flush, 128-col tiles, 4 x 8-col stages
+    if (m > 8) {
+        // cross-step deferral (9..16 pending terms, rank <= 32).  Default: the hybrid kernel with the B operand in its stages
+        // (k_downdate_hyb<KS, 8-col stages, 4 stages, BST, 3 CTAs/SM>): 0.520 ms at 10k SYM = 0.94 of the measured HBM peak,
+        // FULL storage 0.983 ms = 0.996 (profiles/r02/sweep_flush_call1.jsonl); the round-1 TMA-in/TMA-out kernel (0.660 ms,
+        // 0.74) stays selectable (variant 13; 21 = its 64-column 4-CTA/SM shape) and is the fallback without a Bt scratch buffer.
+        bool done = false;
+        if (Bt != nullptr && variant != 13 && variant != 21) {
+            switch ((m + 1) / 2) {
+                case 5: done = launch_dd_hyb_v<5>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+                case 6: done = launch_dd_hyb_v<6>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+                case 7: done = launch_dd_hyb_v<7>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+                default: done = launch_dd_hyb_v<8>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+            }
+        }
+        if (done) return;
         switch ((m + 1) / 2) {
-            // MINB = 3: 72 registers x 288 threads and 70 KB of shared memory both allow 3 CTAs/SM; without the bound the
-            // 8-k-step kernel takes 80 registers -> 2 CTAs/SM and the flush goes from 0.674 to 0.773 ms (profiles/README.md)
+            // MINB = 3: 72 registers x 288 threads and 70 KB of shared memory both allow 3 CTAs/SM
             case 5: launch_dd_tma<5, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             case 6: launch_dd_tma<6, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             case 7: launch_dd_tma<7, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off); break;
             default:
-                if (variant == 21) launch_dd_tma<8, 64, 8, 4, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);   // 56 registers, 51.7 KB: 4 CTAs/SM (0.679 ms vs 0.674)
+                if (variant == 21) launch_dd_tma<8, 64, 8, 4, 1, 4>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 else launch_dd_tma<8, 128, 8, 4, 1, 3>(st, P, ld, n, ncols, sym, Kall, Ball, lds, m, col_off);
                 break;
         }
