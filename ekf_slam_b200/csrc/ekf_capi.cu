@@ -101,6 +101,7 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
     do { if (!(h)) return EKF_EINVAL; } while (0)
 
 static int32_t flush(ekf_handle* h);
+static int32_t exec_sharded(ekf_handle* h);
 #define FLUSH(h) do { int32_t rc__ = flush(h); if (rc__ != EKF_OK) return rc__; } while (0)
 
 // Called after every stream synchronisation: surface what the kernels flagged since the last one.
@@ -326,7 +327,9 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
     h->world = world;
     h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
     h->pend_cap = h->defer;
-    if (world == 1 && p->defer_m > EKF_MAX_DEFER) {
+    // cross-step deferral: single GPU, or SYM column slabs (every rank holds all of K_q and B_q = (P H')', so the exchanged
+    // P0 columns can be corrected by the pending terms on arrival); FULL slabs keep B_q only where its column lives: <= 8
+    if ((world == 1 || p->storage == EKF_STORAGE_SYM) && p->defer_m > EKF_MAX_DEFER) {
         h->pend_cap = p->defer_m > EKF_MAX_PEND ? EKF_MAX_PEND : p->defer_m;
         h->xstep = true;
     }
@@ -439,6 +442,13 @@ extern "C" int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N) {
     return EKF_OK;
 }
 
+extern "C" int32_t ekf_defer_info(ekf_handle* h, int32_t* batch, int32_t* pend_cap) {
+    CKH(h);
+    if (batch) *batch = h->defer;
+    if (pend_cap) *pend_cap = h->pend_cap;
+    return EKF_OK;
+}
+
 extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh) {
     CKH(h);
     h->p.C = C; h->p.Rc[0] = Rc[0]; h->p.Rc[1] = Rc[1]; h->p.s_cost = s_cost; h->p.s_thresh = s_thresh;
@@ -451,6 +461,7 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     if (!u) return fail(h, EKF_EINVAL, "u is null");
     CK(cudaSetDevice(h->p.device));
     if (!h->xstep) FLUSH(h);                 // cross-step deferral keeps the terms pending and transforms them below
+    else if (h->world > 1) { int32_t rcq = exec_sharded(h); if (rcq != EKF_OK) return rcq; }   // x must be final before the motion step
     if (h->async_x) {
         // state half first, on the side stream, as soon as the last writer of x is done (not the flush behind it);
         // covariance half on the main stream with the heading the state half saved (EKF_SLAM.m:42,63-64 use theta before f())
@@ -466,6 +477,11 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         if (h->xstep && h->m_pend > 0) { launch_predict_slabs(h->stream, h->Kd, h->Bd, h->ld, h->m_pend, h->xprev, u[0]); h->launches += 1; }
         CK(cudaGetLastError());
         CK(cudaEventRecord(h->ev_pp, h->stream));   // NOT ev_mx: a reader of x must not wait for this kernel (it sits behind the flush)
+    } else if (h->world > 1 && h->xstep && h->m_pend > 0) {   // single stream, slab: covariance half, slab transform, state half
+        launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+        launch_predict_slabs(h->stream, h->Kd, h->Bd, h->ld, h->m_pend, h->x, u[0]);
+        launch_predict_x(h->stream, h->x, u[0], u[1]);
+        h->launches += 1;
     } else if (h->world > 1)
         launch_predict_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n_of(h), u[0], u[1], h->p.C, sym_of(h));
     else if (h->xstep && h->m_pend > 0) {    // single stream: covariance half, slab transform, then the state half (all see the pre-motion heading)
@@ -544,11 +560,41 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
     return EKF_OK;
 }
 
-// Sharded flush = execute the queued batch: one exchange of the 3 + 2k owner columns, k communication-free
-// linearise/gain steps replicated on every rank, one rank-2k pass over the local slab.
-static int32_t flush_sharded(ekf_handle* h) {
+// Sharded filters queue their observations (h->q) and execute them as batches of <= defer_m:
+//   exec_sharded      one exchange of the 3 + 2k slot columns of P0, then k communication-free linearise/gain steps
+//                     replicated on every rank (x, K_q, B_q final; m_pend grows by k)
+//   downdate_sharded  one rank-2 m_pend pass over the local slab
+// Without cross-step deferral the two always run back to back (flush_sharded).  With it (SYM slabs, defer_m = 9..16) the
+// terms of a batch stay pending across predict exactly as on one GPU: the exchanged columns are raw P0 and every rank
+// corrects them by the pending terms it already holds (k_batch_lin / k_batch_gain with m0), so the slab is streamed
+// once per pend_cap observations.
+static int32_t downdate_sharded(ekf_handle* h) {
+    if (h->m_pend == 0) return EKF_OK;
+    const int ncl = ncols_loc(h);
+    if (ncl > 0) {
+        int32_t rc = prof_begin(h);
+        if (rc != EKF_OK) return rc;
+        launch_downdate(h->stream, h->P, h->ld, n_of(h), ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, h->m_pend, h->c_lo,
+                        h->dd_variant, h->Bt);
+        rc = prof_end(h);
+        if (rc != EKF_OK) return rc;
+        h->dd_launches += 1;
+        h->dd_terms += h->m_pend;
+        h->launches += 1;
+        CK(cudaGetLastError());
+    }
+    h->m_pend = 0;
+    return EKF_OK;
+}
+
+static int32_t exec_sharded(ekf_handle* h) {
     const int k = (int)h->q.size();
     if (k == 0) return EKF_OK;
+    if (h->m_pend + k > h->pend_cap) {      // make room: one pass over the slab for everything pending
+        int32_t rc = downdate_sharded(h);
+        if (rc != EKF_OK) return rc;
+    }
+    const int m0 = h->m_pend;
     const int n = n_of(h);
     SlotSet ss;
     ss.n = 3 + 2 * k;
@@ -557,7 +603,7 @@ static int32_t flush_sharded(ekf_handle* h) {
     int32_t rcx = exchange_cols(h, ss, n);
     if (rcx != EKF_OK) return rcx;
     if (k >= 2 && !getenv("EKF_SHARD_PEROBS")) {
-        // fused: one warp walks the k linearisations on the exchanged (3+2k)^2 block, one grid-wide kernel builds all
+        // fused: one CTA walks the k linearisations on the exchanged (3+2k)^2 block, one grid-wide kernel builds all
         // k gain slabs (replicated on every rank from identical inputs) -- 2 launches per batch
         BatchObs ob;
         ob.k = k;
@@ -566,33 +612,28 @@ static int32_t flush_sharded(ekf_handle* h) {
             ob.z0[m] = o.z0; ob.z1[m] = o.z1; ob.R0[m] = o.R0; ob.R1[m] = o.R1; ob.a[m] = o.a;
         }
         launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n, sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc_cur, h->ld,
-                              h->c_lo, h->c_hi);
+                              h->c_lo, h->c_hi, m0);
         h->launches += 2;
     } else {
-        for (int m = 0; m < k; ++m) {
+        for (int m = 0; m < k; ++m) {       // slab slot m0 + m; cur_col subtracts the m0 + m terms before it
             const ekf_handle::QObs& o = h->q[m];
             launch_lin_gain_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, n, o.a, 3 + 2 * m, o.z0, o.z1, o.R0, o.R1,
-                                  ss, h->Pc_cur, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m, sym_of(h));
+                                  ss, h->Pc_cur, h->ld, h->lin, h->Kd, h->Bd, h->ld, h->Bc, m0 + m, sym_of(h));
         }
         h->launches += 2 * k;
     }
     CK(cudaGetLastError());
-    MARK_X(h);                              // x of the batch is final here, before the slab flush
-    const int ncl = ncols_loc(h);
-    if (ncl > 0) {
-        int32_t rc = prof_begin(h);
-        if (rc != EKF_OK) return rc;
-        launch_downdate(h->stream, h->P, h->ld, n, ncl, sym_of(h), h->Kd, h->Bd + h->c_lo, h->ld, k, h->c_lo, h->dd_variant, h->Bt);
-        rc = prof_end(h);
-        if (rc != EKF_OK) return rc;
-        h->dd_launches += 1;
-        h->dd_terms += k;
-        h->launches += 1;
-        CK(cudaGetLastError());
-    }
+    MARK_X(h);                              // x of the batch is final here, before any slab flush
     h->q.clear();
-    h->m_pend = 0;
+    h->m_pend = m0 + k;
+    if (h->m_pend >= h->pend_cap) return downdate_sharded(h);    // full: same flush points as the single-GPU path (bitwise equal)
     return EKF_OK;
+}
+
+static int32_t flush_sharded(ekf_handle* h) {
+    int32_t rc = exec_sharded(h);
+    if (rc != EKF_OK) return rc;
+    return downdate_sharded(h);
 }
 
 static int32_t flush(ekf_handle* h) {
@@ -634,8 +675,7 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     const int a = 3 + 2 * (idx1 - 1);
     if (h->world > 1) {                   // queue; the batch runs at the next flush point
         h->q.push_back({z[0], z[1], Rdiag[0], Rdiag[1], a});
-        h->m_pend = (int)h->q.size();
-        if (h->m_pend >= h->defer) FLUSH(h);
+        if ((int)h->q.size() >= h->defer) return h->xstep ? exec_sharded(h) : flush_sharded(h);
         return EKF_OK;
     }
     launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
@@ -736,7 +776,8 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
         int32_t rc = ekf_update(h, zi, Ri, idx1[i]);
         if (rc != EKF_OK) return rc;
     }
-    return h->xstep ? EKF_OK : flush(h);
+    if (h->xstep) return h->world > 1 ? exec_sharded(h) : EKF_OK;      // x final; the terms stay pending
+    return flush(h);
 }
 
 // measure() control flow, EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151 (host-driven in this revision).
@@ -857,7 +898,8 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
         int32_t rc = drain();
         if (rc != EKF_OK) return rc;
     }
-    return h->xstep ? EKF_OK : flush(h);                                   // P is whole again when measure() returns (cross-step deferral: at the next getter)
+    if (h->xstep) return h->world > 1 ? exec_sharded(h) : EKF_OK;          // cross-step deferral: P is whole again at the next getter
+    return flush(h);                                                       // P is whole again when measure() returns
 }
 
 // ---------------------------------------------------------------- state access
@@ -865,7 +907,10 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     CKH(h);
     if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
     CK(cudaSetDevice(h->p.device));
-    if (h->world > 1) FLUSH(h);           // sharded: x of queued observations is produced by the batch
+    if (h->world > 1) {                   // sharded: x of queued observations is produced by the batch
+        int32_t rcq = h->xstep ? exec_sharded(h) : flush_sharded(h);
+        if (rcq != EKF_OK) return rcq;
+    }
     cudaStream_t st = h->stream;
     if (h->async_x) {                     // behind the last writer of x, not behind the flush that follows it
         st = h->sx;

@@ -189,7 +189,14 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
     const int gi = tid / ns, gj = tid - gi * ns;                   // this thread's entry of G (tid < ns * ns <= 361)
     const bool gown = tid < ns * ns;
     // m0 = 0: nothing is pending at batch start; m0 > 0 (cross-step deferral): current = stored - the pending terms
-    if (gown) G[gi][gj] = Pc ? Pc[(int64_t)gj * ldc + col[gi]] : ldP_def(P, ld, col[gi], col[gj], sym, Kall, Ball, lds, m0);
+    if (gown) {
+        if (Pc) {       // exchanged raw P0 column (sharded): the pending terms are subtracted here, in ldP_def's order
+            double v = Pc[(int64_t)gj * ldc + col[gi]];
+            const int lo = (sym && col[gi] > col[gj]) ? col[gj] : col[gi], hi = (sym && col[gi] > col[gj]) ? col[gi] : col[gj];
+            for (int q = 0; q < m0; ++q) v = rank2_sub(v, Kall[q * lds + lo], Ball[q * lds + hi]);
+            G[gi][gj] = v;
+        } else G[gi][gj] = ldP_def(P, ld, col[gi], col[gj], sym, Kall, Ball, lds, m0);
+    }
     if (tid < ns) xs[tid] = x[col[tid]];
     const bool gup = gown && (!sym || col[gi] <= col[gj]);         // SYM: the live element is (min, max)
     __syncthreads();
@@ -255,7 +262,7 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
     for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
         ((double*)&L)[e] = ((const double*)lin)[e];
     const int k = ob.k, ns = 3 + 2 * k;
-    const bool pend = m0 > 0 && !Pc;                               // cross-step deferral: current = stored - pending terms
+    const bool pend = m0 > 0;                                      // cross-step deferral: current = stored (or exchanged) P0 - pending terms
     if (pend)
         for (int e = threadIdx.x; e < m0 * ns; e += blockDim.x) {
             const int q = e / ns, sl = e - q * ns;

@@ -265,6 +265,12 @@ class _FilterBase:
     def flush(self):
         self._ck(self._lib.ekf_flush(self._h))
 
+    def pend_cap(self):
+        """Rank-2 terms that may be pending before a pass over P is forced (what defer_m became on this handle)."""
+        b, c = ct.c_int32(), ct.c_int32()
+        self._ck(self._lib.ekf_defer_info(self._h, ct.byref(b), ct.byref(c)))
+        return c.value
+
     def sync(self):
         self._ck(self._lib.ekf_sync(self._h))
 

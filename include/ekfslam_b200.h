@@ -58,7 +58,7 @@ typedef struct ekf_params {
     int32_t  storage;            /* EKF_STORAGE_* */
     int32_t  capacity_landmarks; /* P is allocated once at 3+2*capacity (reference reallocates per append, EKF_SLAM.m:91) */
     int32_t  device;             /* CUDA device ordinal */
-    int32_t  defer_m;            /* <=1: one pass over P per observation; 2..8: deferred, one rank-2m pass per m observations (same sequence of linearisations, bit-identical); 9..16 (single GPU): terms also stay pending across ekf_predict, which transforms them (K_q <- F K_q, B_q <- B_q F'): equal to rounding, not bit for bit */
+    int32_t  defer_m;            /* <=1: one pass over P per observation; 2..8: deferred, one rank-2m pass per m observations (same sequence of linearisations, bit-identical); 9..16 (single GPU, or SYM slabs of a sharded filter): terms also stay pending across ekf_predict, which transforms them (K_q <- F K_q, B_q <- B_q F'): equal to rounding, not bit for bit */
     uint64_t stream;             /* cudaStream_t to enqueue on, 0 = library creates one */
 } ekf_params;
 
@@ -144,6 +144,9 @@ int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo);
 /* Property writes (public, mutable after construction in the reference). */
 int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh);
 
+/* What the handle does with defer_m: *batch = observations linearised per fused batch (<= 8), *pend_cap = rank-2 terms
+ * that may be pending before a pass over P is forced (> 8: cross-step deferral is on). */
+int32_t ekf_defer_info(ekf_handle* h, int32_t* batch, int32_t* pend_cap);
 /* Apply any deferred (defer_m > 1) rank-2 terms to P now.  predict, append, getters of P and the end of
  * ekf_measure_batch flush implicitly; ekf_update flushes when defer_m terms are pending.  With defer_m = 9..16 predict and
  * the end of ekf_measure_batch / ekf_update_batch do NOT flush (append, mode-B association and the getters of P still do). */

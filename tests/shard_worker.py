@@ -113,6 +113,49 @@ def main():
         assert np.array_equal(slab * mk, Pref[:, c_lo:c_lo + slab.shape[1]] * mk), rel(slab * mk, Pref[:, c_lo:c_lo + slab.shape[1]] * mk)
         print('rank %d populated 1k/%s: slab bit-identical to the single-GPU path' % (rank, storage), flush=True)
         g.close(); ref.close()
+
+    # (c) cross-step deferral on SYM slabs (defer_m = 16: terms stay pending across predict, the exchanged P0 columns are
+    # corrected by the pending terms on arrival): bitwise equal to the single-GPU defer-16 path, x read mid-run included
+    N = 1000
+    x, A, d, s, lms = synthetic_spd_state(N, seed=3)
+    g = E.shard.create_sharded(E.EKF_SLAM, dist, local, storage='sym', capacity_landmarks=N, defer_m=16)
+    ref = E.EKF_SLAM(capacity_landmarks=N, storage='sym', device=local, defer_m=16)
+    assert g.pend_cap() == 16 and ref.pend_cap() == 16
+    for f in (g, ref):
+        f.set_state_lowrank(x, s, A, d)
+    rng = np.random.default_rng(12)
+    for step in range(9):
+        rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:(8, 11, 5, 8, 1, 8, 8, 3, 8)[step]]
+        Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+        for f in (g, ref):
+            f.predict([0.3, 1.0])
+            if step == 4:
+                f.update(rows[0, :2], Rd[0], int(rows[0, 2]))
+            else:
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+        if step % 3 == 1:
+            assert np.array_equal(g.x, ref.x), (step, rel(g.x, ref.x))
+    slab, c_lo = g.P_slab()
+    Pref = ref.P
+    assert np.array_equal(g.x, ref.x), rel(g.x, ref.x)
+    mk = live(slab, c_lo, 'sym')
+    assert np.array_equal(slab * mk, Pref[:, c_lo:c_lo + slab.shape[1]] * mk), rel(slab * mk, Pref[:, c_lo:c_lo + slab.shape[1]] * mk)
+    print('rank %d populated 1k/sym defer 16 (cross-step deferral on slabs): slab bit-identical to the single-GPU path' % rank, flush=True)
+    g.close(); ref.close()
+    # and the full loop with appends and associations against the oracle
+    w = make_world(N=20, T=300, k=5, mode='nearest')
+    g = E.shard.create_sharded(E.EKF_SLAM_UC, dist, local, storage='sym', capacity_landmarks=20, defer_m=16)
+    o = O.EKF_SLAM_UC()
+    for t in range(w.T):
+        g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
+        o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
+    assert g.chosen == o.chosen
+    slab, c_lo = g.P_slab()
+    mk = live(slab, c_lo, 'sym')
+    ex, eP = rel(g.x, o.x), rel(slab * mk, o.P[:, c_lo:c_lo + slab.shape[1]] * mk)
+    assert ex <= 1e-9 and eP <= 1e-9, (rank, ex, eP)
+    print('rank %d UC loop sym defer 16: rel err x %.2e P %.2e' % (rank, ex, eP), flush=True)
+    g.close()
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
