@@ -438,6 +438,8 @@ def reduce_measurements(torch, dist, world, m, K, k):
 # ncu --set full captures of the shipped K3 kernels (profiles/): dram__bytes_read.sum + dram__bytes_write.sum per launch.
 # Keyed by (landmarks, storage, world, terms per launch); anything else prints null rather than a number from another kernel.
 NCU_TRAFFIC = {
+    (10000, 'sym', 1, 16): (1.645896e9 + 1.552833e9, 'profiles/ncu_downdate_r02_hyb_rank32_raw.csv: k_downdate_hyb<8,8,4,1,3>, ncu --set full at commit b2987cd (506.7 us under ncu)'),
+    (10000, 'sym', 1, 8): (1.629e9 + 1.551e9, 'profiles/ncu_downdate_r01_final_rank16_raw.csv: k_downdate_tma<4,128,8,4,1> (kernel unchanged since round 1)'),
 }
 
 

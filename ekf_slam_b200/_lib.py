@@ -39,6 +39,7 @@ SIGNATURES = {
     'ekf_destroy': [_H],
     'ekf_nccl_unique_id': [C.POINTER(C.c_uint8)],
     'ekf_create_sharded': [C.POINTER(EkfParams), C.c_int32, C.c_int32, C.POINTER(C.c_uint8), C.POINTER(_H)],
+    'ekf_create_multi': [C.POINTER(EkfParams), C.c_int32, _IP, C.POINTER(_H)],
     'ekf_shard_info': [_H, _IP, _IP, _IP, _IP],
     'ekf_slab_range': [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _IP, _IP],
     'ekf_update_batch': [_H, C.c_int32, _DP, _DP, _IP],

@@ -32,6 +32,11 @@ struct ekf_handle {
     // ---- column-slab sharding (world > 1): this rank stores columns [c_lo, c_hi) of P, FULL storage ----
     int rank = 0, world = 1;
     int c_lo = 0, c_hi = 0;
+    // ---- single-process multi-device filter (ekf_create_multi): the FRONT handle owns one sub-handle per device and fans
+    // every call out to them; a sub-handle is an ordinary slab handle whose peers live in the same process (direct peer
+    // pointers after cudaDeviceEnablePeerAccess, no cudaIpc, no NCCL)
+    std::vector<ekf_handle*> subs;
+    bool in_process = false;   // sub-handle of a multi front: peers are plain pointers
     ncclComm_t comm = nullptr;
     double* Pc = nullptr;      // 2 x EKF_MAX_SLOTS x ld: exchanged columns of the current batch (double-buffered by batch parity)
     double* Pc_cur = nullptr;  // buffer holding the batch being consumed
@@ -227,11 +232,17 @@ extern "C" int32_t ekf_params_default(ekf_params* p, int32_t variant) {
 
 extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (!h) return EKF_OK;
+    if (!h->subs.empty()) {
+        for (ekf_handle* sh : h->subs) { cudaSetDevice(sh->p.device); if (sh->stream) cudaStreamSynchronize(sh->stream); }
+        for (ekf_handle* sh : h->subs) ekf_destroy(sh);
+        delete h;
+        return EKF_OK;
+    }
     cudaSetDevice(h->p.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd); cudaFree(h->Bt);
-    for (int g = 0; g < h->world && h->p2p; ++g)
+    for (int g = 0; g < h->world && h->p2p && !h->in_process; ++g)
         if (g != h->rank) { if (h->peers.pc[g]) cudaIpcCloseMemHandle(h->peers.pc[g]); if (h->peers.flags[g]) cudaIpcCloseMemHandle(h->peers.flags[g]); }
     for (auto e : h->xev) cudaEventDestroy(e);
     cudaFree(h->Pc); cudaFree(h->Bc); cudaFree(h->xflags); cudaFree(h->xticket);
@@ -308,10 +319,11 @@ static int32_t setup_p2p(ekf_handle* h) {
     return EKF_OK;
 }
 
-static int32_t create_common(const ekf_params* p, int rank, int world, const uint8_t* id128, ekf_handle** out) {
+static int32_t create_common(const ekf_params* p, int rank, int world, const uint8_t* id128, ekf_handle** out,
+                             bool in_process = false) {
     if (!p || !out || p->capacity_landmarks < 1) return EKF_EINVAL;
     *out = nullptr;
-    if (world < 1 || rank < 0 || rank >= world || (world > 1 && !id128)) return EKF_EINVAL;
+    if (world < 1 || rank < 0 || rank >= world || (world > 1 && !id128 && !in_process)) return EKF_EINVAL;
     if (world > 1 && p->capacity_landmarks < world) {
         fprintf(stderr, "ekfslam_b200: sharded filters need capacity_landmarks >= world\n");
         return EKF_EINVAL;
@@ -325,6 +337,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
     h->p = *p;
     h->rank = rank;
     h->world = world;
+    h->in_process = in_process;
     h->defer = p->defer_m < 1 ? 1 : (p->defer_m > EKF_MAX_DEFER ? EKF_MAX_DEFER : p->defer_m);
     h->pend_cap = h->defer;
     // cross-step deferral: single GPU, or SYM column slabs (every rank holds all of K_q and B_q = (P H')', so the exchanged
@@ -342,7 +355,15 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         h->ld = ((int64_t)h->cap_n + 15) / 16 * 16;
         ekf_slab_range(p->capacity_landmarks, world, rank, p->storage, &h->c_lo, &h->c_hi);
         CK(cudaMalloc(&h->P, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
-        if (world > 1) {
+        if (world > 1 && in_process) {       // peers are wired by ekf_create_multi once every sub-handle exists
+            CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS * 2));
+            h->Pc_cur = h->Pc;
+            CK(cudaMalloc(&h->Bc, sizeof(double2) * EKF_MAX_DEFER * EKF_MAX_SLOTS));
+            CK(cudaMalloc(&h->xflags, sizeof(int) * EKF_MAX_PEERS));
+            CK(cudaMemset(h->xflags, 0, sizeof(int) * EKF_MAX_PEERS));
+            CK(cudaMalloc(&h->xticket, sizeof(unsigned int)));
+            CK(cudaMemset(h->xticket, 0, sizeof(unsigned int)));
+        } else if (world > 1) {
             if (!nccl_load(h->err)) return EKF_ENCCL;
             CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS * 2));
             h->Pc_cur = h->Pc;
@@ -417,6 +438,77 @@ extern "C" int32_t ekf_create_sharded(const ekf_params* p, int32_t rank, int32_t
     return create_common(p, rank, world, id128, out);
 }
 
+// One process, G devices (SURVEY 8(b) "Threading": MATLAB calls MEX from its single interpreter thread, so a sharded
+// filter under MATLAB cannot be one process per GPU).  The front handle owns G ordinary slab handles and makes every
+// call on each of them in turn; all work is asynchronous on the devices' streams, so the G slabs run concurrently.  The
+// per-batch column exchange is the same peer-memory scatter as in the multi-process path, with the peers' buffers
+// addressed directly (cudaDeviceEnablePeerAccess) instead of through cudaIpc handles; no NCCL is involved.
+extern "C" int32_t ekf_create_multi(const ekf_params* p, int32_t n_devices, const int32_t* devices, ekf_handle** out) {
+    if (!p || !out || n_devices < 1 || n_devices > EKF_MAX_PEERS) return EKF_EINVAL;
+    *out = nullptr;
+    if (n_devices == 1) {
+        ekf_params q = *p;
+        if (devices) q.device = devices[0];
+        return ekf_create(&q, out);
+    }
+    if (p->stream != 0) { fprintf(stderr, "ekfslam_b200: ekf_create_multi creates its own streams (params.stream must be 0)\n"); return EKF_EINVAL; }
+    for (int g = 0; g < n_devices; ++g)
+        for (int q = 0; q < g; ++q)
+            if ((devices ? devices[g] : g) == (devices ? devices[q] : q)) {
+                fprintf(stderr, "ekfslam_b200: ekf_create_multi needs %d distinct devices (slabs that wait on each other must not share a GPU)\n", n_devices);
+                return EKF_EINVAL;
+            }
+    ekf_handle* f = new ekf_handle();
+    f->p = *p;
+    f->world = n_devices;
+    int32_t rc = EKF_OK;
+    for (int g = 0; g < n_devices && rc == EKF_OK; ++g) {
+        ekf_params q = *p;
+        q.device = devices ? devices[g] : g;
+        ekf_handle* sh = nullptr;
+        rc = create_common(&q, g, n_devices, nullptr, &sh, true);
+        if (rc == EKF_OK) f->subs.push_back(sh);
+    }
+    for (int g = 0; g < n_devices && rc == EKF_OK; ++g) {      // wire the peers: every slab sees every slab's Pc and flag words
+        ekf_handle* sh = f->subs[g];
+        cudaSetDevice(sh->p.device);
+        memset(&sh->peers, 0, sizeof(sh->peers));
+        sh->peers.world = n_devices; sh->peers.rank = g;
+        for (int q = 0; q < n_devices; ++q) {
+            if (q != g) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, sh->p.device, f->subs[q]->p.device);
+                cudaError_t e = can ? cudaDeviceEnablePeerAccess(f->subs[q]->p.device, 0) : cudaErrorInvalidDevice;
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                    fprintf(stderr, "ekfslam_b200: ekf_create_multi: device %d cannot map device %d (peer access is required)\n",
+                            sh->p.device, f->subs[q]->p.device);
+                    rc = EKF_ECUDA;
+                }
+                cudaGetLastError();
+            }
+            sh->peers.pc[q] = f->subs[q]->Pc;
+            sh->peers.flags[q] = f->subs[q]->xflags;
+        }
+        sh->p2p = true;
+    }
+    if (rc != EKF_OK) { ekf_destroy(f); return rc; }
+    ekf_handle* s0 = f->subs[0];
+    f->defer = s0->defer; f->pend_cap = s0->pend_cap; f->xstep = s0->xstep;
+    f->cap_n = s0->cap_n; f->ld = s0->ld; f->c_lo = 0; f->c_hi = s0->cap_n;
+    *out = f;
+    return EKF_OK;
+}
+
+// Multi front: make `call` on every sub-handle; the first failure is returned with that sub-handle's message.
+#define FAN_OUT(h, sh, call)                                                                       \
+    do {                                                                                           \
+        for (ekf_handle* sh : (h)->subs) {                                                         \
+            int32_t rc__ = (call);                                                                 \
+            if (rc__ != EKF_OK) { (h)->err = "device " + std::to_string(sh->p.device) + ": " + sh->err; return rc__; }   \
+        }                                                                                          \
+    } while (0)
+static inline bool is_front(const ekf_handle* h) { return !h->subs.empty(); }
+
 extern "C" int32_t ekf_shard_info(ekf_handle* h, int32_t* rank, int32_t* world, int32_t* c_lo, int32_t* c_hi) {
     CKH(h);
     if (rank) *rank = h->rank;
@@ -430,6 +522,7 @@ extern "C" const char* ekf_last_error(ekf_handle* h) { return h ? h->err.c_str()
 
 extern "C" int32_t ekf_sync(ekf_handle* h) {
     CKH(h);
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_sync(sh)); return EKF_OK; }
     CK(cudaStreamSynchronize(h->stream));
     if (h->sx) CK(cudaStreamSynchronize(h->sx));
     return after_sync(h);
@@ -444,13 +537,14 @@ extern "C" int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N) {
 
 extern "C" int32_t ekf_defer_info(ekf_handle* h, int32_t* batch, int32_t* pend_cap) {
     CKH(h);
-    if (batch) *batch = h->defer;
+    if (batch) *batch = h->defer;          // (a multi front mirrors its sub-handles' values)
     if (pend_cap) *pend_cap = h->pend_cap;
     return EKF_OK;
 }
 
 extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh) {
     CKH(h);
+    if (is_front(h)) FAN_OUT(h, sh, ekf_set_noise(sh, C, Rc, s_cost, s_thresh));
     h->p.C = C; h->p.Rc[0] = Rc[0]; h->p.Rc[1] = Rc[1]; h->p.s_cost = s_cost; h->p.s_thresh = s_thresh;
     return EKF_OK;
 }
@@ -459,6 +553,7 @@ extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], do
 extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     CKH(h);
     if (!u) return fail(h, EKF_EINVAL, "u is null");
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_predict(sh, u)); return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     if (!h->xstep) FLUSH(h);                 // cross-step deferral keeps the terms pending and transforms them below
     else if (h->world > 1) { int32_t rcq = exec_sharded(h); if (rcq != EKF_OK) return rcq; }   // x must be final before the motion step
@@ -637,6 +732,7 @@ static int32_t flush_sharded(ekf_handle* h) {
 }
 
 static int32_t flush(ekf_handle* h) {
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_flush(sh)); return EKF_OK; }
     if (h->world > 1) return flush_sharded(h);
     if (h->m_pend == 0) return EKF_OK;
     if (h->prof) {
@@ -662,6 +758,7 @@ static int32_t flush(ekf_handle* h) {
 
 extern "C" int32_t ekf_flush(ekf_handle* h) {
     CKH(h);
+    if (is_front(h)) return flush(h);
     CK(cudaSetDevice(h->p.device));
     return flush(h);
 }
@@ -671,6 +768,7 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     if (!z || !Rdiag) return fail(h, EKF_EINVAL, "null argument");
     if (idx1 < 1 || idx1 > h->N)      // MATLAB would raise "index exceeds array bounds" at EKF_SLAM.m:125
         return fail(h, EKF_EINVAL, "ekf_update: landmark index " + std::to_string(idx1) + " outside 1.." + std::to_string(h->N));
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_update(sh, z, Rdiag, idx1)); return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     const int a = 3 + 2 * (idx1 - 1);
     if (h->world > 1) {                   // queue; the batch runs at the next flush point
@@ -694,6 +792,7 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
     if (!u || !Rdiag || !pos) return fail(h, EKF_EINVAL, "null argument");
     if (h->N >= h->p.capacity_landmarks)
         return fail(h, EKF_ECAPACITY, "ekf_append: capacity_landmarks=" + std::to_string(h->p.capacity_landmarks) + " reached");
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_append(sh, u, Rdiag, pos, signature)); h->N += 1; return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     if (h->world > 1) {                   // the new rows need P(:,1:3): one 3-column broadcast from rank 0
@@ -718,6 +817,11 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
     CKH(h);
     if (!z || !Rdiag || !newLL || !idx1) return fail(h, EKF_EINVAL, "null argument");
     if (h->N == 0) { *newLL = 1; *idx1 = 1; return EKF_OK; }   // Correspondence.m:33,40 with an empty loop
+    if (is_front(h)) {                     // mode A reads only s, which every slab holds
+        int32_t rcf = ekf_associate(h->subs[0], z, Rdiag, newLL, idx1);
+        if (rcf != EKF_OK) h->err = h->subs[0]->err;
+        return rcf;
+    }
     CK(cudaSetDevice(h->p.device));
     if (h->world > 1 && h->p.assoc_mode == EKF_ASSOC_POSITION)
         return fail(h, EKF_EINVAL, "ekf_associate: position-cost association is not available on a sharded filter");
@@ -743,6 +847,13 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
 extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, const double* Rdiag, const int32_t* idx1) {
     CKH(h);
     if (k < 0 || (k > 0 && (!z || !Rdiag || !idx1))) return fail(h, EKF_EINVAL, "null argument");
+    if (is_front(h)) {
+        for (int j = 0; j < k; ++j)
+            if (idx1[j] < 1 || idx1[j] > h->N)
+                return fail(h, EKF_EINVAL, "ekf_update_batch: landmark index " + std::to_string(idx1[j]) + " outside 1.." + std::to_string(h->N));
+        FAN_OUT(h, sh, ekf_update_batch(sh, k, z, Rdiag, idx1));
+        return EKF_OK;
+    }
     CK(cudaSetDevice(h->p.device));
     int i = 0;
     if (h->world == 1 && h->defer >= 2 && k >= 2) {
@@ -820,20 +931,21 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
     // Mode-A associations of rows [from, k) against the current s, <= EKF_ASSOC_BATCH per launch + one D2H copy.
     const bool batch_assoc = h->p.variant == EKF_VARIANT_UC && h->p.assoc_mode == EKF_ASSOC_SIGNATURE;
     int assoc_from = 0, assoc_to = 0;                                      // h_res[j - assoc_from] valid for j in [from, to)
+    ekf_handle* dv = is_front(h) ? h->subs[0] : h;                         // device-side resources (a multi front: s is replicated on every slab)
     auto associate_ahead = [&](int from) -> int32_t {
         AssocBatchZ zb;
         const int cnt = std::min(k - from, EKF_ASSOC_BATCH);
         for (int j = 0; j < cnt; ++j) zb.z2[j] = obs[from + j + 2 * k];
-        CK(cudaSetDevice(h->p.device));
-        cudaStream_t st = h->stream;
-        if (h->async_x) {                   // mode A reads only s (written by append): no need to wait for a flush
-            st = h->sx;
-            CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
+        CK(cudaSetDevice(dv->p.device));
+        cudaStream_t st = dv->stream;
+        if (dv->async_x) {                  // mode A reads only s (written by append): no need to wait for a flush
+            st = dv->sx;
+            CK(cudaStreamWaitEvent(st, dv->ev_mx, 0));
         }
-        launch_associate_sig_batch(st, h->s, h->N, zb, cnt, h->p.s_cost, h->p.s_thresh, h->d_res);
-        h->launches += 1;
+        launch_associate_sig_batch(st, dv->s, dv->N, zb, cnt, h->p.s_cost, h->p.s_thresh, dv->d_res);
+        dv->launches += 1;
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult) * cnt, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(dv->h_res, dv->d_res, sizeof(AssocResult) * cnt, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         assoc_from = from; assoc_to = from + cnt;
         return EKF_OK;
@@ -867,8 +979,8 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
                 if (ii - 1 >= assoc_to || ii - 1 < assoc_from) {
                     if ((rc = associate_ahead(ii - 1)) != EKF_OK) return rc;
                 }
-                newLL = h->h_res[ii - 1 - assoc_from].newLL;               // EKF_SLAM_UC.m:119
-                idx = h->h_res[ii - 1 - assoc_from].index1;
+                newLL = dv->h_res[ii - 1 - assoc_from].newLL;              // EKF_SLAM_UC.m:119
+                idx = dv->h_res[ii - 1 - assoc_from].index1;
             } else {
                 if ((rc = drain()) != EKF_OK) return rc;                   // mode B scores against the current x, P
                 rc = ekf_associate(h, z, Rd, &newLL, &idx);                // EKF_SLAM_UC.m:119
@@ -898,7 +1010,7 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
         int32_t rc = drain();
         if (rc != EKF_OK) return rc;
     }
-    if (h->xstep) return h->world > 1 ? exec_sharded(h) : EKF_OK;          // cross-step deferral: P is whole again at the next getter
+    if (h->xstep) return (h->world > 1 && !is_front(h)) ? exec_sharded(h) : EKF_OK;   // cross-step deferral: P is whole again at the next getter
     return flush(h);                                                       // P is whole again when measure() returns
 }
 
@@ -906,6 +1018,16 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
 extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     CKH(h);
     if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
+    if (is_front(h)) {                    // every slab executes its queued batch (they wait for each other's columns), then slab 0 answers
+        for (ekf_handle* sh : h->subs) {
+            cudaSetDevice(sh->p.device);
+            int32_t rcq = sh->xstep ? exec_sharded(sh) : flush_sharded(sh);
+            if (rcq != EKF_OK) { h->err = sh->err; return rcq; }
+        }
+        int32_t rcf = ekf_get_x(h->subs[0], x, len);
+        if (rcf != EKF_OK) h->err = h->subs[0]->err;
+        return rcf;
+    }
     CK(cudaSetDevice(h->p.device));
     if (h->world > 1) {                   // sharded: x of queued observations is produced by the batch
         int32_t rcq = h->xstep ? exec_sharded(h) : flush_sharded(h);
@@ -925,6 +1047,7 @@ extern "C" int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len) {
     CKH(h);
     if (h->N == 0) return EKF_OK;
     if (!s || len < h->N) return fail(h, EKF_EINVAL, "ekf_get_s: buffer too small");
+    if (is_front(h)) { int32_t rcf = ekf_get_s(h->subs[0], s, len); if (rcf != EKF_OK) h->err = h->subs[0]->err; return rcf; }
     CK(cudaSetDevice(h->p.device));
     CK(cudaMemcpyAsync(s, h->s, sizeof(double) * h->N, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
@@ -935,6 +1058,14 @@ extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
     CKH(h);
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_get_P: lda < n");
+    if (is_front(h)) {                    // assemble the slabs; SYM slabs hold rows <= column: mirror on the host
+        int32_t rcf = ekf_get_P_block(h, 0, 0, n, n, P, lda);
+        if (rcf != EKF_OK) return rcf;
+        if (sym_of(h))
+            for (int j = 0; j < n; ++j)
+                for (int i = j + 1; i < n; ++i) P[(size_t)i + (size_t)j * lda] = P[(size_t)j + (size_t)i * lda];
+        return EKF_OK;
+    }
     if (h->world > 1) return fail(h, EKF_EINVAL, "ekf_get_P: sharded filter, read the local slab with ekf_get_P_block");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
@@ -951,6 +1082,16 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
     const int n = n_of(h);
     if (!out || r0 < 0 || c0 < 0 || nr < 1 || nc < 1 || r0 + nr > n || c0 + nc > n || ldo < nr)
         return fail(h, EKF_EINVAL, "ekf_get_P_block: bad block");
+    if (is_front(h)) {                    // every slab delivers the columns it stores
+        FAN_OUT(h, sh, ekf_flush(sh));    // all of them first: a flush executes queued batches, which exchange columns
+        for (ekf_handle* sh : h->subs) {
+            const int lo = std::max(c0, sh->c_lo), hi = std::min(c0 + nc, std::min(sh->c_hi, n));
+            if (hi <= lo) continue;
+            int32_t rcf = ekf_get_P_block(sh, r0, lo, nr, hi - lo, out + (size_t)(lo - c0) * ldo, ldo);
+            if (rcf != EKF_OK) { h->err = sh->err; return rcf; }
+        }
+        return EKF_OK;
+    }
     if (c0 < h->c_lo || c0 + nc > h->c_hi)
         return fail(h, EKF_EINVAL, "ekf_get_P_block: columns outside this rank's slab [" + std::to_string(h->c_lo) + "," +
                                        std::to_string(h->c_hi) + ")");
@@ -968,7 +1109,7 @@ extern "C" int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo) {
     CKH(h);
     const int nb = h->N + 1;
     if (!out || ldo < nb) return fail(h, EKF_EINVAL, "ekf_get_ellipses: buffer too small");
-    if (h->world > 1) return fail(h, EKF_EINVAL, "ekf_get_ellipses: not available on a sharded filter (diagonal blocks live on different ranks)");
+    if (h->world > 1 || is_front(h)) return fail(h, EKF_EINVAL, "ekf_get_ellipses: not available on a sharded filter (diagonal blocks live on different ranks)");
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     double* d = nullptr;
@@ -988,6 +1129,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     if (N < 0 || N > h->p.capacity_landmarks) return fail(h, EKF_ECAPACITY, "ekf_set_state: N beyond capacity");
     const int n = 3 + 2 * N;
     if (!x || !P || lda < n || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state: bad argument");
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_set_state(sh, x, P, lda, s, N)); h->N = N; return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
     CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
@@ -1014,6 +1156,11 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
 extern "C" int32_t ekf_set_x(ekf_handle* h, const double* x, int32_t len) {
     CKH(h);
     if (!x || len != n_of(h)) return fail(h, EKF_EINVAL, "ekf_set_x: expected " + std::to_string(n_of(h)) + " elements (3 + 2 N); use ekf_set_state to change the number of landmarks");
+    if (is_front(h)) {                    // enqueue every slab's flush first: a flush exchanges columns, and set_x synchronises
+        FAN_OUT(h, sh, ekf_flush(sh));
+        FAN_OUT(h, sh, ekf_set_x(sh, x, len));
+        return EKF_OK;
+    }
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);                             // sharded handles: queued observations still have to read the old x
     CK(cudaStreamSynchronize(h->stream));
@@ -1028,6 +1175,7 @@ extern "C" int32_t ekf_set_s(ekf_handle* h, const double* s, int32_t len) {
     CKH(h);
     if (len != h->N || (len > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_s: expected " + std::to_string(h->N) + " signatures");
     if (len == 0) return EKF_OK;
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_set_s(sh, s, len)); return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     CK(cudaStreamSynchronize(h->stream));
     if (h->sx) CK(cudaStreamSynchronize(h->sx));
@@ -1041,6 +1189,7 @@ extern "C" int32_t ekf_set_P(ekf_handle* h, const double* P, int32_t lda) {
     CKH(h);
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_set_P: lda < n");
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_flush(sh)); FAN_OUT(h, sh, ekf_set_P(sh, P, lda)); return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     const int hi = std::min(h->c_hi, n);  // a sharded handle keeps its own columns of the caller's full matrix
@@ -1058,6 +1207,7 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     if (N < 0 || N > h->p.capacity_landmarks) return fail(h, EKF_ECAPACITY, "ekf_set_state_lowrank: N beyond capacity");
     const int n = 3 + 2 * N;
     if (!x || !A || !d || r < 1 || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state_lowrank: bad argument");
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_set_state_lowrank(sh, x, s, N, A, r, d)); h->N = N; return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
     double *dA = nullptr, *dd = nullptr;
@@ -1087,6 +1237,8 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
 // ---------------------------------------------------------------- measurement hooks
 extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
     CKH(h);
+    if (is_front(h)) { FAN_OUT(h, sh, ekf_profile_enable(sh, on)); return EKF_OK; }
+    CK(cudaSetDevice(h->p.device));
     CK(cudaStreamSynchronize(h->stream));
     h->prof = on != 0;
     if (h->prof) {          // create the event pool here, outside anybody's timed region (cudaEventCreate costs microseconds)
@@ -1107,6 +1259,21 @@ extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
 extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, int64_t* downdate_launches,
                                     int64_t* kernel_launches_total) {
     CKH(h);
+    if (is_front(h)) {                    // the slowest slab's downdate time, launches summed over the slabs
+        double worst = -1.0; int64_t nd = 0, nl = 0;
+        for (size_t g = 0; g < h->subs.size(); ++g) {
+            double ms = 0.0; int64_t d1 = 0, l1 = 0;
+            int32_t rcf = ekf_profile_read(h->subs[g], &ms, &d1, &l1);
+            if (rcf != EKF_OK) { h->err = h->subs[g]->err; return rcf; }
+            if (ms > worst) { worst = ms; nd = d1; h->rank = (int)g; }      // front->rank: slab the roofline numbers refer to
+            nl += l1;
+        }
+        if (downdate_ms_total) *downdate_ms_total = worst;
+        if (downdate_launches) *downdate_launches = nd;
+        if (kernel_launches_total) *kernel_launches_total = nl;
+        return EKF_OK;
+    }
+    CK(cudaSetDevice(h->p.device));
     CK(cudaStreamSynchronize(h->stream));
     for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
         float ms = 0.f;
@@ -1122,6 +1289,21 @@ extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, in
 
 extern "C" int32_t ekf_profile_exchange(ekf_handle* h, double* exchange_ms_total, int64_t* exchanges, int32_t* p2p) {
     CKH(h);
+    if (is_front(h)) {
+        double worst = 0.0; int64_t cnt = 0; int32_t pp = 1;
+        for (ekf_handle* sh : h->subs) {
+            double ms = 0.0; int64_t c1 = 0; int32_t p1 = 0;
+            int32_t rcf = ekf_profile_exchange(sh, &ms, &c1, &p1);
+            if (rcf != EKF_OK) { h->err = sh->err; return rcf; }
+            if (ms > worst) worst = ms;
+            cnt = c1; pp &= p1;
+        }
+        if (exchange_ms_total) *exchange_ms_total = worst;
+        if (exchanges) *exchanges = cnt;
+        if (p2p) *p2p = pp;
+        return EKF_OK;
+    }
+    CK(cudaSetDevice(h->p.device));
     CK(cudaStreamSynchronize(h->stream));
     const int64_t cnt = (int64_t)(h->xev_used / 2);
     for (size_t i = 0; i + 1 < h->xev_used; i += 2) {
@@ -1140,6 +1322,7 @@ extern "C" int32_t ekf_profile_exchange(ekf_handle* h, double* exchange_ms_total
 extern "C" int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes) {
     CKH(h);
     if (!bytes) return fail(h, EKF_EINVAL, "bytes is null");
+    if (is_front(h)) return ekf_downdate_bytes(h->subs[(size_t)h->rank < h->subs.size() ? h->rank : 0], bytes);   // slab of the last ekf_profile_read
     const double n = (double)n_of(h);
     if (h->world > 1) {                                         // local slab
         const double lo = (double)h->c_lo, hi = lo + (double)ncols_loc(h);

@@ -31,7 +31,7 @@ class _FilterBase:
     _VARIANT = L.VARIANT_KNOWN
 
     def __init__(self, capacity_landmarks=1024, storage='full', device=0, stream=0,
-                 assoc_mode='signature', defer_m=0, rank=0, world=1, nccl_id=None):
+                 assoc_mode='signature', defer_m=0, rank=0, world=1, nccl_id=None, devices=None):
         self._lib = L.load()
         p = L.EkfParams()
         L.check(None, self._lib.ekf_params_default(ct.byref(p), self._VARIANT))
@@ -43,7 +43,10 @@ class _FilterBase:
         p.stream = int(stream)
         self._p = p
         self._h = L._H()
-        if world > 1:
+        if devices is not None and len(devices) > 1:       # one process, several GPUs: column slabs behind ONE handle
+            dv = np.ascontiguousarray(devices, dtype=np.int32)
+            rc = self._lib.ekf_create_multi(ct.byref(p), int(dv.size), L.iptr(dv), ct.byref(self._h))
+        elif world > 1:
             idbuf = (ct.c_uint8 * 128).from_buffer_copy(bytes(nccl_id))
             rc = self._lib.ekf_create_sharded(ct.byref(p), int(rank), int(world), idbuf, ct.byref(self._h))
         else:

@@ -82,6 +82,13 @@ int32_t ekf_destroy(ekf_handle* h);
  * mirroring); association mode B is not available.  (The reference has no counterpart: EKF_SLAM.m is single-process.) */
 int32_t ekf_nccl_unique_id(uint8_t* id128);
 int32_t ekf_create_sharded(const ekf_params* p, int32_t rank, int32_t world, const uint8_t* id128, ekf_handle** out);
+/* The same filter from ONE process over n_devices GPUs (what a MATLAB host needs: MEX runs on the interpreter's single
+ * thread, SLAM.m:21-40 constructs one object in one process).  The returned handle is used exactly like a single-GPU one
+ * -- every entry point of this header accepts it -- and internally owns one column-slab handle per device; the per-batch
+ * column exchange goes through directly mapped peer memory (cudaDeviceEnablePeerAccess), no NCCL, no launcher.  Devices
+ * must be distinct and peer-accessible (EKF_ECUDA otherwise); params.stream must be 0; devices == NULL means 0..n-1.
+ * ekf_get_P / ekf_get_P_block assemble the slabs on the host; association mode B and ekf_get_ellipses are not available. */
+int32_t ekf_create_multi(const ekf_params* p, int32_t n_devices, const int32_t* devices, ekf_handle** out);
 int32_t ekf_shard_info(ekf_handle* h, int32_t* rank, int32_t* world, int32_t* c_lo, int32_t* c_hi);
 /* Pure host helper: column range of `rank` for a given capacity (landmark-aligned, rank 0 holds the robot). */
 int32_t ekf_slab_range(int32_t capacity_landmarks, int32_t world, int32_t rank, int32_t storage,

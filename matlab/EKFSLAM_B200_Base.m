@@ -41,7 +41,8 @@ classdef EKFSLAM_B200_Base < handle
     methods
         function h = EKFSLAM_B200_Base(variant, opts)
             % variant 0 = EKF_SLAM, 1 = EKF_SLAM_UC; opts: struct with optional fields
-            % capacity_landmarks (default 1024), storage (0 full / 1 sym), assoc_mode, device, defer_m.
+            % capacity_landmarks (default 1024), storage (0 full / 1 sym), assoc_mode, device, defer_m,
+            % devices ([0 1 2 3]: ONE filter in column slabs over several GPUs, still one MATLAB process).
             if nargin < 2 || isempty(opts)
                 opts = struct();
             end

@@ -86,7 +86,21 @@ void mexFunction(int nlhs, mxArray* plhs[], int nrhs, const mxArray* prhs[]) {
             p.defer_m = (int32_t)scalar_field(o, "defer_m", p.defer_m);
         }
         {
-            int32_t rc = ekf_create(&p, &h);
+            /* opts.devices = [0 1 2 3]: ONE filter in column slabs over several GPUs, driven from this one process */
+            const mxArray* dv = (nrhs > 2 && mxIsStruct(prhs[2])) ? mxGetField(prhs[2], 0, "devices") : NULL;
+            size_t nd = dv ? mxGetNumberOfElements(dv) : 0;
+            int32_t rc;
+            if (nd > 1) {
+                int32_t devs[8];
+                size_t g;
+                const double* dd = dbl(dv, nd, "devices");
+                if (nd > 8) mexErrMsgIdAndTxt("ekfslam:EINVAL", "at most 8 devices");
+                for (g = 0; g < nd; ++g) devs[g] = (int32_t)dd[g];
+                rc = ekf_create_multi(&p, (int32_t)nd, devs, &h);
+            } else {
+                if (nd == 1) p.device = (int32_t)mxGetScalar(dv);
+                rc = ekf_create(&p, &h);
+            }
             if (rc != EKF_OK) mexErrMsgIdAndTxt(code_name(rc), "ekf_create failed (a CUDA device is required; there is no CPU fallback)");
         }
         plhs[0] = handle_out(h);

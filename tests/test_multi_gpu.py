@@ -1,0 +1,79 @@
+"""Single-process multi-device filter (ekf_create_multi: what a MATLAB host can drive, SURVEY 8(b) "Threading"): ONE
+handle, the covariance in column slabs on several GPUs of this process.  Needs >= 2 GPUs on the box; skipped otherwise."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+def _rel(a, b):
+    return float(np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300))
+
+
+@pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 8), ('sym', 16), ('sym', 0)])
+@pytest.mark.parametrize('G', [2, 4, 8])
+def test_multi_device_handle_is_bit_identical_to_single_gpu(G, storage, defer_m):
+    """Populated 1k map, predict + ragged update batches + single updates, x / P / P_block read mid-run: the multi-device
+    handle returns the very bits of the single-GPU path (same kernels, same operands, same order)."""
+    if _ngpu() < G:
+        pytest.skip('needs %d GPUs' % G)
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
+    N = 1000
+    x, A, d, s, lms = synthetic_spd_state(N, seed=3)
+    m = E.EKF_SLAM(capacity_landmarks=N, storage=storage, defer_m=defer_m, devices=list(range(G)))
+    ref = E.EKF_SLAM(capacity_landmarks=N, storage=storage, defer_m=defer_m, device=0)
+    assert m.shard_info()[1] == G
+    for f in (m, ref):
+        f.set_state_lowrank(x, s, A, d)
+    rng = np.random.default_rng(21)
+    for step in range(8):
+        rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:(8, 11, 5, 8, 1, 8, 3, 8)[step]]
+        Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+        for f in (m, ref):
+            f.predict([0.3, 1.0])
+            if step == 4:
+                f.update(rows[0, :2], Rd[0], int(rows[0, 2]))
+            else:
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+        if step % 3 == 1:
+            assert np.array_equal(m.x, ref.x), (step, _rel(m.x, ref.x))
+        if step == 5:
+            assert np.array_equal(m.P_block(3, 100, 40, 1500), ref.P_block(3, 100, 40, 1500))   # spans slab boundaries
+    assert np.array_equal(m.x, ref.x) and np.array_equal(m.s, ref.s)
+    assert np.array_equal(m.P, ref.P), _rel(m.P, ref.P)
+    m.close(); ref.close()
+
+
+@pytest.mark.parametrize('variant', ['known', 'uc'])
+def test_multi_device_full_loop_vs_oracle(variant):
+    """The reference-facing loop (predict / measure with appends, associations, the idx = ii quirk) through a 2-device
+    handle against the dense-literal oracle, incl. property writes on the multi handle."""
+    if _ngpu() < 2:
+        pytest.skip('needs 2 GPUs')
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    from oracle import dense_literal as O
+    w = make_world(N=20, T=400, k=5, mode='prefix' if variant == 'known' else 'nearest')
+    g = (E.EKF_SLAM if variant == 'known' else E.EKF_SLAM_UC)(capacity_landmarks=20, storage='sym', defer_m=16, devices=[0, 1])
+    o = (O.EKF_SLAM if variant == 'known' else O.EKF_SLAM_UC)()
+    for t in range(w.T):
+        g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
+        o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
+        if t == 200:
+            g.x = g.x; g.P = g.P                 # round trip through the property setters of the multi handle
+    assert g.chosen == o.chosen
+    assert _rel(g.x, o.x) <= 1e-9 and _rel(g.P, o.P) <= 1e-9
+    assert np.array_equal(g.s, o.s)
+    g.close()
+
+
+def test_multi_device_rejects_duplicate_devices():
+    import ekf_slam_b200 as E
+    with pytest.raises(E.EkfError):
+        E.EKF_SLAM(capacity_landmarks=16, devices=[0, 0])
