@@ -421,3 +421,36 @@ def test_f_motion_model_matches_the_oracle():
     x = np.array([0.0, 0.0, 90.0])
     _, F = _FilterBase.f(None, x, [2.0, 45.0])
     assert F[0, 2] == -2.0 and F[1, 2] == 0.0                          # sind(90) = 1, cosd(90) = 0 exactly
+
+
+def test_reference_witness_roundtrip_and_pin_if_present(tmp_path):
+    """matlab/run_reference_fixture.m runs the UNMODIFIED reference on tests/golden/ref_inputs and writes CSVs;
+    tests/golden/compare_reference_fixture.py turns them into the pin of the oracle.  (a) The exported inputs are the
+    golden inputs bit for bit; (b) the comparer accepts the oracle's own outputs written in the script's format (so a
+    format slip cannot fake a mismatch); (c) if somebody has run the script under MATLAB/Octave and dropped the outputs
+    into tests/golden/ref_outputs, they must match the oracle to 1e-9 -- that is the reference pin."""
+    import os
+    from tests.golden import compare_reference_fixture as C
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+    for name in G.CASES:
+        g = G.load(name)
+        d = os.path.join(here, 'ref_inputs', name)
+        assert open(os.path.join(d, 'class.txt')).read().strip() == G.CASES[name]
+        for key in ('u', 'obs_rows', 'table_loc'):
+            a = np.genfromtxt(os.path.join(d, key + '.csv'), delimiter=',').reshape(np.asarray(g[key]).shape)
+            assert np.array_equal(a, g[key]), (name, key)
+        out = tmp_path / name
+        out.mkdir()
+        wr = lambda fn, M: np.savetxt(str(out / fn), np.atleast_2d(M), delimiter=',', fmt='%.17g')
+        wr('x_final.csv', g['x_final']); wr('P_final.csv', g['P_final']); wr('s_final.csv', g['s_final'])
+        wr('x_checkpoints.csv', g['x_checkpoints'])
+        off = np.concatenate([[0], np.cumsum(g['obs_counts'])])
+        wr('n_landmarks.csv', np.cumsum([(g['actions'][off[t]:off[t + 1]] < 0).sum() for t in range(len(g['obs_counts']))]))
+        r = C.compare_case(name, str(tmp_path))
+        assert r['pinned'] and r['x_final'] == 0.0 and r['P_final'] == 0.0, r
+    real = os.path.join(here, 'ref_outputs')
+    if os.path.isdir(real):
+        for name in G.CASES:
+            if os.path.isdir(os.path.join(real, name)):
+                r = C.compare_case(name, real)
+                assert r['pinned'], (name, r)
