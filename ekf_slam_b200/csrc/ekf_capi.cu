@@ -51,6 +51,7 @@ struct ekf_handle {
     double2* Bc = nullptr;     // EKF_MAX_DEFER x EKF_MAX_SLOTS: B_q(:, col(slot))
     struct QObs { double z0, z1, R0, R1; int a; };
     std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
+    SlotSet ss_cur;            // slot columns of the batch between exec_send and exec_finish
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
     // ---- decoupled state chain (EKF_ASYNC_X=0 disables) ----
     // x, s and the mode-A association do not depend on the O(n^2) flush of P, so the state half of predict, the batched
@@ -107,6 +108,8 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
 
 static int32_t flush(ekf_handle* h);
 static int32_t exec_sharded(ekf_handle* h);
+static int32_t front_exec(ekf_handle* f);
+static int32_t front_flush(ekf_handle* f);
 #define FLUSH(h) do { int32_t rc__ = flush(h); if (rc__ != EKF_OK) return rc__; } while (0)
 
 // Called after every stream synchronisation: surface what the kernels flagged since the last one.
@@ -553,7 +556,12 @@ extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], do
 extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     CKH(h);
     if (!u) return fail(h, EKF_EINVAL, "u is null");
-    if (is_front(h)) { FAN_OUT(h, sh, ekf_predict(sh, u)); return EKF_OK; }
+    if (is_front(h)) {                       // x must be final on every slab before the motion step
+        int32_t rcf = h->xstep ? front_exec(h) : front_flush(h);
+        if (rcf != EKF_OK) return rcf;
+        FAN_OUT(h, sh, ekf_predict(sh, u));
+        return EKF_OK;
+    }
     CK(cudaSetDevice(h->p.device));
     if (!h->xstep) FLUSH(h);                 // cross-step deferral keeps the terms pending and transforms them below
     else if (h->world > 1) { int32_t rcq = exec_sharded(h); if (rcq != EKF_OK) return rcq; }   // x must be final before the motion step
@@ -612,9 +620,12 @@ static int32_t prof_end(ekf_handle* h) {
 // The one data-path collective: make the current columns of the slot set available on every rank.
 //   FULL slabs: broadcast each column from its owner (robot columns from rank 0).
 //   SYM  slabs: each rank contributes the part of every symmetric column it stores, zero elsewhere; all-reduce.
-static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
+// phase: 0 = whole exchange; 1 = send only, 2 = wait only (a multi-device front sends on EVERY device before it lets any
+// of them wait: with one host thread, a spinning waiter whose peers' sends are not enqueued yet would stall the first
+// call that has to synchronise that context -- lazy module loading of a not-yet-used kernel is enough)
+static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n, int phase = 0) {
     const int sym = sym_of(h);
-    if (h->prof) {
+    if (h->prof && phase != 2) {
         if (h->xev_used + 2 > h->xev.size()) {
             size_t old = h->xev.size();
             h->xev.resize(old + 256);
@@ -624,14 +635,19 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
     }
     if (h->p2p) {
         // peer-memory scatter: every rank stores the elements it owns into every rank's buffer, then publishes the batch
-        h->epoch += 1;
-        const int64_t buf_off = (int64_t)(h->epoch & 1) * EKF_MAX_SLOTS * h->ld;
-        launch_scatter_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->peers, buf_off, sym, h->epoch, h->xticket,
-                            h->xflags, h->xch_timeout, h->dflags + 1);
-        h->Pc_cur = h->Pc + buf_off;
-        h->launches += 2;
+        if (phase != 2) {
+            h->epoch += 1;
+            const int64_t buf_off = (int64_t)(h->epoch & 1) * EKF_MAX_SLOTS * h->ld;
+            launch_scatter_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->peers, buf_off, sym, h->epoch, h->xticket);
+            h->Pc_cur = h->Pc + buf_off;
+            h->launches += 1;
+        }
+        if (phase != 1) {
+            launch_wait_flags(h->stream, h->xflags, h->world, h->epoch, h->xch_timeout, h->dflags + 1);
+            h->launches += 1;
+        }
         CK(cudaGetLastError());
-    } else {
+    } else if (phase != 2) {
         h->Pc_cur = h->Pc;
         launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld, sym);
         CK(cudaGetLastError());
@@ -648,7 +664,7 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n) {
         }
         h->launches += 1;
     }
-    if (h->prof) {
+    if (h->prof && phase != 1) {
         CK(cudaEventRecord(h->xev[h->xev_used + 1], h->stream));
         h->xev_used += 2;
     }
@@ -682,20 +698,29 @@ static int32_t downdate_sharded(ekf_handle* h) {
     return EKF_OK;
 }
 
-static int32_t exec_sharded(ekf_handle* h) {
+// exec in two halves (see exchange_cols): exec_send = make room + send this slab's share of the slot columns;
+// exec_finish = wait for everybody's share, linearise, gains.
+static int32_t exec_send(ekf_handle* h) {
     const int k = (int)h->q.size();
     if (k == 0) return EKF_OK;
     if (h->m_pend + k > h->pend_cap) {      // make room: one pass over the slab for everything pending
         int32_t rc = downdate_sharded(h);
         if (rc != EKF_OK) return rc;
     }
-    const int m0 = h->m_pend;
-    const int n = n_of(h);
-    SlotSet ss;
+    SlotSet& ss = h->ss_cur;
     ss.n = 3 + 2 * k;
     ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
     for (int m = 0; m < k; ++m) { ss.col[3 + 2 * m] = h->q[m].a; ss.col[4 + 2 * m] = h->q[m].a + 1; }
-    int32_t rcx = exchange_cols(h, ss, n);
+    return exchange_cols(h, ss, n_of(h), 1);
+}
+
+static int32_t exec_finish(ekf_handle* h) {
+    const int k = (int)h->q.size();
+    if (k == 0) return EKF_OK;
+    const int m0 = h->m_pend;
+    const int n = n_of(h);
+    const SlotSet& ss = h->ss_cur;
+    int32_t rcx = exchange_cols(h, ss, n, 2);
     if (rcx != EKF_OK) return rcx;
     if (k >= 2 && !getenv("EKF_SHARD_PEROBS")) {
         // fused: one CTA walks the k linearisations on the exchanged (3+2k)^2 block, one grid-wide kernel builds all
@@ -725,6 +750,25 @@ static int32_t exec_sharded(ekf_handle* h) {
     return EKF_OK;
 }
 
+static int32_t exec_sharded(ekf_handle* h) {
+    int32_t rc = exec_send(h);
+    if (rc != EKF_OK) return rc;
+    return exec_finish(h);
+}
+
+// Multi-device front: the same batch on every slab, all sends before any wait.
+static int32_t front_exec(ekf_handle* f) {
+    for (ekf_handle* sh : f->subs) { cudaSetDevice(sh->p.device); int32_t rc = exec_send(sh); if (rc != EKF_OK) { f->err = sh->err; return rc; } }
+    for (ekf_handle* sh : f->subs) { cudaSetDevice(sh->p.device); int32_t rc = exec_finish(sh); if (rc != EKF_OK) { f->err = sh->err; return rc; } }
+    return EKF_OK;
+}
+static int32_t front_flush(ekf_handle* f) {
+    int32_t rc = front_exec(f);
+    if (rc != EKF_OK) return rc;
+    for (ekf_handle* sh : f->subs) { cudaSetDevice(sh->p.device); rc = downdate_sharded(sh); if (rc != EKF_OK) { f->err = sh->err; return rc; } }
+    return EKF_OK;
+}
+
 static int32_t flush_sharded(ekf_handle* h) {
     int32_t rc = exec_sharded(h);
     if (rc != EKF_OK) return rc;
@@ -732,7 +776,7 @@ static int32_t flush_sharded(ekf_handle* h) {
 }
 
 static int32_t flush(ekf_handle* h) {
-    if (is_front(h)) { FAN_OUT(h, sh, ekf_flush(sh)); return EKF_OK; }
+    if (is_front(h)) return front_flush(h);
     if (h->world > 1) return flush_sharded(h);
     if (h->m_pend == 0) return EKF_OK;
     if (h->prof) {
@@ -768,11 +812,16 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     if (!z || !Rdiag) return fail(h, EKF_EINVAL, "null argument");
     if (idx1 < 1 || idx1 > h->N)      // MATLAB would raise "index exceeds array bounds" at EKF_SLAM.m:125
         return fail(h, EKF_EINVAL, "ekf_update: landmark index " + std::to_string(idx1) + " outside 1.." + std::to_string(h->N));
-    if (is_front(h)) { FAN_OUT(h, sh, ekf_update(sh, z, Rdiag, idx1)); return EKF_OK; }
+    if (is_front(h)) {                       // queue on every slab; the front executes full batches in lockstep
+        FAN_OUT(h, sh, ekf_update(sh, z, Rdiag, idx1));
+        if ((int)h->subs[0]->q.size() >= h->defer) return h->xstep ? front_exec(h) : front_flush(h);
+        return EKF_OK;
+    }
     CK(cudaSetDevice(h->p.device));
     const int a = 3 + 2 * (idx1 - 1);
     if (h->world > 1) {                   // queue; the batch runs at the next flush point
         h->q.push_back({z[0], z[1], Rdiag[0], Rdiag[1], a});
+        if (h->in_process) return EKF_OK;     // the multi-device front decides when its slabs execute
         if ((int)h->q.size() >= h->defer) return h->xstep ? exec_sharded(h) : flush_sharded(h);
         return EKF_OK;
     }
@@ -786,23 +835,42 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
     return EKF_OK;
 }
 
+// append on a slab: the new rows need P(:,1:3), one 3-column exchange from rank 0 (phase as in exchange_cols)
+static int32_t append_sharded(ekf_handle* h, const double u[2], const double Rdiag[2], const double pos[2], double signature,
+                              int phase) {
+    SlotSet ss; ss.n = 3; ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
+    int32_t rcx = exchange_cols(h, ss, n_of(h), phase);
+    if (rcx != EKF_OK || phase == 1) return rcx;
+    launch_append_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1],
+                        pos[0], pos[1], signature, h->Pc_cur, h->ld);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    MARK_X(h);
+    h->N += 1;
+    return EKF_OK;
+}
+
 extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdiag[2], const double pos[2],
                               double signature) {
     CKH(h);
     if (!u || !Rdiag || !pos) return fail(h, EKF_EINVAL, "null argument");
     if (h->N >= h->p.capacity_landmarks)
         return fail(h, EKF_ECAPACITY, "ekf_append: capacity_landmarks=" + std::to_string(h->p.capacity_landmarks) + " reached");
-    if (is_front(h)) { FAN_OUT(h, sh, ekf_append(sh, u, Rdiag, pos, signature)); h->N += 1; return EKF_OK; }
+    if (is_front(h)) {                    // flush everywhere, then the 3-column exchange: all sends before any wait
+        int32_t rcq = front_flush(h);
+        if (rcq != EKF_OK) return rcq;
+        for (int phase = 1; phase <= 2; ++phase)
+            for (ekf_handle* sh : h->subs) {
+                cudaSetDevice(sh->p.device);
+                int32_t rcf = append_sharded(sh, u, Rdiag, pos, signature, phase);
+                if (rcf != EKF_OK) { h->err = sh->err; return rcf; }
+            }
+        h->N += 1;
+        return EKF_OK;
+    }
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
-    if (h->world > 1) {                   // the new rows need P(:,1:3): one 3-column broadcast from rank 0
-        SlotSet ss; ss.n = 3; ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
-        int32_t rcx = exchange_cols(h, ss, n_of(h));
-        if (rcx != EKF_OK) return rcx;
-        launch_append_shard(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1],
-                            pos[0], pos[1], signature, h->Pc_cur, h->ld);
-        h->launches += 1;
-    } else
+    if (h->world > 1) return append_sharded(h, u, Rdiag, pos, signature, 0);
     launch_append(h->stream, h->P, h->ld, h->x, h->s, h->N, u[0], u[1], Rdiag[0], Rdiag[1], pos[0], pos[1],
                   signature, sym_of(h));
     h->launches += 1;
@@ -851,8 +919,12 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
         for (int j = 0; j < k; ++j)
             if (idx1[j] < 1 || idx1[j] > h->N)
                 return fail(h, EKF_EINVAL, "ekf_update_batch: landmark index " + std::to_string(idx1[j]) + " outside 1.." + std::to_string(h->N));
-        FAN_OUT(h, sh, ekf_update_batch(sh, k, z, Rdiag, idx1));
-        return EKF_OK;
+        for (int j = 0; j < k; ++j) {
+            const double zj[2] = {z[j], z[j + k]}, Rj[2] = {Rdiag[j], Rdiag[j + k]};
+            int32_t rcf = ekf_update(h, zj, Rj, idx1[j]);
+            if (rcf != EKF_OK) return rcf;
+        }
+        return h->xstep ? front_exec(h) : front_flush(h);
     }
     CK(cudaSetDevice(h->p.device));
     int i = 0;
@@ -1019,11 +1091,8 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     CKH(h);
     if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
     if (is_front(h)) {                    // every slab executes its queued batch (they wait for each other's columns), then slab 0 answers
-        for (ekf_handle* sh : h->subs) {
-            cudaSetDevice(sh->p.device);
-            int32_t rcq = sh->xstep ? exec_sharded(sh) : flush_sharded(sh);
-            if (rcq != EKF_OK) { h->err = sh->err; return rcq; }
-        }
+        int32_t rcq = h->xstep ? front_exec(h) : front_flush(h);
+        if (rcq != EKF_OK) return rcq;
         int32_t rcf = ekf_get_x(h->subs[0], x, len);
         if (rcf != EKF_OK) h->err = h->subs[0]->err;
         return rcf;
@@ -1083,7 +1152,7 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
     if (!out || r0 < 0 || c0 < 0 || nr < 1 || nc < 1 || r0 + nr > n || c0 + nc > n || ldo < nr)
         return fail(h, EKF_EINVAL, "ekf_get_P_block: bad block");
     if (is_front(h)) {                    // every slab delivers the columns it stores
-        FAN_OUT(h, sh, ekf_flush(sh));    // all of them first: a flush executes queued batches, which exchange columns
+        { int32_t rcq = front_flush(h); if (rcq != EKF_OK) return rcq; }
         for (ekf_handle* sh : h->subs) {
             const int lo = std::max(c0, sh->c_lo), hi = std::min(c0 + nc, std::min(sh->c_hi, n));
             if (hi <= lo) continue;
@@ -1157,7 +1226,7 @@ extern "C" int32_t ekf_set_x(ekf_handle* h, const double* x, int32_t len) {
     CKH(h);
     if (!x || len != n_of(h)) return fail(h, EKF_EINVAL, "ekf_set_x: expected " + std::to_string(n_of(h)) + " elements (3 + 2 N); use ekf_set_state to change the number of landmarks");
     if (is_front(h)) {                    // enqueue every slab's flush first: a flush exchanges columns, and set_x synchronises
-        FAN_OUT(h, sh, ekf_flush(sh));
+        { int32_t rcq = front_flush(h); if (rcq != EKF_OK) return rcq; }
         FAN_OUT(h, sh, ekf_set_x(sh, x, len));
         return EKF_OK;
     }
@@ -1189,7 +1258,7 @@ extern "C" int32_t ekf_set_P(ekf_handle* h, const double* P, int32_t lda) {
     CKH(h);
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_set_P: lda < n");
-    if (is_front(h)) { FAN_OUT(h, sh, ekf_flush(sh)); FAN_OUT(h, sh, ekf_set_P(sh, P, lda)); return EKF_OK; }
+    if (is_front(h)) { int32_t rcq = front_flush(h); if (rcq != EKF_OK) return rcq; FAN_OUT(h, sh, ekf_set_P(sh, P, lda)); return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     FLUSH(h);
     const int hi = std::min(h->c_hi, n);  // a sharded handle keeps its own columns of the caller's full matrix

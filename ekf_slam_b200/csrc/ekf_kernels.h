@@ -50,8 +50,9 @@ void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xpre
 #define EKF_MAX_PEERS 8
 struct PeerSet { double* pc[EKF_MAX_PEERS]; int* flags[EKF_MAX_PEERS]; int world, rank; };   // cudaIpc-mapped Pc buffers / flag words of every rank
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags,
-                         long long timeout_cycles, int* err_word);   // err_word: mapped host memory, set to 1 when a peer does not answer in time
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket);
+// wait (bounded) until every rank has published `epoch`; err_word: mapped host memory, set to 1 when a peer does not answer in time
+void launch_wait_flags(cudaStream_t st, const int* flags, int world, int epoch, long long timeout_cycles, int* err_word);
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
                       double* Pc, int64_t ldc, int sym);
 void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, int a,

@@ -109,11 +109,13 @@ __global__ void k_wait_flags(const int* __restrict__ flags, int world, int epoch
 }
 
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const int* flags,
-                         long long timeout_cycles, int* err_word) {
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket) {
     dim3 grid((n + 255) / 256, ss.n);
     k_scatter_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, ps, buf_off, sym, epoch, ticket);
-    k_wait_flags<<<1, 32, 0, st>>>(flags, ps.world, epoch, timeout_cycles, err_word);
+}
+
+void launch_wait_flags(cudaStream_t st, const int* flags, int world, int epoch, long long timeout_cycles, int* err_word) {
+    k_wait_flags<<<1, 32, 0, st>>>(flags, world, epoch, timeout_cycles, err_word);
 }
 
 // One warp, replicated on every rank: EKF_SLAM.m:125-143 from the broadcast columns, plus B_m(:, c) for every
