@@ -45,6 +45,8 @@ struct ekf_handle {
     int* xflags = nullptr;     // [world] batch number last published by each rank
     unsigned int* xticket = nullptr;
     int epoch = 0;
+    int aepoch = 0;            // epoch of the sharded mode-B association (candidate exchange)
+    void* d_cand = nullptr;    // this rank's (cost, index) candidate + (NCCL fallback) the all-gathered ones: (1 + EKF_MAX_PEERS) x 16 B
     double xch_ms = 0.0;       // profile: exchange time (CUDA events)
     std::vector<cudaEvent_t> xev;
     size_t xev_used = 0;
@@ -248,7 +250,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     for (int g = 0; g < h->world && h->p2p && !h->in_process; ++g)
         if (g != h->rank) { if (h->peers.pc[g]) cudaIpcCloseMemHandle(h->peers.pc[g]); if (h->peers.flags[g]) cudaIpcCloseMemHandle(h->peers.flags[g]); }
     for (auto e : h->xev) cudaEventDestroy(e);
-    cudaFree(h->Pc); cudaFree(h->Bc); cudaFree(h->xflags); cudaFree(h->xticket);
+    cudaFree(h->Pc); cudaFree(h->Bc); cudaFree(h->xflags); cudaFree(h->xticket); cudaFree(h->d_cand);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
@@ -283,8 +285,8 @@ static int32_t init_state(ekf_handle* h) {
 // creation.  If any rank cannot map a peer (no P2P path), every rank falls back to the NCCL exchange together.
 static int32_t setup_p2p(ekf_handle* h) {
     const int W = h->world;
-    CK(cudaMalloc(&h->xflags, sizeof(int) * EKF_MAX_PEERS));
-    CK(cudaMemset(h->xflags, 0, sizeof(int) * EKF_MAX_PEERS));
+    CK(cudaMalloc(&h->xflags, sizeof(int) * EKF_XF_INTS));
+    CK(cudaMemset(h->xflags, 0, sizeof(int) * EKF_XF_INTS));
     CK(cudaMalloc(&h->xticket, sizeof(unsigned int)));
     CK(cudaMemset(h->xticket, 0, sizeof(unsigned int)));
     struct Pack { cudaIpcMemHandle_t pc, fl; int ok; int pad[15]; };
@@ -362,8 +364,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS * 2));
             h->Pc_cur = h->Pc;
             CK(cudaMalloc(&h->Bc, sizeof(double2) * EKF_MAX_DEFER * EKF_MAX_SLOTS));
-            CK(cudaMalloc(&h->xflags, sizeof(int) * EKF_MAX_PEERS));
-            CK(cudaMemset(h->xflags, 0, sizeof(int) * EKF_MAX_PEERS));
+            CK(cudaMalloc(&h->xflags, sizeof(int) * EKF_XF_INTS));
+            CK(cudaMemset(h->xflags, 0, sizeof(int) * EKF_XF_INTS));
             CK(cudaMalloc(&h->xticket, sizeof(unsigned int)));
             CK(cudaMemset(h->xticket, 0, sizeof(unsigned int)));
         } else if (world > 1) {
@@ -407,6 +409,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
         CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
         CK(cudaMalloc(&h->d_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
+        if (world > 1) CK(cudaMalloc(&h->d_cand, 16 * (1 + EKF_MAX_PEERS)));
         CK(cudaMallocHost(&h->h_res, sizeof(AssocResult) * EKF_ASSOC_BATCH));
         {
             const char* ax = getenv("EKF_ASYNC_X");
@@ -880,19 +883,85 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
     return EKF_OK;
 }
 
+// Mode-B association on a slab (Correspondence.m:49-87 with :74): every rank scores the landmarks whose columns it stores
+// -- their 2x2 diagonal block and robot cross-columns are local, the robot 3x3 block (and, FULL storage, the robot
+// columns) comes from one 3-column exchange --, reduces them to one lexicographic (cost, index) candidate, and the
+// candidates cross NVLink as 16-byte stores into the peers' flag area (all-gather over NCCL without peer memory).
+// stage 1: send the robot columns; 2: wait for them, score, send the candidate; 3: fold.  0: all three.
+static int32_t associate_b_sharded(ekf_handle* h, const double z[3], const double Rdiag[2], int stage) {
+    SlotSet ss; ss.n = 3; ss.col[0] = 0; ss.col[1] = 1; ss.col[2] = 2;
+    const int n = n_of(h);
+    if (stage == 0 || stage == 1) {
+        int32_t rc = exchange_cols(h, ss, n, stage == 0 ? 0 : 1);
+        if (rc != EKF_OK || stage == 1) return rc;
+    }
+    if (stage == 0 || stage == 2) {
+        if (stage == 2) { int32_t rc = exchange_cols(h, ss, n, 2); if (rc != EKF_OK) return rc; }
+        const int lo = std::max(h->c_lo, 3), hi = std::min(h->c_hi, n);
+        const int lm_lo = (lo - 3) / 2, lm_cnt = hi > lo ? (hi - lo) / 2 : 0;
+        launch_associate_slab(h->stream, h->P, h->ld, h->c_lo, lm_lo, lm_cnt, h->x, h->s, h->N, z[0], z[1], z[2], Rdiag[0], Rdiag[1],
+                              h->p.s_cost, h->p.s_thresh, sym_of(h), h->Pc_cur, h->ld, h->partial, h->ticket, h->d_cand);
+        h->launches += 1;
+        CK(cudaGetLastError());
+        if (h->p2p) {
+            h->aepoch += 1;
+            launch_cand_send(h->stream, h->d_cand, h->peers, h->aepoch);
+            h->launches += 1;
+            CK(cudaGetLastError());
+        }
+        if (stage == 2) return EKF_OK;
+    }
+    if (h->p2p) launch_cand_fold(h->stream, h->xflags, h->world, h->aepoch, h->xch_timeout, h->dflags + 1, h->N, h->d_res);
+    else {
+        char* all = (char*)h->d_cand + 16;
+        CKN(g_nccl.AllGather(h->d_cand, all, 16, ncclChar, h->comm, h->stream));
+        launch_cand_fold_gathered(h->stream, all, h->world, h->N, h->d_res);
+    }
+    h->launches += 1;
+    CK(cudaGetLastError());
+    return EKF_OK;
+}
+
 extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double Rdiag[2], int32_t* newLL,
                                  int32_t* idx1) {
     CKH(h);
     if (!z || !Rdiag || !newLL || !idx1) return fail(h, EKF_EINVAL, "null argument");
     if (h->N == 0) { *newLL = 1; *idx1 = 1; return EKF_OK; }   // Correspondence.m:33,40 with an empty loop
-    if (is_front(h)) {                     // mode A reads only s, which every slab holds
-        int32_t rcf = ekf_associate(h->subs[0], z, Rdiag, newLL, idx1);
+    if (is_front(h)) {
+        if (h->p.assoc_mode == EKF_ASSOC_POSITION) {       // every slab scores its landmarks; all sends before any wait
+            int32_t rcq = front_flush(h);
+            if (rcq != EKF_OK) return rcq;
+            for (int stage = 1; stage <= 3; ++stage)
+                for (ekf_handle* sh : h->subs) {
+                    cudaSetDevice(sh->p.device);
+                    int32_t rcf = associate_b_sharded(sh, z, Rdiag, stage);
+                    if (rcf != EKF_OK) { h->err = sh->err; return rcf; }
+                }
+            ekf_handle* s0 = h->subs[0];
+            cudaSetDevice(s0->p.device);
+            if (cudaMemcpyAsync(s0->h_res, s0->d_res, sizeof(AssocResult), cudaMemcpyDeviceToHost, s0->stream) != cudaSuccess ||
+                cudaStreamSynchronize(s0->stream) != cudaSuccess) return fail(h, EKF_ECUDA, "ekf_associate: copy of the result failed");
+            *newLL = s0->h_res->newLL;
+            *idx1 = s0->h_res->index1;
+            int32_t rca = after_sync(s0);
+            if (rca != EKF_OK) h->err = s0->err;
+            return rca;
+        }
+        int32_t rcf = ekf_associate(h->subs[0], z, Rdiag, newLL, idx1);   // mode A reads only s, which every slab holds
         if (rcf != EKF_OK) h->err = h->subs[0]->err;
         return rcf;
     }
     CK(cudaSetDevice(h->p.device));
-    if (h->world > 1 && h->p.assoc_mode == EKF_ASSOC_POSITION)
-        return fail(h, EKF_EINVAL, "ekf_associate: position-cost association is not available on a sharded filter");
+    if (h->world > 1 && h->p.assoc_mode == EKF_ASSOC_POSITION) {
+        FLUSH(h);
+        int32_t rcb = associate_b_sharded(h, z, Rdiag, 0);
+        if (rcb != EKF_OK) return rcb;
+        CK(cudaMemcpyAsync(h->h_res, h->d_res, sizeof(AssocResult), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        *newLL = h->h_res->newLL;
+        *idx1 = h->h_res->index1;
+        return after_sync(h);
+    }
     if (h->p.assoc_mode == EKF_ASSOC_POSITION) FLUSH(h);      // mode B reads P blocks; mode A only s
     cudaStream_t st = h->stream;
     if (h->async_x && h->p.assoc_mode == EKF_ASSOC_SIGNATURE) {   // mode A: behind the last writer of s, not behind a flush

@@ -382,21 +382,30 @@ __device__ __forceinline__ bool cand_less(double c1, int i1, double c2, int i2) 
     return (c1 < c2) || (c1 == c2 && i1 < i2);     // strict '<' scan == lexicographic (cost, index) min
 }
 
+// Slab form (sharded filters, mode B): the grid covers the `lm_cnt` landmarks starting at `lm_lo` whose columns this
+// rank stores (P = local slab, column c at P + (c - c_lo) * ld); everything that lives in the robot columns comes from
+// the exchanged copies Pc[j][i] = P(i, j), j < 3; the block minima fold into `cand_out` (this rank's candidate) instead
+// of the final result.  lm_lo = 0, lm_cnt = N, c_lo = 0, Pc = cand_out = null is the single-GPU kernel, bit for bit.
 __global__ void k_associate(const double* __restrict__ P, int64_t ld, const double* __restrict__ x,
                             const double* __restrict__ s, int N, double z0, double z1, double z2,
                             double R0, double R1, double s_cost, double s_thresh, int mode, int sym,
                             Cand* __restrict__ partial, unsigned int* __restrict__ ticket,
-                            AssocResult* __restrict__ out) {
+                            AssocResult* __restrict__ out, int lm_lo, int lm_cnt, int c_lo,
+                            const double* __restrict__ Pc, int64_t ldc, Cand* __restrict__ cand_out) {
     __shared__ double Prr[3][3];
     __shared__ double wc[32];
     __shared__ int wi[32];
     __shared__ bool is_last;
-    if (mode == 1 && threadIdx.x < 9) Prr[threadIdx.x / 3][threadIdx.x % 3] = ldP(P, ld, threadIdx.x / 3, threadIdx.x % 3, sym);
+    if (mode == 1 && threadIdx.x < 9)
+        Prr[threadIdx.x / 3][threadIdx.x % 3] = Pc ? Pc[(int64_t)(threadIdx.x % 3) * ldc + threadIdx.x / 3]
+                                                   : ldP(P, ld, threadIdx.x / 3, threadIdx.x % 3, sym);
     __syncthreads();
-    int kk = blockIdx.x * blockDim.x + threadIdx.x;            // 0-based landmark
+    const int kl = blockIdx.x * blockDim.x + threadIdx.x;
+    int kk = lm_lo + kl;                                       // 0-based landmark
     double best = CUDART_INF;
     int bidx = INT_MAX;
-    if (kk < N) {
+    P -= (int64_t)c_lo * ld;                                   // global column index -> local slab
+    if (kl < lm_cnt) {
         double d = __dsub_rn(z2, s[kk]);
         double sig = __dmul_rn(__dmul_rn(d, 1.0 / s_cost), d); // Correspondence.m:71
         double ll = sig;                                       // :75
@@ -410,7 +419,7 @@ __global__ void k_associate(const double* __restrict__ P, int64_t ld, const doub
             for (int i = 0; i < 3; ++i)
                 for (int m = 0; m < 2; ++m) {
                     Pcc[i][3 + m] = P[(int64_t)i + (int64_t)(a + m) * ld];
-                    Pcc[3 + m][i] = sym ? Pcc[i][3 + m] : P[(int64_t)(a + m) + (int64_t)i * ld];
+                    Pcc[3 + m][i] = sym ? Pcc[i][3 + m] : (Pc ? Pc[(int64_t)i * ldc + (a + m)] : P[(int64_t)(a + m) + (int64_t)i * ld]);
                 }
             Pcc[3][3] = P[(int64_t)a + (int64_t)a * ld];
             Pcc[3][4] = P[(int64_t)a + (int64_t)(a + 1) * ld];
@@ -471,11 +480,65 @@ __global__ void k_associate(const double* __restrict__ P, int64_t ld, const doub
         }
         if (lane == 0) {
             bool found = (bidx != INT_MAX);
-            out->newLL = found ? 0 : 1;                        // :33,82
-            out->index1 = found ? bidx : N + 1;                // :40,84
-            out->cost = best;
+            if (cand_out) { cand_out->cost = best; cand_out->idx = bidx; }     // slab: this rank's candidate
+            else {
+                out->newLL = found ? 0 : 1;                    // :33,82
+                out->index1 = found ? bidx : N + 1;            // :40,84
+                out->cost = best;
+            }
             *ticket = 0;
         }
+    }
+}
+
+// Candidate exchange of the sharded mode-B association: rank r stores its (cost, index) into slot r of every peer's
+// candidate area (inside the flag allocation: EKF_XF_CAND, double-buffered by epoch parity) and publishes the epoch in
+// the peers' association flag words (EKF_XF_ASSOC + r); k_cand_fold waits (bounded, like k_wait_flags) for all ranks
+// and takes the lexicographic (cost, index) minimum == the strict-'<' first-minimum scan of Correspondence.m:81 over
+// all landmarks.  Every rank computes the same result.  `gathered` (NCCL fallback): candidates already all-gathered.
+__global__ void k_cand_none(Cand* c) { c->cost = CUDART_INF; c->idx = INT_MAX; }
+
+__global__ void k_cand_send(const Cand* __restrict__ mine, PeerSet ps, int epoch) {
+    const int g = threadIdx.x;
+    if (g < ps.world) {
+        Cand* dst = (Cand*)(ps.flags[g] + EKF_XF_CAND) + (epoch & 1) * EKF_MAX_PEERS + ps.rank;
+        *dst = *mine;
+        __threadfence_system();
+        asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(ps.flags[g] + EKF_XF_ASSOC + ps.rank), "r"(epoch) : "memory");
+    }
+}
+
+__global__ void k_cand_fold(const int* __restrict__ flags, const Cand* __restrict__ gathered, int world, int epoch,
+                            long long timeout, int* __restrict__ err, int N, AssocResult* __restrict__ out) {
+    const int g = threadIdx.x;
+    double best = CUDART_INF;
+    int bidx = INT_MAX;
+    if (g < world) {
+        if (gathered) { best = gathered[g].cost; bidx = gathered[g].idx; }
+        else {
+            const long long t0 = clock64();
+            int v;
+            do {
+                asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(flags + EKF_XF_ASSOC + g) : "memory");
+                if (v >= epoch) break;
+                if (*(volatile int*)err) break;
+                if (clock64() - t0 > timeout) { *(volatile int*)err = 1; __threadfence_system(); break; }
+            } while (true);
+            const volatile Cand* c = (const volatile Cand*)(flags + EKF_XF_CAND) + (epoch & 1) * EKF_MAX_PEERS + g;
+            best = c->cost; bidx = c->idx;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double oc = __shfl_down_sync(0xffffffffu, best, o);
+        int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+        if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+    }
+    if (g == 0) {
+        const bool found = (bidx != INT_MAX);
+        out->newLL = found ? 0 : 1;                            // Correspondence.m:33,82
+        out->index1 = found ? bidx : N + 1;                    // :40,84
+        out->cost = best;
     }
 }
 
@@ -638,7 +701,28 @@ void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double
                       double z0, double z1, double z2, double R0, double R1, double s_cost, double s_thresh,
                       int mode, int sym, void* partial, unsigned int* ticket, AssocResult* out) {
     k_associate<<<assoc_blocks(N), 256, 0, st>>>(P, ld, x, s, N, z0, z1, z2, R0, R1, s_cost, s_thresh, mode, sym,
-                                                 (Cand*)partial, ticket, out);
+                                                 (Cand*)partial, ticket, out, 0, N, 0, nullptr, 0, nullptr);
+}
+
+// ---- association mode B on a slab: local candidate, then a 16-byte (cost, index) exchange over the peer flag words ----
+void launch_associate_slab(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int lm_lo, int lm_cnt, const double* x,
+                           const double* s, int N, double z0, double z1, double z2, double R0, double R1, double s_cost,
+                           double s_thresh, int sym, const double* Pc, int64_t ldc, void* partial, unsigned int* ticket,
+                           void* cand_out) {
+    if (lm_cnt <= 0) { k_cand_none<<<1, 1, 0, st>>>((Cand*)cand_out); return; }
+    k_associate<<<assoc_blocks(lm_cnt), 256, 0, st>>>(Ploc, ld, x, s, N, z0, z1, z2, R0, R1, s_cost, s_thresh, 1, sym,
+                                                      (Cand*)partial, ticket, nullptr, lm_lo, lm_cnt, c_lo, Pc, ldc, (Cand*)cand_out);
+}
+
+void launch_cand_send(cudaStream_t st, const void* mine, const PeerSet& ps, int epoch) {
+    k_cand_send<<<1, 32, 0, st>>>((const Cand*)mine, ps, epoch);
+}
+void launch_cand_fold(cudaStream_t st, const int* flags, int world, int epoch, long long timeout_cycles, int* err_word, int N,
+                      AssocResult* out) {
+    k_cand_fold<<<1, 32, 0, st>>>(flags, nullptr, world, epoch, timeout_cycles, err_word, N, out);
+}
+void launch_cand_fold_gathered(cudaStream_t st, const void* all, int world, int N, AssocResult* out) {
+    k_cand_fold<<<1, 32, 0, st>>>(nullptr, (const Cand*)all, world, 0, 0, nullptr, N, out);
 }
 
 void launch_associate_sig_batch(cudaStream_t st, const double* s, int N, const AssocBatchZ& zb, int k, double s_cost,

@@ -48,6 +48,11 @@ void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, dou
 void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym);   // covariance half
 // ---- column-slab sharded filter (ekf_shard.cu) ----
 #define EKF_MAX_PEERS 8
+// layout of a rank's flag allocation (ints): [0, 8) column-exchange epochs per source rank, [EKF_XF_ASSOC, +8) association
+// epochs, [EKF_XF_CAND, ...) 2 x 8 candidates of 16 bytes (cost, index) for the sharded mode-B association
+#define EKF_XF_ASSOC 8
+#define EKF_XF_CAND 64
+#define EKF_XF_INTS 256
 struct PeerSet { double* pc[EKF_MAX_PEERS]; int* flags[EKF_MAX_PEERS]; int world, rank; };   // cudaIpc-mapped Pc buffers / flag words of every rank
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
                          const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket);
@@ -65,6 +70,14 @@ void launch_predict_shard_P(cudaStream_t st, double* Ploc, int64_t ld, int c_lo,
 void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, double* s, int N,
                          double u1, double u2, double R0, double R1, double px, double py, double sig, const double* Pc,
                          int64_t ldc);
+void launch_associate_slab(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int lm_lo, int lm_cnt, const double* x,
+                           const double* s, int N, double z0, double z1, double z2, double R0, double R1, double s_cost,
+                           double s_thresh, int sym, const double* Pc, int64_t ldc, void* partial, unsigned int* ticket,
+                           void* cand_out);                      // mode B over the landmarks of this slab -> one 16-byte candidate
+void launch_cand_send(cudaStream_t st, const void* mine, const PeerSet& ps, int epoch);
+void launch_cand_fold(cudaStream_t st, const int* flags, int world, int epoch, long long timeout_cycles, int* err_word, int N,
+                      AssocResult* out);
+void launch_cand_fold_gathered(cudaStream_t st, const void* all, int world, int N, AssocResult* out);
 void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n);
 void launch_ellipses(cudaStream_t st, const double* P, int64_t ld, const double* x, int N, double* out, int64_t ldo);
 

@@ -156,6 +156,47 @@ def main():
     assert ex <= 1e-9 and eP <= 1e-9, (rank, ex, eP)
     print('rank %d UC loop sym defer 16: rel err x %.2e P %.2e' % (rank, ex, eP), flush=True)
     g.close()
+    # (d) association mode B (Correspondence.m:74: Mahalanobis + signature) on slabs: every rank scores its own landmarks,
+    # 16-byte candidates cross NVLink; indices identical to the single-GPU kernel and to oracle/structured.c, incl. a
+    # duplicated landmark whose twin lives on another rank (tie -> first index) and a one-ulp twin
+    from oracle import structured as S
+    from ekf_slam_b200.synth import lowrank_to_dense
+    for storage in ('sym', 'full'):
+        N = 600
+        x, A, d, s, lms = synthetic_spd_state(N, seed=5)
+        P = lowrank_to_dense(A, d)
+        for a, b, ulp in ((7, 580, False), (40, 300, True), (590, 12, False)):
+            ia, ib = 3 + 2 * a, 3 + 2 * b
+            x[ib:ib + 2] = x[ia:ia + 2]; lms[b] = lms[a]
+            P[:3, ib:ib + 2] = P[:3, ia:ia + 2]; P[ib:ib + 2, :3] = P[ia:ia + 2, :3]
+            P[ib:ib + 2, ib:ib + 2] = P[ia:ia + 2, ia:ia + 2]
+            if ulp:
+                x[ib] = np.nextafter(x[ib], np.inf)
+        ones = np.ones(N)
+        g = E.shard.create_sharded(E.EKF_SLAM_UC, dist, local, storage=storage, capacity_landmarks=N, assoc_mode='position')
+        ref = E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, device=local, assoc_mode='position')
+        for f in (g, ref):
+            f.correspondence.s_thresh = 9.21
+            f._sync_corr()
+            f.set_state(x, P, ones)
+        o = S.EKF_SLAM_UC(capacity_landmarks=N, assoc_mode=1)
+        o.s_thresh = 9.21
+        o.set_state(x, P, ones)
+        rng = np.random.default_rng(2)
+        ids = np.concatenate([[7, 580, 40, 300, 590, 12], rng.choice(N, 120, replace=False)])
+        rows = observe_from_truth(lms, x[:3], ids, rng, seam_deg=0.0)
+        n_new = 0
+        for r in rows:
+            z = np.array([r[0], r[1], 1.0])
+            Rd = np.array([z[0] * 0.1, z[1] * 5.0])
+            got = g.correspondence.estimateCorrespondence(z, np.diag(Rd))
+            assert got == ref.correspondence.estimateCorrespondence(z, np.diag(Rd)) == o.associate(z, Rd), (rank, z, got)
+            n_new += int(got[0])
+        z = np.array([50.0, 170.0, 1.0])                 # far from everything: gated out on every rank -> new landmark N + 1
+        assert g.correspondence.estimateCorrespondence(z, np.diag([5.0, 850.0])) == (True, N + 1)
+        print('rank %d mode B on slabs/%s: %d queries identical to the single-GPU kernel and the C oracle (%d new)' %
+              (rank, storage, len(rows), n_new), flush=True)
+        g.close(); ref.close()
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:

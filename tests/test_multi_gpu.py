@@ -77,3 +77,45 @@ def test_multi_device_rejects_duplicate_devices():
     import ekf_slam_b200 as E
     with pytest.raises(E.EkfError):
         E.EKF_SLAM(capacity_landmarks=16, devices=[0, 0])
+
+
+@pytest.mark.parametrize('storage', ['sym', 'full'])
+def test_multi_device_mode_b_association(storage):
+    """Association mode B through a 2-device handle: indices identical to the single-GPU kernel, incl. a duplicated
+    landmark whose twin lives on the other device; and a full EKF_SLAM_UC loop in mode B (association -> drain -> append)."""
+    if _ngpu() < 2:
+        pytest.skip('needs 2 GPUs')
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, lowrank_to_dense, observe_from_truth, make_world
+    N = 400
+    x, A, d, s, lms = synthetic_spd_state(N, seed=5)
+    P = lowrank_to_dense(A, d)
+    a, b = 9, 390
+    ia, ib = 3 + 2 * a, 3 + 2 * b
+    x[ib:ib + 2] = x[ia:ia + 2]; lms[b] = lms[a]
+    P[:3, ib:ib + 2] = P[:3, ia:ia + 2]; P[ib:ib + 2, :3] = P[ia:ia + 2, :3]
+    P[ib:ib + 2, ib:ib + 2] = P[ia:ia + 2, ia:ia + 2]
+    fs = [E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, assoc_mode='position', devices=[0, 1]),
+          E.EKF_SLAM_UC(capacity_landmarks=N, storage=storage, assoc_mode='position', device=0)]
+    for f in fs:
+        f.correspondence.s_thresh = 9.21
+        f._sync_corr()
+        f.set_state(x, P, np.ones(N))
+    rng = np.random.default_rng(2)
+    rows = observe_from_truth(lms, x[:3], np.concatenate([[a, b], rng.choice(N, 80, replace=False)]), rng, seam_deg=0.0)
+    for r in rows:
+        z = np.array([r[0], r[1], 1.0])
+        R = np.diag([z[0] * 0.1, z[1] * 5.0])
+        assert fs[0].correspondence.estimateCorrespondence(z, R) == fs[1].correspondence.estimateCorrespondence(z, R)
+    for f in fs:
+        f.close()
+    w = make_world(N=16, T=120, k=4, mode='nearest', seed=5)
+    fs = [E.EKF_SLAM_UC(capacity_landmarks=16, storage=storage, assoc_mode='position', defer_m=8, devices=[0, 1]),
+          E.EKF_SLAM_UC(capacity_landmarks=16, storage=storage, assoc_mode='position', defer_m=8, device=0)]
+    for t in range(w.T):
+        for f in fs:
+            f.predict(w.u[t]); f.measure(None, w.u[t], w.stub(t))
+    assert fs[0].chosen == fs[1].chosen
+    assert np.array_equal(fs[0].x, fs[1].x) and np.array_equal(fs[0].P, fs[1].P)
+    for f in fs:
+        f.close()
