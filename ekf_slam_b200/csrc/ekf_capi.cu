@@ -54,6 +54,7 @@ struct ekf_handle {
     struct QObs { double z0, z1, R0, R1; int a; };
     std::vector<QObs> q;       // sharded: observations queued since the last flush (executed as one batch)
     SlotSet ss_cur;            // slot columns of the batch between exec_send and exec_finish
+    bool lazy_now = false;     // that batch takes the lazy-flush path
     int m_pend = 0;            // pending (not yet flushed) rank-2 terms
     // ---- decoupled state chain (EKF_ASYNC_X=0 disables) ----
     // x, s and the mode-A association do not depend on the O(n^2) flush of P, so the state half of predict, the batched
@@ -73,6 +74,16 @@ struct ekf_handle {
     // path (F is applied to P0 and to the terms separately), but the same estimator to rounding: parity <= 1e-9.
     int pend_cap = 1;          // = defer unless cross-step
     bool xstep = false;
+    // lazy flush (cross-step deferral, SYM storage; EKF_LAZY_FLUSH=0 disables): a full set of pending terms is not flushed
+    // when it fills up but when the NEXT batch arrives: that batch's slot columns are copied out of P0 first (local gather /
+    // sharded exchange), then the K3 pass runs on the main stream while the batch is linearised on the side stream `sg`
+    // from those copies + the pending terms, writing its gains into the other pair of slabs (Kd2, Bd2).  Same operands,
+    // same order as flush-then-linearise: bit-identical, but k_batch_lin / k_batch_gain leave the critical path.
+    bool lazy = false;
+    double2* Kd2 = nullptr;
+    double2* Bd2 = nullptr;
+    cudaStream_t sg = nullptr;
+    cudaEvent_t ev_g1 = nullptr, ev_g2 = nullptr;
     int dd_variant = -1;       // downdate kernel variant (-1 = library default; EKF_DOWNDATE_VARIANT env at create)
     Lin* lin = nullptr;
     BatchLin* blin = nullptr;  // scratch of the fused batch linearisation (ekf_update_batch)
@@ -110,6 +121,7 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
 
 static int32_t flush(ekf_handle* h);
 static int32_t exec_sharded(ekf_handle* h);
+static int32_t downdate_sharded(ekf_handle* h);
 static int32_t front_exec(ekf_handle* f);
 static int32_t front_flush(ekf_handle* f);
 #define FLUSH(h) do { int32_t rc__ = flush(h); if (rc__ != EKF_OK) return rc__; } while (0)
@@ -247,6 +259,10 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd); cudaFree(h->Bt);
+    cudaFree(h->Kd2); cudaFree(h->Bd2);
+    if (h->sg) { cudaStreamSynchronize(h->sg); cudaStreamDestroy(h->sg); }
+    if (h->ev_g1) cudaEventDestroy(h->ev_g1);
+    if (h->ev_g2) cudaEventDestroy(h->ev_g2);
     for (int g = 0; g < h->world && h->p2p && !h->in_process; ++g)
         if (g != h->rank) { if (h->peers.pc[g]) cudaIpcCloseMemHandle(h->peers.pc[g]); if (h->peers.flags[g]) cudaIpcCloseMemHandle(h->peers.flags[g]); }
     for (auto e : h->xev) cudaEventDestroy(e);
@@ -414,6 +430,22 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         {
             const char* ax = getenv("EKF_ASYNC_X");
             h->async_x = !(ax && atoi(ax) == 0);
+        }
+        {
+            const char* lz = getenv("EKF_LAZY_FLUSH");
+            h->lazy = h->xstep && p->storage == EKF_STORAGE_SYM && !(lz && atoi(lz) == 0);
+        }
+        if (h->lazy) {
+            int pr_lo = 0, pr_hi = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&pr_lo, &pr_hi));
+            CK(cudaStreamCreateWithPriority(&h->sg, cudaStreamNonBlocking, pr_hi));
+            CK(cudaEventCreateWithFlags(&h->ev_g1, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_g2, cudaEventDisableTiming));
+            CK(cudaMalloc(&h->Kd2, sizeof(double2) * h->ld * EKF_MAX_PEND));
+            CK(cudaMalloc(&h->Bd2, sizeof(double2) * h->ld * EKF_MAX_PEND));
+            CK(cudaMemset(h->Kd2, 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
+            CK(cudaMemset(h->Bd2, 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
+            if (world == 1) { CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS)); h->Pc_cur = h->Pc; }
         }
         if (h->async_x) {
             // highest priority: its tiny kernels must be scheduled at once beside a flush that still has ~20 waves of
@@ -674,6 +706,28 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n, int phase 
     return EKF_OK;
 }
 
+// Lazy flush (see ekf_handle::lazy).  On entry the raw slot columns of the batch `ob` sit in h->Pc_cur (enqueued on the
+// main stream) and h->m_pend terms are pending in (Kd, Bd).  Launches the K3 pass over P on the main stream and, beside it
+// on `sg`, the batch's linearisation + gains from the copies corrected by those terms, into (Kd2, Bd2); then swaps.
+static int32_t lazy_flush_and_batch(ekf_handle* h, const BatchObs& ob) {
+    const int m_old = h->m_pend;
+    CK(cudaEventRecord(h->ev_g1, h->stream));                  // the copies are complete here; nothing has touched P yet
+    int32_t rc = (h->world > 1) ? downdate_sharded(h) : flush(h);              // K3 on the main stream; m_pend = 0
+    if (rc != EKF_OK) return rc;
+    CK(cudaStreamWaitEvent(h->sg, h->ev_g1, 0));
+    launch_batch_lin_gain(h->sg, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc_cur, h->ld,
+                          h->c_lo, std::min(h->c_hi, h->cap_n), m_old, h->Kd2, h->Bd2, 0);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->sg));      // x of the batch is final after the gain kernel on sg
+    CK(cudaEventRecord(h->ev_g2, h->sg));
+    CK(cudaStreamWaitEvent(h->stream, h->ev_g2, 0));           // later main-stream work sees x and the new terms
+    std::swap(h->Kd, h->Kd2);
+    std::swap(h->Bd, h->Bd2);
+    h->m_pend = ob.k;
+    return EKF_OK;
+}
+
 // Sharded filters queue their observations (h->q) and execute them as batches of <= defer_m:
 //   exec_sharded      one exchange of the 3 + 2k slot columns of P0, then k communication-free linearise/gain steps
 //                     replicated on every rank (x, K_q, B_q final; m_pend grows by k)
@@ -706,7 +760,8 @@ static int32_t downdate_sharded(ekf_handle* h) {
 static int32_t exec_send(ekf_handle* h) {
     const int k = (int)h->q.size();
     if (k == 0) return EKF_OK;
-    if (h->m_pend + k > h->pend_cap) {      // make room: one pass over the slab for everything pending
+    h->lazy_now = h->lazy && h->m_pend > 0 && h->m_pend + k > h->pend_cap && k >= 2 && !getenv("EKF_SHARD_PEROBS");
+    if (h->m_pend + k > h->pend_cap && !h->lazy_now) {      // make room: one pass over the slab for everything pending
         int32_t rc = downdate_sharded(h);
         if (rc != EKF_OK) return rc;
     }
@@ -725,6 +780,17 @@ static int32_t exec_finish(ekf_handle* h) {
     const SlotSet& ss = h->ss_cur;
     int32_t rcx = exchange_cols(h, ss, n, 2);
     if (rcx != EKF_OK) return rcx;
+    if (h->lazy_now) {                      // the exchanged columns are raw P0: flush on the main stream, this batch beside it
+        BatchObs ob;
+        ob.k = k;
+        for (int m = 0; m < k; ++m) {
+            const ekf_handle::QObs& o = h->q[m];
+            ob.z0[m] = o.z0; ob.z1[m] = o.z1; ob.R0[m] = o.R0; ob.R1[m] = o.R1; ob.a[m] = o.a;
+        }
+        h->q.clear();
+        h->lazy_now = false;
+        return lazy_flush_and_batch(h, ob);
+    }
     if (k >= 2 && !getenv("EKF_SHARD_PEROBS")) {
         // fused: one CTA walks the k linearisations on the exchanged (3+2k)^2 block, one grid-wide kernel builds all
         // k gain slabs (replicated on every rank from identical inputs) -- 2 launches per batch
@@ -749,7 +815,7 @@ static int32_t exec_finish(ekf_handle* h) {
     MARK_X(h);                              // x of the batch is final here, before any slab flush
     h->q.clear();
     h->m_pend = m0 + k;
-    if (h->m_pend >= h->pend_cap) return downdate_sharded(h);    // full: same flush points as the single-GPU path (bitwise equal)
+    if (h->m_pend >= h->pend_cap && !h->lazy) return downdate_sharded(h);    // full: same flush points as the single-GPU path (bitwise equal)
     return EKF_OK;
 }
 
@@ -828,13 +894,14 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
         if ((int)h->q.size() >= h->defer) return h->xstep ? exec_sharded(h) : flush_sharded(h);
         return EKF_OK;
     }
+    if (h->m_pend >= h->pend_cap) FLUSH(h);      // lazy flush leaves a full set pending: make room first
     launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
                           h->lin, h->Kd, h->Bd, h->ld, h->m_pend);
     h->launches += 2;
     CK(cudaGetLastError());
     MARK_X(h);
     h->m_pend += 1;
-    if (h->m_pend >= h->pend_cap) FLUSH(h);
+    if (h->m_pend >= h->pend_cap && !h->lazy) FLUSH(h);     // lazy: a full set waits for the next observation / batch
     return EKF_OK;
 }
 
@@ -1006,12 +1073,23 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
         while (k - i >= 2) {
             BatchObs ob;
             ob.k = std::min(k - i, std::min(h->defer, EKF_BATCH_MAX));
-            if (h->xstep && h->m_pend + ob.k > h->pend_cap) FLUSH(h);       // make room: one pass over P for everything pending
             for (int q = 0; q < ob.k; ++q) {
                 ob.z0[q] = z[i + q]; ob.z1[q] = z[i + q + k];
                 ob.R0[q] = Rdiag[i + q]; ob.R1[q] = Rdiag[i + q + k];
                 ob.a[q] = 3 + 2 * (idx1[i + q] - 1);
             }
+            if (h->lazy && h->m_pend > 0 && h->m_pend + ob.k > h->pend_cap) {
+                // lazy flush: copy the batch's slot columns out of P0, then K3 on the main stream || lin + gain on sg
+                launch_gather_cols(h->stream, h->P, h->ld, n_of(h), sym_of(h), ob, h->Pc, h->ld);
+                h->Pc_cur = h->Pc;
+                h->launches += 1;
+                CK(cudaGetLastError());
+                int32_t rcl = lazy_flush_and_batch(h, ob);
+                if (rcl != EKF_OK) return rcl;
+                i += ob.k;
+                continue;
+            }
+            if (h->xstep && h->m_pend + ob.k > h->pend_cap) FLUSH(h);       // make room: one pass over P for everything pending
             const int m0 = h->xstep ? h->m_pend : 0;
             launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
                                   nullptr, 0, 0, 0, m0);
@@ -1019,7 +1097,7 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
             CK(cudaGetLastError());
             MARK_X(h);                      // x is final for this chunk here, before the flush
             h->m_pend = m0 + ob.k;
-            if (!h->xstep || h->m_pend >= h->pend_cap) FLUSH(h);
+            if (!h->xstep || (h->m_pend >= h->pend_cap && !h->lazy)) FLUSH(h);   // lazy: a full set waits for the next batch
             i += ob.k;
         }
     }
@@ -1271,6 +1349,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
     CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
+    if (h->Kd2) CK(cudaMemsetAsync(h->Kd2, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
     CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
@@ -1355,6 +1434,7 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
         CK(cudaMemcpyAsync(dA, A, sizeof(double) * (size_t)n * r, cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemcpyAsync(dd, d, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
+        if (h->Kd2) CK(cudaMemsetAsync(h->Kd2, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
         CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
         CK(cudaMemcpyAsync(h->x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
         if (N > 0) CK(cudaMemcpyAsync(h->s, s, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));

@@ -256,7 +256,11 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
 __global__ void __launch_bounds__(128)
 k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, BatchObs ob,
              const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
-             const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi, int m0) {
+             const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi, int m0,
+             double2* __restrict__ Kout, double2* __restrict__ Bout, int o0) {
+    // Kall / Ball: the m0 pending terms (read only).  The k new terms go to slots o0 .. o0+k-1 of Kout / Bout: the same
+    // slabs with o0 = m0 normally; the OTHER pair of slabs with o0 = 0 when the pending terms are being flushed by a
+    // concurrent K3 launch (lazy flush, ekf_capi.cu).
     __shared__ BatchLin L;
     __shared__ double2 Kc[EKF_MAX_PEND][EKF_BATCH_SLOTS], Bc[EKF_MAX_PEND][EKF_BATCH_SLOTS];   // pending K_q(col_s,:), B_q(:,col_s)
     for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
@@ -315,8 +319,8 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
             gain_from_ph(ph0, ph1, L.Sinv[q], L.nu[q], k0, k1, dx);
             xi = __dadd_rn(xi, dx);
             const double2 Ki = make_double2(k0, k1), Bi = make_double2(b0, b1);
-            Kall[(m0 + q) * lds + i] = Ki;
-            if (sym || mine) Ball[(m0 + q) * lds + i] = Bi;        // FULL slabs: B_q(:, i) only where column i lives
+            Kout[(o0 + q) * lds + i] = Ki;
+            if (sym || mine) Bout[(o0 + q) * lds + i] = Bi;        // FULL slabs: B_q(:, i) only where column i lives
 #pragma unroll
             for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
                 if (s < ns) {
@@ -327,6 +331,22 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
         }
     }
     x[i] = xi;
+}
+
+// Raw copies of the slot columns of a batch, Pc[slot][i] = stored P(i, col(slot)) (SYM: the live element (min, max)):
+// what the sharded exchange delivers, gathered locally.  Taken BEFORE a flush is launched, so that the batch can be
+// linearised from them (plus the pending terms) while that flush rewrites P.
+__global__ void k_gather_cols(const double* __restrict__ P, int64_t ld, int n, int sym, BatchObs ob,
+                              double* __restrict__ Pc, int64_t ldc) {
+    const int slot = blockIdx.y;
+    const int c = slot < 3 ? slot : ob.a[(slot - 3) >> 1] + ((slot - 3) & 1);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) Pc[(int64_t)slot * ldc + i] = ldP(P, ld, i, c, sym);
+}
+
+void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc) {
+    dim3 grid((n + 255) / 256, 3 + 2 * ob.k);
+    k_gather_cols<<<grid, 256, 0, st>>>(P, ld, n, sym, ob, Pc, ldc);
 }
 
 // ------------------------------------------------------------------ K5 append
@@ -681,12 +701,13 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc, int64_t ldc,
-                           int c_lo, int c_hi, int m0) {
+                           int c_lo, int c_hi, int m0, double2* Kout, double2* Bout, int o0) {
     if (!Pc) { c_lo = 0; c_hi = n; }
+    if (!Kout) { Kout = Kall; Bout = Ball; o0 = m0; }
     k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc, Kall, Ball, lds, m0);   // >= EKF_BATCH_SLOTS^2 = 361 threads
     static int gb = 0;                     // rows per CTA of the gain kernel (EKF_GAIN_BLOCK = 32 | 64 | 128, default 128)
     if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
-    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0);
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0, Kout, Bout, o0);
 }
 
 

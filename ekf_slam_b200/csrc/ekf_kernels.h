@@ -27,7 +27,9 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
 // Pc != null (sharded): slot columns come from the exchanged Pc[slot][0..n), P is the local slab of columns [c_lo, c_hi)
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc = nullptr,
-                           int64_t ldc = 0, int c_lo = 0, int c_hi = 0, int m0 = 0);   // m0: terms already pending in slabs 0..m0-1; this batch fills m0..m0+k-1
+                           int64_t ldc = 0, int c_lo = 0, int c_hi = 0, int m0 = 0,    // m0: terms already pending in slabs 0..m0-1; this batch fills m0..m0+k-1
+                           double2* Kout = nullptr, double2* Bout = nullptr, int o0 = 0);   // ... or slots o0.. of another pair of slabs (lazy flush)
+void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc);
 // predict with m pending terms: P0 takes F . F' + Q as usual, the slabs take K_q <- F K_q, B_q <- B_q F' (rows / columns 0, 1 only)
 void launch_predict_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int m, const double* xpre, double u1);
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,

@@ -192,8 +192,9 @@ def main():
             got = g.correspondence.estimateCorrespondence(z, np.diag(Rd))
             assert got == ref.correspondence.estimateCorrespondence(z, np.diag(Rd)) == o.associate(z, Rd), (rank, z, got)
             n_new += int(got[0])
-        z = np.array([50.0, 170.0, 1.0])                 # far from everything: gated out on every rank -> new landmark N + 1
-        assert g.correspondence.estimateCorrespondence(z, np.diag([5.0, 850.0])) == (True, N + 1)
+        z = np.array([500.0, 170.0, 1.0])                # far from everything: gated out on every rank -> new landmark N + 1
+        far = g.correspondence.estimateCorrespondence(z, np.diag([1e-3, 1e-3]))
+        assert far == ref.correspondence.estimateCorrespondence(z, np.diag([1e-3, 1e-3])) == (True, N + 1), far
         print('rank %d mode B on slabs/%s: %d queries identical to the single-GPU kernel and the C oracle (%d new)' %
               (rank, storage, len(rows), n_new), flush=True)
         g.close(); ref.close()

@@ -338,3 +338,39 @@ def test_failed_measure_leaves_the_rows_before_the_error_applied(defer_m):
         o._update(r, np.diag([r[0] * 0.1, r[1] * 5.0]), int(r[2]))
     assert _rel(g.x, o.x) <= TOL and _rel(g.P, o.P) <= TOL
     g.close()
+
+
+@pytest.mark.parametrize('defer_m', [16, 11])
+def test_lazy_flush_is_bit_identical_to_flush_then_linearise(defer_m, monkeypatch):
+    """Lazy flush (cross-step deferral, SYM): the K3 pass runs on the main stream while the next batch is linearised on a
+    side stream from copies of its slot columns + the pending terms, gains into the other pair of slabs.  Same operands
+    and order as flush-first: x read at every step and the final P must equal the EKF_LAZY_FLUSH=0 path bit for bit,
+    with ragged batches, single updates, getters and appends in between."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
+    N = 700
+    x, A, d, s, lms = synthetic_spd_state(N, seed=13)
+    runs = []
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_LAZY_FLUSH', flag)
+        f = E.EKF_SLAM(capacity_landmarks=N + 4, storage='sym', defer_m=defer_m)
+        f.set_state_lowrank(x, s, A, d)
+        rng = np.random.default_rng(31)
+        xs = []
+        for step in range(14):
+            rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:(8, 8, 8, 11, 5, 8, 1, 8, 8, 3, 8, 8, 8, 8)[step]]
+            Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+            f.predict([0.3, 1.0])
+            if step == 6:
+                f.update(rows[0, :2], Rd[0], int(rows[0, 2]))
+            else:
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+            xs.append(f.x)
+            if step == 8:
+                xs.append(f.P_block(0, 0, 5, 5))
+            if step == 10:
+                f.append([0.3, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], N + 1)
+        runs.append((xs, f.P))
+        f.close()
+    assert all(np.array_equal(a, b) for a, b in zip(runs[0][0], runs[1][0])), 'x differs somewhere in the loop'
+    assert np.array_equal(runs[0][1], runs[1][1])
