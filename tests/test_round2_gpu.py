@@ -341,11 +341,13 @@ def test_failed_measure_leaves_the_rows_before_the_error_applied(defer_m):
 
 
 @pytest.mark.parametrize('defer_m', [16, 11])
-def test_lazy_flush_is_bit_identical_to_flush_then_linearise(defer_m, monkeypatch):
-    """Lazy flush (cross-step deferral, SYM): the K3 pass runs on the main stream while the next batch is linearised on a
-    side stream from copies of its slot columns + the pending terms, gains into the other pair of slabs.  Same operands
-    and order as flush-first: x read at every step and the final P must equal the EKF_LAZY_FLUSH=0 path bit for bit,
-    with ragged batches, single updates, getters and appends in between."""
+def test_lazy_flush_matches_flush_then_linearise(defer_m, monkeypatch):
+    """Lazy flush (cross-step deferral, SYM): a full set of pending terms is flushed when the NEXT batch arrives -- the K3
+    pass runs on the main stream while that batch is linearised on a side stream from copies of its slot columns + the
+    pending terms, gains into the other pair of slabs.  The linearisation itself sees the same operands in the same
+    order as flush-first; what differs from EKF_LAZY_FLUSH=0 is that a full set now also crosses the predict in between
+    (transformed there, as every pending term is), i.e. rounding in rows / columns 0-1 only: x at every step and the
+    final P agree to 1e-12, with ragged batches, single updates, getters and an append in between."""
     import ekf_slam_b200 as E
     from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
     N = 700
@@ -372,5 +374,5 @@ def test_lazy_flush_is_bit_identical_to_flush_then_linearise(defer_m, monkeypatc
                 f.append([0.3, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], N + 1)
         runs.append((xs, f.P))
         f.close()
-    assert all(np.array_equal(a, b) for a, b in zip(runs[0][0], runs[1][0])), 'x differs somewhere in the loop'
-    assert np.array_equal(runs[0][1], runs[1][1])
+    assert max(_rel(a, b) for a, b in zip(runs[0][0], runs[1][0])) <= 1e-12
+    assert _rel(runs[0][1], runs[1][1]) <= 1e-12
