@@ -174,6 +174,13 @@ __device__ __forceinline__ void innovation_cov(const double Hs[2][5], const doub
     ic_inv(S, Si);
 }
 
+// Three-term dot product with one rounding per operation, left to right (MATLAB's scalar order; never contracted): the
+// append arithmetic (EKF_SLAM.m:91-97) of the single-GPU, slab and Monte-Carlo kernels goes through it, so that the
+// three stay bit-identical whatever each translation unit's compiler would have fused.
+__device__ __forceinline__ double dot3(double a0, double b0, double a1, double b1, double a2, double b2) {
+    return __dadd_rn(__dadd_rn(__dmul_rn(a0, b0), __dmul_rn(a1, b1)), __dmul_rn(a2, b2));
+}
+
 // Gain arithmetic shared by every path (per-observation k_gain, fused k_batch_*, sharded k_gain_shard): explicit FMA
 // forms in a fixed order, so that the three paths stay bit-identical to each other whatever the compiler would contract.
 //   ph  += P(i, c_k) * Hs(:,k)                 row i of P H'  (EKF_SLAM.m:143, left factor)

@@ -361,8 +361,8 @@ __global__ void k_append(double* __restrict__ P, int64_t ld, double* __restrict_
         int a = 3 + 2 * t;
         for (int m = 0; m < 2; ++m) {
             double p0 = ldP(P, ld, a + m, 0, sym), p1 = ldP(P, ld, a + m, 1, sym), p2 = ldP(P, ld, a + m, 2, sym);
-            double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;        // jxr * P(lm,1:3)'
-            double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+            double f0 = dot3(1.0, p0, 0.0, p1, j02, p2);        // jxr * P(lm,1:3)'
+            double f1 = dot3(0.0, p0, 1.0, p1, j12, p2);
             P[(int64_t)(a + m) + (int64_t)n * ld] = f0;        // G (upper part)
             P[(int64_t)(a + m) + (int64_t)(n + 1) * ld] = f1;
             P[(int64_t)n + (int64_t)(a + m) * ld] = f0;        // F (lower part; don't-care in SYM)
@@ -377,17 +377,17 @@ __global__ void k_append(double* __restrict__ P, int64_t ld, double* __restrict_
         const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};     // :87-88
         double JP[2][3];
         for (int r = 0; r < 2; ++r)
-            for (int j = 0; j < 3; ++j) JP[r][j] = jxr[r][0] * Prr[0][j] + jxr[r][1] * Prr[1][j] + jxr[r][2] * Prr[2][j];
-        double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+            for (int j = 0; j < 3; ++j) JP[r][j] = dot3(jxr[r][0], Prr[0][j], jxr[r][1], Prr[1][j], jxr[r][2], Prr[2][j]);
+        double JR[2][2] = {{__dmul_rn(jz[0][0], R0), __dmul_rn(jz[0][1], R1)}, {__dmul_rn(jz[1][0], R0), __dmul_rn(jz[1][1], R1)}};
         for (int r = 0; r < 2; ++r)
             for (int c = 0; c < 2; ++c) {
-                double v = (JP[r][0] * jxr[c][0] + JP[r][1] * jxr[c][1] + JP[r][2] * jxr[c][2]) +
-                           (JR[r][0] * jz[c][0] + JR[r][1] * jz[c][1]);                  // :91
+                double v = __dadd_rn(dot3(JP[r][0], jxr[c][0], JP[r][1], jxr[c][1], JP[r][2], jxr[c][2]),
+                           __dadd_rn(__dmul_rn(JR[r][0], jz[c][0]), __dmul_rn(JR[r][1], jz[c][1])));                  // :91
                 P[(int64_t)(n + r) + (int64_t)(n + c) * ld] = v;
             }
         for (int i = 0; i < 3; ++i)
             for (int c = 0; c < 2; ++c) {
-                double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];   // :92
+                double v = dot3(Prr[i][0], jxr[c][0], Prr[i][1], jxr[c][1], Prr[i][2], jxr[c][2]);   // :92
                 P[(int64_t)i + (int64_t)(n + c) * ld] = v;
                 P[(int64_t)(n + c) + (int64_t)i * ld] = v;                                          // :93
             }

@@ -237,8 +237,8 @@ k_mc_step(McArgs a) {
                     const int al = 3 + 2 * t;
                     for (int mm = 0; mm < 2; ++mm) {
                         const double p0 = ldP(P, ld, al + mm, 0, sym), p1 = ldP(P, ld, al + mm, 1, sym), p2 = ldP(P, ld, al + mm, 2, sym);
-                        const double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;    // jxr * P(lm,1:3)', :95
-                        const double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+                        const double f0 = dot3(1.0, p0, 0.0, p1, j02, p2);    // jxr * P(lm,1:3)', :95
+                        const double f1 = dot3(0.0, p0, 1.0, p1, j12, p2);
                         P[(int64_t)(al + mm) + (int64_t)n * ld] = f0;
                         P[(int64_t)(al + mm) + (int64_t)(n + 1) * ld] = f1;
                         P[(int64_t)n + (int64_t)(al + mm) * ld] = f0;
@@ -253,16 +253,16 @@ k_mc_step(McArgs a) {
                     const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};             // :87-88
                     double JP[2][3];
                     for (int r = 0; r < 2; ++r)
-                        for (int j = 0; j < 3; ++j) JP[r][j] = jxr[r][0] * Prr[0][j] + jxr[r][1] * Prr[1][j] + jxr[r][2] * Prr[2][j];
-                    const double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+                        for (int j = 0; j < 3; ++j) JP[r][j] = dot3(jxr[r][0], Prr[0][j], jxr[r][1], Prr[1][j], jxr[r][2], Prr[2][j]);
+                    const double JR[2][2] = {{__dmul_rn(jz[0][0], R0), __dmul_rn(jz[0][1], R1)}, {__dmul_rn(jz[1][0], R0), __dmul_rn(jz[1][1], R1)}};
                     for (int r = 0; r < 2; ++r)
                         for (int c = 0; c < 2; ++c)
                             P[(int64_t)(n + r) + (int64_t)(n + c) * ld] =
-                                (JP[r][0] * jxr[c][0] + JP[r][1] * jxr[c][1] + JP[r][2] * jxr[c][2]) +
-                                (JR[r][0] * jz[c][0] + JR[r][1] * jz[c][1]);             // :91
+                                __dadd_rn(dot3(JP[r][0], jxr[c][0], JP[r][1], jxr[c][1], JP[r][2], jxr[c][2]),
+                                __dadd_rn(__dmul_rn(JR[r][0], jz[c][0]), __dmul_rn(JR[r][1], jz[c][1])));             // :91
                     for (int i = 0; i < 3; ++i)
                         for (int c = 0; c < 2; ++c) {
-                            const double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];   // :92
+                            const double v = dot3(Prr[i][0], jxr[c][0], Prr[i][1], jxr[c][1], Prr[i][2], jxr[c][2]);   // :92
                             P[(int64_t)i + (int64_t)(n + c) * ld] = v;
                             P[(int64_t)(n + c) + (int64_t)i * ld] = v;                   // :93
                         }
@@ -845,8 +845,8 @@ k_mc_front(McArgs a) {
                     const int al = 3 + 2 * t;
                     for (int mm = 0; mm < 2; ++mm) {
                         const double p0 = ldP(P, ld, al + mm, 0, SYM), p1 = ldP(P, ld, al + mm, 1, SYM), p2 = ldP(P, ld, al + mm, 2, SYM);
-                        const double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;    // jxr * P(lm,1:3)', :95
-                        const double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+                        const double f0 = dot3(1.0, p0, 0.0, p1, j02, p2);    // jxr * P(lm,1:3)', :95
+                        const double f1 = dot3(0.0, p0, 1.0, p1, j12, p2);
                         P[(int64_t)(al + mm) + (int64_t)n * ld] = f0;
                         P[(int64_t)(al + mm) + (int64_t)(n + 1) * ld] = f1;
                         P[(int64_t)n + (int64_t)(al + mm) * ld] = f0;
@@ -862,7 +862,7 @@ k_mc_front(McArgs a) {
                     double JP[2][3];
                     for (int rr = 0; rr < 2; ++rr)
                         for (int j = 0; j < 3; ++j) JP[rr][j] = jxr[rr][0] * Prr[0][j] + jxr[rr][1] * Prr[1][j] + jxr[rr][2] * Prr[2][j];
-                    const double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+                    const double JR[2][2] = {{__dmul_rn(jz[0][0], R0), __dmul_rn(jz[0][1], R1)}, {__dmul_rn(jz[1][0], R0), __dmul_rn(jz[1][1], R1)}};
                     for (int rr = 0; rr < 2; ++rr)
                         for (int c = 0; c < 2; ++c)
                             P[(int64_t)(n + rr) + (int64_t)(n + c) * ld] =
@@ -870,7 +870,7 @@ k_mc_front(McArgs a) {
                                 (JR[rr][0] * jz[c][0] + JR[rr][1] * jz[c][1]);           // :91
                     for (int i = 0; i < 3; ++i)
                         for (int c = 0; c < 2; ++c) {
-                            const double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];   // :92
+                            const double v = dot3(Prr[i][0], jxr[c][0], Prr[i][1], jxr[c][1], Prr[i][2], jxr[c][2]);   // :92
                             P[(int64_t)i + (int64_t)(n + c) * ld] = v;
                             P[(int64_t)(n + c) + (int64_t)i * ld] = v;                   // :93
                         }

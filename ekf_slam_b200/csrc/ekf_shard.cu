@@ -250,8 +250,8 @@ __global__ void k_append_shard(double* __restrict__ Ploc, int64_t ld, int c_lo, 
         const int a = 3 + 2 * t;
         for (int m = 0; m < 2; ++m) {
             double p0 = Pc[a + m], p1 = Pc[ldc + a + m], p2 = Pc[2 * ldc + a + m];
-            double f0 = 1.0 * p0 + 0.0 * p1 + j02 * p2;
-            double f1 = 0.0 * p0 + 1.0 * p1 + j12 * p2;
+            double f0 = dot3(1.0, p0, 0.0, p1, j02, p2);
+            double f1 = dot3(0.0, p0, 1.0, p1, j12, p2);
             if (own_new) {
                 Ploc[(int64_t)(a + m) + (int64_t)(n - c_lo) * ld] = f0;
                 Ploc[(int64_t)(a + m) + (int64_t)(n + 1 - c_lo) * ld] = f1;
@@ -270,17 +270,17 @@ __global__ void k_append_shard(double* __restrict__ Ploc, int64_t ld, int c_lo, 
         const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};
         double JP[2][3];
         for (int r = 0; r < 2; ++r)
-            for (int j = 0; j < 3; ++j) JP[r][j] = jxr[r][0] * Prr[0][j] + jxr[r][1] * Prr[1][j] + jxr[r][2] * Prr[2][j];
-        double JR[2][2] = {{jz[0][0] * R0, jz[0][1] * R1}, {jz[1][0] * R0, jz[1][1] * R1}};
+            for (int j = 0; j < 3; ++j) JP[r][j] = dot3(jxr[r][0], Prr[0][j], jxr[r][1], Prr[1][j], jxr[r][2], Prr[2][j]);
+        double JR[2][2] = {{__dmul_rn(jz[0][0], R0), __dmul_rn(jz[0][1], R1)}, {__dmul_rn(jz[1][0], R0), __dmul_rn(jz[1][1], R1)}};
         for (int r = 0; r < 2; ++r)
             for (int c = 0; c < 2; ++c) {
-                double v = (JP[r][0] * jxr[c][0] + JP[r][1] * jxr[c][1] + JP[r][2] * jxr[c][2]) +
-                           (JR[r][0] * jz[c][0] + JR[r][1] * jz[c][1]);
+                double v = __dadd_rn(dot3(JP[r][0], jxr[c][0], JP[r][1], jxr[c][1], JP[r][2], jxr[c][2]),
+                           __dadd_rn(__dmul_rn(JR[r][0], jz[c][0]), __dmul_rn(JR[r][1], jz[c][1])));
                 if (own_new) Ploc[(int64_t)(n + r) + (int64_t)(n + c - c_lo) * ld] = v;
             }
         for (int i = 0; i < 3; ++i)
             for (int c = 0; c < 2; ++c) {
-                double v = Prr[i][0] * jxr[c][0] + Prr[i][1] * jxr[c][1] + Prr[i][2] * jxr[c][2];
+                double v = dot3(Prr[i][0], jxr[c][0], Prr[i][1], jxr[c][1], Prr[i][2], jxr[c][2]);
                 if (own_new) Ploc[(int64_t)i + (int64_t)(n + c - c_lo) * ld] = v;
                 if (c_lo == 0) Ploc[(int64_t)(n + c) + (int64_t)i * ld] = v;
             }
