@@ -106,6 +106,7 @@ struct McArgs {
     int* Mpend;                                  // split step: pending rank-2 terms per filter
     double C, Rc0, Rc1, s_cost, s_thresh;
     int variant, assoc_mode, sym, do_predict, do_measure, maxd;
+    int robot_cache;                             // split front: keep the 3 robot rows of P0 in shared memory for the whole step
 };
 
 enum { MC_ERR_TABLE = 1, MC_ERR_CAPACITY = 2, MC_ERR_INDEX = 3 };

@@ -29,6 +29,7 @@ struct McShared {                                // small per-CTA scratch (the s
     int wi[32];
     double best; int bidx;
     int N, m, action, fatal;
+    int rr_ok;                                   // the shared-memory copy of the robot rows matches P0
     double pos[2];
 };
 
@@ -123,9 +124,24 @@ k_mc_step(McArgs a) {
     double2* Bs = SPLIT ? a.Bg + (int64_t)f * a.maxd * lds : Ks + (int64_t)a.maxd * lds;
     if (!SPLIT)
         for (int64_t e = tid; e < 2 * (int64_t)a.maxd * lds; e += T) Ks[e] = make_double2(0.0, 0.0);
-    if (tid == 0) { sh.N = a.N[f]; sh.m = 0; sh.fatal = 0; }
+    if (tid == 0) { sh.N = a.N[f]; sh.m = 0; sh.fatal = 0; sh.rr_ok = 0; }
     __syncthreads();
     const double u1 = a.u[2 * f], u2 = a.u[2 * f + 1];
+    // Robot-row cache (split front): every update needs P(0:2, i) for all i -- in column-major storage one 32-byte sector
+    // per column at stride ld, the same 400 scattered sectors for each of the step's observations.  P0 does not change
+    // during a split step (the terms stay pending), so the three rows are read ONCE per step -- predict has them in its
+    // hands anyway -- and served from shared memory afterwards: rr[k * ld + i] = stored P0(k, i).  Same values, same
+    // arithmetic: bit-identical.  An append or an in-kernel flush rewrites P0 and invalidates the copy.
+    double* rr = (SPLIT && a.robot_cache) ? (double*)mc_dyn : nullptr;
+    auto rr_fill = [&](int n_) {
+        for (int t = tid; t < n_; t += T) {
+            const double* col = P + (int64_t)t * ld;
+            rr[t] = col[0]; rr[ld + t] = col[1]; rr[2 * ld + t] = col[2];
+        }
+        __syncthreads();
+        if (tid == 0) sh.rr_ok = 1;
+        __syncthreads();
+    };
 
     // ------------------------------------------------------------ predict (EKF_SLAM.m:40-51), nothing pending
     if (a.do_predict) {
@@ -150,8 +166,10 @@ k_mc_step(McArgs a) {
         for (int t = 3 + tid; t < n; t += T) {
             double* col = P + (int64_t)t * ld;
             const double p2 = col[2];
-            col[0] = col[0] + fa * p2;
-            col[1] = col[1] + fb * p2;
+            const double c0 = col[0] + fa * p2, c1 = col[1] + fb * p2;
+            col[0] = c0;
+            col[1] = c1;
+            if (rr) { rr[t] = c0; rr[ld + t] = c1; rr[2 * ld + t] = p2; }
             if (!sym) {
                 const double q2 = P[t + 2 * ld];
                 P[t] = P[t] + q2 * fa;
@@ -159,6 +177,11 @@ k_mc_step(McArgs a) {
             }
         }
         __syncthreads();
+        if (rr) {                                                // columns 0..2 (the corner thread 0 just wrote)
+            if (tid < 3) { const double* col = P + (int64_t)tid * ld; rr[tid] = col[0]; rr[ld + tid] = col[1]; rr[2 * ld + tid] = col[2]; }
+            if (tid == 0) sh.rr_ok = 1;
+            __syncthreads();
+        }
     }
 
     // ------------------------------------------------------------ measure (EKF_SLAM.m:100-151, EKF_SLAM_UC.m:102-152)
@@ -271,7 +294,7 @@ k_mc_step(McArgs a) {
                 }
             }
             __syncthreads();
-            if (tid == 0) { sh.N = N + 1; sh.m = 0; }
+            if (tid == 0) { sh.N = N + 1; sh.m = 0; sh.rr_ok = 0; }
             __syncthreads();
             continue;
         }
@@ -279,6 +302,7 @@ k_mc_step(McArgs a) {
         // -------------------------------------------------------- update (EKF_SLAM.m:124-145)
         const int al = 3 + 2 * (idx - 1);
         const int c[5] = {0, 1, 2, al, al + 1};
+        if (rr && !sh.rr_ok) rr_fill(n);                 // block-uniform: no predict in this call, or P0 was rewritten
         // pending gains of the 5 slot rows / columns, gathered once per observation: every later correction then
         // costs shared-memory reads instead of a chain of dependent L2 round trips (same terms, same order as mc_cur)
         if (tid < 10 * m) {
@@ -324,8 +348,9 @@ k_mc_step(McArgs a) {
             double pc[5], pr[5];
 #pragma unroll
             for (int k = 0; k < 5; ++k) {
-                if (sym) pc[k] = i <= c[k] ? P[(int64_t)i + (int64_t)c[k] * ld] : P[(int64_t)c[k] + (int64_t)i * ld];
-                else { pc[k] = P[(int64_t)i + (int64_t)c[k] * ld]; pr[k] = P[(int64_t)c[k] + (int64_t)i * ld]; }
+                const bool cached = rr && k < 3;         // P(k, i): the robot rows, from shared memory
+                if (sym) pc[k] = i <= c[k] ? P[(int64_t)i + (int64_t)c[k] * ld] : (cached ? rr[(int64_t)k * ld + i] : P[(int64_t)c[k] + (int64_t)i * ld]);
+                else { pc[k] = P[(int64_t)i + (int64_t)c[k] * ld]; pr[k] = cached ? rr[(int64_t)k * ld + i] : P[(int64_t)c[k] + (int64_t)i * ld]; }
             }
             for (int q0 = 0; q0 < m; q0 += 4) {                  // pending terms four at a time: their slab loads overlap too
                 double2 kq[4], bq[4];
@@ -365,7 +390,7 @@ k_mc_step(McArgs a) {
         if (m + 1 >= a.maxd && !(SPLIT && ii == cnt)) {        // slabs full (split: the last batch is left to k_mc_flush)
             mc_flush(P, ld, n, sym, Ks, Bs, lds, m + 1);
             __syncthreads();
-            if (tid == 0) sh.m = 0;
+            if (tid == 0) { sh.m = 0; sh.rr_ok = 0; }
         } else if (tid == 0) sh.m = m + 1;
         __syncthreads();
     }
@@ -861,13 +886,13 @@ k_mc_front(McArgs a) {
                     const double jz[2][2] = {{cu, -u1 * su}, {su, u1 * cu}};             // :87-88
                     double JP[2][3];
                     for (int rr = 0; rr < 2; ++rr)
-                        for (int j = 0; j < 3; ++j) JP[rr][j] = jxr[rr][0] * Prr[0][j] + jxr[rr][1] * Prr[1][j] + jxr[rr][2] * Prr[2][j];
+                        for (int j = 0; j < 3; ++j) JP[rr][j] = dot3(jxr[rr][0], Prr[0][j], jxr[rr][1], Prr[1][j], jxr[rr][2], Prr[2][j]);
                     const double JR[2][2] = {{__dmul_rn(jz[0][0], R0), __dmul_rn(jz[0][1], R1)}, {__dmul_rn(jz[1][0], R0), __dmul_rn(jz[1][1], R1)}};
                     for (int rr = 0; rr < 2; ++rr)
                         for (int c = 0; c < 2; ++c)
                             P[(int64_t)(n + rr) + (int64_t)(n + c) * ld] =
-                                (JP[rr][0] * jxr[c][0] + JP[rr][1] * jxr[c][1] + JP[rr][2] * jxr[c][2]) +
-                                (JR[rr][0] * jz[c][0] + JR[rr][1] * jz[c][1]);           // :91
+                                __dadd_rn(dot3(JP[rr][0], jxr[c][0], JP[rr][1], jxr[c][1], JP[rr][2], jxr[c][2]),
+                                __dadd_rn(__dmul_rn(JR[rr][0], jz[c][0]), __dmul_rn(JR[rr][1], jz[c][1])));   // :91
                     for (int i = 0; i < 3; ++i)
                         for (int c = 0; c < 2; ++c) {
                             const double v = dot3(Prr[i][0], jxr[c][0], Prr[i][1], jxr[c][1], Prr[i][2], jxr[c][2]);   // :92
@@ -933,8 +958,15 @@ void launch_mc_front(cudaStream_t st, const McArgs& a, int n_filters, size_t sme
         }
         return;
     }
-    if (mb) k_mc_step<1, 1><<<n_filters, 128, 0, st>>>(a);
-    else k_mc_step<0, 1><<<n_filters, 128, 0, st>>>(a);
+    // robot-row cache: 3 ld doubles of dynamic shared memory per filter (9.9 KB at 200 landmarks; 4 CTAs/SM stay resident)
+    static int rc_env = -1;
+    if (rc_env < 0) { const char* v = getenv("EKF_MC_ROBOT_CACHE"); rc_env = v ? atoi(v) : 1; }
+    McArgs b = a;
+    const size_t rsm = 3 * sizeof(double) * (size_t)a.ldp;
+    b.robot_cache = rc_env && rsm <= 40 * 1024;
+    const size_t dyn = b.robot_cache ? rsm : 0;
+    if (mb) k_mc_step<1, 1><<<n_filters, 128, dyn, st>>>(b);
+    else k_mc_step<0, 1><<<n_filters, 128, dyn, st>>>(b);
 }
 
 void launch_mc_flush(cudaStream_t st, const McArgs& a, int n_filters, int cap_n, int m_max) {
