@@ -48,6 +48,8 @@ SIGNATURES = {
     'ekf_append': [_H, _DP, _DP, _DP, C.c_double],
     'ekf_associate': [_H, _DP, _DP, _IP, _IP],
     'ekf_measure_batch': [_H, _DP, C.c_int32, _DP, _DP, _IP, C.c_int32, _IP],
+    'ekf_measure_batch_async': [_H, _DP, C.c_int32, _DP, _DP, _IP, C.c_int32, _IP],
+    'ekf_measure_wait': [_H],
     'ekf_n_landmarks': [_H, _IP],
     'ekf_get_x': [_H, _DP, C.c_int32],
     'ekf_get_s': [_H, _DP, C.c_int32],

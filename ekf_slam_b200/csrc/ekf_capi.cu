@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <string>
 #include <vector>
+#include <unordered_map>
 
 using namespace ekf;
 
@@ -91,6 +92,24 @@ struct ekf_handle {
     unsigned int* ticket = nullptr;
     AssocResult* d_res = nullptr;
     AssocResult* h_res = nullptr;   // pinned
+    // ---- measure() decided on the device (EKF_SLAM_UC, mode A; EKF_ASYNC_MEASURE=0 disables): ekf_measure_batch_async
+    // uploads observed_LL, lets k_measure_decide pick the slots, enqueues the update kernels behind it and returns without
+    // waiting; the actions reach the caller at the next call on the handle (or ekf_measure_wait).  The host takes this path
+    // only when every row's signature is already in the map -- `sigs` mirrors the signatures it has appended / uploaded --
+    // so that no row can need the landmark table (an append), which only exists for the duration of the call.
+    std::unordered_map<uint64_t, int> sigs;
+    bool am_enable = false, am_pending = false;
+    int am_k = 0;
+    int32_t* am_act_out = nullptr;
+    double* am_obs_h = nullptr;      // pinned staging of observed_LL (k x 3)
+    double* am_obs_d = nullptr;
+    BatchObs* am_chunks = nullptr;   // EKF_ASSOC_BATCH / EKF_BATCH_MAX batch descriptions
+    int* am_skip = nullptr;
+    int* am_status = nullptr;        // mapped pinned: [0] = 1 if the device found a row it could not serve, [1 + i] = action of row i
+    int* am_status_d = nullptr;
+    int* am_scratch = nullptr;
+    unsigned int* am_ticket = nullptr;
+    cudaEvent_t ev_dec = nullptr;
     // sticky device->host status words in mapped pinned memory (kernels write them only when something is wrong; the host
     // looks at them after every synchronisation): [0] non-finite innovation covariance, [1] peer exchange timed out
     int* hflags = nullptr;
@@ -138,6 +157,28 @@ static int32_t after_sync(ekf_handle* h) {
     }
     return EKF_OK;
 }
+
+static inline uint64_t sig_key(double v) { uint64_t k; if (v == 0.0) v = 0.0; memcpy(&k, &v, 8); return k; }
+static void sigs_reset(ekf_handle* h, const double* s, int N) {
+    h->sigs.clear();
+    for (int i = 0; i < N; ++i) h->sigs[sig_key(s[i])] += 1;
+}
+
+// Decisions of the last ekf_measure_batch_async: wait for the decision kernel (NOT for the updates or the flush behind
+// it), hand the actions to the caller's buffer.  Called at the top of every entry point; usually the kernel is long done.
+static int32_t resolve_measure(ekf_handle* h) {
+    if (!h->am_pending) return EKF_OK;
+    h->am_pending = false;
+    CK(cudaEventSynchronize(h->ev_dec));
+    if (h->am_act_out)
+        for (int i = 0; i < h->am_k; ++i) h->am_act_out[i] = h->am_status[1 + i];
+    h->am_act_out = nullptr;
+    if (h->am_status[0])        // cannot happen while the signature mirror is right; the batch contributed nothing
+        return fail(h, EKF_EINVAL, "measure: the device found a row whose signature is not in the map although the host's "
+                                   "signature mirror said otherwise; that measure() was not applied");
+    return EKF_OK;
+}
+#define RESOLVE(h) do { if ((h)->am_pending) { int32_t rc__ = resolve_measure(h); if (rc__ != EKF_OK) return rc__; } } while (0)
 
 static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing main-stream work that touches x / s
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->stream));
@@ -271,6 +312,10 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
     if (h->hflags) cudaFreeHost(h->hflags);
+    if (h->am_obs_h) cudaFreeHost(h->am_obs_h);
+    if (h->am_status) cudaFreeHost(h->am_status);
+    cudaFree(h->am_obs_d); cudaFree(h->am_chunks); cudaFree(h->am_skip); cudaFree(h->am_scratch); cudaFree(h->am_ticket);
+    if (h->ev_dec) cudaEventDestroy(h->ev_dec);
     if (h->sx) { cudaStreamSynchronize(h->sx); cudaStreamDestroy(h->sx); }
     if (h->ev_mx) cudaEventDestroy(h->ev_mx);
     if (h->ev_px) cudaEventDestroy(h->ev_px);
@@ -294,6 +339,7 @@ static int32_t init_state(ekf_handle* h) {
     CK(cudaStreamSynchronize(h->stream));
     h->N = 0;
     h->m_pend = 0;
+    h->sigs.clear();
     return EKF_OK;
 }
 
@@ -447,6 +493,25 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             CK(cudaMemset(h->Bd2, 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
             if (world == 1) { CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS)); h->Pc_cur = h->Pc; }
         }
+        {
+            const char* am = getenv("EKF_ASYNC_MEASURE");
+            h->am_enable = world == 1 && h->async_x && h->defer >= 2 && p->variant == EKF_VARIANT_UC &&
+                           p->assoc_mode == EKF_ASSOC_SIGNATURE && !(am && atoi(am) == 0);
+        }
+        if (h->am_enable) {
+            CK(cudaMallocHost(&h->am_obs_h, sizeof(double) * 3 * EKF_ASSOC_BATCH));
+            CK(cudaMalloc(&h->am_obs_d, sizeof(double) * 3 * EKF_ASSOC_BATCH));
+            CK(cudaMalloc(&h->am_chunks, sizeof(BatchObs) * (EKF_ASSOC_BATCH / EKF_BATCH_MAX)));
+            CK(cudaMalloc(&h->am_skip, sizeof(int)));
+            CK(cudaMemset(h->am_skip, 0, sizeof(int)));
+            CK(cudaHostAlloc(&h->am_status, sizeof(int) * (1 + EKF_ASSOC_BATCH), cudaHostAllocMapped | cudaHostAllocPortable));
+            memset(h->am_status, 0, sizeof(int) * (1 + EKF_ASSOC_BATCH));
+            CK(cudaHostGetDevicePointer(&h->am_status_d, h->am_status, 0));
+            CK(cudaMalloc(&h->am_scratch, sizeof(int) * EKF_ASSOC_BATCH));
+            CK(cudaMalloc(&h->am_ticket, sizeof(unsigned int)));
+            CK(cudaMemset(h->am_ticket, 0, sizeof(unsigned int)));
+            CK(cudaEventCreateWithFlags(&h->ev_dec, cudaEventDisableTiming));
+        }
         if (h->async_x) {
             // highest priority: its tiny kernels must be scheduled at once beside a flush that still has ~20 waves of
             // CTAs waiting (at equal priority the block scheduler drains the flush's grid first)
@@ -560,6 +625,7 @@ extern "C" const char* ekf_last_error(ekf_handle* h) { return h ? h->err.c_str()
 
 extern "C" int32_t ekf_sync(ekf_handle* h) {
     CKH(h);
+    RESOLVE(h);
     if (is_front(h)) { FAN_OUT(h, sh, ekf_sync(sh)); return EKF_OK; }
     CK(cudaStreamSynchronize(h->stream));
     if (h->sx) CK(cudaStreamSynchronize(h->sx));
@@ -582,6 +648,7 @@ extern "C" int32_t ekf_defer_info(ekf_handle* h, int32_t* batch, int32_t* pend_c
 
 extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost, double s_thresh) {
     CKH(h);
+    RESOLVE(h);
     if (is_front(h)) FAN_OUT(h, sh, ekf_set_noise(sh, C, Rc, s_cost, s_thresh));
     h->p.C = C; h->p.Rc[0] = Rc[0]; h->p.Rc[1] = Rc[1]; h->p.s_cost = s_cost; h->p.s_thresh = s_thresh;
     return EKF_OK;
@@ -590,6 +657,7 @@ extern "C" int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], do
 // ---------------------------------------------------------------- predict / update / append / associate
 extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
     CKH(h);
+    RESOLVE(h);
     if (!u) return fail(h, EKF_EINVAL, "u is null");
     if (is_front(h)) {                       // x must be final on every slab before the motion step
         int32_t rcf = h->xstep ? front_exec(h) : front_flush(h);
@@ -709,14 +777,14 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n, int phase 
 // Lazy flush (see ekf_handle::lazy).  On entry the raw slot columns of the batch `ob` sit in h->Pc_cur (enqueued on the
 // main stream) and h->m_pend terms are pending in (Kd, Bd).  Launches the K3 pass over P on the main stream and, beside it
 // on `sg`, the batch's linearisation + gains from the copies corrected by those terms, into (Kd2, Bd2); then swaps.
-static int32_t lazy_flush_and_batch(ekf_handle* h, const BatchObs& ob) {
+static int32_t lazy_flush_and_batch(ekf_handle* h, const BatchObs& ob, ObSrc src = ObSrc{nullptr, nullptr}) {
     const int m_old = h->m_pend;
     CK(cudaEventRecord(h->ev_g1, h->stream));                  // the copies are complete here; nothing has touched P yet
     int32_t rc = (h->world > 1) ? downdate_sharded(h) : flush(h);              // K3 on the main stream; m_pend = 0
     if (rc != EKF_OK) return rc;
     CK(cudaStreamWaitEvent(h->sg, h->ev_g1, 0));
     launch_batch_lin_gain(h->sg, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc_cur, h->ld,
-                          h->c_lo, std::min(h->c_hi, h->cap_n), m_old, h->Kd2, h->Bd2, 0);
+                          h->c_lo, std::min(h->c_hi, h->cap_n), m_old, h->Kd2, h->Bd2, 0, src);
     h->launches += 2;
     CK(cudaGetLastError());
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->sg));      // x of the batch is final after the gain kernel on sg
@@ -871,6 +939,7 @@ static int32_t flush(ekf_handle* h) {
 
 extern "C" int32_t ekf_flush(ekf_handle* h) {
     CKH(h);
+    RESOLVE(h);
     if (is_front(h)) return flush(h);
     CK(cudaSetDevice(h->p.device));
     return flush(h);
@@ -878,6 +947,7 @@ extern "C" int32_t ekf_flush(ekf_handle* h) {
 
 extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdiag[2], int32_t idx1) {
     CKH(h);
+    RESOLVE(h);
     if (!z || !Rdiag) return fail(h, EKF_EINVAL, "null argument");
     if (idx1 < 1 || idx1 > h->N)      // MATLAB would raise "index exceeds array bounds" at EKF_SLAM.m:125
         return fail(h, EKF_EINVAL, "ekf_update: landmark index " + std::to_string(idx1) + " outside 1.." + std::to_string(h->N));
@@ -923,6 +993,7 @@ static int32_t append_sharded(ekf_handle* h, const double u[2], const double Rdi
 extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdiag[2], const double pos[2],
                               double signature) {
     CKH(h);
+    RESOLVE(h);
     if (!u || !Rdiag || !pos) return fail(h, EKF_EINVAL, "null argument");
     if (h->N >= h->p.capacity_landmarks)
         return fail(h, EKF_ECAPACITY, "ekf_append: capacity_landmarks=" + std::to_string(h->p.capacity_landmarks) + " reached");
@@ -947,6 +1018,7 @@ extern "C" int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdi
     CK(cudaGetLastError());
     MARK_X(h);
     h->N += 1;
+    h->sigs[sig_key(signature)] += 1;
     return EKF_OK;
 }
 
@@ -992,6 +1064,7 @@ static int32_t associate_b_sharded(ekf_handle* h, const double z[3], const doubl
 extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double Rdiag[2], int32_t* newLL,
                                  int32_t* idx1) {
     CKH(h);
+    RESOLVE(h);
     if (!z || !Rdiag || !newLL || !idx1) return fail(h, EKF_EINVAL, "null argument");
     if (h->N == 0) { *newLL = 1; *idx1 = 1; return EKF_OK; }   // Correspondence.m:33,40 with an empty loop
     if (is_front(h)) {
@@ -1048,8 +1121,33 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
 
 // k updates with explicit slots: the update branch of measure() (EKF_SLAM.m:124-145) for a batch whose
 // correspondences are already decided.  z is k x 2 and Rdiag k x 2, column-major like observed_LL.
+// One fused chunk (<= 8 observations with decided slots) on a single-GPU handle: make room / lazy flush, k_batch_lin +
+// k_batch_gain, flush policy.  `ob` carries the batch by value, or only its size when `src` names a device-side
+// description (slots decided by k_measure_decide).
+static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
+    if (h->lazy && h->m_pend > 0 && h->m_pend + ob.k > h->pend_cap) {
+        // lazy flush: copy the batch's slot columns out of P0, then K3 on the main stream || lin + gain on sg
+        launch_gather_cols(h->stream, h->P, h->ld, n_of(h), sym_of(h), ob, h->Pc, h->ld, src);
+        h->Pc_cur = h->Pc;
+        h->launches += 1;
+        CK(cudaGetLastError());
+        return lazy_flush_and_batch(h, ob, src);
+    }
+    if (h->xstep && h->m_pend + ob.k > h->pend_cap) FLUSH(h);       // make room: one pass over P for everything pending
+    const int m0 = h->xstep ? h->m_pend : 0;
+    launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
+                          nullptr, 0, 0, 0, m0, nullptr, nullptr, 0, src);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    MARK_X(h);                      // x is final for this chunk here, before the flush
+    h->m_pend = m0 + ob.k;
+    if (!h->xstep || (h->m_pend >= h->pend_cap && !h->lazy)) FLUSH(h);   // lazy: a full set waits for the next batch
+    return EKF_OK;
+}
+
 extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, const double* Rdiag, const int32_t* idx1) {
     CKH(h);
+    RESOLVE(h);
     if (k < 0 || (k > 0 && (!z || !Rdiag || !idx1))) return fail(h, EKF_EINVAL, "null argument");
     if (is_front(h)) {
         for (int j = 0; j < k; ++j)
@@ -1078,26 +1176,8 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
                 ob.R0[q] = Rdiag[i + q]; ob.R1[q] = Rdiag[i + q + k];
                 ob.a[q] = 3 + 2 * (idx1[i + q] - 1);
             }
-            if (h->lazy && h->m_pend > 0 && h->m_pend + ob.k > h->pend_cap) {
-                // lazy flush: copy the batch's slot columns out of P0, then K3 on the main stream || lin + gain on sg
-                launch_gather_cols(h->stream, h->P, h->ld, n_of(h), sym_of(h), ob, h->Pc, h->ld);
-                h->Pc_cur = h->Pc;
-                h->launches += 1;
-                CK(cudaGetLastError());
-                int32_t rcl = lazy_flush_and_batch(h, ob);
-                if (rcl != EKF_OK) return rcl;
-                i += ob.k;
-                continue;
-            }
-            if (h->xstep && h->m_pend + ob.k > h->pend_cap) FLUSH(h);       // make room: one pass over P for everything pending
-            const int m0 = h->xstep ? h->m_pend : 0;
-            launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
-                                  nullptr, 0, 0, 0, m0);
-            h->launches += 2;
-            CK(cudaGetLastError());
-            MARK_X(h);                      // x is final for this chunk here, before the flush
-            h->m_pend = m0 + ob.k;
-            if (!h->xstep || (h->m_pend >= h->pend_cap && !h->lazy)) FLUSH(h);   // lazy: a full set waits for the next batch
+            int32_t rcc = fused_chunk(h, ob, ObSrc{nullptr, nullptr});
+            if (rcc != EKF_OK) return rcc;
             i += ob.k;
         }
     }
@@ -1110,12 +1190,76 @@ extern "C" int32_t ekf_update_batch(ekf_handle* h, int32_t k, const double* z, c
     return flush(h);
 }
 
-// measure() control flow, EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151 (host-driven in this revision).
+// The whole measure() on the device when it can be (see ekf_handle::sigs): returns 1 when it enqueued the call, 0 when the
+// host loop has to run (an append may be needed, a variant / mode the device path does not serve), < 0 on error.
+static int32_t measure_on_device(ekf_handle* h, const double* obs, int32_t k, int32_t* action_out) {
+    if (!h->am_enable || h->N == 0 || k < 1 || k > EKF_ASSOC_BATCH) return 0;
+    for (int i = 0; i < k; ++i)
+        if (h->sigs.find(sig_key(obs[i + 2 * k])) == h->sigs.end()) return 0;     // unseen signature: an append may be needed
+    CK(cudaSetDevice(h->p.device));
+    memcpy(h->am_obs_h, obs, sizeof(double) * 3 * k);
+    // decisions on the side stream, behind the last writer of s (like the batched association), not behind a flush
+    CK(cudaStreamWaitEvent(h->sx, h->ev_mx, 0));
+    CK(cudaMemcpyAsync(h->am_obs_d, h->am_obs_h, sizeof(double) * 3 * k, cudaMemcpyHostToDevice, h->sx));
+    launch_measure_decide(h->sx, h->s, h->N, h->am_obs_d, k, h->p.Rc[0], h->p.Rc[1], h->p.s_cost, h->p.s_thresh, h->am_chunks,
+                          h->am_skip, h->am_status_d, h->am_scratch, h->am_ticket);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(h->ev_dec, h->sx));
+    CK(cudaStreamWaitEvent(h->stream, h->ev_dec, 0));
+    if (h->sg) CK(cudaStreamWaitEvent(h->sg, h->ev_dec, 0));
+    if (!h->xstep) FLUSH(h);
+    for (int c = 0; c * EKF_BATCH_MAX < k; ++c) {                      // rows 8c .. 8c+7, in order (EKF_SLAM_UC.m:109)
+        BatchObs ob;
+        memset(&ob, 0, sizeof(ob));
+        ob.k = std::min(EKF_BATCH_MAX, k - c * EKF_BATCH_MAX);
+        int32_t rc = fused_chunk(h, ob, ObSrc{h->am_chunks + c, h->am_skip});
+        if (rc != EKF_OK) return rc;
+    }
+    h->am_pending = true;
+    h->am_k = k;
+    h->am_act_out = action_out;
+    return 1;
+}
+
+extern "C" int32_t ekf_measure_wait(ekf_handle* h) {
+    CKH(h);
+    if (is_front(h)) return EKF_OK;
+    return resolve_measure(h);
+}
+
+static int32_t measure_host_loop(ekf_handle* h, const double* obs, int32_t k, const double u[2], const double* loc_table,
+                                 const int32_t* index_table, int32_t n_table, int32_t* action_out);
+
+// measure(): EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151.  _async: the actions (and a possible error of the device path)
+// arrive at the next call on the handle or at ekf_measure_wait; action_out must stay valid until then.
+extern "C" int32_t ekf_measure_batch_async(ekf_handle* h, const double* obs, int32_t k, const double u[2],
+                                           const double* loc_table, const int32_t* index_table, int32_t n_table,
+                                           int32_t* action_out) {
+    CKH(h);
+    if (k < 0 || (k > 0 && !obs) || !u) return fail(h, EKF_EINVAL, "null argument");
+    if (!is_front(h)) {
+        RESOLVE(h);
+        int32_t rd = measure_on_device(h, obs, k, action_out);
+        if (rd != 0) {
+            if (rd < 0) return rd;
+            return h->xstep ? EKF_OK : flush(h);
+        }
+    }
+    return measure_host_loop(h, obs, k, u, loc_table, index_table, n_table, action_out);
+}
+
 extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k, const double u[2],
                                      const double* loc_table, const int32_t* index_table, int32_t n_table,
                                      int32_t* action_out) {
-    CKH(h);
-    if (k < 0 || (k > 0 && !obs) || !u) return fail(h, EKF_EINVAL, "null argument");
+    int32_t rc = ekf_measure_batch_async(h, obs, k, u, loc_table, index_table, n_table, action_out);
+    if (rc != EKF_OK) return rc;
+    return ekf_measure_wait(h);
+}
+
+// measure() control flow on the host (appends, mode-B association, the known-correspondence variant, sharded handles).
+static int32_t measure_host_loop(ekf_handle* h, const double* obs, int32_t k, const double u[2], const double* loc_table,
+                                 const int32_t* index_table, int32_t n_table, int32_t* action_out) {
     auto loc_by_index = [&](double want, double pos[2]) -> bool {          // find([..index]==want), first hit
         for (int i = 0; i < n_table; ++i)
             if ((double)index_table[i] == want) { pos[0] = loc_table[i]; pos[1] = loc_table[i + n_table]; return true; }
@@ -1236,10 +1380,15 @@ extern "C" int32_t ekf_measure_batch(ekf_handle* h, const double* obs, int32_t k
 // ---------------------------------------------------------------- state access
 extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     CKH(h);
+    RESOLVE(h);
     if (!x || len < n_of(h)) return fail(h, EKF_EINVAL, "ekf_get_x: buffer too small");
     if (is_front(h)) {                    // every slab executes its queued batch (they wait for each other's columns), then slab 0 answers
         int32_t rcq = h->xstep ? front_exec(h) : front_flush(h);
         if (rcq != EKF_OK) return rcq;
+        for (size_t g = 1; g < h->subs.size(); ++g) {            // a full pending set: see below (slab 0 does its own inside get_x)
+            ekf_handle* sh = h->subs[g];
+            if (sh->lazy && sh->m_pend >= sh->pend_cap) { cudaSetDevice(sh->p.device); rcq = downdate_sharded(sh); if (rcq != EKF_OK) { h->err = sh->err; return rcq; } }
+        }
         int32_t rcf = ekf_get_x(h->subs[0], x, len);
         if (rcf != EKF_OK) h->err = h->subs[0]->err;
         return rcf;
@@ -1255,12 +1404,20 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
         CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
     }
     CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, st));
+    if (h->lazy && h->async_x && h->m_pend >= h->pend_cap) {
+        // The caller is about to block on x while a full set of terms is pending: start its K3 pass now, so that it runs
+        // during the host's turnaround instead of waiting (lazily) for the next batch.  A loop that never reads x keeps the
+        // lazy overlap; a loop that reads x every step (the reference's, SLAM.m:110-116) keeps the device busy this way.
+        int32_t rcl = (h->world > 1) ? downdate_sharded(h) : flush(h);
+        if (rcl != EKF_OK) return rcl;
+    }
     CK(cudaStreamSynchronize(st));
     return after_sync(h);
 }
 
 extern "C" int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len) {
     CKH(h);
+    RESOLVE(h);
     if (h->N == 0) return EKF_OK;
     if (!s || len < h->N) return fail(h, EKF_EINVAL, "ekf_get_s: buffer too small");
     if (is_front(h)) { int32_t rcf = ekf_get_s(h->subs[0], s, len); if (rcf != EKF_OK) h->err = h->subs[0]->err; return rcf; }
@@ -1272,6 +1429,7 @@ extern "C" int32_t ekf_get_s(ekf_handle* h, double* s, int32_t len) {
 
 extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
     CKH(h);
+    RESOLVE(h);
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_get_P: lda < n");
     if (is_front(h)) {                    // assemble the slabs; SYM slabs hold rows <= column: mirror on the host
@@ -1295,6 +1453,7 @@ extern "C" int32_t ekf_get_P(ekf_handle* h, double* P, int32_t lda) {
 extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_t nr, int32_t nc, double* out,
                                    int32_t ldo) {
     CKH(h);
+    RESOLVE(h);
     const int n = n_of(h);
     if (!out || r0 < 0 || c0 < 0 || nr < 1 || nc < 1 || r0 + nr > n || c0 + nc > n || ldo < nr)
         return fail(h, EKF_EINVAL, "ekf_get_P_block: bad block");
@@ -1323,6 +1482,7 @@ extern "C" int32_t ekf_get_P_block(ekf_handle* h, int32_t r0, int32_t c0, int32_
 // Headless stand-in for the ellipse part of plot() (EKF_SLAM.m:180-229): numbers instead of figure calls.
 extern "C" int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo) {
     CKH(h);
+    RESOLVE(h);
     const int nb = h->N + 1;
     if (!out || ldo < nb) return fail(h, EKF_EINVAL, "ekf_get_ellipses: buffer too small");
     if (h->world > 1 || is_front(h)) return fail(h, EKF_EINVAL, "ekf_get_ellipses: not available on a sharded filter (diagonal blocks live on different ranks)");
@@ -1342,6 +1502,7 @@ extern "C" int32_t ekf_get_ellipses(ekf_handle* h, double* out, int32_t ldo) {
 extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P, int32_t lda, const double* s,
                                  int32_t N) {
     CKH(h);
+    RESOLVE(h);
     if (N < 0 || N > h->p.capacity_landmarks) return fail(h, EKF_ECAPACITY, "ekf_set_state: N beyond capacity");
     const int n = 3 + 2 * N;
     if (!x || !P || lda < n || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state: bad argument");
@@ -1364,6 +1525,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     h->q.clear();
     h->N = N;
     if (h->hflags) h->hflags[0] = 0;
+    sigs_reset(h, s, N);
     return EKF_OK;
 }
 
@@ -1372,6 +1534,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
 // the old P); x and s are final as soon as their last kernel has run.
 extern "C" int32_t ekf_set_x(ekf_handle* h, const double* x, int32_t len) {
     CKH(h);
+    RESOLVE(h);
     if (!x || len != n_of(h)) return fail(h, EKF_EINVAL, "ekf_set_x: expected " + std::to_string(n_of(h)) + " elements (3 + 2 N); use ekf_set_state to change the number of landmarks");
     if (is_front(h)) {                    // enqueue every slab's flush first: a flush exchanges columns, and set_x synchronises
         { int32_t rcq = front_flush(h); if (rcq != EKF_OK) return rcq; }
@@ -1390,6 +1553,7 @@ extern "C" int32_t ekf_set_x(ekf_handle* h, const double* x, int32_t len) {
 
 extern "C" int32_t ekf_set_s(ekf_handle* h, const double* s, int32_t len) {
     CKH(h);
+    RESOLVE(h);
     if (len != h->N || (len > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_s: expected " + std::to_string(h->N) + " signatures");
     if (len == 0) return EKF_OK;
     if (is_front(h)) { FAN_OUT(h, sh, ekf_set_s(sh, s, len)); return EKF_OK; }
@@ -1399,11 +1563,13 @@ extern "C" int32_t ekf_set_s(ekf_handle* h, const double* s, int32_t len) {
     CK(cudaMemcpyAsync(h->s, s, sizeof(double) * len, cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     MARK_X(h);
+    sigs_reset(h, s, len);
     return EKF_OK;
 }
 
 extern "C" int32_t ekf_set_P(ekf_handle* h, const double* P, int32_t lda) {
     CKH(h);
+    RESOLVE(h);
     const int n = n_of(h);
     if (!P || lda < n) return fail(h, EKF_EINVAL, "ekf_set_P: lda < n");
     if (is_front(h)) { int32_t rcq = front_flush(h); if (rcq != EKF_OK) return rcq; FAN_OUT(h, sh, ekf_set_P(sh, P, lda)); return EKF_OK; }
@@ -1421,6 +1587,7 @@ extern "C" int32_t ekf_set_P(ekf_handle* h, const double* P, int32_t lda) {
 extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const double* s, int32_t N, const double* A,
                                          int32_t r, const double* d) {
     CKH(h);
+    RESOLVE(h);
     if (N < 0 || N > h->p.capacity_landmarks) return fail(h, EKF_ECAPACITY, "ekf_set_state_lowrank: N beyond capacity");
     const int n = 3 + 2 * N;
     if (!x || !A || !d || r < 1 || (N > 0 && !s)) return fail(h, EKF_EINVAL, "ekf_set_state_lowrank: bad argument");
@@ -1449,12 +1616,14 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     if (rc != EKF_OK) return rc;
     h->N = N;
     if (h->hflags) h->hflags[0] = 0;
+    sigs_reset(h, s, N);
     return EKF_OK;
 }
 
 // ---------------------------------------------------------------- measurement hooks
 extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
     CKH(h);
+    RESOLVE(h);
     if (is_front(h)) { FAN_OUT(h, sh, ekf_profile_enable(sh, on)); return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     CK(cudaStreamSynchronize(h->stream));
@@ -1477,6 +1646,7 @@ extern "C" int32_t ekf_profile_enable(ekf_handle* h, int32_t on) {
 extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, int64_t* downdate_launches,
                                     int64_t* kernel_launches_total) {
     CKH(h);
+    RESOLVE(h);
     if (is_front(h)) {                    // the slowest slab's downdate time, launches summed over the slabs
         double worst = -1.0; int64_t nd = 0, nl = 0;
         for (size_t g = 0; g < h->subs.size(); ++g) {
@@ -1507,6 +1677,7 @@ extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, in
 
 extern "C" int32_t ekf_profile_exchange(ekf_handle* h, double* exchange_ms_total, int64_t* exchanges, int32_t* p2p) {
     CKH(h);
+    RESOLVE(h);
     if (is_front(h)) {
         double worst = 0.0; int64_t cnt = 0; int32_t pp = 1;
         for (ekf_handle* sh : h->subs) {
@@ -1539,6 +1710,7 @@ extern "C" int32_t ekf_profile_exchange(ekf_handle* h, double* exchange_ms_total
 
 extern "C" int32_t ekf_downdate_bytes(ekf_handle* h, double* bytes) {
     CKH(h);
+    RESOLVE(h);
     if (!bytes) return fail(h, EKF_EINVAL, "bytes is null");
     if (is_front(h)) return ekf_downdate_bytes(h->subs[(size_t)h->rank < h->subs.size() ? h->rank : 0], bytes);   // slab of the last ekf_profile_read
     const double n = (double)n_of(h);

@@ -169,9 +169,32 @@ struct GSel {
     __device__ Row operator[](int a) const { return Row{g, sl, a}; }
 };
 
-__global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
-                            BatchObs ob, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc,
-                            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0) {
+// The batch description reaches the kernels either by value (slots decided on the host) or from device memory (`src.ob`,
+// written by k_measure_decide: slots decided on the device, the host never sees them before it enqueues the update).
+// Either way it is staged in shared memory once per CTA.  `src.skip` (device word, may be null): the decision kernel
+// found a row the device path cannot serve; the batch then contributes ZERO terms (k_batch_gain fills its slots with
+// zeros and leaves x alone), so every flush the host has already enqueued behind it stays valid.
+__device__ __forceinline__ void stage_batch_obs(BatchObs& sh, const BatchObs& arg, const BatchObs* dev) {
+    const int q = threadIdx.x;
+    if (q < EKF_BATCH_MAX) {
+        if (dev) { sh.z0[q] = dev->z0[q]; sh.z1[q] = dev->z1[q]; sh.R0[q] = dev->R0[q]; sh.R1[q] = dev->R1[q]; sh.a[q] = dev->a[q]; }
+        else { sh.z0[q] = arg.z0[q]; sh.z1[q] = arg.z1[q]; sh.R0[q] = arg.R0[q]; sh.R1[q] = arg.R1[q]; sh.a[q] = arg.a[q]; }
+    }
+    if (q == 0) sh.k = dev ? dev->k : arg.k;
+    __syncthreads();
+}
+
+// __launch_bounds__(384, 4): <= 42 registers, i.e. 16 K registers per CTA.  Under the lazy flush this kernel has to start
+// beside a K3 grid that fills every SM (3 CTAs x 288 threads x 72 registers): the slot one retiring flush CTA frees is
+// 20.7 K registers, and a CTA that does not fit it waits for the flush's tail instead of overlapping with it.
+__global__ void __launch_bounds__(384, 4)
+k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
+                            const BatchObs ob_arg, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc,
+                            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0,
+                            ObSrc src) {
+    __shared__ BatchObs ob;
+    stage_batch_obs(ob, ob_arg, src.ob);
+    if (src.skip && *src.skip) return;
     __shared__ double G[EKF_BATCH_SLOTS][EKF_BATCH_SLOTS + 1];
     __shared__ double xs[EKF_BATCH_SLOTS];
     __shared__ double2 Ks[EKF_BATCH_SLOTS], Bs[EKF_BATCH_SLOTS];
@@ -254,10 +277,18 @@ __global__ void k_batch_lin(const double* __restrict__ P, int64_t ld, const doub
 }
 
 __global__ void __launch_bounds__(128)
-k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, BatchObs ob,
+k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, const BatchObs ob_arg,
              const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
              const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi, int m0,
-             double2* __restrict__ Kout, double2* __restrict__ Bout, int o0) {
+             double2* __restrict__ Kout, double2* __restrict__ Bout, int o0, ObSrc src) {
+    __shared__ BatchObs ob;
+    stage_batch_obs(ob, ob_arg, src.ob);
+    if (src.skip && *src.skip) {           // the batch contributes nothing: zero terms in its slots, x untouched
+        const int i0 = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i0 < n)
+            for (int q = 0; q < ob.k; ++q) { Kout[(o0 + q) * lds + i0] = make_double2(0.0, 0.0); Bout[(o0 + q) * lds + i0] = make_double2(0.0, 0.0); }
+        return;
+    }
     // Kall / Ball: the m0 pending terms (read only).  The k new terms go to slots o0 .. o0+k-1 of Kout / Bout: the same
     // slabs with o0 = m0 normally; the OTHER pair of slabs with o0 = 0 when the pending terms are being flushed by a
     // concurrent K3 launch (lazy flush, ekf_capi.cu).
@@ -336,17 +367,21 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
 // Raw copies of the slot columns of a batch, Pc[slot][i] = stored P(i, col(slot)) (SYM: the live element (min, max)):
 // what the sharded exchange delivers, gathered locally.  Taken BEFORE a flush is launched, so that the batch can be
 // linearised from them (plus the pending terms) while that flush rewrites P.
-__global__ void k_gather_cols(const double* __restrict__ P, int64_t ld, int n, int sym, BatchObs ob,
-                              double* __restrict__ Pc, int64_t ldc) {
+__global__ void k_gather_cols(const double* __restrict__ P, int64_t ld, int n, int sym, const BatchObs ob_arg,
+                              double* __restrict__ Pc, int64_t ldc, ObSrc src) {
+    __shared__ BatchObs ob;
+    stage_batch_obs(ob, ob_arg, src.ob);
     const int slot = blockIdx.y;
+    if (slot >= 3 + 2 * ob.k) return;
     const int c = slot < 3 ? slot : ob.a[(slot - 3) >> 1] + ((slot - 3) & 1);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) Pc[(int64_t)slot * ldc + i] = ldP(P, ld, i, c, sym);
 }
 
-void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc) {
-    dim3 grid((n + 255) / 256, 3 + 2 * ob.k);
-    k_gather_cols<<<grid, 256, 0, st>>>(P, ld, n, sym, ob, Pc, ldc);
+void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc,
+                        ObSrc src) {
+    dim3 grid((n + 255) / 256, 3 + 2 * ob.k);      // ob.k on the host is the chunk size in both modes
+    k_gather_cols<<<grid, 256, 0, st>>>(P, ld, n, sym, ob, Pc, ldc, src);
 }
 
 // ------------------------------------------------------------------ K5 append
@@ -607,6 +642,89 @@ __global__ void k_associate_sig_batch(const double* __restrict__ s, int N, Assoc
 }
 
 
+// ------------------------------------------------------------------ measure() decisions on the device
+// EKF_SLAM_UC.measure, mode A (EKF_SLAM_UC.m:107-124 with Correspondence.m:28-88 as shipped): block b associates row b
+// of observed_LL (the k_associate_sig_batch scan), the last block to finish turns the k results into the batch
+// descriptions the update kernels read from device memory -- chunk c = rows 8c .. 8c+7: z, R = z .* Rc (:108), slot
+// a = 3 + 2 (idx - 1) -- and writes the actions (+idx) into mapped host memory.  The host enqueues the update kernels
+// behind this one WITHOUT waiting for it.  It only takes this path when every row's signature is already in the map
+// (it keeps the set of signatures it appended), so no row can need an append; should one disagree (newLL), `skip` is
+// raised, the update kernels contribute nothing, and status[0] = 1 tells the host at its next call.
+__global__ void k_measure_decide(const double* __restrict__ s, int N, const double* __restrict__ obs, int k, double Rc0,
+                                 double Rc1, double s_cost, double s_thresh, BatchObs* __restrict__ chunks,
+                                 int* __restrict__ skip, int* __restrict__ status, int* __restrict__ scratch,
+                                 unsigned int* __restrict__ ticket) {
+    __shared__ double wc[32];
+    __shared__ int wi[32];
+    __shared__ bool is_last;
+    const int b = blockIdx.x;
+    const double z2 = obs[b + 2 * k];
+    const double inv = 1.0 / s_cost;
+    double best = CUDART_INF;
+    int bidx = INT_MAX;
+    for (int kk = threadIdx.x; kk < N; kk += blockDim.x) {         // ascending kk per thread: strict '<' keeps the first
+        double d = __dsub_rn(z2, s[kk]);
+        double ll = __dmul_rn(__dmul_rn(d, inv), d);               // Correspondence.m:71,75
+        if (ll <= s_thresh && ll < best) { best = ll; bidx = kk + 1; }   // :78,:81
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double oc = __shfl_down_sync(0xffffffffu, best, o);
+        int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+        if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { wc[w] = best; wi[w] = bidx; }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        best = (lane < nw) ? wc[lane] : CUDART_INF;
+        bidx = (lane < nw) ? wi[lane] : INT_MAX;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            double oc = __shfl_down_sync(0xffffffffu, best, o);
+            int oi = __shfl_down_sync(0xffffffffu, bidx, o);
+            if (cand_less(oc, oi, best, bidx)) { best = oc; bidx = oi; }
+        }
+        if (lane == 0) {
+            scratch[b] = bidx;                                     // INT_MAX: newLL (EKF_SLAM_UC.m:121 would append)
+            __threadfence();
+            is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+        }
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    const int t = threadIdx.x;
+    int bad = 0;
+    if (t < k) {
+        const int idx = ((volatile int*)scratch)[t];
+        const int c = t / EKF_BATCH_MAX, q = t - c * EKF_BATCH_MAX;
+        const double z0 = obs[t], z1 = obs[t + k];
+        bad = (idx == INT_MAX || idx < 1 || idx > N) ? 1 : 0;
+        chunks[c].z0[q] = z0;
+        chunks[c].z1[q] = z1;
+        chunks[c].R0[q] = __dmul_rn(z0, Rc0);                     // EKF_SLAM_UC.m:110, R = diag(z(1) Rc(1), z(2) Rc(2))
+        chunks[c].R1[q] = __dmul_rn(z1, Rc1);
+        chunks[c].a[q] = bad ? 3 : 3 + 2 * (idx - 1);
+        status[1 + t] = bad ? 0 : idx;                             // action: +idx = update of slot idx
+        if (q == 0) chunks[c].k = min(EKF_BATCH_MAX, k - c * EKF_BATCH_MAX);
+    }
+    const int any_bad = __syncthreads_or(bad);
+    if (t == 0) {
+        *skip = any_bad;
+        status[0] = any_bad;
+        *ticket = 0;
+        __threadfence_system();
+    }
+}
+
+void launch_measure_decide(cudaStream_t st, const double* s, int N, const double* obs, int k, double Rc0, double Rc1,
+                           double s_cost, double s_thresh, BatchObs* ob_chunks, int* skip, int* status_host, int* scratch,
+                           unsigned int* ticket) {
+    k_measure_decide<<<k, 256, 0, st>>>(s, N, obs, k, Rc0, Rc1, s_cost, s_thresh, ob_chunks, skip, status_host, scratch, ticket);
+}
+
 // ------------------------------------------------------------------ state initialisation helpers
 __global__ void k_init_lowrank(double* __restrict__ P, int64_t ld, int n, int c_lo, const double* __restrict__ A, int r,
                                const double* __restrict__ d) {
@@ -701,13 +819,13 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc, int64_t ldc,
-                           int c_lo, int c_hi, int m0, double2* Kout, double2* Bout, int o0) {
+                           int c_lo, int c_hi, int m0, double2* Kout, double2* Bout, int o0, ObSrc src) {
     if (!Pc) { c_lo = 0; c_hi = n; }
     if (!Kout) { Kout = Kall; Bout = Ball; o0 = m0; }
-    k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc, Kall, Ball, lds, m0);   // >= EKF_BATCH_SLOTS^2 = 361 threads
+    k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc, Kall, Ball, lds, m0, src);   // >= EKF_BATCH_SLOTS^2 = 361 threads
     static int gb = 0;                     // rows per CTA of the gain kernel (EKF_GAIN_BLOCK = 32 | 64 | 128, default 128)
     if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
-    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0, Kout, Bout, o0);
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0, Kout, Bout, o0, src);
 }
 
 

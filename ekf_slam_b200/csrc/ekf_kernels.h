@@ -15,6 +15,7 @@ void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, do
 #define EKF_MAX_PEND 16                             // single-GPU handles: rank-2 terms that may stay pending across predict (defer_m = 9..16)
 #define EKF_MAX_SLOTS (3 + 2 * EKF_MAX_DEFER)      // columns exchanged per sharded batch: robot + 2 per observation
 struct SlotSet { int n; int col[EKF_MAX_SLOTS]; }; // global column index of each slot (passed by value)
+struct ObSrc { const BatchObs* ob; const int* skip; };   // device-side batch description + skip word (both null: by-value BatchObs)
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,
                            double R0, double R1, int sym, Lin* lin, double2* Kall, double2* Ball, int64_t lds, int m);
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
@@ -28,8 +29,14 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc = nullptr,
                            int64_t ldc = 0, int c_lo = 0, int c_hi = 0, int m0 = 0,    // m0: terms already pending in slabs 0..m0-1; this batch fills m0..m0+k-1
-                           double2* Kout = nullptr, double2* Bout = nullptr, int o0 = 0);   // ... or slots o0.. of another pair of slabs (lazy flush)
-void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc);
+                           double2* Kout = nullptr, double2* Bout = nullptr, int o0 = 0,    // ... or slots o0.. of another pair of slabs (lazy flush)
+                           ObSrc src = ObSrc{nullptr, nullptr});
+void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc,
+                        ObSrc src = ObSrc{nullptr, nullptr});
+// measure() decisions on the device (EKF_SLAM_UC.m:107-124, mode A): per row of observed_LL the slot it updates; see ekf_kernels.cu
+void launch_measure_decide(cudaStream_t st, const double* s, int N, const double* obs, int k, double Rc0, double Rc1,
+                           double s_cost, double s_thresh, BatchObs* ob_chunks, int* skip, int* status_host, int* scratch,
+                           unsigned int* ticket);
 // predict with m pending terms: P0 takes F . F' + Q as usual, the slabs take K_q <- F K_q, B_q <- B_q F' (rows / columns 0, 1 only)
 void launch_predict_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int m, const double* xpre, double u1);
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,

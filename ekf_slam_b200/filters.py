@@ -60,12 +60,14 @@ class _FilterBase:
         self._s_thresh = p.s_thresh
         self.landmark_list = None          # EKF_SLAM.m:18
         self.observed = None               # EKF_SLAM.m:19
-        self.chosen = []                   # per observation: ('update'|'append', idx) -- parity log
+        self._chosen = []                  # per observation: ('update'|'append', idx) -- parity log
+        self._pending_act = None           # actions of the last measure(), filled by the library at its next call
         self._last_predict = None
 
     # ---- lifetime ------------------------------------------------------
     def close(self):
         if getattr(self, '_h', None):
+            self._pending_act = None
             self._lib.ekf_destroy(self._h)
             self._h = None
 
@@ -77,6 +79,19 @@ class _FilterBase:
 
     def _ck(self, rc):
         L.check(self._h, rc)
+
+    def _collect_actions(self):
+        """measure() does not wait for the device's decisions (ekf_measure_batch_async); fetch them when somebody looks."""
+        act, self._pending_act = self._pending_act, None
+        if act is not None:
+            self._ck(self._lib.ekf_measure_wait(self._h))
+            for a in act:
+                self._chosen.append(('update', int(a)) if a > 0 else ('append', int(-a)))
+
+    @property
+    def chosen(self):
+        self._collect_actions()
+        return self._chosen
 
     # ---- public properties of the reference classes (EKF_SLAM.m:5-22) ----
     @property
@@ -246,11 +261,11 @@ class _FilterBase:
         if n_tab == 0:
             idx = np.zeros(1, dtype=np.int32)
             loc = np.zeros((1, 2), order='F')
-        rc = self._lib.ekf_measure_batch(self._h, L.dptr(obs), k, L.dptr(_f64(u, 2)), L.dptr(loc),
-                                         L.iptr(idx), n_tab, L.iptr(act))
+        self._collect_actions()            # the previous call's (the library writes them at its next call: read first)
+        rc = self._lib.ekf_measure_batch_async(self._h, L.dptr(obs), k, L.dptr(_f64(u, 2)), L.dptr(loc),
+                                               L.iptr(idx), n_tab, L.iptr(act))
+        self._pending_act = act            # keeps the buffer alive until the actions are in
         self._ck(rc)
-        for a in act:
-            self.chosen.append(('update', int(a)) if a > 0 else ('append', int(-a)))
 
     def plot(self, landmark_list=None):
         """EKF_SLAM.m:154-234 draws MATLAB figures; unavailable on this box (no graphics stack).  The numbers it

@@ -124,6 +124,22 @@ int32_t ekf_measure_batch(ekf_handle* h, const double* observed_LL, int32_t k,
                           const int32_t* index_table, int32_t n_table,
                           int32_t* action_out);
 
+/* The same call without the wait: EKF_SLAM_UC with the shipped (signature) association decides append / associate /
+ * update per row ON THE DEVICE (k_measure_decide), the update kernels read the chosen slots from device memory, and the
+ * call returns as soon as everything is enqueued -- no device-to-host copy inside it.  action_out (may be NULL) is filled
+ * at the next call on the handle or by ekf_measure_wait, and must stay valid until then.  The library takes the device
+ * path when every row's signature is already in the map (it mirrors the signatures it was given, so it knows that no row
+ * can need the landmark table, which only exists during the call); otherwise -- an unseen signature, the first landmark,
+ * the known-correspondence class (which needs no association and was never blocking), mode B, sharded handles -- the
+ * host loop runs as in ekf_measure_batch.  ekf_measure_wait blocks for the decision kernel only, not for the updates or
+ * the covariance flush behind it.  ekf_measure_batch == ekf_measure_batch_async + ekf_measure_wait.
+ * EKF_ASYNC_MEASURE=0 forces the host loop. */
+int32_t ekf_measure_batch_async(ekf_handle* h, const double* observed_LL, int32_t k,
+                                const double u[2], const double* loc_table,
+                                const int32_t* index_table, int32_t n_table,
+                                int32_t* action_out);
+int32_t ekf_measure_wait(ekf_handle* h);
+
 /* State access (public properties x, P, s of the reference classes, EKF_SLAM.m:6-9). */
 int32_t ekf_n_landmarks(ekf_handle* h, int32_t* N);
 /* ekf_get_x returns x as of every call made before it.  It waits for the last kernel that writes x, not for the

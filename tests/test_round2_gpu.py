@@ -376,3 +376,47 @@ def test_lazy_flush_matches_flush_then_linearise(defer_m, monkeypatch):
         f.close()
     assert max(_rel(a, b) for a, b in zip(runs[0][0], runs[1][0])) <= 1e-12
     assert _rel(runs[0][1], runs[1][1]) <= 1e-12
+
+
+@pytest.mark.parametrize('storage,defer_m', [('sym', 16), ('sym', 8), ('full', 8), ('full', 3)])
+def test_measure_decided_on_device_is_bit_identical_to_the_host_loop(storage, defer_m, monkeypatch):
+    """ekf_measure_batch_async (EKF_SLAM_UC, signature association): rows whose signatures are all in the map are
+    associated by k_measure_decide and the update kernels read the slots from device memory -- no device-to-host copy
+    inside the call; rows with an unseen signature (appends) take the host loop.  Same kernels, same slots: actions, x
+    at every step and the final P are bit-identical to EKF_ASYNC_MEASURE=0, over an exploration phase (appends mixed in)
+    and a populated-map phase with batches of 1..11 rows (several fused chunks)."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world, synthetic_spd_state, observe_from_truth, LandmarkStub
+    w = make_world(N=24, T=160, k=6, mode='nearest', seed=11)
+    N2 = 300
+    x2, A2, d2, s2, lms2 = synthetic_spd_state(N2, seed=19)
+    table2 = [SimpleNamespace(index=i + 1, loc=lms2[i]) for i in range(N2)]
+    runs = {}
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_ASYNC_MEASURE', flag)
+        g = E.EKF_SLAM_UC(capacity_landmarks=24, storage=storage, defer_m=defer_m)
+        xs = []
+        for t in range(w.T):
+            g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t), pass_x=(t % 2 == 0))
+            if t % 3 == 0:
+                xs.append(g.x)
+        out = [xs, list(g.chosen), g.P, g.s]
+        g.close()
+        g = E.EKF_SLAM_UC(capacity_landmarks=N2, storage=storage, defer_m=defer_m)
+        g.set_state_lowrank(x2, s2, A2, d2)
+        rng = np.random.default_rng(3)
+        for step in range(12):
+            rows = observe_from_truth(lms2, x2[:3], rng.choice(N2, 30, replace=False), rng)[:(8, 11, 1, 5, 8, 2, 9, 8, 3, 8, 8, 7)[step]]
+            g.predict([0.3, 1.0]); g.measure(None, [0.3, 1.0], LandmarkStub(rows, table2), pass_x=False)
+            if step % 4 == 1:
+                xs.append(g.x)
+            if step == 6:
+                g.s = g.s                                # property write in between (rebuilds the signature mirror)
+        out += [list(g.chosen), g.x, g.P]
+        g.close()
+        runs[flag] = out
+    a, b = runs['0'], runs['1']
+    assert a[1] == b[1] and a[4] == b[4], 'actions differ'
+    assert len(a[0]) == len(b[0]) and all(np.array_equal(p, q) for p, q in zip(a[0], b[0]))
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[5], b[5]) and np.array_equal(a[6], b[6])
+    assert all(act == 'update' for act, _ in b[4]) and len(b[4]) == 78
