@@ -479,7 +479,11 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         }
         {
             const char* lz = getenv("EKF_LAZY_FLUSH");
-            h->lazy = h->xstep && p->storage == EKF_STORAGE_SYM && !(lz && atoi(lz) == 0);
+            // default: on for slabs, off on one GPU.  Measured (profiles/r02): one GPU 25 784 -> 25 864 updates/s while K3
+            // slows from 0.520 to 0.530 ms beside the side-stream kernels (the batch after a flush is the cheap one, m0 = 0,
+            // so only ~28 us per two steps can hide and the gather + the slower flush eat them); at 1k landmarks the extra
+            // launches cost 15 %.  EKF_LAZY_FLUSH=1 / 0 forces it.
+            h->lazy = h->xstep && p->storage == EKF_STORAGE_SYM && (lz ? atoi(lz) != 0 : world > 1);
         }
         if (h->lazy) {
             int pr_lo = 0, pr_hi = 0;
@@ -677,10 +681,11 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         CK(cudaEventRecord(h->ev_px, h->sx));
         CK(cudaStreamWaitEvent(h->stream, h->ev_px, 0));
         if (h->world > 1)
-            launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
+            launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h),
+                                   h->Kd, h->Bd, h->ld, h->xstep ? h->m_pend : 0);
         else
-            launch_predict_P(h->stream, h->P, h->ld, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h));
-        if (h->xstep && h->m_pend > 0) { launch_predict_slabs(h->stream, h->Kd, h->Bd, h->ld, h->m_pend, h->xprev, u[0]); h->launches += 1; }
+            launch_predict_P(h->stream, h->P, h->ld, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h),
+                             h->Kd, h->Bd, h->ld, h->xstep ? h->m_pend : 0);      // the pending slabs ride in the same launch
         CK(cudaGetLastError());
         CK(cudaEventRecord(h->ev_pp, h->stream));   // NOT ev_mx: a reader of x must not wait for this kernel (it sits behind the flush)
     } else if (h->world > 1 && h->xstep && h->m_pend > 0) {   // single stream, slab: covariance half, slab transform, state half
@@ -1404,7 +1409,7 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
         CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
     }
     CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, st));
-    if (h->lazy && h->async_x && h->m_pend >= h->pend_cap) {
+    if (h->lazy && h->m_pend >= h->pend_cap) {
         // The caller is about to block on x while a full set of terms is pending: start its K3 pass now, so that it runs
         // during the host's turnaround instead of waiting (lazily) for the next batch.  A loop that never reads x keeps the
         // lazy overlap; a loop that reads x every step (the reference's, SLAM.m:110-116) keeps the device busy this way.

@@ -18,11 +18,22 @@ namespace ekf {
 // owns the 3x3 corner (both passes, then + Q = (W C) W', EKF_SLAM.m:42-47).  x is NOT written here so that
 // every block sees the pre-motion heading (EKF_SLAM.m:42,63-64 use theta before f()).
 __global__ void k_predict_P(double* __restrict__ P, int64_t ld, const double* __restrict__ x, int n,
-                            double u1, double u2, double C, int sym) {
+                            double u1, double u2, double C, int sym,
+                            double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds, int m) {
     const double th = x[2];
     const double st = sind(th), ct = cosd(th);
     const double a = -1.0 * u1 * st;      // F(1,3), EKF_SLAM.m:63
     const double b = u1 * ct;             // F(2,3), EKF_SLAM.m:64
+    if (m > 0 && blockIdx.x == gridDim.x - 1) {      // extra block: the pending slabs take K_q <- F K_q, B_q <- B_q F' (k_predict_slabs)
+        const int t = threadIdx.x;
+        if (t < 2 * m) {
+            double2* S = (t & 1 ? Ball : Kall) + (int64_t)(t >> 1) * lds;
+            const double2 v0 = S[0], v1 = S[1], v2 = S[2];
+            S[0] = make_double2(v0.x + a * v2.x, v0.y + a * v2.y);
+            S[1] = make_double2(v1.x + b * v2.x, v1.y + b * v2.y);
+        }
+        return;
+    }
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t == 0) {
         double M[3][3];
@@ -796,7 +807,7 @@ void launch_ellipses(cudaStream_t st, const double* P, int64_t ld, const double*
 
 
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym) {
-    k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, u1, u2, C, sym);
+    k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, u1, u2, C, sym, nullptr, nullptr, 0, 0);
     k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr);
 }
 
@@ -807,8 +818,9 @@ void launch_predict_x(cudaStream_t st, double* x, double u1, double u2) { k_pred
 void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev) {
     k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, xprev);
 }
-void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym) {
-    k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, xprev, n, u1, u2, C, sym);
+void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym,
+                      double2* Kall, double2* Ball, int64_t lds, int m) {
+    k_predict_P<<<cdiv(n, 256) + (m > 0 ? 1 : 0), 256, 0, st>>>(P, ld, xprev, n, u1, u2, C, sym, Kall, Ball, lds, m);
 }
 
 void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int a, double z0, double z1,

@@ -54,7 +54,8 @@ void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo
                          const double* d);
 void launch_predict_x(cudaStream_t st, double* x, double u1, double u2);
 void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev);      // decoupled predict, state half (side stream)
-void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym);   // covariance half
+void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym,
+                      double2* Kall = nullptr, double2* Ball = nullptr, int64_t lds = 0, int m = 0);   // covariance half (+ the m pending slabs, one extra block)
 // ---- column-slab sharded filter (ekf_shard.cu) ----
 #define EKF_MAX_PEERS 8
 // layout of a rank's flag allocation (ints): [0, 8) column-exchange epochs per source rank, [EKF_XF_ASSOC, +8) association
@@ -75,7 +76,8 @@ void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int 
 void launch_predict_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, double u1,
                           double u2, double C, int sym);
 void launch_predict_shard_P(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, const double* xprev, int n,
-                            double u1, double u2, double C, int sym);   // covariance half of the decoupled predict
+                            double u1, double u2, double C, int sym, double2* Kall = nullptr, double2* Ball = nullptr,
+                            int64_t lds = 0, int m = 0);   // covariance half of the decoupled predict (+ the m pending slabs)
 void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, double* s, int N,
                          double u1, double u2, double R0, double R1, double px, double py, double sig, const double* Pc,
                          int64_t ldc);

@@ -83,9 +83,9 @@ __global__ void k_scatter_cols(const double* __restrict__ Ploc, int64_t ld, int 
         if (have)
             for (int g = 0; g < ps.world; ++g) ps.pc[g][buf_off + (int64_t)slot * ld + i] = v;
     }
-    __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence_system();                                // cumulative: covers the block's stores ordered before it by the barrier
         const unsigned int total = gridDim.x * gridDim.y;
         if (atomicAdd(ticket, 1u) == total - 1) {              // last block: every block's stores are fenced
             *ticket = 0;
@@ -208,10 +208,21 @@ __global__ void k_gain_shard(const double* __restrict__ Ploc, int64_t ld, int c_
 
 // predict on a slab: the row pass is local to every owned column, the column pass and the corner live on rank 0.
 __global__ void k_predict_shard(double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, const double* __restrict__ x,
-                                int n, double u1, double u2, double C, int sym) {
+                                int n, double u1, double u2, double C, int sym,
+                                double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds, int m) {
     const double th = x[2];
     const double st = sind(th), ct = cosd(th);
     const double a = -1.0 * u1 * st, b = u1 * ct;
+    if (m > 0 && blockIdx.x == gridDim.x - 1) {      // extra block: the pending slabs take K_q <- F K_q, B_q <- B_q F' (k_predict_slabs)
+        const int t = threadIdx.x;
+        if (t < 2 * m) {
+            double2* S = (t & 1 ? Ball : Kall) + (int64_t)(t >> 1) * lds;
+            const double2 v0 = S[0], v1 = S[1], v2 = S[2];
+            S[0] = make_double2(v0.x + a * v2.x, v0.y + a * v2.y);
+            S[1] = make_double2(v1.x + b * v2.x, v1.y + b * v2.y);
+        }
+        return;
+    }
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t == 0 && c_lo == 0) {
         double M[3][3];
@@ -308,14 +319,14 @@ void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int 
 
 void launch_predict_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, double u1,
                           double u2, double C, int sym) {
-    k_predict_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, x, n, u1, u2, C, sym);
+    k_predict_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, x, n, u1, u2, C, sym, nullptr, nullptr, 0, 0);
     launch_predict_x(st, x, u1, u2);
 }
 
 // covariance half alone (decoupled predict): the heading comes from the pre-motion pose the state half saved
 void launch_predict_shard_P(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, const double* xprev, int n,
-                            double u1, double u2, double C, int sym) {
-    k_predict_shard<<<cdiv(n, 256), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, xprev, n, u1, u2, C, sym);
+                            double u1, double u2, double C, int sym, double2* Kall, double2* Ball, int64_t lds, int m) {
+    k_predict_shard<<<cdiv(n, 256) + (m > 0 ? 1 : 0), 256, 0, st>>>(Ploc, ld, c_lo, c_hi, xprev, n, u1, u2, C, sym, Kall, Ball, lds, m);
 }
 
 void launch_append_shard(cudaStream_t st, double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, double* s, int N,

@@ -118,8 +118,10 @@ def main():
     # corrected by the pending terms on arrival): bitwise equal to the single-GPU defer-16 path, x read mid-run included
     N = 1000
     x, A, d, s, lms = synthetic_spd_state(N, seed=3)
+    os.environ['EKF_LAZY_FLUSH'] = '1'       # same flush policy on both sides (default: lazy on slabs, eager on one GPU)
     g = E.shard.create_sharded(E.EKF_SLAM, dist, local, storage='sym', capacity_landmarks=N, defer_m=16)
     ref = E.EKF_SLAM(capacity_landmarks=N, storage='sym', device=local, defer_m=16)
+    del os.environ['EKF_LAZY_FLUSH']
     assert g.pend_cap() == 16 and ref.pend_cap() == 16
     for f in (g, ref):
         f.set_state_lowrank(x, s, A, d)

@@ -17,7 +17,7 @@ def _rel(a, b):
 
 @pytest.mark.parametrize('storage,defer_m', [('sym', 8), ('full', 8), ('sym', 16), ('sym', 0)])
 @pytest.mark.parametrize('G', [2, 4, 8])
-def test_multi_device_handle_is_bit_identical_to_single_gpu(G, storage, defer_m):
+def test_multi_device_handle_is_bit_identical_to_single_gpu(G, storage, defer_m, monkeypatch):
     """Populated 1k map, predict + ragged update batches + single updates, x / P / P_block read mid-run: the multi-device
     handle returns the very bits of the single-GPU path (same kernels, same operands, same order)."""
     if _ngpu() < G:
@@ -26,6 +26,7 @@ def test_multi_device_handle_is_bit_identical_to_single_gpu(G, storage, defer_m)
     from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
     N = 1000
     x, A, d, s, lms = synthetic_spd_state(N, seed=3)
+    monkeypatch.setenv('EKF_LAZY_FLUSH', '1')    # same flush policy on both sides (default: lazy on slabs, eager on one GPU)
     m = E.EKF_SLAM(capacity_landmarks=N, storage=storage, defer_m=defer_m, devices=list(range(G)))
     ref = E.EKF_SLAM(capacity_landmarks=N, storage=storage, defer_m=defer_m, device=0)
     assert m.shard_info()[1] == G
