@@ -47,6 +47,8 @@ SIGNATURES = {
     'ekf_update': [_H, _DP, _DP, C.c_int32],
     'ekf_append': [_H, _DP, _DP, _DP, C.c_double],
     'ekf_associate': [_H, _DP, _DP, _IP, _IP],
+    'ekf_associate_static': [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, _DP, _DP, C.c_double, C.c_double,
+                             C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.c_char_p, C.c_int32],
     'ekf_measure_batch': [_H, _DP, C.c_int32, _DP, _DP, _IP, C.c_int32, _IP],
     'ekf_measure_batch_async': [_H, _DP, C.c_int32, _DP, _DP, _IP, C.c_int32, _IP],
     'ekf_measure_wait': [_H],

@@ -9,6 +9,10 @@
 #include <math_constants.h>
 #include <limits.h>
 #include <cstdlib>
+#include <cstdio>
+#include <mutex>
+#include <string>
+#include "../../include/ekfslam_b200.h"
 
 namespace ekf {
 
@@ -894,3 +898,88 @@ void launch_mirror_upper(cudaStream_t st, double* P, int64_t ld, int n) {
 }
 
 }  // namespace ekf
+
+// ------------------------------------------------------------------ K4 without allocation (ekf_associate_static)
+// No counterpart in the reference: added for callers that may not call
+// cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  K4 needs scratch memory -- one 16-byte
+// (cost, index) candidate per block of 256 landmarks plus the ticket word of the last-block fold; the handle-based
+// ekf_associate keeps that scratch in the handle's own allocations, this entry point keeps it in a file-scope device
+// array of fixed size, so the call allocates nothing (no cudaMalloc / cudaFree, no library that allocates): the caller
+// passes device pointers of the state and of the 16-byte result and a stream, the kernel is the same k_associate.
+// The array exists once per GPU that loads the library (65 792 bytes, until exit) and is shared by every call: calls
+// that overlap on one GPU (two streams, two threads) race on it -- serialise them.  The ticket word is cleared before
+// every launch (a call that was cut short must not poison the next); the candidates need no clearing, every block of
+// the grid writes its own before the fold reads them.
+#define EKF_STATIC_ASSOC_MAX_BLOCKS 4096                      // x 256 landmarks = EKF_ASSOC_STATIC_MAX_LANDMARKS (header)
+#define EKF_STATIC_ASSOC_TICKET_OFF (EKF_STATIC_ASSOC_MAX_BLOCKS * 16)
+static __device__ __align__(256) unsigned char g_assoc_static_scratch[EKF_STATIC_ASSOC_TICKET_OFF + 256];
+
+namespace {
+// In host code `g_assoc_static_scratch` is only a stand-in for the symbol, not a device address: the address every
+// launch passes to the kernel comes from cudaGetSymbolAddress, resolved once per device with that device current.
+constexpr int kMaxDev = 64;
+void* g_static_ptr[kMaxDev];
+bool  g_static_ok[kMaxDev];
+std::mutex g_static_mu;
+
+void put_err(char* errbuf, int32_t errlen, const std::string& m) {
+    if (errbuf && errlen > 0) { snprintf(errbuf, (size_t)errlen, "%s", m.c_str()); }
+}
+}  // namespace
+
+extern "C" int32_t ekf_associate_static(const double* d_x, const double* d_P, int64_t ld, const double* d_s, int32_t N,
+                                        const double z[3], const double Rdiag[2], double s_cost, double s_thresh,
+                                        int32_t assoc_mode, int32_t storage, void* d_result, uint64_t stream,
+                                        char* errbuf, int32_t errlen) {
+    static_assert(sizeof(ekf::Cand) == 16 && sizeof(ekf::AssocResult) == 16, "scratch / result layout");
+    if (!d_x || !d_s || !z || !Rdiag || !d_result) { put_err(errbuf, errlen, "ekf_associate_static: null argument"); return EKF_EINVAL; }
+    if (assoc_mode != EKF_ASSOC_SIGNATURE && assoc_mode != EKF_ASSOC_POSITION) { put_err(errbuf, errlen, "ekf_associate_static: assoc_mode must be EKF_ASSOC_SIGNATURE or EKF_ASSOC_POSITION"); return EKF_EINVAL; }
+    if (storage != EKF_STORAGE_FULL && storage != EKF_STORAGE_SYM) { put_err(errbuf, errlen, "ekf_associate_static: storage must be EKF_STORAGE_FULL or EKF_STORAGE_SYM"); return EKF_EINVAL; }
+    if (N < 1) { put_err(errbuf, errlen, "ekf_associate_static: N must be >= 1 (an empty map has nothing to scan: newLL = 1, index = 1)"); return EKF_EINVAL; }
+    if (N > EKF_ASSOC_STATIC_MAX_LANDMARKS) {
+        put_err(errbuf, errlen, "ekf_associate_static: N = " + std::to_string(N) + " landmarks exceeds the static scratch (EKF_ASSOC_STATIC_MAX_LANDMARKS = " +
+                                    std::to_string(EKF_ASSOC_STATIC_MAX_LANDMARKS) + "); use ekf_associate on a handle");
+        return EKF_EINVAL;
+    }
+    if (assoc_mode == EKF_ASSOC_POSITION && (!d_P || ld < 3 + 2 * (int64_t)N)) { put_err(errbuf, errlen, "ekf_associate_static: mode B needs P with ld >= 3+2N"); return EKF_EINVAL; }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) { put_err(errbuf, errlen, std::string("ekf_associate_static: cudaGetDevice: ") + cudaGetErrorString(e)); return EKF_ECUDA; }
+    {   // the caller's buffers must be device memory of the CURRENT device (a host pointer would fault or, where the GPU can
+        // reach host memory, be read silently); cudaPointerGetAttributes allocates nothing
+        const void* ptrs[4] = {d_x, d_s, d_result, assoc_mode == EKF_ASSOC_POSITION ? d_P : nullptr};
+        const char* names[4] = {"d_x", "d_s", "d_result", "d_P"};
+        for (int i = 0; i < 4; ++i) {
+            if (!ptrs[i]) continue;
+            cudaPointerAttributes at;
+            e = cudaPointerGetAttributes(&at, ptrs[i]);
+            if (e != cudaSuccess || (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged) ||
+                (at.type == cudaMemoryTypeDevice && at.device != dev)) {
+                cudaGetLastError();
+                put_err(errbuf, errlen, std::string("ekf_associate_static: ") + names[i] + " is not device memory of the current device " + std::to_string(dev));
+                return EKF_EINVAL;
+            }
+        }
+    }
+    void* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ok[dev]) {                               // set-up, once per device, that device current
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_assoc_static_scratch);
+            if (e != cudaSuccess || !p) { put_err(errbuf, errlen, std::string("ekf_associate_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e)); return EKF_ECUDA; }
+            g_static_ptr[dev] = p;
+            g_static_ok[dev] = true;
+        }
+        base = g_static_ptr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)(uintptr_t)stream;
+    unsigned int* ticket = (unsigned int*)((unsigned char*)base + EKF_STATIC_ASSOC_TICKET_OFF);
+    e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
+    if (e != cudaSuccess) { put_err(errbuf, errlen, std::string("ekf_associate_static: cudaMemsetAsync: ") + cudaGetErrorString(e)); return EKF_ECUDA; }
+    ekf::launch_associate(st, d_P, ld, d_x, d_s, N, z[0], z[1], z[2], Rdiag[0], Rdiag[1], s_cost, s_thresh, assoc_mode,
+                          storage == EKF_STORAGE_SYM ? 1 : 0, base, ticket, (ekf::AssocResult*)d_result);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { put_err(errbuf, errlen, std::string("ekf_associate_static: launch: ") + cudaGetErrorString(e)); return EKF_ECUDA; }
+    return EKF_OK;
+}

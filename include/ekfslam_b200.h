@@ -113,6 +113,26 @@ int32_t ekf_append(ekf_handle* h, const double u[2], const double Rdiag[2],
 int32_t ekf_associate(ekf_handle* h, const double z[3], const double Rdiag[2],
                       int32_t* newLL, int32_t* idx1);
 
+/* Association (K4, Correspondence.m:28-88 as ekf_associate computes it) for callers that may not allocate.
+ * NO COUNTERPART IN THE REFERENCE: this entry point was added for code under CUDA
+ * graph capture, tight serving loops and harnesses that forbid cudaMalloc.  It takes no handle and calls no cudaMalloc /
+ * cudaFree / allocating library routine: the kernel's scratch (per-block candidates + the fold's ticket word) lives in a
+ * file-scope `static __device__` array of 65 792 bytes that every GPU loading the library holds until exit, which bounds
+ * the map at EKF_ASSOC_STATIC_MAX_LANDMARKS landmarks (EKF_EINVAL beyond, message in errbuf).
+ *   d_x (3+2N), d_s (N), d_P (ld x (3+2N) column-major; read in mode B only, may be NULL in mode A): DEVICE pointers on the
+ *   current device, the caller's; d_result: DEVICE pointer to 16 bytes, written as {int32 newLL; int32 idx1; double cost}
+ *   (cost = min_log_likelihood, Inf when newLL); z = [range, bearing_deg, signature], Rdiag: host; s_cost, s_thresh,
+ *   assoc_mode (EKF_ASSOC_*), storage (EKF_STORAGE_*: SYM reads only elements on/above the diagonal of P) as in ekf_params;
+ *   stream: cudaStream_t on the current device (0 = default stream).  The call enqueues one 4-byte memset and one kernel
+ *   and returns; it does not synchronise.  errbuf (may be NULL) receives the message of a failure.
+ * Every call on a GPU shares the one scratch array: calls that overlap on the GPU (different streams or threads) race;
+ * calls on one stream, or otherwise ordered, are safe back to back. */
+#define EKF_ASSOC_STATIC_MAX_LANDMARKS 1048576
+int32_t ekf_associate_static(const double* d_x, const double* d_P, int64_t ld, const double* d_s, int32_t N,
+                             const double z[3], const double Rdiag[2], double s_cost, double s_thresh,
+                             int32_t assoc_mode, int32_t storage, void* d_result, uint64_t stream,
+                             char* errbuf, int32_t errlen);
+
 /* Whole measure() loop for k observations: EKF_SLAM.m:105-150 / EKF_SLAM_UC.m:107-151.
  * observed_LL is k x 3 column-major ([range | bearing | index], ld = k).
  * loc_table (n_table x 2 column-major) and index_table (n_table) are the fields of
