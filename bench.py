@@ -468,7 +468,8 @@ def main():
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     N, k, K, W = args.landmarks, args.k, args.steps, args.warmup
     n = 3 + 2 * N
-    tstream = torch.cuda.Stream()          # non-default stream: torch events and the library share it
+    tstream = torch.cuda.Stream(priority=-1)   # non-default stream: torch events and the library share it; above the lowest priority so that the
+                                              # state chain overlaps the library's K3 stream (continuous flush)
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
 

@@ -85,6 +85,29 @@ struct ekf_handle {
     double2* Bd2 = nullptr;
     cudaStream_t sg = nullptr;
     cudaEvent_t ev_g1 = nullptr, ev_g2 = nullptr;
+    // continuous flush ("shadow"; single GPU, SYM storage, cross-step deferral, n >= shadow_min_n; EKF_SHADOW=0 disables):
+    // the K3 pass of a full set of terms runs OUT OF PLACE on its own low-priority stream `sf` (P -> P2, from frozen copies
+    // Kf / Bf of the set), while predict and the following batches carry on from the untouched P on the handle's stream: the
+    // gather of a batch's slot columns reads P + the robot strip (rows 0..2, which predict rewrites; ekf_kernels.cu) and the
+    // pending-aware linearisation / gain kernels correct them by the whole window [0, m_pend) = the mA terms of the pass in
+    // flight + the mQ terms of the pass queued behind it (their copies in the window keep following predict's F) + the set
+    // that is filling up.  A set is closed the moment it is full: its pass is enqueued on `sf` at once -- behind the running
+    // one, from that one's output back into the buffer the chain is still reading, which is why the chain then has to retire
+    // the running pass (wait for it, let the strip drop its terms, swap P and P2) before it may gather again.  The K3 kernel
+    // so runs back to back, and every latency-bound kernel, and the host's turnaround between calls, hides beside it.
+    bool shadow = false;
+    int shadow_min_n = 0;      // state size from which the mode is used (below it the pass is too short to hide anything)
+    double* P2 = nullptr;
+    double* strip = nullptr;   // 4 x ld doubles
+    bool strip_valid = false;
+    double2* Kf[2] = {nullptr, nullptr};   // frozen copies of a closed set, alternating between consecutive passes
+    double2* Bf[2] = {nullptr, nullptr};
+    cudaStream_t sf = nullptr;
+    cudaEvent_t ev_fz = nullptr, ev_fd[2] = {nullptr, nullptr};
+    int nfl = 0;               // passes outstanding on sf: 0, 1 (running) or 2 (running + queued)
+    int fcur = 0;              // ev_fd / Kf index of the running pass
+    int mA = 0;                // terms of the running pass (window slots [0, mA))
+    int mQ = 0;                // terms of the queued pass (window slots [mA, mA + mQ))
     int dd_variant = -1;       // downdate kernel variant (-1 = library default; EKF_DOWNDATE_VARIANT env at create)
     Lin* lin = nullptr;
     BatchLin* blin = nullptr;  // scratch of the fused batch linearisation (ekf_update_batch)
@@ -139,6 +162,8 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
     do { if (!(h)) return EKF_EINVAL; } while (0)
 
 static int32_t flush(ekf_handle* h);
+static int32_t shadow_strip_ready(ekf_handle* h);
+static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src);
 static int32_t exec_sharded(ekf_handle* h);
 static int32_t downdate_sharded(ekf_handle* h);
 static int32_t front_exec(ekf_handle* f);
@@ -188,6 +213,7 @@ static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing ma
 
 static inline int n_of(const ekf_handle* h) { return 3 + 2 * h->N; }
 static inline int sym_of(const ekf_handle* h) { return h->p.storage == EKF_STORAGE_SYM ? 1 : 0; }
+static inline bool shadow_on(const ekf_handle* h) { return h->shadow && n_of(h) >= h->shadow_min_n; }   // continuous flush in use at this size
 
 // ---- NCCL is bound lazily (dlopen) so that the single-GPU library loads anywhere libcudart does ----
 struct NcclApi {
@@ -301,6 +327,10 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     for (auto e : h->ev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd); cudaFree(h->Bt);
     cudaFree(h->Kd2); cudaFree(h->Bd2);
+    if (h->sf) { cudaStreamSynchronize(h->sf); cudaStreamDestroy(h->sf); }
+    if (h->ev_fz) cudaEventDestroy(h->ev_fz);
+    for (int i = 0; i < 2; ++i) { if (h->ev_fd[i]) cudaEventDestroy(h->ev_fd[i]); cudaFree(h->Kf[i]); cudaFree(h->Bf[i]); }
+    cudaFree(h->P2); cudaFree(h->strip);
     if (h->sg) { cudaStreamSynchronize(h->sg); cudaStreamDestroy(h->sg); }
     if (h->ev_g1) cudaEventDestroy(h->ev_g1);
     if (h->ev_g2) cudaEventDestroy(h->ev_g2);
@@ -339,6 +369,9 @@ static int32_t init_state(ekf_handle* h) {
     CK(cudaStreamSynchronize(h->stream));
     h->N = 0;
     h->m_pend = 0;
+    h->mA = h->mQ = 0;
+    h->nfl = 0;
+    h->strip_valid = false;
     h->sigs.clear();
     return EKF_OK;
 }
@@ -416,12 +449,51 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
     if (const char* v = getenv("EKF_DOWNDATE_VARIANT")) h->dd_variant = atoi(v);
     int32_t rc = [&]() -> int32_t {
         CK(cudaSetDevice(p->device));
-        if (p->stream) { h->stream = (cudaStream_t)(uintptr_t)p->stream; }
-        else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
         h->cap_n = 3 + 2 * p->capacity_landmarks;
         h->ld = ((int64_t)h->cap_n + 15) / 16 * 16;
+        {
+            // continuous flush: needs a second P (checked against the free memory), a stream of its own making (the chain
+            // must outrank the K3 pass in the block scheduler) and the decoupled state chain
+            const char* sh = getenv("EKF_SHADOW");
+            const char* ax = getenv("EKF_ASYNC_X");
+            const char* lz = getenv("EKF_LAZY_FLUSH");
+            h->shadow = world == 1 && !in_process && h->xstep && p->storage == EKF_STORAGE_SYM &&
+                        !(sh && atoi(sh) == 0) && !(ax && atoi(ax) == 0) && !(lz && atoi(lz) != 0);
+            if (h->shadow) {
+                size_t fr = 0, tot = 0;
+                CK(cudaMemGetInfo(&fr, &tot));
+                const size_t need = 2 * sizeof(double) * (size_t)h->ld * (size_t)h->cap_n + ((size_t)2 << 30);
+                if (fr < need) h->shadow = false;
+            }
+        }
+        int pr_lo = 0, pr_hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&pr_lo, &pr_hi));
+        if (p->stream) { h->stream = (cudaStream_t)(uintptr_t)p->stream; }      // continuous flush: give it a priority above the lowest, or nothing overlaps
+        else if (h->shadow) { CK(cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, pr_hi)); h->own_stream = true; }
+        else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
+        if (h->shadow) {
+            CK(cudaStreamCreateWithPriority(&h->sf, cudaStreamNonBlocking, pr_lo));
+            CK(cudaEventCreateWithFlags(&h->ev_fz, cudaEventDisableTiming));
+            for (int i = 0; i < 2; ++i) CK(cudaEventCreateWithFlags(&h->ev_fd[i], cudaEventDisableTiming));
+            const char* mn = getenv("EKF_SHADOW_MIN_N");
+            h->shadow_min_n = mn ? atoi(mn) : 8000;       // below ~4000 landmarks a K3 pass is shorter than the kernels it would hide
+        }
         ekf_slab_range(p->capacity_landmarks, world, rank, p->storage, &h->c_lo, &h->c_hi);
         CK(cudaMalloc(&h->P, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
+        if (h->shadow) {
+            CK(cudaMalloc(&h->P2, sizeof(double) * h->ld * h->cap_n));
+            CK(cudaMemset(h->P2, 0, sizeof(double) * h->ld * h->cap_n));
+            CK(cudaMalloc(&h->strip, sizeof(double) * 4 * h->ld));
+            CK(cudaMemset(h->strip, 0, sizeof(double) * 4 * h->ld));
+            for (int i = 0; i < 2; ++i) {
+                CK(cudaMalloc(&h->Kf[i], sizeof(double2) * h->ld * EKF_MAX_PEND));
+                CK(cudaMalloc(&h->Bf[i], sizeof(double2) * h->ld * EKF_MAX_PEND));
+                CK(cudaMemset(h->Kf[i], 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
+                CK(cudaMemset(h->Bf[i], 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
+            }
+            CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS));
+            h->Pc_cur = h->Pc;
+        }
         if (world > 1 && in_process) {       // peers are wired by ekf_create_multi once every sub-handle exists
             CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS * 2));
             h->Pc_cur = h->Pc;
@@ -446,8 +518,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
-        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * EKF_MAX_PEND));
-        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * EKF_MAX_PEND));
+        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * (h->shadow ? EKF_MAX_WINDOW : EKF_MAX_PEND)));
+        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * (h->shadow ? EKF_MAX_WINDOW : EKF_MAX_PEND)));
         CK(cudaMalloc(&h->Bt, sizeof(double) * EKF_BT_SROW * ((size_t)(h->c_hi - h->c_lo) + 16)));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->blin, sizeof(BatchLin)));
@@ -483,7 +555,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             // slows from 0.520 to 0.530 ms beside the side-stream kernels (the batch after a flush is the cheap one, m0 = 0,
             // so only ~28 us per two steps can hide and the gather + the slower flush eat them); at 1k landmarks the extra
             // launches cost 15 %.  EKF_LAZY_FLUSH=1 / 0 forces it.
-            h->lazy = h->xstep && p->storage == EKF_STORAGE_SYM && (lz ? atoi(lz) != 0 : world > 1);
+            h->lazy = !h->shadow && h->xstep && p->storage == EKF_STORAGE_SYM && (lz ? atoi(lz) != 0 : world > 1);
         }
         if (h->lazy) {
             int pr_lo = 0, pr_hi = 0;
@@ -633,6 +705,7 @@ extern "C" int32_t ekf_sync(ekf_handle* h) {
     if (is_front(h)) { FAN_OUT(h, sh, ekf_sync(sh)); return EKF_OK; }
     CK(cudaStreamSynchronize(h->stream));
     if (h->sx) CK(cudaStreamSynchronize(h->sx));
+    if (h->sf) CK(cudaStreamSynchronize(h->sf));
     return after_sync(h);
 }
 
@@ -680,7 +753,11 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         launch_predict_x_save(h->sx, h->x, u[0], u[1], h->xprev);
         CK(cudaEventRecord(h->ev_px, h->sx));
         CK(cudaStreamWaitEvent(h->stream, h->ev_px, 0));
-        if (h->world > 1)
+        if (shadow_on(h)) {                  // covariance half on the robot strip: P itself may be under a K3 pass
+            int32_t rcs = shadow_strip_ready(h);
+            if (rcs != EKF_OK) return rcs;
+            launch_predict_strip(h->stream, h->strip, h->xprev, n_of(h), u[0], u[1], h->p.C, h->Kd, h->Bd, h->ld, h->m_pend);
+        } else if (h->world > 1)
             launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h),
                                    h->Kd, h->Bd, h->ld, h->xstep ? h->m_pend : 0);
         else
@@ -917,9 +994,102 @@ static int32_t flush_sharded(ekf_handle* h) {
     return downdate_sharded(h);
 }
 
+// ---- continuous flush (see ekf_handle::shadow) ----
+static int32_t prof_slot(ekf_handle* h) {
+    if (h->ev_used + 2 > h->ev.size()) {
+        size_t old = h->ev.size();
+        h->ev.resize(old + 512);
+        for (size_t i = old; i < h->ev.size(); ++i) CK(cudaEventCreate(&h->ev[i]));
+    }
+    return EKF_OK;
+}
+static int32_t shadow_strip_ready(ekf_handle* h) {
+    if (h->strip_valid) return EKF_OK;
+    launch_strip_load(h->stream, h->P, h->ld, n_of(h), h->strip);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    h->strip_valid = true;
+    return EKF_OK;
+}
+// The running pass is done (the chain waits for it here): its output buffer becomes the matrix, the strip drops the
+// retired terms, the window keeps what came after them; a queued pass becomes the running one.
+static int32_t shadow_retire(ekf_handle* h) {
+    if (h->nfl == 0) return EKF_OK;
+    CK(cudaStreamWaitEvent(h->stream, h->ev_fd[h->fcur], 0));
+    launch_strip_fix(h->stream, h->strip, n_of(h), h->Kd, h->Bd, h->ld, h->mA);
+    std::swap(h->P, h->P2);
+    launch_rotate_slabs(h->stream, h->Kd, h->Bd, h->ld, n_of(h), h->mA, h->m_pend - h->mA, nullptr, nullptr);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    h->m_pend -= h->mA;
+    h->mA = h->mQ;
+    h->mQ = 0;
+    h->nfl -= 1;
+    h->fcur ^= 1;
+    return EKF_OK;
+}
+// Close the set that is filling up (window slots [mA + mQ, m_pend)) and enqueue its K3 pass on `sf`, out of place: as the
+// running pass (P -> P2) when nothing is outstanding, else queued behind the running one (its output P2 -> back into P;
+// the chain must retire the running pass before it reads P again).  Needs a free place in the queue (nfl < 2, mQ == 0).
+static int32_t shadow_close(ekf_handle* h) {
+    const int off = h->mA + h->mQ, m = h->m_pend - off;
+    if (m <= 0) return EKF_OK;
+    if (h->nfl >= 2 || h->mQ != 0) return fail(h, EKF_EINVAL, "internal: continuous flush queue is full");
+    const int slot = h->nfl == 0 ? h->fcur : (h->fcur ^ 1);
+    launch_rotate_slabs(h->stream, h->Kd + (int64_t)off * h->ld, h->Bd + (int64_t)off * h->ld, h->ld, n_of(h), 0, m,
+                        h->Kf[slot], h->Bf[slot]);    // freeze the set: predict keeps transforming its copy in the window
+    CK(cudaEventRecord(h->ev_fz, h->stream));     // also: every gather enqueued so far has read the buffer a queued pass overwrites
+    CK(cudaStreamWaitEvent(h->sf, h->ev_fz, 0));
+    if (h->prof) { int32_t rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->sf)); }
+    double* src = h->nfl == 0 ? h->P : h->P2;
+    double* dst = h->nfl == 0 ? h->P2 : h->P;
+    launch_downdate(h->sf, src, h->ld, n_of(h), n_of(h), 1, h->Kf[slot], h->Bf[slot], h->ld, m, 0, h->dd_variant, h->Bt, dst);
+    if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->sf)); h->ev_used += 2; }
+    CK(cudaEventRecord(h->ev_fd[slot], h->sf));
+    CK(cudaGetLastError());
+    h->dd_launches += 1;
+    h->dd_terms += m;
+    h->launches += 2;
+    if (h->nfl == 0) h->mA = m; else h->mQ = m;
+    h->nfl += 1;
+    return EKF_OK;
+}
+// Forget everything pending (the state is about to be replaced).
+static int32_t shadow_reset(ekf_handle* h) {
+    if (!h->shadow) return EKF_OK;
+    if (h->nfl > 0) { CK(cudaStreamSynchronize(h->sf)); }
+    if (h->nfl == 1) { /* the running pass wrote P2; P is still the matrix the caller replaces */ }
+    h->nfl = 0;
+    h->mA = h->mQ = 0;
+    h->strip_valid = false;
+    return EKF_OK;
+}
+
 static int32_t flush(ekf_handle* h) {
     if (is_front(h)) return front_flush(h);
     if (h->world > 1) return flush_sharded(h);
+    if (h->shadow) {
+        // P must be whole: retire the pass in flight, apply what is left of the window in place, put the strip back
+        int32_t rc = EKF_OK;
+        while (h->nfl > 0) if ((rc = shadow_retire(h)) != EKF_OK) return rc;
+        if (h->m_pend > 0) {
+            if (h->prof) { rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->stream)); }
+            launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), 1, h->Kd, h->Bd, h->ld, h->m_pend, 0, h->dd_variant, h->Bt);
+            if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream)); h->ev_used += 2; }
+            if (h->strip_valid) launch_strip_fix(h->stream, h->strip, n_of(h), h->Kd, h->Bd, h->ld, h->m_pend);
+            h->dd_launches += 1;
+            h->dd_terms += h->m_pend;
+            h->launches += 2;
+            h->m_pend = 0;
+        }
+        if (h->strip_valid) {
+            launch_strip_store(h->stream, h->P, h->ld, n_of(h), h->strip);
+            h->launches += 1;
+            h->strip_valid = false;
+        }
+        CK(cudaGetLastError());
+        return EKF_OK;
+    }
     if (h->m_pend == 0) return EKF_OK;
     if (h->prof) {
         if (h->ev_used + 2 > h->ev.size()) {
@@ -968,6 +1138,12 @@ extern "C" int32_t ekf_update(ekf_handle* h, const double z[2], const double Rdi
         if (h->in_process) return EKF_OK;     // the multi-device front decides when its slabs execute
         if ((int)h->q.size() >= h->defer) return h->xstep ? exec_sharded(h) : flush_sharded(h);
         return EKF_OK;
+    }
+    if (shadow_on(h)) {                   // one-observation batch through the strip-aware path
+        BatchObs ob;
+        memset(&ob, 0, sizeof(ob));
+        ob.k = 1; ob.z0[0] = z[0]; ob.z1[0] = z[1]; ob.R0[0] = Rdiag[0]; ob.R1[0] = Rdiag[1]; ob.a[0] = a;
+        return fused_chunk(h, ob, ObSrc{nullptr, nullptr});
     }
     if (h->m_pend >= h->pend_cap) FLUSH(h);      // lazy flush leaves a full set pending: make room first
     launch_linearize_gain(h->stream, h->P, h->ld, h->x, n_of(h), a, z[0], z[1], Rdiag[0], Rdiag[1], sym_of(h),
@@ -1130,6 +1306,25 @@ extern "C" int32_t ekf_associate(ekf_handle* h, const double z[3], const double 
 // k_batch_gain, flush policy.  `ob` carries the batch by value, or only its size when `src` names a device-side
 // description (slots decided by k_measure_decide).
 static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
+    if (shadow_on(h)) {
+        int32_t rc = shadow_strip_ready(h);
+        if (rc != EKF_OK) return rc;
+        if (h->mQ > 0 && (rc = shadow_retire(h)) != EKF_OK) return rc;     // a queued pass writes into P: move on to the new P first
+        if (h->m_pend - h->mA + ob.k > h->pend_cap) {                        // does not fit the filling set: close it now
+            if ((rc = shadow_close(h)) != EKF_OK) return rc;
+            if (h->mQ > 0 && (rc = shadow_retire(h)) != EKF_OK) return rc;
+        }
+        launch_gather_cols_strip(h->stream, h->P, h->ld, n_of(h), ob, h->Pc, h->ld, src, h->strip);
+        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), 1, ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc, h->ld,
+                              0, n_of(h), h->m_pend, nullptr, nullptr, 0, src);
+        h->launches += 3;
+        CK(cudaGetLastError());
+        MARK_X(h);
+        h->m_pend += ob.k;
+        if (h->m_pend - h->mA - h->mQ + std::min(h->defer, EKF_BATCH_MAX) > h->pend_cap)   // no further full chunk fits: its pass can start
+            return shadow_close(h);
+        return EKF_OK;
+    }
     if (h->lazy && h->m_pend > 0 && h->m_pend + ob.k > h->pend_cap) {
         // lazy flush: copy the batch's slot columns out of P0, then K3 on the main stream || lin + gain on sg
         launch_gather_cols(h->stream, h->P, h->ld, n_of(h), sym_of(h), ob, h->Pc, h->ld, src);
@@ -1514,6 +1709,7 @@ extern "C" int32_t ekf_set_state(ekf_handle* h, const double* x, const double* P
     if (is_front(h)) { FAN_OUT(h, sh, ekf_set_state(sh, x, P, lda, s, N)); h->N = N; return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
+    { int32_t rcs = shadow_reset(h); if (rcs != EKF_OK) return rcs; }
     CK(cudaMemsetAsync(h->Kd, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
     if (h->Kd2) CK(cudaMemsetAsync(h->Kd2, 0, sizeof(double2) * h->ld * EKF_MAX_PEND, h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
@@ -1599,6 +1795,7 @@ extern "C" int32_t ekf_set_state_lowrank(ekf_handle* h, const double* x, const d
     if (is_front(h)) { FAN_OUT(h, sh, ekf_set_state_lowrank(sh, x, s, N, A, r, d)); h->N = N; return EKF_OK; }
     CK(cudaSetDevice(h->p.device));
     h->m_pend = 0;
+    { int32_t rcs = shadow_reset(h); if (rcs != EKF_OK) return rcs; }
     double *dA = nullptr, *dd = nullptr;
     int32_t rc = [&]() -> int32_t {               // scratch freed on every path
         CK(cudaMalloc(&dA, sizeof(double) * (size_t)n * r));
@@ -1668,6 +1865,7 @@ extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, in
     }
     CK(cudaSetDevice(h->p.device));
     CK(cudaStreamSynchronize(h->stream));
+    if (h->sf) CK(cudaStreamSynchronize(h->sf));
     for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));

@@ -226,7 +226,7 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 // storage column tile y keeps row tiles 0 .. min(R, f(y)) - 1, f(y) = floor((A + y) / RPC) + 1 with
 // A = floor((col_off + TC - 1) / TC): the tiles that touch the upper triangle.  Launching exactly those (1-D grid, column
 // tile major) instead of the R x CT rectangle removes ~half the CTAs of a SYM launch, which only existed to exit.
-struct TileMap { int R, CT, A, RPC, ystar, order; };   // ystar: first column tile whose live count is clipped at R; order 1: two fronts (k_downdate_tma)
+struct TileMap { int R, CT, A, RPC, ystar, order, zero; };   // ystar: first column tile whose live count is clipped at R; order 1: two fronts (k_downdate_tma)
 __host__ __device__ inline long long tm_G(long long m, int r) {          // sum_{t<m} floor(t / r)
     const long long q = m / r, rem = m % r;
     return (long long)r * q * (q - 1) / 2 + q * rem;
@@ -237,7 +237,7 @@ __host__ __device__ inline long long tm_prefix(const TileMap& tm, int Y) {   // 
 }
 static inline TileMap tm_make(int R, int CT, int TC, int RPC, int col_off, int sym) {
     TileMap tm;
-    tm.R = R; tm.CT = CT; tm.RPC = RPC; tm.order = 0;
+    tm.R = R; tm.CT = CT; tm.RPC = RPC; tm.order = 0; tm.zero = 0;   // zero: a 0 the compiler cannot see (k_downdate_hyb's slot release)
     tm.A = (col_off + TC - 1) / TC;
     long long ys = sym ? (long long)RPC * (R - 1) - tm.A : 0;            // f(y) >= R  <=>  y >= RPC (R - 1) - A
     tm.ystar = (int)(ys < 0 ? 0 : (ys > CT ? CT : ys));
@@ -522,7 +522,7 @@ __global__ void k_pack_bt(const double2* __restrict__ Ball, int64_t lds, int M, 
 
 template <int KS, int SCOLS, int NSTAGE, int BST, int MINB>
 __global__ void __launch_bounds__(288, MINB)
-k_downdate_hyb(double* __restrict__ P, int64_t ld, int n, int ncols, const double2* __restrict__ Kall,
+k_downdate_hyb(const double* P, double* Pout, int64_t ld, int n, int ncols, const double2* __restrict__ Kall,
                const double2* __restrict__ Ball, const double* __restrict__ Bt, int64_t lds, int M, TileMap tm) {
     typedef HybCfg<KS, SCOLS, NSTAGE, BST> C;
     extern __shared__ __align__(128) unsigned char smem[];
@@ -593,7 +593,7 @@ k_downdate_hyb(double* __restrict__ P, int64_t ld, int n, int ncols, const doubl
         }
     }
     const int row_off = (warp * 16 + 4 * t) * 8;                     // byte offset of this lane's 4 rows within a column
-    double* gp = P + (int64_t)(i0 + 4 * t) + (int64_t)(c0 + r) * ld;  // this lane's 4 rows of column r of group 0
+    double* gp = Pout + (int64_t)(i0 + 4 * t) + (int64_t)(c0 + r) * ld;  // this lane's 4 rows of column r of group 0 (Pout == P: in place)
     if (!BST) asm volatile("bar.sync 1, 256;" ::: "memory");         // B operand staged (consumer warps only)
     constexpr int NG = SCOLS / 8;
     for (int s = 0; s < ns; ++s) {
@@ -613,19 +613,27 @@ k_downdate_hyb(double* __restrict__ P, int64_t ld, int n, int ncols, const doubl
                 lo[g] = pv[0]; hi[g] = pv[1];
             }
         }
+        int dep = 0;
 #pragma unroll
         for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
             for (int g = 0; g < NG; ++g) {
                 // columns beyond the tile read stale operand rows: they only reach accumulator rows that are never stored
                 const double a = bop[(g * 8 + r) * C::SROW + 4 * ks + t];
+                if (BST && ks + 3 >= KS) dep ^= __double2hiint(a);
                 dmma8x8x4(lo[g].x, lo[g].y, a, kf[0][ks]);
                 dmma8x8x4(hi[g].x, hi[g].y, a, kf[1][ks]);
             }
         }
-        // every shared-memory read of this stage has been consumed by an issued DMMA: the slot may be refilled
+        // The slot may be refilled once every shared-memory read of this stage has RETURNED.  With the B operand in the stage
+        // (BST) the last reads happen late, and ptxas schedules the arrive between them and the DMMAs that consume them (an
+        // LDS that has only been issued can still be waiting in the memory pipe -- beside kernels that flood it with
+        // uncoalesced loads, long enough for the producer's refill to land first: seen as wrong elements when this kernel
+        // ran next to the gather / gain kernels of the continuous flush).  So the arrive's address is made to depend on the
+        // values of the last reads: dep is compared with a pattern, and the offset it would select is a zero the compiler
+        // cannot see (tm.zero) -- the arrive cannot issue before those loads have written their registers.
         __syncwarp();
-        if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+        if (lane == 0) mbar_arrive(empty0 + 8 * slot + (BST && dep == 0x7ff4dead ? (uint32_t)tm.zero : 0u));
 #pragma unroll
         for (int g = 0; g < NG; ++g)
             if (ok[g]) {
@@ -637,7 +645,7 @@ k_downdate_hyb(double* __restrict__ P, int64_t ld, int n, int ncols, const doubl
 
 template <int KS, int SCOLS, int NSTAGE, int BST, int MINB>
 static void launch_dd_hyb(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                          const double2* Ball, double* Bt, int64_t lds, int M, int col_off) {
+                          const double2* Ball, double* Bt, int64_t lds, int M, int col_off, double* Pout) {
     typedef HybCfg<KS, SCOLS, NSTAGE, BST> C;
     smem_optin<k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB>>(C::SMEM);
     const int R = (n + C::TR - 1) / C::TR, CT = (ncols + C::TC - 1) / C::TC;
@@ -647,14 +655,14 @@ static void launch_dd_hyb(cudaStream_t st, double* P, int64_t ld, int n, int nco
     const long long live = tm_prefix(tm, CT);
     if (live <= 0 || live > 0x3fffffffLL) return;
     if (BST) k_pack_bt<KS><<<cdiv(ncols, 128), 128, 0, st>>>(Ball, lds, M, ncols, Bt);
-    k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, ld, n, ncols, Kall, Ball, Bt, lds, M, tm);
+    k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, Pout ? Pout : P, ld, n, ncols, Kall, Ball, Bt, lds, M, tm);
 }
 
 // hybrid variants by number (EKF_DOWNDATE_VARIANT >= 30); returns false when `v` names none
 template <int KS>
 static bool launch_dd_hyb_v(int v, cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                            const double2* Ball, double* Bt, int64_t lds, int M, int col_off) {
-#define HY(SC, NS, BS, MB) launch_dd_hyb<KS, SC, NS, BS, MB>(st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, M, col_off); return true
+                            const double2* Ball, double* Bt, int64_t lds, int M, int col_off, double* Pout = nullptr) {
+#define HY(SC, NS, BS, MB) launch_dd_hyb<KS, SC, NS, BS, MB>(st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, M, col_off, Pout); return true
     if (Bt == nullptr && v != 30 && v != 37) return false;       // the in-stage operand needs the Bt scratch buffer
     switch (v) {
         case 30: HY(8, 4, 0, 3);       // operand tile per CTA as in k_downdate_tma, 4 x 8-col stages
@@ -681,12 +689,24 @@ static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int ncols, 
 
 // m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
-                     int64_t lds, int m, int col_off, int variant, double* Bt) {
+                     int64_t lds, int m, int col_off, int variant, double* Bt, double* Pout) {
     if (m < 1) return;
+    if (Pout && Pout != P) {
+        // out of place (continuous flush): the hybrid kernels store straight from registers, so the destination is just
+        // another pointer; any other kernel choice gets a copy of the matrix first and runs in place on it
+        static int force_copy = -1;
+        if (force_copy < 0) { const char* e = getenv("EKF_SHADOW_DEBUG"); force_copy = (e && (atoi(e) & 64)) ? 1 : 0; }
+        const bool hyb = !force_copy && ((variant == 30 || variant == 37) || (Bt != nullptr && ((variant >= 31 && variant <= 38) || (variant < 30 && m > 8 && variant != 13 && variant != 21))));
+        if (!hyb) {
+            cudaMemcpyAsync(Pout, P, sizeof(double) * (size_t)ld * (size_t)ncols, cudaMemcpyDeviceToDevice, st);
+            P = Pout;
+            Pout = nullptr;
+        }
+    }
     if (variant >= 30) {    // hybrid kernels (bulk-async in, registers out), any rank
         bool done = false;
         switch ((m + 1) / 2) {
-#define HV(KS_) case KS_: done = launch_dd_hyb_v<KS_>(variant, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+#define HV(KS_) case KS_: done = launch_dd_hyb_v<KS_>(variant, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
             HV(1) HV(2) HV(3) HV(4) HV(5) HV(6) HV(7) HV(8)
 #undef HV
             default: break;
@@ -707,10 +727,10 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
         bool done = false;
         if (Bt != nullptr && variant != 13 && variant != 21) {
             switch ((m + 1) / 2) {
-                case 5: done = launch_dd_hyb_v<5>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
-                case 6: done = launch_dd_hyb_v<6>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
-                case 7: done = launch_dd_hyb_v<7>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
-                default: done = launch_dd_hyb_v<8>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off); break;
+                case 5: done = launch_dd_hyb_v<5>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
+                case 6: done = launch_dd_hyb_v<6>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
+                case 7: done = launch_dd_hyb_v<7>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
+                default: done = launch_dd_hyb_v<8>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
             }
         }
         if (done) return;

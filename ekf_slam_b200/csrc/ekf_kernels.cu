@@ -308,7 +308,7 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
     // slabs with o0 = m0 normally; the OTHER pair of slabs with o0 = 0 when the pending terms are being flushed by a
     // concurrent K3 launch (lazy flush, ekf_capi.cu).
     __shared__ BatchLin L;
-    __shared__ double2 Kc[EKF_MAX_PEND][EKF_BATCH_SLOTS], Bc[EKF_MAX_PEND][EKF_BATCH_SLOTS];   // pending K_q(col_s,:), B_q(:,col_s)
+    __shared__ double2 Kc[EKF_MAX_WINDOW][EKF_BATCH_SLOTS], Bc[EKF_MAX_WINDOW][EKF_BATCH_SLOTS];   // pending K_q(col_s,:), B_q(:,col_s)
     for (int e = threadIdx.x; e < (int)(sizeof(BatchLin) / sizeof(double)); e += blockDim.x)
         ((double*)&L)[e] = ((const double*)lin)[e];
     const int k = ob.k, ns = 3 + 2 * k;
@@ -397,6 +397,134 @@ void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int
                         ObSrc src) {
     dim3 grid((n + 255) / 256, 3 + 2 * ob.k);      // ob.k on the host is the chunk size in both modes
     k_gather_cols<<<grid, 256, 0, st>>>(P, ld, n, sym, ob, Pc, ldc, src);
+}
+
+// ------------------------------------------------------------------ robot strip (continuous flush, ekf_capi.cu "shadow")
+// While a K3 pass streams the whole of P on its own stream, nothing else may write P -- but predict rewrites rows 0, 1
+// of every column (F P F' + Q).  In that mode the authoritative copy of rows 0..2 of the stored matrix lives in a strip,
+// S[4 j + r] = P0(r, j) (one 32-byte sector per column; the 3 x 3 corner is stored in full): predict works on the strip,
+// the gather of a batch's slot columns takes every element with a row or column index < 3 from it, and when a pass
+// retires the strip catches up with it (k_strip_fix: S <- S - sum_q K_q B_q over the retired terms, which the
+// predicts since have transformed together with the strip).  k_strip_store writes it back when P must be whole.
+__global__ void k_strip_load(const double* __restrict__ P, int64_t ld, int n, double* __restrict__ S) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) S[4 * (int64_t)j + r] = ldP(P, ld, r, j, 1);
+    S[4 * (int64_t)j + 3] = 0.0;
+}
+
+__global__ void k_strip_store(double* __restrict__ P, int64_t ld, int n, const double* __restrict__ S) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+        if (r <= j) P[(int64_t)r + (int64_t)j * ld] = S[4 * (int64_t)j + r];
+}
+
+// k_predict_P on the strip (same expressions), plus the pending window's K_q <- F K_q, B_q <- B_q F' in an extra block.
+__global__ void k_predict_strip(double* __restrict__ S, const double* __restrict__ x, int n, double u1, double u2, double C,
+                                double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds, int m) {
+    const double th = x[2];
+    const double st = sind(th), ct = cosd(th);
+    const double a = -1.0 * u1 * st;      // F(1,3), EKF_SLAM.m:63
+    const double b = u1 * ct;             // F(2,3), EKF_SLAM.m:64
+    if (m > 0 && blockIdx.x == gridDim.x - 1) {
+        const int t = threadIdx.x;
+        if (t < 2 * m) {
+            double2* Sl = (t & 1 ? Ball : Kall) + (int64_t)(t >> 1) * lds;
+            const double2 v0 = Sl[0], v1 = Sl[1], v2 = Sl[2];
+            Sl[0] = make_double2(v0.x + a * v2.x, v0.y + a * v2.y);
+            Sl[1] = make_double2(v1.x + b * v2.x, v1.y + b * v2.y);
+        }
+        return;
+    }
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) {
+        double M[3][3];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) M[i][j] = S[4 * (i > j ? i : j) + (i > j ? j : i)];      // the live (min, max) entry, like ldP
+        for (int j = 0; j < 3; ++j) {     // F*P
+            M[0][j] = M[0][j] + a * M[2][j];
+            M[1][j] = M[1][j] + b * M[2][j];
+        }
+        for (int i = 0; i < 3; ++i) {     // (F*P)*F'
+            M[i][0] = M[i][0] + M[i][2] * a;
+            M[i][1] = M[i][1] + M[i][2] * b;
+        }
+        double W[3] = {u1 * ct, u1 * st, u2};      // EKF_SLAM.m:42
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) S[4 * j + i] = M[i][j] + (W[i] * C) * W[j];   // :44,47
+    } else if (t >= 3 && t < n) {
+        double* col = S + 4 * (int64_t)t;
+        const double p2 = col[2];
+        col[0] = col[0] + a * p2;
+        col[1] = col[1] + b * p2;
+    }
+}
+
+// The m retired terms leave the strip: S(r, j) <- S(r, j) - sum_q K_q(min) B_q(max), in ldP_def's order.
+__global__ void k_strip_fix(double* __restrict__ S, int n, const double2* __restrict__ Kall, const double2* __restrict__ Ball,
+                            int64_t lds, int m) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    double v[3];
+    int lo[3], hi[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) { lo[r] = r < j ? r : j; hi[r] = r < j ? j : r; v[r] = S[4 * (int64_t)hi[r] + lo[r]]; }
+    __syncthreads();                      // corner: every thread of block 0 has read before any of them writes a mirror entry
+    for (int q = 0; q < m; ++q) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) v[r] = rank2_sub(v[r], Kall[q * lds + lo[r]], Ball[q * lds + hi[r]]);
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) S[4 * (int64_t)j + r] = v[r];
+}
+
+// k_gather_cols with the strip in charge of rows / columns 0..2.
+__global__ void k_gather_cols_strip(const double* __restrict__ P, int64_t ld, int n, const BatchObs ob_arg,
+                                    double* __restrict__ Pc, int64_t ldc, ObSrc src, const double* __restrict__ S) {
+    __shared__ BatchObs ob;
+    stage_batch_obs(ob, ob_arg, src.ob);
+    const int slot = blockIdx.y;
+    if (slot >= 3 + 2 * ob.k) return;
+    const int c = slot < 3 ? slot : ob.a[(slot - 3) >> 1] + ((slot - 3) & 1);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int lo = i < c ? i : c, hi = i < c ? c : i;
+    Pc[(int64_t)slot * ldc + i] = lo < 3 ? S[4 * (int64_t)hi + lo] : P[(int64_t)lo + (int64_t)hi * ld];
+}
+
+// Window bookkeeping: terms [mA, mA + mB) move to the front of the window (the mA retired ones drop out) and, when Kf is
+// given, are also frozen into (Kf, Bf) for the K3 pass that is about to start (predict keeps transforming the window).
+__global__ void k_rotate_slabs(double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds, int rows, int mA, int mB,
+                               double2* __restrict__ Kf, double2* __restrict__ Bf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    for (int q = 0; q < mB; ++q) {        // ascending q: reads stay ahead of writes
+        const double2 kv = Kall[(int64_t)(mA + q) * lds + i], bv = Ball[(int64_t)(mA + q) * lds + i];
+        if (mA > 0) { Kall[(int64_t)q * lds + i] = kv; Ball[(int64_t)q * lds + i] = bv; }
+        if (Kf) { Kf[(int64_t)q * lds + i] = kv; Bf[(int64_t)q * lds + i] = bv; }
+    }
+}
+
+void launch_strip_load(cudaStream_t st, const double* P, int64_t ld, int n, double* S) { k_strip_load<<<(n + 255) / 256, 256, 0, st>>>(P, ld, n, S); }
+void launch_strip_store(cudaStream_t st, double* P, int64_t ld, int n, const double* S) { k_strip_store<<<(n + 255) / 256, 256, 0, st>>>(P, ld, n, S); }
+void launch_predict_strip(cudaStream_t st, double* S, const double* xprev, int n, double u1, double u2, double C,
+                          double2* Kall, double2* Ball, int64_t lds, int m) {
+    k_predict_strip<<<(n + 255) / 256 + (m > 0 ? 1 : 0), 256, 0, st>>>(S, xprev, n, u1, u2, C, Kall, Ball, lds, m);
+}
+void launch_strip_fix(cudaStream_t st, double* S, int n, const double2* Kall, const double2* Ball, int64_t lds, int m) {
+    if (m > 0) k_strip_fix<<<(n + 255) / 256, 256, 0, st>>>(S, n, Kall, Ball, lds, m);
+}
+void launch_gather_cols_strip(cudaStream_t st, const double* P, int64_t ld, int n, const BatchObs& ob, double* Pc, int64_t ldc,
+                              ObSrc src, const double* S) {
+    dim3 grid((n + 255) / 256, 3 + 2 * ob.k);
+    k_gather_cols_strip<<<grid, 256, 0, st>>>(P, ld, n, ob, Pc, ldc, src, S);
+}
+void launch_rotate_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int rows, int mA, int mB, double2* Kf,
+                         double2* Bf) {
+    if (mB > 0 && (mA > 0 || Kf)) k_rotate_slabs<<<(rows + 255) / 256, 256, 0, st>>>(Kall, Ball, lds, rows, mA, mB, Kf, Bf);
 }
 
 // ------------------------------------------------------------------ K5 append

@@ -13,6 +13,7 @@ struct BatchLin;
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym);
 #define EKF_MAX_DEFER 8
 #define EKF_MAX_PEND 16                             // single-GPU handles: rank-2 terms that may stay pending across predict (defer_m = 9..16)
+#define EKF_MAX_WINDOW (2 * EKF_MAX_PEND)            // continuous flush: the set a K3 pass is applying + the set that is filling up
 #define EKF_MAX_SLOTS (3 + 2 * EKF_MAX_DEFER)      // columns exchanged per sharded batch: robot + 2 per observation
 struct SlotSet { int n; int col[EKF_MAX_SLOTS]; }; // global column index of each slot (passed by value)
 struct ObSrc { const BatchObs* ob; const int* skip; };   // device-side batch description + skip word (both null: by-value BatchObs)
@@ -21,8 +22,9 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                      const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1,
-                     double* Bt = nullptr);   // col_off: global index of column 0 (SYM slabs); variant < 0: default; Bt: scratch of
+                     double* Bt = nullptr, double* Pout = nullptr);   // col_off: global index of column 0 (SYM slabs); variant < 0: default; Bt: scratch of
                                               // ncols x EKF_BT_SROW doubles for the kernels that carry the B operand in their stages
+                                              // Pout != null: out of place, Pout = P - sum K_q B_q on every live tile, P untouched (continuous flush)
 #define EKF_BT_SROW (4 * 8 + 4)
 // fused batch (<= 8 observations with known slots; nothing may be pending): fills gain slabs 0..k-1 and updates x
 // Pc != null (sharded): slot columns come from the exchanged Pc[slot][0..n), P is the local slab of columns [c_lo, c_hi)
@@ -33,6 +35,16 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            ObSrc src = ObSrc{nullptr, nullptr});
 void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc,
                         ObSrc src = ObSrc{nullptr, nullptr});
+// ---- continuous flush ("shadow", single GPU, SYM storage): robot strip S[4 j + r] = P0(r, j), r < 3; see ekf_kernels.cu ----
+void launch_strip_load(cudaStream_t st, const double* P, int64_t ld, int n, double* S);
+void launch_strip_store(cudaStream_t st, double* P, int64_t ld, int n, const double* S);
+void launch_predict_strip(cudaStream_t st, double* S, const double* xprev, int n, double u1, double u2, double C,
+                          double2* Kall, double2* Ball, int64_t lds, int m);
+void launch_strip_fix(cudaStream_t st, double* S, int n, const double2* Kall, const double2* Ball, int64_t lds, int m);
+void launch_gather_cols_strip(cudaStream_t st, const double* P, int64_t ld, int n, const BatchObs& ob, double* Pc, int64_t ldc,
+                              ObSrc src, const double* S);
+void launch_rotate_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int rows, int mA, int mB, double2* Kf,
+                         double2* Bf);
 // measure() decisions on the device (EKF_SLAM_UC.m:107-124, mode A): per row of observed_LL the slot it updates; see ekf_kernels.cu
 void launch_measure_decide(cudaStream_t st, const double* s, int N, const double* obs, int k, double Rc0, double Rc1,
                            double s_cost, double s_thresh, BatchObs* ob_chunks, int* skip, int* status_host, int* scratch,

@@ -378,6 +378,54 @@ def test_lazy_flush_matches_flush_then_linearise(defer_m, monkeypatch):
     assert _rel(runs[0][1], runs[1][1]) <= 1e-12
 
 
+@pytest.mark.parametrize('defer_m', [16, 11])
+def test_continuous_flush_matches_in_place_deferral(defer_m, monkeypatch):
+    """Continuous flush (single GPU, SYM, cross-step deferral; EKF_SHADOW=0 disables): the K3 pass of a full set runs out
+    of place on its own stream while predict and the next batches carry on from the untouched matrix + the robot strip +
+    the whole window of pending terms.  Same estimator as the in-place deferral; what differs is when a term reaches
+    the stored matrix relative to the predicts around it, i.e. rounding in rows / columns 0-1: x at every step, blocks of P
+    read mid-run (which settle everything) and the final P agree to 1e-12 over 60 steps (>= 25 passes) with ragged
+    batches, single updates, an append, a property write and getters in between."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
+    N = 700
+    x, A, d, s, lms = synthetic_spd_state(N, seed=17)
+    sizes = (8, 8, 8, 11, 5, 8, 1, 8, 8, 3, 8, 8, 8, 8, 16, 8, 2, 8, 8, 8)
+    runs = []
+    monkeypatch.setenv('EKF_SHADOW_MIN_N', '0')      # the mode is for large maps (default: n >= 8000); force it at this size
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_SHADOW', flag)
+        f = E.EKF_SLAM(capacity_landmarks=N + 4, storage='sym', defer_m=defer_m)
+        f.set_state_lowrank(x, s, A, d)
+        rng = np.random.default_rng(41)
+        xs = []
+        for step in range(60):
+            rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:sizes[step % len(sizes)]]
+            Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+            f.predict([0.3, 1.0])
+            if step % 20 == 6:
+                f.update(rows[0, :2], Rd[0], int(rows[0, 2]))
+            else:
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+            xs.append(f.x)
+            if step in (8, 33):
+                xs.append(f.P_block(0, 0, 7, 7))
+                xs.append(f.P_block(3, 100, 40, 300))
+            if step == 10:
+                f.append([0.3, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], N + 1)
+            if step == 21:
+                f.predict([0.1, -2.0])          # two predicts in a row while a pass is in flight
+            if step == 40:
+                xv = f.x
+                xv[0] += 0.25
+                f.x = xv                          # property write: pending terms are applied first
+        runs.append((xs, f.P))
+        f.close()
+    assert max(_rel(a, b) for a, b in zip(runs[0][0], runs[1][0])) <= 1e-12
+    assert _rel(runs[0][1], runs[1][1]) <= 1e-12
+    assert np.array_equal(runs[1][1], runs[1][1].T)
+
+
 @pytest.mark.parametrize('storage,defer_m', [('sym', 16), ('sym', 8), ('full', 8), ('full', 3)])
 def test_measure_decided_on_device_is_bit_identical_to_the_host_loop(storage, defer_m, monkeypatch):
     """ekf_measure_batch_async (EKF_SLAM_UC, signature association): rows whose signatures are all in the map are
