@@ -438,7 +438,7 @@ def reduce_measurements(torch, dist, world, m, K, k):
 # ncu --set full captures of the shipped K3 kernels (profiles/): dram__bytes_read.sum + dram__bytes_write.sum per launch.
 # Keyed by (landmarks, storage, world, terms per launch); anything else prints null rather than a number from another kernel.
 NCU_TRAFFIC = {
-    (10000, 'sym', 1, 16): (1.645896e9 + 1.552833e9, 'profiles/ncu_downdate_r02_hyb_rank32_raw.csv: k_downdate_hyb<8,8,4,1,3>, ncu --set full at commit b2987cd (506.7 us under ncu)'),
+    (10000, 'sym', 1, 16): (1.700704e9 + 1.564460e9, 'profiles/ncu_downdate_r02_shadow_rank32_raw.csv: k_downdate_hyb<8,8,4,1,3> out of place (P -> P2, the continuous flush), ncu --set full of the shipped kernel (505.9 us under ncu, where kernels are serialised)'),
     (10000, 'sym', 1, 8): (1.629e9 + 1.551e9, 'profiles/ncu_downdate_r01_final_rank16_raw.csv: k_downdate_tma<4,128,8,4,1> (kernel unchanged since round 1)'),
 }
 
@@ -488,6 +488,24 @@ def main():
     # ---------------- secondary line (single GPU, cross-step deferral only): the same workload with one pass over P per
     # batch of 8 (defer_m = 8), where K3 is a pure streaming kernel -- its HBM fraction is reported beside the main roofline
     streaming = None
+    in_place = None
+    shadow_on = world == 1 and args.defer > 8 and args.storage == 'sym' and n >= int(os.environ.get('EKF_SHADOW_MIN_N', '8000')) \
+        and os.environ.get('EKF_SHADOW', '1') != '0' and os.environ.get('EKF_ASYNC_X', '1') != '0' and os.environ.get('EKF_LAZY_FLUSH', '0') == '0'
+    if shadow_on and not args.no_streaming_variant:
+        # the same workload with the K3 pass in place on the handle's stream (EKF_SHADOW=0): what the rank-32 kernel does when it
+        # has the GPU to itself, beside the main roofline, which times it while the state chain runs next to it
+        os.environ['EKF_SHADOW'] = '0'
+        try:
+            mi = measure_filter(E, L, dist, world, rank, local, stream, barrier, N, k, min(K, 100), W, args.storage, args.defer,
+                                want_e2e=False, parity_steps=0)
+        finally:
+            os.environ.pop('EKF_SHADOW', None)
+        mi.pop('inputs')
+        Ki = min(K, 100)
+        di = mi['dd_ms'] / max(mi['dd_n'], 1)
+        in_place = {'steps': Ki, 'updates_per_s': Ki * k / (mi['ms'] * 1e-3), 'ms_per_step': mi['ms'] / Ki, 'k3_avg_launch_ms': di,
+                    'k3_bytes_per_launch': mi['dd_bytes'], 'achieved': mi['dd_bytes'] / (di * 1e-3) / 1e9, 'unit': 'GB/s',
+                    'what': 'EKF_SHADOW=0: the same rank-32 kernel in place on the one stream, nothing running beside it'}
     if world == 1 and args.defer > 8 and not args.no_streaming_variant:
         m8 = measure_filter(E, L, dist, world, rank, local, stream, barrier, N, k, min(K, 100), W, args.storage, 8,
                             want_e2e=False, parity_steps=0)
@@ -548,11 +566,15 @@ def main():
         'config': workload_config(N, k),
         'implementation': {
             'storage': args.storage, 'defer_m': m['pend_cap'],
-            'downdate': ('one rank-%d pass over P per %d observations%s' % (2 * per_pass, per_pass, ' (terms stay pending across predict: %d steps per pass)' % (per_pass // k) if per_pass > k else '')),
+            'downdate': ('one rank-%d pass over P per %d observations%s' % (2 * per_pass, per_pass, ' (terms stay pending across predict: %d steps per pass)' % (per_pass // k) if per_pass > k else ''))
+                        + ('; continuous flush: the pass runs out of place (P -> P2) on its own stream, back to back, while predict / gather / '
+                           'linearise / gain of the next batches run beside it from P + the robot strip + the window of pending terms' if shadow_on else ''),
             'parallelism': ('one filter, P in %d column slabs (%s storage), per batch one exchange of the 3+2k current columns '
                             '(peer-memory scatter; EKF_SHARD_EXCHANGE=nccl: NCCL %s); slowest slab cols [%d,%d)'
                             % (world, args.storage, 'all-reduce' if args.storage == 'sym' else 'broadcast group', m['slab'][2], m['slab'][3])) if world > 1 else 'single GPU',
-            'serial_per_step': 'predict (P0 rows/cols 0-1 + pending slabs), exchange (sharded), k_batch_lin (k dependent linearisations), k_batch_gain'},
+            'serial_per_step': ('nothing on the K3 stream (passes are queued one ahead); beside it: predict on the strip, k_gather_cols_strip, '
+                                'k_batch_lin (k dependent linearisations), k_batch_gain, and per pass strip fix + window rotation') if shadow_on else
+                               'predict (P0 rows/cols 0-1 + pending slabs), exchange (sharded), k_batch_lin (k dependent linearisations), k_batch_gain'},
         'roofline': roof,
         'exchange': ({'avg_ms': m['xch_ms'] / max(m['xch_n'], 1), 'per_step': m['xch_n'] / K,
                       'path': 'peer-memory scatter (cudaIpc, NVLink stores + flag words)' if m['xch_p2p'] else 'NCCL'} if world > 1 else None),
@@ -569,6 +591,10 @@ def main():
         line['sustained'] = {'steps': sm['steps'], 'value': sm['steps'] * k / (sm['ms'] * 1e-3), 'unit': UNIT,
                              'ms_per_step': sm['ms'] / sm['steps'], 'k3_avg_launch_ms': sm['k3_avg_launch_ms'],
                              'what': 'the same resident loop continued for %d more steps (what the rate settles at under the power cap)' % sm['steps']}
+    if in_place is not None:
+        in_place['frac'] = in_place['achieved'] / peak
+        line['roofline_in_place_variant'] = in_place
+        line['roofline']['measured'] = 'while the state chain of the next batches runs beside the pass (see roofline_in_place_variant for the kernel alone)'
     if streaming is not None:
         streaming['frac'] = streaming['achieved'] / peak
         line['roofline_streaming_variant'] = streaming

@@ -68,6 +68,9 @@ struct ekf_handle {
     cudaStream_t sx = nullptr;
     cudaEvent_t ev_mx = nullptr, ev_px = nullptr, ev_pp = nullptr;
     double* xprev = nullptr;   // pre-motion pose saved by the state half of predict for the covariance half
+    double* x_pin = nullptr;   // pinned staging of x for ekf_get_x (a copy into pageable memory goes through the driver's bounce buffers)
+    bool x_host = false;       // x_pin holds the device's x, except (x_head_dirty) the pose x(1:3) that a predict has moved since:
+    bool x_head_dirty = false; // the read-back after predict then copies 24 bytes instead of 8 n (single-GPU handles)
     int defer = 1;             // flush when m_pend reaches this (1 = immediate); also the chunk size of the fused batch (<= 8)
     // cross-step deferral (single GPU, defer_m = 9..EKF_MAX_PEND): terms stay pending across measure() and predict();
     // the flush runs when the next chunk would not fit (or at a getter / append / mode-B association).  predict then
@@ -206,6 +209,7 @@ static int32_t resolve_measure(ekf_handle* h) {
 #define RESOLVE(h) do { if ((h)->am_pending) { int32_t rc__ = resolve_measure(h); if (rc__ != EKF_OK) return rc__; } } while (0)
 
 static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing main-stream work that touches x / s
+    h->x_host = false;
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->stream));
     return EKF_OK;
 }
@@ -341,6 +345,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
+    if (h->x_pin) cudaFreeHost(h->x_pin);
     if (h->hflags) cudaFreeHost(h->hflags);
     if (h->am_obs_h) cudaFreeHost(h->am_obs_h);
     if (h->am_status) cudaFreeHost(h->am_status);
@@ -517,6 +522,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             }
         }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
+        CK(cudaMallocHost(&h->x_pin, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
         CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * (h->shadow ? EKF_MAX_WINDOW : EKF_MAX_PEND)));
         CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * (h->shadow ? EKF_MAX_WINDOW : EKF_MAX_PEND)));
@@ -743,6 +749,7 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         return EKF_OK;
     }
     CK(cudaSetDevice(h->p.device));
+    h->x_head_dirty = true;                  // predict moves x(1:3) only (EKF_SLAM.m:57-60)
     if (!h->xstep) FLUSH(h);                 // cross-step deferral keeps the terms pending and transforms them below
     else if (h->world > 1) { int32_t rcq = exec_sharded(h); if (rcq != EKF_OK) return rcq; }   // x must be final before the motion step
     if (h->async_x) {
@@ -869,6 +876,7 @@ static int32_t lazy_flush_and_batch(ekf_handle* h, const BatchObs& ob, ObSrc src
                           h->c_lo, std::min(h->c_hi, h->cap_n), m_old, h->Kd2, h->Bd2, 0, src);
     h->launches += 2;
     CK(cudaGetLastError());
+    h->x_host = false;
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->sg));      // x of the batch is final after the gain kernel on sg
     CK(cudaEventRecord(h->ev_g2, h->sg));
     CK(cudaStreamWaitEvent(h->stream, h->ev_g2, 0));           // later main-stream work sees x and the new terms
@@ -1043,7 +1051,13 @@ static int32_t shadow_close(ekf_handle* h) {
     if (h->prof) { int32_t rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->sf)); }
     double* src = h->nfl == 0 ? h->P : h->P2;
     double* dst = h->nfl == 0 ? h->P2 : h->P;
-    launch_downdate(h->sf, src, h->ld, n_of(h), n_of(h), 1, h->Kf[slot], h->Bf[slot], h->ld, m, 0, h->dd_variant, h->Bt, dst);
+    // EKF_SHADOW_VARIANT: hybrid kernel shape of the overlapped pass.  Default = the library's (4-stage ring, 3 CTAs/SM).  The
+    // 2-CTA/SM shapes (33, 35, 38: as fast when alone) leave a third of every SM free for the chain's CTAs -- measured at 10k:
+    // end to end 23.6k -> 24.6k updates/s, but the pass itself slows from 0.563 to 0.603 ms beside them (resident 27.4k -> 26.2k).
+    static int sv = -2;
+    if (sv == -2) { const char* e = getenv("EKF_SHADOW_VARIANT"); sv = e ? atoi(e) : -1; }
+    launch_downdate(h->sf, src, h->ld, n_of(h), n_of(h), 1, h->Kf[slot], h->Bf[slot], h->ld, m, 0,
+                    h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? sv : -1), h->Bt, dst);
     if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->sf)); h->ev_used += 2; }
     CK(cudaEventRecord(h->ev_fd[slot], h->sf));
     CK(cudaGetLastError());
@@ -1603,7 +1617,10 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
         st = h->sx;
         CK(cudaStreamWaitEvent(st, h->ev_mx, 0));
     }
-    CK(cudaMemcpyAsync(x, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, st));
+    double* dst = h->x_pin ? h->x_pin : x;
+    const bool head_only = h->x_pin && h->x_host && h->world == 1;         // only predict has touched x since the last read
+    if (!head_only) CK(cudaMemcpyAsync(dst, h->x, sizeof(double) * n_of(h), cudaMemcpyDeviceToHost, st));
+    else if (h->x_head_dirty) CK(cudaMemcpyAsync(dst, h->x, sizeof(double) * 3, cudaMemcpyDeviceToHost, st));
     if (h->lazy && h->m_pend >= h->pend_cap) {
         // The caller is about to block on x while a full set of terms is pending: start its K3 pass now, so that it runs
         // during the host's turnaround instead of waiting (lazily) for the next batch.  A loop that never reads x keeps the
@@ -1612,6 +1629,9 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
         if (rcl != EKF_OK) return rcl;
     }
     CK(cudaStreamSynchronize(st));
+    if (h->x_pin) memcpy(x, h->x_pin, sizeof(double) * n_of(h));
+    h->x_host = h->x_pin != nullptr && h->world == 1;
+    h->x_head_dirty = false;
     return after_sync(h);
 }
 
@@ -1870,6 +1890,14 @@ extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, in
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
         h->dd_ms += ms;
+    }
+    if (getenv("EKF_PROFILE_GAPS") && h->ev_used >= 4) {       // debug aid: idle time between consecutive K3 passes
+        double gap = 0.0, gmax = 0.0; int ng = 0;
+        for (size_t i = 2; i + 1 < h->ev_used; i += 2) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, h->ev[i - 1], h->ev[i]) == cudaSuccess) { gap += ms; gmax = ms > gmax ? ms : gmax; ++ng; }
+        }
+        fprintf(stderr, "ekfslam_b200: %d K3 passes, mean gap between passes %.4f ms (max %.4f)\n", ng + 1, ng ? gap / ng : 0.0, gmax);
     }
     h->ev_used = 0;
     if (downdate_ms_total) *downdate_ms_total = h->dd_ms;

@@ -694,9 +694,7 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
     if (Pout && Pout != P) {
         // out of place (continuous flush): the hybrid kernels store straight from registers, so the destination is just
         // another pointer; any other kernel choice gets a copy of the matrix first and runs in place on it
-        static int force_copy = -1;
-        if (force_copy < 0) { const char* e = getenv("EKF_SHADOW_DEBUG"); force_copy = (e && (atoi(e) & 64)) ? 1 : 0; }
-        const bool hyb = !force_copy && ((variant == 30 || variant == 37) || (Bt != nullptr && ((variant >= 31 && variant <= 38) || (variant < 30 && m > 8 && variant != 13 && variant != 21))));
+        const bool hyb = (variant == 30 || variant == 37) || (Bt != nullptr && ((variant >= 31 && variant <= 38) || (variant < 30 && m > 8 && variant != 13 && variant != 21)));
         if (!hyb) {
             cudaMemcpyAsync(Pout, P, sizeof(double) * (size_t)ld * (size_t)ncols, cudaMemcpyDeviceToDevice, st);
             P = Pout;

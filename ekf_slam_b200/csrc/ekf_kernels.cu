@@ -337,14 +337,25 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
         }
     }
     if (pend) {
-        // same terms, same order as ldP_def element by element; this row's K_q(i,:), B_q(:,i) are loaded once per term
-        for (int q = 0; q < m0; ++q) {
-            const double2 ki = Kall[q * lds + i], bi = Ball[q * lds + i];
+        // same terms, same order as ldP_def element by element; this row's K_q(i,:), B_q(:,i) are loaded once per term,
+        // four terms ahead (beside a K3 pass that saturates HBM every dependent load costs microseconds)
+        for (int q0 = 0; q0 < m0; q0 += 4) {
+            double2 kq[4], bq[4];
 #pragma unroll
-            for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
-                if (s < ns) {
-                    pc[s] = own[s] ? rank2_sub(pc[s], ki, Bc[q][s]) : rank2_sub(pc[s], Kc[q][s], bi);
-                    if (!sym) pr[s] = rank2_sub(pr[s], Kc[q][s], bi);
+            for (int u = 0; u < 4; ++u)
+                if (q0 + u < m0) { kq[u] = Kall[(q0 + u) * lds + i]; bq[u] = Ball[(q0 + u) * lds + i]; }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (q0 + u < m0) {
+                    const int q = q0 + u;
+                    const double2 ki = kq[u], bi = bq[u];
+#pragma unroll
+                    for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
+                        if (s < ns) {
+                            pc[s] = own[s] ? rank2_sub(pc[s], ki, Bc[q][s]) : rank2_sub(pc[s], Kc[q][s], bi);
+                            if (!sym) pr[s] = rank2_sub(pr[s], Kc[q][s], bi);
+                        }
+                    }
                 }
             }
         }

@@ -426,6 +426,34 @@ def test_continuous_flush_matches_in_place_deferral(defer_m, monkeypatch):
     assert np.array_equal(runs[1][1], runs[1][1].T)
 
 
+@pytest.mark.parametrize('defer_m', [0, 8, 16])
+def test_x_read_back_after_predict_is_the_full_state(defer_m):
+    """ekf_get_x keeps the last x it returned in pinned memory and, when only predict has run since (it moves x(1:3),
+    EKF_SLAM.m:57-60), copies just the pose.  A filter whose x is read after EVERY call must return the bits of a twin
+    that reads x only after a measure (always a full copy), through updates, appends, property writes and double predicts."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    w = make_world(N=16, T=60, k=4, mode='nearest', seed=5)
+    a = E.EKF_SLAM_UC(capacity_landmarks=16, storage='sym', defer_m=defer_m)
+    b = E.EKF_SLAM_UC(capacity_landmarks=16, storage='sym', defer_m=defer_m)
+    for t in range(w.T):
+        a.predict(w.u[t]); xa = a.x
+        b.predict(w.u[t])
+        if t % 5 == 2:
+            a.predict(w.u[t]); xa2 = a.x; b.predict(w.u[t])
+            assert np.array_equal(xa2[3:], xa[3:])
+        if t == 30:
+            for f in (a, b):
+                v = f.x; v[1] -= 0.5; f.x = v
+            assert np.array_equal(a.x, b.x)
+        a.measure(None, w.u[t], w.stub(t)); b.measure(None, w.u[t], w.stub(t))
+        xa, xb = a.x, b.x
+        assert np.array_equal(xa, xb), t
+        assert np.array_equal(a.x, xa)                  # a second read with nothing in between
+    assert a.chosen == b.chosen and np.array_equal(a.P, b.P)
+    a.close(); b.close()
+
+
 @pytest.mark.parametrize('storage,defer_m', [('sym', 16), ('sym', 8), ('full', 8), ('full', 3)])
 def test_measure_decided_on_device_is_bit_identical_to_the_host_loop(storage, defer_m, monkeypatch):
     """ekf_measure_batch_async (EKF_SLAM_UC, signature association): rows whose signatures are all in the map are
