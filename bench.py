@@ -335,7 +335,7 @@ def measure_filter(E, L, dist, world, rank, local, stream, barrier, N, k, K, W, 
     dd_ms, dd_n, launches = f.profile_read()
     xch_ms, xch_n, xch_p2p = f.profile_exchange() if world > 1 else (0.0, 0, False)
     out.update(dd_ms=dd_ms, dd_n=dd_n, launches=launches, xch_ms=xch_ms, xch_n=xch_n, xch_p2p=xch_p2p,
-               dd_bytes=f.downdate_bytes(), slab=f.shard_info(), pend_cap=f.pend_cap())
+               dd_bytes=f.downdate_bytes(), slab=f.shard_info(), pend_cap=f.pend_cap(), continuous=f.flush_info()[0])
     if sustained_steps > 0:             # same loop, longer: what the rate settles at once the power cap has had time to act
         f.profile_enable(True)
         barrier()
@@ -489,9 +489,8 @@ def main():
     # batch of 8 (defer_m = 8), where K3 is a pure streaming kernel -- its HBM fraction is reported beside the main roofline
     streaming = None
     in_place = None
-    shadow_on = world == 1 and args.defer > 8 and args.storage == 'sym' and n >= int(os.environ.get('EKF_SHADOW_MIN_N', '8000')) \
-        and os.environ.get('EKF_SHADOW', '1') != '0' and os.environ.get('EKF_ASYNC_X', '1') != '0' and os.environ.get('EKF_LAZY_FLUSH', '0') == '0'
-    if shadow_on and not args.no_streaming_variant:
+    shadow_on = bool(m.get('continuous'))            # what the handle reports (ekf_flush_info)
+    if shadow_on and world == 1 and not args.no_streaming_variant:
         # the same workload with the K3 pass in place on the handle's stream (EKF_SHADOW=0): what the rank-32 kernel does when it
         # has the GPU to itself, beside the main roofline, which times it while the state chain runs next to it
         os.environ['EKF_SHADOW'] = '0'

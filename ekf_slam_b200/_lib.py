@@ -65,6 +65,7 @@ SIGNATURES = {
     'ekf_set_state_lowrank': [_H, _DP, _DP, C.c_int32, _DP, C.c_int32, _DP],
     'ekf_set_noise': [_H, C.c_double, _DP, C.c_double, C.c_double],
     'ekf_defer_info': [_H, _IP, _IP],
+    'ekf_flush_info': [_H, _IP, _IP],
     'ekf_flush': [_H],
     'ekf_sync': [_H],
     'ekf_last_error': [_H],

@@ -166,6 +166,9 @@ static int32_t fail(ekf_handle* h, int32_t code, const std::string& msg) {
 
 static int32_t flush(ekf_handle* h);
 static int32_t shadow_strip_ready(ekf_handle* h);
+static int32_t shadow_retire(ekf_handle* h);
+static int32_t shadow_close(ekf_handle* h);
+static int32_t shadow_settle(ekf_handle* h);
 static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src);
 static int32_t exec_sharded(ekf_handle* h);
 static int32_t downdate_sharded(ekf_handle* h);
@@ -462,13 +465,27 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             const char* sh = getenv("EKF_SHADOW");
             const char* ax = getenv("EKF_ASYNC_X");
             const char* lz = getenv("EKF_LAZY_FLUSH");
-            h->shadow = world == 1 && !in_process && h->xstep && p->storage == EKF_STORAGE_SYM &&
+            // On slabs the mode is built and tested but off unless EKF_SHADOW_SLABS=1: measured at 10k landmarks on 2 GPUs it is
+            // slower than the lazy flush (36.9k vs 39.1k updates/s) -- beside a pass that saturates HBM the exchange /
+            // linearise / gain chain of a batch takes ~0.2 ms instead of ~0.07 ms, more than the slab's pass (0.14 ms per step).
+            const char* ss = getenv("EKF_SHADOW_SLABS");
+            h->shadow = h->xstep && p->storage == EKF_STORAGE_SYM && (world == 1 || (ss && atoi(ss) != 0)) &&
                         !(sh && atoi(sh) == 0) && !(ax && atoi(ax) == 0) && !(lz && atoi(lz) != 0);
             if (h->shadow) {
                 size_t fr = 0, tot = 0;
                 CK(cudaMemGetInfo(&fr, &tot));
-                const size_t need = 2 * sizeof(double) * (size_t)h->ld * (size_t)h->cap_n + ((size_t)2 << 30);
-                if (fr < need) h->shadow = false;
+                if (world == 1) {
+                    const size_t need = 2 * sizeof(double) * (size_t)h->ld * (size_t)h->cap_n + ((size_t)2 << 30);
+                    if (fr < need) h->shadow = false;
+                } else {
+                    // slabs: every rank must take the same decision (x and the gains are replicated: the modes differ in
+                    // rounding), so it is made from numbers all ranks share: the largest slab (rank 0's) twice, plus
+                    // margin, within 60 % of the device's total memory.  10k landmarks: yes; 80k: no (stays with the lazy flush)
+                    int lo0 = 0, hi0 = 0;
+                    ekf_slab_range(p->capacity_landmarks, world, 0, p->storage, &lo0, &hi0);
+                    const double need = 2.0 * sizeof(double) * (double)h->ld * (double)(hi0 - lo0) + 4.0 * (double)((size_t)1 << 30);
+                    if (need > 0.6 * (double)tot) h->shadow = false;
+                }
             }
         }
         int pr_lo = 0, pr_hi = 0;
@@ -486,8 +503,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         ekf_slab_range(p->capacity_landmarks, world, rank, p->storage, &h->c_lo, &h->c_hi);
         CK(cudaMalloc(&h->P, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
         if (h->shadow) {
-            CK(cudaMalloc(&h->P2, sizeof(double) * h->ld * h->cap_n));
-            CK(cudaMemset(h->P2, 0, sizeof(double) * h->ld * h->cap_n));
+            CK(cudaMalloc(&h->P2, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
+            CK(cudaMemset(h->P2, 0, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
             CK(cudaMalloc(&h->strip, sizeof(double) * 4 * h->ld));
             CK(cudaMemset(h->strip, 0, sizeof(double) * 4 * h->ld));
             for (int i = 0; i < 2; ++i) {
@@ -496,8 +513,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
                 CK(cudaMemset(h->Kf[i], 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
                 CK(cudaMemset(h->Bf[i], 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
             }
-            CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS));
-            h->Pc_cur = h->Pc;
+            if (world == 1) { CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS)); h->Pc_cur = h->Pc; }
         }
         if (world > 1 && in_process) {       // peers are wired by ekf_create_multi once every sub-handle exists
             CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS * 2));
@@ -763,7 +779,7 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         if (shadow_on(h)) {                  // covariance half on the robot strip: P itself may be under a K3 pass
             int32_t rcs = shadow_strip_ready(h);
             if (rcs != EKF_OK) return rcs;
-            launch_predict_strip(h->stream, h->strip, h->xprev, n_of(h), u[0], u[1], h->p.C, h->Kd, h->Bd, h->ld, h->m_pend);
+            launch_predict_strip(h->stream, h->strip, h->xprev, h->c_lo, ncols_loc(h), u[0], u[1], h->p.C, h->Kd, h->Bd, h->ld, h->m_pend);
         } else if (h->world > 1)
             launch_predict_shard_P(h->stream, h->P, h->ld, h->c_lo, h->c_hi, h->xprev, n_of(h), u[0], u[1], h->p.C, sym_of(h),
                                    h->Kd, h->Bd, h->ld, h->xstep ? h->m_pend : 0);
@@ -830,7 +846,8 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n, int phase 
         if (phase != 2) {
             h->epoch += 1;
             const int64_t buf_off = (int64_t)(h->epoch & 1) * EKF_MAX_SLOTS * h->ld;
-            launch_scatter_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->peers, buf_off, sym, h->epoch, h->xticket);
+            launch_scatter_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->peers, buf_off, sym, h->epoch, h->xticket,
+                                h->strip_valid ? h->strip : nullptr);
             h->Pc_cur = h->Pc + buf_off;
             h->launches += 1;
         }
@@ -841,7 +858,7 @@ static int32_t exchange_cols(ekf_handle* h, const SlotSet& ss, int n, int phase 
         CK(cudaGetLastError());
     } else if (phase != 2) {
         h->Pc_cur = h->Pc;
-        launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld, sym);
+        launch_pack_cols(h->stream, h->P, h->ld, h->c_lo, h->c_hi, ss, n, h->Pc, h->ld, sym, h->strip_valid ? h->strip : nullptr);
         CK(cudaGetLastError());
         if (sym) {
             CKN(g_nccl.AllReduce(h->Pc, h->Pc, (size_t)ss.n * h->ld, ncclDouble, ncclSum, h->comm, h->stream));
@@ -895,6 +912,7 @@ static int32_t lazy_flush_and_batch(ekf_handle* h, const BatchObs& ob, ObSrc src
 // corrects them by the pending terms it already holds (k_batch_lin / k_batch_gain with m0), so the slab is streamed
 // once per pend_cap observations.
 static int32_t downdate_sharded(ekf_handle* h) {
+    if (h->shadow) return shadow_settle(h);
     if (h->m_pend == 0) return EKF_OK;
     const int ncl = ncols_loc(h);
     if (ncl > 0) {
@@ -919,7 +937,15 @@ static int32_t exec_send(ekf_handle* h) {
     const int k = (int)h->q.size();
     if (k == 0) return EKF_OK;
     h->lazy_now = h->lazy && h->m_pend > 0 && h->m_pend + k > h->pend_cap && k >= 2 && !getenv("EKF_SHARD_PEROBS");
-    if (h->m_pend + k > h->pend_cap && !h->lazy_now) {      // make room: one pass over the slab for everything pending
+    if (shadow_on(h)) {                                     // continuous flush on the slab: same state machine as fused_chunk
+        int32_t rc = shadow_strip_ready(h);
+        if (rc != EKF_OK) return rc;
+        if (h->mQ > 0 && (rc = shadow_retire(h)) != EKF_OK) return rc;
+        if (h->m_pend - h->mA + k > h->pend_cap) {
+            if ((rc = shadow_close(h)) != EKF_OK) return rc;
+            if (h->mQ > 0 && (rc = shadow_retire(h)) != EKF_OK) return rc;
+        }
+    } else if (h->m_pend + k > h->pend_cap && !h->lazy_now) {      // make room: one pass over the slab for everything pending
         int32_t rc = downdate_sharded(h);
         if (rc != EKF_OK) return rc;
     }
@@ -973,6 +999,10 @@ static int32_t exec_finish(ekf_handle* h) {
     MARK_X(h);                              // x of the batch is final here, before any slab flush
     h->q.clear();
     h->m_pend = m0 + k;
+    if (shadow_on(h)) {
+        if (h->m_pend - h->mA - h->mQ + std::min(h->defer, EKF_BATCH_MAX) > h->pend_cap) return shadow_close(h);
+        return EKF_OK;
+    }
     if (h->m_pend >= h->pend_cap && !h->lazy) return downdate_sharded(h);    // full: same flush points as the single-GPU path (bitwise equal)
     return EKF_OK;
 }
@@ -1013,7 +1043,7 @@ static int32_t prof_slot(ekf_handle* h) {
 }
 static int32_t shadow_strip_ready(ekf_handle* h) {
     if (h->strip_valid) return EKF_OK;
-    launch_strip_load(h->stream, h->P, h->ld, n_of(h), h->strip);
+    launch_strip_load(h->stream, h->P, h->ld, h->c_lo, ncols_loc(h), h->strip);
     h->launches += 1;
     CK(cudaGetLastError());
     h->strip_valid = true;
@@ -1024,7 +1054,7 @@ static int32_t shadow_strip_ready(ekf_handle* h) {
 static int32_t shadow_retire(ekf_handle* h) {
     if (h->nfl == 0) return EKF_OK;
     CK(cudaStreamWaitEvent(h->stream, h->ev_fd[h->fcur], 0));
-    launch_strip_fix(h->stream, h->strip, n_of(h), h->Kd, h->Bd, h->ld, h->mA);
+    launch_strip_fix(h->stream, h->strip, h->c_lo, ncols_loc(h), h->Kd, h->Bd, h->ld, h->mA);
     std::swap(h->P, h->P2);
     launch_rotate_slabs(h->stream, h->Kd, h->Bd, h->ld, n_of(h), h->mA, h->m_pend - h->mA, nullptr, nullptr);
     h->launches += 2;
@@ -1051,13 +1081,15 @@ static int32_t shadow_close(ekf_handle* h) {
     if (h->prof) { int32_t rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->sf)); }
     double* src = h->nfl == 0 ? h->P : h->P2;
     double* dst = h->nfl == 0 ? h->P2 : h->P;
+    const int ncl = ncols_loc(h);                 // a slab passes its own columns (and B_q from its first column on)
     // EKF_SHADOW_VARIANT: hybrid kernel shape of the overlapped pass.  Default = the library's (4-stage ring, 3 CTAs/SM).  The
     // 2-CTA/SM shapes (33, 35, 38: as fast when alone) leave a third of every SM free for the chain's CTAs -- measured at 10k:
     // end to end 23.6k -> 24.6k updates/s, but the pass itself slows from 0.563 to 0.603 ms beside them (resident 27.4k -> 26.2k).
     static int sv = -2;
     if (sv == -2) { const char* e = getenv("EKF_SHADOW_VARIANT"); sv = e ? atoi(e) : -1; }
-    launch_downdate(h->sf, src, h->ld, n_of(h), n_of(h), 1, h->Kf[slot], h->Bf[slot], h->ld, m, 0,
-                    h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? sv : -1), h->Bt, dst);
+    if (ncl > 0)
+        launch_downdate(h->sf, src, h->ld, n_of(h), ncl, 1, h->Kf[slot], h->Bf[slot] + h->c_lo, h->ld, m, h->c_lo,
+                        h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? sv : -1), h->Bt, dst);
     if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->sf)); h->ev_used += 2; }
     CK(cudaEventRecord(h->ev_fd[slot], h->sf));
     CK(cudaGetLastError());
@@ -1079,31 +1111,36 @@ static int32_t shadow_reset(ekf_handle* h) {
     return EKF_OK;
 }
 
-static int32_t flush(ekf_handle* h) {
-    if (is_front(h)) return front_flush(h);
-    if (h->world > 1) return flush_sharded(h);
-    if (h->shadow) {
-        // P must be whole: retire the pass in flight, apply what is left of the window in place, put the strip back
-        int32_t rc = EKF_OK;
-        while (h->nfl > 0) if ((rc = shadow_retire(h)) != EKF_OK) return rc;
-        if (h->m_pend > 0) {
+// P (the local slab) must be whole: retire the passes in flight, apply what is left of the window in place, put the strip back.
+static int32_t shadow_settle(ekf_handle* h) {
+    int32_t rc = EKF_OK;
+    while (h->nfl > 0) if ((rc = shadow_retire(h)) != EKF_OK) return rc;
+    const int ncl = ncols_loc(h);
+    if (h->m_pend > 0) {
+        if (ncl > 0) {
             if (h->prof) { rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->stream)); }
-            launch_downdate(h->stream, h->P, h->ld, n_of(h), n_of(h), 1, h->Kd, h->Bd, h->ld, h->m_pend, 0, h->dd_variant, h->Bt);
+            launch_downdate(h->stream, h->P, h->ld, n_of(h), ncl, 1, h->Kd, h->Bd + h->c_lo, h->ld, h->m_pend, h->c_lo, h->dd_variant, h->Bt);
             if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->stream)); h->ev_used += 2; }
-            if (h->strip_valid) launch_strip_fix(h->stream, h->strip, n_of(h), h->Kd, h->Bd, h->ld, h->m_pend);
+            if (h->strip_valid) launch_strip_fix(h->stream, h->strip, h->c_lo, ncl, h->Kd, h->Bd, h->ld, h->m_pend);
             h->dd_launches += 1;
             h->dd_terms += h->m_pend;
             h->launches += 2;
-            h->m_pend = 0;
         }
-        if (h->strip_valid) {
-            launch_strip_store(h->stream, h->P, h->ld, n_of(h), h->strip);
-            h->launches += 1;
-            h->strip_valid = false;
-        }
-        CK(cudaGetLastError());
-        return EKF_OK;
+        h->m_pend = 0;
     }
+    if (h->strip_valid) {
+        launch_strip_store(h->stream, h->P, h->ld, h->c_lo, ncl, h->strip);
+        h->launches += 1;
+        h->strip_valid = false;
+    }
+    CK(cudaGetLastError());
+    return EKF_OK;
+}
+
+static int32_t flush(ekf_handle* h) {
+    if (is_front(h)) return front_flush(h);
+    if (h->world > 1) return flush_sharded(h);
+    if (h->shadow) return shadow_settle(h);
     if (h->m_pend == 0) return EKF_OK;
     if (h->prof) {
         if (h->ev_used + 2 > h->ev.size()) {
@@ -1123,6 +1160,14 @@ static int32_t flush(ekf_handle* h) {
     h->launches += 1;
     h->m_pend = 0;
     CK(cudaGetLastError());
+    return EKF_OK;
+}
+
+extern "C" int32_t ekf_flush_info(ekf_handle* h, int32_t* continuous, int32_t* passes_outstanding) {
+    CKH(h);
+    const ekf_handle* q = is_front(h) ? h->subs[0] : h;
+    if (continuous) *continuous = shadow_on(q) ? 1 : 0;
+    if (passes_outstanding) *passes_outstanding = q->nfl;
     return EKF_OK;
 }
 

@@ -417,24 +417,29 @@ void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int
 // the gather of a batch's slot columns takes every element with a row or column index < 3 from it, and when a pass
 // retires the strip catches up with it (k_strip_fix: S <- S - sum_q K_q B_q over the retired terms, which the
 // predicts since have transformed together with the strip).  k_strip_store writes it back when P must be whole.
-__global__ void k_strip_load(const double* __restrict__ P, int64_t ld, int n, double* __restrict__ S) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+// All strip kernels take a column range: the whole matrix on one GPU (c_lo = 0, ncols = n), the local columns [c_lo, c_lo + ncols)
+// of a slab otherwise (P = local slab, S[4 t + r] = P0(r, c_lo + t)); the 3 x 3 corner lives on the rank with c_lo = 0.
+__global__ void k_strip_load(const double* __restrict__ P, int64_t ld, int c_lo, int ncols, double* __restrict__ S) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ncols) return;
+    const int j = c_lo + t;
 #pragma unroll
-    for (int r = 0; r < 3; ++r) S[4 * (int64_t)j + r] = ldP(P, ld, r, j, 1);
-    S[4 * (int64_t)j + 3] = 0.0;
+    for (int r = 0; r < 3; ++r) S[4 * (int64_t)t + r] = r <= j ? P[(int64_t)r + (int64_t)t * ld] : P[(int64_t)j + (int64_t)r * ld];   // r > j only in the corner (c_lo = 0)
+    S[4 * (int64_t)t + 3] = 0.0;
 }
 
-__global__ void k_strip_store(double* __restrict__ P, int64_t ld, int n, const double* __restrict__ S) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+__global__ void k_strip_store(double* __restrict__ P, int64_t ld, int c_lo, int ncols, const double* __restrict__ S) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ncols) return;
+    const int j = c_lo + t;
 #pragma unroll
     for (int r = 0; r < 3; ++r)
-        if (r <= j) P[(int64_t)r + (int64_t)j * ld] = S[4 * (int64_t)j + r];
+        if (r <= j) P[(int64_t)r + (int64_t)t * ld] = S[4 * (int64_t)t + r];
 }
 
-// k_predict_P on the strip (same expressions), plus the pending window's K_q <- F K_q, B_q <- B_q F' in an extra block.
-__global__ void k_predict_strip(double* __restrict__ S, const double* __restrict__ x, int n, double u1, double u2, double C,
+// k_predict_P / k_predict_shard on the strip (same expressions), plus the pending window's K_q <- F K_q, B_q <- B_q F' in an
+// extra block (every rank transforms its own replica of the slabs).
+__global__ void k_predict_strip(double* __restrict__ S, const double* __restrict__ x, int c_lo, int ncols, double u1, double u2, double C,
                                 double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds, int m) {
     const double th = x[2];
     const double st = sind(th), ct = cosd(th);
@@ -451,13 +456,14 @@ __global__ void k_predict_strip(double* __restrict__ S, const double* __restrict
         return;
     }
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t == 0) {
+    const int j = c_lo + t;
+    if (t == 0 && c_lo == 0) {
         double M[3][3];
         for (int i = 0; i < 3; ++i)
-            for (int j = 0; j < 3; ++j) M[i][j] = S[4 * (i > j ? i : j) + (i > j ? j : i)];      // the live (min, max) entry, like ldP
-        for (int j = 0; j < 3; ++j) {     // F*P
-            M[0][j] = M[0][j] + a * M[2][j];
-            M[1][j] = M[1][j] + b * M[2][j];
+            for (int jj = 0; jj < 3; ++jj) M[i][jj] = S[4 * (i > jj ? i : jj) + (i > jj ? jj : i)];      // the live (min, max) entry, like ldP
+        for (int jj = 0; jj < 3; ++jj) {     // F*P
+            M[0][jj] = M[0][jj] + a * M[2][jj];
+            M[1][jj] = M[1][jj] + b * M[2][jj];
         }
         for (int i = 0; i < 3; ++i) {     // (F*P)*F'
             M[i][0] = M[i][0] + M[i][2] * a;
@@ -465,8 +471,8 @@ __global__ void k_predict_strip(double* __restrict__ S, const double* __restrict
         }
         double W[3] = {u1 * ct, u1 * st, u2};      // EKF_SLAM.m:42
         for (int i = 0; i < 3; ++i)
-            for (int j = 0; j < 3; ++j) S[4 * j + i] = M[i][j] + (W[i] * C) * W[j];   // :44,47
-    } else if (t >= 3 && t < n) {
+            for (int jj = 0; jj < 3; ++jj) S[4 * jj + i] = M[i][jj] + (W[i] * C) * W[jj];   // :44,47
+    } else if (j >= 3 && t < ncols) {
         double* col = S + 4 * (int64_t)t;
         const double p2 = col[2];
         col[0] = col[0] + a * p2;
@@ -474,36 +480,51 @@ __global__ void k_predict_strip(double* __restrict__ S, const double* __restrict
     }
 }
 
-// The m retired terms leave the strip: S(r, j) <- S(r, j) - sum_q K_q(min) B_q(max), in ldP_def's order.
-__global__ void k_strip_fix(double* __restrict__ S, int n, const double2* __restrict__ Kall, const double2* __restrict__ Ball,
+// The m retired terms leave the strip: S(r, j) <- S(r, j) - sum_q K_q(min) B_q(max), in ldP_def's order (K, B: all rows, global index).
+__global__ void k_strip_fix(double* __restrict__ S, int c_lo, int ncols, const double2* __restrict__ Kall, const double2* __restrict__ Ball,
                             int64_t lds, int m) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in = t < ncols;
+    const int j = c_lo + t;
     double v[3];
     int lo[3], hi[3];
 #pragma unroll
-    for (int r = 0; r < 3; ++r) { lo[r] = r < j ? r : j; hi[r] = r < j ? j : r; v[r] = S[4 * (int64_t)hi[r] + lo[r]]; }
+    for (int r = 0; r < 3; ++r) {
+        lo[r] = r < j ? r : j; hi[r] = r < j ? j : r;
+        v[r] = in ? S[4 * (int64_t)(hi[r] - c_lo) + lo[r]] : 0.0;     // hi != j only in the corner, where c_lo = 0
+    }
     __syncthreads();                      // corner: every thread of block 0 has read before any of them writes a mirror entry
+    if (!in) return;
     for (int q = 0; q < m; ++q) {
 #pragma unroll
         for (int r = 0; r < 3; ++r) v[r] = rank2_sub(v[r], Kall[q * lds + lo[r]], Ball[q * lds + hi[r]]);
     }
 #pragma unroll
-    for (int r = 0; r < 3; ++r) S[4 * (int64_t)j + r] = v[r];
+    for (int r = 0; r < 3; ++r) S[4 * (int64_t)t + r] = v[r];
 }
 
-// k_gather_cols with the strip in charge of rows / columns 0..2.
+// k_gather_cols with the strip in charge of rows / columns 0..2.  One thread = one row of ALL slot columns (<= 19 independent
+// loads): the grid is n / 256 CTAs instead of 19 n / 256 -- beside a K3 pass that fills every SM a CTA can only start when a
+// pass CTA retires, so the number of CTAs, not the work, sets this kernel's latency.
 __global__ void k_gather_cols_strip(const double* __restrict__ P, int64_t ld, int n, const BatchObs ob_arg,
                                     double* __restrict__ Pc, int64_t ldc, ObSrc src, const double* __restrict__ S) {
     __shared__ BatchObs ob;
     stage_batch_obs(ob, ob_arg, src.ob);
-    const int slot = blockIdx.y;
-    if (slot >= 3 + 2 * ob.k) return;
-    const int c = slot < 3 ? slot : ob.a[(slot - 3) >> 1] + ((slot - 3) & 1);
+    const int ns = 3 + 2 * ob.k;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int lo = i < c ? i : c, hi = i < c ? c : i;
-    Pc[(int64_t)slot * ldc + i] = lo < 3 ? S[4 * (int64_t)hi + lo] : P[(int64_t)lo + (int64_t)hi * ld];
+    double v[EKF_BATCH_SLOTS];
+#pragma unroll
+    for (int slot = 0; slot < EKF_BATCH_SLOTS; ++slot) {
+        if (slot < ns) {
+            const int c = slot < 3 ? slot : ob.a[(slot - 3) >> 1] + ((slot - 3) & 1);
+            const int lo = i < c ? i : c, hi = i < c ? c : i;
+            v[slot] = lo < 3 ? S[4 * (int64_t)hi + lo] : P[(int64_t)lo + (int64_t)hi * ld];
+        }
+    }
+#pragma unroll
+    for (int slot = 0; slot < EKF_BATCH_SLOTS; ++slot)
+        if (slot < ns) Pc[(int64_t)slot * ldc + i] = v[slot];
 }
 
 // Window bookkeeping: terms [mA, mA + mB) move to the front of the window (the mA retired ones drop out) and, when Kf is
@@ -519,19 +540,23 @@ __global__ void k_rotate_slabs(double2* __restrict__ Kall, double2* __restrict__
     }
 }
 
-void launch_strip_load(cudaStream_t st, const double* P, int64_t ld, int n, double* S) { k_strip_load<<<(n + 255) / 256, 256, 0, st>>>(P, ld, n, S); }
-void launch_strip_store(cudaStream_t st, double* P, int64_t ld, int n, const double* S) { k_strip_store<<<(n + 255) / 256, 256, 0, st>>>(P, ld, n, S); }
-void launch_predict_strip(cudaStream_t st, double* S, const double* xprev, int n, double u1, double u2, double C,
-                          double2* Kall, double2* Ball, int64_t lds, int m) {
-    k_predict_strip<<<(n + 255) / 256 + (m > 0 ? 1 : 0), 256, 0, st>>>(S, xprev, n, u1, u2, C, Kall, Ball, lds, m);
+void launch_strip_load(cudaStream_t st, const double* P, int64_t ld, int c_lo, int ncols, double* S) {
+    if (ncols > 0) k_strip_load<<<(ncols + 255) / 256, 256, 0, st>>>(P, ld, c_lo, ncols, S);
 }
-void launch_strip_fix(cudaStream_t st, double* S, int n, const double2* Kall, const double2* Ball, int64_t lds, int m) {
-    if (m > 0) k_strip_fix<<<(n + 255) / 256, 256, 0, st>>>(S, n, Kall, Ball, lds, m);
+void launch_strip_store(cudaStream_t st, double* P, int64_t ld, int c_lo, int ncols, const double* S) {
+    if (ncols > 0) k_strip_store<<<(ncols + 255) / 256, 256, 0, st>>>(P, ld, c_lo, ncols, S);
+}
+void launch_predict_strip(cudaStream_t st, double* S, const double* xprev, int c_lo, int ncols, double u1, double u2, double C,
+                          double2* Kall, double2* Ball, int64_t lds, int m) {
+    const int nb = (ncols + 255) / 256 + (m > 0 ? 1 : 0);
+    if (nb > 0) k_predict_strip<<<nb, 256, 0, st>>>(S, xprev, c_lo, ncols, u1, u2, C, Kall, Ball, lds, m);
+}
+void launch_strip_fix(cudaStream_t st, double* S, int c_lo, int ncols, const double2* Kall, const double2* Ball, int64_t lds, int m) {
+    if (m > 0 && ncols > 0) k_strip_fix<<<(ncols + 255) / 256, 256, 0, st>>>(S, c_lo, ncols, Kall, Ball, lds, m);
 }
 void launch_gather_cols_strip(cudaStream_t st, const double* P, int64_t ld, int n, const BatchObs& ob, double* Pc, int64_t ldc,
                               ObSrc src, const double* S) {
-    dim3 grid((n + 255) / 256, 3 + 2 * ob.k);
-    k_gather_cols_strip<<<grid, 256, 0, st>>>(P, ld, n, ob, Pc, ldc, src, S);
+    k_gather_cols_strip<<<(n + 255) / 256, 256, 0, st>>>(P, ld, n, ob, Pc, ldc, src, S);
 }
 void launch_rotate_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int rows, int mA, int mB, double2* Kf,
                          double2* Bf) {

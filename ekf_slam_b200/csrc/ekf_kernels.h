@@ -36,11 +36,11 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
 void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc,
                         ObSrc src = ObSrc{nullptr, nullptr});
 // ---- continuous flush ("shadow", single GPU, SYM storage): robot strip S[4 j + r] = P0(r, j), r < 3; see ekf_kernels.cu ----
-void launch_strip_load(cudaStream_t st, const double* P, int64_t ld, int n, double* S);
-void launch_strip_store(cudaStream_t st, double* P, int64_t ld, int n, const double* S);
-void launch_predict_strip(cudaStream_t st, double* S, const double* xprev, int n, double u1, double u2, double C,
+void launch_strip_load(cudaStream_t st, const double* P, int64_t ld, int c_lo, int ncols, double* S);       // column range: (0, n) on one GPU,
+void launch_strip_store(cudaStream_t st, double* P, int64_t ld, int c_lo, int ncols, const double* S);      // the local columns of a slab otherwise
+void launch_predict_strip(cudaStream_t st, double* S, const double* xprev, int c_lo, int ncols, double u1, double u2, double C,
                           double2* Kall, double2* Ball, int64_t lds, int m);
-void launch_strip_fix(cudaStream_t st, double* S, int n, const double2* Kall, const double2* Ball, int64_t lds, int m);
+void launch_strip_fix(cudaStream_t st, double* S, int c_lo, int ncols, const double2* Kall, const double2* Ball, int64_t lds, int m);
 void launch_gather_cols_strip(cudaStream_t st, const double* P, int64_t ld, int n, const BatchObs& ob, double* Pc, int64_t ldc,
                               ObSrc src, const double* S);
 void launch_rotate_slabs(cudaStream_t st, double2* Kall, double2* Ball, int64_t lds, int rows, int mA, int mB, double2* Kf,
@@ -77,11 +77,12 @@ void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xpre
 #define EKF_XF_INTS 256
 struct PeerSet { double* pc[EKF_MAX_PEERS]; int* flags[EKF_MAX_PEERS]; int world, rank; };   // cudaIpc-mapped Pc buffers / flag words of every rank
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket);
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket,
+                         const double* strip = nullptr);     // strip (continuous flush): rows 0..2 of the local columns come from it
 // wait (bounded) until every rank has published `epoch`; err_word: mapped host memory, set to 1 when a peer does not answer in time
 void launch_wait_flags(cudaStream_t st, const int* flags, int world, int epoch, long long timeout_cycles, int* err_word);
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                      double* Pc, int64_t ldc, int sym);
+                      double* Pc, int64_t ldc, int sym, const double* strip = nullptr);
 void launch_lin_gain_shard(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, double* x, int n, int a,
                            int sa, double z0, double z1, double R0, double R1, const SlotSet& ss, const double* Pc,
                            int64_t ldc, Lin* lin, double2* Kall, double2* Ball, int64_t lds, double2* Bc, int m, int sym);

@@ -32,15 +32,16 @@ __device__ __forceinline__ double cur_col(const double* __restrict__ Pc, int64_t
 
 // SYM slabs: every rank writes the part of each symmetric column it holds (zeros elsewhere); an all-reduce(sum)
 // then assembles the columns exactly (each element has one non-zero contributor).
+// S (continuous flush, may be null): strip of the local columns, S[4 t + r] = P0(r, c_lo + t) -- in charge of rows 0..2.
 __global__ void k_pack_cols_sym(const double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, SlotSet ss, int n,
-                                double* __restrict__ Pc, int64_t ldc) {
+                                double* __restrict__ Pc, int64_t ldc, const double* __restrict__ S) {
     const int slot = blockIdx.y;
     const int c = ss.col[slot];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double v = 0.0;
-    if (i <= c) { if (c >= c_lo && c < c_hi) v = Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld]; }
-    else if (i >= c_lo && i < c_hi) v = Ploc[(int64_t)c + (int64_t)(i - c_lo) * ld];
+    if (i <= c) { if (c >= c_lo && c < c_hi) v = (S && i < 3) ? S[4 * (int64_t)(c - c_lo) + i] : Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld]; }
+    else if (i >= c_lo && i < c_hi) v = (S && c < 3) ? S[4 * (int64_t)(i - c_lo) + c] : Ploc[(int64_t)c + (int64_t)(i - c_lo) * ld];
     Pc[(int64_t)slot * ldc + i] = v;
 }
 
@@ -70,18 +71,26 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
     return v;
 }
 
+// One thread = one row of all slot columns (grid n / 256 CTAs: see k_gather_cols_strip for why the CTA count matters).
 __global__ void k_scatter_cols(const double* __restrict__ Ploc, int64_t ld, int c_lo, int c_hi, SlotSet ss, int n,
-                               PeerSet ps, int64_t buf_off, int sym, int epoch, unsigned int* __restrict__ ticket) {
-    const int slot = blockIdx.y;
-    const int c = ss.col[slot];
+                               PeerSet ps, int64_t buf_off, int sym, int epoch, unsigned int* __restrict__ ticket,
+                               const double* __restrict__ S) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
-        bool have = false;
-        double v = 0.0;
-        if (!sym || i <= c) { if (c >= c_lo && c < c_hi) { v = Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld]; have = true; } }
-        else if (i >= c_lo && i < c_hi) { v = Ploc[(int64_t)c + (int64_t)(i - c_lo) * ld]; have = true; }   // (c, i) lives in column i
-        if (have)
-            for (int g = 0; g < ps.world; ++g) ps.pc[g][buf_off + (int64_t)slot * ld + i] = v;
+        double v[EKF_MAX_SLOTS];
+        unsigned int have = 0u;
+#pragma unroll
+        for (int slot = 0; slot < EKF_MAX_SLOTS; ++slot) {
+            if (slot < ss.n) {
+                const int c = ss.col[slot];
+                if (!sym || i <= c) { if (c >= c_lo && c < c_hi) { v[slot] = (S && i < 3) ? S[4 * (int64_t)(c - c_lo) + i] : Ploc[(int64_t)i + (int64_t)(c - c_lo) * ld]; have |= 1u << slot; } }
+                else if (i >= c_lo && i < c_hi) { v[slot] = (S && c < 3) ? S[4 * (int64_t)(i - c_lo) + c] : Ploc[(int64_t)c + (int64_t)(i - c_lo) * ld]; have |= 1u << slot; }   // (c, i) lives in column i
+            }
+        }
+#pragma unroll
+        for (int slot = 0; slot < EKF_MAX_SLOTS; ++slot)
+            if (have & (1u << slot))
+                for (int g = 0; g < ps.world; ++g) ps.pc[g][buf_off + (int64_t)slot * ld + i] = v[slot];
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -109,9 +118,8 @@ __global__ void k_wait_flags(const int* __restrict__ flags, int world, int epoch
 }
 
 void launch_scatter_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket) {
-    dim3 grid((n + 255) / 256, ss.n);
-    k_scatter_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, ps, buf_off, sym, epoch, ticket);
+                         const PeerSet& ps, int64_t buf_off, int sym, int epoch, unsigned int* ticket, const double* strip) {
+    k_scatter_cols<<<(n + 255) / 256, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, ps, buf_off, sym, epoch, ticket, strip);
 }
 
 void launch_wait_flags(cudaStream_t st, const int* flags, int world, int epoch, long long timeout_cycles, int* err_word) {
@@ -304,9 +312,9 @@ __global__ void k_append_shard(double* __restrict__ Ploc, int64_t ld, int c_lo, 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
 void launch_pack_cols(cudaStream_t st, const double* Ploc, int64_t ld, int c_lo, int c_hi, const SlotSet& ss, int n,
-                      double* Pc, int64_t ldc, int sym) {
+                      double* Pc, int64_t ldc, int sym, const double* strip) {
     dim3 grid(cdiv(n, 256), ss.n);
-    if (sym) k_pack_cols_sym<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, Pc, ldc);
+    if (sym) k_pack_cols_sym<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, Pc, ldc, strip);
     else k_pack_cols<<<grid, 256, 0, st>>>(Ploc, ld, c_lo, c_hi, ss, n, Pc, ldc);
 }
 

@@ -283,6 +283,12 @@ class _FilterBase:
     def flush(self):
         self._ck(self._lib.ekf_flush(self._h))
 
+    def flush_info(self):
+        """(continuous flush in use at the current size, K3 passes outstanding on its stream)."""
+        a, b = ct.c_int32(), ct.c_int32()
+        self._ck(self._lib.ekf_flush_info(self._h, ct.byref(a), ct.byref(b)))
+        return bool(a.value), b.value
+
     def pend_cap(self):
         """Rank-2 terms that may be pending before a pass over P is forced (what defer_m became on this handle)."""
         b, c = ct.c_int32(), ct.c_int32()

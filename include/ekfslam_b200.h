@@ -190,6 +190,11 @@ int32_t ekf_set_noise(ekf_handle* h, double C, const double Rc[2], double s_cost
 /* What the handle does with defer_m: *batch = observations linearised per fused batch (<= 8), *pend_cap = rank-2 terms
  * that may be pending before a pass over P is forced (> 8: cross-step deferral is on). */
 int32_t ekf_defer_info(ekf_handle* h, int32_t* batch, int32_t* pend_cap);
+/* Whether the handle runs the continuous flush at its current size (the K3 pass of a full set of terms out of place on a
+ * stream of its own, beside predict and the next batches: SYM storage, defer_m = 9..16, n >= EKF_SHADOW_MIN_N (8000), room for
+ * a second copy of P / of the largest slab; EKF_SHADOW=0 disables), and how many passes are outstanding on that stream right
+ * now (0..2).  No counterpart in the reference (its P = (I - K H) P is one dense statement, EKF_SLAM.m:145); bench.py prints it. */
+int32_t ekf_flush_info(ekf_handle* h, int32_t* continuous, int32_t* passes_outstanding);
 /* Apply any deferred (defer_m > 1) rank-2 terms to P now.  predict, append, getters of P and the end of
  * ekf_measure_batch flush implicitly; ekf_update flushes when defer_m terms are pending.  With defer_m = 9..16 predict and
  * the end of ekf_measure_batch / ekf_update_batch do NOT flush (append, mode-B association and the getters of P still do). */

@@ -38,10 +38,12 @@ def main():
         # of P against the matrix-free oracle; 1e-9 relative
         from bench import make_inputs
         from oracle.lowrank_lazy import LazyLowRankFilter
-        N, k, T = int(os.environ.get('SHARD_LANDMARKS', '80000')), 8, 2
+        N, k, T = int(os.environ.get('SHARD_LANDMARKS', '80000')), 8, int(os.environ.get('SHARD_STEPS', '2'))
         x, A, d, s, lms, us, obs = make_inputs(N, k, T)
-        g = E.shard.create_sharded(E.EKF_SLAM_UC, dist, local, storage='sym', capacity_landmarks=N, defer_m=8)
+        g = E.shard.create_sharded(E.EKF_SLAM_UC, dist, local, storage='sym', capacity_landmarks=N, defer_m=int(os.environ.get('SHARD_DEFER', '8')))
         g.set_state_lowrank(x, s, A, d)
+        if os.environ.get('EKF_SHADOW_SLABS') == '1':
+            assert g.flush_info()[0], 'continuous flush not active on this slab'
         o = LazyLowRankFilter(x, A, d, s, Rc=g.Rc)
         for t in range(T):
             g.predict(us[t]); o.predict(us[t])
@@ -158,6 +160,57 @@ def main():
     assert ex <= 1e-9 and eP <= 1e-9, (rank, ex, eP)
     print('rank %d UC loop sym defer 16: rel err x %.2e P %.2e' % (rank, ex, eP), flush=True)
     g.close()
+    # (c2) continuous flush on SYM slabs (the K3 pass of every slab out of place on its own stream, robot strip, window of
+    # pending terms; forced at this size): same estimator as the single-GPU continuous flush -- x at checkpoints and the slab
+    # to 1e-12 -- with ragged batches, a single update, x / slab reads mid-run (which settle), and the UC loop with appends
+    # and associations against the oracle
+    os.environ['EKF_SHADOW_MIN_N'] = '0'
+    os.environ['EKF_SHADOW_SLABS'] = '1'          # off by default on slabs (slower than the lazy flush at 10k landmarks)
+    N = 1000
+    x, A, d, s, lms = synthetic_spd_state(N, seed=3)
+    g = E.shard.create_sharded(E.EKF_SLAM, dist, local, storage='sym', capacity_landmarks=N, defer_m=16)
+    ref = E.EKF_SLAM(capacity_landmarks=N, storage='sym', device=local, defer_m=16)
+    for f in (g, ref):
+        f.set_state_lowrank(x, s, A, d)
+    rng = np.random.default_rng(12)
+    sizes = (8, 11, 5, 8, 1, 8, 8, 3, 8, 16, 8, 8)
+    for step in range(36):
+        rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:sizes[step % len(sizes)]]
+        Rd = np.column_stack([rows[:, 0] * 0.01, rows[:, 1] * 5.0])
+        for f in (g, ref):
+            f.predict([0.3, 1.0])
+            if step % 12 == 4:
+                f.update(rows[0, :2], Rd[0], int(rows[0, 2]))
+            else:
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+        if step % 3 == 1:
+            assert rel(g.x, ref.x) <= 1e-12, (step, rel(g.x, ref.x))
+        if step == 17:
+            slab, c_lo = g.P_slab()
+            mk = live(slab, c_lo, 'sym')
+            e17 = rel(slab * mk, ref.P[:, c_lo:c_lo + slab.shape[1]] * mk)
+            assert e17 <= 1e-12, (rank, e17)
+    slab, c_lo = g.P_slab()
+    mk = live(slab, c_lo, 'sym')
+    eP = rel(slab * mk, ref.P[:, c_lo:c_lo + slab.shape[1]] * mk)
+    assert rel(g.x, ref.x) <= 1e-12 and eP <= 1e-12, (rank, rel(g.x, ref.x), eP)
+    print('rank %d continuous flush on slabs vs single GPU: rel err x %.2e slab %.2e' % (rank, rel(g.x, ref.x), eP), flush=True)
+    g.close(); ref.close()
+    w = make_world(N=20, T=300, k=5, mode='nearest')
+    g = E.shard.create_sharded(E.EKF_SLAM_UC, dist, local, storage='sym', capacity_landmarks=20, defer_m=16)
+    o = O.EKF_SLAM_UC()
+    for t in range(w.T):
+        g.predict(w.u[t]); g.measure(None, w.u[t], w.stub(t))
+        o.predict(w.u[t]); o.measure(None, w.u[t], w.stub(t))
+    assert g.chosen == o.chosen
+    slab, c_lo = g.P_slab()
+    mk = live(slab, c_lo, 'sym')
+    ex, eP = rel(g.x, o.x), rel(slab * mk, o.P[:, c_lo:c_lo + slab.shape[1]] * mk)
+    assert ex <= 1e-9 and eP <= 1e-9, (rank, ex, eP)
+    print('rank %d UC loop, continuous flush on slabs: rel err x %.2e P %.2e' % (rank, ex, eP), flush=True)
+    g.close()
+    del os.environ['EKF_SHADOW_MIN_N']
+    del os.environ['EKF_SHADOW_SLABS']
     # (d) association mode B (Correspondence.m:74: Mahalanobis + signature) on slabs: every rank scores its own landmarks,
     # 16-byte candidates cross NVLink; indices identical to the single-GPU kernel and to oracle/structured.c, incl. a
     # duplicated landmark whose twin lives on another rank (tie -> first index) and a one-ulp twin

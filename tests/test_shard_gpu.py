@@ -40,3 +40,19 @@ def test_80k_landmarks_rows_vs_matrix_free_oracle(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
     print(r.stdout[-4000:]); print(r.stderr[-4000:])
     assert r.returncode == 0 and 'SHARD_WORKER_OK' in r.stdout
+
+
+@pytest.mark.parametrize('world', [2, 8])
+def test_10k_landmarks_continuous_flush_on_slabs_vs_matrix_free_oracle(world):
+    """The bench's multi-GPU configuration over a horizon: 10 000 landmarks in SYM slabs, defer_m = 16 with the continuous
+    flush (every slab's K3 pass out of place on its own stream beside the exchange / linearise / gain chain; opt-in on slabs:
+    EKF_SHADOW_SLABS=1), 40 steps of
+    predict + 8 updates = 20 passes; x and sampled rows of every rank's slab against oracle/lowrank_lazy.py, 1e-9."""
+    if _ngpu() < world:
+        pytest.skip('needs %d GPUs' % world)
+    env = dict(os.environ, SHARD_CASE='80k', SHARD_LANDMARKS='10000', SHARD_STEPS='40', SHARD_DEFER='16', EKF_SHADOW_SLABS='1')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
+           '--master-addr', '127.0.0.1', '--master-port', str(29560 + world), os.path.join(ROOT, 'tests', 'shard_worker.py')]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    print(r.stdout[-4000:]); print(r.stderr[-4000:])
+    assert r.returncode == 0 and 'SHARD_WORKER_OK' in r.stdout
