@@ -226,14 +226,24 @@ k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__
     __syncthreads();
     const int gi = tid / ns, gj = tid - gi * ns;                   // this thread's entry of G (tid < ns * ns <= 361)
     const bool gown = tid < ns * ns;
-    // m0 = 0: nothing is pending at batch start; m0 > 0 (cross-step deferral): current = stored - the pending terms
+    // m0 = 0: nothing is pending at batch start; m0 > 0 (cross-step deferral): current = stored - the pending terms.
+    // The pending K_q(col_s), B_q(col_s) are staged in shared memory first -- one round trip to memory for all of them
+    // instead of one per term and entry (beside a K3 pass that saturates HBM a dependent load costs microseconds);
+    // every entry then subtracts the same terms in the same order as ldP_def.
+    __shared__ double2 Kp[EKF_MAX_WINDOW][EKF_BATCH_SLOTS], Bp[EKF_MAX_WINDOW][EKF_BATCH_SLOTS];
+    for (int e = tid; e < m0 * ns; e += blockDim.x) {
+        const int q = e / ns, sl = e - q * ns;
+        Kp[q][sl] = Kall[q * lds + col[sl]];
+        Bp[q][sl] = Ball[q * lds + col[sl]];
+    }
+    double g0 = 0.0;
+    if (gown) g0 = Pc ? Pc[(int64_t)gj * ldc + col[gi]] : ldP(P, ld, col[gi], col[gj], sym);   // raw stored / exchanged element
+    __syncthreads();
     if (gown) {
-        if (Pc) {       // exchanged raw P0 column (sharded): the pending terms are subtracted here, in ldP_def's order
-            double v = Pc[(int64_t)gj * ldc + col[gi]];
-            const int lo = (sym && col[gi] > col[gj]) ? col[gj] : col[gi], hi = (sym && col[gi] > col[gj]) ? col[gi] : col[gj];
-            for (int q = 0; q < m0; ++q) v = rank2_sub(v, Kall[q * lds + lo], Ball[q * lds + hi]);
-            G[gi][gj] = v;
-        } else G[gi][gj] = ldP_def(P, ld, col[gi], col[gj], sym, Kall, Ball, lds, m0);
+        const bool sw = sym && col[gi] > col[gj];                  // SYM: the live element is (min, max)
+        const int si = sw ? gj : gi, sj = sw ? gi : gj;
+        for (int q = 0; q < m0; ++q) g0 = rank2_sub(g0, Kp[q][si], Bp[q][sj]);
+        G[gi][gj] = g0;
     }
     if (tid < ns) xs[tid] = x[col[tid]];
     const bool gup = gown && (!sym || col[gi] <= col[gj]);         // SYM: the live element is (min, max)
@@ -495,9 +505,20 @@ __global__ void k_strip_fix(double* __restrict__ S, int c_lo, int ncols, const d
     }
     __syncthreads();                      // corner: every thread of block 0 has read before any of them writes a mirror entry
     if (!in) return;
-    for (int q = 0; q < m; ++q) {
+    for (int q0 = 0; q0 < m; q0 += 4) {                    // four terms' operands in flight at a time
+        double2 kq[4][3], bq[4][3];
 #pragma unroll
-        for (int r = 0; r < 3; ++r) v[r] = rank2_sub(v[r], Kall[q * lds + lo[r]], Ball[q * lds + hi[r]]);
+        for (int u = 0; u < 4; ++u)
+            if (q0 + u < m) {
+#pragma unroll
+                for (int r = 0; r < 3; ++r) { kq[u][r] = Kall[(q0 + u) * lds + lo[r]]; bq[u][r] = Ball[(q0 + u) * lds + hi[r]]; }
+            }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (q0 + u < m) {
+#pragma unroll
+                for (int r = 0; r < 3; ++r) v[r] = rank2_sub(v[r], kq[u][r], bq[u][r]);
+            }
     }
 #pragma unroll
     for (int r = 0; r < 3; ++r) S[4 * (int64_t)t + r] = v[r];
@@ -533,6 +554,7 @@ __global__ void k_rotate_slabs(double2* __restrict__ Kall, double2* __restrict__
                                double2* __restrict__ Kf, double2* __restrict__ Bf) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows) return;
+#pragma unroll 4
     for (int q = 0; q < mB; ++q) {        // ascending q: reads stay ahead of writes
         const double2 kv = Kall[(int64_t)(mA + q) * lds + i], bv = Ball[(int64_t)(mA + q) * lds + i];
         if (mA > 0) { Kall[(int64_t)q * lds + i] = kv; Ball[(int64_t)q * lds + i] = bv; }
