@@ -984,8 +984,13 @@ static int32_t exec_finish(ekf_handle* h) {
             const ekf_handle::QObs& o = h->q[m];
             ob.z0[m] = o.z0; ob.z1[m] = o.z1; ob.R0[m] = o.R0; ob.R1[m] = o.R1; ob.a[m] = o.a;
         }
-        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n, sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc_cur, h->ld,
-                              h->c_lo, h->c_hi, m0);
+        static int fr = -1;
+        if (fr < 0) { const char* e = getenv("EKF_BATCH_FRONT"); fr = e ? atoi(e) : 1; }
+        if (fr && sym_of(h) && m0 > 0)      // pending terms: their correction of the exchanged columns runs beside the linearisation chain
+            launch_batch_front_gain(h->stream, h->P, h->ld, nullptr, h->x, n, ob, h->blin, h->Pc_cur, h->ld, 0, h->Kd, h->Bd, h->ld, m0);
+        else
+            launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n, sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc_cur, h->ld,
+                                  h->c_lo, h->c_hi, m0);
         h->launches += 2;
     } else {
         for (int m = 0; m < k; ++m) {       // slab slot m0 + m; cur_col subtracts the m0 + m terms before it
@@ -1373,10 +1378,18 @@ static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
             if ((rc = shadow_close(h)) != EKF_OK) return rc;
             if (h->mQ > 0 && (rc = shadow_retire(h)) != EKF_OK) return rc;
         }
-        launch_gather_cols_strip(h->stream, h->P, h->ld, n_of(h), ob, h->Pc, h->ld, src, h->strip);
-        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), 1, ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc, h->ld,
-                              0, n_of(h), h->m_pend, nullptr, nullptr, 0, src);
-        h->launches += 3;
+        static int fr = -1;                                                 // EKF_BATCH_FRONT=0: gather, k_batch_lin, k_batch_gain(m0) one after another
+        if (fr < 0) { const char* e = getenv("EKF_BATCH_FRONT"); fr = e ? atoi(e) : 1; }
+        if (fr) {
+            launch_batch_front_gain(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld,
+                                    h->m_pend, src);
+            h->launches += 2;
+        } else {
+            launch_gather_cols_strip(h->stream, h->P, h->ld, n_of(h), ob, h->Pc, h->ld, src, h->strip);
+            launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), 1, ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc, h->ld,
+                                  0, n_of(h), h->m_pend, nullptr, nullptr, 0, src);
+            h->launches += 3;
+        }
         CK(cudaGetLastError());
         MARK_X(h);
         h->m_pend += ob.k;

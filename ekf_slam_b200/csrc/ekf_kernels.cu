@@ -199,54 +199,59 @@ __device__ __forceinline__ void stage_batch_obs(BatchObs& sh, const BatchObs& ar
     __syncthreads();
 }
 
-// __launch_bounds__(384, 4): <= 42 registers, i.e. 16 K registers per CTA.  Under the lazy flush this kernel has to start
-// beside a K3 grid that fills every SM (3 CTAs x 288 threads x 72 registers): the slot one retiring flush CTA frees is
-// 20.7 K registers, and a CTA that does not fit it waits for the flush's tail instead of overlapping with it.
-__global__ void __launch_bounds__(384, 4)
-k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
-                            const BatchObs ob_arg, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc,
-                            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0,
-                            ObSrc src) {
-    __shared__ BatchObs ob;
-    stage_batch_obs(ob, ob_arg, src.ob);
-    if (src.skip && *src.skip) return;
+// The linearisation chain of a batch on the (3+2k)^2 slot block, for a CTA of NT threads (shared by k_batch_lin, NT = 384: one
+// G entry per thread, and by block 0 of k_batch_front, NT = 128: three).  Warp 0 walks the chain, warp 1 evaluates the bearing
+// (atan2d, the longest single piece) beside it -- lanes of ONE warp would run the two branches one after the other.  Same
+// pieces, same bits as the one-warp form.  Kp / Bp: shared-memory staging for the pending terms' slot entries.
+// Raw slot block: exchanged / gathered copies Pc when given, else the stored matrix (rows / columns 0..2 from the strip S
+// when given).
+template <int NT>
+__device__ __forceinline__ void batch_lin_body(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
+                                               const BatchObs& ob, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc,
+                                               const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0,
+                                               const double* __restrict__ S,
+                                               double2 (*Kp)[EKF_BATCH_SLOTS], double2 (*Bp)[EKF_BATCH_SLOTS]) {
     __shared__ double G[EKF_BATCH_SLOTS][EKF_BATCH_SLOTS + 1];
     __shared__ double xs[EKF_BATCH_SLOTS];
     __shared__ double2 Ks[EKF_BATCH_SLOTS], Bs[EKF_BATCH_SLOTS];
     __shared__ double Hs[2][5], HPs[2][5], Ss[2][2], Sinv[2][2], nu[2];
     __shared__ int col[EKF_BATCH_SLOTS];
     __shared__ int bad;
-    // 12 warps: warp 0 walks the linearisation chain, warp 1 evaluates the bearing (atan2d, the longest single piece)
-    // beside it -- lanes of ONE warp would run the two branches one after the other --, and every thread owns one
-    // entry of the slot block for the rank-2 refresh.  Same pieces, same bits as the one-warp form.
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int k = ob.k, ns = 3 + 2 * k;
     if (tid < ns) col[tid] = tid < 3 ? tid : ob.a[(tid - 3) >> 1] + ((tid - 3) & 1);
     if (tid == 0) bad = 0;
     __syncthreads();
-    const int gi = tid / ns, gj = tid - gi * ns;                   // this thread's entry of G (tid < ns * ns <= 361)
-    const bool gown = tid < ns * ns;
     // m0 = 0: nothing is pending at batch start; m0 > 0 (cross-step deferral): current = stored - the pending terms.
     // The pending K_q(col_s), B_q(col_s) are staged in shared memory first -- one round trip to memory for all of them
     // instead of one per term and entry (beside a K3 pass that saturates HBM a dependent load costs microseconds);
     // every entry then subtracts the same terms in the same order as ldP_def.
-    __shared__ double2 Kp[EKF_MAX_WINDOW][EKF_BATCH_SLOTS], Bp[EKF_MAX_WINDOW][EKF_BATCH_SLOTS];
-    for (int e = tid; e < m0 * ns; e += blockDim.x) {
+    for (int e = tid; e < m0 * ns; e += NT) {
         const int q = e / ns, sl = e - q * ns;
         Kp[q][sl] = Kall[q * lds + col[sl]];
         Bp[q][sl] = Ball[q * lds + col[sl]];
     }
-    double g0 = 0.0;
-    if (gown) g0 = Pc ? Pc[(int64_t)gj * ldc + col[gi]] : ldP(P, ld, col[gi], col[gj], sym);   // raw stored / exchanged element
-    __syncthreads();
-    if (gown) {
-        const bool sw = sym && col[gi] > col[gj];                  // SYM: the live element is (min, max)
-        const int si = sw ? gj : gi, sj = sw ? gi : gj;
-        for (int q = 0; q < m0; ++q) g0 = rank2_sub(g0, Kp[q][si], Bp[q][sj]);
+    for (int e = tid; e < ns * ns; e += NT) {                      // raw stored / exchanged element
+        const int gi = e / ns, gj = e - gi * ns;
+        double g0;
+        if (Pc) g0 = Pc[(int64_t)gj * ldc + col[gi]];
+        else {
+            const int ci = col[gi], cj = col[gj];
+            const int lo = (sym && ci > cj) ? cj : ci, hi = (sym && ci > cj) ? ci : cj;
+            g0 = (S && lo < 3) ? S[4 * (int64_t)hi + lo] : P[(int64_t)lo + (int64_t)hi * ld];
+        }
         G[gi][gj] = g0;
     }
     if (tid < ns) xs[tid] = x[col[tid]];
-    const bool gup = gown && (!sym || col[gi] <= col[gj]);         // SYM: the live element is (min, max)
+    __syncthreads();
+    for (int e = tid; e < ns * ns; e += NT) {
+        const int gi = e / ns, gj = e - gi * ns;
+        const bool sw = sym && col[gi] > col[gj];                  // SYM: the live element is (min, max)
+        const int si = sw ? gj : gi, sj = sw ? gi : gj;
+        double g0 = G[gi][gj];
+        for (int q = 0; q < m0; ++q) g0 = rank2_sub(g0, Kp[q][si], Bp[q][sj]);
+        G[gi][gj] = g0;
+    }
     __syncthreads();
     for (int q = 0; q < k; ++q) {
         const int sa = 3 + 2 * q;
@@ -295,10 +300,91 @@ k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__
             out->Bslot[q][tid] = Bs[tid];
         }
         __syncthreads();
-        if (gown) G[gi][gj] = rank2_sub(G[gi][gj], gup ? Ks[gi] : Ks[gj], gup ? Bs[gj] : Bs[gi]);   // keep the block current: P <- P - K_q B_q
+        for (int e = tid; e < ns * ns; e += NT) {                  // keep the block current: P <- P - K_q B_q
+            const int gi = e / ns, gj = e - gi * ns;
+            const bool gup = !sym || col[gi] <= col[gj];           // SYM: the live element is (min, max)
+            G[gi][gj] = rank2_sub(G[gi][gj], gup ? Ks[gi] : Ks[gj], gup ? Bs[gj] : Bs[gi]);
+        }
         __syncthreads();
     }
     if (tid == 0) { out->nonfinite = bad; if (bad) report_nonfinite(out->nf); }
+}
+
+// __launch_bounds__(384, 4): <= 42 registers, i.e. 16 K registers per CTA.  Under the lazy flush this kernel has to start
+// beside a K3 grid that fills every SM (3 CTAs x 288 threads x 72 registers): the slot one retiring flush CTA frees is
+// 20.7 K registers, and a CTA that does not fit it waits for the flush's tail instead of overlapping with it.
+__global__ void __launch_bounds__(384, 4)
+k_batch_lin(const double* __restrict__ P, int64_t ld, const double* __restrict__ x, int sym,
+                            const BatchObs ob_arg, BatchLin* __restrict__ out, const double* __restrict__ Pc, int64_t ldc,
+                            const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0,
+                            ObSrc src) {
+    __shared__ BatchObs ob;
+    stage_batch_obs(ob, ob_arg, src.ob);
+    if (src.skip && *src.skip) return;
+    __shared__ double2 Kp[EKF_MAX_WINDOW][EKF_BATCH_SLOTS], Bp[EKF_MAX_WINDOW][EKF_BATCH_SLOTS];
+    batch_lin_body<384>(P, ld, x, sym, ob, out, Pc, ldc, Kall, Ball, lds, m0, nullptr, Kp, Bp);
+}
+
+// Front of a batch in ONE launch (SYM storage): block 0 walks the linearisation chain on the slot block while blocks 1.. bring
+// every state row's 3+2k slot entries up to date -- gathered from the stored matrix + robot strip (gather != 0: continuous
+// flush) or taken from the exchanged copies (slabs), then corrected by the m0 pending terms exactly as k_batch_gain would
+// (same terms, same order, same operands) -- and leave them in Pc.  k_batch_gain then runs with nothing pending (m0 = 0,
+// output slots o0 = m0): the pending-term phase of the gains, which does not depend on the linearisation, has left the
+// serial chain, and so have the gather kernel's launch and its round trip.  Bit-identical to lin + gain(m0).
+__global__ void __launch_bounds__(128)
+k_batch_front(const double* __restrict__ P, int64_t ld, const double* __restrict__ S, const double* __restrict__ x, int n,
+              const BatchObs ob_arg, BatchLin* __restrict__ out, double* __restrict__ Pc, int64_t ldc, int gather,
+              const double2* __restrict__ Kall, const double2* __restrict__ Ball, int64_t lds, int m0, ObSrc src) {
+    __shared__ BatchObs ob;
+    stage_batch_obs(ob, ob_arg, src.ob);
+    if (src.skip && *src.skip) return;
+    __shared__ double2 Kc[EKF_MAX_WINDOW][EKF_BATCH_SLOTS], Bc[EKF_MAX_WINDOW][EKF_BATCH_SLOTS];   // pending K_q(col_s,:), B_q(:,col_s)
+    if (blockIdx.x == 0) {
+        batch_lin_body<128>(P, ld, x, 1, ob, out, gather ? nullptr : Pc, ldc, Kall, Ball, lds, m0, S, Kc, Bc);
+        return;
+    }
+    const int k = ob.k, ns = 3 + 2 * k;
+    for (int e = threadIdx.x; e < m0 * ns; e += blockDim.x) {
+        const int q = e / ns, sl = e - q * ns;
+        const int c = sl < 3 ? sl : ob.a[(sl - 3) >> 1] + ((sl - 3) & 1);
+        Kc[q][sl] = Kall[q * lds + c];
+        Bc[q][sl] = Ball[q * lds + c];
+    }
+    __syncthreads();
+    const int i = (blockIdx.x - 1) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double pc[EKF_BATCH_SLOTS];
+    bool own[EKF_BATCH_SLOTS];                                     // element (i, col_s) is stored as (i, col_s), i <= col_s
+#pragma unroll
+    for (int s = 0; s < EKF_BATCH_SLOTS; ++s) {
+        pc[s] = 0.0; own[s] = true;
+        if (s < ns) {
+            const int c = s < 3 ? s : ob.a[(s - 3) >> 1] + ((s - 3) & 1);
+            own[s] = i <= c;
+            if (gather) {
+                const int lo = i < c ? i : c, hi = i < c ? c : i;
+                pc[s] = (S && lo < 3) ? S[4 * (int64_t)hi + lo] : P[(int64_t)lo + (int64_t)hi * ld];
+            } else pc[s] = Pc[(int64_t)s * ldc + i];
+        }
+    }
+    for (int q0 = 0; q0 < m0; q0 += 4) {                           // as in k_batch_gain: four terms' operands in flight
+        double2 kq[4], bq[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (q0 + u < m0) { kq[u] = Kall[(q0 + u) * lds + i]; bq[u] = Ball[(q0 + u) * lds + i]; }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (q0 + u < m0) {
+                const int q = q0 + u;
+#pragma unroll
+                for (int s = 0; s < EKF_BATCH_SLOTS; ++s)
+                    if (s < ns) pc[s] = own[s] ? rank2_sub(pc[s], kq[u], Bc[q][s]) : rank2_sub(pc[s], Kc[q][s], bq[u]);
+            }
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < EKF_BATCH_SLOTS; ++s)
+        if (s < ns) Pc[(int64_t)s * ldc + i] = pc[s];
 }
 
 __global__ void __launch_bounds__(128)
@@ -923,7 +1009,8 @@ __global__ void k_measure_decide(const double* __restrict__ s, int N, const doub
 void launch_measure_decide(cudaStream_t st, const double* s, int N, const double* obs, int k, double Rc0, double Rc1,
                            double s_cost, double s_thresh, BatchObs* ob_chunks, int* skip, int* status_host, int* scratch,
                            unsigned int* ticket) {
-    k_measure_decide<<<k, 256, 0, st>>>(s, N, obs, k, Rc0, Rc1, s_cost, s_thresh, ob_chunks, skip, status_host, scratch, ticket);
+    // one block per observation scans all N signatures: 1024 threads on a large map (10 loop trips per thread at 10k instead of 40)
+    k_measure_decide<<<k, N >= 4096 ? 1024 : 256, 0, st>>>(s, N, obs, k, Rc0, Rc1, s_cost, s_thresh, ob_chunks, skip, status_host, scratch, ticket);
 }
 
 // ------------------------------------------------------------------ state initialisation helpers
@@ -1030,6 +1117,17 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
     k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0, Kout, Bout, o0, src);
 }
 
+
+// front (linearisation + slot entries brought up to date) and gains of a batch, SYM storage: see k_batch_front
+void launch_batch_front_gain(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
+                             BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
+                             ObSrc src) {
+    const int rows = (gather || m0 > 0) ? cdiv(n, 128) : 0;        // nothing pending and nothing to gather: the chain alone
+    k_batch_front<<<1 + rows, 128, 0, st>>>(P, ld, S, x, n, ob, lin, Pc, ldc, gather, Kall, Ball, lds, m0, src);
+    static int gb = 0;
+    if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, 1, ob, lin, Kall, Ball, lds, Pc, ldc, 0, n, 0, Kall, Ball, m0, src);
+}
 
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,
                    double R0, double R1, double px, double py, double sig, int sym) {

@@ -426,6 +426,45 @@ def test_continuous_flush_matches_in_place_deferral(defer_m, monkeypatch):
     assert np.array_equal(runs[1][1], runs[1][1].T)
 
 
+@pytest.mark.parametrize('defer_m', [16, 11])
+def test_batch_front_kernel_is_bit_identical_to_gather_lin_gain(defer_m, monkeypatch):
+    """k_batch_front runs the linearisation chain (block 0) beside the gather + pending-term correction of every row's slot
+    entries, and k_batch_gain then starts with nothing pending: the same terms in the same order on the same operands as
+    gather -> k_batch_lin -> k_batch_gain(m0) (EKF_BATCH_FRONT=0).  x at every step and the final P must be the same bits,
+    with windows of up to 32 pending terms, ragged batches, single updates and the device-decided measure()."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth, LandmarkStub
+    N = 600
+    x, A, d, s, lms = synthetic_spd_state(N, seed=23)
+    table = [SimpleNamespace(index=i + 1, loc=lms[i]) for i in range(N)]
+    sizes = (8, 8, 8, 11, 5, 8, 1, 8, 8, 3, 8, 16)
+    monkeypatch.setenv('EKF_SHADOW_MIN_N', '0')
+    runs = []
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_BATCH_FRONT', flag)
+        f = E.EKF_SLAM_UC(capacity_landmarks=N, storage='sym', defer_m=defer_m)
+        f.set_state_lowrank(x, s, A, d)
+        assert f.flush_info()[0]
+        rng = np.random.default_rng(7)
+        xs = []
+        for step in range(36):
+            rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:sizes[step % len(sizes)]]
+            Rd = np.column_stack([rows[:, 0] * f.Rc[0], rows[:, 1] * f.Rc[1]])
+            f.predict([0.3, 1.0])
+            if step % 12 == 6:
+                f.update(rows[0, :2], Rd[0], int(rows[0, 2]))
+            elif step % 3 == 0:
+                f.measure(None, [0.3, 1.0], LandmarkStub(rows, table))          # decided on the device
+            else:
+                f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+            xs.append(f.x)
+        runs.append((xs, f.P, list(f.chosen)))
+        f.close()
+    assert runs[0][2] == runs[1][2]
+    assert all(np.array_equal(a, b) for a, b in zip(runs[0][0], runs[1][0]))
+    assert np.array_equal(runs[0][1], runs[1][1])
+
+
 @pytest.mark.parametrize('defer_m', [0, 8, 16])
 def test_x_read_back_after_predict_is_the_full_state(defer_m):
     """ekf_get_x keeps the last x it returned in pinned memory and, when only predict has run since (it moves x(1:3),
