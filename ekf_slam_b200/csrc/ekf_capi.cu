@@ -1407,8 +1407,13 @@ static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
     }
     if (h->xstep && h->m_pend + ob.k > h->pend_cap) FLUSH(h);       // make room: one pass over P for everything pending
     const int m0 = h->xstep ? h->m_pend : 0;
-    launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
-                          nullptr, 0, 0, 0, m0, nullptr, nullptr, 0, src);
+    static int fr = -1;
+    if (fr < 0) { const char* e = getenv("EKF_BATCH_FRONT"); fr = e ? atoi(e) : 1; }
+    if (fr && h->shadow && h->Pc && m0 > 0)         // in-place deferral on a handle that has the copies buffer: same front kernel, no strip
+        launch_batch_front_gain(h->stream, h->P, h->ld, nullptr, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, m0, src);
+    else
+        launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
+                              nullptr, 0, 0, 0, m0, nullptr, nullptr, 0, src);
     h->launches += 2;
     CK(cudaGetLastError());
     MARK_X(h);                      // x is final for this chunk here, before the flush
