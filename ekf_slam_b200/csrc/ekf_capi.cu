@@ -465,11 +465,14 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             const char* sh = getenv("EKF_SHADOW");
             const char* ax = getenv("EKF_ASYNC_X");
             const char* lz = getenv("EKF_LAZY_FLUSH");
-            // On slabs the mode is built and tested but off unless EKF_SHADOW_SLABS=1: measured at 10k landmarks on 2 GPUs it is
-            // slower than the lazy flush (36.9k vs 39.1k updates/s) -- beside a pass that saturates HBM the exchange /
-            // linearise / gain chain of a batch takes ~0.2 ms instead of ~0.07 ms, more than the slab's pass (0.14 ms per step).
+            // On slabs the mode pays only while a slab's pass is longer than the per-batch chain it hides (exchange, linearise,
+            // gains: ~0.06 ms alone, more beside a pass).  Measured at 10k landmarks: 2 GPUs 40.5k -> 44.3k updates/s, 8 GPUs
+            // 63.4k -> 57.6k.  Default: on when a rank's live share of P is >= 0.6 GB (10k: 2 GPUs yes, 4 and 8 no) -- a number
+            // every rank computes alike; EKF_SHADOW_SLABS=0 / 1 overrides.
             const char* ss = getenv("EKF_SHADOW_SLABS");
-            h->shadow = h->xstep && p->storage == EKF_STORAGE_SYM && (world == 1 || (ss && atoi(ss) != 0)) &&
+            const double live_per_rank = 4.0 * (double)h->cap_n * (double)(h->cap_n + 1) / (double)world;
+            const bool slabs_ok = world == 1 || (ss ? atoi(ss) != 0 : live_per_rank >= 0.6e9);
+            h->shadow = h->xstep && p->storage == EKF_STORAGE_SYM && slabs_ok &&
                         !(sh && atoi(sh) == 0) && !(ax && atoi(ax) == 0) && !(lz && atoi(lz) != 0);
             if (h->shadow) {
                 size_t fr = 0, tot = 0;
@@ -1091,10 +1094,11 @@ static int32_t shadow_close(ekf_handle* h) {
     // 2-CTA/SM shapes (33, 35, 38: as fast when alone) leave a third of every SM free for the chain's CTAs -- measured at 10k:
     // end to end 23.6k -> 24.6k updates/s, but the pass itself slows from 0.563 to 0.603 ms beside them (resident 27.4k -> 26.2k).
     static int sv = -2;
-    if (sv == -2) { const char* e = getenv("EKF_SHADOW_VARIANT"); sv = e ? atoi(e) : -1; }
+    if (sv == -2) { const char* e = getenv("EKF_SHADOW_VARIANT"); sv = (e && *e) ? atoi(e) : -3; }
+    const int svh = sv != -3 ? sv : (h->world > 1 ? 33 : -1);     // slabs: the 2-CTA/SM shape (2 GPUs, 10k: 41.2k -> 44.3k updates/s)
     if (ncl > 0)
         launch_downdate(h->sf, src, h->ld, n_of(h), ncl, 1, h->Kf[slot], h->Bf[slot] + h->c_lo, h->ld, m, h->c_lo,
-                        h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? sv : -1), h->Bt, dst);
+                        h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? svh : -1), h->Bt, dst);
     if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->sf)); h->ev_used += 2; }
     CK(cudaEventRecord(h->ev_fd[slot], h->sf));
     CK(cudaGetLastError());
