@@ -142,6 +142,8 @@ struct ekf_handle {
     int* dflags = nullptr;     // device alias of hflags
     long long xch_timeout = 0; // clock cycles k_wait_flags spins before it gives up (EKF_XCHG_TIMEOUT_MS, default 20 s)
     bool prof = false;
+    std::vector<cudaEvent_t> cev;      // EKF_CHAIN_TIMING (debug)
+    size_t cev_used = 0;
     std::vector<cudaEvent_t> ev;
     size_t ev_used = 0;
     double dd_ms = 0.0;
@@ -332,6 +334,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     cudaSetDevice(h->p.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
+    for (auto e : h->cev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd); cudaFree(h->Bt);
     cudaFree(h->Kd2); cudaFree(h->Bd2);
     if (h->sf) { cudaStreamSynchronize(h->sf); cudaStreamDestroy(h->sf); }
@@ -1384,7 +1387,20 @@ static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
         }
         static int fr = -1;                                                 // EKF_BATCH_FRONT=0: gather, k_batch_lin, k_batch_gain(m0) one after another
         if (fr < 0) { const char* e = getenv("EKF_BATCH_FRONT"); fr = e ? atoi(e) : 1; }
-        if (fr) {
+        static int ct = -1;                                                 // EKF_CHAIN_TIMING=1 (debug): CUDA-event times of front and gains
+        if (ct < 0) ct = getenv("EKF_CHAIN_TIMING") ? 1 : 0;
+        if (fr && ct) {
+            if (h->cev.empty()) { h->cev.resize(3 * 4096); for (auto& e : h->cev) CK(cudaEventCreate(&e)); }
+            if (h->cev_used + 3 <= h->cev.size()) {
+                CK(cudaEventRecord(h->cev[h->cev_used], h->stream));
+                launch_batch_front_only(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, h->m_pend, src);
+                CK(cudaEventRecord(h->cev[h->cev_used + 1], h->stream));
+                launch_batch_gain_only(h->stream, h->P, h->ld, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, h->Kd, h->Bd, h->ld, h->m_pend, src);
+                CK(cudaEventRecord(h->cev[h->cev_used + 2], h->stream));
+                h->cev_used += 3;
+            } else launch_batch_front_gain(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, h->m_pend, src);
+            h->launches += 2;
+        } else if (fr) {
             launch_batch_front_gain(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld,
                                     h->m_pend, src);
             h->launches += 2;
@@ -1957,6 +1973,18 @@ extern "C" int32_t ekf_profile_read(ekf_handle* h, double* downdate_ms_total, in
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
         h->dd_ms += ms;
+    }
+    if (h->cev_used >= 3) {
+        double tf = 0.0, tg = 0.0, tf_max = 0.0, tg_max = 0.0; int nc = 0;
+        for (size_t i = 0; i + 2 < h->cev_used; i += 3) {
+            float a = 0.f, b = 0.f;
+            if (cudaEventElapsedTime(&a, h->cev[i], h->cev[i + 1]) == cudaSuccess && cudaEventElapsedTime(&b, h->cev[i + 1], h->cev[i + 2]) == cudaSuccess) {
+                tf += a; tg += b; tf_max = a > tf_max ? a : tf_max; tg_max = b > tg_max ? b : tg_max; ++nc;
+            }
+        }
+        fprintf(stderr, "ekfslam_b200: %d batches: k_batch_front mean %.1f us (max %.1f), k_batch_gain mean %.1f us (max %.1f)\n", nc,
+                nc ? 1e3 * tf / nc : 0.0, 1e3 * tf_max, nc ? 1e3 * tg / nc : 0.0, 1e3 * tg_max);
+        h->cev_used = 0;
     }
     if (getenv("EKF_PROFILE_GAPS") && h->ev_used >= 4) {       // debug aid: idle time between consecutive K3 passes
         double gap = 0.0, gmax = 0.0; int ng = 0;

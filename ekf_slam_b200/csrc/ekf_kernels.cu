@@ -1119,14 +1119,23 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
 
 
 // front (linearisation + slot entries brought up to date) and gains of a batch, SYM storage: see k_batch_front
-void launch_batch_front_gain(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
+void launch_batch_front_only(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
                              BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
                              ObSrc src) {
     const int rows = (gather || m0 > 0) ? cdiv(n, 128) : 0;        // nothing pending and nothing to gather: the chain alone
     k_batch_front<<<1 + rows, 128, 0, st>>>(P, ld, S, x, n, ob, lin, Pc, ldc, gather, Kall, Ball, lds, m0, src);
+}
+void launch_batch_gain_only(cudaStream_t st, const double* P, int64_t ld, double* x, int n, const BatchObs& ob, BatchLin* lin,
+                            double* Pc, int64_t ldc, double2* Kall, double2* Ball, int64_t lds, int m0, ObSrc src) {
     static int gb = 0;
     if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
     k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, 1, ob, lin, Kall, Ball, lds, Pc, ldc, 0, n, 0, Kall, Ball, m0, src);
+}
+void launch_batch_front_gain(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
+                             BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
+                             ObSrc src) {
+    launch_batch_front_only(st, P, ld, S, x, n, ob, lin, Pc, ldc, gather, Kall, Ball, lds, m0, src);
+    launch_batch_gain_only(st, P, ld, x, n, ob, lin, Pc, ldc, Kall, Ball, lds, m0, src);
 }
 
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,

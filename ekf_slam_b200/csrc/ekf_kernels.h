@@ -38,6 +38,11 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
 void launch_batch_front_gain(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
                              BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
                              ObSrc src = ObSrc{nullptr, nullptr});
+void launch_batch_front_only(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
+                             BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
+                             ObSrc src = ObSrc{nullptr, nullptr});
+void launch_batch_gain_only(cudaStream_t st, const double* P, int64_t ld, double* x, int n, const BatchObs& ob, BatchLin* lin,
+                            double* Pc, int64_t ldc, double2* Kall, double2* Ball, int64_t lds, int m0, ObSrc src = ObSrc{nullptr, nullptr});
 void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc,
                         ObSrc src = ObSrc{nullptr, nullptr});
 // ---- continuous flush ("shadow", single GPU, SYM storage): robot strip S[4 j + r] = P0(r, j), r < 3; see ekf_kernels.cu ----
