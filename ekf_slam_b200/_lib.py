@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libekfslam_b200.so')
+LIB_PATH = os.environ.get('EKFSLAM_B200_LIB') or os.path.join(_HERE, 'libekfslam_b200.so')      # override: A/B of two builds on one box
 
 EKF_OK, EKF_EINVAL, EKF_ECAPACITY, EKF_ECUDA, EKF_ENCCL, EKF_ENONFINITE = 0, -1, -2, -3, -4, -5
 VARIANT_KNOWN, VARIANT_UC = 0, 1

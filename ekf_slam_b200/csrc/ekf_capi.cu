@@ -103,8 +103,14 @@ struct ekf_handle {
     double* P2 = nullptr;
     double* strip = nullptr;   // 4 x ld doubles
     bool strip_valid = false;
-    double2* Kf[2] = {nullptr, nullptr};   // frozen copies of a closed set, alternating between consecutive passes
-    double2* Bf[2] = {nullptr, nullptr};
+    // The window of pending terms is [Kd, Kd + m_pend) with Kd / Bd moving through a larger allocation (Kd0 / Bd0, EKF_WIN_SLOTS
+    // slabs): retiring a pass advances the base past its terms instead of moving the rest down, and a pass reads its set
+    // where it lies -- predict keeps rewriting rows 0, 1 of those slabs (K_q <- F K_q, B_q <- B_q F'), which only ever reach
+    // rows / columns 0-1 of the pass's output, the part of the matrix the strip stands in for.  Compacted to the start
+    // (with nothing in flight) when the end of the allocation comes near: once in ~13 passes.
+    double2* Kd0 = nullptr;
+    double2* Bd0 = nullptr;
+    int kw0 = 0;               // slabs between Kd0 and Kd
     cudaStream_t sf = nullptr;
     cudaEvent_t ev_fz = nullptr, ev_fd[2] = {nullptr, nullptr};
     int nfl = 0;               // passes outstanding on sf: 0, 1 (running) or 2 (running + queued)
@@ -335,11 +341,11 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto e : h->cev) cudaEventDestroy(e);
-    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd); cudaFree(h->Bd); cudaFree(h->Bt);
+    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd0 ? h->Kd0 : h->Kd); cudaFree(h->Bd0 ? h->Bd0 : h->Bd); cudaFree(h->Bt);
     cudaFree(h->Kd2); cudaFree(h->Bd2);
     if (h->sf) { cudaStreamSynchronize(h->sf); cudaStreamDestroy(h->sf); }
     if (h->ev_fz) cudaEventDestroy(h->ev_fz);
-    for (int i = 0; i < 2; ++i) { if (h->ev_fd[i]) cudaEventDestroy(h->ev_fd[i]); cudaFree(h->Kf[i]); cudaFree(h->Bf[i]); }
+    for (int i = 0; i < 2; ++i) if (h->ev_fd[i]) cudaEventDestroy(h->ev_fd[i]);
     cudaFree(h->P2); cudaFree(h->strip);
     if (h->sg) { cudaStreamSynchronize(h->sg); cudaStreamDestroy(h->sg); }
     if (h->ev_g1) cudaEventDestroy(h->ev_g1);
@@ -368,6 +374,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
 }
 
 static int32_t init_state(ekf_handle* h) {
+    if (h->Kd0) { h->Kd = h->Kd0; h->Bd = h->Bd0; h->kw0 = 0; }
     // x = [0 0 0], P = 0.1*eye(3), s = []   (EKF_SLAM.m:28-31)
     CK(cudaMemsetAsync(h->P, 0, sizeof(double) * h->ld * (h->c_hi - h->c_lo), h->stream));
     CK(cudaMemsetAsync(h->x, 0, sizeof(double) * h->ld, h->stream));
@@ -513,12 +520,6 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             CK(cudaMemset(h->P2, 0, sizeof(double) * h->ld * (h->c_hi - h->c_lo)));
             CK(cudaMalloc(&h->strip, sizeof(double) * 4 * h->ld));
             CK(cudaMemset(h->strip, 0, sizeof(double) * 4 * h->ld));
-            for (int i = 0; i < 2; ++i) {
-                CK(cudaMalloc(&h->Kf[i], sizeof(double2) * h->ld * EKF_MAX_PEND));
-                CK(cudaMalloc(&h->Bf[i], sizeof(double2) * h->ld * EKF_MAX_PEND));
-                CK(cudaMemset(h->Kf[i], 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
-                CK(cudaMemset(h->Bf[i], 0, sizeof(double2) * h->ld * EKF_MAX_PEND));
-            }
             if (world == 1) { CK(cudaMalloc(&h->Pc, sizeof(double) * h->ld * EKF_MAX_SLOTS)); h->Pc_cur = h->Pc; }
         }
         if (world > 1 && in_process) {       // peers are wired by ekf_create_multi once every sub-handle exists
@@ -546,8 +547,13 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMallocHost(&h->x_pin, sizeof(double) * h->ld));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
-        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * (h->shadow ? EKF_MAX_WINDOW : EKF_MAX_PEND)));
-        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * (h->shadow ? EKF_MAX_WINDOW : EKF_MAX_PEND)));
+        CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * (h->shadow ? EKF_WIN_SLOTS : EKF_MAX_PEND)));
+        CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * (h->shadow ? EKF_WIN_SLOTS : EKF_MAX_PEND)));
+        if (h->shadow) {
+            h->Kd0 = h->Kd; h->Bd0 = h->Bd;
+            CK(cudaMemset(h->Kd0, 0, sizeof(double2) * h->ld * EKF_WIN_SLOTS));
+            CK(cudaMemset(h->Bd0, 0, sizeof(double2) * h->ld * EKF_WIN_SLOTS));
+        }
         CK(cudaMalloc(&h->Bt, sizeof(double) * EKF_BT_SROW * ((size_t)(h->c_hi - h->c_lo) + 16)));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->blin, sizeof(BatchLin)));
@@ -1067,8 +1073,10 @@ static int32_t shadow_retire(ekf_handle* h) {
     CK(cudaStreamWaitEvent(h->stream, h->ev_fd[h->fcur], 0));
     launch_strip_fix(h->stream, h->strip, h->c_lo, ncols_loc(h), h->Kd, h->Bd, h->ld, h->mA);
     std::swap(h->P, h->P2);
-    launch_rotate_slabs(h->stream, h->Kd, h->Bd, h->ld, n_of(h), h->mA, h->m_pend - h->mA, nullptr, nullptr);
-    h->launches += 2;
+    h->Kd += (int64_t)h->mA * h->ld;              // the window starts behind the retired terms now
+    h->Bd += (int64_t)h->mA * h->ld;
+    h->kw0 += h->mA;
+    h->launches += 1;
     CK(cudaGetLastError());
     h->m_pend -= h->mA;
     h->mA = h->mQ;
@@ -1081,13 +1089,22 @@ static int32_t shadow_retire(ekf_handle* h) {
 // running pass (P -> P2) when nothing is outstanding, else queued behind the running one (its output P2 -> back into P;
 // the chain must retire the running pass before it reads P again).  Needs a free place in the queue (nfl < 2, mQ == 0).
 static int32_t shadow_close(ekf_handle* h) {
-    const int off = h->mA + h->mQ, m = h->m_pend - off;
-    if (m <= 0) return EKF_OK;
+    if (h->m_pend - h->mA - h->mQ <= 0) return EKF_OK;
     if (h->nfl >= 2 || h->mQ != 0) return fail(h, EKF_EINVAL, "internal: continuous flush queue is full");
+    if (h->kw0 + 2 * EKF_MAX_WINDOW > EKF_WIN_SLOTS) {
+        // the window has wandered to the end of its allocation: bring it back to the start.  Passes in flight read their
+        // sets where they lie, so they are retired first (a wait of at most one pass, once in ~13 passes).
+        int32_t rc = EKF_OK;
+        while (h->nfl > 0) if ((rc = shadow_retire(h)) != EKF_OK) return rc;
+        launch_rotate_slabs(h->stream, h->Kd0, h->Bd0, h->ld, n_of(h), h->kw0, h->m_pend, nullptr, nullptr);
+        h->Kd = h->Kd0; h->Bd = h->Bd0; h->kw0 = 0;
+        h->launches += 1;
+    }
+    const int off = h->mA + h->mQ, m = h->m_pend - off;
     const int slot = h->nfl == 0 ? h->fcur : (h->fcur ^ 1);
-    launch_rotate_slabs(h->stream, h->Kd + (int64_t)off * h->ld, h->Bd + (int64_t)off * h->ld, h->ld, n_of(h), 0, m,
-                        h->Kf[slot], h->Bf[slot]);    // freeze the set: predict keeps transforming its copy in the window
-    CK(cudaEventRecord(h->ev_fz, h->stream));     // also: every gather enqueued so far has read the buffer a queued pass overwrites
+    const double2* Kset = h->Kd + (int64_t)off * h->ld;
+    const double2* Bset = h->Bd + (int64_t)off * h->ld;
+    CK(cudaEventRecord(h->ev_fz, h->stream));     // the set is complete; every gather enqueued so far has read the buffer a queued pass overwrites
     CK(cudaStreamWaitEvent(h->sf, h->ev_fz, 0));
     if (h->prof) { int32_t rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->sf)); }
     double* src = h->nfl == 0 ? h->P : h->P2;
@@ -1100,14 +1117,14 @@ static int32_t shadow_close(ekf_handle* h) {
     if (sv == -2) { const char* e = getenv("EKF_SHADOW_VARIANT"); sv = (e && *e) ? atoi(e) : -3; }
     const int svh = sv != -3 ? sv : (h->world > 1 ? 33 : -1);     // slabs: the 2-CTA/SM shape (2 GPUs, 10k: 41.2k -> 44.3k updates/s)
     if (ncl > 0)
-        launch_downdate(h->sf, src, h->ld, n_of(h), ncl, 1, h->Kf[slot], h->Bf[slot] + h->c_lo, h->ld, m, h->c_lo,
+        launch_downdate(h->sf, src, h->ld, n_of(h), ncl, 1, Kset, Bset + h->c_lo, h->ld, m, h->c_lo,
                         h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? svh : -1), h->Bt, dst);
     if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->sf)); h->ev_used += 2; }
     CK(cudaEventRecord(h->ev_fd[slot], h->sf));
     CK(cudaGetLastError());
     h->dd_launches += 1;
     h->dd_terms += m;
-    h->launches += 2;
+    h->launches += 1;
     if (h->nfl == 0) h->mA = m; else h->mQ = m;
     h->nfl += 1;
     return EKF_OK;
@@ -1120,6 +1137,7 @@ static int32_t shadow_reset(ekf_handle* h) {
     h->nfl = 0;
     h->mA = h->mQ = 0;
     h->strip_valid = false;
+    if (h->Kd0) { h->Kd = h->Kd0; h->Bd = h->Bd0; h->kw0 = 0; }
     return EKF_OK;
 }
 
@@ -1145,6 +1163,7 @@ static int32_t shadow_settle(ekf_handle* h) {
         h->launches += 1;
         h->strip_valid = false;
     }
+    if (h->Kd0) { h->Kd = h->Kd0; h->Bd = h->Bd0; h->kw0 = 0; }      // nothing pending: the window starts over
     CK(cudaGetLastError());
     return EKF_OK;
 }

@@ -14,6 +14,7 @@ void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, do
 #define EKF_MAX_DEFER 8
 #define EKF_MAX_PEND 16                             // single-GPU handles: rank-2 terms that may stay pending across predict (defer_m = 9..16)
 #define EKF_MAX_WINDOW (2 * EKF_MAX_PEND)            // continuous flush: the set a K3 pass is applying + the set that is filling up
+#define EKF_WIN_SLOTS 256                             // slabs the window's allocation holds (the window moves through it, see ekf_capi.cu)
 #define EKF_MAX_SLOTS (3 + 2 * EKF_MAX_DEFER)      // columns exchanged per sharded batch: robot + 2 per observation
 struct SlotSet { int n; int col[EKF_MAX_SLOTS]; }; // global column index of each slot (passed by value)
 struct ObSrc { const BatchObs* ob; const int* skip; };   // device-side batch description + skip word (both null: by-value BatchObs)

@@ -426,6 +426,53 @@ def test_continuous_flush_matches_in_place_deferral(defer_m, monkeypatch):
     assert np.array_equal(runs[1][1], runs[1][1].T)
 
 
+def test_continuous_flush_settles_for_everything_that_needs_P(monkeypatch):
+    """Entry points that need the whole matrix while passes are in flight: the ellipses, a mode-B association (reads P
+    blocks), an append, replacing the state (set_state_lowrank: everything pending is dropped) and closing the handle
+    with passes outstanding.  Continuous flush (forced at this size) against the in-place deferral, 1e-12."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import synthetic_spd_state, observe_from_truth
+    N = 500
+    x, A, d, s, lms = synthetic_spd_state(N, seed=29)
+    monkeypatch.setenv('EKF_SHADOW_MIN_N', '0')
+    runs = []
+    for flag in ('0', '1'):
+        monkeypatch.setenv('EKF_SHADOW', flag)
+        f = E.EKF_SLAM_UC(capacity_landmarks=N + 2, storage='sym', defer_m=16, assoc_mode='position')
+        f.correspondence.s_thresh = 9.21
+        f._sync_corr()
+        f.set_state_lowrank(x, np.ones(N), A, d)
+        assert f.flush_info()[0] == (flag == '1')
+        rng = np.random.default_rng(3)
+        out = []
+        for step in range(30):
+            rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:8]
+            Rd = np.column_stack([rows[:, 0] * f.Rc[0], rows[:, 1] * f.Rc[1]])
+            f.predict([0.3, 1.0])
+            f.update_batch(rows[:, :2], Rd, rows[:, 2].astype(np.int32))
+            if step == 7:
+                out.append(f.covariance_ellipses())
+            if step == 11:
+                z = np.array([rows[0, 0], rows[0, 1], 1.0])
+                out.append(np.array(f.correspondence.estimateCorrespondence(z, np.diag([z[0] * 0.1, z[1] * 5.0])), dtype=float))
+            if step == 15:
+                f.append([0.3, 1.0], np.diag([0.02, 100.0]), [1.0, 2.0], 1.0)
+            if step == 20:                                   # replace the state with passes in flight
+                f.set_state_lowrank(x, np.ones(N), A, d)
+            out.append(f.x)
+        out.append(f.P)
+        runs.append(out)
+        g = E.EKF_SLAM_UC(capacity_landmarks=N, storage='sym', defer_m=16)      # closed with passes outstanding
+        g.set_state_lowrank(x, s, A, d)
+        for step in range(5):
+            rows = observe_from_truth(lms, x[:3], rng.choice(N, 24, replace=False), rng)[:8]
+            g.predict([0.3, 1.0])
+            g.update_batch(rows[:, :2], np.column_stack([rows[:, 0] * g.Rc[0], rows[:, 1] * g.Rc[1]]), rows[:, 2].astype(np.int32))
+        g.close(); f.close()
+    assert len(runs[0]) == len(runs[1])
+    assert max(_rel(a, b) for a, b in zip(runs[0], runs[1])) <= 1e-12
+
+
 @pytest.mark.parametrize('defer_m', [16, 11])
 def test_batch_front_kernel_is_bit_identical_to_gather_lin_gain(defer_m, monkeypatch):
     """k_batch_front runs the linearisation chain (block 0) beside the gather + pending-term correction of every row's slot
