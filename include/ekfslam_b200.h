@@ -58,7 +58,7 @@ typedef struct ekf_params {
     int32_t  storage;            /* EKF_STORAGE_* */
     int32_t  capacity_landmarks; /* P is allocated once at 3+2*capacity (reference reallocates per append, EKF_SLAM.m:91) */
     int32_t  device;             /* CUDA device ordinal */
-    int32_t  defer_m;            /* <=1: one pass over P per observation; 2..8: deferred, one rank-2m pass per m observations (same sequence of linearisations, bit-identical); 9..16 (single GPU, or SYM slabs of a sharded filter): terms also stay pending across ekf_predict, which transforms them (K_q <- F K_q, B_q <- B_q F'): equal to rounding, not bit for bit */
+    int32_t  defer_m;            /* <=1: one pass over P per observation; 2..8: deferred, one rank-2m pass per m observations (same sequence of linearisations, bit-identical); 9..16 (single GPU, or SYM slabs of a sharded filter): terms also stay pending across ekf_predict, which transforms them (K_q <- F K_q, B_q <- B_q F'): equal to rounding, not bit for bit; on a large map (n >= 8000, SYM storage) the rank-32 pass then runs out of place on a stream of its own beside predict and the next batches (continuous flush: ekf_flush_info, EKF_SHADOW=0 disables; needs room for a second copy of P) */
     uint64_t stream;             /* cudaStream_t to enqueue on, 0 = library creates one */
 } ekf_params;
 

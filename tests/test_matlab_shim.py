@@ -182,3 +182,61 @@ def test_gateway_full_loop_matches_oracle(mex, variant):
     assert e.value.ident == 'ekfslam:EINVAL'
     mex('destroy', h, nlhs=0)
     g.close()
+
+
+@pytest.mark.gpu
+def test_gateway_batch_verbs_match_filter_batch(mex):
+    """The Monte-Carlo batch through the MEX verbs ('batch_create' / 'batch_step' / 'batch_get_*' / 'batch_poses' /
+    'batch_set_state'), the way matlab/EKFSLAM_B200_Batch.m drives them, == ekf_slam_b200.FilterBatch bit for bit
+    (same library underneath), incl. the update_batch / flush_info / defer_info verbs of a single filter."""
+    import ekf_slam_b200 as E
+    from ekf_slam_b200.synth import make_world
+    nf, max_obs, cap = 6, 4, 12
+    w = make_world(N=cap, T=40, k=max_obs, mode='nearest', seed=9)
+    hb = mex('batch_create', 1.0, float(nf), float(max_obs), float(cap), {'capacity_landmarks': cap, 'storage': 1, 'defer_m': 8})[0]
+    fb = E.FilterBatch('EKF_SLAM_UC', nf, capacity_landmarks=cap, max_obs=max_obs, max_table=cap, storage='sym', defer_m=8)
+    scale = 1.0 + 0.01 * np.arange(nf)
+    for t in range(w.T):
+        stub = w.stub(t)
+        obs = np.asarray(stub.getLandmark(None, None), dtype=np.float64).reshape(-1, 3)
+        tab = stub.landmarkObj.landmark
+        U = np.outer(scale, w.u[t])                                   # nf x 2
+        packed = np.zeros((max_obs, 3, nf), order='F')
+        packed[:obs.shape[0], :, :] = obs[:, :, None]
+        acts = mex('batch_step', hb, U.T, packed.reshape(max_obs, 3 * nf, order='F'), np.full((nf, 1), float(obs.shape[0])),
+                   np.array([e.loc for e in tab]).reshape(-1, 2), np.array([[float(e.index)] for e in tab]).reshape(-1, 1), 1.0, 1.0)[0]
+        want = fb.step(U, [obs] * nf, tab, want_actions=True)
+        assert np.array_equal(acts.T.astype(np.int32), want), t
+    N = mex('batch_n_landmarks', hb)[0].ravel().astype(int)
+    assert np.array_equal(N, fb.n_landmarks())
+    assert np.array_equal(mex('batch_poses', hb)[0].T, fb.poses())
+    for f in range(nf):
+        assert np.array_equal(mex('batch_get_x', hb, float(f + 1))[0].ravel(), fb[f].x)
+        assert np.array_equal(mex('batch_get_P', hb, float(f + 1))[0], fb[f].P)
+        assert np.array_equal(mex('batch_get_s', hb, float(f + 1))[0].ravel(), fb[f].s)
+    x0, P0, s0 = fb[0].x, fb[0].P, fb[0].s
+    mex('batch_set_state', hb, 0.0, x0, P0, s0.reshape(-1, 1), nlhs=0)        # every filter <- filter 1's state
+    mex('batch_sync', hb, nlhs=0)
+    assert np.array_equal(mex('batch_get_P', hb, float(nf))[0], P0)
+    with pytest.raises(MexError) as e:
+        mex('batch_get_x', hb, float(nf + 1))
+    assert e.value.ident == 'ekfslam:EINVAL'
+    mex('batch_destroy', hb, nlhs=0)
+    fb.close()
+    # single-filter verbs added in round 2
+    h = mex('create', 0.0, {'capacity_landmarks': cap, 'storage': 1, 'defer_m': 16})[0]
+    g = E.EKF_SLAM(capacity_landmarks=cap, storage='sym', defer_m=16)
+    mex('set_state', h, x0, P0, s0.reshape(-1, 1), nlhs=0)
+    g.set_state(x0, P0, s0)
+    k = min(3, int(N[0]))
+    z = np.column_stack([np.linspace(1.0, 2.0, k), np.linspace(10.0, 40.0, k)])
+    Rd = np.column_stack([z[:, 0] * 0.01, z[:, 1] * 5.0])
+    mex('update_batch', h, z, Rd, np.arange(1.0, k + 1).reshape(-1, 1), nlhs=0)
+    g.update_batch(z, Rd, np.arange(1, k + 1))
+    assert np.array_equal(mex('get_x', h)[0].ravel(), g.x)
+    bsz, capm = mex('defer_info', h, nlhs=2)
+    assert (bsz[0, 0], capm[0, 0]) == (8.0, 16.0)
+    cont, outst = mex('flush_info', h, nlhs=2)
+    assert cont is False and outst[0, 0] == 0.0                   # 12 landmarks: far below the continuous-flush threshold
+    mex('destroy', h, nlhs=0)
+    g.close()
