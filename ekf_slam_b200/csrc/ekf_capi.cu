@@ -339,6 +339,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     }
     cudaSetDevice(h->p.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->sf) cudaStreamSynchronize(h->sf);          // a K3 pass of the continuous flush may still be running
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto e : h->cev) cudaEventDestroy(e);
     cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd0 ? h->Kd0 : h->Kd); cudaFree(h->Bd0 ? h->Bd0 : h->Bd); cudaFree(h->Bt);
