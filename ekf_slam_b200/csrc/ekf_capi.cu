@@ -70,7 +70,10 @@ struct ekf_handle {
     double* xprev = nullptr;   // pre-motion pose saved by the state half of predict for the covariance half
     double* x_pin = nullptr;   // pinned staging of x for ekf_get_x (a copy into pageable memory goes through the driver's bounce buffers)
     bool x_host = false;       // x_pin holds the device's x, except (x_head_dirty) the pose x(1:3) that a predict has moved since:
-    bool x_head_dirty = false; // the read-back after predict then copies 24 bytes instead of 8 n (single-GPU handles)
+    bool x_head_dirty = false; // the read-back after predict then needs 24 bytes instead of 8 n (single-GPU handles) -- and those the
+    double* pose_host = nullptr;   // state half of predict has already written into mapped pinned memory (pose_dev = its device alias),
+    double* pose_dev = nullptr;    // so the read waits for that kernel's event and copies nothing
+    bool pose_fresh = false;
     int defer = 1;             // flush when m_pend reaches this (1 = immediate); also the chunk size of the fused batch (<= 8)
     // cross-step deferral (single GPU, defer_m = 9..EKF_MAX_PEND): terms stay pending across measure() and predict();
     // the flush runs when the next chunk would not fit (or at a getter / append / mode-B association).  predict then
@@ -221,6 +224,7 @@ static int32_t resolve_measure(ekf_handle* h) {
 
 static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing main-stream work that touches x / s
     h->x_host = false;
+    h->pose_fresh = false;
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->stream));
     return EKF_OK;
 }
@@ -359,6 +363,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     cudaFree(h->lin); cudaFree(h->blin); cudaFree(h->partial); cudaFree(h->ticket); cudaFree(h->d_res);
     if (h->h_res) cudaFreeHost(h->h_res);
     if (h->x_pin) cudaFreeHost(h->x_pin);
+    if (h->pose_host) cudaFreeHost(h->pose_host);
     if (h->hflags) cudaFreeHost(h->hflags);
     if (h->am_obs_h) cudaFreeHost(h->am_obs_h);
     if (h->am_status) cudaFreeHost(h->am_status);
@@ -547,6 +552,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
         }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
         CK(cudaMallocHost(&h->x_pin, sizeof(double) * h->ld));
+        CK(cudaHostAlloc(&h->pose_host, 4 * sizeof(double), cudaHostAllocMapped | cudaHostAllocPortable));
+        CK(cudaHostGetDevicePointer(&h->pose_dev, h->pose_host, 0));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
         CK(cudaMalloc(&h->Kd, sizeof(double2) * h->ld * (h->shadow ? EKF_WIN_SLOTS : EKF_MAX_PEND)));
         CK(cudaMalloc(&h->Bd, sizeof(double2) * h->ld * (h->shadow ? EKF_WIN_SLOTS : EKF_MAX_PEND)));
@@ -786,8 +793,9 @@ extern "C" int32_t ekf_predict(ekf_handle* h, const double u[2]) {
         // covariance half on the main stream with the heading the state half saved (EKF_SLAM.m:42,63-64 use theta before f())
         CK(cudaStreamWaitEvent(h->sx, h->ev_mx, 0));
         CK(cudaStreamWaitEvent(h->sx, h->ev_pp, 0));
-        launch_predict_x_save(h->sx, h->x, u[0], u[1], h->xprev);
+        launch_predict_x_save(h->sx, h->x, u[0], u[1], h->xprev, h->world == 1 ? h->pose_dev : nullptr);
         CK(cudaEventRecord(h->ev_px, h->sx));
+        h->pose_fresh = h->world == 1 && h->pose_dev != nullptr;
         CK(cudaStreamWaitEvent(h->stream, h->ev_px, 0));
         if (shadow_on(h)) {                  // covariance half on the robot strip: P itself may be under a K3 pass
             int32_t rcs = shadow_strip_ready(h);
@@ -1714,6 +1722,15 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
     if (h->world > 1) {                   // sharded: x of queued observations is produced by the batch
         int32_t rcq = h->xstep ? exec_sharded(h) : flush_sharded(h);
         if (rcq != EKF_OK) return rcq;
+    }
+    if (h->async_x && h->x_pin && h->x_host && h->x_head_dirty && h->pose_fresh && h->world == 1) {
+        // only predict has run since the last read, and its state kernel wrote the new pose into mapped host memory:
+        // wait for that kernel, no copy at all
+        CK(cudaEventSynchronize(h->ev_px));
+        h->x_pin[0] = h->pose_host[0]; h->x_pin[1] = h->pose_host[1]; h->x_pin[2] = h->pose_host[2];
+        memcpy(x, h->x_pin, sizeof(double) * n_of(h));
+        h->x_head_dirty = false;
+        return after_sync(h);
     }
     cudaStream_t st = h->stream;
     if (h->async_x) {                     // behind the last writer of x, not behind the flush that follows it

@@ -69,12 +69,16 @@ __global__ void k_predict_P(double* __restrict__ P, int64_t ld, const double* __
 
 // `prev` (may be null): receives the pre-motion pose.  The decoupled predict (ekf_capi.cu, async_x) runs this kernel
 // FIRST on the side stream and hands k_predict_P `prev` as its x, so that it still sees the heading before f().
-__global__ void k_predict_x(double* __restrict__ x, double u1, double u2, double* __restrict__ prev) {   // EKF_SLAM.m:57-60, :50
+// `pose_host` (may be null): mapped pinned host memory that receives the new pose as well, so that a caller who reads x
+// right after predict (the reference's loop does: getLandmark(laserData, h.x), EKF_SLAM.m:102) needs no copy, only the event.
+__global__ void k_predict_x(double* __restrict__ x, double u1, double u2, double* __restrict__ prev, double* __restrict__ pose_host) {   // EKF_SLAM.m:57-60, :50
     double th = x[2];
     if (prev) { prev[0] = x[0]; prev[1] = x[1]; prev[2] = th; }
-    x[0] = x[0] + u1 * cosd(th + u2);
-    x[1] = x[1] + u1 * sind(th + u2);
-    x[2] = wrapTo360(th + u2);
+    const double x0 = x[0] + u1 * cosd(th + u2);
+    const double x1 = x[1] + u1 * sind(th + u2);
+    const double x2 = wrapTo360(th + u2);
+    x[0] = x0; x[1] = x1; x[2] = x2;
+    if (pose_host) { pose_host[0] = x0; pose_host[1] = x1; pose_host[2] = x2; __threadfence_system(); }
 }
 
 // predict while m rank-2 terms are pending (cross-step deferral): the covariance is P0 - sum_q K_q B_q, so
@@ -1085,15 +1089,15 @@ void launch_ellipses(cudaStream_t st, const double* P, int64_t ld, const double*
 
 void launch_predict(cudaStream_t st, double* P, int64_t ld, double* x, int n, double u1, double u2, double C, int sym) {
     k_predict_P<<<cdiv(n, 256), 256, 0, st>>>(P, ld, x, n, u1, u2, C, sym, nullptr, nullptr, 0, 0);
-    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr);
+    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr, nullptr);
 }
 
-void launch_predict_x(cudaStream_t st, double* x, double u1, double u2) { k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr); }
+void launch_predict_x(cudaStream_t st, double* x, double u1, double u2) { k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, nullptr, nullptr); }
 
 // The two halves of launch_predict for the decoupled path: the state half saves the pre-motion pose into xprev, the
 // covariance half reads its heading from there (same arithmetic, bit-identical results).
-void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev) {
-    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, xprev);
+void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev, double* pose_host) {
+    k_predict_x<<<1, 1, 0, st>>>(x, u1, u2, xprev, pose_host);
 }
 void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym,
                       double2* Kall, double2* Ball, int64_t lds, int m) {

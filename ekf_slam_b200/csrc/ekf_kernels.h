@@ -76,7 +76,7 @@ void launch_associate(cudaStream_t st, const double* P, int64_t ld, const double
 void launch_init_lowrank(cudaStream_t st, double* P, int64_t ld, int n, int c_lo, int ncols, const double* A, int r,
                          const double* d);
 void launch_predict_x(cudaStream_t st, double* x, double u1, double u2);
-void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev);      // decoupled predict, state half (side stream)
+void launch_predict_x_save(cudaStream_t st, double* x, double u1, double u2, double* xprev, double* pose_host = nullptr);      // decoupled predict, state half (side stream)
 void launch_predict_P(cudaStream_t st, double* P, int64_t ld, const double* xprev, int n, double u1, double u2, double C, int sym,
                       double2* Kall = nullptr, double2* Ball = nullptr, int64_t lds = 0, int m = 0);   // covariance half (+ the m pending slabs, one extra block)
 // ---- column-slab sharded filter (ekf_shard.cu) ----
