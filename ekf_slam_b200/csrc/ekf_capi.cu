@@ -74,6 +74,8 @@ struct ekf_handle {
     double* pose_host = nullptr;   // state half of predict has already written into mapped pinned memory (pose_dev = its device alias),
     double* pose_dev = nullptr;    // so the read waits for that kernel's event and copies nothing
     bool pose_fresh = false;
+    double* x_pin_dev = nullptr;   // device alias of x_pin (mapped): k_batch_gain writes x there as well
+    bool xpin_fresh = false;       // x_pin is the device's x once ev_mx has fired (the last writer of x was such a gain kernel)
     int defer = 1;             // flush when m_pend reaches this (1 = immediate); also the chunk size of the fused batch (<= 8)
     // cross-step deferral (single GPU, defer_m = 9..EKF_MAX_PEND): terms stay pending across measure() and predict();
     // the flush runs when the next chunk would not fit (or at a getter / append / mode-B association).  predict then
@@ -225,6 +227,7 @@ static int32_t resolve_measure(ekf_handle* h) {
 static inline int32_t mark_x(ekf_handle* h) {         // call after enqueuing main-stream work that touches x / s
     h->x_host = false;
     h->pose_fresh = false;
+    h->xpin_fresh = false;
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->stream));
     return EKF_OK;
 }
@@ -551,7 +554,8 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             }
         }
         CK(cudaMalloc(&h->x, sizeof(double) * h->ld));
-        CK(cudaMallocHost(&h->x_pin, sizeof(double) * h->ld));
+        CK(cudaHostAlloc(&h->x_pin, sizeof(double) * h->ld, cudaHostAllocMapped | cudaHostAllocPortable));
+        CK(cudaHostGetDevicePointer(&h->x_pin_dev, h->x_pin, 0));
         CK(cudaHostAlloc(&h->pose_host, 4 * sizeof(double), cudaHostAllocMapped | cudaHostAllocPortable));
         CK(cudaHostGetDevicePointer(&h->pose_dev, h->pose_host, 0));
         CK(cudaMalloc(&h->s, sizeof(double) * (p->capacity_landmarks + 1)));
@@ -914,7 +918,7 @@ static int32_t lazy_flush_and_batch(ekf_handle* h, const BatchObs& ob, ObSrc src
                           h->c_lo, std::min(h->c_hi, h->cap_n), m_old, h->Kd2, h->Bd2, 0, src);
     h->launches += 2;
     CK(cudaGetLastError());
-    h->x_host = false;
+    h->x_host = false; h->xpin_fresh = false; h->pose_fresh = false;
     if (h->async_x) CK(cudaEventRecord(h->ev_mx, h->sg));      // x of the batch is final after the gain kernel on sg
     CK(cudaEventRecord(h->ev_g2, h->sg));
     CK(cudaStreamWaitEvent(h->stream, h->ev_g2, 0));           // later main-stream work sees x and the new terms
@@ -1415,6 +1419,7 @@ static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
         }
         static int fr = -1;                                                 // EKF_BATCH_FRONT=0: gather, k_batch_lin, k_batch_gain(m0) one after another
         if (fr < 0) { const char* e = getenv("EKF_BATCH_FRONT"); fr = e ? atoi(e) : 1; }
+        double* xh = h->async_x ? h->x_pin_dev : nullptr;                   // the gains also write x into mapped host memory
         static int ct = -1;                                                 // EKF_CHAIN_TIMING=1 (debug): CUDA-event times of front and gains
         if (ct < 0) ct = getenv("EKF_CHAIN_TIMING") ? 1 : 0;
         if (fr && ct) {
@@ -1423,23 +1428,24 @@ static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
                 CK(cudaEventRecord(h->cev[h->cev_used], h->stream));
                 launch_batch_front_only(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, h->m_pend, src);
                 CK(cudaEventRecord(h->cev[h->cev_used + 1], h->stream));
-                launch_batch_gain_only(h->stream, h->P, h->ld, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, h->Kd, h->Bd, h->ld, h->m_pend, src);
+                launch_batch_gain_only(h->stream, h->P, h->ld, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, h->Kd, h->Bd, h->ld, h->m_pend, src, xh);
                 CK(cudaEventRecord(h->cev[h->cev_used + 2], h->stream));
                 h->cev_used += 3;
-            } else launch_batch_front_gain(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, h->m_pend, src);
+            } else launch_batch_front_gain(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, h->m_pend, src, xh);
             h->launches += 2;
         } else if (fr) {
             launch_batch_front_gain(h->stream, h->P, h->ld, h->strip, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld,
-                                    h->m_pend, src);
+                                    h->m_pend, src, xh);
             h->launches += 2;
         } else {
             launch_gather_cols_strip(h->stream, h->P, h->ld, n_of(h), ob, h->Pc, h->ld, src, h->strip);
             launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), 1, ob, h->blin, h->Kd, h->Bd, h->ld, h->Pc, h->ld,
-                                  0, n_of(h), h->m_pend, nullptr, nullptr, 0, src);
+                                  0, n_of(h), h->m_pend, nullptr, nullptr, 0, src, xh);
             h->launches += 3;
         }
         CK(cudaGetLastError());
         MARK_X(h);
+        if (xh) { h->xpin_fresh = true; h->x_head_dirty = false; }          // x_pin is x once ev_mx (just recorded) has fired
         h->m_pend += ob.k;
         if (h->m_pend - h->mA - h->mQ + std::min(h->defer, EKF_BATCH_MAX) > h->pend_cap)   // no further full chunk fits: its pass can start
             return shadow_close(h);
@@ -1457,14 +1463,16 @@ static int32_t fused_chunk(ekf_handle* h, const BatchObs& ob, ObSrc src) {
     const int m0 = h->xstep ? h->m_pend : 0;
     static int fr = -1;
     if (fr < 0) { const char* e = getenv("EKF_BATCH_FRONT"); fr = e ? atoi(e) : 1; }
+    double* xh = h->async_x ? h->x_pin_dev : nullptr;               // the gains also write x into mapped host memory
     if (fr && h->shadow && h->Pc && m0 > 0)         // in-place deferral on a handle that has the copies buffer: same front kernel, no strip
-        launch_batch_front_gain(h->stream, h->P, h->ld, nullptr, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, m0, src);
+        launch_batch_front_gain(h->stream, h->P, h->ld, nullptr, h->x, n_of(h), ob, h->blin, h->Pc, h->ld, 1, h->Kd, h->Bd, h->ld, m0, src, xh);
     else
         launch_batch_lin_gain(h->stream, h->P, h->ld, h->x, n_of(h), sym_of(h), ob, h->blin, h->Kd, h->Bd, h->ld,
-                              nullptr, 0, 0, 0, m0, nullptr, nullptr, 0, src);
+                              nullptr, 0, 0, 0, m0, nullptr, nullptr, 0, src, xh);
     h->launches += 2;
     CK(cudaGetLastError());
     MARK_X(h);                      // x is final for this chunk here, before the flush
+    if (xh) { h->xpin_fresh = true; h->x_head_dirty = false; }      // x_pin is x once ev_mx (just recorded) has fired
     h->m_pend = m0 + ob.k;
     if (!h->xstep || (h->m_pend >= h->pend_cap && !h->lazy)) FLUSH(h);   // lazy: a full set waits for the next batch
     return EKF_OK;
@@ -1723,12 +1731,18 @@ extern "C" int32_t ekf_get_x(ekf_handle* h, double* x, int32_t len) {
         int32_t rcq = h->xstep ? exec_sharded(h) : flush_sharded(h);
         if (rcq != EKF_OK) return rcq;
     }
-    if (h->async_x && h->x_pin && h->x_host && h->x_head_dirty && h->pose_fresh && h->world == 1) {
-        // only predict has run since the last read, and its state kernel wrote the new pose into mapped host memory:
-        // wait for that kernel, no copy at all
-        CK(cudaEventSynchronize(h->ev_px));
-        h->x_pin[0] = h->pose_host[0]; h->x_pin[1] = h->pose_host[1]; h->x_pin[2] = h->pose_host[2];
+    if (h->async_x && h->x_pin && h->world == 1 && (h->x_host || h->xpin_fresh) && (!h->x_head_dirty || h->pose_fresh)) {
+        // No copy at all: the body of x is in pinned memory already -- from the last read (x_host), or because the gain
+        // kernel of the last batch wrote it there beside the device copy (xpin_fresh: wait for that kernel's event) -- and
+        // if a predict has moved the pose since, its state kernel wrote the new pose into mapped memory too.
+        if (h->xpin_fresh) CK(cudaEventSynchronize(h->ev_mx));
+        if (h->x_head_dirty) {
+            CK(cudaEventSynchronize(h->ev_px));
+            h->x_pin[0] = h->pose_host[0]; h->x_pin[1] = h->pose_host[1]; h->x_pin[2] = h->pose_host[2];
+        }
         memcpy(x, h->x_pin, sizeof(double) * n_of(h));
+        h->x_host = true;
+        h->xpin_fresh = false;
         h->x_head_dirty = false;
         return after_sync(h);
     }

@@ -395,13 +395,17 @@ __global__ void __launch_bounds__(128)
 k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, int n, int sym, const BatchObs ob_arg,
              const BatchLin* __restrict__ lin, double2* __restrict__ Kall, double2* __restrict__ Ball, int64_t lds,
              const double* __restrict__ Pc, int64_t ldc, int c_lo, int c_hi, int m0,
-             double2* __restrict__ Kout, double2* __restrict__ Bout, int o0, ObSrc src) {
+             double2* __restrict__ Kout, double2* __restrict__ Bout, int o0, ObSrc src, double* __restrict__ xhost) {
+    // xhost (may be null): mapped pinned host copy of x, written beside x so that a caller who reads x after the batch waits
+    // for this kernel's event and needs no device-to-host copy behind it
     __shared__ BatchObs ob;
     stage_batch_obs(ob, ob_arg, src.ob);
     if (src.skip && *src.skip) {           // the batch contributes nothing: zero terms in its slots, x untouched
         const int i0 = blockIdx.x * blockDim.x + threadIdx.x;
-        if (i0 < n)
+        if (i0 < n) {
             for (int q = 0; q < ob.k; ++q) { Kout[(o0 + q) * lds + i0] = make_double2(0.0, 0.0); Bout[(o0 + q) * lds + i0] = make_double2(0.0, 0.0); }
+            if (xhost) xhost[i0] = x[i0];
+        }
         return;
     }
     // Kall / Ball: the m0 pending terms (read only).  The k new terms go to slots o0 .. o0+k-1 of Kout / Bout: the same
@@ -488,6 +492,7 @@ k_batch_gain(const double* __restrict__ P, int64_t ld, double* __restrict__ x, i
         }
     }
     x[i] = xi;
+    if (xhost) xhost[i] = xi;
 }
 
 // Raw copies of the slot columns of a batch, Pc[slot][i] = stored P(i, col(slot)) (SYM: the live element (min, max)):
@@ -1112,13 +1117,13 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 
 void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double* x, int n, int sym, const BatchObs& ob,
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc, int64_t ldc,
-                           int c_lo, int c_hi, int m0, double2* Kout, double2* Bout, int o0, ObSrc src) {
+                           int c_lo, int c_hi, int m0, double2* Kout, double2* Bout, int o0, ObSrc src, double* xhost) {
     if (!Pc) { c_lo = 0; c_hi = n; }
     if (!Kout) { Kout = Kall; Bout = Ball; o0 = m0; }
     k_batch_lin<<<1, 384, 0, st>>>(P, ld, x, sym, ob, lin, Pc, ldc, Kall, Ball, lds, m0, src);   // >= EKF_BATCH_SLOTS^2 = 361 threads
     static int gb = 0;                     // rows per CTA of the gain kernel (EKF_GAIN_BLOCK = 32 | 64 | 128, default 128)
     if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
-    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0, Kout, Bout, o0, src);
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, sym, ob, lin, Kall, Ball, lds, Pc, ldc, c_lo, c_hi, m0, Kout, Bout, o0, src, xhost);
 }
 
 
@@ -1130,16 +1135,16 @@ void launch_batch_front_only(cudaStream_t st, const double* P, int64_t ld, const
     k_batch_front<<<1 + rows, 128, 0, st>>>(P, ld, S, x, n, ob, lin, Pc, ldc, gather, Kall, Ball, lds, m0, src);
 }
 void launch_batch_gain_only(cudaStream_t st, const double* P, int64_t ld, double* x, int n, const BatchObs& ob, BatchLin* lin,
-                            double* Pc, int64_t ldc, double2* Kall, double2* Ball, int64_t lds, int m0, ObSrc src) {
+                            double* Pc, int64_t ldc, double2* Kall, double2* Ball, int64_t lds, int m0, ObSrc src, double* xhost) {
     static int gb = 0;
     if (gb == 0) { const char* v = getenv("EKF_GAIN_BLOCK"); gb = v ? atoi(v) : 128; if (gb != 32 && gb != 64) gb = 128; }
-    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, 1, ob, lin, Kall, Ball, lds, Pc, ldc, 0, n, 0, Kall, Ball, m0, src);
+    k_batch_gain<<<cdiv(n, gb), gb, 0, st>>>(P, ld, x, n, 1, ob, lin, Kall, Ball, lds, Pc, ldc, 0, n, 0, Kall, Ball, m0, src, xhost);
 }
 void launch_batch_front_gain(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
                              BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
-                             ObSrc src) {
+                             ObSrc src, double* xhost) {
     launch_batch_front_only(st, P, ld, S, x, n, ob, lin, Pc, ldc, gather, Kall, Ball, lds, m0, src);
-    launch_batch_gain_only(st, P, ld, x, n, ob, lin, Pc, ldc, Kall, Ball, lds, m0, src);
+    launch_batch_gain_only(st, P, ld, x, n, ob, lin, Pc, ldc, Kall, Ball, lds, m0, src, xhost);
 }
 
 void launch_append(cudaStream_t st, double* P, int64_t ld, double* x, double* s, int N, double u1, double u2,

@@ -33,17 +33,18 @@ void launch_batch_lin_gain(cudaStream_t st, const double* P, int64_t ld, double*
                            BatchLin* lin, double2* Kall, double2* Ball, int64_t lds, const double* Pc = nullptr,
                            int64_t ldc = 0, int c_lo = 0, int c_hi = 0, int m0 = 0,    // m0: terms already pending in slabs 0..m0-1; this batch fills m0..m0+k-1
                            double2* Kout = nullptr, double2* Bout = nullptr, int o0 = 0,    // ... or slots o0.. of another pair of slabs (lazy flush)
-                           ObSrc src = ObSrc{nullptr, nullptr});
+                           ObSrc src = ObSrc{nullptr, nullptr}, double* xhost = nullptr);   // xhost: mapped host copy of x written beside x
 // SYM storage: linearisation chain (block 0) beside the gather / pending-term correction of every row's slot entries (into Pc),
 // then the gains with nothing pending, written to slots m0..: bit-identical to launch_batch_lin_gain(..., m0), one launch less
 void launch_batch_front_gain(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
                              BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
-                             ObSrc src = ObSrc{nullptr, nullptr});
+                             ObSrc src = ObSrc{nullptr, nullptr}, double* xhost = nullptr);
 void launch_batch_front_only(cudaStream_t st, const double* P, int64_t ld, const double* S, double* x, int n, const BatchObs& ob,
                              BatchLin* lin, double* Pc, int64_t ldc, int gather, double2* Kall, double2* Ball, int64_t lds, int m0,
                              ObSrc src = ObSrc{nullptr, nullptr});
 void launch_batch_gain_only(cudaStream_t st, const double* P, int64_t ld, double* x, int n, const BatchObs& ob, BatchLin* lin,
-                            double* Pc, int64_t ldc, double2* Kall, double2* Ball, int64_t lds, int m0, ObSrc src = ObSrc{nullptr, nullptr});
+                            double* Pc, int64_t ldc, double2* Kall, double2* Ball, int64_t lds, int m0, ObSrc src = ObSrc{nullptr, nullptr},
+                            double* xhost = nullptr);
 void launch_gather_cols(cudaStream_t st, const double* P, int64_t ld, int n, int sym, const BatchObs& ob, double* Pc, int64_t ldc,
                         ObSrc src = ObSrc{nullptr, nullptr});
 // ---- continuous flush ("shadow", single GPU, SYM storage): robot strip S[4 j + r] = P0(r, j), r < 3; see ekf_kernels.cu ----
