@@ -454,3 +454,141 @@ def test_reference_witness_roundtrip_and_pin_if_present(tmp_path):
             if os.path.isdir(os.path.join(real, name)):
                 r = C.compare_case(name, real)
                 assert r['pinned'], (name, r)
+
+
+# ---------------------------------------------------------------- round 2: the continuous-flush schedule, modelled in NumPy
+def test_continuous_flush_schedule_on_the_dense_oracle():
+    """The bookkeeping behind the continuous flush, modelled in NumPy and checked against the
+    reference's dense algebra (oracle/dense_literal.py) over a loop of predicts and updates:
+
+      * the stored matrix `base` is only ever replaced by the output of a pass, base' = base - sum_{q in set} K_q B_q, computed
+        from the terms AS THEY WERE WHEN THE SET WAS CLOSED and finishing an arbitrary number of steps later;
+      * predict never touches `base`: it works on the robot strip (rows 0..2) and on the window of pending terms
+        (K_q <- F K_q, B_q <- B_q F');
+      * the current covariance every linearisation sees is  (base with rows / columns 0..2 taken from the strip)
+        - sum over the whole window (sets in flight + the set that is filling up);
+      * when a pass retires, the strip drops that set's terms (in their CURRENT, transformed form) and the pass's output
+        becomes `base`; rows 0..2 of that output are never read.
+
+    Only the upper triangle (i <= j) of anything is ever used, as in SYM storage."""
+    from oracle import dense_literal as O
+    from oracle.matlab_compat import sind, cosd, atan2d, wrapTo360, inv2
+    rng = np.random.default_rng(11)
+    N, T, k, cap = 9, 40, 3, 6                      # sets of <= 6 terms (the library: 16), 3 observations per step
+    n = 3 + 2 * N
+    A = rng.standard_normal((n, n))
+    P0 = A @ A.T / n * 0.05 + np.diag(np.concatenate([[0.1, 0.1, 0.05], np.full(2 * N, 0.3)]))
+    lms = rng.uniform(-20, 20, (N, 2))
+    x0 = np.concatenate([[0.5, -0.3, 30.0], (lms + rng.normal(0, 0.2, lms.shape)).ravel()])
+    o = O.EKF_SLAM()
+    o.x, o.P, o.s = x0.copy(), P0.copy(), list(range(1, N + 1))
+    C, Rc = o.C, o.Rc
+
+    def upper(M):                                   # what SYM storage keeps
+        return np.triu(M) + np.triu(M, 1).T
+
+    # ---- the model's state
+    x = x0.copy()
+    base = P0.copy()
+    strip = P0[:3, :].copy()                        # strip[r, j] = base(r, j), r < 3
+    window = []                                     # [K (n x 2), B (2 x n)] of every pending term, in order, current frame
+    passes = []                                     # in flight: (number of terms, output matrix computed at close time, steps left)
+    n_closed = 0                                    # terms of the window that belong to passes in flight (a prefix)
+
+    def current_P():
+        M = base.copy()
+        M[:3, :] = strip
+        M = upper(M)                                # column j < 3 below row 2 comes from the strip by symmetry
+        for K, B in window:
+            M = M - upper(np.triu(K @ B))           # element (i, j), i <= j: K_q(i,:) B_q(:,j)
+        return M
+
+    def retire():
+        nonlocal base, strip, window, n_closed
+        m, out, _ = passes.pop(0)
+        for K, B in window[:m]:
+            strip = strip - (K @ B)[:3, :]          # the set's terms as they are NOW (every predict since has transformed them)
+        base = out                                  # rows 0..2 of `out` are stale on purpose: never read
+        window = window[m:]
+        n_closed -= m
+
+    def close():
+        nonlocal n_closed
+        fill = window[n_closed:]
+        if not fill:
+            return
+        src = passes[-1][1] if passes else base     # a queued pass starts from the output of the one before it
+        out = src.copy()
+        for K, B in fill:
+            out = out - K @ B                       # frozen: the terms as they are at close time
+        out[:3, :] = np.nan                         # prove that nobody reads rows 0..2 of a pass's output ...
+        out[:, :3] = np.nan                         # ... nor columns 0..2 (their live part is rows 0..2)
+        passes.append((len(fill), out, int(rng.integers(1, 4))))
+        n_closed += len(fill)
+
+    for t in range(T):
+        u = np.array([0.3 + 0.1 * rng.random(), rng.normal(0, 3.0)])
+        # ---------------- predict: reference (dense) and model (strip + window)
+        th = x[2]
+        o.predict(u)
+        a, b = -1 * u[0] * sind(th), u[0] * cosd(th)
+        W = np.array([u[0] * cosd(th), u[0] * sind(th), u[1]])
+        M3 = upper(strip[:, :3].copy())
+        strip[0, 3:] += a * strip[2, 3:]; strip[1, 3:] += b * strip[2, 3:]
+        F3 = np.eye(3); F3[0, 2] = a; F3[1, 2] = b
+        strip[:, :3] = F3 @ M3 @ F3.T + np.outer(W * C, W)
+        for K, B in window:
+            K[0] += a * K[2]; K[1] += b * K[2]
+            B[:, 0] += a * B[:, 2]; B[:, 1] += b * B[:, 2]
+        x = x.copy()
+        x[0] += u[0] * cosd(th + u[1]); x[1] += u[0] * sind(th + u[1]); x[2] = wrapTo360(th + u[1])
+        # passes finish whenever they like
+        for i in range(len(passes)):
+            passes[i] = (passes[i][0], passes[i][1], passes[i][2] - 1)
+        # ---------------- k observations of known landmarks, applied one after another
+        ids = rng.choice(N, k, replace=False) + 1
+        if len(passes) == 2:                        # a queued pass writes into the buffer the chain reads: retire first
+            retire()
+        if len(window) - n_closed + k > cap:        # the filling set cannot take this batch: close it
+            close()
+            if len(passes) == 2:
+                retire()
+        for idx in ids:
+            tr = lms[idx - 1]
+            d = tr - x[:2]
+            z = np.array([np.hypot(*d) + rng.normal(0, 0.05), wrapTo360(atan2d(d[1], d[0]) - x[2]) + rng.normal(0, 0.5), idx])
+            R = np.diag([z[0] * Rc[0], z[1] * Rc[1]])
+            o._update(z, R, int(idx))
+            # model: the same formulas on the reconstructed covariance, at 5 columns
+            P = current_P()
+            c = [0, 1, 2, 3 + 2 * (idx - 1), 4 + 2 * (idx - 1)]
+            dk = x[c[3]:c[3] + 2] - x[:2]
+            q = float(dk @ dk); sq = np.sqrt(q)
+            zk = np.array([sq, wrapTo360(atan2d(dk[1], dk[0]) - x[2])])
+            H = (1.0 / q) * np.array([[-sq * dk[0], -sq * dk[1], 0.0, sq * dk[0], sq * dk[1]],
+                                      [dk[1], -dk[0], -q, -dk[1], dk[0]]])
+            PHt = P[:, c] @ H.T                    # n x 2
+            S = H @ P[np.ix_(c, c)] @ H.T + R
+            K = PHt @ inv2(S)
+            x = x + K @ (z[:2] - zk)
+            window.append([K, PHt.T.copy()])        # B = (P H')' in SYM storage
+        if len(window) - n_closed + k > cap and len(passes) < 2:
+            close()                                 # eager: the pass of a full set is enqueued at once
+        while passes and passes[0][2] <= 0 and len(passes) == 2:
+            retire()
+        if t % 7 == 6:                              # now and then somebody needs P whole: settle
+            while passes:
+                retire()
+            for K, B in window:
+                base = base - K @ B
+                strip = strip - (K @ B)[:3, :]
+            window, n_closed = [], 0
+            base[:3, :] = strip
+            base = upper(base)
+            assert np.linalg.norm(base - o.P) / np.linalg.norm(o.P) < 1e-10, t
+    while passes:
+        retire()
+    P_end = current_P()
+    assert not np.isnan(P_end).any()
+    assert np.linalg.norm(x - o.x) / np.linalg.norm(o.x) < 1e-10
+    assert np.linalg.norm(P_end - o.P) / np.linalg.norm(o.P) < 1e-10
