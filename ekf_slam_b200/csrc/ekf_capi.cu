@@ -30,6 +30,7 @@ struct ekf_handle {
     double2* Kd = nullptr;     // EKF_MAX_DEFER slabs of ld double2: gains K_q of the pending observations
     double2* Bd = nullptr;     // EKF_MAX_DEFER slabs: B_q = H_q P
     double* Bt = nullptr;      // (local columns) x EKF_BT_SROW: column-major copy of the pending B slabs for the hybrid flush kernels
+    double* Bt2 = nullptr;     // continuous flush: the operand of the other pass of the queue (packed when its set is closed)
     // ---- column-slab sharding (world > 1): this rank stores columns [c_lo, c_hi) of P, FULL storage ----
     int rank = 0, world = 1;
     int c_lo = 0, c_hi = 0;
@@ -349,7 +350,7 @@ extern "C" int32_t ekf_destroy(ekf_handle* h) {
     if (h->sf) cudaStreamSynchronize(h->sf);          // a K3 pass of the continuous flush may still be running
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto e : h->cev) cudaEventDestroy(e);
-    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd0 ? h->Kd0 : h->Kd); cudaFree(h->Bd0 ? h->Bd0 : h->Bd); cudaFree(h->Bt);
+    cudaFree(h->P); cudaFree(h->x); cudaFree(h->s); cudaFree(h->Kd0 ? h->Kd0 : h->Kd); cudaFree(h->Bd0 ? h->Bd0 : h->Bd); cudaFree(h->Bt); cudaFree(h->Bt2);
     cudaFree(h->Kd2); cudaFree(h->Bd2);
     if (h->sf) { cudaStreamSynchronize(h->sf); cudaStreamDestroy(h->sf); }
     if (h->ev_fz) cudaEventDestroy(h->ev_fz);
@@ -567,6 +568,7 @@ static int32_t create_common(const ekf_params* p, int rank, int world, const uin
             CK(cudaMemset(h->Bd0, 0, sizeof(double2) * h->ld * EKF_WIN_SLOTS));
         }
         CK(cudaMalloc(&h->Bt, sizeof(double) * EKF_BT_SROW * ((size_t)(h->c_hi - h->c_lo) + 16)));
+        if (h->shadow) CK(cudaMalloc(&h->Bt2, sizeof(double) * EKF_BT_SROW * ((size_t)(h->c_hi - h->c_lo) + 16)));
         CK(cudaMalloc(&h->lin, sizeof(Lin)));
         CK(cudaMalloc(&h->blin, sizeof(BatchLin)));
         CK(cudaMemset(h->lin, 0, sizeof(Lin)));
@@ -1117,12 +1119,15 @@ static int32_t shadow_close(ekf_handle* h) {
     const int slot = h->nfl == 0 ? h->fcur : (h->fcur ^ 1);
     const double2* Kset = h->Kd + (int64_t)off * h->ld;
     const double2* Bset = h->Bd + (int64_t)off * h->ld;
+    const int ncl = ncols_loc(h);                 // a slab passes its own columns (and B_q from its first column on)
+    double* bt = slot ? h->Bt2 : h->Bt;           // the pass two places back used this buffer: it has been retired
+    const bool pre = m > 8 && h->dd_variant < 0;  // the default (hybrid, operand in the stage) kernel: pack its B operand here, on the chain's stream
+    if (pre && ncl > 0) { launch_pack_bt(h->stream, Bset + h->c_lo, h->ld, m, ncl, bt); h->launches += 1; }
     CK(cudaEventRecord(h->ev_fz, h->stream));     // the set is complete; every gather enqueued so far has read the buffer a queued pass overwrites
     CK(cudaStreamWaitEvent(h->sf, h->ev_fz, 0));
     if (h->prof) { int32_t rc = prof_slot(h); if (rc != EKF_OK) return rc; CK(cudaEventRecord(h->ev[h->ev_used], h->sf)); }
     double* src = h->nfl == 0 ? h->P : h->P2;
     double* dst = h->nfl == 0 ? h->P2 : h->P;
-    const int ncl = ncols_loc(h);                 // a slab passes its own columns (and B_q from its first column on)
     // EKF_SHADOW_VARIANT: hybrid kernel shape of the overlapped pass.  Default = the library's (4-stage ring, 3 CTAs/SM).  The
     // 2-CTA/SM shapes (33, 35, 38: as fast when alone) leave a third of every SM free for the chain's CTAs -- measured at 10k:
     // end to end 23.6k -> 24.6k updates/s, but the pass itself slows from 0.563 to 0.603 ms beside them (resident 27.4k -> 26.2k).
@@ -1131,7 +1136,7 @@ static int32_t shadow_close(ekf_handle* h) {
     const int svh = sv != -3 ? sv : (h->world > 1 ? 33 : -1);     // slabs: the 2-CTA/SM shape (2 GPUs, 10k: 41.2k -> 44.3k updates/s)
     if (ncl > 0)
         launch_downdate(h->sf, src, h->ld, n_of(h), ncl, 1, Kset, Bset + h->c_lo, h->ld, m, h->c_lo,
-                        h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? svh : -1), h->Bt, dst);
+                        h->dd_variant >= 0 ? h->dd_variant : (m > 8 ? svh : -1), bt, dst, pre);
     if (h->prof) { CK(cudaEventRecord(h->ev[h->ev_used + 1], h->sf)); h->ev_used += 2; }
     CK(cudaEventRecord(h->ev_fd[slot], h->sf));
     CK(cudaGetLastError());

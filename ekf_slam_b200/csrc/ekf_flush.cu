@@ -645,7 +645,7 @@ k_downdate_hyb(const double* P, double* Pout, int64_t ld, int n, int ncols, cons
 
 template <int KS, int SCOLS, int NSTAGE, int BST, int MINB>
 static void launch_dd_hyb(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                          const double2* Ball, double* Bt, int64_t lds, int M, int col_off, double* Pout) {
+                          const double2* Ball, double* Bt, int64_t lds, int M, int col_off, double* Pout, bool prepacked) {
     typedef HybCfg<KS, SCOLS, NSTAGE, BST> C;
     smem_optin<k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB>>(C::SMEM);
     const int R = (n + C::TR - 1) / C::TR, CT = (ncols + C::TC - 1) / C::TC;
@@ -654,15 +654,16 @@ static void launch_dd_hyb(cudaStream_t st, double* P, int64_t ld, int n, int nco
       tm.order = !sym ? 0 : (ord == -2 ? 1 : ord); }
     const long long live = tm_prefix(tm, CT);
     if (live <= 0 || live > 0x3fffffffLL) return;
-    if (BST) k_pack_bt<KS><<<cdiv(ncols, 128), 128, 0, st>>>(Ball, lds, M, ncols, Bt);
+    if (BST && !prepacked) k_pack_bt<KS><<<cdiv(ncols, 128), 128, 0, st>>>(Ball, lds, M, ncols, Bt);
     k_downdate_hyb<KS, SCOLS, NSTAGE, BST, MINB><<<(unsigned)live, C::THREADS, C::SMEM, st>>>(P, Pout ? Pout : P, ld, n, ncols, Kall, Ball, Bt, lds, M, tm);
 }
 
 // hybrid variants by number (EKF_DOWNDATE_VARIANT >= 30); returns false when `v` names none
 template <int KS>
 static bool launch_dd_hyb_v(int v, cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
-                            const double2* Ball, double* Bt, int64_t lds, int M, int col_off, double* Pout = nullptr) {
-#define HY(SC, NS, BS, MB) launch_dd_hyb<KS, SC, NS, BS, MB>(st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, M, col_off, Pout); return true
+                            const double2* Ball, double* Bt, int64_t lds, int M, int col_off, double* Pout = nullptr,
+                            bool prepacked = false) {
+#define HY(SC, NS, BS, MB) launch_dd_hyb<KS, SC, NS, BS, MB>(st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, M, col_off, Pout, prepacked); return true
     if (Bt == nullptr && v != 30 && v != 37) return false;       // the in-stage operand needs the Bt scratch buffer
     switch (v) {
         case 30: HY(8, 4, 0, 3);       // operand tile per CTA as in k_downdate_tma, 4 x 8-col stages
@@ -687,9 +688,21 @@ static void launch_dd(cudaStream_t st, double* P, int64_t ld, int n, int ncols, 
 }
 
 
+// The B operand of the hybrid kernels, packed ahead of the pass (continuous flush: on the chain's stream when the set is
+// closed, into the buffer of that pass, so that nothing stands between two passes on the pass stream).
+void launch_pack_bt(cudaStream_t st, const double2* Ball, int64_t lds, int m, int ncols, double* Bt) {
+    if (m < 1 || ncols < 1) return;
+    switch ((m + 1) / 2) {
+#define PB(KS_) case KS_: k_pack_bt<KS_><<<cdiv(ncols, 128), 128, 0, st>>>(Ball, lds, m, ncols, Bt); break;
+        PB(1) PB(2) PB(3) PB(4) PB(5) PB(6) PB(7) PB(8)
+#undef PB
+        default: break;
+    }
+}
+
 // m pending rank-2 terms (1 <= m <= EKF_MAX_DEFER) applied in one pass over P.
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall, const double2* Ball,
-                     int64_t lds, int m, int col_off, int variant, double* Bt, double* Pout) {
+                     int64_t lds, int m, int col_off, int variant, double* Bt, double* Pout, bool prepacked) {
     if (m < 1) return;
     if (Pout && Pout != P) {
         // out of place (continuous flush): the hybrid kernels store straight from registers, so the destination is just
@@ -704,7 +717,7 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
     if (variant >= 30) {    // hybrid kernels (bulk-async in, registers out), any rank
         bool done = false;
         switch ((m + 1) / 2) {
-#define HV(KS_) case KS_: done = launch_dd_hyb_v<KS_>(variant, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
+#define HV(KS_) case KS_: done = launch_dd_hyb_v<KS_>(variant, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout, prepacked); break;
             HV(1) HV(2) HV(3) HV(4) HV(5) HV(6) HV(7) HV(8)
 #undef HV
             default: break;
@@ -725,10 +738,10 @@ void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, i
         bool done = false;
         if (Bt != nullptr && variant != 13 && variant != 21) {
             switch ((m + 1) / 2) {
-                case 5: done = launch_dd_hyb_v<5>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
-                case 6: done = launch_dd_hyb_v<6>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
-                case 7: done = launch_dd_hyb_v<7>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
-                default: done = launch_dd_hyb_v<8>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout); break;
+                case 5: done = launch_dd_hyb_v<5>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout, prepacked); break;
+                case 6: done = launch_dd_hyb_v<6>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout, prepacked); break;
+                case 7: done = launch_dd_hyb_v<7>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout, prepacked); break;
+                default: done = launch_dd_hyb_v<8>(32, st, P, ld, n, ncols, sym, Kall, Ball, Bt, lds, m, col_off, Pout, prepacked); break;
             }
         }
         if (done) return;

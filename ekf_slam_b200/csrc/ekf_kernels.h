@@ -23,7 +23,8 @@ void launch_linearize_gain(cudaStream_t st, const double* P, int64_t ld, double*
 // n rows x ncols columns of P (square: ncols == n; a column slab passes its own width and Ball + first column)
 void launch_downdate(cudaStream_t st, double* P, int64_t ld, int n, int ncols, int sym, const double2* Kall,
                      const double2* Ball, int64_t lds, int m, int col_off = 0, int variant = -1,
-                     double* Bt = nullptr, double* Pout = nullptr);   // col_off: global index of column 0 (SYM slabs); variant < 0: default; Bt: scratch of
+                     double* Bt = nullptr, double* Pout = nullptr, bool prepacked = false);   // prepacked: Bt already holds the B operand (launch_pack_bt)
+void launch_pack_bt(cudaStream_t st, const double2* Ball, int64_t lds, int m, int ncols, double* Bt);   // col_off: global index of column 0 (SYM slabs); variant < 0: default; Bt: scratch of
                                               // ncols x EKF_BT_SROW doubles for the kernels that carry the B operand in their stages
                                               // Pout != null: out of place, Pout = P - sum K_q B_q on every live tile, P untouched (continuous flush)
 #define EKF_BT_SROW (4 * 8 + 4)
