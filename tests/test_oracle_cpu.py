@@ -592,3 +592,59 @@ def test_continuous_flush_schedule_on_the_dense_oracle():
     assert not np.isnan(P_end).any()
     assert np.linalg.norm(x - o.x) / np.linalg.norm(o.x) < 1e-10
     assert np.linalg.norm(P_end - o.P) / np.linalg.norm(o.P) < 1e-10
+
+
+@pytest.mark.parametrize('cap', [16, 13, 11, 9])
+def test_continuous_flush_queue_bookkeeping_bounds(cap):
+    """A Python mirror of the host bookkeeping of the continuous flush (ekf_capi.cu: shadow_close / shadow_retire /
+    shadow_settle and the arrival logic of fused_chunk), run over long random sequences of batch sizes and settles:
+    the window of pending terms never exceeds EKF_MAX_WINDOW = 32 slabs (the kernels stage it in shared-memory arrays of
+    that size), never reaches past the EKF_WIN_SLOTS = 256 slabs of its allocation, at most two passes are outstanding,
+    and a closed set has 1..cap terms.  (The arithmetic of the schedule is the subject of the test above.)"""
+    import random
+    WIN, MAXW, CHUNK = 256, 32, 8
+    for seed in range(4):
+        rnd = random.Random(1000 * cap + seed)
+        st = dict(m_pend=0, mA=0, mQ=0, nfl=0, kw0=0)
+
+        def retire():
+            if st['nfl'] == 0:
+                return
+            st['kw0'] += st['mA']; st['m_pend'] -= st['mA']; st['mA'] = st['mQ']; st['mQ'] = 0; st['nfl'] -= 1
+
+        def close():
+            if st['m_pend'] - st['mA'] - st['mQ'] <= 0:
+                return
+            assert st['nfl'] < 2 and st['mQ'] == 0
+            if st['kw0'] + 2 * MAXW > WIN:                      # compaction: passes retired first, window back to the start
+                while st['nfl'] > 0:
+                    retire()
+                st['kw0'] = 0
+            m = st['m_pend'] - st['mA'] - st['mQ']
+            assert 1 <= m <= cap
+            if st['nfl'] == 0:
+                st['mA'] = m
+            else:
+                st['mQ'] = m
+            st['nfl'] += 1
+
+        for _ in range(20000):
+            if rnd.random() < 0.02:                             # a getter / append: settle
+                while st['nfl'] > 0:
+                    retire()
+                st['m_pend'] = 0; st['kw0'] = 0
+                continue
+            k = rnd.choice([1, 1, 2, 3, 5, 8, 8, 8])
+            if st['mQ'] > 0:
+                retire()
+            if st['m_pend'] - st['mA'] + k > cap:
+                close()
+                if st['mQ'] > 0:
+                    retire()
+            m0 = st['m_pend']
+            assert m0 < MAXW and m0 + k <= MAXW                 # staged pending terms, and the slots the batch writes
+            assert st['kw0'] + m0 + k <= WIN
+            assert st['nfl'] <= 2
+            st['m_pend'] += k
+            if st['m_pend'] - st['mA'] - st['mQ'] + CHUNK > cap:
+                close()
