@@ -8,8 +8,14 @@ evaluation order (dense F, Q, H_k, eye(n) -- O(n^3) exactly like the reference),
 keeping every quirk.  Each function cites the
 reference file:line it follows.
 
-parity unpinned: the reference has no tests / golden vectors and cannot be run
-here (no MATLAB/Octave in the image); the only pin is the source text itself.
+Parity status: the reference has no tests / golden vectors and MATLAB / Octave are
+absent from this image.  Since round 2 this restatement is pinned to the reference's
+SOURCE TEXT mechanically: oracle/mini_matlab.py executes the unmodified EKF_SLAM.m,
+EKF_SLAM_UC.m and Correspondence.m on the golden worlds, tests/golden/refrun_*.npz
+hold what they computed, and tests/test_oracle_cpu.py requires this module to agree
+(landmark counts and s exactly, x and P to 1e-12).  What stays unpinned are the
+MathWorks built-ins (matlab_compat.py), which both sides share: "parity unpinned" in
+that sense, until matlab/run_reference_fixture.m is run under MATLAB or Octave.
 """
 import numpy as np
 

@@ -5,7 +5,8 @@ calls.  Their source is NOT in /root/reference (MathWorks core + Mapping
 Toolbox, version unpinned by the reference), so the published semantics are
 restated here; call sites in the reference are cited per function.
 
-parity unpinned: the reference ships no golden vectors and MATLAB/Octave are
+parity unpinned (these built-ins; the reading of the reference's own statements is pinned by oracle/mini_matlab.py):
+the reference ships no golden vectors and MATLAB/Octave are
 absent from this image, so these helpers are pinned only by MathWorks'
 documented behaviour (exact values at multiples of 90 deg, wrapTo360(360)=360).
 """

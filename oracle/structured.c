@@ -14,8 +14,10 @@
  * the CUDA library (ekf_slam_b200/csrc/ekf_math_shared.h, < 1.3 ulp), every other operation is IEEE-exact, so index
  * decisions that hang on a cost comparison (association mode B) can be required to match the GPU bit for bit.
  *
- * parity unpinned: the reference has no tests / golden vectors and cannot be run here (no MATLAB/Octave in the
- * image); this file is pinned by the source text, by agreement with dense_literal.py on the golden worlds
+ * parity: pinned through oracle/dense_literal.py (which tests hold to the reference's source text as executed by
+ * oracle/mini_matlab.py, tests/golden/refrun_*.npz); MathWorks' built-ins stay unpinned: the reference has no tests /
+ * golden vectors and cannot be run under MATLAB/Octave here (neither is in the image).  This file itself is pinned by
+ * agreement with dense_literal.py on the golden worlds
  * (tests/test_oracle_cpu.py) and by the 50-digit mpmath restatement there.
  *
  * Layout: x[n] (x, y, theta_deg, l1x, l1y, ...), P column-major with leading dimension ld >= n_cap, s[N] signatures.

@@ -5,7 +5,8 @@ The reference (SamShue/EKF_SLAM, pure MATLAB) ships no golden vectors, tests or 
 this image (no MATLAB / Octave), so these vectors are produced by the dense-literal oracle (oracle/dense_literal.py,
 a line-by-line restatement of EKF_SLAM.m / EKF_SLAM_UC.m / Correspondence.m) on seeded synthetic worlds
 (ekf_slam_b200/synth.py).  They pin the oracle against regressions and give the GPU tests fixed
-byte-identical inputs/outputs; they do NOT pin the oracle to MATLAB ("parity unpinned").
+byte-identical inputs/outputs; they do NOT pin the oracle to the reference -- make_reference_run.py (refrun_*.npz: the
+reference's unmodified source executed by oracle/mini_matlab.py) does that for its statements, DESIGN.md section 6.
 """
 import os
 import sys

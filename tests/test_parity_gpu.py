@@ -293,6 +293,31 @@ def test_gpu_reproduces_golden_vectors(name, storage, defer_m):
     f.close()
 
 
+@pytest.mark.parametrize('storage,defer_m', [('full', 0), ('sym', 0), ('sym', 8), ('sym', 16)])
+@pytest.mark.parametrize('name', ['known_prefix_N20', 'known_quirk_N20', 'uc_nearest_N20', 'uc_nearest_N8_seed7'])
+def test_gpu_matches_the_reference_text_run(name, storage, defer_m):
+    """tests/golden/refrun_*.npz: what the UNMODIFIED EKF_SLAM.m / EKF_SLAM_UC.m / Correspondence.m computed on these
+    inputs, executed from their own source by oracle/mini_matlab.py (tests/golden/make_reference_run.py).  The CUDA path
+    through the class API: landmark count after every step and s exactly, x at every checkpoint, final x and P <= 1e-9."""
+    import os
+    import ekf_slam_b200 as E
+    from tests import golden_util as GU
+    g = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_%s.npz' % name)))
+    f = getattr(E, GU.CASES[name])(capacity_landmarks=20, storage=storage, defer_m=defer_m)
+    cps = {int(s): i for i, s in enumerate(g['checkpoint_steps'])}
+    for t, u, stub in GU.steps(g):
+        f.predict(u)
+        f.measure(None, u, stub)
+        assert f.N == int(g['n_landmarks'][t]), (name, t)
+        if (t + 1) in cps:
+            want = g['x_checkpoints'][cps[t + 1]]
+            want = want[~np.isnan(want)]
+            assert GU.rel(f.x, want) <= 1e-9, (name, t)
+    assert np.array_equal(f.s, g['s_final'].ravel())
+    assert GU.rel(f.x, g['x_final']) <= 1e-9 and GU.rel(f.P, g['P_final']) <= 1e-9
+    f.close()
+
+
 @pytest.mark.parametrize('storage', ['full', 'sym'])
 def test_gpu_golden_association_cases(storage):
     import ekf_slam_b200 as E
