@@ -5,7 +5,7 @@ property defaults and methods, functions with several outputs, if / for / switch
 white-space rules, ranges, 1-based indexing with growth on assignment, transpose, the matrix operators, struct-array
 field lists `[a.f]`, handle and value classes).  It exists for one purpose: to EXECUTE THE UNMODIFIED SOURCE TEXT of
 
-    EKF_SLAM.m   EKF_SLAM_UC.m   Correspondence.m
+    EKF_SLAM.m   EKF_SLAM_UC.m   Correspondence.m   (classes)      append.m   example.m: predict, f   (free functions)
 
 from a checkout of SamShue/EKF_SLAM (read where it lies, never copied) on the committed golden inputs, so that
 oracle/dense_literal.py -- the hand restatement every parity test leans on -- is compared with what the reference's own
@@ -149,7 +149,25 @@ class Parser:
         self.skip_nl()
         if self.peek().kind == 'KW' and self.peek().val == 'classdef':
             return self.parse_classdef()
-        raise MiniMatlabError('only classdef files are supported')
+        return self.parse_functions()
+
+    def parse_functions(self):
+        """A function file (append.m), or a script whose local functions follow the script part (example.m): the script
+        statements are skipped token by token up to the first `function` that starts a line; only the functions are kept."""
+        funcs = {}
+        at_line_start = True
+        while self.peek().kind != 'EOF':
+            tok = self.peek()
+            if at_line_start and tok.kind == 'KW' and tok.val == 'function':
+                f = self.parse_function()
+                funcs[f['name']] = f
+                at_line_start = True
+                continue
+            self.next()
+            at_line_start = tok.kind == 'NL'
+        if not funcs:
+            raise MiniMatlabError('no classdef and no function in this file')
+        return {'kind': 'functions', 'functions': funcs}
 
     def parse_classdef(self):
         self.expect('classdef')
@@ -531,6 +549,7 @@ def _num(v):
 class Interpreter:
     def __init__(self, stubs=None):
         self.classes = {}
+        self.functions = {}              # function files / local functions of a script, by name
         self.builtins = {
             'length': lambda a: float(max(a.shape)) if isinstance(a, np.ndarray) and a.size else 0.0,
             'numel': lambda a: float(a.size),
@@ -588,6 +607,9 @@ class Interpreter:
     # ---- loading
     def load_source(self, src):
         node = Parser(tokenize(src)).parse_file()
+        if node['kind'] == 'functions':
+            self.functions.update(node['functions'])
+            return sorted(node['functions'])
         node['handle'] = node['super'] == 'handle'
         self.classes[node['name']] = node
         return node['name']
@@ -637,6 +659,8 @@ class Interpreter:
             return [np.array([[float(shp[0])]]), np.array([[float(shp[1])]])]
         if name in self.classes:
             return [self.construct(name, args)]
+        if name in self.functions:
+            return self.call_function(self.functions[name], args, nargout)
         if name in self.builtins:
             out = self.builtins[name](*args)
             return [to_matlab(out)]

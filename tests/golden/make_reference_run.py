@@ -79,8 +79,40 @@ def association_case(ref_dir):
     return dict(x=a['x'], P=a['P'], s=a['s'], z=a['z'], Rdiag=a['Rdiag'], mode_a=np.array(out, dtype=np.int32))
 
 
+def functions_case(ref_dir, seed=3, cases=6):
+    """The free-function forms of the path the reference also ships: append.m:1-27 `[x,P]=append(x,P,u,idx,R,pos)`
+    and the local functions of example.m:24-45, `[x,P]=predict(x,u,P,C)` and `[x_new,F]=f(x,u)`, executed from their own
+    source on seeded states of 0..5 landmarks (append: once with idx beyond the map -- the landmark is added -- and once
+    with idx inside it -- nothing changes)."""
+    it = Interpreter()
+    it.load_file(os.path.join(ref_dir, 'append.m'))
+    it.load_file(os.path.join(ref_dir, 'example.m'))
+    rng = np.random.default_rng(seed)
+    out = {'n_cases': np.array(cases, dtype=np.int32)}
+    for c in range(cases):
+        nl = c
+        n = 3 + 2 * nl
+        A = rng.standard_normal((n, n))
+        P = 0.01 * (A @ A.T) + 0.1 * np.eye(n)
+        x = np.concatenate([[rng.uniform(-2, 2), rng.uniform(-2, 2), rng.uniform(0, 720)], rng.uniform(-8, 8, 2 * nl)])
+        u = np.array([rng.uniform(0.1, 1.5), rng.uniform(-40, 40)])
+        R = np.diag([0.01 * rng.uniform(0.5, 3), 5.0])
+        pos = rng.uniform(-8, 8, 2)
+        M = [to_matlab(v) for v in (x, P, u)]
+        xa, Pa = it.call('append', M + [to_matlab(float(nl + 1)), to_matlab(R), to_matlab(pos)], 2, {})
+        xk, Pk = it.call('append', M + [to_matlab(float(max(nl, 0))), to_matlab(R), to_matlab(pos)], 2, {})
+        xp, Pp = it.call('predict', [to_matlab(x), to_matlab(u), to_matlab(P), to_matlab(0.2)], 2, {})
+        xf, F = it.call('f', [to_matlab(x), to_matlab(u)], 2, {})
+        out.update({'x%d' % c: x, 'P%d' % c: P, 'u%d' % c: u, 'R%d' % c: R, 'pos%d' % c: pos,
+                    'append_x%d' % c: xa.ravel(), 'append_P%d' % c: Pa, 'keep_x%d' % c: xk.ravel(), 'keep_P%d' % c: Pk,
+                    'predict_x%d' % c: xp.ravel(), 'predict_P%d' % c: Pp, 'f_x%d' % c: xf.ravel(), 'f_F%d' % c: F})
+    return out
+
+
 def main():
     ref_dir = sys.argv[1] if len(sys.argv) > 1 else '/root/reference'
+    np.savez_compressed(os.path.join(HERE, 'refrun_functions.npz'), **functions_case(ref_dir))
+    print('functions: append.m, example.m predict / f on 6 seeded states')
     for name, cls in GU.CASES.items():
         out = run_case(ref_dir, cls, in_domain(GU.load(name)))
         np.savez_compressed(os.path.join(HERE, 'refrun_%s.npz' % name), **out)

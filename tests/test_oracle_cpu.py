@@ -2,6 +2,7 @@
 quirks, and an independent 50-digit mpmath restatement of the update/predict/append algebra
 that pins the oracle's floating-point path to the exact value of the source expressions."""
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -696,6 +697,29 @@ def test_oracle_association_matches_the_reference_text_run():
     assert 0 < int(a['mode_a'][:, 0].sum()) < len(got)
 
 
+def test_oracle_matches_the_reference_free_functions():
+    """append.m:1-27 and example.m:24-45 (predict, f) -- the free-function forms SURVEY 8(a) cites beside the class methods --
+    executed from their own source (tests/golden/refrun_functions.npz): the oracle's append / predict / f give the same
+    x, P and F bit for bit on states of 0..5 landmarks; an index inside the map leaves x and P untouched (append.m:4)."""
+    from oracle import dense_literal as O
+    from tests import golden_util as GU
+    g = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_functions.npz')))
+    for c in range(int(g['n_cases'])):
+        x, P, u, R, pos = (g['%s%d' % (k, c)] for k in ('x', 'P', 'u', 'R', 'pos'))
+        o = O.EKF_SLAM(); o.x = x.copy(); o.P = P.copy(); o.s = [float(i) for i in range((x.size - 3) // 2)]
+        o.append(u, R, pos, 99.0)
+        assert np.array_equal(o.x, g['append_x%d' % c]) and np.array_equal(o.P, g['append_P%d' % c]), c
+        assert g['append_x%d' % c].size == x.size + 2
+        assert np.array_equal(g['keep_x%d' % c], x) and np.array_equal(g['keep_P%d' % c], P), c
+        o = O.EKF_SLAM(); o.x = x.copy(); o.P = P.copy()
+        o.predict(u)
+        assert np.array_equal(o.x, g['predict_x%d' % c]) and np.array_equal(o.P, g['predict_P%d' % c]), c
+        assert 0.0 <= o.x[2] < 360.0 or o.x[2] == 360.0
+        o = O.EKF_SLAM(); o.x = x.copy(); o.P = P.copy()
+        xn, F = o.f(x, u)
+        assert np.array_equal(np.asarray(xn).ravel(), g['f_x%d' % c]) and np.array_equal(F, g['f_F%d' % c]), c
+
+
 def test_mini_matlab_grammar_known_answers():
     """The interpreter that executes the reference text (oracle/mini_matlab.py) against MATLAB's documented behaviour on
     the constructs the three files use: white space inside [ ], transpose versus string quote, precedence of unary minus
@@ -834,6 +858,14 @@ def test_reference_run_fixture_is_reproducible():
         r.measure(None, u, stub)
     assert np.array_equal(r.x, g['x_final']) and np.array_equal(r.P, g['P_final']) and np.array_equal(r.s, g['s_final'].ravel())
     assert np.array_equal(np.array(r.n_landmarks), g['n_landmarks'])
+    sys.path.insert(0, GU.GOLDEN)
+    try:
+        import make_reference_run as MR
+        f = MR.functions_case('/root/reference')
+    finally:
+        sys.path.remove(GU.GOLDEN)
+    gf = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_functions.npz')))
+    assert sorted(f) == sorted(gf) and all(np.array_equal(f[k], gf[k]) for k in gf)
     g0 = GU.load('known_quirk_N20')                  # the original world: 5 new landmarks in the first frame
     r = ReferenceFilter('/root/reference', 'EKF_SLAM')
     t, u, stub = next(GU.steps(g0))
