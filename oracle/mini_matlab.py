@@ -26,7 +26,9 @@ Grammar notes (only what the three files need; anything else raises MiniMatlabEr
   * precedence, tightest first: postfix ' and ^ ; unary + - ~ ; * / .* ./ ; + - ; : ; comparisons ; & ; | ; && ; ||
     (an exponent may carry its own unary minus: `phi_k^-1`);
   * `x(i)` on a vector keeps the vector's orientation; `x(i) = v`, `A(i,j) = V` grow the array with zeros;
-  * `A^-1` of a square matrix is the inverse (matlab_compat.inv2), `a*B` with a scalar operand is element-wise.
+  * `A^-1` of a square matrix is the inverse (matlab_compat.inv2), `a*B` with a scalar operand is element-wise;
+  * `name word` at statement level is command syntax, name('word')  (`hold on` in the classes' plot method);
+  * a file that is not a classdef contributes its functions (append.m; the local functions behind example.m's script part).
 """
 import copy
 import re
@@ -305,6 +307,10 @@ class Parser:
                 self.next()
                 return ('return', tok.line)
             raise MiniMatlabError('line %d: statement %r not supported' % (tok.line, tok.val))
+        if tok.kind == 'ID' and self.peek(1).kind == 'ID' and self.peek(1).sp and \
+                (self.peek(2).kind in ('NL', 'EOF') or (self.peek(2).kind == 'OP' and self.peek(2).val in (';', ','))):
+            self.next(); arg = self.next().val              # command syntax: `hold on` is hold('on')
+            return ('expr', ('index', ('id', tok.val), [('str', arg)]), tok.line)
         lhs = self.parse_expr()
         if self.at('='):
             self.next()
@@ -560,6 +566,10 @@ class Interpreter:
             'sind': lambda a: self._ew(MC.sind, a),
             'atan2d': lambda y, x: np.array([[MC.atan2d(float(_num(y).ravel()[0]), float(_num(x).ravel()[0]))]]),
             'wrapTo360': lambda a: self._ew(MC.wrapTo360, a),
+            'cos': lambda a: np.cos(_num(a)),
+            'sin': lambda a: np.sin(_num(a)),
+            'atan': lambda a: np.arctan(_num(a)),
+            'eig': None,                 # two outputs: handled in call()
             'find': self._find,
             'zeros': self._zeros,
             'eye': self._eye,
@@ -657,6 +667,12 @@ class Interpreter:
             if nargout <= 1:
                 return [np.array([[float(shp[0]), float(shp[1])]])]
             return [np.array([[float(shp[0])]]), np.array([[float(shp[1])]])]
+        if name == 'eig':
+            # MathWorks built-in (LAPACK): a symmetric input gives ascending eigenvalues and orthonormal vectors (dsyev),
+            # anything else goes through the general solver; [V,D] = eig(A) returns D as a diagonal matrix.
+            a = _num(args[0])
+            w, v = np.linalg.eigh(a) if np.array_equal(a, a.T) else np.linalg.eig(a)
+            return [v, np.diag(w)] if nargout >= 2 else [w.reshape(-1, 1)]
         if name in self.classes:
             return [self.construct(name, args)]
         if name in self.functions:
@@ -1039,7 +1055,10 @@ class ReferenceFilter:
 
     def __init__(self, ref_dir, cls_name):
         import os
-        self.it = Interpreter(stubs={'RANSAC': lambda: np.zeros((0, 0))})
+        self.curves = []                 # what plot() hands to the figure: one (xr, yr) pair per ellipse
+        noop = lambda *a: None
+        self.it = Interpreter(stubs={'RANSAC': lambda: np.zeros((0, 0)), 'hold': noop, 'drawRobot': noop, 'scatter': noop,
+                                     'plot': lambda xr, yr: self.curves.append((_num(xr).ravel().copy(), _num(yr).ravel().copy()))})
         for f in ('Correspondence.m', 'EKF_SLAM.m', 'EKF_SLAM_UC.m'):
             self.it.load_file(os.path.join(ref_dir, f))
         self.obj = self.it.construct(cls_name, [])
@@ -1055,6 +1074,16 @@ class ReferenceFilter:
     def measure(self, laserData, u, landmark_list):
         self._method('measure', laserData, np.asarray(u, dtype=np.float64), PyObj(landmark_list))
         self.n_landmarks.append((self.x.size - 3) // 2)
+
+    def plot_curves(self):
+        """Run the class's own plot(h, landmark_list) (EKF_SLAM.m:154-234) with the figure calls (hold, drawRobot, scatter,
+        the landmark object's plot) as no-ops and plot(xr, yr) as a recorder: returns the covariance-ellipse polylines the
+        reference would draw, robot first, as an array (1 + N, 2, len(t))."""
+        from types import SimpleNamespace
+        self.curves = []
+        lm = SimpleNamespace(landmarkObj=SimpleNamespace(plot=lambda x, observed: None))
+        self._method('plot', PyObj(lm))
+        return np.array([[cx, cy] for cx, cy in self.curves])
 
     @property
     def x(self):

@@ -60,6 +60,9 @@ def run_case(ref_dir, cls, g, every=25):
     out = dict(g)
     out.update(x_final=r.x, P_final=r.P, s_final=r.s, n_landmarks=np.array(r.n_landmarks, dtype=np.int32),
                x_checkpoints=np.array(xs), checkpoint_steps=np.array(cps, dtype=np.int32))
+    # the class's own plot() on the final state (EKF_SLAM.m:154-234), figure calls recorded instead of drawn: the
+    # covariance-ellipse polylines, robot first; every 4th of the 629 points of t = -pi:0.01:pi is kept
+    out['ellipse_curves'] = r.plot_curves()[:, :, ::4]
     return out
 
 

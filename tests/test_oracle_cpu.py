@@ -697,6 +697,26 @@ def test_oracle_association_matches_the_reference_text_run():
     assert 0 < int(a['mode_a'][:, 0].sum()) < len(got)
 
 
+@pytest.mark.parametrize('name', REFRUN_CASES)
+def test_oracle_ellipses_match_the_reference_plot_text(name):
+    """EKF_SLAM.plot / EKF_SLAM_UC.plot (EKF_SLAM.m:154-234) executed from source on the final state of each reference
+    run, figure calls recorded instead of drawn: the polylines it hands to plot(xr, yr) are the ellipses
+    oracle.ellipse_params describes (centre, semi-axes along the drawn x / y directions, rotation), robot first, to 1e-12
+    of the map's extent.  (eig, cos, sin, atan are MathWorks built-ins, served by NumPy on both sides.)"""
+    from oracle import dense_literal as O
+    from tests import golden_util as GU
+    g = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_%s.npz' % name)))
+    e = O.ellipse_params(g['x_final'], g['P_final'])
+    c = g['ellipse_curves']
+    assert c.shape == (1 + (g['x_final'].size - 3) // 2, 2, 158)
+    t = (-np.pi + 0.01 * np.arange(629))[::4]
+    scale = max(1.0, float(np.abs(g['x_final']).max()))
+    for k, (cx, cy, ax, ay, arc) in enumerate(e):
+        X = cx + np.cos(arc) * ax * np.cos(t) - np.sin(arc) * ay * np.sin(t)
+        Y = cy + np.sin(arc) * ax * np.cos(t) + np.cos(arc) * ay * np.sin(t)
+        assert max(np.abs(X - c[k, 0]).max(), np.abs(Y - c[k, 1]).max()) <= 1e-12 * scale, (name, k)
+
+
 def test_oracle_matches_the_reference_free_functions():
     """append.m:1-27 and example.m:24-45 (predict, f) -- the free-function forms SURVEY 8(a) cites beside the class methods --
     executed from their own source (tests/golden/refrun_functions.npz): the oracle's append / predict / f give the same
@@ -809,10 +829,27 @@ classdef T < handle
         function r = m16(h)
             r = size(zeros(3,5),1) + length(zeros(3,5))*10 + size(eye(size(zeros(4,4))),2)*100;
         end
+        function r = m17(h)
+            t = -1:0.5:1;
+            r = [t(1) t(5) length(t)];
+        end
+        function r = m18(h)
+            hold on;
+            [V,D] = eig([2 0; 0 1]);
+            hold off
+            r = [D(1,1) D(2,2) abs(V(2,1)) abs(V(1,2))];
+        end
+        function r = m19(h)
+            r = 0;
+            for ii=4:2:9
+                r = r*10 + ii;
+            end
+        end
     end
 end
 """
-    it = Interpreter()
+    held = []
+    it = Interpreter(stubs={'hold': lambda s: held.append(s)})
     it.load_source(src)
     t = it.construct('T', [])
 
@@ -837,6 +874,10 @@ end
     assert call('m14')[0][0, 0] == 111
     assert np.array_equal(call('m15')[0], [[5], [2]])
     assert call('m16')[0][0, 0] == 3 + 50 + 400
+    assert np.array_equal(call('m17')[0], [[-1, 1, 5]])                # a:step:b
+    assert np.array_equal(call('m19')[0], [[468]])                     # 4:2:9 stops at 8
+    assert np.array_equal(call('m18')[0], [[1, 2, 1, 1]])              # eig of a symmetric matrix: ascending, D diagonal
+    assert held == ['on', 'off']                                       # command syntax: `hold on` is hold('on')
     a, b = call('two', np.array([4.0, 9.0]), nargout=2)
     assert a.shape == (2, 1) and np.array_equal(b, [[4, -9]])
     call('bump', nargout=0); call('bump', nargout=0)
@@ -858,6 +899,7 @@ def test_reference_run_fixture_is_reproducible():
         r.measure(None, u, stub)
     assert np.array_equal(r.x, g['x_final']) and np.array_equal(r.P, g['P_final']) and np.array_equal(r.s, g['s_final'].ravel())
     assert np.array_equal(np.array(r.n_landmarks), g['n_landmarks'])
+    assert np.array_equal(r.plot_curves()[:, :, ::4], g['ellipse_curves'])
     sys.path.insert(0, GU.GOLDEN)
     try:
         import make_reference_run as MR
