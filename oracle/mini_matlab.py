@@ -12,6 +12,11 @@ oracle/dense_literal.py -- the hand restatement every parity test leans on -- is
 statements compute, statement by statement as MATLAB's grammar orders them, and not only with a reading of them
 (tests/golden/make_reference_run.py writes the vectors, tests/test_oracle_cpu.py checks the oracle against them).
 
+A second use (tests/matlab_host.py, tests/test_matlab_classes.py): the repo's own MATLAB host classes in matlab/ are
+executed by the same interpreter -- for them it also knows superclass chains (`h@Base(...)`, `method@Base(h, ...)`),
+Dependent properties served by get.p / set.p, nargin, scalar structs, `~` inputs and stand-ins for MEX files that
+see nargout -- because no MATLAB or Octave exists here to run them.
+
 What this does and does not pin.  MATLAB and Octave are absent from this image and from the GPU box; the MathWorks
 run-time functions the reference calls (sind, cosd, atan2d, wrapTo360, the LAPACK inverse behind `^-1`, the BLAS behind
 `*`) are closed source and are served here by the same restatements the oracle uses (oracle/matlab_compat.py, NumPy).  So a
@@ -177,12 +182,12 @@ class Parser:
         sup = None
         if self.at('<'):
             self.next(); sup = self.next().val
-        props, methods = [], {}
+        props, methods, dependent = [], {}, set()
         self.skip_nl()
         while not (self.peek().kind == 'KW' and self.peek().val == 'end'):
             kw = self.next()
             if kw.val == 'properties':
-                self._skip_attrs(); self.skip_nl()
+                attrs = self._skip_attrs(); self.skip_nl()
                 while not (self.peek().kind == 'KW' and self.peek().val == 'end'):
                     pname = self.next()
                     if pname.kind != 'ID':
@@ -190,7 +195,10 @@ class Parser:
                     default = None
                     if self.at('='):
                         self.next(); default = self.parse_expr()
-                    props.append((pname.val, default))
+                    if 'Dependent' in attrs:
+                        dependent.add(pname.val)         # no storage: served by get.<name> / set.<name>
+                    else:
+                        props.append((pname.val, default))
                     self.skip_nl()
                 self.expect('end'); self.skip_nl()
             elif kw.val == 'methods':
@@ -203,9 +211,10 @@ class Parser:
             else:
                 raise MiniMatlabError('line %d: unexpected %r in classdef' % (kw.line, kw.val))
         self.expect('end')
-        return {'kind': 'class', 'name': name, 'super': sup, 'props': props, 'methods': methods}
+        return {'kind': 'class', 'name': name, 'super': sup, 'props': props, 'methods': methods, 'dependent': dependent}
 
     def _skip_attrs(self):
+        seen = []
         if self.at('('):
             depth = 0
             while True:
@@ -216,6 +225,9 @@ class Parser:
                     depth -= 1
                     if depth == 0:
                         break
+                elif tok.kind == 'ID':
+                    seen.append(tok.val)
+        return seen
 
     def parse_function(self):
         self.expect('function')
@@ -234,6 +246,8 @@ class Parser:
                 self.next(); outs = [first]; name = self.next().val
             else:
                 name = first
+        if name in ('get', 'set') and self.at('.') and self.peek(1).kind == 'ID':      # property accessors: get.x / set.x
+            self.next(); name = name + '.' + self.next().val
         params = []
         if self.at('('):
             self.next()
@@ -241,6 +255,8 @@ class Parser:
                 tok = self.next()
                 if tok.kind == 'ID':
                     params.append(tok.val)
+                elif tok.kind == 'OP' and tok.val == '~':
+                    params.append('~')                     # an ignored input still takes its position
             self.expect(')')
         body = self.parse_block(('end',))
         self.expect('end')
@@ -418,6 +434,8 @@ class Parser:
                 a = ('index', a, args)
             elif tok.kind == 'OP' and tok.val == '.' and self.peek(1).kind == 'ID' and not tok.sp:
                 self.next(); a = ('field', a, self.next().val)
+            elif tok.kind == 'OP' and tok.val == '@' and not tok.sp and a[0] == 'id' and self.peek(1).kind == 'ID':
+                self.next(); a = ('superref', a[1], self.next().val)     # h@Base(...) / method@Base(h, ...)
             else:
                 return a
 
@@ -495,6 +513,13 @@ class PyObj:
         self.o = o
 
 
+class MStruct:
+    """A scalar MATLAB struct built inside the interpreter (struct(), s.f = v): a value type."""
+
+    def __init__(self, fields=None):
+        self.f = dict(fields or {})
+
+
 class _Return(Exception):
     pass
 
@@ -504,6 +529,8 @@ def _copy_value(v):
         return v.copy()
     if isinstance(v, MObject):
         return v if v.cls['handle'] else v.copy()
+    if isinstance(v, MStruct):
+        return MStruct({k: _copy_value(e) for k, e in v.f.items()})
     return v
 
 
@@ -511,8 +538,10 @@ def to_matlab(v):
     """Python value -> interpreter value."""
     if v is None:
         return np.zeros((0, 0))
-    if isinstance(v, (MObject, StructArray, PyObj, str, BoundMethod)):
+    if isinstance(v, (MObject, StructArray, PyObj, str, BoundMethod, MStruct)):
         return v
+    if isinstance(v, np.ndarray) and v.dtype == np.uint64:
+        return v.reshape(1, 1).copy() if v.ndim < 2 else v.copy()
     if isinstance(v, (bool, np.bool_)):
         return np.array([[bool(v)]])
     if isinstance(v, (int, float, np.integer, np.floating)):
@@ -555,6 +584,7 @@ def _num(v):
 class Interpreter:
     def __init__(self, stubs=None):
         self.classes = {}
+        self._in_accessor = set()        # (object, accessor) pairs being served: inside get.p / set.p the property is plain
         self.functions = {}              # function files / local functions of a script, by name
         self.builtins = {
             'length': lambda a: float(max(a.shape)) if isinstance(a, np.ndarray) and a.size else 0.0,
@@ -570,6 +600,14 @@ class Interpreter:
             'sin': lambda a: np.sin(_num(a)),
             'atan': lambda a: np.arctan(_num(a)),
             'eig': None,                 # two outputs: handled in call()
+            'uint64': lambda a: np.array([[int(_num(a).ravel()[0])]], dtype=np.uint64),
+            'strcmp': lambda a, b: isinstance(a, str) and isinstance(b, str) and a == b,
+            'max': lambda a, b=None: np.max(_num(a)) if b is None else np.maximum(_num(a), _num(b)),
+            'min': lambda a, b=None: np.min(_num(a)) if b is None else np.minimum(_num(a), _num(b)),
+            'struct': self._struct,
+            'isfield': lambda st, name: isinstance(st, MStruct) and name in st.f,
+            'reshape': self._reshape,
+            'error': self._error,
             'find': self._find,
             'zeros': self._zeros,
             'eye': self._eye,
@@ -609,6 +647,47 @@ class Interpreter:
         return np.eye(r, c)
 
     @staticmethod
+    def _struct(*args):
+        if len(args) % 2:
+            raise MiniMatlabError('struct: field names and values come in pairs')
+        return MStruct({args[i]: args[i + 1] for i in range(0, len(args), 2)})
+
+    @staticmethod
+    def _reshape(a, *dims):
+        a = _num(a)
+        if len(dims) == 1:
+            dims = tuple(_num(dims[0]).ravel())
+        d = [None if (isinstance(x, np.ndarray) and x.size == 0) else int(_num(x).ravel()[0]) for x in dims]
+        if d.count(None) > 1 or len(d) != 2:
+            raise MiniMatlabError('reshape: two dimensions, at most one of them []')
+        if None in d:
+            known = d[1 - d.index(None)]
+            if known == 0 or a.size % known:
+                raise MiniMatlabError('reshape: size is not divisible')
+            d[d.index(None)] = a.size // known
+        if d[0] * d[1] != a.size:
+            raise MiniMatlabError('reshape: number of elements must not change')
+        return a.reshape((d[0], d[1]), order='F').copy()
+
+    @staticmethod
+    def _error(ident, *rest):
+        raise MiniMatlabError('error %s: %s' % (ident, rest[0] if rest else ''))
+
+    # ---- classes: inheritance
+    def _chain(self, cls):
+        """The class and its user-defined superclasses, most derived first (`handle` ends the chain)."""
+        out = [cls]
+        while out[-1]['super'] in self.classes:
+            out.append(self.classes[out[-1]['super']])
+        return out
+
+    def find_method(self, cls, name):
+        for c in self._chain(cls):
+            if name in c['methods']:
+                return c['methods'][name]
+        return None
+
+    @staticmethod
     def _find(a):
         a = _num(a)
         idx = np.flatnonzero(a.ravel(order='F') != 0) + 1.0
@@ -620,7 +699,7 @@ class Interpreter:
         if node['kind'] == 'functions':
             self.functions.update(node['functions'])
             return sorted(node['functions'])
-        node['handle'] = node['super'] == 'handle'
+        node['handle'] = node['super'] == 'handle' or (node['super'] in self.classes and self.classes[node['super']]['handle'])
         self.classes[node['name']] = node
         return node['name']
 
@@ -632,19 +711,23 @@ class Interpreter:
     def construct(self, name, args):
         cls = self.classes[name]
         obj = MObject(cls)
-        for pname, default in cls['props']:
-            obj.props[pname] = self.eval(default, {}) if default is not None else np.zeros((0, 0))
-        ctor = cls['methods'].get(name)
-        if ctor is None:
-            return obj
-        return self.call_function(ctor, args, 1, preset={ctor['outs'][0]: obj})[0]
+        for c in reversed(self._chain(cls)):
+            for pname, default in c['props']:
+                obj.props[pname] = self.eval(default, {}) if default is not None else np.zeros((0, 0))
+        for c in self._chain(cls):                       # a class without a constructor hands its arguments up
+            ctor = c['methods'].get(c['name'])
+            if ctor is not None:
+                return self.call_function(ctor, args, 1, preset={ctor['outs'][0]: obj})[0]
+        return obj
 
     def call_function(self, f, args, nargout, preset=None):
         if len(args) > len(f['params']):
             raise MiniMatlabError('%s: too many input arguments' % f['name'])
         env = dict(preset or {})
+        env['nargin'] = np.array([[float(len(args))]])
         for p, a in zip(f['params'], args):
-            env[p] = _copy_value(a)
+            if p != '~':
+                env[p] = _copy_value(a)
         try:
             self.exec_block(f['body'], env)
         except _Return:
@@ -677,8 +760,15 @@ class Interpreter:
             return [self.construct(name, args)]
         if name in self.functions:
             return self.call_function(self.functions[name], args, nargout)
+        if args and isinstance(args[0], MObject) and name not in self.builtins:       # function-call form of a method: delete(obj)
+            m = self.find_method(args[0].cls, name)
+            if m is not None:
+                return self.call_function(m, args, nargout)
         if name in self.builtins:
-            out = self.builtins[name](*args)
+            fn = self.builtins[name]
+            if getattr(fn, 'wants_nargout', False):        # a stand-in for a MEX file: fn(nargout, *args) -> list of outputs
+                return [to_matlab(o) for o in fn(nargout, *args)]
+            out = fn(*args)
             return [to_matlab(out)]
         raise MiniMatlabError('undefined function or variable %r' % name)
 
@@ -750,7 +840,7 @@ class Interpreter:
                 raise MiniMatlabError('statement %r' % k)
         except MiniMatlabError as e:
             if 'line' not in str(e):
-                raise MiniMatlabError('line %s: %s' % (s[-1], e))
+                raise type(e)('line %s: %s' % (s[-1], e))
             raise
 
     # ---- assignment
@@ -761,8 +851,25 @@ class Interpreter:
             env[node[1]] = val
         elif k == 'field':
             base = self._eval_or_none(node[1], env)
+            if base is None or isinstance(base, MStruct):
+                base = MStruct() if base is None else _copy_value(base)
+                base.f[node[2]] = val
+                self.assign(node[1], base, env)
+                return
             if not isinstance(base, MObject):
                 raise MiniMatlabError('field assignment on a non-object')
+            setter = self.find_method(base.cls, 'set.' + node[2])
+            key = (id(base), 'set.' + node[2])
+            if setter is not None and key not in self._in_accessor:
+                self._in_accessor.add(key)
+                try:
+                    out = self.call_function(setter, [base, val], 1 if setter['outs'] else 0)
+                finally:
+                    self._in_accessor.discard(key)
+                if setter['outs']:                          # value class: obj = set.p(obj, v)
+                    base = out[0]
+                self.assign(node[1], base, env)
+                return
             if node[2] not in base.props:
                 raise MiniMatlabError('no property %r' % node[2])
             base.props[node[2]] = val
@@ -857,11 +964,30 @@ class Interpreter:
                 out.append(v)
         return out
 
+    def _super_call(self, ref, args, nargout, env):
+        """`obj@Super(args)` inside a constructor runs the superclass constructor on the object under construction;
+        `method@Super(obj, args)` calls the superclass's version of an overridden method."""
+        _, left, sup = ref
+        if sup not in self.classes:
+            raise MiniMatlabError('unknown superclass %r' % sup)
+        if left in env and isinstance(env[left], MObject):
+            ctor = self.classes[sup]['methods'].get(sup)
+            if ctor is None:
+                return []
+            env[left] = self.call_function(ctor, args, 1, preset={ctor['outs'][0]: env[left]})[0]
+            return []
+        m = self.find_method(self.classes[sup], left)
+        if m is None:
+            raise MiniMatlabError('%s has no method %r' % (sup, left))
+        return self.call_function(m, args, nargout)
+
     # ---- expressions
     def eval_multi(self, node, env, nargout):
         """Evaluate a call-like expression asking for `nargout` outputs; anything else yields one value."""
         if node[0] == 'index':
             base = node[1]
+            if base[0] == 'superref':
+                return self._super_call(base, self._args(node[2], env), nargout, env)
             if base[0] == 'id' and base[1] not in env:
                 args = self._args(node[2], env)
                 return self.call(base[1], args, nargout, env)
@@ -937,11 +1063,24 @@ class Interpreter:
             base = self.eval(node[1], env)
             name = node[2]
             if isinstance(base, MObject):
+                getter = self.find_method(base.cls, 'get.' + name)
+                key = (id(base), 'get.' + name)
+                if getter is not None and key not in self._in_accessor:
+                    self._in_accessor.add(key)
+                    try:
+                        return self.call_function(getter, [base], 1)[0]
+                    finally:
+                        self._in_accessor.discard(key)
                 if name in base.props:
                     return base.props[name]
-                if name in base.cls['methods']:
-                    return BoundMethod(base, base.cls['methods'][name])
+                m = self.find_method(base.cls, name)
+                if m is not None:
+                    return BoundMethod(base, m)
                 raise MiniMatlabError('no property or method %r of %s' % (name, base.cls['name']))
+            if isinstance(base, MStruct):
+                if name not in base.f:
+                    raise MiniMatlabError('reference to non-existent field %r' % name)
+                return base.f[name]
             if isinstance(base, StructArray):
                 vals = [to_matlab(getattr(it, name)) for it in base.items]
                 return vals[0] if len(vals) == 1 else CSList(vals)
