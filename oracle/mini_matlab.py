@@ -53,7 +53,7 @@ _KEYWORDS = {'if', 'elseif', 'else', 'end', 'for', 'while', 'switch', 'case', 'o
 _NUM = re.compile(r'(\d+\.?\d*([eE][+-]?\d+)?|\.\d+([eE][+-]?\d+)?)')
 _ID = re.compile(r'[A-Za-z_]\w*')
 _OPS = ['...', '==', '~=', '<=', '>=', '&&', '||', '.*', './', '.^', ".'", '+', '-', '*', '/', '^', '<', '>', '=', '~',
-        '&', '|', ':', '(', ')', '[', ']', ',', ';', '.', '@']
+        '&', '|', ':', '(', ')', '[', ']', ',', ';', '.', '@', '{', '}']
 
 
 class Tok:
@@ -453,6 +453,9 @@ class Parser:
             self.expect(')')
             self.mdepth = saved
             return ('paren', e)
+        if tok.kind == 'OP' and tok.val == '{':
+            self.expect('}')                                # only the empty cell, as in struct('f', {}) -> 0x0 struct array
+            return ('emptycell',)
         if tok.kind == 'OP' and tok.val == '[':
             saved, self.mdepth = self.mdepth, 1
             rows, row = [], []
@@ -501,6 +504,10 @@ class StructArray:
         self.items = list(items)
 
 
+class EmptyCell:
+    pass
+
+
 class CSList:
     def __init__(self, vals):
         self.vals = vals
@@ -538,7 +545,7 @@ def to_matlab(v):
     """Python value -> interpreter value."""
     if v is None:
         return np.zeros((0, 0))
-    if isinstance(v, (MObject, StructArray, PyObj, str, BoundMethod, MStruct)):
+    if isinstance(v, (MObject, StructArray, PyObj, str, BoundMethod, MStruct, EmptyCell)):
         return v
     if isinstance(v, np.ndarray) and v.dtype == np.uint64:
         return v.reshape(1, 1).copy() if v.ndim < 2 else v.copy()
@@ -650,6 +657,12 @@ class Interpreter:
     def _struct(*args):
         if len(args) % 2:
             raise MiniMatlabError('struct: field names and values come in pairs')
+        if any(isinstance(v, EmptyCell) for v in args[1::2]):           # struct('a', {}, 'b', {}): an empty struct array
+            if not all(isinstance(v, EmptyCell) for v in args[1::2]):
+                raise MiniMatlabError('struct: cell-array values are supported only as {}')
+            sa = StructArray([])
+            sa.fields = list(args[0::2])
+            return sa
         return MStruct({args[i]: args[i + 1] for i in range(0, len(args), 2)})
 
     @staticmethod
@@ -849,6 +862,23 @@ class Interpreter:
         k = node[0]
         if k == 'id':
             env[node[1]] = val
+        elif k == 'field' and node[1][0] == 'index' and isinstance(self._eval_or_none(node[1][1], env), StructArray):
+            # lm(k).f = v on a struct array: grows it, new elements get every known field as []
+            from types import SimpleNamespace
+            sa = self._eval_or_none(node[1][1], env)
+            i = self._index_arg(node[1][2][0], env)
+            if len(node[1][2]) != 1 or i.size != 1:
+                raise MiniMatlabError('struct-array assignment takes one scalar index')
+            fields = list(getattr(sa, 'fields', [])) or (sorted(vars(sa.items[0])) if sa.items else [])
+            if node[2] not in fields:
+                fields.append(node[2])
+            items = [SimpleNamespace(**{f: getattr(it, f, np.zeros((0, 0))) for f in fields}) for it in sa.items]
+            while len(items) <= int(i[0]):
+                items.append(SimpleNamespace(**{f: np.zeros((0, 0)) for f in fields}))
+            setattr(items[int(i[0])], node[2], val)
+            out = StructArray(items)
+            out.fields = fields
+            self.assign(node[1][1], out, env)
         elif k == 'field':
             base = self._eval_or_none(node[1], env)
             if base is None or isinstance(base, MStruct):
@@ -1010,6 +1040,8 @@ class Interpreter:
             return np.array([[node[1]]])
         if k == 'str':
             return node[1]
+        if k == 'emptycell':
+            return EmptyCell()
         if k == 'paren':
             v = self.eval(node[1], env)
             if isinstance(v, CSList):

@@ -2,8 +2,10 @@
 """Turn the outputs of matlab/run_reference_fixture.m into the missing pin of the oracle:
     python tests/golden/compare_reference_fixture.py [tests/golden/ref_outputs]
 For every case directory found: x at every checkpoint, final x / P / s and the landmark count after every step, as the
-UNMODIFIED reference produced them, against what oracle/dense_literal.py produced for the same inputs
-(tests/golden/<case>.npz).  Bar: 1e-9 relative (north star), landmark counts and signatures identical."""
+UNMODIFIED reference produced them under MATLAB / Octave, against tests/golden/refrun_<case>.npz -- the same source text
+executed on the same inputs by oracle/mini_matlab.py with restated built-ins, which oracle/dense_literal.py reproduces to
+1e-12 (tests/test_oracle_cpu.py).  Agreement therefore pins what is still open: MathWorks' built-ins.
+Bar: 1e-9 relative (north star), landmark counts and signatures identical."""
 import os
 import sys
 
@@ -11,7 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
-from tests.golden_util import CASES, load, rel       # noqa: E402
+from tests.golden_util import CASES, rel       # noqa: E402
 
 
 def _csv(path):
@@ -19,7 +21,7 @@ def _csv(path):
 
 
 def compare_case(name, out_dir, tol=1e-9):
-    g = load(name)
+    g = dict(np.load(os.path.join(HERE, 'refrun_%s.npz' % name)))
     d = os.path.join(out_dir, name)
     res = {}
     x = _csv(os.path.join(d, 'x_final.csv')).reshape(-1)
@@ -36,9 +38,7 @@ def compare_case(name, out_dir, tol=1e-9):
         got = xs[i][~np.isnan(xs[i])]
         cp = max(cp, rel(got, want) if got.size == want.size else np.inf)
     res['x_checkpoints'] = cp
-    off = np.concatenate([[0], np.cumsum(g['obs_counts'])])
-    appends = np.array([(g['actions'][off[t]:off[t + 1]] < 0).sum() for t in range(len(g['obs_counts']))])
-    res['landmark_counts_identical'] = bool(np.array_equal(nl, np.cumsum(appends)))
+    res['landmark_counts_identical'] = bool(np.array_equal(nl, g['n_landmarks']))
     res['pinned'] = bool(res['x_final'] <= tol and res['P_final'] <= tol and cp <= tol and res['s_identical'] and res['landmark_counts_identical'])
     return res
 

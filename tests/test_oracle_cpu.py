@@ -429,17 +429,18 @@ def test_f_motion_model_matches_the_oracle():
 def test_reference_witness_roundtrip_and_pin_if_present(tmp_path):
     """matlab/run_reference_fixture.m runs the UNMODIFIED reference on tests/golden/ref_inputs and writes CSVs;
     tests/golden/compare_reference_fixture.py turns them into the pin of the oracle.  (a) The exported inputs are the
-    golden inputs bit for bit; (b) the comparer accepts the oracle's own outputs written in the script's format (so a
+    inputs of the reference-text run (refrun_*.npz: a first frame the reference can run) bit for bit; (b) the comparer accepts the oracle's own outputs written in the script's format (so a
     format slip cannot fake a mismatch); (c) if somebody has run the script under MATLAB/Octave and dropped the outputs
     into tests/golden/ref_outputs, they must match the oracle to 1e-9 -- that is the reference pin."""
     import os
     from tests.golden import compare_reference_fixture as C
     here = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
     for name in G.CASES:
-        g = G.load(name)
+        g = dict(np.load(os.path.join(here, 'refrun_%s.npz' % name)))       # the in-domain worlds (make_reference_run.py)
+        assert int(g['obs_counts'][0]) == 1 and int(g['n_table'][0]) == 1   # a first frame the reference can run
         d = os.path.join(here, 'ref_inputs', name)
         assert open(os.path.join(d, 'class.txt')).read().strip() == G.CASES[name]
-        for key in ('u', 'obs_rows', 'table_loc'):
+        for key in ('u', 'obs_rows', 'table_loc', 'obs_counts', 'n_table', 'table_index', 'checkpoint_steps'):
             a = np.genfromtxt(os.path.join(d, key + '.csv'), delimiter=',').reshape(np.asarray(g[key]).shape)
             assert np.array_equal(a, g[key]), (name, key)
         out = tmp_path / name
@@ -447,8 +448,7 @@ def test_reference_witness_roundtrip_and_pin_if_present(tmp_path):
         wr = lambda fn, M: np.savetxt(str(out / fn), np.atleast_2d(M), delimiter=',', fmt='%.17g')
         wr('x_final.csv', g['x_final']); wr('P_final.csv', g['P_final']); wr('s_final.csv', g['s_final'])
         wr('x_checkpoints.csv', g['x_checkpoints'])
-        off = np.concatenate([[0], np.cumsum(g['obs_counts'])])
-        wr('n_landmarks.csv', np.cumsum([(g['actions'][off[t]:off[t + 1]] < 0).sum() for t in range(len(g['obs_counts']))]))
+        wr('n_landmarks.csv', g['n_landmarks'])
         r = C.compare_case(name, str(tmp_path))
         assert r['pinned'] and r['x_final'] == 0.0 and r['P_final'] == 0.0, r
     real = os.path.join(here, 'ref_outputs')
@@ -715,6 +715,28 @@ def test_oracle_ellipses_match_the_reference_plot_text(name):
         X = cx + np.cos(arc) * ax * np.cos(t) - np.sin(arc) * ay * np.sin(t)
         Y = cy + np.sin(arc) * ax * np.cos(t) + np.cos(arc) * ay * np.sin(t)
         assert max(np.abs(X - c[k, 0]).max(), np.abs(Y - c[k, 1]).max()) <= 1e-12 * scale, (name, k)
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference'), reason='the reference checkout is not on this machine')
+def test_witness_stub_drives_the_reference_text():
+    """matlab/RefFixtureStub.m -- the landmark_list stand-in matlab/run_reference_fixture.m hands to the unmodified
+    reference under MATLAB / Octave -- executed from its own text (struct array built with lm(k).f = v, wrapped in
+    struct('landmark', lm)) and read by the reference's own expressions (EKF_SLAM_UC.m:113,123): the run reproduces
+    refrun_uc_nearest_N8_seed7.npz bit for bit, so the witness's duck typing is what the reference expects."""
+    from oracle.mini_matlab import ReferenceFilter, to_matlab
+    from tests import golden_util as GU
+    g = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_uc_nearest_N8_seed7.npz')))
+    r = ReferenceFilter('/root/reference', 'EKF_SLAM_UC')
+    r.it.load_file(os.path.join(os.path.dirname(GU.GOLDEN), os.pardir, 'matlab', 'RefFixtureStub.m'))
+    off = np.concatenate([[0], np.cumsum(g['obs_counts'])])
+    for t in range(len(g['obs_counts'])):
+        nt = int(g['n_table'][t])
+        stub = r.it.construct('RefFixtureStub', [to_matlab(g['obs_rows'][off[t]:off[t + 1]].reshape(-1, 3)),
+                                                 to_matlab(g['table_index'][:nt].astype(np.float64).reshape(-1, 1)),
+                                                 to_matlab(g['table_loc'][:nt].reshape(-1, 2))])
+        r.predict(g['u'][t])
+        r._method('measure', np.zeros((0, 0)), g['u'][t], stub)
+    assert np.array_equal(r.x, g['x_final']) and np.array_equal(r.P, g['P_final']) and np.array_equal(r.s, g['s_final'].ravel())
 
 
 def test_oracle_matches_the_reference_free_functions():
