@@ -421,6 +421,7 @@ class Parser:
             elif tok.kind == 'OP' and tok.val == '(' and not (self.mdepth > 0 and tok.sp):
                 self.next()
                 saved, self.mdepth = self.mdepth, 0
+                self.idepth = getattr(self, 'idepth', 0) + 1
                 args = []
                 while not self.at(')'):
                     if self.at(':') and self.peek(1).val in (',', ')'):
@@ -431,6 +432,7 @@ class Parser:
                         self.next()
                 self.expect(')')
                 self.mdepth = saved
+                self.idepth -= 1
                 a = ('index', a, args)
             elif tok.kind == 'OP' and tok.val == '.' and self.peek(1).kind == 'ID' and not tok.sp:
                 self.next(); a = ('field', a, self.next().val)
@@ -447,6 +449,8 @@ class Parser:
             return ('str', tok.val)
         if tok.kind == 'ID':
             return ('id', tok.val)
+        if tok.kind == 'KW' and tok.val == 'end' and getattr(self, 'idepth', 0) > 0:
+            return ('end',)                                 # last index of the dimension it stands in
         if tok.kind == 'OP' and tok.val == '(':
             saved, self.mdepth = self.mdepth, 0
             e = self.parse_expr()
@@ -471,6 +475,9 @@ class Parser:
                     continue
                 if nt.kind == 'OP' and nt.val == ',':
                     self.next()
+                    continue
+                if nt.kind == 'OP' and nt.val == '~' and self.peek(1).kind == 'OP' and self.peek(1).val in (',', ']'):
+                    self.next(); row.append(('tilde',))     # [~, order] = sort(v): an output nobody keeps
                     continue
                 row.append(self.parse_expr())
             if row:
@@ -591,17 +598,20 @@ def _num(v):
 class Interpreter:
     def __init__(self, stubs=None):
         self.classes = {}
+        self._end_stack = []
         self._in_accessor = set()        # (object, accessor) pairs being served: inside get.p / set.p the property is plain
         self.functions = {}              # function files / local functions of a script, by name
         self.builtins = {
             'length': lambda a: float(max(a.shape)) if isinstance(a, np.ndarray) and a.size else 0.0,
-            'numel': lambda a: float(a.size),
+            'numel': lambda a: float(len(a.items)) if isinstance(a, StructArray) else float(a.size),
             'isempty': lambda a: (a.size == 0) if isinstance(a, np.ndarray) else (len(a.items) == 0 if isinstance(a, StructArray) else False),
             'sqrt': lambda a: np.sqrt(_num(a)),
             'abs': lambda a: np.abs(_num(a)),
             'cosd': lambda a: self._ew(MC.cosd, a),
             'sind': lambda a: self._ew(MC.sind, a),
-            'atan2d': lambda y, x: np.array([[MC.atan2d(float(_num(y).ravel()[0]), float(_num(x).ravel()[0]))]]),
+            'atan2d': lambda y, x: np.array([[MC.atan2d(float(_num(y).ravel()[0]), float(_num(x).ravel()[0]))]])
+                                   if _num(y).size == 1 and _num(x).size == 1 else
+                                   np.vectorize(MC.atan2d, otypes=[np.float64])(_num(y), _num(x)),
             'wrapTo360': lambda a: self._ew(MC.wrapTo360, a),
             'cos': lambda a: np.cos(_num(a)),
             'sin': lambda a: np.sin(_num(a)),
@@ -612,6 +622,15 @@ class Interpreter:
             'max': lambda a, b=None: np.max(_num(a)) if b is None else np.maximum(_num(a), _num(b)),
             'min': lambda a, b=None: np.min(_num(a)) if b is None else np.minimum(_num(a), _num(b)),
             'struct': self._struct,
+            'mod': lambda a, b: np.mod(_num(a), _num(b)),
+            'sum': lambda a, d=None: (np.sum(_num(a)) if min(_num(a).shape) == 1 else np.sum(_num(a), axis=0, keepdims=True)) if d is None
+                                     else np.sum(_num(a), axis=int(_num(d).ravel()[0]) - 1, keepdims=True),
+            'any': lambda a: bool(np.any(_num(a) != 0)),
+            'all': lambda a: bool(np.all(_num(a) != 0)),
+            'double': lambda a: _num(a).astype(np.float64),
+            'trace': lambda a: float(np.trace(_num(a))),
+            'fprintf': lambda *a: None,
+            'sort': None,                # two outputs: handled in call()
             'isfield': lambda st, name: isinstance(st, MStruct) and name in st.f,
             'reshape': self._reshape,
             'error': self._error,
@@ -763,6 +782,18 @@ class Interpreter:
             if nargout <= 1:
                 return [np.array([[float(shp[0]), float(shp[1])]])]
             return [np.array([[float(shp[0])]]), np.array([[float(shp[1])]])]
+        if name == 'sort':
+            a = _num(args[0])
+            if min(a.shape) > 1:
+                raise MiniMatlabError('sort: vectors only')
+            order = np.argsort(a.ravel(order='F'), kind='stable')
+            vals = a.ravel(order='F')[order].reshape(a.shape)
+            return [vals, (order + 1.0).reshape(a.shape)][:max(nargout, 1)]
+        if name == 'find' and len(args) == 2:
+            hit = self._find(args[0])
+            n = int(_num(args[1]).ravel()[0])
+            flat = hit.ravel()[:n]
+            return [flat.reshape(1, -1) if hit.shape[0] <= 1 else flat.reshape(-1, 1)]
         if name == 'eig':
             # MathWorks built-in (LAPACK): a symmetric input gives ascending eigenvalues and orthonormal vectors (dsyev),
             # anything else goes through the general solver; [V,D] = eig(A) returns D as a diagonal matrix.
@@ -862,6 +893,31 @@ class Interpreter:
         k = node[0]
         if k == 'id':
             env[node[1]] = val
+        elif k == 'tilde':
+            pass
+        elif k == 'index' and isinstance(val, MStruct) and isinstance(self._eval_or_none(node[1], env), StructArray):
+            # lm(end + 1) = struct(...): one element of a struct array
+            from types import SimpleNamespace
+            sa = self._eval_or_none(node[1], env)
+            self._end_stack.append(len(sa.items))
+            try:
+                i = self._index_arg(node[2][0], env)
+            finally:
+                self._end_stack.pop()
+            if len(node[2]) != 1 or i.size != 1 or int(i[0]) > len(sa.items):
+                raise MiniMatlabError('struct-array assignment takes one scalar index, at most one past the end')
+            fields = list(getattr(sa, 'fields', [])) or (sorted(vars(sa.items[0])) if sa.items else sorted(val.f))
+            if sorted(fields) != sorted(val.f):
+                raise MiniMatlabError('subscripted assignment between dissimilar structures')
+            items = list(sa.items)
+            item = SimpleNamespace(**{f: _copy_value(val.f[f]) for f in fields})
+            if int(i[0]) == len(items):
+                items.append(item)
+            else:
+                items[int(i[0])] = item
+            out = StructArray(items)
+            out.fields = fields
+            self.assign(node[1], out, env)
         elif k == 'field' and node[1][0] == 'index' and isinstance(self._eval_or_none(node[1][1], env), StructArray):
             # lm(k).f = v on a struct array: grows it, new elements get every known field as []
             from types import SimpleNamespace
@@ -910,7 +966,7 @@ class Interpreter:
                 cur = np.zeros((0, 0))
             if not isinstance(cur, np.ndarray):
                 raise MiniMatlabError('indexed assignment on a non-array')
-            idx = [self._index_arg(a, env) for a in node[2]]
+            idx = self._index_args(cur, node[2], env)
             self.assign(node[1], self._index_assign(cur, idx, val), env)
         else:
             raise MiniMatlabError('cannot assign to %r' % k)
@@ -919,6 +975,21 @@ class Interpreter:
         if node[0] == 'id' and node[1] not in env:
             return None
         return self.eval(node, env)
+
+    def _index_args(self, arr, nodes, env):
+        """Index arguments of arr(...), with `end` standing for the last index of its position."""
+        out = []
+        for j, a in enumerate(nodes):
+            if isinstance(arr, StructArray):
+                last = len(arr.items)
+            else:
+                last = arr.size if len(nodes) == 1 else (arr.shape[j] if j < 2 else 1)
+            self._end_stack.append(last)
+            try:
+                out.append(self._index_arg(a, env))
+            finally:
+                self._end_stack.pop()
+        return out
 
     def _index_arg(self, a, env):
         if a[0] == 'colon_all':
@@ -1042,6 +1113,10 @@ class Interpreter:
             return node[1]
         if k == 'emptycell':
             return EmptyCell()
+        if k == 'end':
+            if not self._end_stack:
+                raise MiniMatlabError('`end` outside an index')
+            return np.array([[float(self._end_stack[-1])]])
         if k == 'paren':
             v = self.eval(node[1], env)
             if isinstance(v, CSList):
@@ -1135,11 +1210,14 @@ class Interpreter:
                     raise MiniMatlabError('method returned nothing')
                 return out[0]
             if isinstance(bv, StructArray):
-                idx = self._index_arg(node[2][0], env)
+                idx = self._index_args(bv, node[2][:1], env)[0]
                 return StructArray([bv.items[i] for i in idx])
             if isinstance(bv, np.ndarray):
-                idx = [self._index_arg(a, env) for a in node[2]]
+                idx = self._index_args(bv, node[2], env)
                 return self._index(bv, idx)
+            if isinstance(bv, str):                         # name(1): characters of a string
+                idx = self._index_arg(node[2][0], env)
+                return ''.join(bv[i] for i in idx)
             raise MiniMatlabError('cannot index a %r' % type(bv))
         raise MiniMatlabError('expression %r' % k)
 

@@ -208,6 +208,26 @@ class MatlabHost:
         for f in CLASS_FILES:
             self.it.load_file(os.path.join(MATLAB_DIR, f))
 
+    def load(self, *files):
+        for f in files:
+            self.it.load_file(os.path.join(MATLAB_DIR, f))
+        return self
+
+    def with_rng(self, seed=0):
+        """rng / rand / randn served by NumPy (not MATLAB's streams: runs are reproducible here, not comparable with MATLAB's)
+        and fprintf recorded in self.printed as (format, args...)."""
+        rs = np.random.RandomState(seed)
+
+        def dims(a):
+            d = [int(v.ravel()[0]) for v in a]
+            return (1, 1) if not d else ((d[0], d[0]) if len(d) == 1 else tuple(d))
+        self.printed = []
+        self.it.builtins.update({'rng': lambda sd, kind=None: rs.seed(int(sd.ravel()[0]) % (2 ** 32)),
+                                 'rand': lambda *a: rs.random_sample(dims(a)),
+                                 'randn': lambda *a: rs.standard_normal(dims(a)),
+                                 'fprintf': lambda *a: self.printed.append(a)})
+        return self
+
     def new(self, cls, *args):
         return self.it.construct(cls, [to_matlab(a) for a in args])
 

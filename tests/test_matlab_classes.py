@@ -163,6 +163,50 @@ def test_matlab_landmark_seam():
         H.run("LM = Landmark('RANSAC');")
 
 
+def test_example_sim_script_runs_end_to_end():
+    """matlab/example_sim.m -- the runnable stand-in for the reference's example.m / test_SLAM.m -- executed
+    as written: SyntheticSensor.m behind Landmark.m, EKF_SLAM_UC over the gateway, 1000 steps of predict / measure.  Random
+    numbers come from NumPy, so only the outcome is checked: most of the 20 landmarks mapped, the estimated pose on the
+    true one, the filter destroyed at the end."""
+    gw = OracleGateway()
+    H = MatlabHost(gw).load('SyntheticSensor.m').with_rng(1)
+    ws = H.run(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'matlab', 'example_sim.m')).read())
+    fmt, nmap, ex, ey, eth, tx, ty, tth = [v if isinstance(v, str) else float(v.ravel()[0]) for v in H.printed[0]]
+    assert fmt.startswith('%d landmarks mapped') and 15 <= nmap <= 20
+    assert np.hypot(ex - tx, ey - ty) < 0.3 and abs((eth - tth + 180) % 360 - 180) < 3.0
+    assert H.printed[1][0].startswith('trace(P_rr)') and float(H.printed[1][1].ravel()[0]) > 0
+    assert gw.calls.count('predict') == 1000 and gw.calls[-1] == 'destroy' and not gw.filters
+    idx = np.array([float(e.index.ravel()[0]) for e in H.get(ws['sensor'], 'landmark').items])
+    assert np.array_equal(idx, np.arange(1, idx.size + 1))            # numbered in order of first sighting (RANSAC.m:262)
+
+
+def test_synthetic_sensor_prefix_mode_drives_the_known_correspondence_class():
+    """EKF_SLAM updates slot ii with row ii (EKF_SLAM.m:123), so its sensor must emit landmarks 1..m in index order
+    (SyntheticSensor.prefix): 360 steps -- one lap -- through matlab/EKF_SLAM.m, every frame's third column is 1..k."""
+    gw = OracleGateway()
+    H = MatlabHost(gw).load('SyntheticSensor.m').with_rng(2)
+    ws = H.run("""
+sensor = SyntheticSensor(12, 7);
+sensor.prefix = true;
+LM = Landmark('SYNTH', sensor);
+slam = EKF_SLAM(struct('capacity_landmarks', 12));
+ok = true;
+for t = 1:360
+    u = sensor.step();
+    slam.predict(u);
+    slam.measure([], u, LM);
+    k = size(slam.observed, 1);
+    if k > 0
+        ok = ok && all(slam.observed(:, 3) == (1:k)');
+    end
+end
+x = slam.x; N = slam.numLandmarks(); pose = sensor.pose;
+""")
+    assert ws['ok'][0, 0] and 3 <= ws['N'][0, 0] <= 12
+    x, pose = ws['x'].ravel(), ws['pose'].ravel()
+    assert np.hypot(x[0] - pose[0], x[1] - pose[1]) < 0.3 and abs((x[2] - pose[2] + 180) % 360 - 180) < 3.0
+
+
 def test_matlab_constructor_without_a_device_raises_ecuda():
     """Through the compiled gateway: EKF_SLAM() on a machine without a CUDA device stops with ekfslam:ECUDA -- no CPU path."""
     import torch
