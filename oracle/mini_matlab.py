@@ -436,6 +436,13 @@ class Parser:
                 a = ('index', a, args)
             elif tok.kind == 'OP' and tok.val == '.' and self.peek(1).kind == 'ID' and not tok.sp:
                 self.next(); a = ('field', a, self.next().val)
+            elif tok.kind == 'OP' and tok.val == '.' and self.peek(1).kind == 'OP' and self.peek(1).val == '(' and not tok.sp:
+                self.next(); self.next()                    # o.(name): the field whose name is the value of an expression
+                saved, self.mdepth = self.mdepth, 0
+                e = self.parse_expr()
+                self.expect(')')
+                self.mdepth = saved
+                a = ('dynfield', a, e)
             elif tok.kind == 'OP' and tok.val == '@' and not tok.sp and a[0] == 'id' and self.peek(1).kind == 'ID':
                 self.next(); a = ('superref', a[1], self.next().val)     # h@Base(...) / method@Base(h, ...)
             else:
@@ -821,6 +828,8 @@ class Interpreter:
             if isinstance(fv.obj, PyObj):
                 out = fv.func(*[self._to_python(a) for a in args])
                 return [to_matlab(out)]
+            if fv.obj is None:                              # static method
+                return self.call_function(fv.func, list(args), nargout)
             return self.call_function(fv.func, [fv.obj] + list(args), nargout)
         raise MiniMatlabError('value is not callable')
 
@@ -1166,6 +1175,16 @@ class Interpreter:
             if not rows:
                 return np.zeros((0, 0))
             return np.vstack(rows)
+        if k == 'dynfield':
+            name = self.eval(node[2], env)
+            if not isinstance(name, str):
+                raise MiniMatlabError('dynamic field name must be a string')
+            return self.eval(('field', node[1], name), env)
+        if k == 'field' and node[1][0] == 'id' and node[1][1] not in env and node[1][1] in self.classes:
+            m = self.find_method(self.classes[node[1][1]], node[2])                 # ClassName.method: a static method
+            if m is None:
+                raise MiniMatlabError('%s has no method %r' % (node[1][1], node[2]))
+            return BoundMethod(None, m)
         if k == 'field':
             base = self.eval(node[1], env)
             name = node[2]

@@ -170,6 +170,84 @@ class OracleGateway:
     v_sync = v_flush
 
 
+class OracleBatchGateway(OracleGateway):
+    """The batch_* verbs (matlab/ekfslam_mex.c: n_filters objects of one reference class stepped in lock step) answered by
+    n_filters oracle objects, behind the gateway's own size checks."""
+
+    def __call__(self, nargout, verb, *a):
+        if not verb.startswith('batch_'):
+            return super().__call__(nargout, verb, *a)
+        self.calls.append(verb)
+        if verb == 'batch_create':
+            if len(a) < 4:
+                raise GatewayError('ekfslam:EINVAL: batch_create needs variant, n_filters, max_obs, max_table')
+            variant, nf, mo, mt = (int(v.ravel()[0]) for v in a[:4])
+            cap = 1024 if len(a) < 5 else int(a[4].f.get('capacity_landmarks', np.array([[1024.0]])).ravel()[0])
+            fl = [(O.EKF_SLAM_UC if variant == 1 else O.EKF_SLAM)() for _ in range(nf)]
+            for o in fl:
+                o.capacity = cap
+            self._next += 8
+            self.filters[self._next] = SimpleNamespace(f=fl, nf=nf, mo=mo, mt=mt)
+            return [np.array([[self._next]], dtype=np.uint64)]
+        if not a or not (isinstance(a[0], np.ndarray) and a[0].dtype == np.uint64 and a[0].size == 1):
+            raise GatewayError('ekfslam:EINVAL: batch handle must be a uint64 scalar')
+        b = self.filters.get(int(a[0].ravel()[0]))
+        if b is None:
+            raise GatewayError('ekfslam:EINVAL: batch handle is null or destroyed')
+        a = a[1:]
+        if verb == 'batch_destroy':
+            del self.filters[[k for k, v in self.filters.items() if v is b][0]]
+            return []
+        if verb == 'batch_sync':
+            return []
+        if verb == 'batch_step':
+            if len(a) < 7:
+                raise GatewayError('ekfslam:EINVAL: batch_step needs u, observed_LL, counts, loc, index, do_predict, do_measure')
+            U, obs, counts, loc, idx = a[:5]
+            do_p, do_m = (float(v.ravel()[0]) != 0.0 for v in a[5:7])
+            T = idx.size
+            if T > b.mt:
+                raise GatewayError('ekfslam:EINVAL: landmark table has %d entries, max_table is %d' % (T, b.mt))
+            counts = self._vec(counts, b.nf, 'counts').astype(int)
+            U = self._vec(U, 2 * b.nf, 'u').reshape((2, b.nf), order='F')
+            obs = self._vec(obs, 3 * b.mo * b.nf, 'observed_LL').reshape((b.mo, 3, b.nf), order='F')
+            idx = self._vec(idx, T, 'index table')
+            loc = self._vec(loc, 2 * T, 'loc table').reshape((T, 2), order='F')
+            table = [SimpleNamespace(index=int(i), loc=l.copy()) for i, l in zip(idx, loc)]
+            act = np.zeros((b.mo, b.nf))
+            for f, o in enumerate(b.f):
+                if do_p:
+                    o.predict(U[:, f])
+                if do_m:
+                    before = len(o.chosen)
+                    o.measure(None, U[:, f], _Stub(obs[:counts[f], :, f].copy(), table))
+                    got = [(1 if w == 'update' else -1) * int(i) for w, i in o.chosen[before:]]
+                    act[:len(got), f] = got
+            return [act]
+        if verb == 'batch_n_landmarks':
+            return [np.array([[(o.x.size - 3) // 2] for o in b.f], dtype=np.float64)]
+        if verb == 'batch_poses':
+            return [np.array([o.x[:3] for o in b.f]).T.copy()]
+        if verb in ('batch_get_x', 'batch_get_s', 'batch_get_P'):
+            if not a:
+                raise GatewayError("ekfslam:EINVAL: verb '%s' needs a filter index" % verb)
+            f = int(a[0].ravel()[0])
+            if f < 1 or f > b.nf:
+                raise GatewayError('ekfslam:EINVAL: filter index %d outside 1..%d' % (f, b.nf))
+            o = b.f[f - 1]
+            return [{'x': o.x.reshape(1, -1), 's': np.asarray(o.s, dtype=np.float64).reshape(-1, 1), 'P': o.P}[verb[10]].copy()]
+        if verb == 'batch_set_state':
+            if len(a) < 4:
+                raise GatewayError('ekfslam:EINVAL: batch_set_state needs f, x, P, s')
+            f = int(a[0].ravel()[0])
+            if f < 0 or f > b.nf:
+                raise GatewayError('ekfslam:EINVAL: filter index %d outside 1..%d' % (f, b.nf))
+            for o in (b.f if f == 0 else [b.f[f - 1]]):
+                self.v_set_state(0, o, *a[1:4])
+            return []
+        raise GatewayError("ekfslam:EINVAL: unknown verb '%s'" % verb)
+
+
 class MexGateway:
     """The compiled gateway (tests/test_matlab_shim.Mex): interpreter values <-> the stand-in mxArray runtime."""
     wants_nargout = True

@@ -17,7 +17,7 @@ import pytest
 from oracle import dense_literal as O
 from oracle.mini_matlab import MiniMatlabError
 from tests import golden_util as GU
-from tests.matlab_host import GatewayError, MatlabHost, MexGateway, OracleGateway
+from tests.matlab_host import GatewayError, MatlabHost, MexGateway, OracleBatchGateway, OracleGateway
 
 
 class Sensor:
@@ -205,6 +205,60 @@ x = slam.x; N = slam.numLandmarks(); pose = sensor.pose;
     assert ws['ok'][0, 0] and 3 <= ws['N'][0, 0] <= 12
     x, pose = ws['x'].ravel(), ws['pose'].ravel()
     assert np.hypot(x[0] - pose[0], x[1] - pose[1]) < 0.3 and abs((x[2] - pose[2] + 180) % 360 - 180) < 3.0
+
+
+def test_matlab_batch_class_steps_filters_in_lock_step():
+    """matlab/EKFSLAM_B200_Batch.m (what a MATLAB loop over n_filters EKF_SLAM_UC objects calling predict / measure,
+    SLAM.m:110,116, becomes) executed from its text over the batch_* verbs: three filters with their own odometry noise and
+    observation subsets against three oracle objects driven one by one; shapes as the reference's (x 1 x n, s N x 1)."""
+    g = GU.load('uc_nearest_N8_seed7')
+    T, nf, mo = 40, 3, 5
+    off = np.concatenate([[0], np.cumsum(g['obs_counts'])])
+    rng = np.random.default_rng(5)
+    U = g['u'][:T, :, None] * (1 + 0.01 * rng.standard_normal((T, 2, nf)))
+    OBS = np.zeros((T, mo, 3, nf)); CNT = np.zeros((T, nf))
+    for t in range(T):
+        rows = g['obs_rows'][off[t]:off[t + 1]]
+        for f in range(nf):
+            keep = rows if f == 0 or t == 0 else rows[:max(1, len(rows) - f)]     # filter f misses the last f rows
+            OBS[t, :len(keep), :, f] = keep; CNT[t, f] = len(keep)
+    table = [SimpleNamespace(index=int(i), loc=l.copy()) for i, l in zip(g['table_index'], g['table_loc'])]
+    sens = SimpleNamespace(landmark=table)
+    gw = OracleBatchGateway()
+    H = MatlabHost(gw).load('EKFSLAM_B200_Batch.m')
+    # the per-step inputs are 3-D / per-step slices: hand them in through small Python accessors
+    at = lambda t: int(np.ravel(t)[0]) - 1
+    acc = SimpleNamespace(U=lambda t: U[at(t)], O=lambda t: OBS[at(t)], C=lambda t: CNT[at(t)].reshape(-1, 1))
+    ws = H.run("""
+b = EKFSLAM_B200_Batch('EKF_SLAM_UC', nf, struct('capacity_landmarks', 20, 'max_obs', mo));
+LM = Landmark('SYNTH', sens);
+for t = 1:T
+    last = b.step(acc.U(t), acc.O(t), acc.C(t), LM);
+end
+N = b.nLandmarks(); poses = b.poses(); x2 = b.x(2); s2 = b.s(2); P3 = b.P(3);
+b.setState(1, x2, b.P(2), s2);
+x1 = b.x(1);
+b.sync();
+delete(b);
+""", nf=float(nf), mo=float(mo), T=float(T), sens=sens, acc=acc)
+    want = []
+    for f in range(nf):
+        o = O.EKF_SLAM_UC()
+        for t in range(T):
+            o.predict(U[t, :, f])
+            before = len(o.chosen)
+            o.measure(None, U[t, :, f], GU.Stub(OBS[t, :int(CNT[t, f]), :, f], table))
+            last = [(1 if w == 'update' else -1) * int(i) for w, i in o.chosen[before:]]
+        want.append((o, last))
+    assert np.array_equal(ws['N'].ravel(), [(o.x.size - 3) // 2 for o, _ in want])
+    assert ws['poses'].shape == (3, nf) and all(np.array_equal(ws['poses'][:, f], want[f][0].x[:3]) for f in range(nf))
+    assert ws['x2'].shape == (1, want[1][0].x.size) and np.array_equal(ws['x2'].ravel(), want[1][0].x)
+    assert ws['s2'].shape == (want[1][0].s.size, 1) and np.array_equal(ws['P3'], want[2][0].P)
+    assert ws['last'].shape == (mo, nf)
+    for f in range(nf):
+        assert np.array_equal(ws['last'][:len(want[f][1]), f], want[f][1]) and not ws['last'][len(want[f][1]):, f].any()
+    assert np.array_equal(ws['x1'], ws['x2'])                         # setState(1, ...) took filter 2's state
+    assert gw.calls[0] == 'batch_create' and gw.calls[-1] == 'batch_destroy' and not gw.filters
 
 
 def test_matlab_constructor_without_a_device_raises_ecuda():
