@@ -322,6 +322,15 @@ class Parser:
             if tok.val == 'return':
                 self.next()
                 return ('return', tok.line)
+            if tok.val == 'while':
+                self.next()
+                cond = self.parse_expr()
+                body = self.parse_block(('end',))
+                self.expect('end')
+                return ('while', cond, body, tok.line)
+            if tok.val in ('break', 'continue'):
+                self.next()
+                return (tok.val, tok.line)
             raise MiniMatlabError('line %d: statement %r not supported' % (tok.line, tok.val))
         if tok.kind == 'ID' and self.peek(1).kind == 'ID' and self.peek(1).sp and \
                 (self.peek(2).kind in ('NL', 'EOF') or (self.peek(2).kind == 'OP' and self.peek(2).val in (';', ','))):
@@ -545,6 +554,14 @@ class _Return(Exception):
     pass
 
 
+class _Break(Exception):
+    pass
+
+
+class _Continue(Exception):
+    pass
+
+
 def _copy_value(v):
     if isinstance(v, np.ndarray):
         return v.copy()
@@ -606,12 +623,14 @@ class Interpreter:
     def __init__(self, stubs=None):
         self.classes = {}
         self._end_stack = []
+        self.path, self._loaded, self._files, self._fids = [], set(), [], {}
         self._in_accessor = set()        # (object, accessor) pairs being served: inside get.p / set.p the property is plain
         self.functions = {}              # function files / local functions of a script, by name
         self.builtins = {
             'length': lambda a: float(max(a.shape)) if isinstance(a, np.ndarray) and a.size else 0.0,
             'numel': lambda a: float(len(a.items)) if isinstance(a, StructArray) else float(a.size),
-            'isempty': lambda a: (a.size == 0) if isinstance(a, np.ndarray) else (len(a.items) == 0 if isinstance(a, StructArray) else False),
+            'isempty': lambda a: (a.size == 0) if isinstance(a, np.ndarray) else
+                                 (len(a.items) == 0 if isinstance(a, StructArray) else (len(a) == 0 if isinstance(a, str) else False)),
             'sqrt': lambda a: np.sqrt(_num(a)),
             'abs': lambda a: np.abs(_num(a)),
             'cosd': lambda a: self._ew(MC.cosd, a),
@@ -636,7 +655,6 @@ class Interpreter:
             'all': lambda a: bool(np.all(_num(a) != 0)),
             'double': lambda a: _num(a).astype(np.float64),
             'trace': lambda a: float(np.trace(_num(a))),
-            'fprintf': lambda *a: None,
             'sort': None,                # two outputs: handled in call()
             'isfield': lambda st, name: isinstance(st, MStruct) and name in st.f,
             'reshape': self._reshape,
@@ -652,6 +670,7 @@ class Interpreter:
             'false': lambda: np.array([[False]]),
             'pi': lambda: np.array([[np.pi]]),
         }
+        self._io = self._io_builtins()
         for k, v in (stubs or {}).items():
             self.builtins[k] = v
 
@@ -678,6 +697,119 @@ class Interpreter:
     def _eye(self, *args):
         r, c = self._dims(args)
         return np.eye(r, c)
+
+    # ---- files, paths, formatted text: what a driver script needs around the arithmetic
+    @staticmethod
+    def _sprintf(fmt, args):
+        """MATLAB's fprintf / sprintf rule: the arguments are flattened (column-major) and the format is reused until they
+        are used up; with no argument left for a conversion the output stops there; escapes are processed in the format."""
+        import re
+        flat = []
+        for a in args:
+            if isinstance(a, str):
+                flat.append(a)
+            else:
+                flat.extend(_num(a).ravel(order='F').tolist())
+        fmt = fmt.replace('\\n', '\n').replace('\\t', '\t').replace('%%', '\0')
+        parts = re.split(r'(%[-+ 0#]*\d*(?:\.\d+)?[dfegs])', fmt)
+        nconv = sum(1 for p in parts if p.startswith('%'))
+        out, i, first = [], 0, True
+        while first or i < len(flat):
+            first = False
+            for p in parts:
+                if p.startswith('%'):
+                    if i >= len(flat):
+                        return ''.join(out).replace('\0', '%')
+                    v = flat[i]; i += 1
+                    if p.endswith('s'):
+                        out.append(p % (v if isinstance(v, str) else ('%g' % v)))
+                    elif p.endswith('d'):
+                        out.append((p % int(v)) if float(v) == int(v) else (p[:-1] + 'e') % v)
+                    else:
+                        out.append(p % float(v))
+                else:
+                    out.append(p)
+            if nconv == 0:
+                break
+        return ''.join(out).replace('\0', '%')
+
+    def _io_builtins(self):
+        import os
+
+        def fopen(path, mode='r'):
+            try:
+                fh = open(path, mode)
+            except OSError:
+                return -1.0
+            fid = 3 + len(self._fids)
+            self._fids[fid] = fh
+            return float(fid)
+
+        def fid_of(v):
+            return int(_num(v).ravel()[0])
+
+        def fclose(fid):
+            self._fids.pop(fid_of(fid)).close()
+
+        def fprintf(*a):
+            if a and isinstance(a[0], np.ndarray):
+                self._fids[fid_of(a[0])].write(self._sprintf(a[1], a[2:]))
+            else:
+                self.printed.append(self._sprintf(a[0], a[1:]))
+
+        def dir_(path):
+            from types import SimpleNamespace
+            names = ['.', '..'] + sorted(os.listdir(path))
+            sa = StructArray([SimpleNamespace(name=n, isdir=os.path.isdir(os.path.join(path, n))) for n in names])
+            sa.fields = ['name', 'isdir']
+            return sa
+
+        def which(name):
+            if name in self.builtins or name in self._io:
+                return 'built-in'
+            return self._resolve(name) or ''
+
+        def addpath(d, where=None):
+            if d in self.path:
+                self.path.remove(d)
+            if where == '-end':
+                self.path.append(d)
+            else:
+                self.path.insert(0, d)                      # in front, as MATLAB does
+
+        def mfilename(kind=None):
+            f = next((x for x in reversed(self._files) if x), None)
+            if f is None:
+                return ''
+            return os.path.splitext(f)[0] if kind == 'fullpath' else os.path.splitext(os.path.basename(f))[0]
+
+        def assert_(cond, fmt=None, *a):
+            if not _truth(cond if isinstance(cond, np.ndarray) else np.array([[bool(cond)]])):
+                raise MiniMatlabError('assertion failed: ' + (self._sprintf(fmt, a) if fmt else ''))
+
+        def strfind(a, b):
+            hits = [i + 1.0 for i in range(len(a) - len(b) + 1) if a[i:i + len(b)] == b] if b else []
+            return np.array([hits]) if hits else np.zeros((0, 0))
+
+        def sscanf(txt, fmt):
+            if fmt != '%f':
+                raise MiniMatlabError("sscanf: only '%f'")
+            return np.array([float(t) for t in txt.split()]).reshape(-1, 1)
+
+        def fread(fid, n, kind):
+            if kind != 'uint8=>char':
+                raise MiniMatlabError("fread: only 'uint8=>char'")
+            return self._fids[fid_of(fid)].read()
+
+        self.printed = []
+        return {'fopen': fopen, 'fclose': fclose, 'fprintf': fprintf, 'fread': fread, 'sscanf': sscanf, 'dir': dir_,
+                'which': which, 'addpath': addpath, 'mfilename': mfilename, 'assert': assert_, 'strfind': strfind,
+                'fullfile': lambda *p: os.path.join(*p), 'fileparts': lambda p: os.path.dirname(p),
+                'exist': lambda p, kind=None: 7.0 if os.path.isdir(p) else (2.0 if os.path.isfile(p) else 0.0),
+                'mkdir': lambda p: os.makedirs(p, exist_ok=True), 'strtrim': lambda t: t.strip(),
+                'fileread': lambda p: open(p).read(), 'strrep': lambda t, a, b: t.replace(a, b),
+                'nan': lambda *a: np.full(self._dims(a) if a else (1, 1), np.nan),
+                'feval': lambda name, *a: self.call(name, list(a), 1, {})[0]}
 
     @staticmethod
     def _struct(*args):
@@ -744,7 +876,27 @@ class Interpreter:
 
     def load_file(self, path):
         with open(path) as f:
-            return self.load_source(f.read())
+            src = f.read()
+        before = set(self.functions)
+        out = self.load_source(src)
+        for name in (out if isinstance(out, list) else []):
+            self.functions[name]['file'] = path
+        if isinstance(out, str):
+            for m in self.classes[out]['methods'].values():
+                m['file'] = path
+        return out
+
+    def _resolve(self, name):
+        """`name` on the search path (addpath): the first <dir>/<name>.m, loaded on first use as MATLAB does."""
+        import os
+        for d in self.path:
+            f = os.path.join(d, name + '.m')
+            if os.path.isfile(f):
+                if f not in self._loaded:
+                    self._loaded.add(f)
+                    self.load_file(f)
+                return f
+        return None
 
     # ---- objects and calls
     def construct(self, name, args):
@@ -760,6 +912,13 @@ class Interpreter:
         return obj
 
     def call_function(self, f, args, nargout, preset=None):
+        self._files.append(f.get('file'))
+        try:
+            return self._call_function(f, args, nargout, preset)
+        finally:
+            self._files.pop()
+
+    def _call_function(self, f, args, nargout, preset=None):
         if len(args) > len(f['params']):
             raise MiniMatlabError('%s: too many input arguments' % f['name'])
         env = dict(preset or {})
@@ -815,12 +974,18 @@ class Interpreter:
             m = self.find_method(args[0].cls, name)
             if m is not None:
                 return self.call_function(m, args, nargout)
+        if name not in self.builtins and name not in self._io and self.path and self._resolve(name):
+            if name not in self.classes and name not in self.functions:
+                raise MiniMatlabError('%s.m does not define %s' % (name, name))
+            return self.call(name, args, nargout, env)
         if name in self.builtins:
             fn = self.builtins[name]
             if getattr(fn, 'wants_nargout', False):        # a stand-in for a MEX file: fn(nargout, *args) -> list of outputs
                 return [to_matlab(o) for o in fn(nargout, *args)]
             out = fn(*args)
             return [to_matlab(out)]
+        if name in self._io:
+            return [to_matlab(self._io[name](*args))]
         raise MiniMatlabError('undefined function or variable %r' % name)
 
     def call_value(self, fv, args, nargout):
@@ -875,7 +1040,24 @@ class Interpreter:
                 for j in range(rng.shape[1] if rng.size else 0):
                     col = rng[:, j:j + 1]
                     env[s[1]] = col.copy() if col.shape[0] > 1 else col.reshape(1, 1).copy()
-                    self.exec_block(s[3], env)
+                    try:
+                        self.exec_block(s[3], env)
+                    except _Continue:
+                        continue
+                    except _Break:
+                        break
+            elif k == 'while':
+                while _truth(self.eval(s[1], env)):
+                    try:
+                        self.exec_block(s[2], env)
+                    except _Continue:
+                        continue
+                    except _Break:
+                        break
+            elif k == 'break':
+                raise _Break()
+            elif k == 'continue':
+                raise _Continue()
             elif k == 'switch':
                 subj = self.eval(s[1], env)
                 for val, body in s[2]:
@@ -1136,7 +1318,10 @@ class Interpreter:
                 return env[node[1]]
             return self.call(node[1], [], 1, env)[0]
         if k == 'transpose':
-            return _num(self.eval(node[1], env)).T.copy()
+            v = self.eval(node[1], env)
+            if isinstance(v, str):                          # char arrays live here as Python strings, orientation-free
+                return v
+            return _num(v).T.copy()
         if k == 'un':
             a = self.eval(node[2], env)
             if node[1] == '-':
@@ -1266,6 +1451,12 @@ class Interpreter:
 
     @staticmethod
     def _binop(op, a, b):
+        if op in ('==', '~=') and isinstance(a, str) and isinstance(b, str):
+            if len(a) != len(b) and 1 not in (len(a), len(b)):
+                raise MiniMatlabError('char arrays of different lengths compared with ==')
+            n = max(len(a), len(b))
+            eq = np.array([[(a[i % len(a)] == b[i % len(b)]) for i in range(n)]])
+            return eq if op == '==' else ~eq
         if op in ('==', '~=') and (isinstance(a, str) or isinstance(b, str)):
             raise MiniMatlabError('string comparison with == is not supported')
         a, b = _num(a), _num(b)

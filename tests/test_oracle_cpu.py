@@ -739,6 +739,28 @@ def test_witness_stub_drives_the_reference_text():
     assert np.array_equal(r.x, g['x_final']) and np.array_equal(r.P, g['P_final']) and np.array_equal(r.s, g['s_final'].ravel())
 
 
+@pytest.mark.skipif(not os.path.isdir('/root/reference'), reason='the reference checkout is not on this machine')
+def test_witness_script_runs_end_to_end_on_the_reference_checkout(tmp_path):
+    """matlab/run_reference_fixture.m executed as written (addpath of the reference checkout -- its own EKF_SLAM.m,
+    EKF_SLAM_UC.m, Correspondence.m and RANSAC.m are found on the path and loaded unmodified --, the assert that EKF_SLAM
+    resolves into the checkout, dir / fopen / sscanf / fprintf('%.17g') CSV handling, RefFixtureStub) on
+    tests/golden/ref_inputs; tests/golden/compare_reference_fixture.py then reads what it wrote and finds the refrun
+    vectors bit for bit: the CSV round trip loses nothing and the script is ready for whoever has MATLAB or Octave.
+    (Run by oracle/mini_matlab.py, this pins nothing new -- the outputs are NOT committed as tests/golden/ref_outputs.)"""
+    from oracle.mini_matlab import Interpreter
+    from tests.golden import compare_reference_fixture as C
+    from tests import golden_util as GU
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    it = Interpreter()
+    it.load_file(os.path.join(root, 'matlab', 'run_reference_fixture.m'))
+    it.call('run_reference_fixture', ['/root/reference', os.path.join(GU.GOLDEN, 'ref_inputs'), str(tmp_path)], 0, {})
+    assert len(it.printed) == len(GU.CASES) and all('landmarks ->' in line for line in it.printed)
+    assert any(f.startswith('/root/reference/') and f.endswith('RANSAC.m') for f in it._loaded)      # the reference's own constructor ran
+    for name in GU.CASES:
+        r = C.compare_case(name, str(tmp_path))
+        assert r['pinned'] and r['x_final'] == 0.0 and r['P_final'] == 0.0 and r['x_checkpoints'] == 0.0, (name, r)
+
+
 def test_oracle_matches_the_reference_free_functions():
     """append.m:1-27 and example.m:24-45 (predict, f) -- the free-function forms SURVEY 8(a) cites beside the class methods --
     executed from their own source (tests/golden/refrun_functions.npz): the oracle's append / predict / f give the same
