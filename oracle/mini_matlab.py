@@ -870,6 +870,8 @@ class Interpreter:
         if node['kind'] == 'functions':
             self.functions.update(node['functions'])
             return sorted(node['functions'])
+        if node['super'] not in (None, 'handle') and node['super'] not in self.classes and self.path:
+            self._resolve(node['super'])                    # a superclass found on the search path
         node['handle'] = node['super'] == 'handle' or (node['super'] in self.classes and self.classes[node['super']]['handle'])
         self.classes[node['name']] = node
         return node['name']
@@ -1467,7 +1469,8 @@ class Interpreter:
         if op == '.*':
             return a * b
         if op == './':
-            return a / b
+            with np.errstate(divide='ignore', invalid='ignore'):
+                return a / b
         if op == '*':
             if a.size == 1 or b.size == 1:
                 return a * b
@@ -1476,7 +1479,8 @@ class Interpreter:
             return a @ b
         if op == '/':
             if b.size == 1:
-                return a / b
+                with np.errstate(divide='ignore', invalid='ignore'):      # x/0 is Inf in MATLAB, silently
+                    return a / b
             raise MiniMatlabError('matrix right division is not supported')
         if op in ('^', '.^'):
             if op == '^' and a.size > 1:

@@ -261,6 +261,96 @@ delete(b);
     assert gw.calls[0] == 'batch_create' and gw.calls[-1] == 'batch_destroy' and not gw.filters
 
 
+def _ros_stand_ins(g):
+    """What the reference's SLAM.m needs from ROS and the toolboxes around the filter (SLAM.m:23-24,73-74,85-92,107,118-139),
+    fed from a golden world: odometry poses integrated from its odometry, one laser 'message' per step, and RANSAC() --
+    the extractor behind the reference's Landmark.m -- answering with that step's rows and table."""
+    import math
+    NS = SimpleNamespace
+    off = np.concatenate([[0], np.cumsum(g['obs_counts'])])
+    table = [NS(index=int(i), loc=l.copy()) for i, l in zip(g['table_index'], g['table_loc'])]
+    st = NS(t=-1, pose=np.zeros(3))
+
+    class Extractor:
+        @property
+        def landmark(self):
+            return table[:int(g['n_table'][st.t])]
+
+        def getLandmark(self, laserdata, x):
+            return g['obs_rows'][off[laserdata.t]:off[laserdata.t + 1]]
+
+        def plot(self, x, observed):
+            pass
+
+    def receive(topic):
+        if topic == '/scan':
+            st.t += 1
+            u = g['u'][st.t]
+            th = st.pose[2] + u[1]
+            st.pose = np.array([st.pose[0] + u[0] * math.cos(math.radians(th)), st.pose[1] + u[0] * math.sin(math.radians(th)), th])
+            return NS(t=st.t)
+        yaw = math.radians(st.pose[2])
+        return NS(Pose=NS(Pose=NS(Position=NS(X=st.pose[0], Y=st.pose[1]),
+                                  Orientation=NS(W=math.cos(yaw / 2), X=0.0, Y=0.0, Z=math.sin(yaw / 2)))))
+
+    wrap = lambda a: (a + np.pi) % (2 * np.pi) - np.pi
+    noop = lambda *a: None
+    return {'rossubscriber': lambda topic: topic, 'receive': receive, 'RANSAC': lambda: Extractor(),
+            'quat2eul': lambda q: np.array([[math.atan2(2 * (q[0, 0] * q[0, 3] + q[0, 1] * q[0, 2]), 1 - 2 * (q[0, 2] ** 2 + q[0, 3] ** 2)), 0.0, 0.0]]),
+            'rad2deg': lambda a: np.degrees(a), 'deg2rad': lambda a: np.radians(a), 'angdiff': lambda a, b: wrap(b - a),
+            'readCartesian': lambda msg: np.array([[1.0, 0.0], [0.0, 1.0], [1.0, 1.0]]),
+            'ones': lambda r, c: np.ones((int(r.ravel()[0]), int(c.ravel()[0]))),
+            'scatter': noop, 'axis': noop, 'hold': noop, 'drawRobot': noop, 'plot': noop}
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference'), reason='the reference checkout is not on this machine')
+@pytest.mark.parametrize('cls,world', [('EKF_SLAM', 'known_quirk_N20'), ('EKF_SLAM_UC', 'uc_nearest_N8_seed7')])
+def test_reference_caller_drives_either_filter_unmodified(cls, world, tmp_path):
+    """The drop-in claim at the reference's production call site: SLAM.m (constructor :21-40, runSlam :70-145 with
+    predict at :110, measure at :116, plot at :139) and Landmark.m, both UNMODIFIED from the checkout, run once over the
+    reference's own filter classes and once with this repo's EKFSLAM_B200_Base.m / EKF_SLAM.m / EKF_SLAM_UC.m /
+    Correspondence.m copied in front of them on the search path (what a maintainer would do) -- ROS and toolbox calls
+    around the filter served by stand-ins.  Same odometry derived by runSlam, same x, P, s (gateway answered by the
+    oracle on the CPU; the reference side is its own text): <= 1e-12."""
+    import shutil
+    from oracle.mini_matlab import Interpreter, Parser, tokenize, to_matlab
+    from tests.matlab_host import MATLAB_DIR
+    g = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_%s.npz' % world)))
+    for f in ('EKFSLAM_B200_Base.m', 'EKF_SLAM.m', 'EKF_SLAM_UC.m', 'Correspondence.m'):
+        shutil.copy(os.path.join(MATLAB_DIR, f), str(tmp_path / f))
+    src = """
+s = SLAM(cls);
+Us = zeros(T, 2);
+for t = 1:T
+    s.runSlam();
+    Us(t, :) = s.u;
+end
+x = s.slam.x; P = s.slam.P; sg = s.slam.s;
+"""
+    res = {}
+    for who in ('reference', 'ours'):
+        stubs = _ros_stand_ins(g)
+        gw = OracleGateway()
+        stubs['ekfslam_mex'] = gw
+        it = Interpreter(stubs=stubs)
+        it.path = ['/root/reference'] if who == 'reference' else [str(tmp_path), '/root/reference']
+        p = Parser(tokenize(src))
+        stmts = []
+        p.skip_nl()
+        while p.peek().kind != 'EOF':
+            stmts.append(p.parse_statement()); p.skip_nl()
+        ws = {'T': to_matlab(float(len(g['obs_counts']))), 'cls': cls}
+        it.exec_block(stmts, ws)
+        res[who] = ws
+        loaded = {os.path.basename(f): os.path.dirname(f) for f in it._loaded}
+        assert loaded['SLAM.m'] == loaded['Landmark.m'] == '/root/reference'
+        assert loaded[cls + '.m'] == ('/root/reference' if who == 'reference' else str(tmp_path))
+        assert (len(gw.calls) > 0) == (who == 'ours')
+    a, b = res['ours'], res['reference']
+    assert np.array_equal(a['Us'], b['Us']) and a['x'].shape == b['x'].shape == (1, 3 + 2 * int(g['n_landmarks'][-1]))
+    assert GU.rel(a['x'], b['x']) <= 1e-12 and GU.rel(a['P'], b['P']) <= 1e-12 and np.array_equal(a['sg'], b['sg'])
+
+
 def test_matlab_constructor_without_a_device_raises_ecuda():
     """Through the compiled gateway: EKF_SLAM() on a machine without a CUDA device stops with ekfslam:ECUDA -- no CPU path."""
     import torch
