@@ -79,7 +79,29 @@ def association_case(ref_dir):
         new, idx = it.call_function(f, [c, to_matlab(z), to_matlab(np.diag(Rd)), to_matlab(a['x']), to_matlab(a['P']),
                                         to_matlab(a['s'].reshape(-1, 1))], 2)
         out.append([int(bool(new.ravel()[0])), int(idx.ravel()[0])])
-    return dict(x=a['x'], P=a['P'], s=a['s'], z=a['z'], Rdiag=a['Rdiag'], mode_a=np.array(out, dtype=np.int32))
+    # Mode B: the reference's own alternative score, Correspondence.m:74 `%log_likelihood(kk)=position_cost+signiture_cost;`,
+    # which ships commented out.  The text is taken from the checkout and changed IN MEMORY by exactly two characters
+    # -- the `%` in front of line 74 goes, line 75 gets one -- and everything else (position_cost at :69 with the dense
+    # H_k*P*H_k', the gate, the strict-< running minimum) is executed as written.  All signatures equal so that the
+    # Mahalanobis term decides; s_thresh = 9.21 as in association_N12.npz.
+    lines = open(os.path.join(ref_dir, 'Correspondence.m')).read().split('\n')
+    i74 = next(i for i, l in enumerate(lines) if l.strip() == '%log_likelihood(kk)=position_cost+signiture_cost;')
+    assert lines[i74 + 1].strip() == 'log_likelihood(kk)=signiture_cost;'
+    lines[i74] = lines[i74].replace('%', '', 1)
+    lines[i74 + 1] = lines[i74 + 1].replace('log_likelihood', '%log_likelihood', 1)
+    itb = Interpreter()
+    itb.load_source('\n'.join(lines))
+    cb = itb.construct('Correspondence', [to_matlab(1e-11), to_matlab(9.21), 'EKF_SLAM_UC'])
+    fb = cb.cls['methods']['estimateCorrespondence']
+    outb = []
+    sB = np.ones((len(a['s']), 1))
+    for z, Rd in zip(a['z'], a['Rdiag']):
+        zB = z.copy(); zB[2] = 1.0
+        new, idx = itb.call_function(fb, [cb, to_matlab(zB), to_matlab(np.diag(Rd)), to_matlab(a['x']), to_matlab(a['P']),
+                                          to_matlab(sB)], 2)
+        outb.append([int(bool(new.ravel()[0])), int(idx.ravel()[0])])
+    return dict(x=a['x'], P=a['P'], s=a['s'], z=a['z'], Rdiag=a['Rdiag'], mode_a=np.array(out, dtype=np.int32),
+                mode_b=np.array(outb, dtype=np.int32))
 
 
 def functions_case(ref_dir, seed=3, cases=6):

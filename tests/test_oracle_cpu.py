@@ -682,6 +682,27 @@ def test_oracle_matches_the_reference_text_run(name):
     assert GU.rel(o.P, g['P_final']) <= 1e-12
 
 
+@pytest.mark.parametrize('name', REFRUN_CASES)
+def test_structured_oracle_matches_the_reference_text_run(name):
+    """oracle/structured.c -- the O(n^2) form that checks the 10k-landmark runs, where the dense restatement cannot go --
+    against what the reference's own text computed (refrun_*.npz): landmark counts and s exactly, x at every checkpoint,
+    final x and P to 1e-11 (a different grouping of the same products than the reference's dense algebra)."""
+    from oracle import structured as S
+    from tests import golden_util as GU
+    g = dict(np.load(os.path.join(GU.GOLDEN, 'refrun_%s.npz' % name)))
+    o = getattr(S, GU.CASES[name])(capacity_landmarks=24)
+    cps = {int(s): i for i, s in enumerate(g['checkpoint_steps'])}
+    for t, u, stub in GU.steps(g):
+        o.predict(u)
+        o.measure(None, u, stub)
+        assert (o.x.size - 3) // 2 == int(g['n_landmarks'][t]), (name, t)
+        if (t + 1) in cps:
+            want = g['x_checkpoints'][cps[t + 1]]
+            assert GU.rel(o.x, want[~np.isnan(want)]) <= 1e-11, (name, t)
+    assert np.array_equal(np.asarray(o.s, dtype=np.float64).ravel(), g['s_final'].ravel())
+    assert GU.rel(o.x, g['x_final']) <= 1e-11 and GU.rel(o.P, g['P_final']) <= 1e-11
+
+
 def test_oracle_association_matches_the_reference_text_run():
     """Correspondence.estimateCorrespondence as shipped (Correspondence.m:28-88, signature score :75), executed from its
     own source on a fixed state with a duplicated signature (first minimum wins, :81) and unseen signatures (new landmark)."""
@@ -695,6 +716,17 @@ def test_oracle_association_matches_the_reference_text_run():
         got.append([int(bool(new)), int(idx)])
     assert np.array_equal(np.array(got, dtype=np.int32), a['mode_a'])
     assert 0 < int(a['mode_a'][:, 0].sum()) < len(got)
+    # mode B: the reference's own commented-out score (Correspondence.m:74) enabled in memory, everything else as written
+    # (make_reference_run.py): position cost + signature cost, all signatures equal, gate 9.21
+    cb = O.Correspondence(1e-11, 9.21, 'EKF_SLAM_UC', position_cost_in_score=True)
+    gotb = []
+    for z, Rd in zip(a['z'], a['Rdiag']):
+        zB = z.copy(); zB[2] = 1.0
+        new, idx = cb.estimateCorrespondence(zB, np.diag(Rd), a['x'], a['P'], np.ones(len(a['s'])))
+        gotb.append([int(bool(new)), int(idx)])
+    assert np.array_equal(np.array(gotb, dtype=np.int32), a['mode_b'])
+    assert np.array_equal(a['mode_b'], GU.load('association_N12')['modeB'])       # what the GPU association test is held to
+    assert len(set(a['mode_b'][:, 1])) >= 10                                        # the Mahalanobis term really decides
 
 
 @pytest.mark.parametrize('name', REFRUN_CASES)
