@@ -364,6 +364,57 @@ def test_matlab_constructor_without_a_device_raises_ecuda():
         H.run("slam = EKF_SLAM_UC();")
 
 
+class _MexContract:
+    """tests/test_matlab_shim.Mex as MexGateway sees it, without the compiled gateway: accepts exactly what Mex._to_mx can
+    marshal (str, Handle, dict of scalars, float arrays), hands the C side's view (2-D float64, uint64 scalar handle,
+    struct) to the oracle-backed gateway and returns what Mex._from_mx would (Handle, bool, str, 2-D float arrays)."""
+
+    def __init__(self, gw):
+        from tests.test_matlab_shim import Handle
+        from oracle.mini_matlab import MStruct
+        self.gw, self.Handle, self.MStruct = gw, Handle, MStruct
+
+    def __call__(self, *args, nlhs=1):
+        conv = []
+        for a in args:
+            if isinstance(a, str):
+                conv.append(a)
+            elif isinstance(a, self.Handle):
+                conv.append(np.array([[a.v]], dtype=np.uint64))
+            elif isinstance(a, dict):
+                conv.append(self.MStruct({k: np.array([[float(v)]]) for k, v in a.items()}))
+            else:
+                assert isinstance(a, np.ndarray) and a.dtype == np.float64, type(a)
+                conv.append(np.asfortranarray(np.atleast_2d(a)))
+        out = self.gw(nlhs, *conv)[:nlhs]
+        back = []
+        for o in out:
+            if isinstance(o, np.ndarray) and o.dtype == np.uint64:
+                back.append(self.Handle(int(o.ravel()[0])))
+            elif isinstance(o, (bool, np.bool_)):
+                back.append(bool(o))
+            elif isinstance(o, (float, int)):
+                back.append(np.array([[float(o)]]))
+            else:
+                back.append(np.atleast_2d(np.asarray(o, dtype=np.float64)))
+        return back
+
+
+@pytest.mark.parametrize('name', ['known_quirk_N20', 'uc_nearest_N8_seed7'])
+def test_mex_gateway_adapter_marshals_what_the_classes_send(name):
+    """MexGateway (interpreter values <-> tests/test_matlab_shim.Mex) checked on the CPU against the contract of Mex
+    (_MexContract): the driver of the opt-in GPU test below runs through it unchanged and gives the oracle's results."""
+    g = GU.load(name)
+    mg = MexGateway.__new__(MexGateway)
+    from tests.test_matlab_shim import Handle, MexError
+    mg.mex, mg.Handle, mg.MexError, mg.calls = _MexContract(OracleGateway()), Handle, MexError, []
+    ws = MatlabHost(mg).run(DRIVER % GU.CASES[name] + "\ndelete(slam);\n", sensor=Sensor(g), U=g['u'], T=float(len(g['obs_counts'])))
+    o = getattr(O, GU.CASES[name])()
+    want = GU.replay(o, g)
+    assert np.array_equal(ws['x'].ravel(), o.x) and np.array_equal(ws['P'], o.P) and np.array_equal(ws['s'].ravel(), o.s)
+    assert np.array_equal(ws['acts'].ravel().astype(np.int32), want) and mg.calls[-1] == 'destroy'
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(os.environ.get('EKF_TEST_MATLAB_CLASSES_GPU') != '1',
                     reason='opt-in (EKF_TEST_MATLAB_CLASSES_GPU=1): written after the GPU budget of round 2 was spent, not yet run on a GPU')
