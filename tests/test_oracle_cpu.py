@@ -703,6 +703,38 @@ def test_structured_oracle_matches_the_reference_text_run(name):
     assert GU.rel(o.x, g['x_final']) <= 1e-11 and GU.rel(o.P, g['P_final']) <= 1e-11
 
 
+@pytest.mark.skipif(not os.path.isdir('/root/reference'), reason='the reference checkout is not on this machine')
+@pytest.mark.parametrize('seed', range(8))
+def test_oracle_matches_the_reference_text_on_random_worlds(seed):
+    """Beyond the four committed worlds: seeded random worlds (5 - 10 landmarks, 2 - 4 observations per frame, 40 steps,
+    some frames empty -- the isempty(observed_LL) path, EKF_SLAM.m:105 -- known-correspondence class on 'prefix' worlds,
+    unknown-correspondence class on 'nearest' worlds), the reference's text executed live against oracle/dense_literal.py:
+    landmark count after every step and s exactly, x and P <= 1e-12 at every 10th step and at the end."""
+    from ekf_slam_b200 import synth
+    from oracle.mini_matlab import ReferenceFilter
+    from tests import golden_util as GU
+    rng = np.random.default_rng(1000 + seed)
+    cls = 'EKF_SLAM' if seed % 2 == 0 else 'EKF_SLAM_UC'
+    w = synth.make_world(N=int(rng.integers(5, 11)), T=40, k=int(rng.integers(2, 5)), seed=77 + seed,
+                         mode='prefix' if cls == 'EKF_SLAM' else 'nearest')
+    empty = set(int(t) for t in rng.choice(np.arange(3, 40), size=4, replace=False))
+    r, o = ReferenceFilter('/root/reference', cls), getattr(O, cls)()
+    for t in range(w.T):
+        rows = w.observed[t]
+        ntab = w.n_table[t]
+        if t == 0:
+            rows, ntab = rows[:1], 1                 # a first frame the reference can run (one new landmark)
+        if t in empty:
+            rows = np.zeros((0, 3))
+        stub = GU.Stub(rows, w.table[:ntab])
+        r.predict(w.u[t]); r.measure(None, w.u[t], stub)
+        o.predict(w.u[t]); o.measure(None, w.u[t], stub)
+        assert r.x.size == o.x.size, (seed, t)
+        if t % 10 == 9 or t == w.T - 1:
+            assert GU.rel(o.x, r.x) <= 1e-12 and GU.rel(o.P, r.P) <= 1e-12, (seed, t)
+    assert np.array_equal(np.asarray(o.s, dtype=np.float64).ravel(), r.s) and o.x.size >= 3 + 2 * 2
+
+
 def test_oracle_association_matches_the_reference_text_run():
     """Correspondence.estimateCorrespondence as shipped (Correspondence.m:28-88, signature score :75), executed from its
     own source on a fixed state with a duplicated signature (first minimum wins, :81) and unseen signatures (new landmark)."""
